@@ -1,0 +1,179 @@
+/* ======================================================================================
+ * b200md.h -- C ABI of libb200md.so, the B200 (sm_100a) device library behind the LAMMPS
+ * `Pair` / `NPair` / `NBin` / `Fix` / `Comm` style classes with suffix `b200`.
+ *
+ * Conventions (modelled on the reference's own device-library precedent, the `ljl_gpu_*`,
+ * `eam_gpu_*` and `lmp_*_device` entry points that src/GPU/pair_lj_cut_gpu.cpp:34-56,
+ * src/GPU/pair_eam_gpu.cpp:36-60 and src/GPU/fix_gpu.cpp:43-51 declare):
+ *   - plain C, opaque context, raw pointers + sizes; no C++/torch types cross the boundary;
+ *   - host arrays are CALLER-owned and may move between calls (LAMMPS re-allocates atom->x on
+ *     any avec->grow), device arrays are LIBRARY-owned and persist across timesteps;
+ *   - every entry point returns an int status (B200MD_OK == 0); b200md_last_error() gives the
+ *     text.  The status values are the three error conditions the reference path raises
+ *     (src/nbin.cpp:143 non-finite coordinate, src/npair_half_bin_atomonly_newton.cpp:109
+ *     neighbor overflow, src/thermo.cpp lost atoms) plus CUDA/NCCL failures.  The C++ glue turns
+ *     a non-zero status into error->one(FLERR,...) like GPU_EXTRA::check_flag does.
+ *   - one context per MPI rank / per GPU, called from the rank's main thread only.
+ *   - per-type tables are the reference's 1-based layout flattened row-major with leading
+ *     dimension (ntypes+1): element [i][j] at index i*(ntypes+1)+j, row/column 0 unused.
+ *   - per-atom host arrays are the reference's: double x[n][3] contiguous (src/memory.h
+ *     create(double**,n,3)), int type[n], tagint(int32, LAMMPS_SMALLBIG) tag[n],
+ *     imageint(int32) image[n].
+ *
+ * There is NO CPU fallback: every call fails with B200MD_ERR_CUDA when no sm_100 device is
+ * usable.
+ * ====================================================================================== */
+#ifndef B200MD_H
+#define B200MD_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200md_ctx b200md_ctx;
+
+enum {
+  B200MD_OK = 0,
+  B200MD_ERR_NONFINITE = 1,  /* "Non-numeric positions - simulation unstable" (src/nbin.cpp:143)           */
+  B200MD_ERR_NEIGH_OVERFLOW = 2, /* "Neighbor list overflow" (src/npair_half_bin_atomonly_newton.cpp:109)  */
+  B200MD_ERR_LOST_ATOMS = 3, /* "Lost atoms" (src/thermo.cpp lost_check)                                   */
+  B200MD_ERR_CUDA = 4,       /* CUDA or NCCL failure, or no usable device                                   */
+  B200MD_ERR_ARG = 5,        /* invalid argument / call order (the reference's error->all on bad input)    */
+  B200MD_ERR_DOMAIN = 6      /* sub-domain thinner than the ghost cutoff in a decomposed dimension         */
+};
+
+#define B200MD_NCCL_ID_BYTES 128
+
+/* ---- lifetime --------------------------------------------------------------------------
+ * replaces lmp_init_device()/lmp_clear_device() (src/GPU/fix_gpu.cpp:43-49,231,242).
+ * nranks>1: one context per rank, `nccl_id` is the B200MD_NCCL_ID_BYTES blob produced by
+ * b200md_nccl_unique_id() on rank 0 and broadcast by the caller (MPI_Bcast / torch.distributed);
+ * this is what replaces the MPI communicator of Comm (src/comm.h:21-170). */
+int b200md_nccl_unique_id(void *id_out);
+int b200md_create(b200md_ctx **out, int device, int nranks, int rank, const void *nccl_id);
+int b200md_destroy(b200md_ctx *ctx);
+const char *b200md_last_error(const b200md_ctx *ctx);
+/* device bytes currently held (Pair::memory_usage(), ljl_gpu_bytes()) */
+double b200md_memory_usage(const b200md_ctx *ctx);
+
+/* ---- domain / units / masses (Domain: src/domain.h; Update::set_units src/update.cpp:145-207) */
+int b200md_set_units(b200md_ctx *ctx, double boltz, double mvv2e, double ftm2v, double nktv2p);
+/* orthogonal box; procgrid as ProcMap::onelevel_grid would return it (src/procmap.cpp:46) with
+ * uniform cuts like CommBrick::setup (src/comm_brick.cpp:191-260).  rank -> grid location is
+ * x-fastest: rank = (iz*py + iy)*px + ix. */
+int b200md_set_box(b200md_ctx *ctx, const double boxlo[3], const double boxhi[3], const int periodic[3],
+                   const int procgrid[3]);
+int b200md_set_mass(b200md_ctx *ctx, int ntypes, const double *mass /* [ntypes+1] */);
+
+/* ---- atoms: Atom / AtomVecAtomic (src/atom.h:70-73, src/atom_vec_atomic.cpp) -------------
+ * upload replaces the per-step host->device casts of the GPU package (lib/gpu/lal_atom.cu:20);
+ * here it happens once, atoms then stay resident.  v and image may be NULL (zeros / 0 image).
+ * Atoms must belong to this rank's sub-domain after periodic wrapping. */
+int b200md_upload_atoms(b200md_ctx *ctx, int n, const double *x, const double *v, const int *type,
+                        const int *tag, const int *image);
+int b200md_nlocal(const b200md_ctx *ctx);
+int b200md_nghost(const b200md_ctx *ctx);
+/* copy owned atoms back (device order; use `tag` to identify).  Any pointer may be NULL.
+ * Mirrors atomKK->sync(Host, X_MASK|V_MASK|F_MASK|...) of the KOKKOS package. */
+int b200md_download_atoms(b200md_ctx *ctx, double *x, double *v, double *f, int *type, int *tag, int *image);
+/* owned + ghost positions and tags (ghosts after owned), for neighbor-list parity checks */
+int b200md_download_all(b200md_ctx *ctx, double *x /*[nall][3]*/, int *tag /*[nall]*/);
+/* refresh positions/velocities of the resident owned atoms from host arrays given in TAG order
+ * is not offered: use b200md_upload_atoms again (forces a rebuild), as a restart does
+ * (src/neighbor.cpp:2297). */
+
+/* ---- pair_style lj/cut : replaces ljl_gpu_init (src/GPU/pair_lj_cut_gpu.cpp:34-38); tables are
+ * what PairLJCut::init_one fills (src/pair_lj_cut.cpp:501-557) */
+int b200md_lj_init(b200md_ctx *ctx, int ntypes, const double *cutsq, const double *lj1, const double *lj2,
+                   const double *lj3, const double *lj4, const double *offset, const double special_lj[4]);
+
+/* ---- pair_style eam : replaces eam_gpu_init (src/GPU/pair_eam_gpu.cpp:36-43); arrays are what
+ * PairEAM::file2array/array2spline produce (src/MANYBODY/pair_eam.cpp:533-765):
+ * frho_spline[nfrho][nrho+1][7], rhor_spline[nrhor][nr+1][7], z2r_spline[nz2r][nr+1][7] flattened,
+ * type2frho[ntypes+1], type2rhor/type2z2r[(ntypes+1)^2]. */
+int b200md_eam_init(b200md_ctx *ctx, int ntypes, int nrho, int nr, double rdrho, double rdr, double rhomax,
+                    double cutforcesq, int nfrho, const double *frho_spline, int nrhor,
+                    const double *rhor_spline, int nz2r, const double *z2r_spline, const int *type2frho,
+                    const int *type2rhor, const int *type2z2r);
+/* stand-alone hosts: PairEAM::coeff + read_file + file2array + array2spline + init_one for funcfl files
+ * (src/MANYBODY/pair_eam.cpp:372-412, 460-526, 533-765, 435-456).  map[1..ntypes] = index into files[] or -1
+ * (type not covered by EAM).  mass_out[1..ntypes] receives the file masses (pair_coeff sets the type mass,
+ * :404), *cutmax_out the force cutoff.  Ends by calling b200md_eam_init. */
+int b200md_eam_init_funcfl(b200md_ctx *ctx, int ntypes, int nfiles, const char *const *files, const int *map,
+                           double *mass_out, double *cutmax_out);
+/* per-atom EAM intermediates of owned atoms, device order (PairEAM::extract / rho, fp members) */
+int b200md_eam_download(b200md_ctx *ctx, double *rho, double *fp);
+
+/* ---- neighbor : Neighbor settings (src/neighbor.cpp:306-695, 2556-2700) ------------------
+ * cutneighsq[(ntypes+1)^2] = (cut_ij + skin)^2, cutneighmax = max; every/delay/check as
+ * `neigh_modify`; binsize <= 0 selects the device default (one bin per cutneighmax). */
+int b200md_neigh_config(b200md_ctx *ctx, int ntypes, const double *cutneighsq, double cutneighmax, double skin,
+                        int every, int delay, int check, double binsize);
+/* Neighbor::decide + check_distance (src/neighbor.cpp:2293-2374): *flag = 1 if a rebuild is due.
+ * Collective over ranks when nranks > 1 (replaces the MPI_Allreduce at :2371). */
+int b200md_neigh_decide(b200md_ctx *ctx, int *flag);
+/* the whole reneighbor branch of Verlet::run (src/verlet.cpp:283-306): Domain::pbc, Comm::exchange,
+ * spatial sort of owned atoms (Atom::sort), Comm::borders, NBin::bin_atoms (counting sort) and
+ * NPair::build.  Collective. */
+int b200md_neigh_build(b200md_ctx *ctx);
+/* the list as the reference exposes it (lammps_neighlist_element_neighbors, src/library.h:224):
+ * numneigh[nlocal]; neighbors = concatenation of each owned atom's list (device-order indices into
+ * owned+ghost, special bits in the top 2 bits).  The device list is a FULL list (both i->j and j->i).
+ * Call with neighbors == NULL to get numneigh and *total only. */
+int b200md_neigh_export(b200md_ctx *ctx, int *numneigh, int *neighbors, int64_t *total);
+int b200md_neigh_stats(b200md_ctx *ctx, int64_t *nbuilds, int64_t *ndanger, int *maxneigh);
+
+/* ---- Comm : CommBrick::forward_comm (src/comm_brick.cpp:538-591) -------------------------
+ * ghost positions from their owners (self copy, peer copy over NVLink/NCCL).  The device list is
+ * full, so the reference's reverse_comm of ghost forces (:598-639) has no device counterpart. */
+int b200md_halo_forward(b200md_ctx *ctx);
+
+/* ---- force : Verlet::force_clear (src/verlet.cpp:376) + Pair::compute ---------------------
+ * PairLJCut::compute (src/pair_lj_cut.cpp:69-139) or PairEAM::compute incl. its internal
+ * forward_comm of fp (src/MANYBODY/pair_eam.cpp:142-328).  eflag/vflag as Integrate::ev_set gives
+ * them; when set, eng_vdwl and virial[6] (xx,yy,zz,xy,xz,yz) of THIS rank are returned like the
+ * Pair members (src/pair.h:41-44).  eng/virial may be NULL when the flags are 0. */
+int b200md_pair_compute(b200md_ctx *ctx, int eflag, int vflag, double *eng_vdwl, double *virial);
+
+/* ---- fix nve : FixNVE::initial_integrate/final_integrate (src/fix_nve.cpp:64-141) ---------
+ * dtv = dt, dtf = 0.5*dt*ftm2v (src/fix_nve.cpp:51-58) */
+int b200md_nve_initial(b200md_ctx *ctx, double dtv, double dtf);
+int b200md_nve_final(b200md_ctx *ctx, double dtf);
+
+/* ---- thermo: ComputeTemp/ComputePressure/ComputePE (src/compute_temp.cpp:72-100,
+ * src/compute_pressure.cpp:228-341, src/compute_pe.cpp:91-100), summed over ranks.
+ * out[0]=pe out[1]=ke out[2]=temp out[3]=press out[4..9]=pressure tensor xx,yy,zz,xy,xz,yz;
+ * uses eng/virial of the most recent b200md_pair_compute with flags set. */
+int b200md_thermo(b200md_ctx *ctx, double natoms_total, double *out);
+
+/* ---- Verlet::setup / Verlet::run (src/verlet.cpp:93-162, 229-360) kept on the device side so
+ * that no O(N) host work remains per step (what VerletB200 calls).  thermo_every as `thermo N`;
+ * energy/virial are tallied on those steps and the last one (Integrate::ev_set,
+ * src/integrate.cpp:138-183). */
+int b200md_setup(b200md_ctx *ctx);
+int b200md_run(b200md_ctx *ctx, int nsteps, double dt, int thermo_every);
+int64_t b200md_timestep(const b200md_ctx *ctx);
+
+/* ---- host-buffer mode: what the stock Verlet loop gets from a pair/fix plugin whose atoms live
+ * on the host, the GPU package's model (x up, f down every step, src/GPU/pair_lj_cut_gpu.cpp:85-118).
+ * One full timestep: uploads x,v (nlocal atoms, device order of the previous call, i.e. the order
+ * b200md_download_atoms reports), runs initial_integrate / [reneighbor] / force / final_integrate,
+ * downloads x,v,f.  Arrays are [nlocal][3]. */
+int b200md_step_host(b200md_ctx *ctx, double dt, int eflag, int vflag, double *x, double *v, double *f,
+                     int *tag, double *eng_vdwl, double *virial);
+
+/* ---- instrumentation: device time per section in ms since the last reset, named like the
+ * reference's Timer (src/timer.h:23-42): [0]=Pair [1]=Neigh [2]=Comm [3]=Modify [4]=Other;
+ * counts kernels launched by this library since the last reset. */
+int b200md_timers(b200md_ctx *ctx, double ms[5], int64_t *kernel_launches, int reset);
+/* CUDA-event time of the most recent pair kernel / neighbor-build kernel launch (ms) */
+int b200md_last_kernel_ms(b200md_ctx *ctx, double *pair_ms, double *neigh_ms);
+/* opt-in per-kernel event timing (adds two event records per launch) */
+int b200md_profile(b200md_ctx *ctx, int on);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

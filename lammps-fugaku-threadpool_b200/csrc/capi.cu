@@ -1,0 +1,703 @@
+// capi.cu -- the C ABI of libb200md.so (include/b200md.h): context lifetime, settings, atom upload /
+// download, pair-style tables, and the device-resident Verlet loop (src/verlet.cpp:93-162, 229-360).
+// No CPU fallback: b200md_create fails with B200MD_ERR_CUDA when no usable sm_100 device exists.
+#include <math.h>
+#include <stdarg.h>
+#include <stdlib.h>
+
+#include <new>
+#include <vector>
+
+#include "ctx.cuh"
+
+int nve_final_initial(b200md_ctx *c, double dtv, double dtf);
+int comm_init(b200md_ctx *c, const void *nccl_id);
+void comm_destroy(b200md_ctx *c);
+
+static char g_err[512] = "no error";
+
+int b200md_fail(b200md_ctx *c, int code, const char *fmt, ...)
+{
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(c ? c->err : g_err, 512, fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+extern "C" const char *b200md_last_error(const b200md_ctx *c) { return c ? c->err : g_err; }
+
+extern "C" int b200md_create(b200md_ctx **out, int device, int nranks, int rank, const void *nccl_id)
+{
+  b200md_ctx *c = nullptr;
+  if (!out) return b200md_fail(c, B200MD_ERR_ARG, "b200md_create: out == NULL");
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return b200md_fail(c, B200MD_ERR_CUDA, "no CUDA device (%s); libb200md has no CPU fallback",
+                       e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+  if (device < 0 || device >= ndev) return b200md_fail(c, B200MD_ERR_ARG, "device %d out of range (%d devices)", device, ndev);
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return b200md_fail(c, B200MD_ERR_CUDA, "cudaGetDeviceProperties failed");
+  if (prop.major != 10)
+    return b200md_fail(c, B200MD_ERR_CUDA, "device %d is sm_%d%d; libb200md is built for sm_100a only", device, prop.major, prop.minor);
+  if (nranks < 1 || rank < 0 || rank >= nranks) return b200md_fail(c, B200MD_ERR_ARG, "bad nranks/rank %d/%d", nranks, rank);
+  if (cudaSetDevice(device) != cudaSuccess) return b200md_fail(c, B200MD_ERR_CUDA, "cudaSetDevice(%d) failed", device);
+  c = new (std::nothrow) b200md_ctx();
+  if (!c) return b200md_fail(c, B200MD_ERR_ARG, "out of host memory");
+  c->device = device;
+  c->nranks = nranks;
+  c->rank = rank;
+  for (int k = 0; k <= B200MD_MAXTYPES; k++) c->mass_h[k] = 0.0;
+  strcpy(c->err, "no error");
+  *out = c;
+  CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  CU(cudaEventCreate(&c->ev0));
+  CU(cudaEventCreate(&c->ev1));
+  CU(cudaMalloc((void **) &c->red_d, 32 * sizeof(double)));
+  CU(cudaMemset(c->red_d, 0, 32 * sizeof(double)));
+  CU(cudaMallocHost((void **) &c->red_h, 32 * sizeof(double)));
+  CU(cudaMalloc((void **) &c->flags_d, 8 * sizeof(int)));
+  CU(cudaMemset(c->flags_d, 0, 8 * sizeof(int)));
+  CU(cudaMallocHost((void **) &c->flags_h, 64 * sizeof(int)));
+  memset(c->flags_h, 0, 64 * sizeof(int));
+  if (nranks > 1) TRY(comm_init(c, nccl_id));
+  return B200MD_OK;
+}
+
+extern "C" int b200md_destroy(b200md_ctx *c)
+{
+  if (!c) return B200MD_OK;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  comm_destroy(c);
+  dev_free(c, c->mass_d); dev_free(c, c->pos); dev_free(c, c->pos_tmp); dev_free(c, c->xhold);
+  for (int k = 0; k < 3; k++) { dev_free(c, c->v[k]); dev_free(c, c->v_tmp[k]); dev_free(c, c->f[k]); }
+  dev_free(c, c->tag); dev_free(c, c->tag_tmp); dev_free(c, c->image); dev_free(c, c->image_tmp);
+  dev_free(c, c->rho); dev_free(c, c->fp); dev_free(c, c->cutneighsq_d);
+  dev_free(c, c->bin_count); dev_free(c, c->bin_start); dev_free(c, c->atom_bin); dev_free(c, c->cell_list);
+  dev_free(c, c->perm); dev_free(c, c->scan_tmp); dev_free(c, c->numneigh); dev_free(c, c->neigh);
+  dev_free(c, c->ghost_src); dev_free(c, c->border_blockcnt); dev_free(c, c->border_total); dev_free(c, c->ghost_dir);
+  dev_free(c, c->partials); dev_free(c, c->stage);
+  if (c->lj.d) cudaFree(c->lj.d);
+  if (c->eam.frho) cudaFree(c->eam.frho);
+  if (c->eam.rhor) cudaFree(c->eam.rhor);
+  if (c->eam.z2r) cudaFree(c->eam.z2r);
+  if (c->eam.rhoA) cudaFree(c->eam.rhoA);
+  if (c->eam.type2frho) cudaFree(c->eam.type2frho);
+  if (c->eam.type2rhor) cudaFree(c->eam.type2rhor);
+  if (c->eam.type2z2r) cudaFree(c->eam.type2z2r);
+  if (c->red_d) cudaFree(c->red_d);
+  if (c->red_h) cudaFreeHost(c->red_h);
+  if (c->flags_d) cudaFree(c->flags_d);
+  if (c->flags_h) cudaFreeHost(c->flags_h);
+  if (c->ev0) cudaEventDestroy(c->ev0);
+  if (c->ev1) cudaEventDestroy(c->ev1);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+  return B200MD_OK;
+}
+
+extern "C" double b200md_memory_usage(const b200md_ctx *c) { return c ? c->bytes_held : 0.0; }
+
+#define NEED_CTX()                                                                 \
+  if (!c) return b200md_fail(nullptr, B200MD_ERR_ARG, "NULL context");             \
+  if (cudaSetDevice(c->device) != cudaSuccess) return b200md_fail(c, B200MD_ERR_CUDA, "cudaSetDevice failed")
+
+extern "C" int b200md_set_units(b200md_ctx *c, double boltz, double mvv2e, double ftm2v, double nktv2p)
+{
+  NEED_CTX();
+  c->boltz = boltz; c->mvv2e = mvv2e; c->ftm2v = ftm2v; c->nktv2p = nktv2p;
+  return B200MD_OK;
+}
+
+extern "C" int b200md_set_box(b200md_ctx *c, const double boxlo[3], const double boxhi[3], const int periodic[3],
+                              const int procgrid[3])
+{
+  NEED_CTX();
+  int np = procgrid[0] * procgrid[1] * procgrid[2];
+  if (np != c->nranks) return b200md_fail(c, B200MD_ERR_ARG, "procgrid %dx%dx%d != nranks %d", procgrid[0], procgrid[1], procgrid[2], c->nranks);
+  for (int k = 0; k < 3; k++) {
+    if (!(boxhi[k] > boxlo[k])) return b200md_fail(c, B200MD_ERR_ARG, "box hi <= lo in dim %d", k);
+    c->boxlo[k] = boxlo[k]; c->boxhi[k] = boxhi[k]; c->prd[k] = boxhi[k] - boxlo[k];
+    c->periodic[k] = periodic[k]; c->procgrid[k] = procgrid[k];
+  }
+  c->myloc[0] = c->rank % procgrid[0];
+  c->myloc[1] = (c->rank / procgrid[0]) % procgrid[1];
+  c->myloc[2] = c->rank / (procgrid[0] * procgrid[1]);
+  for (int k = 0; k < 3; k++) {
+    // uniform cuts, as CommBrick::setup / Domain::set_local_box (src/domain.cpp: sublo = boxlo + prd*split)
+    c->sublo[k] = c->boxlo[k] + c->prd[k] * ((double) c->myloc[k] / c->procgrid[k]);
+    c->subhi[k] = (c->myloc[k] == c->procgrid[k] - 1) ? c->boxhi[k] : c->boxlo[k] + c->prd[k] * ((double) (c->myloc[k] + 1) / c->procgrid[k]);
+  }
+  c->have_box = true;
+  c->list_valid = false;
+  return B200MD_OK;
+}
+
+extern "C" int b200md_set_mass(b200md_ctx *c, int ntypes, const double *mass)
+{
+  NEED_CTX();
+  if (ntypes < 1 || ntypes > B200MD_MAXTYPES) return b200md_fail(c, B200MD_ERR_ARG, "ntypes %d out of range 1..%d", ntypes, B200MD_MAXTYPES);
+  c->ntypes = ntypes;
+  c->mass_h[0] = 1.0;
+  for (int k = 1; k <= ntypes; k++) {
+    if (!(mass[k] > 0.0)) return b200md_fail(c, B200MD_ERR_ARG, "mass of type %d not set", k);
+    c->mass_h[k] = mass[k];
+  }
+  TRY(dev_ensure(c, c->mass_d, B200MD_MAXTYPES + 1));
+  CU(cudaMemcpyAsync(c->mass_d.p, c->mass_h, (ntypes + 1) * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return B200MD_OK;
+}
+
+// ---- atoms -----------------------------------------------------------------------------------
+__global__ void k_pack_pos(const double *__restrict__ x3, const int *__restrict__ type, double4 *__restrict__ pos, int n)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  pos[i] = make_double4(x3[3 * i], x3[3 * i + 1], x3[3 * i + 2], type_as_w(type[i]));
+}
+__global__ void k_aos_to_soa(const double *__restrict__ a3, double *__restrict__ a, double *__restrict__ b, double *__restrict__ cc, int n)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  a[i] = a3[3 * i]; b[i] = a3[3 * i + 1]; cc[i] = a3[3 * i + 2];
+}
+__global__ void k_soa_to_aos(const double *__restrict__ a, const double *__restrict__ b, const double *__restrict__ cc, double *__restrict__ a3, int n)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  a3[3 * i] = a[i]; a3[3 * i + 1] = b[i]; a3[3 * i + 2] = cc[i];
+}
+__global__ void k_unpack_pos(const double4 *__restrict__ pos, double *__restrict__ x3, int *__restrict__ type, int n)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double4 p = pos[i];
+  x3[3 * i] = p.x; x3[3 * i + 1] = p.y; x3[3 * i + 2] = p.z;
+  if (type) type[i] = pos_type(p);
+}
+__global__ void k_update_pos(const double *__restrict__ x3, double4 *__restrict__ pos, int n)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double4 p = pos[i];
+  p.x = x3[3 * i]; p.y = x3[3 * i + 1]; p.z = x3[3 * i + 2];
+  pos[i] = p;
+}
+
+static int stage_bytes(b200md_ctx *c, size_t bytes)
+{
+  return dev_ensure(c, c->stage, (bytes + 7) / 8);
+}
+
+extern "C" int b200md_upload_atoms(b200md_ctx *c, int n, const double *x, const double *v, const int *type, const int *tag,
+                                   const int *image)
+{
+  NEED_CTX();
+  if (n <= 0 || !x || !type || !tag) return b200md_fail(c, B200MD_ERR_ARG, "upload_atoms: n, x, type, tag are required");
+  size_t est = (size_t) n + n / 4 + 1024;  // head-room for ghosts; grown on demand in borders()
+  TRY(dev_ensure(c, c->pos, est));
+  TRY(dev_ensure(c, c->tag, est));
+  TRY(dev_ensure(c, c->image, (size_t) n));
+  for (int k = 0; k < 3; k++) { TRY(dev_ensure(c, c->v[k], (size_t) n)); TRY(dev_ensure(c, c->f[k], (size_t) n)); }
+  TRY(stage_bytes(c, (size_t) n * 28));
+  double *sx = c->stage.p;
+  int *st = (int *) (sx + (size_t) 3 * n);
+  const int g = cdiv(n, 256);
+  CU(cudaMemcpyAsync(sx, x, (size_t) n * 24, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(st, type, (size_t) n * 4, cudaMemcpyHostToDevice, c->stream));
+  k_pack_pos<<<g, 256, 0, c->stream>>>(sx, st, c->pos.p, n);
+  LAUNCH_CHECK();
+  if (v) {
+    CU(cudaMemcpyAsync(sx, v, (size_t) n * 24, cudaMemcpyHostToDevice, c->stream));
+    k_aos_to_soa<<<g, 256, 0, c->stream>>>(sx, c->v[0].p, c->v[1].p, c->v[2].p, n);
+    LAUNCH_CHECK();
+  } else
+    for (int k = 0; k < 3; k++) CU(cudaMemsetAsync(c->v[k].p, 0, (size_t) n * 8, c->stream));
+  for (int k = 0; k < 3; k++) CU(cudaMemsetAsync(c->f[k].p, 0, (size_t) n * 8, c->stream));
+  CU(cudaMemcpyAsync(c->tag.p, tag, (size_t) n * 4, cudaMemcpyHostToDevice, c->stream));
+  if (image) CU(cudaMemcpyAsync(c->image.p, image, (size_t) n * 4, cudaMemcpyHostToDevice, c->stream));
+  else {
+    // IMGMAX in each of the three fields == image (0,0,0) (src/atom_vec.cpp create_atom)
+    std::vector<int> img((size_t) n, (IMGMAX << IMG2BITS) | (IMGMAX << IMGBITS) | IMGMAX);
+    CU(cudaMemcpyAsync(c->image.p, img.data(), (size_t) n * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+  }
+  CU(cudaStreamSynchronize(c->stream));
+  c->nlocal = n;
+  c->nghost = 0;
+  c->list_valid = false;
+  c->setup_done = false;
+  c->have_ev = false;
+  return B200MD_OK;
+}
+
+extern "C" int b200md_nlocal(const b200md_ctx *c) { return c ? c->nlocal : 0; }
+extern "C" int b200md_nghost(const b200md_ctx *c) { return c ? c->nghost : 0; }
+
+extern "C" int b200md_download_atoms(b200md_ctx *c, double *x, double *v, double *f, int *type, int *tag, int *image)
+{
+  NEED_CTX();
+  const int n = c->nlocal;
+  if (n <= 0) return b200md_fail(c, B200MD_ERR_ARG, "no atoms");
+  TRY(stage_bytes(c, (size_t) n * 28));
+  double *sx = c->stage.p;
+  int *st = (int *) (sx + (size_t) 3 * n);
+  const int g = cdiv(n, 256);
+  if (x || type) {
+    k_unpack_pos<<<g, 256, 0, c->stream>>>(c->pos.p, sx, st, n);
+    LAUNCH_CHECK();
+    if (x) CU(cudaMemcpyAsync(x, sx, (size_t) n * 24, cudaMemcpyDeviceToHost, c->stream));
+    if (type) CU(cudaMemcpyAsync(type, st, (size_t) n * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+  }
+  if (v) {
+    k_soa_to_aos<<<g, 256, 0, c->stream>>>(c->v[0].p, c->v[1].p, c->v[2].p, sx, n);
+    LAUNCH_CHECK();
+    CU(cudaMemcpyAsync(v, sx, (size_t) n * 24, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+  }
+  if (f) {
+    k_soa_to_aos<<<g, 256, 0, c->stream>>>(c->f[0].p, c->f[1].p, c->f[2].p, sx, n);
+    LAUNCH_CHECK();
+    CU(cudaMemcpyAsync(f, sx, (size_t) n * 24, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+  }
+  if (tag) CU(cudaMemcpyAsync(tag, c->tag.p, (size_t) n * 4, cudaMemcpyDeviceToHost, c->stream));
+  if (image) CU(cudaMemcpyAsync(image, c->image.p, (size_t) n * 4, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return B200MD_OK;
+}
+
+extern "C" int b200md_download_all(b200md_ctx *c, double *x, int *tag)
+{
+  NEED_CTX();
+  const int n = c->nlocal + c->nghost;
+  if (n <= 0) return b200md_fail(c, B200MD_ERR_ARG, "no atoms");
+  TRY(stage_bytes(c, (size_t) n * 24));
+  if (x) {
+    k_unpack_pos<<<cdiv(n, 256), 256, 0, c->stream>>>(c->pos.p, c->stage.p, nullptr, n);
+    LAUNCH_CHECK();
+    CU(cudaMemcpyAsync(x, c->stage.p, (size_t) n * 24, cudaMemcpyDeviceToHost, c->stream));
+  }
+  if (tag) CU(cudaMemcpyAsync(tag, c->tag.p, (size_t) n * 4, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return B200MD_OK;
+}
+
+// ---- pair styles ---------------------------------------------------------------------------------
+extern "C" int b200md_lj_init(b200md_ctx *c, int ntypes, const double *cutsq, const double *lj1, const double *lj2,
+                              const double *lj3, const double *lj4, const double *offset, const double special_lj[4])
+{
+  NEED_CTX();
+  if (ntypes < 1 || ntypes > B200MD_MAXTYPES) return b200md_fail(c, B200MD_ERR_ARG, "ntypes %d out of range", ntypes);
+  const int nt2 = (ntypes + 1) * (ntypes + 1);
+  std::vector<double> h((size_t) 6 * nt2);
+  const double *src[6] = {cutsq, lj1, lj2, lj3, lj4, offset};
+  double cutmax = 0.0;
+  for (int t = 0; t < 6; t++)
+    for (int k = 0; k < nt2; k++) h[(size_t) t * nt2 + k] = src[t][k];
+  for (int i = 1; i <= ntypes; i++)
+    for (int j = 1; j <= ntypes; j++) cutmax = fmax(cutmax, sqrt(cutsq[i * (ntypes + 1) + j]));
+  if (c->lj.d) CU(cudaFree(c->lj.d));
+  CU(cudaMalloc((void **) &c->lj.d, h.size() * sizeof(double)));
+  CU(cudaMemcpy(c->lj.d, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice));
+  c->lj.ntypes = ntypes;
+  for (int t = 0; t < 6; t++) c->lj.h_onetype[t] = src[t][(ntypes + 1) + 1];
+  for (int k = 0; k < 4; k++) c->lj.special_lj[k] = special_lj ? special_lj[k] : 1.0;
+  c->pair_style = 1;
+  c->cutforce = cutmax;
+  if (c->ntypes == 0) c->ntypes = ntypes;
+  return B200MD_OK;
+}
+
+extern "C" int b200md_eam_init(b200md_ctx *c, int ntypes, int nrho, int nr, double rdrho, double rdr, double rhomax,
+                               double cutforcesq, int nfrho, const double *frho_spline, int nrhor, const double *rhor_spline,
+                               int nz2r, const double *z2r_spline, const int *type2frho, const int *type2rhor,
+                               const int *type2z2r)
+{
+  NEED_CTX();
+  if (ntypes < 1 || ntypes > B200MD_MAXTYPES) return b200md_fail(c, B200MD_ERR_ARG, "ntypes %d out of range", ntypes);
+  EAMTables &T = c->eam;
+  if (T.frho) { cudaFree(T.frho); cudaFree(T.rhor); cudaFree(T.z2r); cudaFree(T.rhoA); cudaFree(T.type2frho); cudaFree(T.type2rhor); cudaFree(T.type2z2r); }
+  T.ntypes = ntypes; T.nrho = nrho; T.nr = nr; T.nfrho = nfrho; T.nrhor = nrhor; T.nz2r = nz2r;
+  T.rdrho = rdrho; T.rdr = rdr; T.rhomax = rhomax; T.cutforcesq = cutforcesq;
+  const size_t nf = (size_t) nfrho * (nrho + 1) * 7, nrr = (size_t) nrhor * (nr + 1) * 7, nz = (size_t) nz2r * (nr + 1) * 7;
+  const int nt1 = ntypes + 1;
+  CU(cudaMalloc((void **) &T.frho, nf * 8));
+  CU(cudaMalloc((void **) &T.rhor, nrr * 8));
+  CU(cudaMalloc((void **) &T.z2r, nz * 8));
+  CU(cudaMalloc((void **) &T.rhoA, (size_t) nrhor * (nr + 1) * sizeof(double4)));
+  CU(cudaMalloc((void **) &T.type2frho, nt1 * 4));
+  CU(cudaMalloc((void **) &T.type2rhor, nt1 * nt1 * 4));
+  CU(cudaMalloc((void **) &T.type2z2r, nt1 * nt1 * 4));
+  CU(cudaMemcpy(T.frho, frho_spline, nf * 8, cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(T.rhor, rhor_spline, nrr * 8, cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(T.z2r, z2r_spline, nz * 8, cudaMemcpyHostToDevice));
+  std::vector<double> a((size_t) nrhor * (nr + 1) * 4);
+  for (size_t k = 0; k < (size_t) nrhor * (nr + 1); k++)
+    for (int q = 0; q < 4; q++) a[4 * k + q] = rhor_spline[7 * k + 3 + q];
+  CU(cudaMemcpy(T.rhoA, a.data(), a.size() * 8, cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(T.type2frho, type2frho, nt1 * 4, cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(T.type2rhor, type2rhor, nt1 * nt1 * 4, cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(T.type2z2r, type2z2r, nt1 * nt1 * 4, cudaMemcpyHostToDevice));
+  c->pair_style = 2;
+  c->cutforce = sqrt(cutforcesq);
+  if (c->ntypes == 0) c->ntypes = ntypes;
+  return B200MD_OK;
+}
+
+extern "C" int b200md_eam_download(b200md_ctx *c, double *rho, double *fp)
+{
+  NEED_CTX();
+  if (c->pair_style != 2 || !c->rho.p) return b200md_fail(c, B200MD_ERR_ARG, "eam not active");
+  if (rho) CU(cudaMemcpyAsync(rho, c->rho.p, (size_t) c->nlocal * 8, cudaMemcpyDeviceToHost, c->stream));
+  if (fp) CU(cudaMemcpyAsync(fp, c->fp.p, (size_t) c->nlocal * 8, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return B200MD_OK;
+}
+
+// ---- neighbor ------------------------------------------------------------------------------------
+extern "C" int b200md_neigh_config(b200md_ctx *c, int ntypes, const double *cutneighsq, double cutneighmax, double skin,
+                                   int every, int delay, int check, double binsize)
+{
+  NEED_CTX();
+  if (ntypes < 1 || ntypes > B200MD_MAXTYPES) return b200md_fail(c, B200MD_ERR_ARG, "ntypes %d out of range", ntypes);
+  if (every < 1 || delay < 0) return b200md_fail(c, B200MD_ERR_ARG, "Illegal neigh_modify every/delay");
+  const int nt2 = (ntypes + 1) * (ntypes + 1);
+  for (int k = 0; k < nt2; k++) c->cutneighsq_h[k] = cutneighsq[k];
+  TRY(dev_ensure(c, c->cutneighsq_d, (size_t) nt2));
+  CU(cudaMemcpy(c->cutneighsq_d.p, c->cutneighsq_h, nt2 * 8, cudaMemcpyHostToDevice));
+  c->ntypes = ntypes;
+  c->cutneighmax = cutneighmax;
+  c->skin = skin;
+  c->triggersq = 0.25 * skin * skin;  // src/neighbor.cpp:344
+  c->every = every; c->delay = delay; c->dist_check = check ? 1 : 0;
+  c->binsize_user = binsize;
+  c->have_neigh = true;
+  c->list_valid = false;
+  c->maxneigh = 0;
+  return B200MD_OK;
+}
+
+static int neigh_decide(b200md_ctx *c, int *flag)
+{
+  // Neighbor::decide (src/neighbor.cpp:2293-2308)
+  *flag = 0;
+  c->ago++;
+  if (c->ago >= c->delay && c->ago % c->every == 0) {
+    if (!c->dist_check) { *flag = 1; return B200MD_OK; }
+    int moved = 0;
+    TRY(neigh_check_distance(c, &moved));
+    if (moved && c->ago == (c->every > c->delay ? c->every : c->delay)) c->ndanger++;
+    *flag = moved;
+  }
+  return B200MD_OK;
+}
+
+extern "C" int b200md_neigh_decide(b200md_ctx *c, int *flag)
+{
+  NEED_CTX();
+  if (!c->list_valid) { *flag = 1; return B200MD_OK; }
+  return neigh_decide(c, flag);
+}
+
+extern "C" int b200md_neigh_build(b200md_ctx *c)
+{
+  NEED_CTX();
+  return neigh_rebuild(c);
+}
+
+__global__ void k_list_to_csr(const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh, int nlocal,
+                              const long long *__restrict__ first, int *__restrict__ out)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nlocal) return;
+  const int *nb = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
+  int *o = out + first[i];
+  int n = numneigh[i];
+  for (int k = 0; k < n; k++) o[k] = nb[(size_t) k * TILE];
+}
+
+extern "C" int b200md_neigh_export(b200md_ctx *c, int *numneigh, int *neighbors, int64_t *total)
+{
+  NEED_CTX();
+  if (!c->list_valid) return b200md_fail(c, B200MD_ERR_ARG, "no neighbor list built");
+  const int n = c->nlocal;
+  std::vector<int> nn((size_t) n);
+  CU(cudaMemcpyAsync(nn.data(), c->numneigh.p, (size_t) n * 4, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  std::vector<long long> first((size_t) n + 1);
+  first[0] = 0;
+  for (int i = 0; i < n; i++) first[i + 1] = first[i] + nn[i];
+  if (numneigh) memcpy(numneigh, nn.data(), (size_t) n * 4);
+  if (total) *total = first[n];
+  if (neighbors && first[n] > 0) {
+    long long *first_d = nullptr;
+    int *out_d = nullptr;
+    CU(cudaMalloc((void **) &first_d, ((size_t) n + 1) * 8));
+    CU(cudaMalloc((void **) &out_d, (size_t) first[n] * 4));
+    CU(cudaMemcpyAsync(first_d, first.data(), ((size_t) n + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+    k_list_to_csr<<<cdiv(n, 128), 128, 0, c->stream>>>(c->numneigh.p, c->neigh.p, c->maxneigh, n, first_d, out_d);
+    LAUNCH_CHECK();
+    CU(cudaMemcpyAsync(neighbors, out_d, (size_t) first[n] * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    cudaFree(first_d);
+    cudaFree(out_d);
+  }
+  return B200MD_OK;
+}
+
+extern "C" int b200md_neigh_stats(b200md_ctx *c, int64_t *nbuilds, int64_t *ndanger, int *maxneigh)
+{
+  NEED_CTX();
+  if (nbuilds) *nbuilds = c->nbuilds;
+  if (ndanger) *ndanger = c->ndanger;
+  if (maxneigh) *maxneigh = c->maxneigh_seen;
+  return B200MD_OK;
+}
+
+extern "C" int b200md_halo_forward(b200md_ctx *c)
+{
+  NEED_CTX();
+  if (!c->list_valid) return b200md_fail(c, B200MD_ERR_ARG, "halo_forward before the first neighbor build");
+  return halo_forward_pos(c);
+}
+
+// ---- sections, force, integrate, thermo ------------------------------------------------------------
+struct Sect {  // accumulates device time per Timer section when profiling is on
+  b200md_ctx *c;
+  int which;
+  cudaEvent_t a = nullptr, b = nullptr;
+  Sect(b200md_ctx *ctx, int w) : c(ctx), which(w)
+  {
+    if (c->profile) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, c->stream); }
+  }
+  ~Sect()
+  {
+    if (c->profile) {
+      cudaEventRecord(b, c->stream);
+      cudaEventSynchronize(b);
+      float ms = 0;
+      cudaEventElapsedTime(&ms, a, b);
+      c->sect_ms[which] += ms;
+      cudaEventDestroy(a);
+      cudaEventDestroy(b);
+    }
+  }
+};
+
+int comm_allreduce_sum(b200md_ctx *c, double *dev, int n);
+
+static int force_compute(b200md_ctx *c, int eflag, int vflag)
+{
+  if (!c->list_valid) return b200md_fail(c, B200MD_ERR_ARG, "pair_compute before the first neighbor build");
+  if (c->pair_style == 1) TRY(pair_lj_compute(c, eflag, vflag));
+  else if (c->pair_style == 2) TRY(pair_eam_compute(c, eflag, vflag));
+  else return b200md_fail(c, B200MD_ERR_ARG, "no pair style defined");
+  if (c->profile) {
+    CU(cudaEventSynchronize(c->ev1));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    c->last_pair_ms = ms;
+  }
+  if (eflag || vflag) {
+    CU(cudaMemcpyAsync(c->red_h, c->red_d, 9 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->eng_vdwl = c->red_h[0] + (c->pair_style == 2 ? c->red_h[8] : 0.0);
+    for (int k = 0; k < 6; k++) c->virial[k] = c->red_h[1 + k];
+    c->have_ev = true;
+  }
+  return B200MD_OK;
+}
+
+extern "C" int b200md_pair_compute(b200md_ctx *c, int eflag, int vflag, double *eng_vdwl, double *virial)
+{
+  NEED_CTX();
+  {
+    Sect s(c, SECT_PAIR);
+    TRY(force_compute(c, eflag, vflag));
+  }
+  if ((eflag || vflag)) {
+    if (eng_vdwl) *eng_vdwl = c->eng_vdwl;
+    if (virial) for (int k = 0; k < 6; k++) virial[k] = c->virial[k];
+  }
+  return B200MD_OK;
+}
+
+extern "C" int b200md_nve_initial(b200md_ctx *c, double dtv, double dtf)
+{
+  NEED_CTX();
+  Sect s(c, SECT_MODIFY);
+  return nve_initial(c, dtv, dtf);
+}
+
+extern "C" int b200md_nve_final(b200md_ctx *c, double dtf)
+{
+  NEED_CTX();
+  Sect s(c, SECT_MODIFY);
+  return nve_final(c, dtf);
+}
+
+extern "C" int b200md_thermo(b200md_ctx *c, double natoms_total, double *out)
+{
+  NEED_CTX();
+  if (!c->have_ev) return b200md_fail(c, B200MD_ERR_ARG, "thermo needs a pair_compute with eflag/vflag set");
+  double t = 0.0;
+  TRY(thermo_ke(c, &t));
+  double loc[8] = {c->eng_vdwl, t, c->virial[0], c->virial[1], c->virial[2], c->virial[3], c->virial[4], c->virial[5]};
+  if (c->nranks > 1) {
+    CU(cudaMemcpyAsync(c->red_d + 16, loc, sizeof(loc), cudaMemcpyHostToDevice, c->stream));
+    TRY(comm_allreduce_sum(c, c->red_d + 16, 8));
+    CU(cudaMemcpyAsync(loc, c->red_d + 16, sizeof(loc), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+  }
+  // ComputeTemp (src/compute_temp.cpp:55-100): dof = 3N - 3; ComputePressure (src/compute_pressure.cpp:228-260);
+  // KE = 0.5*dof*boltz*T (src/thermo.cpp:1712-1717)
+  const double dof = 3.0 * natoms_total - 3.0;
+  const double tfactor = c->mvv2e / (dof * c->boltz);
+  const double temp = loc[1] * tfactor;
+  const double inv_volume = 1.0 / (c->prd[0] * c->prd[1] * c->prd[2]);
+  out[0] = loc[0];
+  out[1] = 0.5 * dof * c->boltz * temp;
+  out[2] = temp;
+  out[3] = (dof * c->boltz * temp + loc[2] + loc[3] + loc[4]) / 3.0 * inv_volume * c->nktv2p;
+  for (int k = 0; k < 6; k++) out[4 + k] = loc[2 + k];
+  return B200MD_OK;
+}
+
+// ---- Verlet::setup / Verlet::run -----------------------------------------------------------------
+extern "C" int b200md_setup(b200md_ctx *c)
+{
+  NEED_CTX();
+  {
+    Sect s(c, SECT_NEIGH);
+    TRY(neigh_rebuild(c));
+  }
+  c->nbuilds = 0;  // the build inside setup is not counted (Neighbor::init resets ncalls)
+  c->ndanger = 0;
+  {
+    Sect s(c, SECT_PAIR);
+    TRY(force_compute(c, 1, 1));
+  }
+  c->setup_done = true;
+  return B200MD_OK;
+}
+
+extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every)
+{
+  NEED_CTX();
+  if (!c->setup_done) TRY(b200md_setup(c));
+  const double dtv = dt, dtf = 0.5 * dt * c->ftm2v;  // FixNVE::init (src/fix_nve.cpp:51-58)
+  bool pending_final = false;                         // final_integrate of the previous step still to do
+  for (int istep = 1; istep <= nsteps; istep++) {
+    c->ntimestep++;
+    // Integrate::ev_set (src/integrate.cpp:138-183): energy/virial on thermo steps and on the last step
+    const int ev = (istep == nsteps) || (thermo_every > 0 && c->ntimestep % thermo_every == 0);
+    {
+      Sect s(c, SECT_MODIFY);
+      if (pending_final) TRY(nve_final_initial(c, dtv, dtf));
+      else TRY(nve_initial(c, dtv, dtf));
+      pending_final = false;
+    }
+    int nflag = 0;
+    {
+      Sect s(c, SECT_NEIGH);
+      TRY(neigh_decide(c, &nflag));
+    }
+    if (!nflag) {
+      Sect s(c, SECT_COMM);
+      TRY(halo_forward_pos(c));
+    } else {
+      Sect s(c, SECT_NEIGH);
+      TRY(neigh_rebuild(c));
+    }
+    {
+      Sect s(c, SECT_PAIR);
+      TRY(force_compute(c, ev, ev));
+    }
+    if (ev || istep == nsteps) {
+      Sect s(c, SECT_MODIFY);
+      TRY(nve_final(c, dtf));
+    } else
+      pending_final = true;
+  }
+  CU(cudaStreamSynchronize(c->stream));
+  return B200MD_OK;
+}
+
+extern "C" int64_t b200md_timestep(const b200md_ctx *c) { return c ? c->ntimestep : 0; }
+
+// ---- host-buffer mode ------------------------------------------------------------------------------
+extern "C" int b200md_step_host(b200md_ctx *c, double dt, int eflag, int vflag, double *x, double *v, double *f, int *tag,
+                                double *eng_vdwl, double *virial)
+{
+  NEED_CTX();
+  if (!c->setup_done) return b200md_fail(c, B200MD_ERR_ARG, "step_host needs b200md_setup first");
+  const int n = c->nlocal, g = cdiv(n, 256);
+  const double dtv = dt, dtf = 0.5 * dt * c->ftm2v;
+  TRY(stage_bytes(c, (size_t) n * 48));
+  double *sx = c->stage.p, *sv = sx + (size_t) 3 * n;
+  CU(cudaMemcpyAsync(sx, x, (size_t) n * 24, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(sv, v, (size_t) n * 24, cudaMemcpyHostToDevice, c->stream));
+  k_update_pos<<<g, 256, 0, c->stream>>>(sx, c->pos.p, n);
+  LAUNCH_CHECK();
+  k_aos_to_soa<<<g, 256, 0, c->stream>>>(sv, c->v[0].p, c->v[1].p, c->v[2].p, n);
+  LAUNCH_CHECK();
+  c->ntimestep++;
+  TRY(nve_initial(c, dtv, dtf));
+  int nflag = 0;
+  TRY(neigh_decide(c, &nflag));
+  if (!nflag) TRY(halo_forward_pos(c));
+  else TRY(neigh_rebuild(c));
+  TRY(force_compute(c, eflag, vflag));
+  TRY(nve_final(c, dtf));
+  k_unpack_pos<<<g, 256, 0, c->stream>>>(c->pos.p, sx, nullptr, n);
+  LAUNCH_CHECK();
+  CU(cudaMemcpyAsync(x, sx, (size_t) n * 24, cudaMemcpyDeviceToHost, c->stream));
+  k_soa_to_aos<<<g, 256, 0, c->stream>>>(c->v[0].p, c->v[1].p, c->v[2].p, sv, n);
+  LAUNCH_CHECK();
+  CU(cudaMemcpyAsync(v, sv, (size_t) n * 24, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));  // sx is reused for f below
+  k_soa_to_aos<<<g, 256, 0, c->stream>>>(c->f[0].p, c->f[1].p, c->f[2].p, sx, n);
+  LAUNCH_CHECK();
+  CU(cudaMemcpyAsync(f, sx, (size_t) n * 24, cudaMemcpyDeviceToHost, c->stream));
+  if (tag) CU(cudaMemcpyAsync(tag, c->tag.p, (size_t) n * 4, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  if (eflag || vflag) {
+    if (eng_vdwl) *eng_vdwl = c->eng_vdwl;
+    if (virial) for (int k = 0; k < 6; k++) virial[k] = c->virial[k];
+  }
+  return B200MD_OK;
+}
+
+// ---- instrumentation -------------------------------------------------------------------------------
+extern "C" int b200md_timers(b200md_ctx *c, double ms[5], int64_t *kernel_launches, int reset)
+{
+  NEED_CTX();
+  if (ms) for (int k = 0; k < 5; k++) ms[k] = c->sect_ms[k];
+  if (kernel_launches) *kernel_launches = c->launches;
+  if (reset) {
+    for (int k = 0; k < 5; k++) c->sect_ms[k] = 0.0;
+    c->launches = 0;
+  }
+  return B200MD_OK;
+}
+
+extern "C" int b200md_last_kernel_ms(b200md_ctx *c, double *pair_ms, double *neigh_ms)
+{
+  NEED_CTX();
+  if (pair_ms) *pair_ms = c->last_pair_ms;
+  if (neigh_ms) *neigh_ms = c->last_neigh_ms;
+  return B200MD_OK;
+}
+
+extern "C" int b200md_profile(b200md_ctx *c, int on)
+{
+  NEED_CTX();
+  c->profile = on != 0;
+  return B200MD_OK;
+}

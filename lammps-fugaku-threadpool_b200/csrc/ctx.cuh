@@ -1,0 +1,222 @@
+// ctx.cuh -- internal state of libb200md.so (sm_100a).  Not part of the C ABI (include/b200md.h is).
+//
+// Device data layout (all FP64, atoms resident across timesteps):
+//   pos[nall]      double4 {x, y, z, w}; low 32 bits of w hold the atom type (1-based, as in the
+//                  reference's atom->type, src/atom.h:70-73).  One 32-byte sector per gathered neighbor.
+//                  owned atoms [0,nlocal) are kept in bin order (counting sort at every rebuild);
+//                  ghost atoms [nlocal,nall) are grouped by the direction (26 of them) they came from.
+//   v[3][nlocal], f[3][nlocal]   SoA, streamed by the integrate kernels.
+//   tag[nall], image[nlocal]     int32 (LAMMPS_SMALLBIG, src/lmptype.h:90-130).
+//   neigh          FULL neighbor list, "blocked transposed": atoms are grouped in tiles of 32; entry k of
+//                  atom i lives at neigh[(i>>5)*32*maxneigh + k*32 + (i&31)], so a warp reads one
+//                  coalesced 128-byte row per k and each tile is one contiguous slab in HBM.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/b200md.h"
+
+#define NEIGHMASK 0x1FFFFFFF  // src/lmptype.h:61-65
+#define SBBITS 30
+#define IMGMASK 1023          // src/lmptype.h (LAMMPS_SMALLBIG)
+#define IMGBITS 10
+#define IMG2BITS 20
+#define IMGMAX 512
+
+#define B200MD_MAXTYPES 16
+#define BIN_MARGIN 2
+#define NDIR 26               // halo directions (3^3 - 1)
+#define TILE 32
+
+template <class T> struct DevBuf {
+  T *p = nullptr;
+  size_t n = 0;  // capacity in elements
+};
+
+struct HaloPlan {             // passed by value to the halo kernels
+  int goff[NDIR + 1];         // ghost group offsets (relative to nlocal), by direction
+  double shift[NDIR][3];      // periodic shift the SENDER applies (src/atom_vec.cpp:363-379)
+};
+
+struct BinGeom {
+  double lo[3];               // sublo of this rank
+  double inv[3];              // 1 / binsize
+  int nbin[3];                // bins covering the sub-domain
+  int mbin[3];                // nbin + 2*BIN_MARGIN
+  int mbins;
+};
+
+struct LJTables {             // what PairLJCut::init_one fills (src/pair_lj_cut.cpp:501-557)
+  int ntypes;
+  double *d;                  // device: 6 tables of (ntypes+1)^2: cutsq, lj1, lj2, lj3, lj4, offset
+  double special_lj[4];
+  double h_onetype[6];        // ntypes == 1 fast path: the [1][1] entries
+};
+
+struct EAMTables {            // what PairEAM::array2spline produces (src/MANYBODY/pair_eam.cpp:744-797)
+  int ntypes, nrho, nr, nfrho, nrhor, nz2r;
+  double rdrho, rdr, rhomax, cutforcesq;
+  double *frho;               // device [nfrho][nrho+1][7]
+  double4 *rhoA;              // device [nrhor][nr+1]  value coeffs {c3,c4,c5,c6} of rhor_spline  (pass A)
+  double4 *tabC;              // device [nrhor or nz2r][nr+1][...] see pair_eam.cu
+  double *rhor, *z2r;         // device, original 7-coefficient layout
+  int *type2frho, *type2rhor, *type2z2r;  // device
+  int h_type2frho[B200MD_MAXTYPES + 1];
+};
+
+struct b200md_ctx {
+  int device = 0, nranks = 1, rank = 0;
+  cudaStream_t stream = nullptr;
+  char err[512] = {0};
+
+  // units / box (src/update.cpp:145-207, src/domain.h)
+  double boltz = 1, mvv2e = 1, ftm2v = 1, nktv2p = 1;
+  double boxlo[3] = {0, 0, 0}, boxhi[3] = {0, 0, 0}, prd[3] = {0, 0, 0};
+  int periodic[3] = {1, 1, 1}, procgrid[3] = {1, 1, 1}, myloc[3] = {0, 0, 0};
+  double sublo[3], subhi[3];
+  bool have_box = false;
+  int ntypes = 0;
+  double mass_h[B200MD_MAXTYPES + 1];
+  DevBuf<double> mass_d;
+
+  // atoms
+  int nlocal = 0, nghost = 0;
+  DevBuf<double4> pos, pos_tmp, xhold;
+  DevBuf<double> v[3], v_tmp[3], f[3];
+  DevBuf<int> tag, tag_tmp, image, image_tmp;
+
+  // pair styles
+  int pair_style = 0;  // 0 none, 1 lj/cut, 2 eam
+  LJTables lj = {};
+  EAMTables eam = {};
+  DevBuf<double> rho, fp;
+  double cutforce = 0;
+
+  // neighbor settings (src/neighbor.cpp:306-695)
+  DevBuf<double> cutneighsq_d;
+  double cutneighsq_h[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
+  double cutneighmax = 0, skin = 0, triggersq = 0, binsize_user = 0;
+  int every = 1, delay = 0, dist_check = 1;
+  bool have_neigh = false;
+  int ago = 0;
+  int64_t nbuilds = 0, ndanger = 0;
+  bool list_valid = false;
+
+  // bins / sort
+  BinGeom bg;
+  DevBuf<int> bin_count, bin_start, atom_bin, cell_list, perm, scan_tmp;
+
+  // neighbor list
+  int maxneigh = 0;
+  DevBuf<int> numneigh, neigh;
+  int maxneigh_seen = 0;
+
+  // halo
+  HaloPlan hp;
+  int sendcount[NDIR];
+  DevBuf<int> ghost_src, border_blockcnt, border_total;
+  DevBuf<signed char> ghost_dir;
+
+  // reductions / flags
+  DevBuf<double> partials;  // [nblocks][8]
+  double *red_d = nullptr;  // [16] device results
+  double *red_h = nullptr;  // pinned mirror
+  int *flags_d = nullptr;   // [8]: 0 nonfinite, 1 overflow(max count), 2 moved, 3 lost
+  int *flags_h = nullptr;   // pinned mirror
+  double eng_vdwl = 0, virial[6] = {0, 0, 0, 0, 0, 0};
+  bool have_ev = false;
+
+  // run state
+  int64_t ntimestep = 0;
+  bool setup_done = false;
+
+  // instrumentation
+  double sect_ms[5] = {0, 0, 0, 0, 0};
+  int64_t launches = 0;
+  bool profile = false;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  double last_pair_ms = 0, last_neigh_ms = 0;
+  double bytes_held = 0;
+
+  // host-buffer mode staging
+  DevBuf<double> stage;
+};
+
+// ---------------------------------------------------------------------------------------------
+// error handling: no exceptions across the C ABI, int status + text (include/b200md.h)
+// ---------------------------------------------------------------------------------------------
+int b200md_fail(b200md_ctx *c, int code, const char *fmt, ...);
+
+#define CU(call)                                                                                       \
+  do {                                                                                                 \
+    cudaError_t e__ = (call);                                                                          \
+    if (e__ != cudaSuccess)                                                                            \
+      return b200md_fail(c, B200MD_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call,                \
+                         cudaGetErrorString(e__));                                                     \
+  } while (0)
+
+#define TRY(call)                                                                                      \
+  do {                                                                                                 \
+    int s__ = (call);                                                                                  \
+    if (s__ != B200MD_OK) return s__;                                                                  \
+  } while (0)
+
+#define LAUNCH_CHECK()                                                                                 \
+  do {                                                                                                 \
+    c->launches++;                                                                                     \
+    cudaError_t e__ = cudaGetLastError();                                                              \
+    if (e__ != cudaSuccess)                                                                            \
+      return b200md_fail(c, B200MD_ERR_CUDA, "%s:%d kernel launch: %s", __FILE__, __LINE__,            \
+                         cudaGetErrorString(e__));                                                     \
+  } while (0)
+
+template <class T> int dev_ensure(b200md_ctx *c, DevBuf<T> &b, size_t n, bool keep = false)
+{
+  if (n <= b.n) return B200MD_OK;
+  size_t want = n + n / 8 + 64;
+  T *q = nullptr;
+  CU(cudaMalloc((void **) &q, want * sizeof(T)));
+  if (keep && b.p && b.n) CU(cudaMemcpyAsync(q, b.p, b.n * sizeof(T), cudaMemcpyDeviceToDevice, c->stream));
+  if (b.p) {
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaFree(b.p));
+    c->bytes_held -= (double) b.n * sizeof(T);
+  }
+  b.p = q;
+  b.n = want;
+  c->bytes_held += (double) want * sizeof(T);
+  return B200MD_OK;
+}
+
+template <class T> void dev_free(b200md_ctx *c, DevBuf<T> &b)
+{
+  if (b.p) cudaFree(b.p);
+  c->bytes_held -= (double) b.n * sizeof(T);
+  b.p = nullptr;
+  b.n = 0;
+}
+
+static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+// section timers (names as src/timer.h:23-42)
+enum { SECT_PAIR = 0, SECT_NEIGH = 1, SECT_COMM = 2, SECT_MODIFY = 3, SECT_OTHER = 4 };
+
+// ---- internal entry points (one per .cu) ------------------------------------------------------
+int neigh_setup_bins(b200md_ctx *c);
+int neigh_rebuild(b200md_ctx *c);          // pbc + sort + borders + bin + build
+int neigh_check_distance(b200md_ctx *c, int *moved);
+int halo_forward_pos(b200md_ctx *c);
+int halo_forward_scalar(b200md_ctx *c, double *a);
+int pair_lj_compute(b200md_ctx *c, int eflag, int vflag);
+int pair_eam_compute(b200md_ctx *c, int eflag, int vflag);
+int nve_initial(b200md_ctx *c, double dtv, double dtf);
+int nve_final(b200md_ctx *c, double dtf);
+int thermo_ke(b200md_ctx *c, double *sum_mv2);
+int reduce_partials(b200md_ctx *c, int nblocks, int ncomp, int dst);  // partials -> red_d[dst..]
+
+// device helpers
+__device__ __forceinline__ int pos_type(const double4 &p) { return __double2loint(p.w); }
+__device__ __forceinline__ double type_as_w(int t) { return __hiloint2double(0, t); }
+int nve_final_initial(b200md_ctx *c, double dtv, double dtf);

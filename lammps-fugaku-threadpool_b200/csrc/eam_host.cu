@@ -1,0 +1,152 @@
+// eam_host.cu -- host side of pair_style eam for funcfl files: what PairEAM::coeff / read_file /
+// file2array / array2spline / init_one do before the first compute (src/MANYBODY/pair_eam.cpp:372-412,
+// 460-526, 533-765, 435-456).  Produces the spline tables and hands them to b200md_eam_init.  In a LAMMPS
+// build PairEAMB200 inherits these arrays from PairEAM instead; this entry point serves stand-alone hosts.
+#include <math.h>
+#include <stdio.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "ctx.cuh"
+
+namespace {
+
+struct FuncflFile {          // Funcfl (src/MANYBODY/pair_eam.h:78-85); tables are 0-based here
+  double mass = 0, drho = 0, dr = 0, cut = 0;
+  std::vector<double> frho, zr, rhor;
+};
+
+bool read_numbers(FILE *fp, std::vector<double> &dst, int n)
+{
+  dst.resize(n);
+  for (int k = 0; k < n; k++)
+    if (fscanf(fp, "%lg", &dst[k]) != 1) return false;
+  return true;
+}
+
+// line 1 comment, line 2 "Z mass ...", line 3 "nrho drho nr dr cut", then frho[nrho], zr[nr], rhor[nr]
+int read_funcfl(const char *name, FuncflFile &f, std::string &why)
+{
+  FILE *fp = fopen(name, "r");
+  if (!fp) { why = std::string("Cannot open EAM potential file ") + name; return 1; }
+  char line[2048];
+  int iz = 0, nrho = 0, nr = 0;
+  bool ok = fgets(line, sizeof line, fp) && fgets(line, sizeof line, fp) && sscanf(line, "%d %lg", &iz, &f.mass) == 2 &&
+            fgets(line, sizeof line, fp) && sscanf(line, "%d %lg %d %lg %lg", &nrho, &f.drho, &nr, &f.dr, &f.cut) == 5 &&
+            nrho > 4 && nr > 4 && f.drho > 0 && f.dr > 0 && read_numbers(fp, f.frho, nrho) && read_numbers(fp, f.zr, nr) &&
+            read_numbers(fp, f.rhor, nr);
+  fclose(fp);
+  if (!ok) { why = std::string("Invalid EAM potential file ") + name; return 1; }
+  return 0;
+}
+
+// value of a tabulated function (spacing d, first knot at 0) at r by the reference's 4-point Lagrange
+// formula (pair_eam.cpp:580-596); knots are 1-based there, hence the index shifts
+double lagrange4(const std::vector<double> &tab, double d, double r)
+{
+  const int n = (int) tab.size();
+  double p = r / d + 1.0;
+  int k = (int) p;
+  k = std::max(2, std::min(k, n - 2));
+  p -= k;
+  p = std::min(p, 2.0);
+  const double sixth = 1.0 / 6.0;
+  const double w1 = -sixth * p * (p - 1.0) * (p - 2.0);
+  const double w2 = 0.5 * (p * p - 1.0) * (p - 2.0);
+  const double w3 = -0.5 * p * (p + 1.0) * (p - 2.0);
+  const double w4 = sixth * p * (p * p - 1.0);
+  return w1 * tab[k - 2] + w2 * tab[k - 1] + w3 * tab[k] + w4 * tab[k + 1];
+}
+
+// PairEAM::interpolate (pair_eam.cpp:769-797): rows 1..n of a [n+1][7] table, row 0 unused
+void cubic_rows(int n, double delta, const double *f1, double *row0)
+{
+  auto S = [&](int m, int k) -> double & { return row0[(size_t) m * 7 + k]; };
+  for (int m = 1; m <= n; m++) S(m, 6) = f1[m];
+  S(1, 5) = S(2, 6) - S(1, 6);
+  S(2, 5) = 0.5 * (S(3, 6) - S(1, 6));
+  S(n - 1, 5) = 0.5 * (S(n, 6) - S(n - 2, 6));
+  S(n, 5) = S(n, 6) - S(n - 1, 6);
+  for (int m = 3; m <= n - 2; m++) S(m, 5) = ((S(m - 2, 6) - S(m + 2, 6)) + 8.0 * (S(m + 1, 6) - S(m - 1, 6))) / 12.0;
+  for (int m = 1; m < n; m++) {
+    const double d = S(m + 1, 6) - S(m, 6);
+    S(m, 4) = 3.0 * d - 2.0 * S(m, 5) - S(m + 1, 5);
+    S(m, 3) = S(m, 5) + S(m + 1, 5) - 2.0 * d;
+  }
+  S(n, 4) = 0.0;
+  S(n, 3) = 0.0;
+  for (int m = 1; m <= n; m++) {
+    S(m, 2) = S(m, 5) / delta;
+    S(m, 1) = 2.0 * S(m, 4) / delta;
+    S(m, 0) = 3.0 * S(m, 3) / delta;
+  }
+}
+
+}  // namespace
+
+extern "C" int b200md_eam_init_funcfl(b200md_ctx *c, int ntypes, int nfiles, const char *const *files, const int *map,
+                                      double *mass_out, double *cutmax_out)
+{
+  if (!c) return b200md_fail(nullptr, B200MD_ERR_ARG, "NULL context");
+  if (ntypes < 1 || ntypes > B200MD_MAXTYPES || nfiles < 1) return b200md_fail(c, B200MD_ERR_ARG, "eam: bad ntypes/nfiles");
+  std::vector<FuncflFile> F(nfiles);
+  std::string why;
+  for (int k = 0; k < nfiles; k++)
+    if (read_funcfl(files[k], F[k], why)) return b200md_fail(c, B200MD_ERR_ARG, "%s", why.c_str());
+  for (int i = 1; i <= ntypes; i++)
+    if (map[i] < -1 || map[i] >= nfiles) return b200md_fail(c, B200MD_ERR_ARG, "eam: bad map[%d]", i);
+
+  // common grid: largest spacing, largest extent among the files in use (pair_eam.cpp:540-565)
+  double dr = 0, drho = 0, rmax = 0, rhomax = 0, cutmax = 0;
+  for (int k = 0; k < nfiles; k++) {
+    bool used = false;
+    for (int i = 1; i <= ntypes; i++) used |= (map[i] == k);
+    cutmax = std::max(cutmax, F[k].cut);  // init_one: max over ALL files read
+    if (!used) continue;
+    dr = std::max(dr, F[k].dr);
+    drho = std::max(drho, F[k].drho);
+    rmax = std::max(rmax, ((int) F[k].rhor.size() - 1) * F[k].dr);
+    rhomax = std::max(rhomax, ((int) F[k].frho.size() - 1) * F[k].drho);
+  }
+  if (dr <= 0 || drho <= 0) return b200md_fail(c, B200MD_ERR_ARG, "eam: no atom type is mapped to a funcfl file");
+  const int nr = (int) (rmax / dr + 0.5), nrho = (int) (rhomax / drho + 0.5);
+  const int nfrho = nfiles + 1, nrhor = nfiles, nz2r = nfiles * (nfiles + 1) / 2, nt1 = ntypes + 1;
+
+  std::vector<double> g((size_t) std::max(nr, nrho) + 1);
+  std::vector<double> frho_s((size_t) nfrho * (nrho + 1) * 7, 0.0), rhor_s((size_t) nrhor * (nr + 1) * 7, 0.0),
+      z2r_s((size_t) nz2r * (nr + 1) * 7, 0.0);
+  for (int k = 0; k < nfrho; k++) {  // last table stays zero: types without an EAM file (pair_eam.cpp:600-611)
+    for (int m = 1; m <= nrho; m++) g[m] = (k < nfiles) ? lagrange4(F[k].frho, F[k].drho, (m - 1) * drho) : 0.0;
+    cubic_rows(nrho, drho, g.data(), &frho_s[(size_t) k * (nrho + 1) * 7]);
+  }
+  for (int k = 0; k < nrhor; k++) {
+    for (int m = 1; m <= nr; m++) g[m] = lagrange4(F[k].rhor, F[k].dr, (m - 1) * dr);
+    cubic_rows(nr, dr, g.data(), &rhor_s[(size_t) k * (nr + 1) * 7]);
+  }
+  int t = 0;
+  for (int a = 0; a < nfiles; a++)
+    for (int b = 0; b <= a; b++, t++) {  // z2r = 27.2 * 0.529 * Z_a(r) * Z_b(r)   (pair_eam.cpp:690-712)
+      for (int m = 1; m <= nr; m++) {
+        const double r = (m - 1) * dr;
+        g[m] = 27.2 * 0.529 * lagrange4(F[a].zr, F[a].dr, r) * lagrange4(F[b].zr, F[b].dr, r);
+      }
+      cubic_rows(nr, dr, g.data(), &z2r_s[(size_t) t * (nr + 1) * 7]);
+    }
+
+  std::vector<int> t2f(nt1, 0), t2r((size_t) nt1 * nt1, 0), t2z((size_t) nt1 * nt1, 0);
+  for (int i = 1; i <= ntypes; i++) {
+    t2f[i] = map[i] >= 0 ? map[i] : nfrho - 1;
+    for (int j = 1; j <= ntypes; j++) {
+      t2r[(size_t) i * nt1 + j] = map[i];
+      int hi = std::max(map[i], map[j]), lo = std::min(map[i], map[j]);
+      t2z[(size_t) i * nt1 + j] = (lo < 0) ? 0 : hi * (hi + 1) / 2 + lo;
+    }
+  }
+  if (mass_out)
+    for (int i = 1; i <= ntypes; i++) mass_out[i] = map[i] >= 0 ? F[map[i]].mass : 0.0;
+  if (cutmax_out) *cutmax_out = cutmax;
+  return b200md_eam_init(c, ntypes, nrho, nr, 1.0 / drho, 1.0 / dr, rhomax, cutmax * cutmax, nfrho, frho_s.data(),
+                         nrhor, rhor_s.data(), nz2r, z2r_s.data(), t2f.data(), t2r.data(), t2z.data());
+}

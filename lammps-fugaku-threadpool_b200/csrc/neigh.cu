@@ -1,0 +1,604 @@
+// neigh.cu -- the reneighbor branch of Verlet::run (src/verlet.cpp:283-306) on the device:
+//   Domain::pbc            (src/domain.cpp:530-600)      -> k_pbc
+//   Atom::sort + NBinStandard::bin_atoms (src/atom.cpp:2246-2345, src/nbin_standard.cpp:221-261)
+//                                                        -> counting sort k_bin_count / scan / k_bin_place /
+//                                                           k_bin_sortseg / k_permute_owned
+//   CommBrick::borders     (src/comm_brick.cpp:771-979)  -> k_border_count / k_border_scan / k_border_fill /
+//                                                           k_border_apply (single-stage, 26 directions)
+//   NPair::build           (src/npair_half_bin_atomonly_newton.cpp:33-113, full-list semantics of
+//                           src/npair_full_bin_atomonly.cpp) -> k_build_full
+//   Neighbor::check_distance (src/neighbor.cpp:2322-2374) -> k_check_distance
+// This is a from-scratch design: bins are >= cutneighmax wide (27-bin stencil, 9 contiguous x-rows),
+// owned atoms are physically re-ordered by bin at every rebuild, ghosts are made in ONE stage from the
+// 26 direction masks instead of the reference's 6 staged swaps (same ghost set when every sub-domain is
+// at least one ghost cutoff wide), and the list is a full list in a blocked-transposed layout.
+#include <utility>
+
+#include "ctx.cuh"
+
+// ------------------------------------------------------------------------------------------------
+// binning helpers
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int bin_of(const BinGeom &g, double x, double y, double z)
+{
+  int bx = (int) floor((x - g.lo[0]) * g.inv[0]) + BIN_MARGIN;
+  int by = (int) floor((y - g.lo[1]) * g.inv[1]) + BIN_MARGIN;
+  int bz = (int) floor((z - g.lo[2]) * g.inv[2]) + BIN_MARGIN;
+  bx = min(max(bx, 0), g.mbin[0] - 1);
+  by = min(max(by, 0), g.mbin[1] - 1);
+  bz = min(max(bz, 0), g.mbin[2] - 1);
+  return (bz * g.mbin[1] + by) * g.mbin[0] + bx;
+}
+
+// Domain::pbc for an orthogonal box: wrap owned atoms, update image flags (src/domain.cpp:546-600)
+__global__ void k_pbc(double4 *__restrict__ pos, int *__restrict__ image, int n, double3 lo, double3 hi, double3 prd,
+                      int px, int py, int pz, int *__restrict__ flags)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double4 p = pos[i];
+  if (!(isfinite(p.x) && isfinite(p.y) && isfinite(p.z))) { flags[0] = 1; return; }
+  int img = image[i];
+  if (px) {
+    if (p.x < lo.x) { p.x += prd.x; int idim = img & IMGMASK; int other = img ^ idim; idim--; idim &= IMGMASK; img = other | idim; }
+    if (p.x >= hi.x) { p.x -= prd.x; p.x = fmax(p.x, lo.x); int idim = img & IMGMASK; int other = img ^ idim; idim++; idim &= IMGMASK; img = other | idim; }
+  }
+  if (py) {
+    if (p.y < lo.y) { p.y += prd.y; int idim = (img >> IMGBITS) & IMGMASK; int other = img ^ (idim << IMGBITS); idim--; idim &= IMGMASK; img = other | (idim << IMGBITS); }
+    if (p.y >= hi.y) { p.y -= prd.y; p.y = fmax(p.y, lo.y); int idim = (img >> IMGBITS) & IMGMASK; int other = img ^ (idim << IMGBITS); idim++; idim &= IMGMASK; img = other | (idim << IMGBITS); }
+  }
+  if (pz) {
+    if (p.z < lo.z) { p.z += prd.z; int idim = (img >> IMG2BITS) & IMGMASK; int other = img ^ (idim << IMG2BITS); idim--; idim &= IMGMASK; img = other | (idim << IMG2BITS); }
+    if (p.z >= hi.z) { p.z -= prd.z; p.z = fmax(p.z, lo.z); int idim = (img >> IMG2BITS) & IMGMASK; int other = img ^ (idim << IMG2BITS); idim++; idim &= IMGMASK; img = other | (idim << IMG2BITS); }
+  }
+  pos[i] = p;
+  image[i] = img;
+}
+
+__global__ void k_bin_count(const double4 *__restrict__ pos, int n, BinGeom g, int *__restrict__ atom_bin,
+                            int *__restrict__ bin_count)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double4 p = pos[i];
+  int b = bin_of(g, p.x, p.y, p.z);
+  atom_bin[i] = b;
+  atomicAdd(&bin_count[b], 1);
+}
+
+// ---- exclusive scan over n ints (three small kernels; n = mbins+1, at most a few million) ----------
+#define SCAN_BLOCK 256
+#define SCAN_ITEMS 4
+__global__ void k_scan_block(const int *__restrict__ in, int *__restrict__ out, int *__restrict__ sums, int n)
+{
+  __shared__ int wsum[SCAN_BLOCK / 32];
+  int base = blockIdx.x * SCAN_BLOCK * SCAN_ITEMS + threadIdx.x * SCAN_ITEMS;
+  int v[SCAN_ITEMS], t = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; k++) { v[k] = (base + k < n) ? in[base + k] : 0; t += v[k]; }
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  int incl = t;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+  if (lane == 31) wsum[w] = incl;
+  __syncthreads();
+  int woff = 0;
+  for (int k = 0; k < w; k++) woff += wsum[k];
+  int excl = woff + incl - t;
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; k++) { if (base + k < n) out[base + k] = excl; excl += v[k]; }
+  if (threadIdx.x == SCAN_BLOCK - 1) sums[blockIdx.x] = woff + incl;
+}
+
+__global__ void k_scan_sums(int *__restrict__ sums, int nblk)  // one block, in-place exclusive scan
+{
+  __shared__ int wsum[32];
+  __shared__ int carry_s;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int start = 0; start < nblk; start += blockDim.x) {
+    int i = start + threadIdx.x;
+    int t = (i < nblk) ? sums[i] : 0;
+    int incl = t;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+    if (lane == 31) wsum[w] = incl;
+    __syncthreads();
+    int woff = 0;
+    for (int k = 0; k < w; k++) woff += wsum[k];
+    int carry = carry_s;
+    if (i < nblk) sums[i] = carry + woff + incl - t;
+    __syncthreads();
+    if (threadIdx.x == blockDim.x - 1) carry_s = carry + woff + incl;
+    __syncthreads();
+  }
+}
+
+__global__ void k_scan_add(int *__restrict__ out, const int *__restrict__ sums, int n)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] += sums[i / (SCAN_BLOCK * SCAN_ITEMS)];
+}
+
+static int exclusive_scan(b200md_ctx *c, const int *in, int *out, int n)
+{
+  int nblk = cdiv(n, SCAN_BLOCK * SCAN_ITEMS);
+  TRY(dev_ensure(c, c->scan_tmp, (size_t) nblk + 1));
+  k_scan_block<<<nblk, SCAN_BLOCK, 0, c->stream>>>(in, out, c->scan_tmp.p, n);
+  LAUNCH_CHECK();
+  if (nblk > 1) {
+    k_scan_sums<<<1, 1024, 0, c->stream>>>(c->scan_tmp.p, nblk);
+    LAUNCH_CHECK();
+    k_scan_add<<<cdiv(n, 256), 256, 0, c->stream>>>(out, c->scan_tmp.p, n);
+    LAUNCH_CHECK();
+  }
+  return B200MD_OK;
+}
+
+__global__ void k_bin_place(const int *__restrict__ atom_bin, int n, const int *__restrict__ bin_start,
+                            int *__restrict__ cursor, int *__restrict__ list)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int b = atom_bin[i];
+  int slot = bin_start[b] + atomicAdd(&cursor[b], 1);
+  list[slot] = i;
+}
+
+// the atomics above leave each bin's segment in arbitrary order: sort it ascending so that the atom
+// order (hence every floating-point summation order downstream) is reproducible run to run, and equals
+// the reference's "ascending index within a bin" (src/nbin_standard.cpp:254-259).
+__global__ void k_bin_sortseg(const int *__restrict__ bin_start, int mbins, int *__restrict__ list)
+{
+  int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= mbins) return;
+  int s = bin_start[b], e = bin_start[b + 1];
+  for (int a = s + 1; a < e; a++) {
+    int key = list[a];
+    int k = a - 1;
+    while (k >= s && list[k] > key) { list[k + 1] = list[k]; k--; }
+    list[k + 1] = key;
+  }
+}
+
+__global__ void k_permute_owned(const int *__restrict__ perm, int n, const double4 *__restrict__ pos,
+                                double4 *__restrict__ pos_o, const double *__restrict__ vx, const double *__restrict__ vy,
+                                const double *__restrict__ vz, double *__restrict__ vx_o, double *__restrict__ vy_o,
+                                double *__restrict__ vz_o, const int *__restrict__ tag, int *__restrict__ tag_o,
+                                const int *__restrict__ image, int *__restrict__ image_o)
+{
+  int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n) return;
+  int i = perm[s];
+  pos_o[s] = pos[i];
+  vx_o[s] = vx[i];
+  vy_o[s] = vy[i];
+  vz_o[s] = vz[i];
+  tag_o[s] = tag[i];
+  image_o[s] = image[i];
+}
+
+// counting sort of atoms [0,n) into bins: list = atom indices ordered by bin, ascending within a bin
+static int bin_sort(b200md_ctx *c, int n, int *list)
+{
+  const BinGeom &g = c->bg;
+  TRY(dev_ensure(c, c->bin_count, (size_t) g.mbins + 1));
+  TRY(dev_ensure(c, c->bin_start, (size_t) g.mbins + 1));
+  TRY(dev_ensure(c, c->atom_bin, (size_t) n));
+  CU(cudaMemsetAsync(c->bin_count.p, 0, ((size_t) g.mbins + 1) * sizeof(int), c->stream));
+  k_bin_count<<<cdiv(n, 256), 256, 0, c->stream>>>(c->pos.p, n, g, c->atom_bin.p, c->bin_count.p);
+  LAUNCH_CHECK();
+  TRY(exclusive_scan(c, c->bin_count.p, c->bin_start.p, g.mbins + 1));
+  CU(cudaMemsetAsync(c->bin_count.p, 0, ((size_t) g.mbins + 1) * sizeof(int), c->stream));
+  k_bin_place<<<cdiv(n, 256), 256, 0, c->stream>>>(c->atom_bin.p, n, c->bin_start.p, c->bin_count.p, list);
+  LAUNCH_CHECK();
+  k_bin_sortseg<<<cdiv(g.mbins, 128), 128, 0, c->stream>>>(c->bin_start.p, g.mbins, list);
+  LAUNCH_CHECK();
+  return B200MD_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// bins: NBinStandard::setup_bins (src/nbin_standard.cpp:82-215) re-designed for a 27-bin stencil
+// ------------------------------------------------------------------------------------------------
+int neigh_setup_bins(b200md_ctx *c)
+{
+  if (!c->have_box || !c->have_neigh) return b200md_fail(c, B200MD_ERR_ARG, "box and neighbor settings must be set first");
+  BinGeom &g = c->bg;
+  double target = c->binsize_user > c->cutneighmax ? c->binsize_user : c->cutneighmax;
+  long long mb = 1;
+  for (int k = 0; k < 3; k++) {
+    double len = c->subhi[k] - c->sublo[k];
+    bool decomposed_or_periodic = c->periodic[k] || c->procgrid[k] > 1;
+    if (decomposed_or_periodic && len < c->cutneighmax)
+      return b200md_fail(c, B200MD_ERR_DOMAIN, "sub-domain (%g) thinner than the ghost cutoff (%g) in dim %d", len,
+                         c->cutneighmax, k);
+    int nb = (int) (len / target);
+    if (nb < 1) nb = 1;
+    while (nb > 1 && len / nb < c->cutneighmax * (1.0 + 1e-10)) nb--;
+    g.nbin[k] = nb;
+    g.mbin[k] = nb + 2 * BIN_MARGIN;
+    g.lo[k] = c->sublo[k];
+    g.inv[k] = nb / len;
+    mb *= g.mbin[k];
+  }
+  if (mb > 2000000000LL) return b200md_fail(c, B200MD_ERR_ARG, "too many bins");
+  g.mbins = (int) mb;
+  return B200MD_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// borders: single-stage ghost construction
+// ------------------------------------------------------------------------------------------------
+struct BorderGeom {
+  double lo_cut[3];   // sublo + cutghost : atoms with x <= this go to the low-side neighbor  (comm_brick.cpp:425-427)
+  double hi_cut[3];   // subhi - cutghost : atoms with x >= this go to the high-side neighbor (:454-455)
+  int send_lo[3], send_hi[3];  // whether a neighbor exists on that side (periodic or interior)
+};
+
+__device__ __forceinline__ unsigned border_mask(const BorderGeom &b, const double4 &p)
+{
+  int lo0 = b.send_lo[0] && p.x <= b.lo_cut[0], hi0 = b.send_hi[0] && p.x >= b.hi_cut[0];
+  int lo1 = b.send_lo[1] && p.y <= b.lo_cut[1], hi1 = b.send_hi[1] && p.y >= b.hi_cut[1];
+  int lo2 = b.send_lo[2] && p.z <= b.lo_cut[2], hi2 = b.send_hi[2] && p.z >= b.hi_cut[2];
+  if (!(lo0 | hi0 | lo1 | hi1 | lo2 | hi2)) return 0u;
+  unsigned m = 0;
+  int c = 0;
+#pragma unroll
+  for (int dz = -1; dz <= 1; dz++)
+#pragma unroll
+    for (int dy = -1; dy <= 1; dy++)
+#pragma unroll
+      for (int dx = -1; dx <= 1; dx++) {
+        if (dx == 0 && dy == 0 && dz == 0) continue;
+        int ok = (dx == 0 || (dx < 0 ? lo0 : hi0)) && (dy == 0 || (dy < 0 ? lo1 : hi1)) && (dz == 0 || (dz < 0 ? lo2 : hi2));
+        m |= (unsigned) ok << c;
+        c++;
+      }
+  return m;
+}
+
+#define BORDER_BLOCK 256
+__global__ void k_border_count(const double4 *__restrict__ pos, int n, BorderGeom bgm, int nblk, int *__restrict__ blockcnt)
+{
+  __shared__ int cnt[NDIR];
+  if (threadIdx.x < NDIR) cnt[threadIdx.x] = 0;
+  __syncthreads();
+  int i = blockIdx.x * BORDER_BLOCK + threadIdx.x;
+  unsigned m = 0;
+  if (i < n) m = border_mask(bgm, pos[i]);
+  if (__any_sync(0xffffffffu, m != 0)) {
+    for (int d = 0; d < NDIR; d++) {
+      unsigned b = __ballot_sync(0xffffffffu, (m >> d) & 1u);
+      if (b && (threadIdx.x & 31) == 0) atomicAdd(&cnt[d], __popc(b));
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < NDIR) blockcnt[threadIdx.x * nblk + blockIdx.x] = cnt[threadIdx.x];
+}
+
+// one block per direction: exclusive scan of that direction's per-block counts, total to totals[d]
+__global__ void k_border_scan(const int *__restrict__ blockcnt, int *__restrict__ blockoff, int nblk, int *__restrict__ totals)
+{
+  __shared__ int wsum[32];
+  __shared__ int carry_s;
+  int d = blockIdx.x;
+  const int *in = blockcnt + (size_t) d * nblk;
+  int *out = blockoff + (size_t) d * nblk;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int start = 0; start < nblk; start += blockDim.x) {
+    int i = start + threadIdx.x;
+    int t = (i < nblk) ? in[i] : 0;
+    int incl = t;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+    if (lane == 31) wsum[w] = incl;
+    __syncthreads();
+    int woff = 0;
+    for (int k = 0; k < w; k++) woff += wsum[k];
+    int carry = carry_s;
+    if (i < nblk) out[i] = carry + woff + incl - t;
+    __syncthreads();
+    if (threadIdx.x == blockDim.x - 1) carry_s = carry + woff + incl;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) totals[d] = carry_s;
+}
+
+__global__ void k_border_fill(const double4 *__restrict__ pos, int n, BorderGeom bgm, int nblk,
+                              const int *__restrict__ blockcnt, const int *__restrict__ blockoff, HaloPlan hp,
+                              int *__restrict__ send_idx)
+{
+  __shared__ int wcnt[BORDER_BLOCK / 32];
+  int i = blockIdx.x * BORDER_BLOCK + threadIdx.x;
+  unsigned m = 0;
+  if (i < n) m = border_mask(bgm, pos[i]);
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int d = 0; d < NDIR; d++) {
+    if (blockcnt[d * nblk + blockIdx.x] == 0) continue;  // block-uniform
+    unsigned b = __ballot_sync(0xffffffffu, (m >> d) & 1u);
+    if (lane == 0) wcnt[w] = __popc(b);
+    __syncthreads();
+    if ((m >> d) & 1u) {
+      int base = 0;
+      for (int k = 0; k < w; k++) base += wcnt[k];
+      int r = base + __popc(b & ((1u << lane) - 1u));
+      send_idx[hp.goff[d] + blockoff[d * nblk + blockIdx.x] + r] = i;
+    }
+    __syncthreads();
+  }
+}
+
+// create / refresh ghosts that come from this rank itself (periodic images): CommBrick::borders self-swap
+// (src/comm_brick.cpp:893-905) and forward_comm self-copy (:577-589); AtomVec::pack_border adds pbc*prd
+// (src/atom_vec.cpp:808-826)
+template <int WITH_TAG>
+__global__ void k_ghost_self(double4 *__restrict__ pos, int *__restrict__ tag, const int *__restrict__ ghost_src,
+                             signed char *__restrict__ ghost_dir, int nlocal, int nghost, HaloPlan hp)
+{
+  int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= nghost) return;
+  int d;
+  if (WITH_TAG) {
+    d = 0;
+    while (d < NDIR - 1 && g >= hp.goff[d + 1]) d++;
+    ghost_dir[g] = (signed char) d;
+  } else
+    d = ghost_dir[g];
+  int s = ghost_src[g];
+  double4 p = pos[s];
+  p.x += hp.shift[d][0];
+  p.y += hp.shift[d][1];
+  p.z += hp.shift[d][2];
+  pos[nlocal + g] = p;
+  if (WITH_TAG) tag[nlocal + g] = tag[s];
+}
+
+__global__ void k_ghost_scalar(double *__restrict__ a, const int *__restrict__ ghost_src, int nlocal, int nghost)
+{
+  int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g < nghost) a[nlocal + g] = a[ghost_src[g]];
+}
+
+static void dir_vec(int d, int v[3])
+{
+  int full = d < 13 ? d : d + 1;
+  v[0] = full % 3 - 1;
+  v[1] = (full / 3) % 3 - 1;
+  v[2] = full / 9 - 1;
+}
+
+static int borders(b200md_ctx *c)
+{
+  if (c->nranks != 1) return b200md_fail(c, B200MD_ERR_ARG, "multi-rank borders are handled in comm.cu");
+  const int n = c->nlocal;
+  BorderGeom bgm;
+  for (int k = 0; k < 3; k++) {
+    bgm.lo_cut[k] = c->sublo[k] + c->cutneighmax;
+    bgm.hi_cut[k] = c->subhi[k] - c->cutneighmax;
+    bgm.send_lo[k] = c->periodic[k] || c->myloc[k] > 0;
+    bgm.send_hi[k] = c->periodic[k] || c->myloc[k] < c->procgrid[k] - 1;
+  }
+  for (int d = 0; d < NDIR; d++) {
+    int dv[3];
+    dir_vec(d, dv);
+    for (int k = 0; k < 3; k++) {
+      double s = 0.0;
+      if (dv[k] < 0 && c->myloc[k] == 0) s = c->prd[k];
+      if (dv[k] > 0 && c->myloc[k] == c->procgrid[k] - 1) s = -c->prd[k];
+      c->hp.shift[d][k] = s;
+    }
+  }
+  int nblk = cdiv(n, BORDER_BLOCK);
+  if (nblk < 1) nblk = 1;
+  TRY(dev_ensure(c, c->border_blockcnt, (size_t) 2 * NDIR * nblk));
+  TRY(dev_ensure(c, c->border_total, NDIR));
+  int *cnt = c->border_blockcnt.p, *off = cnt + (size_t) NDIR * nblk;
+  k_border_count<<<nblk, BORDER_BLOCK, 0, c->stream>>>(c->pos.p, n, bgm, nblk, cnt);
+  LAUNCH_CHECK();
+  k_border_scan<<<NDIR, 1024, 0, c->stream>>>(cnt, off, nblk, c->border_total.p);
+  LAUNCH_CHECK();
+  CU(cudaMemcpyAsync(c->flags_h + 8, c->border_total.p, NDIR * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  int tot = 0;
+  for (int d = 0; d < NDIR; d++) {
+    c->sendcount[d] = c->flags_h[8 + d];
+    c->hp.goff[d] = tot;
+    tot += c->sendcount[d];
+  }
+  c->hp.goff[NDIR] = tot;
+  c->nghost = tot;
+  size_t nall = (size_t) n + tot;
+  TRY(dev_ensure(c, c->pos, nall, true));
+  TRY(dev_ensure(c, c->tag, nall, true));
+  TRY(dev_ensure(c, c->ghost_src, (size_t) tot + 1));
+  TRY(dev_ensure(c, c->ghost_dir, (size_t) tot + 1));
+  if (tot > 0) {
+    k_border_fill<<<nblk, BORDER_BLOCK, 0, c->stream>>>(c->pos.p, n, bgm, nblk, cnt, off, c->hp, c->ghost_src.p);
+    LAUNCH_CHECK();
+    k_ghost_self<1><<<cdiv(tot, 256), 256, 0, c->stream>>>(c->pos.p, c->tag.p, c->ghost_src.p, c->ghost_dir.p, n, tot, c->hp);
+    LAUNCH_CHECK();
+  }
+  return B200MD_OK;
+}
+
+int halo_forward_pos(b200md_ctx *c)
+{
+  if (c->nghost > 0) {
+    k_ghost_self<0><<<cdiv(c->nghost, 256), 256, 0, c->stream>>>(c->pos.p, c->tag.p, c->ghost_src.p, c->ghost_dir.p,
+                                                                   c->nlocal, c->nghost, c->hp);
+    LAUNCH_CHECK();
+  }
+  return B200MD_OK;
+}
+
+int halo_forward_scalar(b200md_ctx *c, double *a)
+{
+  if (c->nghost > 0) {
+    k_ghost_scalar<<<cdiv(c->nghost, 256), 256, 0, c->stream>>>(a, c->ghost_src.p, c->nlocal, c->nghost);
+    LAUNCH_CHECK();
+  }
+  return B200MD_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// neighbor build: full list, thread per owned atom, 9 contiguous x-rows of 3 bins each
+// distance test exactly as the reference: rsq = delx*delx + dely*dely + delz*delz (no FMA), keep if
+// rsq <= cutneighsq[itype][jtype] (src/npair_half_bin_atomonly_newton.cpp:80-87)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+k_build_full(const double4 *__restrict__ pos, int nlocal, BinGeom g, const int *__restrict__ bin_start,
+             const int *__restrict__ cell_list, const double *__restrict__ cutneighsq, int ntypes, int maxneigh,
+             int *__restrict__ numneigh, int *__restrict__ neigh, int *__restrict__ flags)
+{
+  extern __shared__ double s_cut[];
+  int nt1 = ntypes + 1;
+  for (int k = threadIdx.x; k < nt1 * nt1; k += blockDim.x) s_cut[k] = cutneighsq[k];
+  __syncthreads();
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nlocal) return;
+  const double4 pi = pos[i];
+  const int it = pos_type(pi);
+  const double *cut_i = s_cut + it * nt1;
+  int bx = min(max((int) floor((pi.x - g.lo[0]) * g.inv[0]) + BIN_MARGIN, 1), g.mbin[0] - 2);
+  int by = min(max((int) floor((pi.y - g.lo[1]) * g.inv[1]) + BIN_MARGIN, 1), g.mbin[1] - 2);
+  int bz = min(max((int) floor((pi.z - g.lo[2]) * g.inv[2]) + BIN_MARGIN, 1), g.mbin[2] - 2);
+  int *out = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
+  int n = 0;
+  for (int dz = -1; dz <= 1; dz++)
+    for (int dy = -1; dy <= 1; dy++) {
+      int row = ((bz + dz) * g.mbin[1] + (by + dy)) * g.mbin[0] + bx - 1;
+      int s = bin_start[row], e = bin_start[row + 3];
+      for (int k = s; k < e; k++) {
+        int j = cell_list[k];
+        double4 pj = pos[j];
+        double dx = __dsub_rn(pi.x, pj.x), dy2 = __dsub_rn(pi.y, pj.y), dz2 = __dsub_rn(pi.z, pj.z);
+        double rsq = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy2, dy2)), __dmul_rn(dz2, dz2));
+        if (rsq <= cut_i[pos_type(pj)] && j != i) {
+          if (n < maxneigh) out[(size_t) n * TILE] = j;
+          n++;
+        }
+      }
+    }
+  numneigh[i] = n;
+  unsigned am = __activemask();
+  int nmax = __reduce_max_sync(am, n);
+  if ((threadIdx.x & 31) == (__ffs(am) - 1)) atomicMax(&flags[1], nmax);  // flags[1] = longest list seen
+}
+
+__global__ void k_check_distance(const double4 *__restrict__ pos, const double4 *__restrict__ xhold, int n, double triggersq,
+                                 int *__restrict__ flags)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double4 a = pos[i], b = xhold[i];
+  double dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z;
+  double rsq = dx * dx + dy * dy + dz * dz;
+  if (rsq > triggersq) flags[2] = 1;
+}
+
+int neigh_check_distance(b200md_ctx *c, int *moved)
+{
+  CU(cudaMemsetAsync(c->flags_d + 2, 0, sizeof(int), c->stream));
+  k_check_distance<<<cdiv(c->nlocal, 256), 256, 0, c->stream>>>(c->pos.p, c->xhold.p, c->nlocal, c->triggersq, c->flags_d);
+  LAUNCH_CHECK();
+  CU(cudaMemcpyAsync(c->flags_h + 2, c->flags_d + 2, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  *moved = c->flags_h[2];
+  return B200MD_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// the whole reneighbor sequence
+// ------------------------------------------------------------------------------------------------
+int neigh_rebuild(b200md_ctx *c)
+{
+  const int n = c->nlocal;
+  if (n <= 0) return b200md_fail(c, B200MD_ERR_ARG, "no atoms uploaded");
+  TRY(neigh_setup_bins(c));
+  CU(cudaMemsetAsync(c->flags_d, 0, 4 * sizeof(int), c->stream));
+
+  // Domain::pbc
+  k_pbc<<<cdiv(n, 256), 256, 0, c->stream>>>(c->pos.p, c->image.p, n, make_double3(c->boxlo[0], c->boxlo[1], c->boxlo[2]),
+                                              make_double3(c->boxhi[0], c->boxhi[1], c->boxhi[2]),
+                                              make_double3(c->prd[0], c->prd[1], c->prd[2]), c->periodic[0], c->periodic[1],
+                                              c->periodic[2], c->flags_d);
+  LAUNCH_CHECK();
+
+  // spatial sort of owned atoms (Atom::sort) by neighbor bin
+  TRY(dev_ensure(c, c->perm, (size_t) n));
+  TRY(bin_sort(c, n, c->perm.p));
+  TRY(dev_ensure(c, c->pos_tmp, c->pos.n));
+  TRY(dev_ensure(c, c->tag_tmp, c->tag.n));
+  TRY(dev_ensure(c, c->image_tmp, c->image.n));
+  for (int k = 0; k < 3; k++) TRY(dev_ensure(c, c->v_tmp[k], c->v[k].n));
+  k_permute_owned<<<cdiv(n, 256), 256, 0, c->stream>>>(c->perm.p, n, c->pos.p, c->pos_tmp.p, c->v[0].p, c->v[1].p, c->v[2].p,
+                                                        c->v_tmp[0].p, c->v_tmp[1].p, c->v_tmp[2].p, c->tag.p, c->tag_tmp.p,
+                                                        c->image.p, c->image_tmp.p);
+  LAUNCH_CHECK();
+  std::swap(c->pos, c->pos_tmp);
+  std::swap(c->tag, c->tag_tmp);
+  std::swap(c->image, c->image_tmp);
+  for (int k = 0; k < 3; k++) std::swap(c->v[k], c->v_tmp[k]);
+
+  // ghosts
+  TRY(borders(c));
+  const int nall = n + c->nghost;
+
+  // bin owned + ghost
+  TRY(dev_ensure(c, c->cell_list, (size_t) nall));
+  TRY(bin_sort(c, nall, c->cell_list.p));
+
+  // per-atom arrays that follow nlocal / nall
+  TRY(dev_ensure(c, c->numneigh, (size_t) n));
+  for (int k = 0; k < 3; k++) TRY(dev_ensure(c, c->f[k], (size_t) n));
+  if (c->pair_style == 2) {
+    TRY(dev_ensure(c, c->rho, (size_t) n));
+    TRY(dev_ensure(c, c->fp, (size_t) nall));
+  }
+
+  if (c->maxneigh == 0) {
+    double vol = 1.0;
+    for (int k = 0; k < 3; k++) vol *= c->subhi[k] - c->sublo[k];
+    double expect = 4.18879020478639 * c->cutneighmax * c->cutneighmax * c->cutneighmax * n / vol;
+    int m = (int) (expect * 1.25) + 24;
+    c->maxneigh = (m + 7) / 8 * 8;
+  }
+  const int ntiles = cdiv(n, TILE);
+  for (int attempt = 0; attempt < 8; attempt++) {
+    TRY(dev_ensure(c, c->neigh, (size_t) ntiles * TILE * c->maxneigh));
+    size_t smem = (size_t) (c->ntypes + 1) * (c->ntypes + 1) * sizeof(double);
+    if (c->profile) CU(cudaEventRecord(c->ev0, c->stream));
+    k_build_full<<<cdiv(n, 128), 128, smem, c->stream>>>(c->pos.p, n, c->bg, c->bin_start.p, c->cell_list.p, c->cutneighsq_d.p,
+                                                          c->ntypes, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d);
+    LAUNCH_CHECK();
+    if (c->profile) CU(cudaEventRecord(c->ev1, c->stream));
+    CU(cudaMemcpyAsync(c->flags_h, c->flags_d, 4 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (c->profile) {
+      float ms = 0;
+      cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+      c->last_neigh_ms = ms;
+    }
+    if (c->flags_h[0]) return b200md_fail(c, B200MD_ERR_NONFINITE, "Non-numeric positions - simulation unstable");
+    c->maxneigh_seen = c->flags_h[1];
+    if (c->flags_h[1] > c->maxneigh) {  // "Neighbor list overflow": grow and redo instead of aborting
+      c->maxneigh = (c->flags_h[1] + c->flags_h[1] / 8 + 7) / 8 * 8;
+      CU(cudaMemsetAsync(c->flags_d + 1, 0, sizeof(int), c->stream));
+      continue;
+    }
+    break;
+  }
+  if (c->flags_h[1] > c->maxneigh) return b200md_fail(c, B200MD_ERR_NEIGH_OVERFLOW, "Neighbor list overflow");
+
+  if (c->dist_check) {
+    TRY(dev_ensure(c, c->xhold, (size_t) n));
+    CU(cudaMemcpyAsync(c->xhold.p, c->pos.p, (size_t) n * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
+  }
+  c->ago = 0;
+  c->nbuilds++;
+  c->list_valid = true;
+  return B200MD_OK;
+}

@@ -1,0 +1,217 @@
+// pair_eam.cu -- pair_style eam on the device: PairEAM::compute (src/MANYBODY/pair_eam.cpp:142-328).
+// The reference runs rho (half list + reverse_comm) -> fp -> forward_comm(fp) -> force (half list +
+// reverse_comm of f).  Here a FULL list makes rho_i and f_i complete on the owning thread, so the two
+// reverse_comms disappear; the sequence is
+//   k_eam_rho_fp : rho_i = sum_j rhor(r_ij), then fp_i = F'(rho_i) and the embedding energy, fused
+//                  (pair_eam.cpp:187-247)
+//   halo of fp   : ghost fp from their owners (pair_eam.cpp:251, pack/unpack :855-876)
+//   k_eam_force  : pair_eam.cpp:257-325
+// Spline rows are the reference's 7 coefficients per knot ([0..2] derivative, [3..6] value;
+// PairEAM::interpolate :769-797), 1-based knots m = 1..n, re-packed at init into 32-byte aligned pieces:
+//   rhoA[t][m]  = {c3,c4,c5,c6} of rhor_spline            (pass A reads one double4)
+//   tabC[t][m]  = {r0,r1,r2,-} {z0,z1,z2,z3} {z4,z5,z6,-}  only for the single-type fast path
+#include "ctx.cuh"
+
+__device__ __forceinline__ double4 ld4(const double4 *__restrict__ p)
+{
+  const double2 *q = reinterpret_cast<const double2 *>(p);
+  double2 a = __ldg(q), b = __ldg(q + 1);
+  return make_double4(a.x, a.y, b.x, b.y);
+}
+
+__device__ __forceinline__ double4 ld_pos_e(const double4 *__restrict__ pos, int j) { return ld4(pos + j); }
+
+__device__ __forceinline__ double warp_sum_e(double v)
+{
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  return v;
+}
+
+template <int NC> __device__ __forceinline__ void block_partials_e(double (&acc)[NC], double *__restrict__ partials)
+{
+  __shared__ double s_red[32][NC];
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+#pragma unroll
+  for (int c = 0; c < NC; c++) {
+    double v = warp_sum_e(acc[c]);
+    if (lane == 0) s_red[w][c] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < NC) {
+    double t = 0.0;
+    for (int k = 0; k < nw; k++) t += s_red[k][threadIdx.x];
+    partials[(size_t) blockIdx.x * 8 + threadIdx.x] = t;
+  }
+}
+
+struct EAMParams {
+  int ntypes, nrho, nr;
+  double rdrho, rdr, rhomax, cutforcesq;
+  const double *frho;      // [nfrho][nrho+1][7]
+  const double *rhor;      // [nrhor][nr+1][7]
+  const double *z2r;       // [nz2r][nr+1][7]
+  const double4 *rhoA;     // [nrhor][nr+1]
+  const int *type2frho, *type2rhor, *type2z2r;
+};
+
+template <int EFLAG, int ONETYPE>
+__global__ void __launch_bounds__(128)
+k_eam_rho_fp(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
+             int nlocal, EAMParams P, double *__restrict__ rho_out, double *__restrict__ fp_out, double *__restrict__ partials)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  double acc[1] = {0.0};
+  if (i < nlocal) {
+    const double4 pi = pos[i];
+    const int it = pos_type(pi);
+    const int n = numneigh[i];
+    const int nt1 = P.ntypes + 1;
+    const int *nb = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
+    double rho = 0.0;
+#pragma unroll 4
+    for (int k = 0; k < n; k++) {
+      const int j = __ldcs(nb + (size_t) k * TILE) & NEIGHMASK;
+      const double4 pj = ld_pos_e(pos, j);
+      const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+      const double rsq = dx * dx + dy * dy + dz * dz;
+      if (rsq < P.cutforcesq) {
+        double p = sqrt(rsq) * P.rdr + 1.0;
+        int m = (int) p;
+        m = min(m, P.nr - 1);
+        p -= m;
+        p = fmin(p, 1.0);
+        const int tab = ONETYPE ? 0 : P.type2rhor[pos_type(pj) * nt1 + it];
+        const double4 cf = ld4(P.rhoA + (size_t) tab * (P.nr + 1) + m);
+        rho += ((cf.x * p + cf.y) * p + cf.z) * p + cf.w;
+      }
+    }
+    // pass B (pair_eam.cpp:231-247)
+    double p = rho * P.rdrho + 1.0;
+    int m = (int) p;
+    m = max(1, min(m, P.nrho - 1));
+    p -= m;
+    p = fmin(p, 1.0);
+    const double *cf = P.frho + ((size_t) (ONETYPE ? 0 : P.type2frho[it]) * (P.nrho + 1) + m) * 7;
+    const double fpi = (__ldg(cf) * p + __ldg(cf + 1)) * p + __ldg(cf + 2);
+    rho_out[i] = rho;
+    fp_out[i] = fpi;
+    if (EFLAG) {
+      double phi = ((__ldg(cf + 3) * p + __ldg(cf + 4)) * p + __ldg(cf + 5)) * p + __ldg(cf + 6);
+      if (rho > P.rhomax) phi += fpi * (rho - P.rhomax);
+      acc[0] = phi;
+    }
+  }
+  if (EFLAG) block_partials_e<1>(acc, partials);
+}
+
+template <int EVFLAG, int ONETYPE>
+__global__ void __launch_bounds__(128)
+k_eam_force(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
+            int nlocal, EAMParams P, const double *__restrict__ fp, double *__restrict__ fx, double *__restrict__ fy,
+            double *__restrict__ fz, double *__restrict__ partials)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  if (i < nlocal) {
+    const double4 pi = pos[i];
+    const int it = pos_type(pi);
+    const int n = numneigh[i];
+    const int nt1 = P.ntypes + 1;
+    const double fpi = fp[i];
+    const int *nb = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
+    double fxi = 0.0, fyi = 0.0, fzi = 0.0;
+#pragma unroll 2
+    for (int k = 0; k < n; k++) {
+      const int j = __ldcs(nb + (size_t) k * TILE) & NEIGHMASK;
+      const double4 pj = ld_pos_e(pos, j);
+      const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+      const double rsq = dx * dx + dy * dy + dz * dz;
+      if (rsq < P.cutforcesq) {
+        const double r = sqrt(rsq);
+        double p = r * P.rdr + 1.0;
+        int m = (int) p;
+        m = min(m, P.nr - 1);
+        p -= m;
+        p = fmin(p, 1.0);
+        int t_ij = 0, t_ji = 0, t_z = 0;
+        if (!ONETYPE) {
+          const int jt = pos_type(pj);
+          t_ij = P.type2rhor[it * nt1 + jt];
+          t_ji = P.type2rhor[jt * nt1 + it];
+          t_z = P.type2z2r[it * nt1 + jt];
+        }
+        const double *c1 = P.rhor + ((size_t) t_ij * (P.nr + 1) + m) * 7;
+        const double rhoip = (__ldg(c1) * p + __ldg(c1 + 1)) * p + __ldg(c1 + 2);
+        double rhojp = rhoip;
+        if (!ONETYPE) {
+          const double *c2 = P.rhor + ((size_t) t_ji * (P.nr + 1) + m) * 7;
+          rhojp = (__ldg(c2) * p + __ldg(c2 + 1)) * p + __ldg(c2 + 2);
+        }
+        const double *c3 = P.z2r + ((size_t) t_z * (P.nr + 1) + m) * 7;
+        const double z2p = (__ldg(c3) * p + __ldg(c3 + 1)) * p + __ldg(c3 + 2);
+        const double z2 = ((__ldg(c3 + 3) * p + __ldg(c3 + 4)) * p + __ldg(c3 + 5)) * p + __ldg(c3 + 6);
+        const double recip = 1.0 / r;
+        const double phi = z2 * recip;
+        const double phip = z2p * recip - phi * recip;
+        const double psip = fpi * rhojp + __ldg(fp + j) * rhoip + phip;
+        const double fpair = -psip * recip;
+        fxi += dx * fpair;
+        fyi += dy * fpair;
+        fzi += dz * fpair;
+        if (EVFLAG) {
+          acc[0] += 0.5 * phi;
+          const double hf = 0.5 * fpair;
+          acc[1] += dx * dx * hf;
+          acc[2] += dy * dy * hf;
+          acc[3] += dz * dz * hf;
+          acc[4] += dx * dy * hf;
+          acc[5] += dx * dz * hf;
+          acc[6] += dy * dz * hf;
+        }
+      }
+    }
+    fx[i] = fxi;
+    fy[i] = fyi;
+    fz[i] = fzi;
+  }
+  if (EVFLAG) block_partials_e<7>(acc, partials);
+}
+
+int pair_eam_compute(b200md_ctx *c, int eflag, int vflag)
+{
+  const int n = c->nlocal;
+  const int threads = 128, blocks = cdiv(n, threads);
+  const int ev = (eflag || vflag) ? 1 : 0;
+  if (ev) TRY(dev_ensure(c, c->partials, (size_t) blocks * 8));
+  const EAMTables &T = c->eam;
+  EAMParams P = {T.ntypes, T.nrho, T.nr, T.rdrho, T.rdr, T.rhomax, T.cutforcesq, T.frho, T.rhor, T.z2r, T.rhoA,
+                 T.type2frho, T.type2rhor, T.type2z2r};
+  const int onetype = (T.ntypes == 1 && T.nrhor == 1 && T.nz2r == 1);
+  if (c->profile) CU(cudaEventRecord(c->ev0, c->stream));
+#define A_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, c->rho.p, c->fp.p, c->partials.p
+  if (ev) {
+    if (onetype) k_eam_rho_fp<1, 1><<<blocks, threads, 0, c->stream>>>(A_ARGS);
+    else k_eam_rho_fp<1, 0><<<blocks, threads, 0, c->stream>>>(A_ARGS);
+  } else {
+    if (onetype) k_eam_rho_fp<0, 1><<<blocks, threads, 0, c->stream>>>(A_ARGS);
+    else k_eam_rho_fp<0, 0><<<blocks, threads, 0, c->stream>>>(A_ARGS);
+  }
+#undef A_ARGS
+  LAUNCH_CHECK();
+  if (ev) TRY(reduce_partials(c, blocks, 1, 8));  // embedding energy -> red_d[8]
+  TRY(halo_forward_scalar(c, c->fp.p));
+#define C_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, c->fp.p, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p
+  if (ev) {
+    if (onetype) k_eam_force<1, 1><<<blocks, threads, 0, c->stream>>>(C_ARGS);
+    else k_eam_force<1, 0><<<blocks, threads, 0, c->stream>>>(C_ARGS);
+  } else {
+    if (onetype) k_eam_force<0, 1><<<blocks, threads, 0, c->stream>>>(C_ARGS);
+    else k_eam_force<0, 0><<<blocks, threads, 0, c->stream>>>(C_ARGS);
+  }
+#undef C_ARGS
+  LAUNCH_CHECK();
+  if (c->profile) CU(cudaEventRecord(c->ev1, c->stream));
+  if (ev) TRY(reduce_partials(c, blocks, 7, 0));  // pair energy + virial -> red_d[0..6]; eng = red[0] + red[8]
+  return B200MD_OK;
+}

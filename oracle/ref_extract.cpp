@@ -33,6 +33,9 @@ int main(int argc, char **argv)
   for (int i = 3; i < argc; i++) largs.push_back(argv[i]);
   void *lmp = lammps_open_no_mpi((int) largs.size(), largs.data(), nullptr);
   if (!lmp) return 2;
+  // the library constructor only records "-in file"; main() is what normally runs it (src/main.cpp:77)
+  for (int i = 3; i + 1 < argc; i++)
+    if (std::string(argv[i]) == "-in" || std::string(argv[i]) == "-i") lammps_file(lmp, argv[i + 1]);
 
   int nlocal = lammps_extract_setting(lmp, "nlocal");
   int nghost = lammps_extract_setting(lmp, "nghost");
