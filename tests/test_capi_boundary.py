@@ -1,0 +1,106 @@
+"""The drop-in boundary without a GPU: libb200md.so builds, loads, exports every symbol include/b200md.h
+declares, refuses to work without a device (no CPU fallback), and the product never touches oracle/."""
+from __future__ import annotations
+
+import ctypes as C
+import re
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parents[1]
+HEADER = ROOT / "include" / "b200md.h"
+PKG_DIR = ROOT / "lammps-fugaku-threadpool_b200"
+
+
+def header_symbols():
+    text = re.sub(r"/\*.*?\*/", "", HEADER.read_text(), flags=re.S)
+    return sorted(set(re.findall(r"\b(b200md_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_symbols_exported(pkg):
+    L = pkg.lib.load()
+    names = header_symbols()
+    assert len(names) >= 30
+    for n in names:
+        assert hasattr(L, n), f"{n} declared in include/b200md.h but not exported by libb200md.so"
+
+
+def test_ctypes_prototypes_cover_header(pkg):
+    assert sorted(pkg.lib.PROTOTYPES) == header_symbols()
+
+
+def test_no_cpu_fallback_without_device(pkg):
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(pkg.lib.B200MDError) as e:
+        pkg.lib.Context(0)
+    assert e.value.code == 4  # B200MD_ERR_CUDA
+    assert "no CPU fallback" in str(e.value)
+
+
+def test_null_context_is_an_error_not_a_crash(pkg):
+    L = pkg.lib.load()
+    assert L.b200md_set_units(None, 1.0, 1.0, 1.0, 1.0) == 5  # B200MD_ERR_ARG
+    assert L.b200md_nlocal(None) == 0
+    assert L.b200md_destroy(None) == 0
+
+
+def test_product_never_imports_oracle():
+    """Only tests/, __graft_entry__.smoke() and bench.py's cpu legs may use oracle/."""
+    bad = []
+    for p in list(PKG_DIR.rglob("*.py")) + list(PKG_DIR.rglob("*.cu")) + list(PKG_DIR.rglob("*.cuh")) + \
+            list((ROOT / "include").rglob("*.h")):
+        t = p.read_text()
+        if re.search(r"^\s*(import|from)\s+oracle\b", t, flags=re.M) or "liboracle" in t or "oracle/" in t.replace(
+                "nothing here touches oracle/", ""):
+            bad.append(str(p))
+    assert not bad, bad
+
+
+def test_lj_init_one_tables_match_oracle_semantics(pkg):
+    """PairLJCutB200.init mirrors PairLJCut::init_one (src/pair_lj_cut.cpp:501-557): arithmetic mixing + shift."""
+    class Rec:
+        def __init__(self):
+            self.calls = []
+
+        def call(self, name, *a):
+            self.calls.append(name)
+
+    class Owner:
+        ntypes = 2
+        ctx = Rec()
+
+    p = pkg.PairLJCutB200(Owner())
+    p.settings(2.5)
+    p.coeff(1, 1, 1.0, 1.0, 2.5)
+    p.coeff(2, 2, 0.8, 1.1, 2.2)
+    p.modify(shift=True, mix="arithmetic")
+    cut = p.init()
+    t = p.tables
+    e12, s12, c12 = np.sqrt(0.8), 1.05, 2.35
+    assert cut[1, 2] == pytest.approx(c12, rel=1e-15)
+    assert t["lj1"][1, 2] == pytest.approx(48 * e12 * s12 ** 12, rel=1e-14)
+    assert t["lj4"][2, 1] == pytest.approx(4 * e12 * s12 ** 6, rel=1e-14)
+    assert t["offset"][1, 2] == pytest.approx(4 * e12 * ((s12 / c12) ** 12 - (s12 / c12) ** 6), rel=1e-13)
+    assert Owner.ctx.calls == ["b200md_lj_init"]
+    with pytest.raises(ValueError):
+        p.coeff(3, 1, 1.0, 1.0)
+
+
+def test_inputs_match_oracle_lattice_and_velocities(pkg, oracle):
+    """inputs.py (numpy, product side) == oracle.c (C restatement) bit for bit: lattice, tags, loop-geom velocities."""
+    inp = pkg.inputs
+    a = inp.lattice_scale_lj(0.8442)
+    assert a == oracle.lattice_scale_lj(0.8442)
+    x, cell = inp.fcc_lattice(4, 3, 5, a)
+    tag = inp.fcc_tags(cell, 4, 3)
+    xo, to = oracle.create_fcc(4, 3, 5, a)
+    assert np.array_equal(x, xo) and np.array_equal(tag, to)
+    m = np.ones(len(x))
+    v = inp.velocity_create_geom(x, m, 1.44, 87287, "lj")
+    vo = oracle.velocity_create_geom(x, np.ones(len(x), dtype=np.int32), np.array([0.0, 1.0]), 1.44, 87287, "lj")
+    np.testing.assert_allclose(v, vo, rtol=1e-13, atol=1e-15)

@@ -1,0 +1,89 @@
+"""Pin the oracle (oracle/oracle.c, the CPU restatement) against fixtures minted from the UNMODIFIED
+reference (tests/golden/*.npz, see make_golden.py) and against the reference's shipped benchmark logs
+(bench/log.6Oct16.lj.fixed.icc.1:51-52, bench/log.6Oct16.eam.fixed.icc.1:54-56).  CPU only."""
+from __future__ import annotations
+
+import numpy as np
+import pytest
+
+from conftest import CASES, POT, load_golden, make_oracle_system, thermo_vec
+
+NAMES = list(CASES)
+
+
+def _undirected(pairs3):
+    u = np.sort(pairs3[:, :2], axis=1)
+    return u[np.lexsort((u[:, 1], u[:, 0]))]
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_oracle_state_a(oracle, name):
+    """Fresh neighbor list + forces at the thermalised golden positions: list bit-exact as tag pairs,
+    forces <= 1e-10 of max|f|, PE/KE/P <= 1e-9 relative."""
+    g = load_golden(name)
+    s = make_oracle_system(oracle, name, g)
+    s.setup()
+    assert s.nghost == int(g["a_nghost"][0])
+    assert np.array_equal(_undirected(s.pairs()), g["a_pairs"])
+    a = s.atoms()
+    o = np.argsort(a["tag"])
+    fmax = np.abs(g["a_f"]).max()
+    assert np.abs(a["f"][o] - g["a_f"]).max() <= 1e-10 * fmax
+    np.testing.assert_allclose(thermo_vec(s.thermo()), g["a_thermo"][:3], rtol=1e-9)
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_oracle_trajectory(oracle, name):
+    """nmore Verlet steps with reneighboring from state a reproduce state b (x, v and thermo)."""
+    g = load_golden(name)
+    s = make_oracle_system(oracle, name, g)
+    s.setup()
+    s.run(int(g["nmore"][0]))
+    a = s.atoms()
+    o = np.argsort(a["tag"])
+    assert np.array_equal(a["tag"][o], g["b_tag"])
+    # trajectories are chaotic: a 1-ulp difference in summation order grows ~1e-16 -> 1e-9 over tens of steps
+    box = g["boxhi"] - g["boxlo"]
+    dx = a["x"][o] - g["b_x"]
+    dx -= box * np.round(dx / box)
+    assert np.abs(dx).max() < 1e-7
+    np.testing.assert_allclose(thermo_vec(s.thermo()), g["b_thermo"][:3], rtol=1e-6)
+
+
+def test_oracle_bench_lj_log(oracle):
+    """bench/in.lj at its shipped size for 20 steps is too slow for the suite; 32k atoms, step 0 only:
+    T, E_pair, TotEng, Press printed by the reference's 2016 log (per-atom, `lj` units)."""
+    s = oracle.make_lj_system(20)
+    s.setup()
+    t = s.thermo()
+    n = 32000
+    assert abs(t["temp"] - 1.44) < 5e-9
+    assert abs(t["pe"] / n - (-6.7733681)) < 5e-8
+    assert abs((t["pe"] + t["ke"]) / n - (-4.6134356)) < 5e-8
+    assert abs(t["press"] - (-5.0197073)) < 5e-8
+    b = s.bin_info()
+    assert (b["nbinx"], b["nstencil"]) == (23, 62)
+
+
+def test_oracle_bench_eam_log(oracle):
+    s = oracle.make_eam_system(str(POT), 20)
+    s.setup()
+    t = s.thermo()
+    assert abs(t["temp"] - 1600.0) < 5e-6
+    assert abs(t["pe"] - (-113280.0)) < 0.5
+    assert abs(t["pe"] + t["ke"] - (-106662.09)) < 5e-3
+    assert abs(t["press"] - 18703.573) < 5e-4
+    assert s.bin_info()["nbinx"] == 24
+
+
+def test_oracle_eam_tables_match_funcfl_header(oracle):
+    """Cu_u3.eam header: nrho = nr = 500, drho = 5.01e-4, dr = 1e-2, cut = 4.95 (bench/Cu_u3.eam:2-3); the
+    re-gridded tables have nr = int(rmax/dr + 0.5) = 499 knots (src/MANYBODY/pair_eam.cpp:559-560)."""
+    s = oracle.OracleSystem(1, "metal")
+    s.set_neighbor(1.0)
+    s.pair_eam({1: str(POT)})
+    t = s.eam_tables()
+    assert (t["nrho"], t["nr"]) == (499, 499)
+    assert abs(t["cutmax"] - 4.95) < 1e-12
+    assert abs(1.0 / t["rdr"] - 0.01) < 1e-12
+    assert abs(s.mass(1) - 63.55) < 1e-12
