@@ -168,10 +168,16 @@ int b200md_step_host(b200md_ctx *ctx, double dt, int eflag, int vflag, double *x
  * reference's Timer (src/timer.h:23-42): [0]=Pair [1]=Neigh [2]=Comm [3]=Modify [4]=Other;
  * counts kernels launched by this library since the last reset. */
 int b200md_timers(b200md_ctx *ctx, double ms[5], int64_t *kernel_launches, int reset);
-/* CUDA-event time of the most recent pair kernel / neighbor-build kernel launch (ms) */
-int b200md_last_kernel_ms(b200md_ctx *ctx, double *pair_ms, double *neigh_ms);
-/* opt-in per-kernel event timing (adds two event records per launch) */
-int b200md_profile(b200md_ctx *ctx, int on);
+/* opt-in timing level: 0 off; 1 = two CUDA-event records around each timed kernel on the launching stream,
+ * no host synchronisation (resolved when read); 2 = also the section timers above (blocking). */
+int b200md_profile(b200md_ctx *ctx, int level);
+/* summed CUDA-event duration (ms) and launch count per kernel class since the last reset:
+ * [0] pair force kernel (lj/cut, or the eam force pass) [1] eam rho+fp pass [2] neighbor-build kernel
+ * [3] nve kernels [4] halo gather [5] bin sort + permute.  Arrays of 6. */
+int b200md_kernel_times(b200md_ctx *ctx, double *ms, int64_t *count, int reset);
+/* the cudaStream_t all of this context's work is issued on (for callers that record their own events
+ * or order their own kernels against the library's, as KOKKOS styles do with their execution space) */
+void *b200md_stream(b200md_ctx *ctx);
 
 #ifdef __cplusplus
 }

@@ -53,8 +53,6 @@ extern "C" int b200md_create(b200md_ctx **out, int device, int nranks, int rank,
   strcpy(c->err, "no error");
   *out = c;
   CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-  CU(cudaEventCreate(&c->ev0));
-  CU(cudaEventCreate(&c->ev1));
   CU(cudaMalloc((void **) &c->red_d, 32 * sizeof(double)));
   CU(cudaMemset(c->red_d, 0, 32 * sizeof(double)));
   CU(cudaMallocHost((void **) &c->red_h, 32 * sizeof(double)));
@@ -92,8 +90,7 @@ extern "C" int b200md_destroy(b200md_ctx *c)
   if (c->red_h) cudaFreeHost(c->red_h);
   if (c->flags_d) cudaFree(c->flags_d);
   if (c->flags_h) cudaFreeHost(c->flags_h);
-  if (c->ev0) cudaEventDestroy(c->ev0);
-  if (c->ev1) cudaEventDestroy(c->ev1);
+  for (auto &e : c->kev) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
   return B200MD_OK;
@@ -474,11 +471,11 @@ struct Sect {  // accumulates device time per Timer section when profiling is on
   cudaEvent_t a = nullptr, b = nullptr;
   Sect(b200md_ctx *ctx, int w) : c(ctx), which(w)
   {
-    if (c->profile) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, c->stream); }
+    if (c->profile >= 2) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, c->stream); }
   }
   ~Sect()
   {
-    if (c->profile) {
+    if (c->profile >= 2) {
       cudaEventRecord(b, c->stream);
       cudaEventSynchronize(b);
       float ms = 0;
@@ -498,12 +495,6 @@ static int force_compute(b200md_ctx *c, int eflag, int vflag)
   if (c->pair_style == 1) TRY(pair_lj_compute(c, eflag, vflag));
   else if (c->pair_style == 2) TRY(pair_eam_compute(c, eflag, vflag));
   else return b200md_fail(c, B200MD_ERR_ARG, "no pair style defined");
-  if (c->profile) {
-    CU(cudaEventSynchronize(c->ev1));
-    float ms = 0;
-    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-    c->last_pair_ms = ms;
-  }
   if (eflag || vflag) {
     CU(cudaMemcpyAsync(c->red_h, c->red_d, 9 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
@@ -687,17 +678,38 @@ extern "C" int b200md_timers(b200md_ctx *c, double ms[5], int64_t *kernel_launch
   return B200MD_OK;
 }
 
-extern "C" int b200md_last_kernel_ms(b200md_ctx *c, double *pair_ms, double *neigh_ms)
+void kprof_drain(b200md_ctx *c)
+{
+  if (c->kev_used == 0) return;
+  cudaStreamSynchronize(c->stream);
+  for (size_t k = 0; k < c->kev_used; k++) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, c->kev[k].a, c->kev[k].b) == cudaSuccess) {
+      c->kc_ms[c->kev[k].cls] += ms;
+      c->kc_count[c->kev[k].cls]++;
+    }
+  }
+  c->kev_used = 0;
+}
+
+extern "C" int b200md_kernel_times(b200md_ctx *c, double *ms, int64_t *count, int reset)
 {
   NEED_CTX();
-  if (pair_ms) *pair_ms = c->last_pair_ms;
-  if (neigh_ms) *neigh_ms = c->last_neigh_ms;
+  kprof_drain(c);
+  for (int k = 0; k < KC_N; k++) {
+    if (ms) ms[k] = c->kc_ms[k];
+    if (count) count[k] = c->kc_count[k];
+    if (reset) { c->kc_ms[k] = 0.0; c->kc_count[k] = 0; }
+  }
   return B200MD_OK;
 }
 
-extern "C" int b200md_profile(b200md_ctx *c, int on)
+extern "C" int b200md_profile(b200md_ctx *c, int level)
 {
   NEED_CTX();
-  c->profile = on != 0;
+  kprof_drain(c);
+  c->profile = level < 0 ? 0 : level;
   return B200MD_OK;
 }
+
+extern "C" void *b200md_stream(b200md_ctx *c) { return c ? (void *) c->stream : nullptr; }

@@ -16,6 +16,8 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <vector>
+
 #include "../../include/b200md.h"
 
 #define NEIGHMASK 0x1FFFFFFF  // src/lmptype.h:61-65
@@ -65,6 +67,10 @@ struct EAMTables {            // what PairEAM::array2spline produces (src/MANYBO
   int *type2frho, *type2rhor, *type2z2r;  // device
   int h_type2frho[B200MD_MAXTYPES + 1];
 };
+
+// kernel classes for the event timers (b200md_kernel_times)
+enum { KC_PAIR = 0, KC_EAM_RHO = 1, KC_NEIGH = 2, KC_NVE = 3, KC_HALO = 4, KC_SORT = 5, KC_N = 6 };
+struct KEvent { cudaEvent_t a, b; int cls; };
 
 struct b200md_ctx {
   int device = 0, nranks = 1, rank = 0;
@@ -132,12 +138,15 @@ struct b200md_ctx {
   int64_t ntimestep = 0;
   bool setup_done = false;
 
-  // instrumentation
+  // instrumentation: level 1 = per-kernel-class CUDA events recorded on `stream` without any host sync
+  // (pairs are parked in a ring and resolved when read), level 2 = also the blocking per-section timers
   double sect_ms[5] = {0, 0, 0, 0, 0};
   int64_t launches = 0;
-  bool profile = false;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  double last_pair_ms = 0, last_neigh_ms = 0;
+  int profile = 0;
+  std::vector<KEvent> kev;
+  size_t kev_used = 0;
+  double kc_ms[KC_N] = {0, 0, 0, 0, 0, 0};
+  int64_t kc_count[KC_N] = {0, 0, 0, 0, 0, 0};
   double bytes_held = 0;
 
   // host-buffer mode staging
@@ -199,6 +208,33 @@ template <class T> void dev_free(b200md_ctx *c, DevBuf<T> &b)
 }
 
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+// per-kernel-class timing scope: two event records on the launching stream, no host synchronisation
+void kprof_drain(b200md_ctx *c);
+struct KProf {
+  b200md_ctx *c;
+  KEvent *e = nullptr;
+  KProf(b200md_ctx *ctx, int cls) : c(ctx)
+  {
+    if (!c->profile) return;
+    if (c->kev_used == c->kev.size()) {
+      if (c->kev.size() >= 16384) kprof_drain(c);
+      else {
+        KEvent n;
+        n.cls = cls;
+        if (cudaEventCreate(&n.a) != cudaSuccess || cudaEventCreate(&n.b) != cudaSuccess) return;
+        c->kev.push_back(n);
+      }
+    }
+    e = &c->kev[c->kev_used++];
+    e->cls = cls;
+    cudaEventRecord(e->a, c->stream);
+  }
+  ~KProf()
+  {
+    if (e) cudaEventRecord(e->b, c->stream);
+  }
+};
 
 // section timers (names as src/timer.h:23-42)
 enum { SECT_PAIR = 0, SECT_NEIGH = 1, SECT_COMM = 2, SECT_MODIFY = 3, SECT_OTHER = 4 };

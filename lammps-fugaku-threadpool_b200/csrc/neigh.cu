@@ -427,6 +427,7 @@ static int borders(b200md_ctx *c)
 int halo_forward_pos(b200md_ctx *c)
 {
   if (c->nghost > 0) {
+    KProf kp(c, KC_HALO);
     k_ghost_self<0><<<cdiv(c->nghost, 256), 256, 0, c->stream>>>(c->pos.p, c->tag.p, c->ghost_src.p, c->ghost_dir.p,
                                                                    c->nlocal, c->nghost, c->hp);
     LAUNCH_CHECK();
@@ -437,6 +438,7 @@ int halo_forward_pos(b200md_ctx *c)
 int halo_forward_scalar(b200md_ctx *c, double *a)
 {
   if (c->nghost > 0) {
+    KProf kp(c, KC_HALO);
     k_ghost_scalar<<<cdiv(c->nghost, 256), 256, 0, c->stream>>>(a, c->ghost_src.p, c->nlocal, c->nghost);
     LAUNCH_CHECK();
   }
@@ -570,18 +572,14 @@ int neigh_rebuild(b200md_ctx *c)
   for (int attempt = 0; attempt < 8; attempt++) {
     TRY(dev_ensure(c, c->neigh, (size_t) ntiles * TILE * c->maxneigh));
     size_t smem = (size_t) (c->ntypes + 1) * (c->ntypes + 1) * sizeof(double);
-    if (c->profile) CU(cudaEventRecord(c->ev0, c->stream));
+    {
+    KProf kp(c, KC_NEIGH);
     k_build_full<<<cdiv(n, 128), 128, smem, c->stream>>>(c->pos.p, n, c->bg, c->bin_start.p, c->cell_list.p, c->cutneighsq_d.p,
                                                           c->ntypes, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d);
     LAUNCH_CHECK();
-    if (c->profile) CU(cudaEventRecord(c->ev1, c->stream));
+    }
     CU(cudaMemcpyAsync(c->flags_h, c->flags_d, 4 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
-    if (c->profile) {
-      float ms = 0;
-      cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-      c->last_neigh_ms = ms;
-    }
     if (c->flags_h[0]) return b200md_fail(c, B200MD_ERR_NONFINITE, "Non-numeric positions - simulation unstable");
     c->maxneigh_seen = c->flags_h[1];
     if (c->flags_h[1] > c->maxneigh) {  // "Neighbor list overflow": grow and redo instead of aborting

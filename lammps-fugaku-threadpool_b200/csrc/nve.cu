@@ -85,6 +85,7 @@ k_ke(const double4 *__restrict__ pos, const double *__restrict__ vx, const doubl
 int nve_initial(b200md_ctx *c, double dtv, double dtf)
 {
   const int n = c->nlocal;
+  KProf kp(c, KC_NVE);
   k_nve_initial<<<cdiv(n, 256), 256, 0, c->stream>>>(c->pos.p, c->v[0].p, c->v[1].p, c->v[2].p, c->f[0].p, c->f[1].p,
                                                       c->f[2].p, c->mass_d.p, n, dtv, dtf);
   LAUNCH_CHECK();
@@ -94,6 +95,7 @@ int nve_initial(b200md_ctx *c, double dtv, double dtf)
 int nve_final(b200md_ctx *c, double dtf)
 {
   const int n = c->nlocal;
+  KProf kp(c, KC_NVE);
   k_nve_final<<<cdiv(n, 256), 256, 0, c->stream>>>(c->pos.p, c->v[0].p, c->v[1].p, c->v[2].p, c->f[0].p, c->f[1].p, c->f[2].p,
                                                     c->mass_d.p, n, dtf);
   LAUNCH_CHECK();
@@ -103,6 +105,7 @@ int nve_final(b200md_ctx *c, double dtf)
 int nve_final_initial(b200md_ctx *c, double dtv, double dtf)
 {
   const int n = c->nlocal;
+  KProf kp(c, KC_NVE);
   k_nve_final_initial<<<cdiv(n, 256), 256, 0, c->stream>>>(c->pos.p, c->v[0].p, c->v[1].p, c->v[2].p, c->f[0].p, c->f[1].p,
                                                             c->f[2].p, c->mass_d.p, n, dtv, dtf);
   LAUNCH_CHECK();

@@ -188,7 +188,8 @@ int pair_eam_compute(b200md_ctx *c, int eflag, int vflag)
   EAMParams P = {T.ntypes, T.nrho, T.nr, T.rdrho, T.rdr, T.rhomax, T.cutforcesq, T.frho, T.rhor, T.z2r, T.rhoA,
                  T.type2frho, T.type2rhor, T.type2z2r};
   const int onetype = (T.ntypes == 1 && T.nrhor == 1 && T.nz2r == 1);
-  if (c->profile) CU(cudaEventRecord(c->ev0, c->stream));
+  {
+  KProf kp(c, KC_EAM_RHO);
 #define A_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, c->rho.p, c->fp.p, c->partials.p
   if (ev) {
     if (onetype) k_eam_rho_fp<1, 1><<<blocks, threads, 0, c->stream>>>(A_ARGS);
@@ -199,8 +200,11 @@ int pair_eam_compute(b200md_ctx *c, int eflag, int vflag)
   }
 #undef A_ARGS
   LAUNCH_CHECK();
+  }
   if (ev) TRY(reduce_partials(c, blocks, 1, 8));  // embedding energy -> red_d[8]
   TRY(halo_forward_scalar(c, c->fp.p));
+  {
+  KProf kp(c, KC_PAIR);
 #define C_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, c->fp.p, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p
   if (ev) {
     if (onetype) k_eam_force<1, 1><<<blocks, threads, 0, c->stream>>>(C_ARGS);
@@ -211,7 +215,7 @@ int pair_eam_compute(b200md_ctx *c, int eflag, int vflag)
   }
 #undef C_ARGS
   LAUNCH_CHECK();
-  if (c->profile) CU(cudaEventRecord(c->ev1, c->stream));
+  }
   if (ev) TRY(reduce_partials(c, blocks, 7, 0));  // pair energy + virial -> red_d[0..6]; eng = red[0] + red[8]
   return B200MD_OK;
 }

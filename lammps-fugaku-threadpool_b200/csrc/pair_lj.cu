@@ -140,7 +140,8 @@ int pair_lj_compute(b200md_ctx *c, int eflag, int vflag)
   LJOne one = {c->lj.h_onetype[0], c->lj.h_onetype[1], c->lj.h_onetype[2], c->lj.h_onetype[3], c->lj.h_onetype[4], c->lj.h_onetype[5]};
   const int onetype = (c->lj.ntypes == 1);
   size_t smem = onetype ? 0 : (size_t) 6 * (c->lj.ntypes + 1) * (c->lj.ntypes + 1) * sizeof(double);
-  if (c->profile) CU(cudaEventRecord(c->ev0, c->stream));
+  {
+  KProf kp(c, KC_PAIR);
 #define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p
   if (ev) {
     if (onetype) k_lj_full<1, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
@@ -151,7 +152,7 @@ int pair_lj_compute(b200md_ctx *c, int eflag, int vflag)
   }
 #undef LJ_ARGS
   LAUNCH_CHECK();
-  if (c->profile) CU(cudaEventRecord(c->ev1, c->stream));
+  }
   if (ev) TRY(reduce_partials(c, blocks, 7, 0));
   return B200MD_OK;
 }

@@ -49,8 +49,9 @@ PROTOTYPES = {
     "b200md_timestep": (_i64, [_vp]),
     "b200md_step_host": (_i, [_vp, _d, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "b200md_timers": (_i, [_vp, _vp, _vp, _i]),
-    "b200md_last_kernel_ms": (_i, [_vp, _vp, _vp]),
     "b200md_profile": (_i, [_vp, _i]),
+    "b200md_kernel_times": (_i, [_vp, _vp, _vp, _i]),
+    "b200md_stream": (_vp, [_vp]),
 }
 
 _lib = None

@@ -166,7 +166,8 @@ def test_piecewise_api_equals_device_loop(pkg):
     b = make_device_system(pkg, "lj2_864", g)
     a.run(15)
     b.setup()
-    for _ in range(15):
+    for step in range(15):
+        ev = 1 if step == 14 else 0  # Integrate::ev_set: tallies only on the last step of the run, like b200md_run
         b.fix_nve.initial_integrate()
         flag = C.c_int(0)
         b.ctx.call("b200md_neigh_decide", C.byref(flag))
@@ -175,7 +176,7 @@ def test_piecewise_api_equals_device_loop(pkg):
         else:
             b.ctx.call("b200md_halo_forward")
         e, v = C.c_double(0), np.zeros(6)
-        b.ctx.call("b200md_pair_compute", 1, 1, C.byref(e), v.ctypes.data_as(C.c_void_p))
+        b.ctx.call("b200md_pair_compute", ev, ev, C.byref(e), v.ctypes.data_as(C.c_void_p))
         b.fix_nve.final_integrate()
     ga, gb = a.gather(), b.gather()
     assert np.array_equal(ga["x"], gb["x"]) and np.array_equal(ga["v"], gb["v"]) and np.array_equal(ga["f"], gb["f"])
