@@ -177,7 +177,7 @@ def time_resident(torch, dist, md, steps, warmup, device, nranks):
     return float(ms.item())
 
 
-def time_host_buffers(torch, md, steps, warmup, device):
+def time_host_buffers(torch, dist, md, steps, warmup, device, nranks):
     """The same steps through the host-buffer entry point (b200md_step_host): every step copies x, v from pinned
     host arrays to the device and x, v, f back -- what a Pair/Fix plugin under the stock host-resident Verlet
     loop pays (the reference GPU package's model).  Returns (ms for K steps, h2d bytes/step, d2h bytes/step)."""
@@ -194,6 +194,8 @@ def time_host_buffers(torch, md, steps, warmup, device):
     ext = torch.cuda.ExternalStream(md.ctx.L.b200md_stream(md.ctx.h), device=device)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize(device)
+    if nranks > 1:
+        dist.barrier()
     with torch.cuda.stream(ext):
         e0.record()
     t0 = time.perf_counter()
@@ -203,14 +205,20 @@ def time_host_buffers(torch, md, steps, warmup, device):
         e1.record()
     torch.cuda.synchronize(device)
     wall_ms = (time.perf_counter() - t0) * 1e3
-    return max(e0.elapsed_time(e1), wall_ms), 2 * n * 24, 3 * n * 24
+    ms = torch.tensor([max(e0.elapsed_time(e1), wall_ms), float(2 * n * 24), float(3 * n * 24)], dtype=torch.float64, device=device)
+    if nranks > 1:
+        mx = ms.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(ms, op=dist.ReduceOp.SUM)
+        ms[0] = mx[0]
+    return float(ms[0].item()), int(ms[1].item()), int(ms[2].item())
 
 
 def run_workload(torch, dist, pkg, kind, cells, args, device, nranks, rank, nccl_id, grid, loc, allsum):
     t_gen = time.perf_counter()
     x, v, tag, box, natoms_total = make_atoms(pkg, kind, cells, grid, loc, allsum)
     t_gen = time.perf_counter() - t_gen
-    md = make_system(pkg, kind, device, nranks, rank, nccl_id, grid)
+    md = make_system(pkg, kind, device, nranks, rank, nccl_id(), grid)
     md.box([0, 0, 0], box)
     md.create_atoms(x, v, np.ones(len(x), dtype=np.int32), tag, natoms_total=natoms_total)
     del x, v, tag
@@ -242,10 +250,10 @@ def run_workload(torch, dist, pkg, kind, cells, args, device, nranks, rank, nccl
     out["nghost"] = md.nghost
     out["mem_gb"] = float(md.ctx.L.b200md_memory_usage(md.ctx.h)) / 1e9
 
-    # ---- end to end through host buffers (rank-local; N=1 only has a meaningful single-host number) ----
-    if not args.no_e2e and nranks == 1:
+    # ---- end to end through host buffers: every rank moves its own atoms over its own PCIe link every step ----
+    if not args.no_e2e:
         k = max(3, min(args.steps, 20))
-        ems, bi, bo = time_host_buffers(torch, md, k, 3, device)
+        ems, bi, bo = time_host_buffers(torch, dist, md, k, 3, device, nranks)
         out["e2e"] = dict(value=natoms_total * k / (ems * 1e-3) / 1e6, unit="Matom-steps/s", h2d_bytes_per_step=bi,
                           d2h_bytes_per_step=bo, steps=k, api="b200md_step_host (pinned host x,v in; x,v,f out every step)")
     md.close()
@@ -385,15 +393,18 @@ def main():
     torch.cuda.set_device(local)
     grid = proc_grid(world)
     loc = (rank % grid[0], (rank // grid[0]) % grid[1], rank // (grid[0] * grid[1]))
-    nccl_id = None
+    nccl_id = lambda: None
     allsum = lambda a: a
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        idt = torch.zeros(pkg.lib.NCCL_ID_BYTES, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            idt.copy_(torch.frombuffer(bytearray(pkg.lib.nccl_unique_id()), dtype=torch.uint8))
-        dist.broadcast(idt, 0)
-        nccl_id = bytes(idt.cpu().numpy().tobytes())
+
+        def nccl_id():
+            """a fresh ncclUniqueId per context, made on rank 0 and broadcast (what MPI_Bcast does in a LAMMPS host)"""
+            idt = torch.zeros(pkg.lib.NCCL_ID_BYTES, dtype=torch.uint8, device="cuda")
+            if rank == 0:
+                idt.copy_(torch.frombuffer(bytearray(pkg.lib.nccl_unique_id()), dtype=torch.uint8))
+            dist.broadcast(idt, 0)
+            return bytes(idt.cpu().numpy().tobytes())
 
         def allsum(a):
             t = torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).cuda()

@@ -127,8 +127,14 @@ int b200md_neigh_stats(b200md_ctx *ctx, int64_t *nbuilds, int64_t *ndanger, int 
 
 /* ---- Comm : CommBrick::forward_comm (src/comm_brick.cpp:538-591) -------------------------
  * ghost positions from their owners (self copy, peer copy over NVLink/NCCL).  The device list is
- * full, so the reference's reverse_comm of ghost forces (:598-639) has no device counterpart. */
+ * full, so the reference's reverse_comm of ghost forces (:598-639) has no device counterpart.
+ * Comm::exchange and Comm::borders (:652-979) run inside b200md_neigh_build.  Collective. */
 int b200md_halo_forward(b200md_ctx *ctx);
+/* CommBrick::setup (src/comm_brick.cpp:191-483) for the single-stage 26-direction scheme, host only (no
+ * device needed): peer_send[d] = rank that receives what `rank` sends in direction d, peer_recv[d] = rank
+ * whose direction-d messages `rank` receives; -1 = none (non-periodic face).  d = 0..25 enumerates
+ * (dx,dy,dz) in {-1,0,1}^3 without (0,0,0), x fastest.  Arrays of 26. */
+int b200md_plan_peers(const int procgrid[3], const int periodic[3], int rank, int *peer_send, int *peer_recv);
 
 /* ---- force : Verlet::force_clear (src/verlet.cpp:376) + Pair::compute ---------------------
  * PairLJCut::compute (src/pair_lj_cut.cpp:69-139) or PairEAM::compute incl. its internal

@@ -58,8 +58,8 @@ extern "C" int b200md_create(b200md_ctx **out, int device, int nranks, int rank,
   CU(cudaMallocHost((void **) &c->red_h, 32 * sizeof(double)));
   CU(cudaMalloc((void **) &c->flags_d, 8 * sizeof(int)));
   CU(cudaMemset(c->flags_d, 0, 8 * sizeof(int)));
-  CU(cudaMallocHost((void **) &c->flags_h, 64 * sizeof(int)));
-  memset(c->flags_h, 0, 64 * sizeof(int));
+  CU(cudaMallocHost((void **) &c->flags_h, (size_t) (64 + 32 * (nranks + 1)) * sizeof(int)));
+  memset(c->flags_h, 0, (size_t) (64 + 32 * (nranks + 1)) * sizeof(int));
   if (nranks > 1) TRY(comm_init(c, nccl_id));
   return B200MD_OK;
 }
@@ -76,7 +76,8 @@ extern "C" int b200md_destroy(b200md_ctx *c)
   dev_free(c, c->rho); dev_free(c, c->fp); dev_free(c, c->cutneighsq_d);
   dev_free(c, c->bin_count); dev_free(c, c->bin_start); dev_free(c, c->atom_bin); dev_free(c, c->cell_list);
   dev_free(c, c->perm); dev_free(c, c->scan_tmp); dev_free(c, c->numneigh); dev_free(c, c->neigh);
-  dev_free(c, c->ghost_src); dev_free(c, c->border_blockcnt); dev_free(c, c->border_total); dev_free(c, c->ghost_dir);
+  dev_free(c, c->send_idx); dev_free(c, c->border_blockcnt); dev_free(c, c->border_total); dev_free(c, c->send_dir);
+  dev_free(c, c->sendbuf_i); dev_free(c, c->allcounts); dev_free(c, c->sendbuf4); dev_free(c, c->recvbuf4); dev_free(c, c->sendbuf1);
   dev_free(c, c->partials); dev_free(c, c->stage);
   if (c->lj.d) cudaFree(c->lj.d);
   if (c->eam.frho) cudaFree(c->eam.frho);
@@ -486,8 +487,6 @@ struct Sect {  // accumulates device time per Timer section when profiling is on
     }
   }
 };
-
-int comm_allreduce_sum(b200md_ctx *c, double *dev, int n);
 
 static int force_compute(b200md_ctx *c, int eflag, int vflag)
 {

@@ -38,7 +38,9 @@ template <class T> struct DevBuf {
 };
 
 struct HaloPlan {             // passed by value to the halo kernels
-  int goff[NDIR + 1];         // ghost group offsets (relative to nlocal), by direction
+  int goff[NDIR + 1];         // ghost group offsets (relative to nlocal), by the direction the atoms travelled in
+  int soff[NDIR + 1];         // send-list offsets by direction
+  int self[NDIR];             // 1 if the receiver of direction d is this rank itself (periodic image)
   double shift[NDIR][3];      // periodic shift the SENDER applies (src/atom_vec.cpp:363-379)
 };
 
@@ -119,11 +121,17 @@ struct b200md_ctx {
   DevBuf<int> numneigh, neigh;
   int maxneigh_seen = 0;
 
-  // halo
+  // halo / exchange (comm.cu)
   HaloPlan hp;
-  int sendcount[NDIR];
-  DevBuf<int> ghost_src, border_blockcnt, border_total;
-  DevBuf<signed char> ghost_dir;
+  void *nccl = nullptr;       // ncclComm_t when nranks > 1
+  int peer_send[NDIR], peer_recv[NDIR];
+  int sendcount[NDIR], recvcount[NDIR];
+  int nsend = 0;
+  int64_t nmigrated = 0;
+  DevBuf<int> send_idx, border_blockcnt, border_total, sendbuf_i, allcounts;
+  DevBuf<signed char> send_dir;
+  DevBuf<double4> sendbuf4, recvbuf4;
+  DevBuf<double> sendbuf1;
 
   // reductions / flags
   DevBuf<double> partials;  // [nblocks][8]
@@ -243,6 +251,11 @@ enum { SECT_PAIR = 0, SECT_NEIGH = 1, SECT_COMM = 2, SECT_MODIFY = 3, SECT_OTHER
 int neigh_setup_bins(b200md_ctx *c);
 int neigh_rebuild(b200md_ctx *c);          // pbc + sort + borders + bin + build
 int neigh_check_distance(b200md_ctx *c, int *moved);
+int comm_plan(b200md_ctx *c);
+int comm_exchange(b200md_ctx *c);
+int comm_borders(b200md_ctx *c);
+int comm_allreduce_sum(b200md_ctx *c, double *dev, int n);
+int comm_allreduce_max_int(b200md_ctx *c, int *dev, int n);
 int halo_forward_pos(b200md_ctx *c);
 int halo_forward_scalar(b200md_ctx *c, double *a);
 int pair_lj_compute(b200md_ctx *c, int eflag, int vflag);

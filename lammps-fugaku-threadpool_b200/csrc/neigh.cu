@@ -3,8 +3,7 @@
 //   Atom::sort + NBinStandard::bin_atoms (src/atom.cpp:2246-2345, src/nbin_standard.cpp:221-261)
 //                                                        -> counting sort k_bin_count / scan / k_bin_place /
 //                                                           k_bin_sortseg / k_permute_owned
-//   CommBrick::borders     (src/comm_brick.cpp:771-979)  -> k_border_count / k_border_scan / k_border_fill /
-//                                                           k_border_apply (single-stage, 26 directions)
+//   Comm::exchange / CommBrick::borders                  -> comm.cu (single-stage, 26 directions)
 //   NPair::build           (src/npair_half_bin_atomonly_newton.cpp:33-113, full-list semantics of
 //                           src/npair_full_bin_atomonly.cpp) -> k_build_full
 //   Neighbor::check_distance (src/neighbor.cpp:2322-2374) -> k_check_distance
@@ -228,224 +227,6 @@ int neigh_setup_bins(b200md_ctx *c)
 }
 
 // ------------------------------------------------------------------------------------------------
-// borders: single-stage ghost construction
-// ------------------------------------------------------------------------------------------------
-struct BorderGeom {
-  double lo_cut[3];   // sublo + cutghost : atoms with x <= this go to the low-side neighbor  (comm_brick.cpp:425-427)
-  double hi_cut[3];   // subhi - cutghost : atoms with x >= this go to the high-side neighbor (:454-455)
-  int send_lo[3], send_hi[3];  // whether a neighbor exists on that side (periodic or interior)
-};
-
-__device__ __forceinline__ unsigned border_mask(const BorderGeom &b, const double4 &p)
-{
-  int lo0 = b.send_lo[0] && p.x <= b.lo_cut[0], hi0 = b.send_hi[0] && p.x >= b.hi_cut[0];
-  int lo1 = b.send_lo[1] && p.y <= b.lo_cut[1], hi1 = b.send_hi[1] && p.y >= b.hi_cut[1];
-  int lo2 = b.send_lo[2] && p.z <= b.lo_cut[2], hi2 = b.send_hi[2] && p.z >= b.hi_cut[2];
-  if (!(lo0 | hi0 | lo1 | hi1 | lo2 | hi2)) return 0u;
-  unsigned m = 0;
-  int c = 0;
-#pragma unroll
-  for (int dz = -1; dz <= 1; dz++)
-#pragma unroll
-    for (int dy = -1; dy <= 1; dy++)
-#pragma unroll
-      for (int dx = -1; dx <= 1; dx++) {
-        if (dx == 0 && dy == 0 && dz == 0) continue;
-        int ok = (dx == 0 || (dx < 0 ? lo0 : hi0)) && (dy == 0 || (dy < 0 ? lo1 : hi1)) && (dz == 0 || (dz < 0 ? lo2 : hi2));
-        m |= (unsigned) ok << c;
-        c++;
-      }
-  return m;
-}
-
-#define BORDER_BLOCK 256
-__global__ void k_border_count(const double4 *__restrict__ pos, int n, BorderGeom bgm, int nblk, int *__restrict__ blockcnt)
-{
-  __shared__ int cnt[NDIR];
-  if (threadIdx.x < NDIR) cnt[threadIdx.x] = 0;
-  __syncthreads();
-  int i = blockIdx.x * BORDER_BLOCK + threadIdx.x;
-  unsigned m = 0;
-  if (i < n) m = border_mask(bgm, pos[i]);
-  if (__any_sync(0xffffffffu, m != 0)) {
-    for (int d = 0; d < NDIR; d++) {
-      unsigned b = __ballot_sync(0xffffffffu, (m >> d) & 1u);
-      if (b && (threadIdx.x & 31) == 0) atomicAdd(&cnt[d], __popc(b));
-    }
-  }
-  __syncthreads();
-  if (threadIdx.x < NDIR) blockcnt[threadIdx.x * nblk + blockIdx.x] = cnt[threadIdx.x];
-}
-
-// one block per direction: exclusive scan of that direction's per-block counts, total to totals[d]
-__global__ void k_border_scan(const int *__restrict__ blockcnt, int *__restrict__ blockoff, int nblk, int *__restrict__ totals)
-{
-  __shared__ int wsum[32];
-  __shared__ int carry_s;
-  int d = blockIdx.x;
-  const int *in = blockcnt + (size_t) d * nblk;
-  int *out = blockoff + (size_t) d * nblk;
-  if (threadIdx.x == 0) carry_s = 0;
-  __syncthreads();
-  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  for (int start = 0; start < nblk; start += blockDim.x) {
-    int i = start + threadIdx.x;
-    int t = (i < nblk) ? in[i] : 0;
-    int incl = t;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
-    if (lane == 31) wsum[w] = incl;
-    __syncthreads();
-    int woff = 0;
-    for (int k = 0; k < w; k++) woff += wsum[k];
-    int carry = carry_s;
-    if (i < nblk) out[i] = carry + woff + incl - t;
-    __syncthreads();
-    if (threadIdx.x == blockDim.x - 1) carry_s = carry + woff + incl;
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) totals[d] = carry_s;
-}
-
-__global__ void k_border_fill(const double4 *__restrict__ pos, int n, BorderGeom bgm, int nblk,
-                              const int *__restrict__ blockcnt, const int *__restrict__ blockoff, HaloPlan hp,
-                              int *__restrict__ send_idx)
-{
-  __shared__ int wcnt[BORDER_BLOCK / 32];
-  int i = blockIdx.x * BORDER_BLOCK + threadIdx.x;
-  unsigned m = 0;
-  if (i < n) m = border_mask(bgm, pos[i]);
-  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  for (int d = 0; d < NDIR; d++) {
-    if (blockcnt[d * nblk + blockIdx.x] == 0) continue;  // block-uniform
-    unsigned b = __ballot_sync(0xffffffffu, (m >> d) & 1u);
-    if (lane == 0) wcnt[w] = __popc(b);
-    __syncthreads();
-    if ((m >> d) & 1u) {
-      int base = 0;
-      for (int k = 0; k < w; k++) base += wcnt[k];
-      int r = base + __popc(b & ((1u << lane) - 1u));
-      send_idx[hp.goff[d] + blockoff[d * nblk + blockIdx.x] + r] = i;
-    }
-    __syncthreads();
-  }
-}
-
-// create / refresh ghosts that come from this rank itself (periodic images): CommBrick::borders self-swap
-// (src/comm_brick.cpp:893-905) and forward_comm self-copy (:577-589); AtomVec::pack_border adds pbc*prd
-// (src/atom_vec.cpp:808-826)
-template <int WITH_TAG>
-__global__ void k_ghost_self(double4 *__restrict__ pos, int *__restrict__ tag, const int *__restrict__ ghost_src,
-                             signed char *__restrict__ ghost_dir, int nlocal, int nghost, HaloPlan hp)
-{
-  int g = blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= nghost) return;
-  int d;
-  if (WITH_TAG) {
-    d = 0;
-    while (d < NDIR - 1 && g >= hp.goff[d + 1]) d++;
-    ghost_dir[g] = (signed char) d;
-  } else
-    d = ghost_dir[g];
-  int s = ghost_src[g];
-  double4 p = pos[s];
-  p.x += hp.shift[d][0];
-  p.y += hp.shift[d][1];
-  p.z += hp.shift[d][2];
-  pos[nlocal + g] = p;
-  if (WITH_TAG) tag[nlocal + g] = tag[s];
-}
-
-__global__ void k_ghost_scalar(double *__restrict__ a, const int *__restrict__ ghost_src, int nlocal, int nghost)
-{
-  int g = blockIdx.x * blockDim.x + threadIdx.x;
-  if (g < nghost) a[nlocal + g] = a[ghost_src[g]];
-}
-
-static void dir_vec(int d, int v[3])
-{
-  int full = d < 13 ? d : d + 1;
-  v[0] = full % 3 - 1;
-  v[1] = (full / 3) % 3 - 1;
-  v[2] = full / 9 - 1;
-}
-
-static int borders(b200md_ctx *c)
-{
-  if (c->nranks != 1) return b200md_fail(c, B200MD_ERR_ARG, "multi-rank borders are handled in comm.cu");
-  const int n = c->nlocal;
-  BorderGeom bgm;
-  for (int k = 0; k < 3; k++) {
-    bgm.lo_cut[k] = c->sublo[k] + c->cutneighmax;
-    bgm.hi_cut[k] = c->subhi[k] - c->cutneighmax;
-    bgm.send_lo[k] = c->periodic[k] || c->myloc[k] > 0;
-    bgm.send_hi[k] = c->periodic[k] || c->myloc[k] < c->procgrid[k] - 1;
-  }
-  for (int d = 0; d < NDIR; d++) {
-    int dv[3];
-    dir_vec(d, dv);
-    for (int k = 0; k < 3; k++) {
-      double s = 0.0;
-      if (dv[k] < 0 && c->myloc[k] == 0) s = c->prd[k];
-      if (dv[k] > 0 && c->myloc[k] == c->procgrid[k] - 1) s = -c->prd[k];
-      c->hp.shift[d][k] = s;
-    }
-  }
-  int nblk = cdiv(n, BORDER_BLOCK);
-  if (nblk < 1) nblk = 1;
-  TRY(dev_ensure(c, c->border_blockcnt, (size_t) 2 * NDIR * nblk));
-  TRY(dev_ensure(c, c->border_total, NDIR));
-  int *cnt = c->border_blockcnt.p, *off = cnt + (size_t) NDIR * nblk;
-  k_border_count<<<nblk, BORDER_BLOCK, 0, c->stream>>>(c->pos.p, n, bgm, nblk, cnt);
-  LAUNCH_CHECK();
-  k_border_scan<<<NDIR, 1024, 0, c->stream>>>(cnt, off, nblk, c->border_total.p);
-  LAUNCH_CHECK();
-  CU(cudaMemcpyAsync(c->flags_h + 8, c->border_total.p, NDIR * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaStreamSynchronize(c->stream));
-  int tot = 0;
-  for (int d = 0; d < NDIR; d++) {
-    c->sendcount[d] = c->flags_h[8 + d];
-    c->hp.goff[d] = tot;
-    tot += c->sendcount[d];
-  }
-  c->hp.goff[NDIR] = tot;
-  c->nghost = tot;
-  size_t nall = (size_t) n + tot;
-  TRY(dev_ensure(c, c->pos, nall, true));
-  TRY(dev_ensure(c, c->tag, nall, true));
-  TRY(dev_ensure(c, c->ghost_src, (size_t) tot + 1));
-  TRY(dev_ensure(c, c->ghost_dir, (size_t) tot + 1));
-  if (tot > 0) {
-    k_border_fill<<<nblk, BORDER_BLOCK, 0, c->stream>>>(c->pos.p, n, bgm, nblk, cnt, off, c->hp, c->ghost_src.p);
-    LAUNCH_CHECK();
-    k_ghost_self<1><<<cdiv(tot, 256), 256, 0, c->stream>>>(c->pos.p, c->tag.p, c->ghost_src.p, c->ghost_dir.p, n, tot, c->hp);
-    LAUNCH_CHECK();
-  }
-  return B200MD_OK;
-}
-
-int halo_forward_pos(b200md_ctx *c)
-{
-  if (c->nghost > 0) {
-    KProf kp(c, KC_HALO);
-    k_ghost_self<0><<<cdiv(c->nghost, 256), 256, 0, c->stream>>>(c->pos.p, c->tag.p, c->ghost_src.p, c->ghost_dir.p,
-                                                                   c->nlocal, c->nghost, c->hp);
-    LAUNCH_CHECK();
-  }
-  return B200MD_OK;
-}
-
-int halo_forward_scalar(b200md_ctx *c, double *a)
-{
-  if (c->nghost > 0) {
-    KProf kp(c, KC_HALO);
-    k_ghost_scalar<<<cdiv(c->nghost, 256), 256, 0, c->stream>>>(a, c->ghost_src.p, c->nlocal, c->nghost);
-    LAUNCH_CHECK();
-  }
-  return B200MD_OK;
-}
-
-// ------------------------------------------------------------------------------------------------
 // neighbor build: full list, thread per owned atom, 9 contiguous x-rows of 3 bins each
 // distance test exactly as the reference: rsq = delx*delx + dely*dely + delz*delz (no FMA), keep if
 // rsq <= cutneighsq[itype][jtype] (src/npair_half_bin_atomonly_newton.cpp:80-87)
@@ -506,6 +287,7 @@ int neigh_check_distance(b200md_ctx *c, int *moved)
   CU(cudaMemsetAsync(c->flags_d + 2, 0, sizeof(int), c->stream));
   k_check_distance<<<cdiv(c->nlocal, 256), 256, 0, c->stream>>>(c->pos.p, c->xhold.p, c->nlocal, c->triggersq, c->flags_d);
   LAUNCH_CHECK();
+  TRY(comm_allreduce_max_int(c, c->flags_d + 2, 1));  // the MPI_Allreduce of Neighbor::check_distance (src/neighbor.cpp:2371)
   CU(cudaMemcpyAsync(c->flags_h + 2, c->flags_d + 2, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   *moved = c->flags_h[2];
@@ -517,10 +299,10 @@ int neigh_check_distance(b200md_ctx *c, int *moved)
 // ------------------------------------------------------------------------------------------------
 int neigh_rebuild(b200md_ctx *c)
 {
-  const int n = c->nlocal;
-  if (n <= 0) return b200md_fail(c, B200MD_ERR_ARG, "no atoms uploaded");
+  if (c->nlocal <= 0) return b200md_fail(c, B200MD_ERR_ARG, "no atoms uploaded");
   TRY(neigh_setup_bins(c));
   CU(cudaMemsetAsync(c->flags_d, 0, 4 * sizeof(int), c->stream));
+  int n = c->nlocal;
 
   // Domain::pbc
   k_pbc<<<cdiv(n, 256), 256, 0, c->stream>>>(c->pos.p, c->image.p, n, make_double3(c->boxlo[0], c->boxlo[1], c->boxlo[2]),
@@ -528,6 +310,10 @@ int neigh_rebuild(b200md_ctx *c)
                                               make_double3(c->prd[0], c->prd[1], c->prd[2]), c->periodic[0], c->periodic[1],
                                               c->periodic[2], c->flags_d);
   LAUNCH_CHECK();
+
+  // Comm::exchange: atoms that left this rank's sub-domain migrate (multi-rank only)
+  TRY(comm_exchange(c));
+  n = c->nlocal;
 
   // spatial sort of owned atoms (Atom::sort) by neighbor bin
   TRY(dev_ensure(c, c->perm, (size_t) n));
@@ -546,7 +332,7 @@ int neigh_rebuild(b200md_ctx *c)
   for (int k = 0; k < 3; k++) std::swap(c->v[k], c->v_tmp[k]);
 
   // ghosts
-  TRY(borders(c));
+  TRY(comm_borders(c));
   const int nall = n + c->nghost;
 
   // bin owned + ghost
