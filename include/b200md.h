@@ -124,6 +124,9 @@ int b200md_neigh_build(b200md_ctx *ctx);
  * Call with neighbors == NULL to get numneigh and *total only. */
 int b200md_neigh_export(b200md_ctx *ctx, int *numneigh, int *neighbors, int64_t *total);
 int b200md_neigh_stats(b200md_ctx *ctx, int64_t *nbuilds, int64_t *ndanger, int *maxneigh);
+/* storage form of the device list: owned atoms are grouped in clusters of `cluster_size` consecutive atoms that
+ * share one list of `entries` (summed over clusters) neighbor indices, each with a per-atom membership mask */
+int b200md_neigh_cluster_stats(b200md_ctx *ctx, int *cluster_size, int64_t *nclusters, int64_t *entries);
 
 /* ---- Comm : CommBrick::forward_comm (src/comm_brick.cpp:538-591) -------------------------
  * ghost positions from their owners (self copy, peer copy over NVLink/NCCL).  The device list is

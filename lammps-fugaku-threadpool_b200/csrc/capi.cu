@@ -51,6 +51,10 @@ extern "C" int b200md_create(b200md_ctx **out, int device, int nranks, int rank,
   c->rank = rank;
   for (int k = 0; k <= B200MD_MAXTYPES; k++) c->mass_h[k] = 0.0;
   strcpy(c->err, "no error");
+  if (const char *e = getenv("B200MD_CLUSTER")) {  // tuning knob: atoms per neighbor-list cluster
+    int v = atoi(e);
+    if (v == 1 || v == 2 || v == 4) c->cl = v;
+  }
   *out = c;
   CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CU(cudaMalloc((void **) &c->red_d, 32 * sizeof(double)));
@@ -75,7 +79,7 @@ extern "C" int b200md_destroy(b200md_ctx *c)
   dev_free(c, c->tag); dev_free(c, c->tag_tmp); dev_free(c, c->image); dev_free(c, c->image_tmp);
   dev_free(c, c->rho); dev_free(c, c->fp); dev_free(c, c->cutneighsq_d);
   dev_free(c, c->bin_count); dev_free(c, c->bin_start); dev_free(c, c->atom_bin); dev_free(c, c->cell_list);
-  dev_free(c, c->perm); dev_free(c, c->scan_tmp); dev_free(c, c->numneigh); dev_free(c, c->neigh);
+  dev_free(c, c->perm); dev_free(c, c->scan_tmp); dev_free(c, c->atom_sub); dev_free(c, c->numneigh); dev_free(c, c->neigh);
   dev_free(c, c->send_idx); dev_free(c, c->border_blockcnt); dev_free(c, c->border_total); dev_free(c, c->send_dir);
   dev_free(c, c->sendbuf_i); dev_free(c, c->allcounts); dev_free(c, c->sendbuf4); dev_free(c, c->recvbuf4); dev_free(c, c->sendbuf1);
   dev_free(c, c->partials); dev_free(c, c->stage);
@@ -409,15 +413,35 @@ extern "C" int b200md_neigh_build(b200md_ctx *c)
   return neigh_rebuild(c);
 }
 
-__global__ void k_list_to_csr(const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh, int nlocal,
+// per-atom view of the cluster list: atom i = cluster q, slot a; its neighbors are the cluster's entries whose
+// mask (top 4 bits of the entry) has bit a
+__global__ void k_list_count(const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh, int nlocal, int cl,
+                             int *__restrict__ count)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nlocal) return;
+  const int q = i / cl, a = i % cl;
+  const int *nb = neigh + (size_t) (q >> 5) * TILE * maxneigh + (q & 31);
+  const int n = numneigh[q];
+  int m = 0;
+  for (int k = 0; k < n; k++) m += ((unsigned) nb[(size_t) k * TILE] >> (CLBITS + a)) & 1u;
+  count[i] = m;
+}
+
+__global__ void k_list_to_csr(const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh, int nlocal, int cl,
                               const long long *__restrict__ first, int *__restrict__ out)
 {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nlocal) return;
-  const int *nb = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
+  const int q = i / cl, a = i % cl;
+  const int *nb = neigh + (size_t) (q >> 5) * TILE * maxneigh + (q & 31);
   int *o = out + first[i];
-  int n = numneigh[i];
-  for (int k = 0; k < n; k++) o[k] = nb[(size_t) k * TILE];
+  const int n = numneigh[q];
+  int m = 0;
+  for (int k = 0; k < n; k++) {
+    const unsigned e = (unsigned) nb[(size_t) k * TILE];
+    if ((e >> (CLBITS + a)) & 1u) o[m++] = (int) (e & CLJMASK);
+  }
 }
 
 extern "C" int b200md_neigh_export(b200md_ctx *c, int *numneigh, int *neighbors, int64_t *total)
@@ -426,8 +450,13 @@ extern "C" int b200md_neigh_export(b200md_ctx *c, int *numneigh, int *neighbors,
   if (!c->list_valid) return b200md_fail(c, B200MD_ERR_ARG, "no neighbor list built");
   const int n = c->nlocal;
   std::vector<int> nn((size_t) n);
-  CU(cudaMemcpyAsync(nn.data(), c->numneigh.p, (size_t) n * 4, cudaMemcpyDeviceToHost, c->stream));
+  int *cnt_d = nullptr;
+  CU(cudaMalloc((void **) &cnt_d, (size_t) n * 4));
+  k_list_count<<<cdiv(n, 128), 128, 0, c->stream>>>(c->numneigh.p, c->neigh.p, c->maxneigh, n, c->cl, cnt_d);
+  LAUNCH_CHECK();
+  CU(cudaMemcpyAsync(nn.data(), cnt_d, (size_t) n * 4, cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
+  cudaFree(cnt_d);
   std::vector<long long> first((size_t) n + 1);
   first[0] = 0;
   for (int i = 0; i < n; i++) first[i + 1] = first[i] + nn[i];
@@ -439,13 +468,29 @@ extern "C" int b200md_neigh_export(b200md_ctx *c, int *numneigh, int *neighbors,
     CU(cudaMalloc((void **) &first_d, ((size_t) n + 1) * 8));
     CU(cudaMalloc((void **) &out_d, (size_t) first[n] * 4));
     CU(cudaMemcpyAsync(first_d, first.data(), ((size_t) n + 1) * 8, cudaMemcpyHostToDevice, c->stream));
-    k_list_to_csr<<<cdiv(n, 128), 128, 0, c->stream>>>(c->numneigh.p, c->neigh.p, c->maxneigh, n, first_d, out_d);
+    k_list_to_csr<<<cdiv(n, 128), 128, 0, c->stream>>>(c->numneigh.p, c->neigh.p, c->maxneigh, n, c->cl, first_d, out_d);
     LAUNCH_CHECK();
     CU(cudaMemcpyAsync(neighbors, out_d, (size_t) first[n] * 4, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     cudaFree(first_d);
     cudaFree(out_d);
   }
+  return B200MD_OK;
+}
+
+extern "C" int b200md_neigh_cluster_stats(b200md_ctx *c, int *cluster_size, int64_t *nclusters, int64_t *entries)
+{
+  NEED_CTX();
+  if (!c->list_valid) return b200md_fail(c, B200MD_ERR_ARG, "no neighbor list built");
+  const int nclus = cdiv(c->nlocal, c->cl);
+  std::vector<int> nn((size_t) nclus);
+  CU(cudaMemcpyAsync(nn.data(), c->numneigh.p, (size_t) nclus * 4, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  int64_t t = 0;
+  for (int q = 0; q < nclus; q++) t += nn[q];
+  if (cluster_size) *cluster_size = c->cl;
+  if (nclusters) *nclusters = nclus;
+  if (entries) *entries = t;
   return B200MD_OK;
 }
 

@@ -20,8 +20,13 @@
 
 #include "../../include/b200md.h"
 
-#define NEIGHMASK 0x1FFFFFFF  // src/lmptype.h:61-65
+#define NEIGHMASK 0x1FFFFFFF  // src/lmptype.h:61-65 (what b200md_neigh_export hands out)
 #define SBBITS 30
+// device list entry: neighbor index in the low 28 bits, membership mask of the (up to 4) atoms of the cluster
+// in the top 4 bits -- bit a set <=> j is in the reference's list of atom a of the cluster
+#define CLBITS 28
+#define CLJMASK 0x0FFFFFFF
+#define CLMAX 4
 #define IMGMASK 1023          // src/lmptype.h (LAMMPS_SMALLBIG)
 #define IMGBITS 10
 #define IMG2BITS 20
@@ -115,8 +120,10 @@ struct b200md_ctx {
   // bins / sort
   BinGeom bg;
   DevBuf<int> bin_count, bin_start, atom_bin, cell_list, perm, scan_tmp;
+  DevBuf<unsigned char> atom_sub;
 
   // neighbor list
+  int cl = 1;                 // cluster size of the neighbor list (1, 2 or 4 atoms per list), env B200MD_CLUSTER
   int maxneigh = 0;
   DevBuf<int> numneigh, neigh;
   int maxneigh_seen = 0;
@@ -189,10 +196,10 @@ int b200md_fail(b200md_ctx *c, int code, const char *fmt, ...);
                          cudaGetErrorString(e__));                                                     \
   } while (0)
 
-template <class T> int dev_ensure(b200md_ctx *c, DevBuf<T> &b, size_t n, bool keep = false)
+template <class T> int dev_ensure(b200md_ctx *c, DevBuf<T> &b, size_t n, bool keep = false, bool slack = true)
 {
   if (n <= b.n) return B200MD_OK;
-  size_t want = n + n / 8 + 64;
+  size_t want = slack ? n + n / 8 + 64 : n;
   T *q = nullptr;
   CU(cudaMalloc((void **) &q, want * sizeof(T)));
   if (keep && b.p && b.n) CU(cudaMemcpyAsync(q, b.p, b.n * sizeof(T), cudaMemcpyDeviceToDevice, c->stream));
@@ -266,6 +273,27 @@ int thermo_ke(b200md_ctx *c, double *sum_mv2);
 int reduce_partials(b200md_ctx *c, int nblocks, int ncomp, int dst);  // partials -> red_d[dst..]
 
 // device helpers
+// one 32-byte gather of a position record: sm_100 has 256-bit global loads (LDG.E.ENL2.256), which halves the
+// LSU requests and L1 tag look-ups of a double4 gather compared with two 128-bit loads
+__device__ __forceinline__ double4 ld_pos256(const double4 *__restrict__ p)
+{
+  double4 r;
+  asm("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p));
+  return r;
+}
+// 1/x for finite positive x: MUFU.RCP64H seed (about 20 good bits) + two Newton-Raphson steps = 4 DFMA, within
+// 1 ulp of the correctly rounded quotient -- the compiler's 1.0/x spends about twice that and carries a
+// divergent slow-path call for denormals/infinities that a squared distance never needs
+__device__ __forceinline__ double rcp_pos(double x)
+{
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  double e = fma(-x, y, 1.0);
+  y = fma(y, e, y);
+  e = fma(-x, y, 1.0);
+  y = fma(y, e, y);
+  return y;
+}
 __device__ __forceinline__ int pos_type(const double4 &p) { return __double2loint(p.w); }
 __device__ __forceinline__ double type_as_w(int t) { return __hiloint2double(0, t); }
 int nve_final_initial(b200md_ctx *c, double dtv, double dtf);

@@ -11,6 +11,8 @@
 // owned atoms are physically re-ordered by bin at every rebuild, ghosts are made in ONE stage from the
 // 26 direction masks instead of the reference's 6 staged swaps (same ghost set when every sub-domain is
 // at least one ghost cutoff wide), and the list is a full list in a blocked-transposed layout.
+#include <stdlib.h>
+
 #include <utility>
 
 #include "ctx.cuh"
@@ -54,14 +56,28 @@ __global__ void k_pbc(double4 *__restrict__ pos, int *__restrict__ image, int n,
   image[i] = img;
 }
 
+// sub-cell of an atom inside its bin: 4x4x4 cells in Morton order.  Owned atoms are ordered by (bin, sub-cell,
+// previous index) so that CL consecutive atoms -- one cluster of the cluster neighbor list -- are spatially
+// compact (about half of a cluster's candidate neighbors then serve more than one of its atoms).
+__device__ __forceinline__ int subcell_of(const BinGeom &g, double x, double y, double z)
+{
+  double fx = (x - g.lo[0]) * g.inv[0], fy = (y - g.lo[1]) * g.inv[1], fz = (z - g.lo[2]) * g.inv[2];
+  int sx = min(3, max(0, (int) ((fx - floor(fx)) * 4.0)));
+  int sy = min(3, max(0, (int) ((fy - floor(fy)) * 4.0)));
+  int sz = min(3, max(0, (int) ((fz - floor(fz)) * 4.0)));
+  return (sx & 1) | ((sy & 1) << 1) | ((sz & 1) << 2) | ((sx & 2) << 2) | ((sy & 2) << 3) | ((sz & 2) << 4);
+}
+
+template <int WITH_SUB>
 __global__ void k_bin_count(const double4 *__restrict__ pos, int n, BinGeom g, int *__restrict__ atom_bin,
-                            int *__restrict__ bin_count)
+                            int *__restrict__ bin_count, unsigned char *__restrict__ atom_sub)
 {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   double4 p = pos[i];
   int b = bin_of(g, p.x, p.y, p.z);
   atom_bin[i] = b;
+  if (WITH_SUB) atom_sub[i] = (unsigned char) subcell_of(g, p.x, p.y, p.z);
   atomicAdd(&bin_count[b], 1);
 }
 
@@ -145,19 +161,46 @@ __global__ void k_bin_place(const int *__restrict__ atom_bin, int n, const int *
   list[slot] = i;
 }
 
-// the atomics above leave each bin's segment in arbitrary order: sort it ascending so that the atom
-// order (hence every floating-point summation order downstream) is reproducible run to run, and equals
-// the reference's "ascending index within a bin" (src/nbin_standard.cpp:254-259).
-__global__ void k_bin_sortseg(const int *__restrict__ bin_start, int mbins, int *__restrict__ list)
+// the atomics above leave each bin's segment in arbitrary order: sort it so that the atom order (hence every
+// floating-point summation order downstream) is reproducible run to run.  Key = (sub-cell, index) for the
+// owned-atom sort, index alone for the owned+ghost cell list ("ascending index within a bin",
+// src/nbin_standard.cpp:254-259).
+#define SORTSEG_LOCAL 48
+template <int WITH_SUB>
+__global__ void k_bin_sortseg(const int *__restrict__ bin_start, int mbins, int *__restrict__ list,
+                              const unsigned char *__restrict__ atom_sub)
 {
   int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= mbins) return;
-  int s = bin_start[b], e = bin_start[b + 1];
-  for (int a = s + 1; a < e; a++) {
-    int key = list[a];
-    int k = a - 1;
-    while (k >= s && list[k] > key) { list[k + 1] = list[k]; k--; }
-    list[k + 1] = key;
+  const int s = bin_start[b], e = bin_start[b + 1], n = e - s;
+  if (n <= 1) return;
+  if (n <= SORTSEG_LOCAL) {
+    long long key[SORTSEG_LOCAL];
+    for (int t = 0; t < n; t++) {
+      int idx = list[s + t];
+      key[t] = WITH_SUB ? (((long long) atom_sub[idx] << 32) | (long long) idx) : (long long) idx;
+    }
+    for (int a = 1; a < n; a++) {
+      long long kk = key[a];
+      int k = a - 1;
+      while (k >= 0 && key[k] > kk) { key[k + 1] = key[k]; k--; }
+      key[k + 1] = kk;
+    }
+    for (int t = 0; t < n; t++) list[s + t] = (int) (key[t] & 0xffffffffLL);
+  } else {
+    for (int a = s + 1; a < e; a++) {
+      int idx = list[a];
+      long long kk = WITH_SUB ? (((long long) atom_sub[idx] << 32) | (long long) idx) : (long long) idx;
+      int k = a - 1;
+      while (k >= s) {
+        int jdx = list[k];
+        long long kj = WITH_SUB ? (((long long) atom_sub[jdx] << 32) | (long long) jdx) : (long long) jdx;
+        if (kj <= kk) break;
+        list[k + 1] = jdx;
+        k--;
+      }
+      list[k + 1] = idx;
+    }
   }
 }
 
@@ -178,21 +221,26 @@ __global__ void k_permute_owned(const int *__restrict__ perm, int n, const doubl
   image_o[s] = image[i];
 }
 
-// counting sort of atoms [0,n) into bins: list = atom indices ordered by bin, ascending within a bin
-static int bin_sort(b200md_ctx *c, int n, int *list)
+// counting sort of atoms [0,n) into bins: list = atom indices ordered by bin; within a bin by (sub-cell, index)
+// when with_sub, else by index
+static int bin_sort(b200md_ctx *c, int n, int *list, bool with_sub)
 {
   const BinGeom &g = c->bg;
   TRY(dev_ensure(c, c->bin_count, (size_t) g.mbins + 1));
   TRY(dev_ensure(c, c->bin_start, (size_t) g.mbins + 1));
   TRY(dev_ensure(c, c->atom_bin, (size_t) n));
+  if (with_sub) TRY(dev_ensure(c, c->atom_sub, (size_t) n));
+  KProf kp(c, KC_SORT);
   CU(cudaMemsetAsync(c->bin_count.p, 0, ((size_t) g.mbins + 1) * sizeof(int), c->stream));
-  k_bin_count<<<cdiv(n, 256), 256, 0, c->stream>>>(c->pos.p, n, g, c->atom_bin.p, c->bin_count.p);
+  if (with_sub) k_bin_count<1><<<cdiv(n, 256), 256, 0, c->stream>>>(c->pos.p, n, g, c->atom_bin.p, c->bin_count.p, c->atom_sub.p);
+  else k_bin_count<0><<<cdiv(n, 256), 256, 0, c->stream>>>(c->pos.p, n, g, c->atom_bin.p, c->bin_count.p, nullptr);
   LAUNCH_CHECK();
   TRY(exclusive_scan(c, c->bin_count.p, c->bin_start.p, g.mbins + 1));
   CU(cudaMemsetAsync(c->bin_count.p, 0, ((size_t) g.mbins + 1) * sizeof(int), c->stream));
   k_bin_place<<<cdiv(n, 256), 256, 0, c->stream>>>(c->atom_bin.p, n, c->bin_start.p, c->bin_count.p, list);
   LAUNCH_CHECK();
-  k_bin_sortseg<<<cdiv(g.mbins, 128), 128, 0, c->stream>>>(c->bin_start.p, g.mbins, list);
+  if (with_sub) k_bin_sortseg<1><<<cdiv(g.mbins, 128), 128, 0, c->stream>>>(c->bin_start.p, g.mbins, list, c->atom_sub.p);
+  else k_bin_sortseg<0><<<cdiv(g.mbins, 128), 128, 0, c->stream>>>(c->bin_start.p, g.mbins, list, nullptr);
   LAUNCH_CHECK();
   return B200MD_OK;
 }
@@ -227,45 +275,86 @@ int neigh_setup_bins(b200md_ctx *c)
 }
 
 // ------------------------------------------------------------------------------------------------
-// neighbor build: full list, thread per owned atom, 9 contiguous x-rows of 3 bins each
-// distance test exactly as the reference: rsq = delx*delx + dely*dely + delz*delz (no FMA), keep if
-// rsq <= cutneighsq[itype][jtype] (src/npair_half_bin_atomonly_newton.cpp:80-87)
+// neighbor build: FULL list stored per CLUSTER of CL consecutive (spatially compact) owned atoms.
+// One thread per cluster scans the bins around the cluster's bounding box; a candidate j is stored once for the
+// cluster if it is a neighbor of ANY of its atoms, with a CL-bit mask saying of which.  The mask is decided
+// exactly as the reference decides list membership: rsq = delx*delx + dely*dely + delz*delz (no FMA), keep if
+// rsq <= cutneighsq[itype][jtype] (src/npair_half_bin_atomonly_newton.cpp:80-87), so the per-atom lists the
+// masks define are bit-identical to the reference's as tag-pair sets.  The force kernels gather x_j once per
+// entry and serve up to CL atoms with it (fewer L1 look-ups and list bytes per pair than a per-atom list).
+// Layout: entry k of cluster q at [(q>>5)*32*maxneigh + k*32 + (q&31)] (one coalesced 128-byte row per k per warp).
 // ------------------------------------------------------------------------------------------------
+template <int CL>
 __global__ void __launch_bounds__(128)
-k_build_full(const double4 *__restrict__ pos, int nlocal, BinGeom g, const int *__restrict__ bin_start,
-             const int *__restrict__ cell_list, const double *__restrict__ cutneighsq, int ntypes, int maxneigh,
-             int *__restrict__ numneigh, int *__restrict__ neigh, int *__restrict__ flags)
+k_build_cluster(const double4 *__restrict__ pos, int nlocal, BinGeom g, const int *__restrict__ bin_start,
+                const int *__restrict__ cell_list, const double *__restrict__ cutneighsq, int ntypes, int maxneigh,
+                int *__restrict__ numneigh, int *__restrict__ neigh, int *__restrict__ flags)
 {
   extern __shared__ double s_cut[];
-  int nt1 = ntypes + 1;
+  const int nt1 = ntypes + 1;
   for (int k = threadIdx.x; k < nt1 * nt1; k += blockDim.x) s_cut[k] = cutneighsq[k];
   __syncthreads();
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= nlocal) return;
-  const double4 pi = pos[i];
-  const int it = pos_type(pi);
-  const double *cut_i = s_cut + it * nt1;
-  int bx = min(max((int) floor((pi.x - g.lo[0]) * g.inv[0]) + BIN_MARGIN, 1), g.mbin[0] - 2);
-  int by = min(max((int) floor((pi.y - g.lo[1]) * g.inv[1]) + BIN_MARGIN, 1), g.mbin[1] - 2);
-  int bz = min(max((int) floor((pi.z - g.lo[2]) * g.inv[2]) + BIN_MARGIN, 1), g.mbin[2] - 2);
-  int *out = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i0 = q * CL;
+  if (i0 >= nlocal) return;
+  double xi[CL], yi[CL], zi[CL];
+  int trow[CL], bx[CL], by[CL], bz[CL];
+#pragma unroll
+  for (int a = 0; a < CL; a++) {
+    if (i0 + a < nlocal) {
+      const double4 p = pos[i0 + a];
+      xi[a] = p.x; yi[a] = p.y; zi[a] = p.z;
+      trow[a] = pos_type(p) * nt1;
+      bx[a] = min(max((int) floor((p.x - g.lo[0]) * g.inv[0]) + BIN_MARGIN, 1), g.mbin[0] - 2);
+      by[a] = min(max((int) floor((p.y - g.lo[1]) * g.inv[1]) + BIN_MARGIN, 1), g.mbin[1] - 2);
+      bz[a] = min(max((int) floor((p.z - g.lo[2]) * g.inv[2]) + BIN_MARGIN, 1), g.mbin[2] - 2);
+    } else {
+      xi[a] = yi[a] = zi[a] = 1e150;  // padding atom of the last cluster: never within any cutoff
+      trow[a] = nt1;
+      bx[a] = bx[0]; by[a] = by[0]; bz[a] = bz[0];
+    }
+  }
+  const size_t base = (size_t) (q >> 5) * TILE * maxneigh + (q & 31);
   int n = 0;
-  for (int dz = -1; dz <= 1; dz++)
-    for (int dy = -1; dy <= 1; dy++) {
-      int row = ((bz + dz) * g.mbin[1] + (by + dy)) * g.mbin[0] + bx - 1;
-      int s = bin_start[row], e = bin_start[row + 3];
-      for (int k = s; k < e; k++) {
-        int j = cell_list[k];
-        double4 pj = pos[j];
-        double dx = __dsub_rn(pi.x, pj.x), dy2 = __dsub_rn(pi.y, pj.y), dz2 = __dsub_rn(pi.z, pj.z);
-        double rsq = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy2, dy2)), __dmul_rn(dz2, dz2));
-        if (rsq <= cut_i[pos_type(pj)] && j != i) {
-          if (n < maxneigh) out[(size_t) n * TILE] = j;
-          n++;
+  // candidates = union of the 27-bin stencils of the cluster's atoms: walk each atom's stencil, skipping every
+  // bin an earlier atom of the cluster already covered (consecutive atoms mostly share their bin)
+#pragma unroll
+  for (int a = 0; a < CL; a++) {
+    bool same = false;
+#pragma unroll
+    for (int b = 0; b < a; b++) same |= (bx[b] == bx[a] && by[b] == by[a] && bz[b] == bz[a]);
+    if (same) continue;
+    for (int dz = -1; dz <= 1; dz++)
+      for (int dy = -1; dy <= 1; dy++) {
+        const int cy = by[a] + dy, cz = bz[a] + dz;
+        const int row = (cz * g.mbin[1] + cy) * g.mbin[0];
+        for (int dx = -1; dx <= 1; dx++) {
+          const int cx = bx[a] + dx;
+          bool covered = false;
+#pragma unroll
+          for (int b = 0; b < a; b++) covered |= (abs(cx - bx[b]) <= 1 && abs(cy - by[b]) <= 1 && abs(cz - bz[b]) <= 1);
+          if (covered) continue;
+          const int s = bin_start[row + cx], e = bin_start[row + cx + 1];
+          for (int k = s; k < e; k++) {
+            const int j = cell_list[k];
+            const double4 pj = ld_pos256(pos + j);
+            const int jt = pos_type(pj);
+            unsigned m = 0;
+#pragma unroll
+            for (int c = 0; c < CL; c++) {
+              const double ddx = __dsub_rn(xi[c], pj.x), ddy = __dsub_rn(yi[c], pj.y), ddz = __dsub_rn(zi[c], pj.z);
+              const double rsq = __dadd_rn(__dadd_rn(__dmul_rn(ddx, ddx), __dmul_rn(ddy, ddy)), __dmul_rn(ddz, ddz));
+              if (rsq <= s_cut[trow[c] + jt] && j != i0 + c) m |= 1u << c;
+            }
+            if (m) {
+              if (n < maxneigh) neigh[base + (size_t) n * TILE] = j | (int) (m << CLBITS);
+              n++;
+            }
+          }
         }
       }
-    }
-  numneigh[i] = n;
+  }
+  numneigh[q] = n;
   unsigned am = __activemask();
   int nmax = __reduce_max_sync(am, n);
   if ((threadIdx.x & 31) == (__ffs(am) - 1)) atomicMax(&flags[1], nmax);  // flags[1] = longest list seen
@@ -297,8 +386,26 @@ int neigh_check_distance(b200md_ctx *c, int *moved)
 // ------------------------------------------------------------------------------------------------
 // the whole reneighbor sequence
 // ------------------------------------------------------------------------------------------------
+// development aid: B200MD_DEBUG_TIMING=1 prints the wall time of every phase of a rebuild (adds a sync per phase)
+#include <chrono>
+struct PhaseTimer {
+  b200md_ctx *c;
+  bool on;
+  std::chrono::steady_clock::time_point t0;
+  PhaseTimer(b200md_ctx *ctx) : c(ctx), on(getenv("B200MD_DEBUG_TIMING") != nullptr), t0(std::chrono::steady_clock::now()) {}
+  void mark(const char *what)
+  {
+    if (!on) return;
+    cudaStreamSynchronize(c->stream);
+    auto t1 = std::chrono::steady_clock::now();
+    fprintf(stderr, "[b200md rebuild] %-14s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+    t0 = t1;
+  }
+};
+
 int neigh_rebuild(b200md_ctx *c)
 {
+  PhaseTimer ph(c);
   if (c->nlocal <= 0) return b200md_fail(c, B200MD_ERR_ARG, "no atoms uploaded");
   TRY(neigh_setup_bins(c));
   CU(cudaMemsetAsync(c->flags_d, 0, 4 * sizeof(int), c->stream));
@@ -311,17 +418,21 @@ int neigh_rebuild(b200md_ctx *c)
                                               c->periodic[2], c->flags_d);
   LAUNCH_CHECK();
 
+  ph.mark("pbc");
   // Comm::exchange: atoms that left this rank's sub-domain migrate (multi-rank only)
   TRY(comm_exchange(c));
+  ph.mark("exchange");
   n = c->nlocal;
 
   // spatial sort of owned atoms (Atom::sort) by neighbor bin
   TRY(dev_ensure(c, c->perm, (size_t) n));
-  TRY(bin_sort(c, n, c->perm.p));
-  TRY(dev_ensure(c, c->pos_tmp, c->pos.n));
-  TRY(dev_ensure(c, c->tag_tmp, c->tag.n));
-  TRY(dev_ensure(c, c->image_tmp, c->image.n));
-  for (int k = 0; k < 3; k++) TRY(dev_ensure(c, c->v_tmp[k], c->v[k].n));
+  TRY(bin_sort(c, n, c->perm.p, true));
+  ph.mark("sort owned");
+  // same capacity as the live arrays, no slack: the pairs are swapped at every rebuild and must not leap-frog
+  TRY(dev_ensure(c, c->pos_tmp, c->pos.n, false, false));
+  TRY(dev_ensure(c, c->tag_tmp, c->tag.n, false, false));
+  TRY(dev_ensure(c, c->image_tmp, c->image.n, false, false));
+  for (int k = 0; k < 3; k++) TRY(dev_ensure(c, c->v_tmp[k], c->v[k].n, false, false));
   k_permute_owned<<<cdiv(n, 256), 256, 0, c->stream>>>(c->perm.p, n, c->pos.p, c->pos_tmp.p, c->v[0].p, c->v[1].p, c->v[2].p,
                                                         c->v_tmp[0].p, c->v_tmp[1].p, c->v_tmp[2].p, c->tag.p, c->tag_tmp.p,
                                                         c->image.p, c->image_tmp.p);
@@ -331,13 +442,17 @@ int neigh_rebuild(b200md_ctx *c)
   std::swap(c->image, c->image_tmp);
   for (int k = 0; k < 3; k++) std::swap(c->v[k], c->v_tmp[k]);
 
+  ph.mark("permute");
   // ghosts
   TRY(comm_borders(c));
+  ph.mark("borders");
   const int nall = n + c->nghost;
+  if (nall > CLJMASK) return b200md_fail(c, B200MD_ERR_ARG, "more than 2^28 owned+ghost atoms on one GPU");
 
   // bin owned + ghost
   TRY(dev_ensure(c, c->cell_list, (size_t) nall));
-  TRY(bin_sort(c, nall, c->cell_list.p));
+  TRY(bin_sort(c, nall, c->cell_list.p, false));
+  ph.mark("bin all");
 
   // per-atom arrays that follow nlocal / nall
   TRY(dev_ensure(c, c->numneigh, (size_t) n));
@@ -347,22 +462,29 @@ int neigh_rebuild(b200md_ctx *c)
     TRY(dev_ensure(c, c->fp, (size_t) nall));
   }
 
+  const int CLs = c->cl;
+  const int nclus = cdiv(n, CLs);
   if (c->maxneigh == 0) {
     double vol = 1.0;
     for (int k = 0; k < 3; k++) vol *= c->subhi[k] - c->sublo[k];
     double expect = 4.18879020478639 * c->cutneighmax * c->cutneighmax * c->cutneighmax * n / vol;
-    int m = (int) (expect * 1.25) + 24;
+    // a cluster's list is the union of its atoms' lists (measured on an LJ melt: x1.4 / x1.9 / x2.6 for 2 / 4 / 8)
+    const double f = CLs == 1 ? 1.0 : CLs == 2 ? 1.5 : 2.0;
+    int m = (int) (expect * f * 1.2) + 24;
     c->maxneigh = (m + 7) / 8 * 8;
   }
-  const int ntiles = cdiv(n, TILE);
+  const int ntiles = cdiv(nclus, TILE);
   for (int attempt = 0; attempt < 8; attempt++) {
     TRY(dev_ensure(c, c->neigh, (size_t) ntiles * TILE * c->maxneigh));
     size_t smem = (size_t) (c->ntypes + 1) * (c->ntypes + 1) * sizeof(double);
     {
-    KProf kp(c, KC_NEIGH);
-    k_build_full<<<cdiv(n, 128), 128, smem, c->stream>>>(c->pos.p, n, c->bg, c->bin_start.p, c->cell_list.p, c->cutneighsq_d.p,
-                                                          c->ntypes, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d);
-    LAUNCH_CHECK();
+      KProf kp(c, KC_NEIGH);
+#define BUILD_ARGS c->pos.p, n, c->bg, c->bin_start.p, c->cell_list.p, c->cutneighsq_d.p, c->ntypes, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d
+      if (CLs == 1) k_build_cluster<1><<<cdiv(nclus, 128), 128, smem, c->stream>>>(BUILD_ARGS);
+      else if (CLs == 2) k_build_cluster<2><<<cdiv(nclus, 128), 128, smem, c->stream>>>(BUILD_ARGS);
+      else k_build_cluster<4><<<cdiv(nclus, 128), 128, smem, c->stream>>>(BUILD_ARGS);
+#undef BUILD_ARGS
+      LAUNCH_CHECK();
     }
     CU(cudaMemcpyAsync(c->flags_h, c->flags_d, 4 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
@@ -377,10 +499,12 @@ int neigh_rebuild(b200md_ctx *c)
   }
   if (c->flags_h[1] > c->maxneigh) return b200md_fail(c, B200MD_ERR_NEIGH_OVERFLOW, "Neighbor list overflow");
 
+  ph.mark("build");
   if (c->dist_check) {
     TRY(dev_ensure(c, c->xhold, (size_t) n));
     CU(cudaMemcpyAsync(c->xhold.p, c->pos.p, (size_t) n * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
   }
+  ph.mark("xhold");
   c->ago = 0;
   c->nbuilds++;
   c->list_valid = true;

@@ -19,7 +19,7 @@ __device__ __forceinline__ double4 ld4(const double4 *__restrict__ p)
   return make_double4(a.x, a.y, b.x, b.y);
 }
 
-__device__ __forceinline__ double4 ld_pos_e(const double4 *__restrict__ pos, int j) { return ld4(pos + j); }
+__device__ __forceinline__ double4 ld_pos_e(const double4 *__restrict__ pos, int j) { return ld_pos256(pos + j); }
 
 __device__ __forceinline__ double warp_sum_e(double v)
 {
@@ -55,133 +55,202 @@ struct EAMParams {
   const int *type2frho, *type2rhor, *type2z2r;
 };
 
-template <int EFLAG, int ONETYPE>
+template <int CL, int EFLAG, int ONETYPE>
 __global__ void __launch_bounds__(128)
 k_eam_rho_fp(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
              int nlocal, EAMParams P, double *__restrict__ rho_out, double *__restrict__ fp_out, double *__restrict__ partials)
 {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i0 = q * CL;
   double acc[1] = {0.0};
-  if (i < nlocal) {
-    const double4 pi = pos[i];
-    const int it = pos_type(pi);
-    const int n = numneigh[i];
+  if (i0 < nlocal) {
     const int nt1 = P.ntypes + 1;
-    const int *nb = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
-    double rho = 0.0;
-#pragma unroll 4
+    double xi[CL], yi[CL], zi[CL], rho[CL];
+    int it[CL];
+#pragma unroll
+    for (int a = 0; a < CL; a++) {
+      rho[a] = 0.0;
+      if (i0 + a < nlocal) {
+        const double4 p = pos[i0 + a];
+        xi[a] = p.x; yi[a] = p.y; zi[a] = p.z;
+        it[a] = pos_type(p);
+      } else {
+        xi[a] = yi[a] = zi[a] = 1e150;
+        it[a] = 1;
+      }
+    }
+    const int n = numneigh[q];
+    const int *nb = neigh + (size_t) (q >> 5) * TILE * maxneigh + (q & 31);
+#pragma unroll 2
     for (int k = 0; k < n; k++) {
-      const int j = __ldcs(nb + (size_t) k * TILE) & NEIGHMASK;
+      const unsigned ent = (unsigned) __ldcs(nb + (size_t) k * TILE);
+      const int j = (int) (ent & CLJMASK);
       const double4 pj = ld_pos_e(pos, j);
-      const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-      const double rsq = dx * dx + dy * dy + dz * dz;
-      if (rsq < P.cutforcesq) {
-        double p = sqrt(rsq) * P.rdr + 1.0;
-        int m = (int) p;
-        m = min(m, P.nr - 1);
-        p -= m;
-        p = fmin(p, 1.0);
-        const int tab = ONETYPE ? 0 : P.type2rhor[pos_type(pj) * nt1 + it];
-        const double4 cf = ld4(P.rhoA + (size_t) tab * (P.nr + 1) + m);
-        rho += ((cf.x * p + cf.y) * p + cf.z) * p + cf.w;
+      const int jt = pos_type(pj);
+#pragma unroll
+      for (int a = 0; a < CL; a++) {
+        const double dx = xi[a] - pj.x, dy = yi[a] - pj.y, dz = zi[a] - pj.z;
+        const double rsq = dx * dx + dy * dy + dz * dz;
+        if (rsq < P.cutforcesq && ((ent >> (CLBITS + a)) & 1u)) {
+          double p = sqrt(rsq) * P.rdr + 1.0;
+          int m = (int) p;
+          m = min(m, P.nr - 1);
+          p -= m;
+          p = fmin(p, 1.0);
+          const int tab = ONETYPE ? 0 : P.type2rhor[jt * nt1 + it[a]];
+          const double4 cf = ld4(P.rhoA + (size_t) tab * (P.nr + 1) + m);
+          rho[a] += ((cf.x * p + cf.y) * p + cf.z) * p + cf.w;
+        }
       }
     }
     // pass B (pair_eam.cpp:231-247)
-    double p = rho * P.rdrho + 1.0;
-    int m = (int) p;
-    m = max(1, min(m, P.nrho - 1));
-    p -= m;
-    p = fmin(p, 1.0);
-    const double *cf = P.frho + ((size_t) (ONETYPE ? 0 : P.type2frho[it]) * (P.nrho + 1) + m) * 7;
-    const double fpi = (__ldg(cf) * p + __ldg(cf + 1)) * p + __ldg(cf + 2);
-    rho_out[i] = rho;
-    fp_out[i] = fpi;
-    if (EFLAG) {
-      double phi = ((__ldg(cf + 3) * p + __ldg(cf + 4)) * p + __ldg(cf + 5)) * p + __ldg(cf + 6);
-      if (rho > P.rhomax) phi += fpi * (rho - P.rhomax);
-      acc[0] = phi;
+#pragma unroll
+    for (int a = 0; a < CL; a++) {
+      if (i0 + a >= nlocal) continue;
+      double p = rho[a] * P.rdrho + 1.0;
+      int m = (int) p;
+      m = max(1, min(m, P.nrho - 1));
+      p -= m;
+      p = fmin(p, 1.0);
+      const double *cf = P.frho + ((size_t) (ONETYPE ? 0 : P.type2frho[it[a]]) * (P.nrho + 1) + m) * 7;
+      const double fpi = (__ldg(cf) * p + __ldg(cf + 1)) * p + __ldg(cf + 2);
+      rho_out[i0 + a] = rho[a];
+      fp_out[i0 + a] = fpi;
+      if (EFLAG) {
+        double phi = ((__ldg(cf + 3) * p + __ldg(cf + 4)) * p + __ldg(cf + 5)) * p + __ldg(cf + 6);
+        if (rho[a] > P.rhomax) phi += fpi * (rho[a] - P.rhomax);
+        acc[0] += phi;
+      }
     }
   }
   if (EFLAG) block_partials_e<1>(acc, partials);
 }
 
-template <int EVFLAG, int ONETYPE>
+template <int CL, int EVFLAG, int ONETYPE>
 __global__ void __launch_bounds__(128)
 k_eam_force(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
             int nlocal, EAMParams P, const double *__restrict__ fp, double *__restrict__ fx, double *__restrict__ fy,
             double *__restrict__ fz, double *__restrict__ partials)
 {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i0 = q * CL;
   double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-  if (i < nlocal) {
-    const double4 pi = pos[i];
-    const int it = pos_type(pi);
-    const int n = numneigh[i];
+  if (i0 < nlocal) {
     const int nt1 = P.ntypes + 1;
-    const double fpi = fp[i];
-    const int *nb = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
-    double fxi = 0.0, fyi = 0.0, fzi = 0.0;
-#pragma unroll 2
+    double xi[CL], yi[CL], zi[CL], fpi[CL], fxi[CL], fyi[CL], fzi[CL];
+    int it[CL];
+#pragma unroll
+    for (int a = 0; a < CL; a++) {
+      fxi[a] = fyi[a] = fzi[a] = 0.0;
+      if (i0 + a < nlocal) {
+        const double4 p = pos[i0 + a];
+        xi[a] = p.x; yi[a] = p.y; zi[a] = p.z;
+        it[a] = pos_type(p);
+        fpi[a] = fp[i0 + a];
+      } else {
+        xi[a] = yi[a] = zi[a] = 1e150;
+        it[a] = 1;
+        fpi[a] = 0.0;
+      }
+    }
+    const int n = numneigh[q];
+    const int *nb = neigh + (size_t) (q >> 5) * TILE * maxneigh + (q & 31);
     for (int k = 0; k < n; k++) {
-      const int j = __ldcs(nb + (size_t) k * TILE) & NEIGHMASK;
+      const unsigned ent = (unsigned) __ldcs(nb + (size_t) k * TILE);
+      const int j = (int) (ent & CLJMASK);
       const double4 pj = ld_pos_e(pos, j);
-      const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-      const double rsq = dx * dx + dy * dy + dz * dz;
-      if (rsq < P.cutforcesq) {
-        const double r = sqrt(rsq);
-        double p = r * P.rdr + 1.0;
-        int m = (int) p;
-        m = min(m, P.nr - 1);
-        p -= m;
-        p = fmin(p, 1.0);
-        int t_ij = 0, t_ji = 0, t_z = 0;
-        if (!ONETYPE) {
-          const int jt = pos_type(pj);
-          t_ij = P.type2rhor[it * nt1 + jt];
-          t_ji = P.type2rhor[jt * nt1 + it];
-          t_z = P.type2z2r[it * nt1 + jt];
-        }
-        const double *c1 = P.rhor + ((size_t) t_ij * (P.nr + 1) + m) * 7;
-        const double rhoip = (__ldg(c1) * p + __ldg(c1 + 1)) * p + __ldg(c1 + 2);
-        double rhojp = rhoip;
-        if (!ONETYPE) {
-          const double *c2 = P.rhor + ((size_t) t_ji * (P.nr + 1) + m) * 7;
-          rhojp = (__ldg(c2) * p + __ldg(c2 + 1)) * p + __ldg(c2 + 2);
-        }
-        const double *c3 = P.z2r + ((size_t) t_z * (P.nr + 1) + m) * 7;
-        const double z2p = (__ldg(c3) * p + __ldg(c3 + 1)) * p + __ldg(c3 + 2);
-        const double z2 = ((__ldg(c3 + 3) * p + __ldg(c3 + 4)) * p + __ldg(c3 + 5)) * p + __ldg(c3 + 6);
-        const double recip = 1.0 / r;
-        const double phi = z2 * recip;
-        const double phip = z2p * recip - phi * recip;
-        const double psip = fpi * rhojp + __ldg(fp + j) * rhoip + phip;
-        const double fpair = -psip * recip;
-        fxi += dx * fpair;
-        fyi += dy * fpair;
-        fzi += dz * fpair;
-        if (EVFLAG) {
-          acc[0] += 0.5 * phi;
-          const double hf = 0.5 * fpair;
-          acc[1] += dx * dx * hf;
-          acc[2] += dy * dy * hf;
-          acc[3] += dz * dz * hf;
-          acc[4] += dx * dy * hf;
-          acc[5] += dx * dz * hf;
-          acc[6] += dy * dz * hf;
+      const double fpj = __ldg(fp + j);
+      const int jt = pos_type(pj);
+#pragma unroll
+      for (int a = 0; a < CL; a++) {
+        const double dx = xi[a] - pj.x, dy = yi[a] - pj.y, dz = zi[a] - pj.z;
+        const double rsq = dx * dx + dy * dy + dz * dz;
+        if (rsq < P.cutforcesq && ((ent >> (CLBITS + a)) & 1u)) {
+          const double r = sqrt(rsq);
+          double p = r * P.rdr + 1.0;
+          int m = (int) p;
+          m = min(m, P.nr - 1);
+          p -= m;
+          p = fmin(p, 1.0);
+          int t_ij = 0, t_ji = 0, t_z = 0;
+          if (!ONETYPE) {
+            t_ij = P.type2rhor[it[a] * nt1 + jt];
+            t_ji = P.type2rhor[jt * nt1 + it[a]];
+            t_z = P.type2z2r[it[a] * nt1 + jt];
+          }
+          const double *c1 = P.rhor + ((size_t) t_ij * (P.nr + 1) + m) * 7;
+          const double rhoip = (__ldg(c1) * p + __ldg(c1 + 1)) * p + __ldg(c1 + 2);
+          double rhojp = rhoip;
+          if (!ONETYPE) {
+            const double *c2 = P.rhor + ((size_t) t_ji * (P.nr + 1) + m) * 7;
+            rhojp = (__ldg(c2) * p + __ldg(c2 + 1)) * p + __ldg(c2 + 2);
+          }
+          const double *c3 = P.z2r + ((size_t) t_z * (P.nr + 1) + m) * 7;
+          const double z2p = (__ldg(c3) * p + __ldg(c3 + 1)) * p + __ldg(c3 + 2);
+          const double z2 = ((__ldg(c3 + 3) * p + __ldg(c3 + 4)) * p + __ldg(c3 + 5)) * p + __ldg(c3 + 6);
+          const double recip = 1.0 / r;
+          const double phi = z2 * recip;
+          const double phip = z2p * recip - phi * recip;
+          const double psip = fpi[a] * rhojp + fpj * rhoip + phip;
+          const double fpair = -psip * recip;
+          fxi[a] += dx * fpair;
+          fyi[a] += dy * fpair;
+          fzi[a] += dz * fpair;
+          if (EVFLAG) {
+            acc[0] += 0.5 * phi;
+            const double hf = 0.5 * fpair;
+            acc[1] += dx * dx * hf;
+            acc[2] += dy * dy * hf;
+            acc[3] += dz * dz * hf;
+            acc[4] += dx * dy * hf;
+            acc[5] += dx * dz * hf;
+            acc[6] += dy * dz * hf;
+          }
         }
       }
     }
-    fx[i] = fxi;
-    fy[i] = fyi;
-    fz[i] = fzi;
+#pragma unroll
+    for (int a = 0; a < CL; a++)
+      if (i0 + a < nlocal) {
+        fx[i0 + a] = fxi[a];
+        fy[i0 + a] = fyi[a];
+        fz[i0 + a] = fzi[a];
+      }
   }
   if (EVFLAG) block_partials_e<7>(acc, partials);
+}
+
+template <int CL> static void launch_eam_rho(b200md_ctx *c, int blocks, int threads, int ev, int onetype, const EAMParams &P, int n)
+{
+#define A_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, c->rho.p, c->fp.p, c->partials.p
+  if (ev) {
+    if (onetype) k_eam_rho_fp<CL, 1, 1><<<blocks, threads, 0, c->stream>>>(A_ARGS);
+    else k_eam_rho_fp<CL, 1, 0><<<blocks, threads, 0, c->stream>>>(A_ARGS);
+  } else {
+    if (onetype) k_eam_rho_fp<CL, 0, 1><<<blocks, threads, 0, c->stream>>>(A_ARGS);
+    else k_eam_rho_fp<CL, 0, 0><<<blocks, threads, 0, c->stream>>>(A_ARGS);
+  }
+#undef A_ARGS
+}
+
+template <int CL> static void launch_eam_force(b200md_ctx *c, int blocks, int threads, int ev, int onetype, const EAMParams &P, int n)
+{
+#define C_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, c->fp.p, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p
+  if (ev) {
+    if (onetype) k_eam_force<CL, 1, 1><<<blocks, threads, 0, c->stream>>>(C_ARGS);
+    else k_eam_force<CL, 1, 0><<<blocks, threads, 0, c->stream>>>(C_ARGS);
+  } else {
+    if (onetype) k_eam_force<CL, 0, 1><<<blocks, threads, 0, c->stream>>>(C_ARGS);
+    else k_eam_force<CL, 0, 0><<<blocks, threads, 0, c->stream>>>(C_ARGS);
+  }
+#undef C_ARGS
 }
 
 int pair_eam_compute(b200md_ctx *c, int eflag, int vflag)
 {
   const int n = c->nlocal;
-  const int threads = 128, blocks = cdiv(n, threads);
+  const int nclus = cdiv(n, c->cl);
+  const int threads = 128, blocks = cdiv(nclus, threads);
   const int ev = (eflag || vflag) ? 1 : 0;
   if (ev) TRY(dev_ensure(c, c->partials, (size_t) blocks * 8));
   const EAMTables &T = c->eam;
@@ -189,32 +258,20 @@ int pair_eam_compute(b200md_ctx *c, int eflag, int vflag)
                  T.type2frho, T.type2rhor, T.type2z2r};
   const int onetype = (T.ntypes == 1 && T.nrhor == 1 && T.nz2r == 1);
   {
-  KProf kp(c, KC_EAM_RHO);
-#define A_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, c->rho.p, c->fp.p, c->partials.p
-  if (ev) {
-    if (onetype) k_eam_rho_fp<1, 1><<<blocks, threads, 0, c->stream>>>(A_ARGS);
-    else k_eam_rho_fp<1, 0><<<blocks, threads, 0, c->stream>>>(A_ARGS);
-  } else {
-    if (onetype) k_eam_rho_fp<0, 1><<<blocks, threads, 0, c->stream>>>(A_ARGS);
-    else k_eam_rho_fp<0, 0><<<blocks, threads, 0, c->stream>>>(A_ARGS);
-  }
-#undef A_ARGS
-  LAUNCH_CHECK();
+    KProf kp(c, KC_EAM_RHO);
+    if (c->cl == 1) launch_eam_rho<1>(c, blocks, threads, ev, onetype, P, n);
+    else if (c->cl == 2) launch_eam_rho<2>(c, blocks, threads, ev, onetype, P, n);
+    else launch_eam_rho<4>(c, blocks, threads, ev, onetype, P, n);
+    LAUNCH_CHECK();
   }
   if (ev) TRY(reduce_partials(c, blocks, 1, 8));  // embedding energy -> red_d[8]
   TRY(halo_forward_scalar(c, c->fp.p));
   {
-  KProf kp(c, KC_PAIR);
-#define C_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, c->fp.p, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p
-  if (ev) {
-    if (onetype) k_eam_force<1, 1><<<blocks, threads, 0, c->stream>>>(C_ARGS);
-    else k_eam_force<1, 0><<<blocks, threads, 0, c->stream>>>(C_ARGS);
-  } else {
-    if (onetype) k_eam_force<0, 1><<<blocks, threads, 0, c->stream>>>(C_ARGS);
-    else k_eam_force<0, 0><<<blocks, threads, 0, c->stream>>>(C_ARGS);
-  }
-#undef C_ARGS
-  LAUNCH_CHECK();
+    KProf kp(c, KC_PAIR);
+    if (c->cl == 1) launch_eam_force<1>(c, blocks, threads, ev, onetype, P, n);
+    else if (c->cl == 2) launch_eam_force<2>(c, blocks, threads, ev, onetype, P, n);
+    else launch_eam_force<4>(c, blocks, threads, ev, onetype, P, n);
+    LAUNCH_CHECK();
   }
   if (ev) TRY(reduce_partials(c, blocks, 7, 0));  // pair energy + virial -> red_d[0..6]; eng = red[0] + red[8]
   return B200MD_OK;

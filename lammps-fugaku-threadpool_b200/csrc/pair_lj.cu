@@ -9,9 +9,7 @@ struct LJOne { double cutsq, lj1, lj2, lj3, lj4, offset; };
 
 __device__ __forceinline__ double4 ld_pos(const double4 *__restrict__ pos, int j)
 {
-  const double2 *q = reinterpret_cast<const double2 *>(pos + j);
-  double2 a = __ldg(q), b = __ldg(q + 1);
-  return make_double4(a.x, a.y, b.x, b.y);
+  return ld_pos256(pos + j);
 }
 
 __device__ __forceinline__ double warp_sum(double v)
@@ -39,11 +37,14 @@ template <int NC> __device__ __forceinline__ void block_partials(double (&acc)[N
   }
 }
 
-template <int EVFLAG, int ONETYPE>
+// One thread per cluster of CL consecutive owned atoms (neigh.cu): x_j is gathered once per list entry (one
+// 256-bit load) and tested against all CL atoms of the cluster.  A pair contributes iff its mask bit is set (it is
+// in the reference's list, decided at build time) and `rsq < cutsq` now -- exactly the reference's two tests.
+template <int CL, int EVFLAG, int ONETYPE>
 __global__ void __launch_bounds__(128)
-k_lj_full(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
-          int nlocal, LJOne one, const double *__restrict__ tables, int ntypes, double *__restrict__ fx,
-          double *__restrict__ fy, double *__restrict__ fz, double *__restrict__ partials)
+k_lj_cluster(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
+             int nlocal, LJOne one, const double *__restrict__ tables, int ntypes, double *__restrict__ fx,
+             double *__restrict__ fy, double *__restrict__ fz, double *__restrict__ partials)
 {
   extern __shared__ double s_tab[];  // 6 tables of (ntypes+1)^2 when !ONETYPE
   const int nt1 = ntypes + 1, nt2 = nt1 * nt1;
@@ -51,44 +52,62 @@ k_lj_full(const double4 *__restrict__ pos, const int *__restrict__ numneigh, con
     for (int k = threadIdx.x; k < 6 * nt2; k += blockDim.x) s_tab[k] = tables[k];
     __syncthreads();
   }
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  double fxi = 0.0, fyi = 0.0, fzi = 0.0;
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i0 = q * CL;
   double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-  if (i < nlocal) {
-    const double4 pi = pos[i];
-    const int n = numneigh[i];
-    const int *nb = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
-    const int trow = ONETYPE ? 0 : pos_type(pi) * nt1;
-#pragma unroll 4
-    for (int k = 0; k < n; k++) {
-      const int j = __ldcs(nb + (size_t) k * TILE) & NEIGHMASK;
-      const double4 pj = ld_pos(pos, j);
-      const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-      const double rsq = dx * dx + dy * dy + dz * dz;
-      double cutsq, lj1, lj2;
-      if (ONETYPE) {
-        cutsq = one.cutsq; lj1 = one.lj1; lj2 = one.lj2;
+  if (i0 < nlocal) {
+    double xi[CL], yi[CL], zi[CL], fxi[CL], fyi[CL], fzi[CL];
+    int trow[CL];
+#pragma unroll
+    for (int a = 0; a < CL; a++) {
+      fxi[a] = fyi[a] = fzi[a] = 0.0;
+      if (i0 + a < nlocal) {
+        const double4 p = pos[i0 + a];
+        xi[a] = p.x; yi[a] = p.y; zi[a] = p.z;
+        trow[a] = ONETYPE ? 0 : pos_type(p) * nt1;
       } else {
-        const int t = trow + pos_type(pj);
-        cutsq = s_tab[t]; lj1 = s_tab[nt2 + t]; lj2 = s_tab[2 * nt2 + t];
+        xi[a] = yi[a] = zi[a] = 1e150;
+        trow[a] = ONETYPE ? 0 : nt1;
       }
-      if (rsq < cutsq) {
-        const double r2inv = 1.0 / rsq;
+    }
+    const int n = numneigh[q];
+    const int *nb = neigh + (size_t) (q >> 5) * TILE * maxneigh + (q & 31);
+#pragma unroll 2
+    for (int k = 0; k < n; k++) {
+      const unsigned ent = (unsigned) __ldcs(nb + (size_t) k * TILE);
+      const int j = (int) (ent & CLJMASK);
+      const double4 pj = ld_pos256(pos + j);
+      const int jt = ONETYPE ? 0 : pos_type(pj);
+#pragma unroll
+      for (int a = 0; a < CL; a++) {
+        const double dx = xi[a] - pj.x, dy = yi[a] - pj.y, dz = zi[a] - pj.z;
+        const double rsq = dx * dx + dy * dy + dz * dz;
+        double cutsq, lj1, lj2;
+        if (ONETYPE) {
+          cutsq = one.cutsq; lj1 = one.lj1; lj2 = one.lj2;
+        } else {
+          const int t = trow[a] + jt;
+          cutsq = s_tab[t]; lj1 = s_tab[nt2 + t]; lj2 = s_tab[2 * nt2 + t];
+        }
+        // branch-free: the CL chains are independent and interleave (a divergent body per atom would serialise
+        // four long FP64 dependency chains); out-of-range pairs are computed and discarded by the select
+        const bool in = rsq < cutsq && ((ent >> (CLBITS + a)) & 1u);
+        const double r2inv = rcp_pos(rsq);
         const double r6inv = r2inv * r2inv * r2inv;
         const double forcelj = r6inv * (lj1 * r6inv - lj2);
-        const double fpair = forcelj * r2inv;
-        fxi += dx * fpair;
-        fyi += dy * fpair;
-        fzi += dz * fpair;
+        const double fpair = in ? forcelj * r2inv : 0.0;
+        fxi[a] += dx * fpair;
+        fyi[a] += dy * fpair;
+        fzi[a] += dz * fpair;
         if (EVFLAG) {
           double lj3, lj4, off;
           if (ONETYPE) {
             lj3 = one.lj3; lj4 = one.lj4; off = one.offset;
           } else {
-            const int t = trow + pos_type(pj);
+            const int t = trow[a] + jt;
             lj3 = s_tab[3 * nt2 + t]; lj4 = s_tab[4 * nt2 + t]; off = s_tab[5 * nt2 + t];
           }
-          acc[0] += 0.5 * (r6inv * (lj3 * r6inv - lj4) - off);
+          acc[0] += in ? 0.5 * (r6inv * (lj3 * r6inv - lj4) - off) : 0.0;
           const double hf = 0.5 * fpair;
           acc[1] += dx * dx * hf;
           acc[2] += dy * dy * hf;
@@ -99,9 +118,13 @@ k_lj_full(const double4 *__restrict__ pos, const int *__restrict__ numneigh, con
         }
       }
     }
-    fx[i] = fxi;
-    fy[i] = fyi;
-    fz[i] = fzi;
+#pragma unroll
+    for (int a = 0; a < CL; a++)
+      if (i0 + a < nlocal) {
+        fx[i0 + a] = fxi[a];
+        fy[i0 + a] = fyi[a];
+        fz[i0 + a] = fzi[a];
+      }
   }
   if (EVFLAG) block_partials<7>(acc, partials);
 }
@@ -131,27 +154,35 @@ int reduce_partials(b200md_ctx *c, int nblocks, int ncomp, int dst)
   return B200MD_OK;
 }
 
+template <int CL> static void launch_lj(b200md_ctx *c, int blocks, int threads, size_t smem, int ev, int onetype, const LJOne &one, int n)
+{
+#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p
+  if (ev) {
+    if (onetype) k_lj_cluster<CL, 1, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+    else k_lj_cluster<CL, 1, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+  } else {
+    if (onetype) k_lj_cluster<CL, 0, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+    else k_lj_cluster<CL, 0, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+  }
+#undef LJ_ARGS
+}
+
 int pair_lj_compute(b200md_ctx *c, int eflag, int vflag)
 {
   const int n = c->nlocal;
-  const int threads = 128, blocks = cdiv(n, threads);
+  const int nclus = cdiv(n, c->cl);
+  const int threads = 128, blocks = cdiv(nclus, threads);
   const int ev = (eflag || vflag) ? 1 : 0;
   if (ev) TRY(dev_ensure(c, c->partials, (size_t) blocks * 8));
   LJOne one = {c->lj.h_onetype[0], c->lj.h_onetype[1], c->lj.h_onetype[2], c->lj.h_onetype[3], c->lj.h_onetype[4], c->lj.h_onetype[5]};
   const int onetype = (c->lj.ntypes == 1);
   size_t smem = onetype ? 0 : (size_t) 6 * (c->lj.ntypes + 1) * (c->lj.ntypes + 1) * sizeof(double);
   {
-  KProf kp(c, KC_PAIR);
-#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p
-  if (ev) {
-    if (onetype) k_lj_full<1, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
-    else k_lj_full<1, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
-  } else {
-    if (onetype) k_lj_full<0, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
-    else k_lj_full<0, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
-  }
-#undef LJ_ARGS
-  LAUNCH_CHECK();
+    KProf kp(c, KC_PAIR);
+    if (c->cl == 1) launch_lj<1>(c, blocks, threads, smem, ev, onetype, one, n);
+    else if (c->cl == 2) launch_lj<2>(c, blocks, threads, smem, ev, onetype, one, n);
+    else launch_lj<4>(c, blocks, threads, smem, ev, onetype, one, n);
+    LAUNCH_CHECK();
   }
   if (ev) TRY(reduce_partials(c, blocks, 7, 0));
   return B200MD_OK;

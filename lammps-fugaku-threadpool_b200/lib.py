@@ -39,6 +39,7 @@ PROTOTYPES = {
     "b200md_neigh_build": (_i, [_vp]),
     "b200md_neigh_export": (_i, [_vp, _vp, _vp, _vp]),
     "b200md_neigh_stats": (_i, [_vp, _vp, _vp, _vp]),
+    "b200md_neigh_cluster_stats": (_i, [_vp, _vp, _vp, _vp]),
     "b200md_halo_forward": (_i, [_vp]),
     "b200md_plan_peers": (_i, [_vp, _vp, _i, _vp, _vp]),
     "b200md_pair_compute": (_i, [_vp, _i, _i, _vp, _vp]),
