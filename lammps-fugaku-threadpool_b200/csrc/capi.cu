@@ -77,7 +77,7 @@ extern "C" int b200md_destroy(b200md_ctx *c)
   dev_free(c, c->mass_d); dev_free(c, c->pos); dev_free(c, c->pos_tmp); dev_free(c, c->xhold);
   for (int k = 0; k < 3; k++) { dev_free(c, c->v[k]); dev_free(c, c->v_tmp[k]); dev_free(c, c->f[k]); }
   dev_free(c, c->tag); dev_free(c, c->tag_tmp); dev_free(c, c->image); dev_free(c, c->image_tmp);
-  dev_free(c, c->rho); dev_free(c, c->fp); dev_free(c, c->cutneighsq_d);
+  dev_free(c, c->rho); dev_free(c, c->fp); dev_free(c, c->posfp); dev_free(c, c->cutneighsq_d);
   dev_free(c, c->bin_count); dev_free(c, c->bin_start); dev_free(c, c->atom_bin); dev_free(c, c->cell_list);
   dev_free(c, c->perm); dev_free(c, c->scan_tmp); dev_free(c, c->atom_sub); dev_free(c, c->numneigh); dev_free(c, c->neigh);
   dev_free(c, c->send_idx); dev_free(c, c->border_blockcnt); dev_free(c, c->border_total); dev_free(c, c->send_dir);
@@ -88,6 +88,7 @@ extern "C" int b200md_destroy(b200md_ctx *c)
   if (c->eam.rhor) cudaFree(c->eam.rhor);
   if (c->eam.z2r) cudaFree(c->eam.z2r);
   if (c->eam.rhoA) cudaFree(c->eam.rhoA);
+  if (c->eam.tab1) cudaFree(c->eam.tab1);
   if (c->eam.type2frho) cudaFree(c->eam.type2frho);
   if (c->eam.type2rhor) cudaFree(c->eam.type2rhor);
   if (c->eam.type2z2r) cudaFree(c->eam.type2z2r);
@@ -324,7 +325,7 @@ extern "C" int b200md_eam_init(b200md_ctx *c, int ntypes, int nrho, int nr, doub
   NEED_CTX();
   if (ntypes < 1 || ntypes > B200MD_MAXTYPES) return b200md_fail(c, B200MD_ERR_ARG, "ntypes %d out of range", ntypes);
   EAMTables &T = c->eam;
-  if (T.frho) { cudaFree(T.frho); cudaFree(T.rhor); cudaFree(T.z2r); cudaFree(T.rhoA); cudaFree(T.type2frho); cudaFree(T.type2rhor); cudaFree(T.type2z2r); }
+  if (T.frho) { cudaFree(T.frho); cudaFree(T.rhor); cudaFree(T.z2r); cudaFree(T.rhoA); cudaFree(T.tab1); cudaFree(T.type2frho); cudaFree(T.type2rhor); cudaFree(T.type2z2r); }
   T.ntypes = ntypes; T.nrho = nrho; T.nr = nr; T.nfrho = nfrho; T.nrhor = nrhor; T.nz2r = nz2r;
   T.rdrho = rdrho; T.rdr = rdr; T.rhomax = rhomax; T.cutforcesq = cutforcesq;
   const size_t nf = (size_t) nfrho * (nrho + 1) * 7, nrr = (size_t) nrhor * (nr + 1) * 7, nz = (size_t) nz2r * (nr + 1) * 7;
@@ -343,6 +344,17 @@ extern "C" int b200md_eam_init(b200md_ctx *c, int ntypes, int nrho, int nr, doub
   for (size_t k = 0; k < (size_t) nrhor * (nr + 1); k++)
     for (int q = 0; q < 4; q++) a[4 * k + q] = rhor_spline[7 * k + 3 + q];
   CU(cudaMemcpy(T.rhoA, a.data(), a.size() * 8, cudaMemcpyHostToDevice));
+  {  // single-type fast path tables (first rhor / z2r table), SoA so that random knots spread over the smem banks
+    const int n1 = nr + 1;
+    std::vector<double> t1((size_t) 11 * n1);
+    for (int m = 0; m < n1; m++) {
+      for (int q = 0; q < 4; q++) t1[(size_t) q * n1 + m] = rhor_spline[7 * m + 3 + q];
+      for (int q = 0; q < 3; q++) t1[(size_t) (4 + q) * n1 + m] = rhor_spline[7 * m + q];
+      for (int q = 0; q < 4; q++) t1[(size_t) (7 + q) * n1 + m] = z2r_spline[7 * m + 3 + q];
+    }
+    CU(cudaMalloc((void **) &T.tab1, t1.size() * 8));
+    CU(cudaMemcpy(T.tab1, t1.data(), t1.size() * 8, cudaMemcpyHostToDevice));
+  }
   CU(cudaMemcpy(T.type2frho, type2frho, nt1 * 4, cudaMemcpyHostToDevice));
   CU(cudaMemcpy(T.type2rhor, type2rhor, nt1 * nt1 * 4, cudaMemcpyHostToDevice));
   CU(cudaMemcpy(T.type2z2r, type2z2r, nt1 * nt1 * 4, cudaMemcpyHostToDevice));

@@ -471,22 +471,25 @@ int comm_borders(b200md_ctx *c)
   return B200MD_OK;
 }
 
-// CommBrick::forward_comm: ghost positions from their owners
-int halo_forward_pos(b200md_ctx *c)
+// CommBrick::forward_comm: ghost records {x,y,z,w} from their owners; the sender adds the periodic shift to x,y,z
+// and passes w through (type for the position array, fp for the EAM {x,y,z,fp} array)
+int halo_forward_vec4(b200md_ctx *c, double4 *arr)
 {
   if (c->nsend > 0) {
     KProf kp(c, KC_HALO);
-    k_halo_pack_pos<0><<<cdiv(c->nsend, 256), 256, 0, c->stream>>>(c->pos.p, c->tag.p, c->send_idx.p, c->send_dir.p, c->nsend,
+    k_halo_pack_pos<0><<<cdiv(c->nsend, 256), 256, 0, c->stream>>>(arr, c->tag.p, c->send_idx.p, c->send_dir.p, c->nsend,
                                                                     c->nlocal, c->hp, c->sendbuf4.p, c->sendbuf_i.p);
     LAUNCH_CHECK();
   }
   if (any_remote(c)) {
     KProf kp(c, KC_HALO);
-    TRY(sendrecv_dirs(c, (const char *) c->sendbuf4.p, c->hp.soff, c->sendcount, (char *) (c->pos.p + c->nlocal), c->hp.goff,
+    TRY(sendrecv_dirs(c, (const char *) c->sendbuf4.p, c->hp.soff, c->sendcount, (char *) (arr + c->nlocal), c->hp.goff,
                       c->recvcount, sizeof(double4)));
   }
   return B200MD_OK;
 }
+
+int halo_forward_pos(b200md_ctx *c) { return halo_forward_vec4(c, c->pos.p); }
 
 // Comm::forward_comm(Pair*) with comm_forward = 1 (EAM fp): a[nlocal + g] from the owner's a[]
 int halo_forward_scalar(b200md_ctx *c, double *a)

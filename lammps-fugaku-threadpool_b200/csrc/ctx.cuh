@@ -69,7 +69,7 @@ struct EAMTables {            // what PairEAM::array2spline produces (src/MANYBO
   double rdrho, rdr, rhomax, cutforcesq;
   double *frho;               // device [nfrho][nrho+1][7]
   double4 *rhoA;              // device [nrhor][nr+1]  value coeffs {c3,c4,c5,c6} of rhor_spline  (pass A)
-  double4 *tabC;              // device [nrhor or nz2r][nr+1][...] see pair_eam.cu
+  double *tab1;               // device, single-type fast path: SoA [11][nr+1] = rhor c3..c6, rhor c0..c2, z2r c3..c6
   double *rhor, *z2r;         // device, original 7-coefficient layout
   int *type2frho, *type2rhor, *type2z2r;  // device
   int h_type2frho[B200MD_MAXTYPES + 1];
@@ -105,6 +105,7 @@ struct b200md_ctx {
   LJTables lj = {};
   EAMTables eam = {};
   DevBuf<double> rho, fp;
+  DevBuf<double4> posfp;      // EAM single-type path: {x, y, z, fp} per atom (owned + ghost), one sector per gather
   double cutforce = 0;
 
   // neighbor settings (src/neighbor.cpp:306-695)
@@ -264,6 +265,7 @@ int comm_borders(b200md_ctx *c);
 int comm_allreduce_sum(b200md_ctx *c, double *dev, int n);
 int comm_allreduce_max_int(b200md_ctx *c, int *dev, int n);
 int halo_forward_pos(b200md_ctx *c);
+int halo_forward_vec4(b200md_ctx *c, double4 *arr);
 int halo_forward_scalar(b200md_ctx *c, double *a);
 int pair_lj_compute(b200md_ctx *c, int eflag, int vflag);
 int pair_eam_compute(b200md_ctx *c, int eflag, int vflag);

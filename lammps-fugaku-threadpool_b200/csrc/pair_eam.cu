@@ -10,6 +10,8 @@
 // PairEAM::interpolate :769-797), 1-based knots m = 1..n, re-packed at init into 32-byte aligned pieces:
 //   rhoA[t][m]  = {c3,c4,c5,c6} of rhor_spline            (pass A reads one double4)
 //   tabC[t][m]  = {r0,r1,r2,-} {z0,z1,z2,z3} {z4,z5,z6,-}  only for the single-type fast path
+#include <stdlib.h>
+
 #include "ctx.cuh"
 
 __device__ __forceinline__ double4 ld4(const double4 *__restrict__ p)
@@ -220,6 +222,161 @@ k_eam_force(const double4 *__restrict__ pos, const int *__restrict__ numneigh, c
   if (EVFLAG) block_partials_e<7>(acc, partials);
 }
 
+// ------------------------------------------------------------------------------------------------
+// single-type fast path (the Cu benchmark): per-atom list, spline coefficients staged in shared memory as SoA
+// rows (random knots then spread over the banks and cost no L1 tag look-ups), r and 1/r from one rsqrt, and the
+// force pass gathers ONE 32-byte record {x,y,z,fp} per neighbor instead of position + fp[j] + 10 table words.
+// ncu on the generic kernels: 7 L1 sectors per pair in the force pass, LSU data pipe at 84 %.
+// ------------------------------------------------------------------------------------------------
+template <int EFLAG>
+__global__ void __launch_bounds__(256)
+k_eam_rho_fp_1t(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
+                int nlocal, EAMParams P, const double *__restrict__ tab1, double *__restrict__ rho_out,
+                double *__restrict__ fp_out, double4 *__restrict__ posfp, double *__restrict__ partials)
+{
+  extern __shared__ double s_t[];  // [4][n1]: rhor c3..c6
+  const int n1 = P.nr + 1;
+  for (int k = threadIdx.x; k < 4 * n1; k += blockDim.x) s_t[k] = tab1[k];
+  __syncthreads();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  double acc[1] = {0.0};
+  if (i < nlocal) {
+    const double4 pi = pos[i];
+    const int n = numneigh[i];
+    const int *nb = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
+    double rho = 0.0;
+#pragma unroll 4
+    for (int k = 0; k < n; k++) {
+      const unsigned ent = (unsigned) __ldcs(nb + (size_t) k * TILE);
+      const double4 pj = ld_pos256(pos + (ent & CLJMASK));
+      const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+      const double rsq = dx * dx + dy * dy + dz * dz;
+      if (rsq < P.cutforcesq) {
+        double p = rsq * rsqrt(rsq) * P.rdr + 1.0;
+        int m = (int) p;
+        m = min(m, P.nr - 1);
+        p -= m;
+        p = fmin(p, 1.0);
+        rho += ((s_t[m] * p + s_t[n1 + m]) * p + s_t[2 * n1 + m]) * p + s_t[3 * n1 + m];
+      }
+    }
+    double p = rho * P.rdrho + 1.0;
+    int m = (int) p;
+    m = max(1, min(m, P.nrho - 1));
+    p -= m;
+    p = fmin(p, 1.0);
+    const double *cf = P.frho + (size_t) m * 7;
+    const double fpi = (__ldg(cf) * p + __ldg(cf + 1)) * p + __ldg(cf + 2);
+    rho_out[i] = rho;
+    fp_out[i] = fpi;
+    posfp[i] = make_double4(pi.x, pi.y, pi.z, fpi);
+    if (EFLAG) {
+      double phi = ((__ldg(cf + 3) * p + __ldg(cf + 4)) * p + __ldg(cf + 5)) * p + __ldg(cf + 6);
+      if (rho > P.rhomax) phi += fpi * (rho - P.rhomax);
+      acc[0] = phi;
+    }
+  }
+  if (EFLAG) block_partials_e<1>(acc, partials);
+}
+
+template <int EVFLAG>
+__global__ void __launch_bounds__(256)
+k_eam_force_1t(const double4 *__restrict__ posfp, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
+               int nlocal, EAMParams P, const double *__restrict__ tab1, double *__restrict__ fx, double *__restrict__ fy,
+               double *__restrict__ fz, double *__restrict__ partials)
+{
+  extern __shared__ double s_t[];  // [7][n1]: rhor c0..c2 (derivative), z2r c3..c6 (value; derivative derived)
+  const int n1 = P.nr + 1;
+  for (int k = threadIdx.x; k < 7 * n1; k += blockDim.x) s_t[k] = tab1[4 * n1 + k];
+  __syncthreads();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  if (i < nlocal) {
+    const double4 pi = posfp[i];
+    const int n = numneigh[i];
+    const int *nb = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
+    double fxi = 0.0, fyi = 0.0, fzi = 0.0;
+#pragma unroll 2
+    for (int k = 0; k < n; k++) {
+      const unsigned ent = (unsigned) __ldcs(nb + (size_t) k * TILE);
+      const double4 pj = ld_pos256(posfp + (ent & CLJMASK));
+      const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+      const double rsq = dx * dx + dy * dy + dz * dz;
+      if (rsq < P.cutforcesq) {
+        const double recip = rsqrt(rsq);
+        const double r = rsq * recip;
+        double p = r * P.rdr + 1.0;
+        int m = (int) p;
+        m = min(m, P.nr - 1);
+        p -= m;
+        p = fmin(p, 1.0);
+        const double rhoip = (s_t[m] * p + s_t[n1 + m]) * p + s_t[2 * n1 + m];
+        const double z3 = s_t[3 * n1 + m], z4 = s_t[4 * n1 + m], z5 = s_t[5 * n1 + m], z6 = s_t[6 * n1 + m];
+        const double z2 = ((z3 * p + z4) * p + z5) * p + z6;
+        const double z2p = ((3.0 * z3 * p + 2.0 * z4) * p + z5) * P.rdr;  // = spline[0..2] of array2spline (:752-754)
+        const double phi = z2 * recip;
+        const double phip = z2p * recip - phi * recip;
+        const double psip = (pi.w + pj.w) * rhoip + phip;  // one type: rhojp == rhoip
+        const double fpair = -psip * recip;
+        fxi += dx * fpair;
+        fyi += dy * fpair;
+        fzi += dz * fpair;
+        if (EVFLAG) {
+          acc[0] += 0.5 * phi;
+          const double hf = 0.5 * fpair;
+          acc[1] += dx * dx * hf;
+          acc[2] += dy * dy * hf;
+          acc[3] += dz * dz * hf;
+          acc[4] += dx * dy * hf;
+          acc[5] += dx * dz * hf;
+          acc[6] += dy * dz * hf;
+        }
+      }
+    }
+    fx[i] = fxi;
+    fy[i] = fyi;
+    fz[i] = fzi;
+  }
+  if (EVFLAG) block_partials_e<7>(acc, partials);
+}
+
+static int pair_eam_compute_1t(b200md_ctx *c, int ev, const EAMParams &P)
+{
+  const int n = c->nlocal, threads = 256, blocks = cdiv(n, threads);
+  const EAMTables &T = c->eam;
+  const size_t n1 = (size_t) T.nr + 1, smemA = 4 * n1 * 8, smemC = 7 * n1 * 8;
+  TRY(dev_ensure(c, c->posfp, (size_t) n + c->nghost));
+  if (ev) TRY(dev_ensure(c, c->partials, (size_t) blocks * 8));
+  static bool attr_done = false;
+  if (!attr_done) {
+    CU(cudaFuncSetAttribute(k_eam_force_1t<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU(cudaFuncSetAttribute(k_eam_force_1t<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU(cudaFuncSetAttribute(k_eam_rho_fp_1t<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU(cudaFuncSetAttribute(k_eam_rho_fp_1t<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr_done = true;
+  }
+  {
+    KProf kp(c, KC_EAM_RHO);
+#define A1 c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->rho.p, c->fp.p, c->posfp.p, c->partials.p
+    if (ev) k_eam_rho_fp_1t<1><<<blocks, threads, smemA, c->stream>>>(A1);
+    else k_eam_rho_fp_1t<0><<<blocks, threads, smemA, c->stream>>>(A1);
+#undef A1
+    LAUNCH_CHECK();
+  }
+  if (ev) TRY(reduce_partials(c, blocks, 1, 8));
+  TRY(halo_forward_vec4(c, c->posfp.p));  // ghosts get {x + shift, fp} from their owners in one message
+  {
+    KProf kp(c, KC_PAIR);
+#define C1 c->posfp.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p
+    if (ev) k_eam_force_1t<1><<<blocks, threads, smemC, c->stream>>>(C1);
+    else k_eam_force_1t<0><<<blocks, threads, smemC, c->stream>>>(C1);
+#undef C1
+    LAUNCH_CHECK();
+  }
+  if (ev) TRY(reduce_partials(c, blocks, 7, 0));
+  return B200MD_OK;
+}
+
 template <int CL> static void launch_eam_rho(b200md_ctx *c, int blocks, int threads, int ev, int onetype, const EAMParams &P, int n)
 {
 #define A_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, c->rho.p, c->fp.p, c->partials.p
@@ -257,6 +414,8 @@ int pair_eam_compute(b200md_ctx *c, int eflag, int vflag)
   EAMParams P = {T.ntypes, T.nrho, T.nr, T.rdrho, T.rdr, T.rhomax, T.cutforcesq, T.frho, T.rhor, T.z2r, T.rhoA,
                  T.type2frho, T.type2rhor, T.type2z2r};
   const int onetype = (T.ntypes == 1 && T.nrhor == 1 && T.nz2r == 1);
+  if (onetype && c->cl == 1 && (size_t) 7 * (T.nr + 1) * 8 <= 96 * 1024 && !getenv("B200MD_EAM_GENERIC"))
+    return pair_eam_compute_1t(c, ev, P);
   {
     KProf kp(c, KC_EAM_RHO);
     if (c->cl == 1) launch_eam_rho<1>(c, blocks, threads, ev, onetype, P, n);
