@@ -90,6 +90,7 @@ struct b200md_ctx {
   int periodic[3] = {1, 1, 1}, procgrid[3] = {1, 1, 1}, myloc[3] = {0, 0, 0};
   double sublo[3], subhi[3];
   bool have_box = false;
+  bool host_ghosts = false;   // host-buffer mode: ghosts are supplied by the caller (hostmode.cu)
   int ntypes = 0;
   double mass_h[B200MD_MAXTYPES + 1];
   DevBuf<double> mass_d;
@@ -258,6 +259,7 @@ enum { SECT_PAIR = 0, SECT_NEIGH = 1, SECT_COMM = 2, SECT_MODIFY = 3, SECT_OTHER
 // ---- internal entry points (one per .cu) ------------------------------------------------------
 int neigh_setup_bins(b200md_ctx *c);
 int neigh_rebuild(b200md_ctx *c);          // pbc + sort + borders + bin + build
+int neigh_build_lists(b200md_ctx *c);      // bin owned+ghost + build (second half of neigh_rebuild)
 int neigh_check_distance(b200md_ctx *c, int *moved);
 int comm_plan(b200md_ctx *c);
 int comm_exchange(b200md_ctx *c);

@@ -257,7 +257,7 @@ int neigh_setup_bins(b200md_ctx *c)
   for (int k = 0; k < 3; k++) {
     double len = c->subhi[k] - c->sublo[k];
     bool decomposed_or_periodic = c->periodic[k] || c->procgrid[k] > 1;
-    if (decomposed_or_periodic && len < c->cutneighmax)
+    if (!c->host_ghosts && decomposed_or_periodic && len < c->cutneighmax)
       return b200md_fail(c, B200MD_ERR_DOMAIN, "sub-domain (%g) thinner than the ghost cutoff (%g) in dim %d", len,
                          c->cutneighmax, k);
     int nb = (int) (len / target);
@@ -446,6 +446,15 @@ int neigh_rebuild(b200md_ctx *c)
   // ghosts
   TRY(comm_borders(c));
   ph.mark("borders");
+  return neigh_build_lists(c);
+}
+
+// bin owned + ghost atoms and build the list from the positions now on the device (also the entry point of the
+// host-buffer mode, where the caller supplies the ghosts: hostmode.cu)
+int neigh_build_lists(b200md_ctx *c)
+{
+  PhaseTimer ph(c);
+  const int n = c->nlocal;
   const int nall = n + c->nghost;
   if (nall > CLJMASK) return b200md_fail(c, B200MD_ERR_ARG, "more than 2^28 owned+ghost atoms on one GPU");
 
