@@ -123,6 +123,7 @@ struct b200md_ctx {
   BinGeom bg;
   DevBuf<int> bin_count, bin_start, atom_bin, cell_list, perm, scan_tmp;
   DevBuf<unsigned char> atom_sub;
+  DevBuf<double> binrec;      // BinRec[nall] (16 B each): FP32 candidate records in cell_list order (neigh.cu)
 
   // neighbor list
   int cl = 1;                 // cluster size of the neighbor list (1, 2 or 4 atoms per list), env B200MD_CLUSTER

@@ -69,13 +69,23 @@ __device__ __forceinline__ int subcell_of(const BinGeom &g, double x, double y, 
 }
 
 template <int WITH_SUB>
-__global__ void k_bin_count(const double4 *__restrict__ pos, int n, BinGeom g, int *__restrict__ atom_bin,
+__global__ void k_bin_count(const double4 *__restrict__ pos, int n, int nowned, BinGeom g, int *__restrict__ atom_bin,
                             int *__restrict__ bin_count, unsigned char *__restrict__ atom_sub)
 {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   double4 p = pos[i];
-  int b = bin_of(g, p.x, p.y, p.z);
+  int b;
+  if (i < nowned) {
+    // owned atoms always land in a bin of the sub-domain proper, also when (x - lo) * inv rounds up to nbin at the
+    // upper face (the case NBin::coord2bin's `x >= hi` branch exists for, src/nbin.cpp:150-157): the warp-per-bin
+    // build walks exactly these bins
+    int bx = min(max((int) floor((p.x - g.lo[0]) * g.inv[0]), 0), g.nbin[0] - 1) + BIN_MARGIN;
+    int by = min(max((int) floor((p.y - g.lo[1]) * g.inv[1]), 0), g.nbin[1] - 1) + BIN_MARGIN;
+    int bz = min(max((int) floor((p.z - g.lo[2]) * g.inv[2]), 0), g.nbin[2] - 1) + BIN_MARGIN;
+    b = (bz * g.mbin[1] + by) * g.mbin[0] + bx;
+  } else
+    b = bin_of(g, p.x, p.y, p.z);
   atom_bin[i] = b;
   if (WITH_SUB) atom_sub[i] = (unsigned char) subcell_of(g, p.x, p.y, p.z);
   atomicAdd(&bin_count[b], 1);
@@ -232,8 +242,8 @@ static int bin_sort(b200md_ctx *c, int n, int *list, bool with_sub)
   if (with_sub) TRY(dev_ensure(c, c->atom_sub, (size_t) n));
   KProf kp(c, KC_SORT);
   CU(cudaMemsetAsync(c->bin_count.p, 0, ((size_t) g.mbins + 1) * sizeof(int), c->stream));
-  if (with_sub) k_bin_count<1><<<cdiv(n, 256), 256, 0, c->stream>>>(c->pos.p, n, g, c->atom_bin.p, c->bin_count.p, c->atom_sub.p);
-  else k_bin_count<0><<<cdiv(n, 256), 256, 0, c->stream>>>(c->pos.p, n, g, c->atom_bin.p, c->bin_count.p, nullptr);
+  if (with_sub) k_bin_count<1><<<cdiv(n, 256), 256, 0, c->stream>>>(c->pos.p, n, c->nlocal, g, c->atom_bin.p, c->bin_count.p, c->atom_sub.p);
+  else k_bin_count<0><<<cdiv(n, 256), 256, 0, c->stream>>>(c->pos.p, n, c->nlocal, g, c->atom_bin.p, c->bin_count.p, nullptr);
   LAUNCH_CHECK();
   TRY(exclusive_scan(c, c->bin_count.p, c->bin_start.p, g.mbins + 1));
   CU(cudaMemsetAsync(c->bin_count.p, 0, ((size_t) g.mbins + 1) * sizeof(int), c->stream));
@@ -358,6 +368,134 @@ k_build_cluster(const double4 *__restrict__ pos, int nlocal, BinGeom g, const in
   unsigned am = __activemask();
   int nmax = __reduce_max_sync(am, n);
   if ((threadIdx.x & 31) == (__ffs(am) - 1)) atomicMax(&flags[1], nmax);  // flags[1] = longest list seen
+}
+
+// ------------------------------------------------------------------------------------------------
+// neighbor build, warp-cooperative form (the default, per-atom lists): ONE WARP PER BIN.
+//   * k_binrec_fill stages every binned atom (owned + ghost, in cell_list order) as a 16-byte record
+//     {float x, y, z relative to the bin-grid origin; j | (type-1) << 28}: the candidates of a bin's 27-bin stencil
+//     are then 9 CONTIGUOUS record ranges (3 bins of an x-row each), read as warp-uniform (broadcast) 128-bit loads
+//     -- no per-lane gathers, no per-lane trip counts.
+//   * lanes = the owned atoms of the bin.  Every lane tests every candidate in FP32 (6 flops); the decision is
+//     final when |rsq_f - cutneighsq| > tol, where tol rigorously bounds the FP32 error (derivation at
+//     build_tolerance()).  Inside the band (about 1 candidate in 10^4) the reference's own FP64 expression decides:
+//     rsq = delx*delx + dely*dely + delz*delz without FMA contraction, keep if rsq <= cutneighsq[itype][jtype]
+//     (src/npair_half_bin_atomonly_newton.cpp:80-87).  List membership is therefore bit-identical to the all-FP64
+//     kernel above and to the reference's list as tag-pair sets.
+//   * entry order per atom = (dz, dy) rows, then cell_list order -- the same order k_build_cluster<1> emits, so the
+//     force summation order (and every bit of the forces) is unchanged.
+// ------------------------------------------------------------------------------------------------
+struct BinRec { float x, y, z; int jt; };
+#define BR_JMASK 0x0FFFFFFF
+
+__global__ void k_binrec_fill(const double4 *__restrict__ pos, const int *__restrict__ cell_list, int nall, double ox, double oy,
+                              double oz, BinRec *__restrict__ rec)
+{
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= nall) return;
+  const int j = cell_list[k];
+  const double4 p = pos[j];
+  BinRec r;
+  r.x = (float) (p.x - ox);
+  r.y = (float) (p.y - oy);
+  r.z = (float) (p.z - oz);
+  r.jt = j | ((pos_type(p) - 1) << 28);
+  rec[k] = r;
+}
+
+__device__ __forceinline__ BinRec ld_rec(const BinRec *__restrict__ p)
+{
+  const int4 v = __ldg(reinterpret_cast<const int4 *>(p));
+  BinRec r;
+  r.x = __int_as_float(v.x); r.y = __int_as_float(v.y); r.z = __int_as_float(v.z); r.jt = v.w;
+  return r;
+}
+
+#define BUILD_WARPS 8
+template <int ONETYPE>
+__global__ void __launch_bounds__(BUILD_WARPS * 32)
+k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int nlocal, BinGeom g,
+             const int *__restrict__ bin_start, const double *__restrict__ cutneighsq, int ntypes, float tol, int maxneigh,
+             int *__restrict__ numneigh, int *__restrict__ neigh, int *__restrict__ flags)
+{
+  __shared__ double s_cut[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
+  __shared__ float s_cutf[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
+  const int nt1 = ntypes + 1;
+  for (int k = threadIdx.x; k < nt1 * nt1; k += blockDim.x) { s_cut[k] = cutneighsq[k]; s_cutf[k] = (float) cutneighsq[k]; }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int wb = blockIdx.x * BUILD_WARPS + (threadIdx.x >> 5);      // owned-bin number, x fastest
+  const int nown = g.nbin[0] * g.nbin[1] * g.nbin[2];
+  if (wb >= nown) return;
+  const int obx = wb % g.nbin[0], oby = (wb / g.nbin[0]) % g.nbin[1], obz = wb / (g.nbin[0] * g.nbin[1]);
+  const int bx = obx + BIN_MARGIN, by = oby + BIN_MARGIN, bz = obz + BIN_MARGIN;
+  const int b = (bz * g.mbin[1] + by) * g.mbin[0] + bx;
+  const int s0 = bin_start[b], e0 = bin_start[b + 1];
+  const float cut1 = s_cutf[nt1 + 1];
+  int nmax = 0;
+  // owned atoms come first in a bin's segment (cell_list is index-ordered within a bin, ghosts have index >= nlocal)
+  for (int gbase = s0; gbase < e0; gbase += 32) {
+    const int kk = gbase + lane;
+    BinRec me;
+    me.x = me.y = me.z = 0.f;
+    me.jt = BR_JMASK;
+    if (kk < e0) me = ld_rec(rec + kk);
+    const int i = me.jt & BR_JMASK;
+    const bool owned = (kk < e0) && i < nlocal;
+    if (!__any_sync(0xffffffffu, owned)) break;
+    const int trow = ONETYPE ? 0 : (((unsigned) me.jt >> 28) + 1) * nt1;
+    const size_t base = (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
+    int n = 0;
+    for (int dz = -1; dz <= 1; dz++)
+      for (int dy = -1; dy <= 1; dy++) {
+        const int cell = ((bz + dz) * g.mbin[1] + (by + dy)) * g.mbin[0] + bx - 1;
+        const int ks = bin_start[cell], ke = bin_start[cell + 3];
+#pragma unroll 4
+        for (int k = ks; k < ke; k++) {
+          const BinRec c = ld_rec(rec + k);
+          const float dx = me.x - c.x, dyy = me.y - c.y, dzz = me.z - c.z;
+          const float rsq = fmaf(dzz, dzz, fmaf(dyy, dyy, dx * dx));
+          const float cut = ONETYPE ? cut1 : s_cutf[trow + ((unsigned) c.jt >> 28) + 1];
+          bool accept = rsq <= cut - tol;
+          if (!accept && rsq <= cut + tol) {   // ambiguity band: the reference's FP64 expression decides
+            const int j = c.jt & BR_JMASK;
+            const double4 pi = pos[min(i, nlocal - 1)], pj = pos[j];
+            const double ddx = __dsub_rn(pi.x, pj.x), ddy = __dsub_rn(pi.y, pj.y), ddz = __dsub_rn(pi.z, pj.z);
+            const double r2 = __dadd_rn(__dadd_rn(__dmul_rn(ddx, ddx), __dmul_rn(ddy, ddy)), __dmul_rn(ddz, ddz));
+            accept = r2 <= s_cut[(ONETYPE ? nt1 : trow) + (ONETYPE ? 1 : ((unsigned) c.jt >> 28) + 1)];
+          }
+          const int j = c.jt & BR_JMASK;
+          if (accept && owned && j != i) {
+            if (n < maxneigh) neigh[base + (size_t) n * TILE] = j | (1 << CLBITS);
+            n++;
+          }
+        }
+      }
+    if (owned) numneigh[i] = n;
+    nmax = max(nmax, owned ? n : 0);
+  }
+  nmax = __reduce_max_sync(0xffffffffu, nmax);
+  if (lane == 0 && nmax > 0) atomicMax(&flags[1], nmax);
+}
+
+// Rigorous bound on |rsq_f - rsq| of k_build_bins for any pair with r <= 2*rc (pairs farther apart differ from the
+// cutoff by more than 3*rc^2, far outside any band): coordinates are stored relative to the bin-grid origin, so
+// |x_f - x| <= u*M with u = 2^-24 and M the grid extent; dx_f carries both conversion errors plus one rounding:
+// |dx_f - dx| <= 2u(M + r); three squared terms and three roundings give
+// |rsq_f - rsq| <= 2*sqrt(3)*r*2u(M + r) + 3u*rsq + (float)cutneighsq conversion (u*rc^2).
+// tol is that bound at r = 2*rc with another factor 2 of slack.  The FP32 path is used only while tol stays
+// below 1 % of the smallest cutneighsq (huge boxes with tiny cutoffs fall back to the all-FP64 kernel).
+static double build_tolerance(const b200md_ctx *c, double *cutsq_min_out)
+{
+  const BinGeom &g = c->bg;
+  double M = 0.0;
+  for (int k = 0; k < 3; k++) M = fmax(M, g.mbin[k] / g.inv[k]);
+  const double u = 1.0 / 16777216.0, rc = c->cutneighmax, r = 2.0 * rc;
+  double cmin = 1e300;
+  for (int i = 1; i <= c->ntypes; i++)
+    for (int j = 1; j <= c->ntypes; j++) cmin = fmin(cmin, c->cutneighsq_h[i * (c->ntypes + 1) + j]);
+  if (cutsq_min_out) *cutsq_min_out = cmin;
+  return 2.0 * (2.0 * 1.7320508075688772 * r * 2.0 * u * (M + r) + 3.0 * u * r * r + u * rc * rc);
 }
 
 __global__ void k_check_distance(const double4 *__restrict__ pos, const double4 *__restrict__ xhold, int n, double triggersq,
@@ -486,7 +624,25 @@ int neigh_build_lists(b200md_ctx *c)
   for (int attempt = 0; attempt < 8; attempt++) {
     TRY(dev_ensure(c, c->neigh, (size_t) ntiles * TILE * c->maxneigh));
     size_t smem = (size_t) (c->ntypes + 1) * (c->ntypes + 1) * sizeof(double);
-    {
+    double cutsq_min = 0.0;
+    const double tol = build_tolerance(c, &cutsq_min);
+    if (CLs == 1 && tol < 0.01 * cutsq_min && !getenv("B200MD_BUILD_FP64")) {
+      const BinGeom &g = c->bg;
+      TRY(dev_ensure(c, c->binrec, (size_t) nall * 2));  // 16-byte records held as double pairs
+      KProf kp(c, KC_NEIGH);
+      BinRec *rec = reinterpret_cast<BinRec *>(c->binrec.p);
+      k_binrec_fill<<<cdiv(nall, 256), 256, 0, c->stream>>>(c->pos.p, c->cell_list.p, nall, g.lo[0] - BIN_MARGIN / g.inv[0],
+                                                            g.lo[1] - BIN_MARGIN / g.inv[1], g.lo[2] - BIN_MARGIN / g.inv[2], rec);
+      LAUNCH_CHECK();
+      const int nown = g.nbin[0] * g.nbin[1] * g.nbin[2];
+      if (c->ntypes == 1)
+        k_build_bins<1><<<cdiv(nown, BUILD_WARPS), BUILD_WARPS * 32, 0, c->stream>>>(
+            c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d);
+      else
+        k_build_bins<0><<<cdiv(nown, BUILD_WARPS), BUILD_WARPS * 32, 0, c->stream>>>(
+            c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d);
+      LAUNCH_CHECK();
+    } else {
       KProf kp(c, KC_NEIGH);
 #define BUILD_ARGS c->pos.p, n, c->bg, c->bin_start.p, c->cell_list.p, c->cutneighsq_d.p, c->ntypes, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d
       if (CLs == 1) k_build_cluster<1><<<cdiv(nclus, 128), 128, smem, c->stream>>>(BUILD_ARGS);

@@ -228,8 +228,11 @@ k_eam_force(const double4 *__restrict__ pos, const int *__restrict__ numneigh, c
 // force pass gathers ONE 32-byte record {x,y,z,fp} per neighbor instead of position + fp[j] + 10 table words.
 // ncu on the generic kernels: 7 L1 sectors per pair in the force pass, LSU data pipe at 84 %.
 // ------------------------------------------------------------------------------------------------
+// one table copy per 512-thread block: fewer, larger blocks leave more of the 228 KB for L1 (ncu, 256-thread blocks:
+// L1 hit rate 17 % in the rho pass with 8 table copies per SM)
+#define EAM1T_THREADS 512
 template <int EFLAG>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(EAM1T_THREADS, 2)
 k_eam_rho_fp_1t(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
                 int nlocal, EAMParams P, const double *__restrict__ tab1, double *__restrict__ rho_out,
                 double *__restrict__ fp_out, double4 *__restrict__ posfp, double *__restrict__ partials)
@@ -245,19 +248,30 @@ k_eam_rho_fp_1t(const double4 *__restrict__ pos, const int *__restrict__ numneig
     const int n = numneigh[i];
     const int *nb = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
     double rho = 0.0;
-#pragma unroll 4
-    for (int k = 0; k < n; k++) {
-      const unsigned ent = (unsigned) __ldcs(nb + (size_t) k * TILE);
-      const double4 pj = ld_pos256(pos + (ent & CLJMASK));
-      const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-      const double rsq = dx * dx + dy * dy + dz * dz;
-      if (rsq < P.cutforcesq) {
-        double p = rsq * rsqrt(rsq) * P.rdr + 1.0;
-        int m = (int) p;
-        m = min(m, P.nr - 1);
-        p -= m;
-        p = fmin(p, 1.0);
-        rho += ((s_t[m] * p + s_t[n1 + m]) * p + s_t[2 * n1 + m]) * p + s_t[3 * n1 + m];
+    // software pipeline (see k_lj_lanes): next batch of list entries in flight while PF gathers are issued together
+    constexpr int PF = 4;
+    const int nlast = max(n - 1, 0);
+    unsigned enx[PF];
+#pragma unroll
+    for (int u = 0; u < PF; u++) enx[u] = (unsigned) __ldcs(nb + (size_t) min(u, nlast) * TILE);
+    for (int k0 = 0; k0 < n; k0 += PF) {
+      double4 pj[PF];
+#pragma unroll
+      for (int u = 0; u < PF; u++) pj[u] = ld_pos256(pos + (enx[u] & CLJMASK));
+#pragma unroll
+      for (int u = 0; u < PF; u++) enx[u] = (unsigned) __ldcs(nb + (size_t) min(k0 + PF + u, nlast) * TILE);
+#pragma unroll
+      for (int u = 0; u < PF; u++) {
+        const double dx = pi.x - pj[u].x, dy = pi.y - pj[u].y, dz = pi.z - pj[u].z;
+        const double rsq = dx * dx + dy * dy + dz * dz;
+        if (rsq < P.cutforcesq && k0 + u < n) {
+          double p = rsq * rsqrt(rsq) * P.rdr + 1.0;
+          int m = (int) p;
+          m = min(m, P.nr - 1);
+          p -= m;
+          p = fmin(p, 1.0);
+          rho += ((s_t[m] * p + s_t[n1 + m]) * p + s_t[2 * n1 + m]) * p + s_t[3 * n1 + m];
+        }
       }
     }
     double p = rho * P.rdrho + 1.0;
@@ -280,7 +294,7 @@ k_eam_rho_fp_1t(const double4 *__restrict__ pos, const int *__restrict__ numneig
 }
 
 template <int EVFLAG>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(EAM1T_THREADS, 2)
 k_eam_force_1t(const double4 *__restrict__ posfp, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
                int nlocal, EAMParams P, const double *__restrict__ tab1, double *__restrict__ fx, double *__restrict__ fy,
                double *__restrict__ fz, double *__restrict__ partials)
@@ -296,40 +310,51 @@ k_eam_force_1t(const double4 *__restrict__ posfp, const int *__restrict__ numnei
     const int n = numneigh[i];
     const int *nb = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
     double fxi = 0.0, fyi = 0.0, fzi = 0.0;
-#pragma unroll 2
-    for (int k = 0; k < n; k++) {
-      const unsigned ent = (unsigned) __ldcs(nb + (size_t) k * TILE);
-      const double4 pj = ld_pos256(posfp + (ent & CLJMASK));
-      const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-      const double rsq = dx * dx + dy * dy + dz * dz;
-      if (rsq < P.cutforcesq) {
-        const double recip = rsqrt(rsq);
-        const double r = rsq * recip;
-        double p = r * P.rdr + 1.0;
-        int m = (int) p;
-        m = min(m, P.nr - 1);
-        p -= m;
-        p = fmin(p, 1.0);
-        const double rhoip = (s_t[m] * p + s_t[n1 + m]) * p + s_t[2 * n1 + m];
-        const double z3 = s_t[3 * n1 + m], z4 = s_t[4 * n1 + m], z5 = s_t[5 * n1 + m], z6 = s_t[6 * n1 + m];
-        const double z2 = ((z3 * p + z4) * p + z5) * p + z6;
-        const double z2p = ((3.0 * z3 * p + 2.0 * z4) * p + z5) * P.rdr;  // = spline[0..2] of array2spline (:752-754)
-        const double phi = z2 * recip;
-        const double phip = z2p * recip - phi * recip;
-        const double psip = (pi.w + pj.w) * rhoip + phip;  // one type: rhojp == rhoip
-        const double fpair = -psip * recip;
-        fxi += dx * fpair;
-        fyi += dy * fpair;
-        fzi += dz * fpair;
-        if (EVFLAG) {
-          acc[0] += 0.5 * phi;
-          const double hf = 0.5 * fpair;
-          acc[1] += dx * dx * hf;
-          acc[2] += dy * dy * hf;
-          acc[3] += dz * dz * hf;
-          acc[4] += dx * dy * hf;
-          acc[5] += dx * dz * hf;
-          acc[6] += dy * dz * hf;
+    constexpr int PF = 4;
+    const int nlast = max(n - 1, 0);
+    unsigned enx[PF];
+#pragma unroll
+    for (int u = 0; u < PF; u++) enx[u] = (unsigned) __ldcs(nb + (size_t) min(u, nlast) * TILE);
+    for (int k0 = 0; k0 < n; k0 += PF) {
+      double4 pjv[PF];
+#pragma unroll
+      for (int u = 0; u < PF; u++) pjv[u] = ld_pos256(posfp + (enx[u] & CLJMASK));
+#pragma unroll
+      for (int u = 0; u < PF; u++) enx[u] = (unsigned) __ldcs(nb + (size_t) min(k0 + PF + u, nlast) * TILE);
+#pragma unroll
+      for (int u = 0; u < PF; u++) {
+        const double4 pj = pjv[u];
+        const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+        const double rsq = dx * dx + dy * dy + dz * dz;
+        if (rsq < P.cutforcesq && k0 + u < n) {
+          const double recip = rsqrt(rsq);
+          const double r = rsq * recip;
+          double p = r * P.rdr + 1.0;
+          int m = (int) p;
+          m = min(m, P.nr - 1);
+          p -= m;
+          p = fmin(p, 1.0);
+          const double rhoip = (s_t[m] * p + s_t[n1 + m]) * p + s_t[2 * n1 + m];
+          const double z3 = s_t[3 * n1 + m], z4 = s_t[4 * n1 + m], z5 = s_t[5 * n1 + m], z6 = s_t[6 * n1 + m];
+          const double z2 = ((z3 * p + z4) * p + z5) * p + z6;
+          const double z2p = ((3.0 * z3 * p + 2.0 * z4) * p + z5) * P.rdr;  // = spline[0..2] of array2spline (:752-754)
+          const double phi = z2 * recip;
+          const double phip = z2p * recip - phi * recip;
+          const double psip = (pi.w + pj.w) * rhoip + phip;  // one type: rhojp == rhoip
+          const double fpair = -psip * recip;
+          fxi += dx * fpair;
+          fyi += dy * fpair;
+          fzi += dz * fpair;
+          if (EVFLAG) {
+            acc[0] += 0.5 * phi;
+            const double hf = 0.5 * fpair;
+            acc[1] += dx * dx * hf;
+            acc[2] += dy * dy * hf;
+            acc[3] += dz * dz * hf;
+            acc[4] += dx * dy * hf;
+            acc[5] += dx * dz * hf;
+            acc[6] += dy * dz * hf;
+          }
         }
       }
     }
@@ -412,7 +437,7 @@ int pair_eam_rho(b200md_ctx *c, int ev)
   const EAMTables &T = c->eam;
   const EAMParams P = eam_params(c);
   if (eam_use_1t(c)) {
-    const int threads = 256, blocks = cdiv(n, threads);
+    const int threads = EAM1T_THREADS, blocks = cdiv(n, threads);
     const size_t n1 = (size_t) T.nr + 1, smemA = 4 * n1 * 8;
     TRY(dev_ensure(c, c->posfp, (size_t) n + c->nghost));
     if (ev) TRY(dev_ensure(c, c->partials, (size_t) blocks * 8));
@@ -451,7 +476,7 @@ int pair_eam_force(b200md_ctx *c, int ev, bool ghost_from_fp)
   const EAMTables &T = c->eam;
   const EAMParams P = eam_params(c);
   if (eam_use_1t(c)) {
-    const int threads = 256, blocks = cdiv(n, threads);
+    const int threads = EAM1T_THREADS, blocks = cdiv(n, threads);
     const size_t n1 = (size_t) T.nr + 1, smemC = 7 * n1 * 8;
     if (ev) TRY(dev_ensure(c, c->partials, (size_t) blocks * 8));
     if (ghost_from_fp && c->nghost > 0) {

@@ -3,6 +3,8 @@
 // force of atom i is written once (this also replaces Verlet::force_clear, src/verlet.cpp:376-421).
 // Energy / virial (EVFLAG) follow Pair::ev_tally_full (src/pair.cpp:1115-1160): half of each pair term
 // per visit, reduced per block and then in a fixed order (reproducible run to run).
+#include <stdlib.h>
+
 #include "ctx.cuh"
 
 struct LJOne { double cutsq, lj1, lj2, lj3, lj4, offset; };
@@ -129,6 +131,108 @@ k_lj_cluster(const double4 *__restrict__ pos, const int *__restrict__ numneigh, 
   if (EVFLAG) block_partials<7>(acc, partials);
 }
 
+// Lane-cluster form: CL consecutive LANES (= CL consecutive, spatially compact atoms) share one list, so a warp
+// step gathers 32/CL distinct x_j -- the CL lanes of a cluster read the same sector, which the L1 data pipe serves
+// as one wavefront.  ncu on the per-atom kernel: LSU data pipe at 88 % of peak with 26 wavefronts per warp step
+// (one per lane: 32 distinct sectors), FP64 pipe at 36 %: trading 1/efficiency more masked-out FP64 work for
+// 1/CL of the gather wavefronts moves the kernel towards the FP64 pipe.
+template <int CL, int EVFLAG, int ONETYPE>
+__global__ void __launch_bounds__(128)
+k_lj_lanes(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
+           int nlocal, LJOne one, const double *__restrict__ tables, int ntypes, double *__restrict__ fx,
+           double *__restrict__ fy, double *__restrict__ fz, double *__restrict__ partials)
+{
+  extern __shared__ double s_tab[];
+  const int nt1 = ntypes + 1, nt2 = nt1 * nt1;
+  if (!ONETYPE) {
+    for (int k = threadIdx.x; k < 6 * nt2; k += blockDim.x) s_tab[k] = tables[k];
+    __syncthreads();
+  }
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  if (i < nlocal) {
+    const int q = i / CL, a = i % CL;
+    const double4 pi = pos[i];
+    const int trow = ONETYPE ? 0 : pos_type(pi) * nt1;
+    const int n = numneigh[q];
+    const int *nb = neigh + (size_t) (q >> 5) * TILE * maxneigh + (q & 31);
+    double fxi = 0.0, fyi = 0.0, fzi = 0.0;
+    // software pipeline, depth PF: the list entries of the NEXT batch are in flight while the PF gathers of this
+    // batch are issued back to back and then consumed (the per-step chain index -> gather -> FP64 otherwise
+    // serialises two DRAM/L2 latencies per neighbor)
+    constexpr int PF = 4;
+    const int nlast = max(n - 1, 0);
+    unsigned enx[PF];
+#pragma unroll
+    for (int u = 0; u < PF; u++) enx[u] = (unsigned) __ldcs(nb + (size_t) min(u, nlast) * TILE);
+    for (int k0 = 0; k0 < n; k0 += PF) {
+      unsigned ent[PF];
+      double4 pj[PF];
+#pragma unroll
+      for (int u = 0; u < PF; u++) {
+        ent[u] = enx[u];
+        pj[u] = ld_pos256(pos + (ent[u] & CLJMASK));
+      }
+#pragma unroll
+      for (int u = 0; u < PF; u++) enx[u] = (unsigned) __ldcs(nb + (size_t) min(k0 + PF + u, nlast) * TILE);
+#pragma unroll
+      for (int u = 0; u < PF; u++) {
+        const double dx = pi.x - pj[u].x, dy = pi.y - pj[u].y, dz = pi.z - pj[u].z;
+        const double rsq = dx * dx + dy * dy + dz * dz;
+        double cutsq, lj1, lj2;
+        if (ONETYPE) {
+          cutsq = one.cutsq; lj1 = one.lj1; lj2 = one.lj2;
+        } else {
+          const int t = trow + pos_type(pj[u]);
+          cutsq = s_tab[t]; lj1 = s_tab[nt2 + t]; lj2 = s_tab[2 * nt2 + t];
+        }
+        const bool in = rsq < cutsq && ((ent[u] >> (CLBITS + a)) & 1u) && (k0 + u < n);
+        const double r2inv = rcp_pos(rsq);
+        const double r6inv = r2inv * r2inv * r2inv;
+        const double forcelj = r6inv * (lj1 * r6inv - lj2);
+        const double fpair = in ? forcelj * r2inv : 0.0;
+        fxi += dx * fpair;
+        fyi += dy * fpair;
+        fzi += dz * fpair;
+        if (EVFLAG) {
+          double lj3, lj4, off;
+          if (ONETYPE) {
+            lj3 = one.lj3; lj4 = one.lj4; off = one.offset;
+          } else {
+            const int t = trow + pos_type(pj[u]);
+            lj3 = s_tab[3 * nt2 + t]; lj4 = s_tab[4 * nt2 + t]; off = s_tab[5 * nt2 + t];
+          }
+          acc[0] += in ? 0.5 * (r6inv * (lj3 * r6inv - lj4) - off) : 0.0;
+          const double hf = 0.5 * fpair;
+          acc[1] += dx * dx * hf;
+          acc[2] += dy * dy * hf;
+          acc[3] += dz * dz * hf;
+          acc[4] += dx * dy * hf;
+          acc[5] += dx * dz * hf;
+          acc[6] += dy * dz * hf;
+        }
+      }
+    }
+    fx[i] = fxi;
+    fy[i] = fyi;
+    fz[i] = fzi;
+  }
+  if (EVFLAG) block_partials<7>(acc, partials);
+}
+
+template <int CL> static void launch_lj_lanes(b200md_ctx *c, int blocks, int threads, size_t smem, int ev, int onetype, const LJOne &one, int n)
+{
+#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p
+  if (ev) {
+    if (onetype) k_lj_lanes<CL, 1, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+    else k_lj_lanes<CL, 1, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+  } else {
+    if (onetype) k_lj_lanes<CL, 0, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+    else k_lj_lanes<CL, 0, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+  }
+#undef LJ_ARGS
+}
+
 // fixed-order reduction of per-block partials (ncomp <= 8 components) into red[dst + c]
 __global__ void k_reduce_partials(const double *__restrict__ partials, int nblocks, int ncomp, double *__restrict__ red, int dst)
 {
@@ -170,7 +274,8 @@ template <int CL> static void launch_lj(b200md_ctx *c, int blocks, int threads, 
 int pair_lj_compute(b200md_ctx *c, int eflag, int vflag)
 {
   const int n = c->nlocal;
-  const int nclus = cdiv(n, c->cl);
+  const bool lanes = c->cl == 1 ? getenv("B200MD_LJ_PLAIN") == nullptr : getenv("B200MD_LANES") != nullptr;
+  const int nclus = lanes ? n : cdiv(n, c->cl);
   const int threads = 128, blocks = cdiv(nclus, threads);
   const int ev = (eflag || vflag) ? 1 : 0;
   if (ev) TRY(dev_ensure(c, c->partials, (size_t) blocks * 8));
@@ -179,7 +284,10 @@ int pair_lj_compute(b200md_ctx *c, int eflag, int vflag)
   size_t smem = onetype ? 0 : (size_t) 6 * (c->lj.ntypes + 1) * (c->lj.ntypes + 1) * sizeof(double);
   {
     KProf kp(c, KC_PAIR);
-    if (c->cl == 1) launch_lj<1>(c, blocks, threads, smem, ev, onetype, one, n);
+    if (lanes && c->cl == 1) launch_lj_lanes<1>(c, blocks, threads, smem, ev, onetype, one, n);
+    else if (lanes && c->cl == 2) launch_lj_lanes<2>(c, blocks, threads, smem, ev, onetype, one, n);
+    else if (lanes) launch_lj_lanes<4>(c, blocks, threads, smem, ev, onetype, one, n);
+    else if (c->cl == 1) launch_lj<1>(c, blocks, threads, smem, ev, onetype, one, n);
     else if (c->cl == 2) launch_lj<2>(c, blocks, threads, smem, ev, onetype, one, n);
     else launch_lj<4>(c, blocks, threads, smem, ev, onetype, one, n);
     LAUNCH_CHECK();
