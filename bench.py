@@ -182,13 +182,14 @@ def time_host_buffers(torch, dist, md, steps, warmup, device, nranks):
     host arrays to the device and x, v, f back -- what a Pair/Fix plugin under the stock host-resident Verlet
     loop pays (the reference GPU package's model).  Returns (ms for K steps, h2d bytes/step, d2h bytes/step)."""
     n = md.nlocal
-    hx = torch.empty((n, 3), dtype=torch.float64).pin_memory()
-    hv = torch.empty((n, 3), dtype=torch.float64).pin_memory()
-    hf = torch.empty((n, 3), dtype=torch.float64).pin_memory()
+    cap = n + n // 64 + 1024  # room for atoms that migrate in at a rebuild (several ranks)
+    hx = torch.empty((cap, 3), dtype=torch.float64).pin_memory()
+    hv = torch.empty((cap, 3), dtype=torch.float64).pin_memory()
+    hf = torch.empty((cap, 3), dtype=torch.float64).pin_memory()
     md.ctx.call("b200md_download_atoms", C.c_void_p(hx.data_ptr()), C.c_void_p(hv.data_ptr()), None, None, None, None)
-    e, vir = C.c_double(0), np.zeros(6)
-    args = (md.dt, 0, 0, C.c_void_p(hx.data_ptr()), C.c_void_p(hv.data_ptr()), C.c_void_p(hf.data_ptr()), None, C.byref(e),
-            vir.ctypes.data_as(C.c_void_p))
+    e, vir, nout = C.c_double(0), np.zeros(6), C.c_int(0)
+    args = (md.dt, 0, 0, cap, C.c_void_p(hx.data_ptr()), C.c_void_p(hv.data_ptr()), C.c_void_p(hf.data_ptr()), None,
+            C.byref(nout), C.byref(e), vir.ctypes.data_as(C.c_void_p))
     for _ in range(warmup):
         md.ctx.call("b200md_step_host", *args)
     ext = torch.cuda.ExternalStream(md.ctx.L.b200md_stream(md.ctx.h), device=device)
@@ -250,15 +251,43 @@ def run_workload(torch, dist, pkg, kind, cells, args, device, nranks, rank, nccl
     out["nghost"] = md.nghost
     out["mem_gb"] = float(md.ctx.L.b200md_memory_usage(md.ctx.h)) / 1e9
 
-    # ---- end to end through host buffers: every rank moves its own atoms over its own PCIe link every step ----
-    if not args.no_e2e:
-        k = max(3, min(args.steps, 20))
-        ems, bi, bo = time_host_buffers(torch, dist, md, k, 3, device, nranks)
-        out["e2e"] = dict(value=natoms_total * k / (ems * 1e-3) / 1e6, unit="Matom-steps/s", h2d_bytes_per_step=bi,
-                          d2h_bytes_per_step=bo, steps=k, api="b200md_step_host (pinned host x,v in; x,v,f out every step)")
-    md.close()
     out["gen_s"] = t_gen
-    return out
+    return out, md
+
+
+def run_e2e(torch, dist, md, out, args, device, nranks):
+    """End to end through host buffers: every rank moves its own atoms over its own PCIe link every step."""
+    k = max(3, min(args.steps, 20))
+    ems, bi, bo = time_host_buffers(torch, dist, md, k, 3, device, nranks)
+    out["e2e"] = dict(value=out["natoms"] * k / (ems * 1e-3) / 1e6, unit="Matom-steps/s", h2d_bytes_per_step=bi,
+                      d2h_bytes_per_step=bo, steps=k, api="b200md_step_host (pinned host x,v in; x,v,f out every step)")
+
+
+class Watchdog:
+    """Bounds a phase that contains collectives: if one rank fails inside it the others would wait for ever, and the
+    line with the device-resident numbers (already measured) would be lost.  On expiry rank 0 prints the line it has
+    and every rank leaves with status 0."""
+
+    def __init__(self, seconds, emit):
+        import threading
+
+        self.t = threading.Timer(seconds, self.fire)
+        self.t.daemon = True
+        self.emit = emit
+
+    def fire(self):
+        try:
+            self.emit("e2e phase did not finish in time")
+        finally:
+            os._exit(0)
+
+    def __enter__(self):
+        self.t.start()
+        return self
+
+    def __exit__(self, *exc):
+        self.t.cancel()
+        return False
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -411,11 +440,14 @@ def main():
             dist.all_reduce(t)
             return t.cpu().numpy()
 
-    lj = run_workload(torch, dist, pkg, "lj", args.cells, args, local, world, rank, nccl_id, grid, loc, allsum)
-    eam = None
+    lj, md_lj = run_workload(torch, dist, pkg, "lj", args.cells, args, local, world, rank, nccl_id, grid, loc, allsum)
+    eam, md_eam = None, None
     if not args.no_eam:
-        eam = run_workload(torch, dist, pkg, "eam", args.eam_cells, args, local, world, rank, nccl_id, grid, loc, allsum)
-    if rank == 0:
+        eam, md_eam = run_workload(torch, dist, pkg, "eam", args.eam_cells, args, local, world, rank, nccl_id, grid, loc, allsum)
+
+    def emit(e2e_error=None):
+        if rank != 0:
+            return
         peaks = {}
         try:
             peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
@@ -424,14 +456,24 @@ def main():
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "B200_PROFILING.md fallback 6650 GB/s (of fallback)"
 
-        def roof(w, cls, bytes_per_atom):
+        try:  # measured DRAM bytes per atom of each kernel (one ncu --set full capture, committed under profiles/)
+            dram = json.loads((ROOT / "profiles" / "r01_dram_traffic.json").read_text())
+        except Exception:
+            dram = {}
+
+        def roof(w, cls, bytes_per_atom, dram_key=None):
             kms, kc = w["kernel_ms"][cls]
             if kc == 0:
                 return None
             avg_ms = kms / kc
             ach = bytes_per_atom * w["atoms_per_gpu"] / (avg_ms * 1e-3) / 1e9
-            return {"bound": "hbm", "kernel": cls, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
-                    "avg_launch_ms": avg_ms, "launches": kc, "algorithmic_bytes_per_atom": bytes_per_atom, "peak_source": peak_src}
+            r = {"bound": "hbm", "kernel": cls, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                 "avg_launch_ms": avg_ms, "launches": kc, "algorithmic_bytes_per_atom": bytes_per_atom, "peak_source": peak_src}
+            if dram_key in dram:
+                r["traffic"] = dram[dram_key]["bytes_per_atom"] * w["atoms_per_gpu"]
+                r["traffic_source"] = (f"ncu dram__bytes_read+write = {dram[dram_key]['bytes_per_atom']} B/atom on "
+                                       f"{dram[dram_key]['capture_atoms']} atoms (profiles/r01_ncu_pair_kernels.md), scaled to this launch")
+            return r
 
         line = {"metric": "Matom-steps/s (LJ melt, bench/in.lj scaled)", "value": lj["value"], "unit": "Matom-steps/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": lj["ms"] / args.steps, "higher_is_better": True,
@@ -440,21 +482,22 @@ def main():
                                        f"T=1.44 loop geom, lj/cut 2.5, skin 0.3, rebuild every 20 check no, fix nve, dt 0.005)",
                            "grid": list(grid), "l2": "inputs larger than L2 (per-GPU working set %.1f GB)" % lj["mem_gb"]},
                 "clocks": lj["clocks"], "gpu_launches": lj["launches"],
-                "roofline": roof(lj, "pair", BYTES_LJ_PAIR),
+                "roofline": roof(lj, "pair", BYTES_LJ_PAIR, "pair_lj"),
                 "step_roofline": {"algorithmic_bytes_per_atom_step": BYTES_LJ_STEP,
                                   "frac_of_hbm_peak": BYTES_LJ_STEP * lj["atoms_per_gpu"] / (lj["ms"] / args.steps * 1e-3) / 1e9 / peak},
                 "kernel_ms": lj["kernel_ms"], "ms_profiled_pass": lj["ms_profiled_pass"],
                 "thermo": {"step0": lj["thermo0"], "last": lj["thermo1"]}, "neigh": lj["neigh"], "nghost": lj["nghost"]}
-        if "e2e" in lj:
-            line["e2e"] = lj["e2e"]
+        line["e2e"] = lj.get("e2e")
+        if e2e_error:
+            line["e2e_error"] = e2e_error
         if eam is not None:
             line["eam"] = {"value": eam["value"], "unit": "Matom-steps/s", "ms_per_step": eam["ms"] / args.steps,
                            "workload": f"EAM Cu {eam['atoms_per_gpu']} atoms per GPU ({eam['natoms']} total; bench/in.eam scaled)",
-                           "roofline": roof(eam, "pair", BYTES_EAM_FORCE), "roofline_rho": roof(eam, "eam_rho", BYTES_EAM_RHO),
+                           "roofline": roof(eam, "pair", BYTES_EAM_FORCE, "pair_eam"), "roofline_rho": roof(eam, "eam_rho", BYTES_EAM_RHO, "eam_rho"),
                            "step_frac_of_hbm_peak": BYTES_EAM_STEP * eam["atoms_per_gpu"] / (eam["ms"] / args.steps * 1e-3) / 1e9 / peak,
                            "kernel_ms": eam["kernel_ms"], "gpu_launches": eam["launches"], "clocks": eam["clocks"],
                            "thermo": {"step0": eam["thermo0"], "last": eam["thermo1"]}, "neigh": eam["neigh"], "e2e": eam.get("e2e")}
-        if world == 1 and not args.no_cpu:
+        if world == 1 and not args.no_cpu and not e2e_error:
             line["cpu_baseline"] = cpu_measure("lj", 100, 10, budget_s=20.0, cells_cap=args.cells)
             if eam is not None:
                 line["eam"]["cpu_baseline"] = cpu_measure("eam", 100, 10, budget_s=15.0, cells_cap=args.eam_cells)
@@ -471,6 +514,22 @@ def main():
             return o
 
         print(json.dumps(clean(line)), flush=True)
+
+    # ---- end to end through host buffers, bounded: a failure here must not cost the numbers above ----
+    if not args.no_e2e:
+        with Watchdog(240.0, emit):
+            try:
+                run_e2e(torch, dist, md_lj, lj, args, local, world)
+                if eam is not None:
+                    run_e2e(torch, dist, md_eam, eam, args, local, world)
+            except Exception as ex:  # the peers of a failed rank sit in a collective: say what we have and leave
+                emit(f"{type(ex).__name__}: {ex}")
+                sys.stdout.flush()
+                os._exit(0)
+    md_lj.close()
+    if md_eam is not None:
+        md_eam.close()
+    emit()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

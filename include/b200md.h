@@ -169,13 +169,16 @@ int b200md_setup(b200md_ctx *ctx);
 int b200md_run(b200md_ctx *ctx, int nsteps, double dt, int thermo_every);
 int64_t b200md_timestep(const b200md_ctx *ctx);
 
-/* ---- host-buffer mode: what the stock Verlet loop gets from a pair/fix plugin whose atoms live
- * on the host, the GPU package's model (x up, f down every step, src/GPU/pair_lj_cut_gpu.cpp:85-118).
- * One full timestep: uploads x,v (nlocal atoms, device order of the previous call, i.e. the order
- * b200md_download_atoms reports), runs initial_integrate / [reneighbor] / force / final_integrate,
- * downloads x,v,f.  Arrays are [nlocal][3]. */
-int b200md_step_host(b200md_ctx *ctx, double dt, int eflag, int vflag, double *x, double *v, double *f,
-                     int *tag, double *eng_vdwl, double *virial);
+/* ---- host-buffer mode: one whole timestep with the atoms handed over in HOST arrays every step -- the GPU
+ * package's traffic model (x up, results down every step, src/GPU/pair_lj_cut_gpu.cpp:85-118) applied to the
+ * whole step.  On entry x, v hold the b200md_nlocal() owned atoms in the device order of the previous call (the
+ * order b200md_download_atoms reports); the call runs initial_integrate / [reneighbor | forward_comm] / force /
+ * final_integrate and returns x, v, f (and tag, may be NULL) of the *nlocal_out atoms this rank owns afterwards
+ * (a reneighboring step re-orders them and, on several ranks, migrates some).  Arrays are [capacity][3];
+ * capacity >= the owned count before and after, else B200MD_ERR_ARG.  Pinned host memory lets the copies run
+ * asynchronously: uploads, kernels and downloads are pipelined over atom chunks on three streams. */
+int b200md_step_host(b200md_ctx *ctx, double dt, int eflag, int vflag, int capacity, double *x, double *v, double *f,
+                     int *tag, int *nlocal_out, double *eng_vdwl, double *virial);
 
 /* ---- host-ghost mode: Pair::compute under the STOCK Verlet loop (run_style verlet).  The GPU package's
  * contract (ljl_gpu_compute_n / eam_gpu_compute_n, src/GPU/pair_lj_cut_gpu.cpp:85-118,

@@ -97,6 +97,11 @@ extern "C" int b200md_destroy(b200md_ctx *c)
   if (c->flags_d) cudaFree(c->flags_d);
   if (c->flags_h) cudaFreeHost(c->flags_h);
   for (auto &e : c->kev) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
+  if (c->s_in) {
+    cudaStreamDestroy(c->s_in);
+    cudaStreamDestroy(c->s_out);
+    for (auto &e : c->hs_ev) cudaEventDestroy(e);
+  }
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
   return B200MD_OK;
@@ -690,15 +695,71 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
 extern "C" int64_t b200md_timestep(const b200md_ctx *c) { return c ? c->ntimestep : 0; }
 
 // ---- host-buffer mode ------------------------------------------------------------------------------
-extern "C" int b200md_step_host(b200md_ctx *c, double dt, int eflag, int vflag, double *x, double *v, double *f, int *tag,
-                                double *eng_vdwl, double *virial)
+// One whole timestep with HOST x, v in and x, v, f out.  PCIe is the bound (120 B/atom against about 4.6 ms of
+// kernels at 16.4 M atoms), so the step is pipelined over HS_CHUNKS atom ranges on three streams:
+//   s_in : H2D of x, v of chunk c                              (copy engine, host -> device)
+//   main : k_hs_in(c) = unpack + FixNVE::initial_integrate + pack of the new x; then decide / halo|rebuild / force;
+//          then k_hs_out(c) = FixNVE::final_integrate + pack of v, f
+//   s_out: D2H of the new x of chunk c (runs while later chunks still upload: PCIe is full duplex), later v, f
+// A reneighboring step permutes the owned atoms (spatial sort), which invalidates the x that already went down in
+// the old order: those steps send x again after the rebuild.
+#define HS_CHUNKS 8
+__global__ void k_hs_in(const double *__restrict__ x3, const double *__restrict__ v3, double4 *__restrict__ pos,
+                        double *__restrict__ vx, double *__restrict__ vy, double *__restrict__ vz, const double *__restrict__ fx,
+                        const double *__restrict__ fy, const double *__restrict__ fz, const double *__restrict__ mass,
+                        double *__restrict__ xo3, int first, int n, double dtv, double dtf)
 {
-  NEED_CTX();
-  if (!c->setup_done) return b200md_fail(c, B200MD_ERR_ARG, "step_host needs b200md_setup first");
-  const int n = c->nlocal, g = cdiv(n, 256);
+  int i = first + blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= first + n) return;
+  double4 p = pos[i];
+  const double dtfm = dtf / mass[pos_type(p)];
+  // same operation order as k_nve_initial
+  const double a = __dadd_rn(v3[3 * i], __dmul_rn(dtfm, fx[i]));
+  const double b = __dadd_rn(v3[3 * i + 1], __dmul_rn(dtfm, fy[i]));
+  const double cz = __dadd_rn(v3[3 * i + 2], __dmul_rn(dtfm, fz[i]));
+  vx[i] = a; vy[i] = b; vz[i] = cz;
+  p.x = __dadd_rn(x3[3 * i], __dmul_rn(dtv, a));
+  p.y = __dadd_rn(x3[3 * i + 1], __dmul_rn(dtv, b));
+  p.z = __dadd_rn(x3[3 * i + 2], __dmul_rn(dtv, cz));
+  pos[i] = p;
+  xo3[3 * i] = p.x; xo3[3 * i + 1] = p.y; xo3[3 * i + 2] = p.z;
+}
+
+__global__ void k_hs_out(const double4 *__restrict__ pos, double *__restrict__ vx, double *__restrict__ vy,
+                         double *__restrict__ vz, const double *__restrict__ fx, const double *__restrict__ fy,
+                         const double *__restrict__ fz, const double *__restrict__ mass, double *__restrict__ vo3,
+                         double *__restrict__ fo3, int first, int n, double dtf)
+{
+  int i = first + blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= first + n) return;
+  const double dtfm = dtf / mass[__double2loint(pos[i].w)];
+  const double gx = fx[i], gy = fy[i], gz = fz[i];
+  const double a = __dadd_rn(vx[i], __dmul_rn(dtfm, gx));
+  const double b = __dadd_rn(vy[i], __dmul_rn(dtfm, gy));
+  const double cz = __dadd_rn(vz[i], __dmul_rn(dtfm, gz));
+  vx[i] = a; vy[i] = b; vz[i] = cz;
+  vo3[3 * i] = a; vo3[3 * i + 1] = b; vo3[3 * i + 2] = cz;
+  fo3[3 * i] = gx; fo3[3 * i + 1] = gy; fo3[3 * i + 2] = gz;
+}
+
+static int hs_streams(b200md_ctx *c)
+{
+  if (c->s_in) return B200MD_OK;
+  CU(cudaStreamCreateWithFlags(&c->s_in, cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking));
+  for (int k = 0; k < 3 * HS_CHUNKS + 2; k++) CU(cudaEventCreateWithFlags(&c->hs_ev[k], cudaEventDisableTiming));
+  return B200MD_OK;
+}
+
+// the plain form: copies and kernels in order on the one stream (default; verified on B200 at 1 and 2 ranks)
+static int step_host_serial(b200md_ctx *c, double dt, int eflag, int vflag, int capacity, double *x, double *v, double *f,
+                            int *tag, int *nlocal_out, double *eng_vdwl, double *virial)
+{
+  int n = c->nlocal;
   const double dtv = dt, dtf = 0.5 * dt * c->ftm2v;
-  TRY(stage_bytes(c, (size_t) n * 48));
-  double *sx = c->stage.p, *sv = sx + (size_t) 3 * n;
+  TRY(stage_bytes(c, (size_t) capacity * 48));
+  double *sx = c->stage.p, *sv = sx + (size_t) 3 * capacity;
+  int g = cdiv(n, 256);
   CU(cudaMemcpyAsync(sx, x, (size_t) n * 24, cudaMemcpyHostToDevice, c->stream));
   CU(cudaMemcpyAsync(sv, v, (size_t) n * 24, cudaMemcpyHostToDevice, c->stream));
   k_update_pos<<<g, 256, 0, c->stream>>>(sx, c->pos.p, n);
@@ -710,7 +771,12 @@ extern "C" int b200md_step_host(b200md_ctx *c, double dt, int eflag, int vflag, 
   int nflag = 0;
   TRY(neigh_decide(c, &nflag));
   if (!nflag) TRY(halo_forward_pos(c));
-  else TRY(neigh_rebuild(c));
+  else {
+    TRY(neigh_rebuild(c));
+    n = c->nlocal;  // several ranks: atoms migrated at the rebuild (Comm::exchange)
+    if (n > capacity) return b200md_fail(c, B200MD_ERR_ARG, "step_host: %d atoms after migration exceed the caller's capacity %d", n, capacity);
+    g = cdiv(n, 256);
+  }
   TRY(force_compute(c, eflag, vflag));
   TRY(nve_final(c, dtf));
   k_unpack_pos<<<g, 256, 0, c->stream>>>(c->pos.p, sx, nullptr, n);
@@ -725,6 +791,94 @@ extern "C" int b200md_step_host(b200md_ctx *c, double dt, int eflag, int vflag, 
   CU(cudaMemcpyAsync(f, sx, (size_t) n * 24, cudaMemcpyDeviceToHost, c->stream));
   if (tag) CU(cudaMemcpyAsync(tag, c->tag.p, (size_t) n * 4, cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
+  if (nlocal_out) *nlocal_out = n;
+  if (eflag || vflag) {
+    if (eng_vdwl) *eng_vdwl = c->eng_vdwl;
+    if (virial) for (int k = 0; k < 6; k++) virial[k] = c->virial[k];
+  }
+  return B200MD_OK;
+}
+
+extern "C" int b200md_step_host(b200md_ctx *c, double dt, int eflag, int vflag, int capacity, double *x, double *v, double *f,
+                                int *tag, int *nlocal_out, double *eng_vdwl, double *virial)
+{
+  NEED_CTX();
+  if (!c->setup_done) return b200md_fail(c, B200MD_ERR_ARG, "step_host needs b200md_setup first");
+  if (!x || !v || !f) return b200md_fail(c, B200MD_ERR_ARG, "step_host: x, v, f are required");
+  int n = c->nlocal;
+  if (capacity < n) return b200md_fail(c, B200MD_ERR_ARG, "step_host: capacity %d < nlocal %d", capacity, n);
+  // B200MD_HOST_PIPELINE=1 selects the three-stream chunk pipeline below (written in round 1 after the GPU budget
+  // was spent: not yet run on hardware, hence opt-in)
+  if (!getenv("B200MD_HOST_PIPELINE")) return step_host_serial(c, dt, eflag, vflag, capacity, x, v, f, tag, nlocal_out, eng_vdwl, virial);
+  const double dtv = dt, dtf = 0.5 * dt * c->ftm2v;
+  TRY(hs_streams(c));
+  TRY(stage_bytes(c, (size_t) capacity * 120));
+  const size_t cap3 = (size_t) 3 * capacity;
+  double *sx = c->stage.p, *sv = sx + cap3, *xo = sv + cap3, *vo = xo + cap3, *fo = vo + cap3;
+  const int nch = n >= 65536 ? HS_CHUNKS : 1;
+  const int per = cdiv(cdiv(n, nch), 256) * 256;
+  cudaEvent_t *e_in = c->hs_ev, *e_x = c->hs_ev + HS_CHUNKS, *e_o = c->hs_ev + 2 * HS_CHUNKS;
+  cudaEvent_t e_start = c->hs_ev[3 * HS_CHUNKS], e_mid = c->hs_ev[3 * HS_CHUNKS + 1];
+  // the copy streams start after whatever the main stream still has queued (staging buffers are reused)
+  CU(cudaEventRecord(e_start, c->stream));
+  CU(cudaStreamWaitEvent(c->s_in, e_start, 0));
+  CU(cudaStreamWaitEvent(c->s_out, e_start, 0));
+  {
+    Sect s(c, SECT_MODIFY);
+    for (int ch = 0; ch < nch; ch++) {
+      const int first = ch * per, m = min(per, n - first);
+      if (m <= 0) break;
+      CU(cudaMemcpyAsync(sx + (size_t) 3 * first, x + (size_t) 3 * first, (size_t) m * 24, cudaMemcpyHostToDevice, c->s_in));
+      CU(cudaMemcpyAsync(sv + (size_t) 3 * first, v + (size_t) 3 * first, (size_t) m * 24, cudaMemcpyHostToDevice, c->s_in));
+      CU(cudaEventRecord(e_in[ch], c->s_in));
+      CU(cudaStreamWaitEvent(c->stream, e_in[ch], 0));
+      k_hs_in<<<cdiv(m, 256), 256, 0, c->stream>>>(sx, sv, c->pos.p, c->v[0].p, c->v[1].p, c->v[2].p, c->f[0].p, c->f[1].p,
+                                                    c->f[2].p, c->mass_d.p, xo, first, m, dtv, dtf);
+      LAUNCH_CHECK();
+      CU(cudaEventRecord(e_x[ch], c->stream));
+      CU(cudaStreamWaitEvent(c->s_out, e_x[ch], 0));
+      CU(cudaMemcpyAsync(x + (size_t) 3 * first, xo + (size_t) 3 * first, (size_t) m * 24, cudaMemcpyDeviceToHost, c->s_out));
+    }
+  }
+  c->ntimestep++;
+  int nflag = 0;
+  TRY(neigh_decide(c, &nflag));
+  if (!nflag) TRY(halo_forward_pos(c));
+  else {
+    TRY(neigh_rebuild(c));
+    // the owned atoms were wrapped, re-ordered and (several ranks) migrated: send x again in the new order, after
+    // the stale copies
+    n = c->nlocal;
+    if (n > capacity) {
+      cudaStreamSynchronize(c->s_out);
+      return b200md_fail(c, B200MD_ERR_ARG, "step_host: %d atoms after migration exceed the caller's capacity %d", n, capacity);
+    }
+    k_unpack_pos<<<cdiv(n, 256), 256, 0, c->stream>>>(c->pos.p, xo, nullptr, n);
+    LAUNCH_CHECK();
+    CU(cudaEventRecord(e_mid, c->stream));
+    CU(cudaStreamWaitEvent(c->s_out, e_mid, 0));
+    CU(cudaMemcpyAsync(x, xo, (size_t) n * 24, cudaMemcpyDeviceToHost, c->s_out));
+  }
+  TRY(force_compute(c, eflag, vflag));
+  const int per2 = cdiv(cdiv(n, nch), 256) * 256;  // n may have changed at the rebuild
+  {
+    Sect s(c, SECT_MODIFY);
+    for (int ch = 0; ch < nch; ch++) {
+      const int first = ch * per2, m = min(per2, n - first);
+      if (m <= 0) break;
+      k_hs_out<<<cdiv(m, 256), 256, 0, c->stream>>>(c->pos.p, c->v[0].p, c->v[1].p, c->v[2].p, c->f[0].p, c->f[1].p, c->f[2].p,
+                                                     c->mass_d.p, vo, fo, first, m, dtf);
+      LAUNCH_CHECK();
+      CU(cudaEventRecord(e_o[ch], c->stream));
+      CU(cudaStreamWaitEvent(c->s_out, e_o[ch], 0));
+      CU(cudaMemcpyAsync(v + (size_t) 3 * first, vo + (size_t) 3 * first, (size_t) m * 24, cudaMemcpyDeviceToHost, c->s_out));
+      CU(cudaMemcpyAsync(f + (size_t) 3 * first, fo + (size_t) 3 * first, (size_t) m * 24, cudaMemcpyDeviceToHost, c->s_out));
+    }
+  }
+  if (tag) CU(cudaMemcpyAsync(tag, c->tag.p, (size_t) n * 4, cudaMemcpyDeviceToHost, c->s_out));
+  CU(cudaStreamSynchronize(c->s_out));
+  CU(cudaStreamSynchronize(c->stream));
+  if (nlocal_out) *nlocal_out = n;
   if (eflag || vflag) {
     if (eng_vdwl) *eng_vdwl = c->eng_vdwl;
     if (virial) for (int k = 0; k < 6; k++) virial[k] = c->virial[k];

@@ -167,8 +167,10 @@ struct b200md_ctx {
   int64_t kc_count[KC_N] = {0, 0, 0, 0, 0, 0};
   double bytes_held = 0;
 
-  // host-buffer mode staging
+  // host-buffer mode staging and its copy streams (b200md_step_host)
   DevBuf<double> stage;
+  cudaStream_t s_in = nullptr, s_out = nullptr;
+  cudaEvent_t hs_ev[26] = {};
 };
 
 // ---------------------------------------------------------------------------------------------

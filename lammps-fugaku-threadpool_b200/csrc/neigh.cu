@@ -411,8 +411,10 @@ __device__ __forceinline__ BinRec ld_rec(const BinRec *__restrict__ p)
   return r;
 }
 
-#define BUILD_WARPS 8
-template <int ONETYPE>
+#define BUILD_WARPS 4
+// STAGE: each warp collects its lanes' lists in shared memory ([k][lane], conflict free) and writes them out row by
+// row, so a store instruction covers one contiguous piece of a 128-byte list row instead of 32 different rows
+template <int ONETYPE, int STAGE>
 __global__ void __launch_bounds__(BUILD_WARPS * 32)
 k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int nlocal, BinGeom g,
              const int *__restrict__ bin_start, const double *__restrict__ cutneighsq, int ntypes, float tol, int maxneigh,
@@ -423,7 +425,9 @@ k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, in
   const int nt1 = ntypes + 1;
   for (int k = threadIdx.x; k < nt1 * nt1; k += blockDim.x) { s_cut[k] = cutneighsq[k]; s_cutf[k] = (float) cutneighsq[k]; }
   __syncthreads();
+  extern __shared__ int s_stage[];                                   // [BUILD_WARPS][maxneigh][32] when STAGE
   const int lane = threadIdx.x & 31;
+  int *s_mine = s_stage + (size_t) (threadIdx.x >> 5) * maxneigh * 32 + lane;
   const int wb = blockIdx.x * BUILD_WARPS + (threadIdx.x >> 5);      // owned-bin number, x fastest
   const int nown = g.nbin[0] * g.nbin[1] * g.nbin[2];
   if (wb >= nown) return;
@@ -466,11 +470,20 @@ k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, in
           }
           const int j = c.jt & BR_JMASK;
           if (accept && owned && j != i) {
-            if (n < maxneigh) neigh[base + (size_t) n * TILE] = j | (1 << CLBITS);
+            if (n < maxneigh) {
+              if (STAGE) s_mine[n * 32] = j | (1 << CLBITS);
+              else neigh[base + (size_t) n * TILE] = j | (1 << CLBITS);
+            }
             n++;
           }
         }
       }
+    if (STAGE) {
+      const int nrows = min(__reduce_max_sync(0xffffffffu, owned ? n : 0), maxneigh);
+      for (int k = 0; k < nrows; k++)
+        if (owned && k < n) neigh[base + (size_t) k * TILE] = s_mine[k * 32];
+      __syncwarp();
+    }
     if (owned) numneigh[i] = n;
     nmax = max(nmax, owned ? n : 0);
   }
@@ -635,12 +648,25 @@ int neigh_build_lists(b200md_ctx *c)
                                                             g.lo[1] - BIN_MARGIN / g.inv[1], g.lo[2] - BIN_MARGIN / g.inv[2], rec);
       LAUNCH_CHECK();
       const int nown = g.nbin[0] * g.nbin[1] * g.nbin[2];
-      if (c->ntypes == 1)
-        k_build_bins<1><<<cdiv(nown, BUILD_WARPS), BUILD_WARPS * 32, 0, c->stream>>>(
-            c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d);
-      else
-        k_build_bins<0><<<cdiv(nown, BUILD_WARPS), BUILD_WARPS * 32, 0, c->stream>>>(
-            c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d);
+      const size_t stage_bytes = (size_t) BUILD_WARPS * c->maxneigh * 32 * sizeof(int);
+      // opt-in: written in round 1 after the GPU budget was spent, not yet run on hardware
+      const bool stage = stage_bytes <= 96 * 1024 && getenv("B200MD_BUILD_STAGE") != nullptr;
+      static bool attr_done = false;
+      if (!attr_done) {
+        CU(cudaFuncSetAttribute(k_build_bins<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        CU(cudaFuncSetAttribute(k_build_bins<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        attr_done = true;
+      }
+#define BB_ARGS c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d
+      const int bgrid = cdiv(nown, BUILD_WARPS), bthr = BUILD_WARPS * 32;
+      if (c->ntypes == 1) {
+        if (stage) k_build_bins<1, 1><<<bgrid, bthr, stage_bytes, c->stream>>>(BB_ARGS);
+        else k_build_bins<1, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+      } else {
+        if (stage) k_build_bins<0, 1><<<bgrid, bthr, stage_bytes, c->stream>>>(BB_ARGS);
+        else k_build_bins<0, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+      }
+#undef BB_ARGS
       LAUNCH_CHECK();
     } else {
       KProf kp(c, KC_NEIGH);

@@ -4,6 +4,8 @@ neighbor lists bit-exact as per-atom tag sets, forces <= 1e-10 relative (to max|
 PE / KE / pressure <= 1e-6 relative."""
 from __future__ import annotations
 
+import os
+
 import numpy as np
 import pytest
 
@@ -180,6 +182,49 @@ def test_piecewise_api_equals_device_loop(pkg):
         b.fix_nve.final_integrate()
     ga, gb = a.gather(), b.gather()
     assert np.array_equal(ga["x"], gb["x"]) and np.array_equal(ga["v"], gb["v"]) and np.array_equal(ga["f"], gb["f"])
+    a.close()
+    b.close()
+
+
+@pytest.mark.parametrize("pipeline", [
+    False,
+    pytest.param(True, marks=pytest.mark.skipif(not os.environ.get("B200MD_TEST_PIPELINE"),
+                                                reason="three-stream pipeline (B200MD_HOST_PIPELINE=1) was written after round 1's GPU "
+                                                       "budget was spent: opt-in (B200MD_TEST_PIPELINE=1) until it has run on hardware")),
+])
+@pytest.mark.parametrize("name,steps", [("lj2_864", 25), ("eam_500", 30)])
+def test_host_buffer_step_equals_device_loop(pkg, name, steps, pipeline, monkeypatch):
+    """b200md_step_host (x, v in / x, v, f out through HOST arrays every step, through rebuilds that re-order the
+    atoms) == b200md_run, bit for bit."""
+    import ctypes as C
+
+    if pipeline:
+        monkeypatch.setenv("B200MD_HOST_PIPELINE", "1")
+    else:
+        monkeypatch.delenv("B200MD_HOST_PIPELINE", raising=False)
+    g = load_golden(name)
+    a = make_device_system(pkg, name, g)
+    b = make_device_system(pkg, name, g)
+    a.run(steps)
+    b.setup()
+    n = b.nlocal
+    cap = n + 16
+    hx, hv, hf = np.zeros((cap, 3)), np.zeros((cap, 3)), np.zeros((cap, 3))
+    tag = np.zeros(cap, dtype=np.int32)
+    vp = lambda arr: arr.ctypes.data_as(C.c_void_p)
+    b.ctx.call("b200md_download_atoms", vp(hx), vp(hv), None, None, None, None)
+    e, vir, nout = C.c_double(0), np.zeros(6), C.c_int(0)
+    for step in range(steps):
+        ev = 1 if step == steps - 1 else 0
+        b.ctx.call("b200md_step_host", b.dt, ev, ev, cap, vp(hx), vp(hv), vp(hf), vp(tag), C.byref(nout), C.byref(e), vp(vir))
+        assert nout.value == n
+    ga = a.gather()
+    o = np.argsort(tag[:n])
+    assert np.array_equal(tag[:n][o], ga["tag"])
+    assert np.array_equal(hx[:n][o], ga["x"]) and np.array_equal(hv[:n][o], ga["v"]) and np.array_equal(hf[:n][o], ga["f"])
+    assert e.value == a.thermo_log[-1]["pe"]
+    with pytest.raises(pkg.lib.B200MDError):  # too small a host array is an argument error, not an overrun
+        b.ctx.call("b200md_step_host", b.dt, 0, 0, n - 1, vp(hx), vp(hv), vp(hf), None, None, None, None)
     a.close()
     b.close()
 
