@@ -237,6 +237,7 @@ extern "C" int b200md_upload_atoms(b200md_ctx *c, int n, const double *x, const 
   CU(cudaStreamSynchronize(c->stream));
   c->nlocal = n;
   c->nghost = 0;
+  c->host_ghosts = false;  // the device makes the ghosts from here on (b200md_host_atoms switches back)
   c->list_valid = false;
   c->setup_done = false;
   c->have_ev = false;

@@ -27,18 +27,30 @@ bool read_numbers(FILE *fp, std::vector<double> &dst, int n)
 }
 
 // line 1 comment, line 2 "Z mass ...", line 3 "nrho drho nr dr cut", then frho[nrho], zr[nr], rhor[nr]
-int read_funcfl(const char *name, FuncflFile &f, std::string &why)
+// `system_real`: the run uses `units real`.  A file whose first line carries "UNITS: metal" is then converted
+// like PairEAM::read_file does through PotentialFileReader (pair_eam.cpp:466-505, utils.cpp:1488-1506:
+// energy x 23.060549 for frho, x sqrt(23.060549) for zr); a "UNITS: real" file under metal gets the inverse.
+int read_funcfl(const char *name, FuncflFile &f, std::string &why, bool system_real)
 {
   FILE *fp = fopen(name, "r");
   if (!fp) { why = std::string("Cannot open EAM potential file ") + name; return 1; }
-  char line[2048];
+  char line[2048], first[2048] = {0};
   int iz = 0, nrho = 0, nr = 0;
-  bool ok = fgets(line, sizeof line, fp) && fgets(line, sizeof line, fp) && sscanf(line, "%d %lg", &iz, &f.mass) == 2 &&
+  bool ok = fgets(first, sizeof first, fp) && fgets(line, sizeof line, fp) && sscanf(line, "%d %lg", &iz, &f.mass) == 2 &&
             fgets(line, sizeof line, fp) && sscanf(line, "%d %lg %d %lg %lg", &nrho, &f.drho, &nr, &f.dr, &f.cut) == 5 &&
             nrho > 4 && nr > 4 && f.drho > 0 && f.dr > 0 && read_numbers(fp, f.frho, nrho) && read_numbers(fp, f.zr, nr) &&
             read_numbers(fp, f.rhor, nr);
   fclose(fp);
   if (!ok) { why = std::string("Invalid EAM potential file ") + name; return 1; }
+  double conv = 1.0;
+  const std::string head(first);
+  if (head.find("UNITS: metal") != std::string::npos && system_real) conv = 23.060549;
+  else if (head.find("UNITS: real") != std::string::npos && !system_real) conv = 1.0 / 23.060549;
+  if (conv != 1.0) {
+    const double sq = sqrt(conv);
+    for (auto &v : f.frho) v *= conv;
+    for (auto &v : f.zr) v *= sq;
+  }
   return 0;
 }
 
@@ -93,8 +105,10 @@ extern "C" int b200md_eam_init_funcfl(b200md_ctx *c, int ntypes, int nfiles, con
   if (ntypes < 1 || ntypes > B200MD_MAXTYPES || nfiles < 1) return b200md_fail(c, B200MD_ERR_ARG, "eam: bad ntypes/nfiles");
   std::vector<FuncflFile> F(nfiles);
   std::string why;
+  // `units real` is recognised by its Boltzmann constant (b200md_set_units carries the constants, src/update.cpp:166-185)
+  const bool system_real = fabs(c->boltz - 0.0019872067) < 1e-12;
   for (int k = 0; k < nfiles; k++)
-    if (read_funcfl(files[k], F[k], why)) return b200md_fail(c, B200MD_ERR_ARG, "%s", why.c_str());
+    if (read_funcfl(files[k], F[k], why, system_real)) return b200md_fail(c, B200MD_ERR_ARG, "%s", why.c_str());
   for (int i = 1; i <= ntypes; i++)
     if (map[i] < -1 || map[i] >= nfiles) return b200md_fail(c, B200MD_ERR_ARG, "eam: bad map[%d]", i);
 

@@ -273,10 +273,20 @@ int neigh_setup_bins(b200md_ctx *c)
     int nb = (int) (len / target);
     if (nb < 1) nb = 1;
     while (nb > 1 && len / nb < c->cutneighmax * (1.0 + 1e-10)) nb--;
+    double inv = nb / len;
+    if (c->host_ghosts && len / nb < c->cutneighmax * (1.0 + 1e-10)) {
+      // host-ghost mode accepts boxes thinner than the cutoff (the caller made several layers of periodic
+      // images): bins stay >= cutneighmax wide, so the 27-bin stencil still covers the cutoff sphere, and simply
+      // overhang the sub-domain
+      const double bs = c->cutneighmax * (1.0 + 1e-10);
+      nb = (int) ceil(len / bs);
+      if (nb < 1) nb = 1;
+      inv = 1.0 / bs;
+    }
     g.nbin[k] = nb;
     g.mbin[k] = nb + 2 * BIN_MARGIN;
     g.lo[k] = c->sublo[k];
-    g.inv[k] = nb / len;
+    g.inv[k] = inv;
     mb *= g.mbin[k];
   }
   if (mb > 2000000000LL) return b200md_fail(c, B200MD_ERR_ARG, "too many bins");

@@ -362,6 +362,13 @@ int orc_eam_read_funcfl(orc_sys *s, const char *filename)
   s->funcfl = (struct funcfl *) realloc(s->funcfl, sizeof(struct funcfl) * (s->nfuncfl + 1));
   struct funcfl *file = &s->funcfl[s->nfuncfl];
   if (!fgets(line, sizeof line, fp)) { fclose(fp); return -2; }
+  /* PotentialFileReader unit conversion (src/MANYBODY/pair_eam.cpp:466-505, src/utils.cpp:1488-1506) */
+  double conv = 1.0;
+  {
+    int sys_real = fabs(s->boltz - 0.0019872067) < 1e-12, sys_metal = fabs(s->boltz - 8.617343e-5) < 1e-15;
+    if (strstr(line, "UNITS: metal") && sys_real) conv = 23.060549;
+    else if (strstr(line, "UNITS: real") && sys_metal) conv = 1.0 / 23.060549;
+  }
   int iz;
   if (!fgets(line, sizeof line, fp) || sscanf(line, "%d %lg", &iz, &file->mass) != 2) { fclose(fp); return -2; }
   if (!fgets(line, sizeof line, fp) ||
@@ -373,6 +380,11 @@ int orc_eam_read_funcfl(orc_sys *s, const char *filename)
   for (int i = 1; i <= file->nr; i++) if (fscanf(fp, "%lg", &file->zr[i]) != 1) { fclose(fp); return -3; }
   for (int i = 1; i <= file->nr; i++) if (fscanf(fp, "%lg", &file->rhor[i]) != 1) { fclose(fp); return -3; }
   fclose(fp);
+  if (conv != 1.0) {
+    double sq = sqrt(conv);
+    for (int i = 1; i <= file->nrho; i++) file->frho[i] *= conv;
+    for (int i = 1; i <= file->nr; i++) file->zr[i] *= sq;
+  }
   return s->nfuncfl++;
 }
 

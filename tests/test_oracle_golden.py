@@ -6,7 +6,7 @@ from __future__ import annotations
 import numpy as np
 import pytest
 
-from conftest import CASES, POT, load_golden, make_oracle_system, thermo_vec
+from conftest import CASES, GOLDEN, POT, load_golden, make_oracle_system, thermo_vec
 
 NAMES = list(CASES)
 
@@ -87,3 +87,31 @@ def test_oracle_eam_tables_match_funcfl_header(oracle):
     assert abs(t["cutmax"] - 4.95) < 1e-12
     assert abs(1.0 / t["rdr"] - 0.01) < 1e-12
     assert abs(s.mass(1) - 63.55) < 1e-12
+
+
+@pytest.mark.parametrize("name,units", [("unittest_atomic_pair_eam", "metal"), ("unittest_atomic_pair_eam_real", "real")])
+def test_oracle_reference_unittest_eam_yaml(oracle, name, units):
+    """The reference's OWN known-answer test for pair eam (unittest/force-styles/tests/atomic-pair-eam.yaml and
+    atomic-pair-eam_real.yaml, minted by tests/golden/make_unittest_golden.py): 32 atoms, two funcfl elements
+    (Al, Cu), a 7 A periodic box thinner than the ghost cutoff (several image layers), newton on;
+    init_* = `run 0`, run_* = 4 nve steps of 1e-4 with neigh_modify delay 2 every 2 check no.  The yaml's own
+    tolerance is epsilon = 6e-12 / 5e-12 (x5 for run_forces); the restatement is held to it."""
+    g = load_golden(name)
+    eps = float(g["epsilon"])
+    s = oracle.OracleSystem(2, units)
+    s.set_dt(0.0001)
+    s.set_box(g["boxlo"], g["boxhi"])
+    s.set_neighbor(2.0, every=2, delay=2, check=0)
+    s.pair_eam({1: str(GOLDEN / "Al_jnp.eam"), 2: str(GOLDEN / "Cu_u3_units.eam")})
+    s.set_atoms(g["x"], g["v"], g["type"], g["tag"])
+    s.setup()
+    for phase in ("init", "run"):
+        if phase == "run":
+            s.run(4)
+        a, t = s.atoms(), s.thermo()
+        o = np.argsort(a["tag"])
+        f_ref = g[f"{phase}_forces"]
+        scale = np.abs(f_ref).max()
+        assert np.abs(a["f"][o] - f_ref).max() <= 5 * eps * scale, phase
+        assert abs(t["pe"] - float(g[f"{phase}_vdwl"])) <= eps * abs(float(g[f"{phase}_vdwl"])), phase
+        assert np.abs(t["virial"] - g[f"{phase}_stress"]).max() <= eps * np.abs(g[f"{phase}_stress"]).max(), phase
