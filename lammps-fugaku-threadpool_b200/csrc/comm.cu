@@ -361,12 +361,13 @@ static int sendrecv_dirs(b200md_ctx *c, const char *sbuf, const int *soff, const
                          const int *rcount, size_t bytes)
 {
   if (c->nranks == 1) return B200MD_OK;
+  cudaStream_t st = c->hstream ? c->hstream : c->stream;  // overlap mode redirects the per-step halo to s_comm
   NC(g_nccl.GroupStart());
   for (int d = 0; d < NDIR; d++) {
     if (c->peer_send[d] >= 0 && c->peer_send[d] != c->rank && scount[d] > 0)
-      NC(g_nccl.Send(sbuf + (size_t) soff[d] * bytes, (size_t) scount[d] * bytes, ncclChar, c->peer_send[d], (ncclComm_t) c->nccl, c->stream));
+      NC(g_nccl.Send(sbuf + (size_t) soff[d] * bytes, (size_t) scount[d] * bytes, ncclChar, c->peer_send[d], (ncclComm_t) c->nccl, st));
     if (c->peer_recv[d] >= 0 && c->peer_recv[d] != c->rank && rcount[d] > 0)
-      NC(g_nccl.Recv(rbuf + (size_t) roff[d] * bytes, (size_t) rcount[d] * bytes, ncclChar, c->peer_recv[d], (ncclComm_t) c->nccl, c->stream));
+      NC(g_nccl.Recv(rbuf + (size_t) roff[d] * bytes, (size_t) rcount[d] * bytes, ncclChar, c->peer_recv[d], (ncclComm_t) c->nccl, st));
   }
   NC(g_nccl.GroupEnd());
   return B200MD_OK;
@@ -477,7 +478,7 @@ int halo_forward_vec4(b200md_ctx *c, double4 *arr)
 {
   if (c->nsend > 0) {
     KProf kp(c, KC_HALO);
-    k_halo_pack_pos<0><<<cdiv(c->nsend, 256), 256, 0, c->stream>>>(arr, c->tag.p, c->send_idx.p, c->send_dir.p, c->nsend,
+    k_halo_pack_pos<0><<<cdiv(c->nsend, 256), 256, 0, c->hstream ? c->hstream : c->stream>>>(arr, c->tag.p, c->send_idx.p, c->send_dir.p, c->nsend,
                                                                     c->nlocal, c->hp, c->sendbuf4.p, c->sendbuf_i.p);
     LAUNCH_CHECK();
   }

@@ -129,9 +129,16 @@ struct b200md_ctx {
   int cl = 1;                 // cluster size of the neighbor list (1, 2 or 4 atoms per list), env B200MD_CLUSTER
   int maxneigh = 0;
   DevBuf<int> numneigh, neigh;
+  DevBuf<int> tile_ghost;     // [ntiles]: != 0 if any atom of the 32-atom tile has a ghost in its list (overlap mode)
+  bool tiles_valid = false;
   int maxneigh_seen = 0;
 
   // halo / exchange (comm.cu)
+  // opt-in (B200MD_OVERLAP=1): the per-step halo runs on s_comm while the main stream computes the tiles whose lists
+  // hold no ghost; hstream != nullptr redirects the halo kernels and NCCL calls to that stream
+  int overlap = 0;
+  cudaStream_t s_comm = nullptr, hstream = nullptr;
+  cudaEvent_t ev_main = nullptr, ev_halo = nullptr;
   HaloPlan hp;
   void *nccl = nullptr;       // ncclComm_t when nranks > 1
   int peer_send[NDIR], peer_recv[NDIR];
@@ -273,6 +280,10 @@ int halo_forward_pos(b200md_ctx *c);
 int halo_forward_vec4(b200md_ctx *c, double4 *arr);
 int halo_forward_scalar(b200md_ctx *c, double *a);
 int pair_lj_compute(b200md_ctx *c, int eflag, int vflag);
+int pair_lj_compute_part(b200md_ctx *c, int part);            // overlap mode: part 0 = ghost-free tiles, 1 = the rest
+int pair_eam_rho_part(b200md_ctx *c, int part);
+int pair_eam_force_part(b200md_ctx *c, int part);
+bool pair_eam_can_split(const b200md_ctx *c);
 int pair_eam_compute(b200md_ctx *c, int eflag, int vflag);
 int pair_eam_rho(b200md_ctx *c, int ev);
 int pair_eam_force(b200md_ctx *c, int ev, bool ghost_from_fp);

@@ -428,7 +428,7 @@ template <int ONETYPE, int STAGE>
 __global__ void __launch_bounds__(BUILD_WARPS * 32)
 k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int nlocal, BinGeom g,
              const int *__restrict__ bin_start, const double *__restrict__ cutneighsq, int ntypes, float tol, int maxneigh,
-             int *__restrict__ numneigh, int *__restrict__ neigh, int *__restrict__ flags)
+             int *__restrict__ numneigh, int *__restrict__ neigh, int *__restrict__ flags, int *__restrict__ tile_ghost)
 {
   __shared__ double s_cut[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
   __shared__ float s_cutf[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
@@ -460,6 +460,7 @@ k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, in
     const int trow = ONETYPE ? 0 : (((unsigned) me.jt >> 28) + 1) * nt1;
     const size_t base = (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
     int n = 0;
+    bool ghost_seen = false;  // overlap mode: does this atom's list hold a ghost?
     for (int dz = -1; dz <= 1; dz++)
       for (int dy = -1; dy <= 1; dy++) {
         const int cell = ((bz + dz) * g.mbin[1] + (by + dy)) * g.mbin[0] + bx - 1;
@@ -480,6 +481,7 @@ k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, in
           }
           const int j = c.jt & BR_JMASK;
           if (accept && owned && j != i) {
+            ghost_seen |= j >= nlocal;
             if (n < maxneigh) {
               if (STAGE) s_mine[n * 32] = j | (1 << CLBITS);
               else neigh[base + (size_t) n * TILE] = j | (1 << CLBITS);
@@ -495,6 +497,7 @@ k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, in
       __syncwarp();
     }
     if (owned) numneigh[i] = n;
+    if (tile_ghost && owned && ghost_seen) atomicOr(&tile_ghost[i >> 5], 1);
     nmax = max(nmax, owned ? n : 0);
   }
   nmax = __reduce_max_sync(0xffffffffu, nmax);
@@ -667,7 +670,14 @@ int neigh_build_lists(b200md_ctx *c)
         CU(cudaFuncSetAttribute(k_build_bins<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
         attr_done = true;
       }
-#define BB_ARGS c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d
+      int *tile_ghost = nullptr;
+      if (c->overlap) {  // B200MD_OVERLAP=1: tile flags for the interior / boundary split of the force kernels
+        TRY(dev_ensure(c, c->tile_ghost, (size_t) ntiles));
+        CU(cudaMemsetAsync(c->tile_ghost.p, 0, (size_t) ntiles * sizeof(int), c->stream));
+        tile_ghost = c->tile_ghost.p;
+      }
+      c->tiles_valid = tile_ghost != nullptr;
+#define BB_ARGS c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d, tile_ghost
       const int bgrid = cdiv(nown, BUILD_WARPS), bthr = BUILD_WARPS * 32;
       if (c->ntypes == 1) {
         if (stage) k_build_bins<1, 1><<<bgrid, bthr, stage_bytes, c->stream>>>(BB_ARGS);
@@ -679,6 +689,7 @@ int neigh_build_lists(b200md_ctx *c)
 #undef BB_ARGS
       LAUNCH_CHECK();
     } else {
+      c->tiles_valid = false;
       KProf kp(c, KC_NEIGH);
 #define BUILD_ARGS c->pos.p, n, c->bg, c->bin_start.p, c->cell_list.p, c->cutneighsq_d.p, c->ntypes, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d
       if (CLs == 1) k_build_cluster<1><<<cdiv(nclus, 128), 128, smem, c->stream>>>(BUILD_ARGS);

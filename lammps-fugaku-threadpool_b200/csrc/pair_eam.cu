@@ -231,11 +231,12 @@ k_eam_force(const double4 *__restrict__ pos, const int *__restrict__ numneigh, c
 // one table copy per 512-thread block: fewer, larger blocks leave more of the 228 KB for L1 (ncu, 256-thread blocks:
 // L1 hit rate 17 % in the rho pass with 8 table copies per SM)
 #define EAM1T_THREADS 512
-template <int EFLAG>
+template <int EFLAG, int SPLIT>
 __global__ void __launch_bounds__(EAM1T_THREADS, 2)
 k_eam_rho_fp_1t(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
                 int nlocal, EAMParams P, const double *__restrict__ tab1, double *__restrict__ rho_out,
-                double *__restrict__ fp_out, double4 *__restrict__ posfp, double *__restrict__ partials)
+                double *__restrict__ fp_out, double4 *__restrict__ posfp, double *__restrict__ partials,
+                const int *__restrict__ tile_ghost, int part)
 {
   extern __shared__ double s_t[];  // [4][n1]: rhor c3..c6
   const int n1 = P.nr + 1;
@@ -243,7 +244,9 @@ k_eam_rho_fp_1t(const double4 *__restrict__ pos, const int *__restrict__ numneig
   __syncthreads();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   double acc[1] = {0.0};
-  if (i < nlocal) {
+  bool active = i < nlocal;
+  if (SPLIT && active) active = (tile_ghost[i >> 5] != 0) == (part != 0);  // overlap mode, see k_lj_lanes
+  if (active) {
     const double4 pi = pos[i];
     const int n = numneigh[i];
     const int *nb = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
@@ -293,11 +296,11 @@ k_eam_rho_fp_1t(const double4 *__restrict__ pos, const int *__restrict__ numneig
   if (EFLAG) block_partials_e<1>(acc, partials);
 }
 
-template <int EVFLAG>
+template <int EVFLAG, int SPLIT>
 __global__ void __launch_bounds__(EAM1T_THREADS, 2)
 k_eam_force_1t(const double4 *__restrict__ posfp, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
                int nlocal, EAMParams P, const double *__restrict__ tab1, double *__restrict__ fx, double *__restrict__ fy,
-               double *__restrict__ fz, double *__restrict__ partials)
+               double *__restrict__ fz, double *__restrict__ partials, const int *__restrict__ tile_ghost, int part)
 {
   extern __shared__ double s_t[];  // [7][n1]: rhor c0..c2 (derivative), z2r c3..c6 (value; derivative derived)
   const int n1 = P.nr + 1;
@@ -305,7 +308,9 @@ k_eam_force_1t(const double4 *__restrict__ posfp, const int *__restrict__ numnei
   __syncthreads();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-  if (i < nlocal) {
+  bool active = i < nlocal;
+  if (SPLIT && active) active = (tile_ghost[i >> 5] != 0) == (part != 0);
+  if (active) {
     const double4 pi = posfp[i];
     const int n = numneigh[i];
     const int *nb = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
@@ -410,10 +415,12 @@ static int eam_attrs_1t(b200md_ctx *c)
 {
   static bool attr_done = false;
   if (!attr_done) {
-    CU(cudaFuncSetAttribute(k_eam_force_1t<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    CU(cudaFuncSetAttribute(k_eam_force_1t<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    CU(cudaFuncSetAttribute(k_eam_rho_fp_1t<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    CU(cudaFuncSetAttribute(k_eam_rho_fp_1t<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CU(cudaFuncSetAttribute(k_eam_force_1t<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CU(cudaFuncSetAttribute(k_eam_force_1t<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CU(cudaFuncSetAttribute(k_eam_rho_fp_1t<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CU(cudaFuncSetAttribute(k_eam_rho_fp_1t<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CU(cudaFuncSetAttribute(k_eam_rho_fp_1t<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CU(cudaFuncSetAttribute(k_eam_force_1t<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     attr_done = true;
   }
   return B200MD_OK;
@@ -444,9 +451,9 @@ int pair_eam_rho(b200md_ctx *c, int ev)
     TRY(eam_attrs_1t(c));
     {
       KProf kp(c, KC_EAM_RHO);
-#define A1 c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->rho.p, c->fp.p, c->posfp.p, c->partials.p
-      if (ev) k_eam_rho_fp_1t<1><<<blocks, threads, smemA, c->stream>>>(A1);
-      else k_eam_rho_fp_1t<0><<<blocks, threads, smemA, c->stream>>>(A1);
+#define A1 c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->rho.p, c->fp.p, c->posfp.p, c->partials.p, nullptr, -1
+      if (ev) k_eam_rho_fp_1t<1, 0><<<blocks, threads, smemA, c->stream>>>(A1);
+      else k_eam_rho_fp_1t<0, 0><<<blocks, threads, smemA, c->stream>>>(A1);
 #undef A1
       LAUNCH_CHECK();
     }
@@ -485,9 +492,9 @@ int pair_eam_force(b200md_ctx *c, int ev, bool ghost_from_fp)
     }
     {
       KProf kp(c, KC_PAIR);
-#define C1 c->posfp.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p
-      if (ev) k_eam_force_1t<1><<<blocks, threads, smemC, c->stream>>>(C1);
-      else k_eam_force_1t<0><<<blocks, threads, smemC, c->stream>>>(C1);
+#define C1 c->posfp.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, -1
+      if (ev) k_eam_force_1t<1, 0><<<blocks, threads, smemC, c->stream>>>(C1);
+      else k_eam_force_1t<0, 0><<<blocks, threads, smemC, c->stream>>>(C1);
 #undef C1
       LAUNCH_CHECK();
     }
@@ -517,4 +524,38 @@ int pair_eam_compute(b200md_ctx *c, int eflag, int vflag)
   if (eam_use_1t(c)) TRY(halo_forward_vec4(c, c->posfp.p));
   else TRY(halo_forward_scalar(c, c->fp.p));
   return pair_eam_force(c, ev, false);
+}
+
+// ---- overlap mode (capi.cu): the single-type passes restricted to the tiles whose ghost flag equals `part` ----
+bool pair_eam_can_split(const b200md_ctx *c) { return eam_use_1t(c); }
+
+int pair_eam_rho_part(b200md_ctx *c, int part)
+{
+  const int n = c->nlocal;
+  const EAMTables &T = c->eam;
+  const EAMParams P = eam_params(c);
+  const int threads = EAM1T_THREADS, blocks = cdiv(n, threads);
+  const size_t n1 = (size_t) T.nr + 1, smemA = 4 * n1 * 8;
+  TRY(dev_ensure(c, c->posfp, (size_t) n + c->nghost));
+  TRY(eam_attrs_1t(c));
+  KProf kp(c, KC_EAM_RHO);
+  k_eam_rho_fp_1t<0, 1><<<blocks, threads, smemA, c->stream>>>(c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->rho.p,
+                                                                c->fp.p, c->posfp.p, c->partials.p, c->tile_ghost.p, part);
+  LAUNCH_CHECK();
+  return B200MD_OK;
+}
+
+int pair_eam_force_part(b200md_ctx *c, int part)
+{
+  const int n = c->nlocal;
+  const EAMTables &T = c->eam;
+  const EAMParams P = eam_params(c);
+  const int threads = EAM1T_THREADS, blocks = cdiv(n, threads);
+  const size_t n1 = (size_t) T.nr + 1, smemC = 7 * n1 * 8;
+  TRY(eam_attrs_1t(c));
+  KProf kp(c, KC_PAIR);
+  k_eam_force_1t<0, 1><<<blocks, threads, smemC, c->stream>>>(c->posfp.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->f[0].p,
+                                                               c->f[1].p, c->f[2].p, c->partials.p, c->tile_ghost.p, part);
+  LAUNCH_CHECK();
+  return B200MD_OK;
 }

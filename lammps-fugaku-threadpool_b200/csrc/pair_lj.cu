@@ -136,11 +136,14 @@ k_lj_cluster(const double4 *__restrict__ pos, const int *__restrict__ numneigh, 
 // as one wavefront.  ncu on the per-atom kernel: LSU data pipe at 88 % of peak with 26 wavefronts per warp step
 // (one per lane: 32 distinct sectors), FP64 pipe at 36 %: trading 1/efficiency more masked-out FP64 work for
 // 1/CL of the gather wavefronts moves the kernel towards the FP64 pipe.
-template <int CL, int EVFLAG, int ONETYPE>
+// SPLIT (overlap mode): only the warps (= 32-atom tiles) whose ghost flag equals `part` work, so the ghost-free
+// tiles can run while the halo is still in flight
+template <int CL, int EVFLAG, int ONETYPE, int SPLIT>
 __global__ void __launch_bounds__(128)
 k_lj_lanes(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
            int nlocal, LJOne one, const double *__restrict__ tables, int ntypes, double *__restrict__ fx,
-           double *__restrict__ fy, double *__restrict__ fz, double *__restrict__ partials)
+           double *__restrict__ fy, double *__restrict__ fz, double *__restrict__ partials,
+           const int *__restrict__ tile_ghost, int part)
 {
   extern __shared__ double s_tab[];
   const int nt1 = ntypes + 1, nt2 = nt1 * nt1;
@@ -150,7 +153,9 @@ k_lj_lanes(const double4 *__restrict__ pos, const int *__restrict__ numneigh, co
   }
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-  if (i < nlocal) {
+  bool active = i < nlocal;
+  if (SPLIT && active) active = (tile_ghost[i >> 5] != 0) == (part != 0);
+  if (active) {
     const int q = i / CL, a = i % CL;
     const double4 pi = pos[i];
     const int trow = ONETYPE ? 0 : pos_type(pi) * nt1;
@@ -222,13 +227,13 @@ k_lj_lanes(const double4 *__restrict__ pos, const int *__restrict__ numneigh, co
 
 template <int CL> static void launch_lj_lanes(b200md_ctx *c, int blocks, int threads, size_t smem, int ev, int onetype, const LJOne &one, int n)
 {
-#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p
+#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, -1
   if (ev) {
-    if (onetype) k_lj_lanes<CL, 1, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
-    else k_lj_lanes<CL, 1, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+    if (onetype) k_lj_lanes<CL, 1, 1, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+    else k_lj_lanes<CL, 1, 0, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
   } else {
-    if (onetype) k_lj_lanes<CL, 0, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
-    else k_lj_lanes<CL, 0, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+    if (onetype) k_lj_lanes<CL, 0, 1, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+    else k_lj_lanes<CL, 0, 0, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
   }
 #undef LJ_ARGS
 }
@@ -293,5 +298,22 @@ int pair_lj_compute(b200md_ctx *c, int eflag, int vflag)
     LAUNCH_CHECK();
   }
   if (ev) TRY(reduce_partials(c, blocks, 7, 0));
+  return B200MD_OK;
+}
+
+// overlap mode (capi.cu): forces of the tiles whose ghost flag equals `part`, no energy/virial tally
+int pair_lj_compute_part(b200md_ctx *c, int part)
+{
+  const int n = c->nlocal;
+  const int threads = 128, blocks = cdiv(n, threads);
+  LJOne one = {c->lj.h_onetype[0], c->lj.h_onetype[1], c->lj.h_onetype[2], c->lj.h_onetype[3], c->lj.h_onetype[4], c->lj.h_onetype[5]};
+  const int onetype = (c->lj.ntypes == 1);
+  size_t smem = onetype ? 0 : (size_t) 6 * (c->lj.ntypes + 1) * (c->lj.ntypes + 1) * sizeof(double);
+  KProf kp(c, KC_PAIR);
+#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, c->tile_ghost.p, part
+  if (onetype) k_lj_lanes<1, 0, 1, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+  else k_lj_lanes<1, 0, 0, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+#undef LJ_ARGS
+  LAUNCH_CHECK();
   return B200MD_OK;
 }
