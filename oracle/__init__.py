@@ -97,6 +97,15 @@ def lib() -> C.CDLL:
         L.orc_get_atoms.argtypes = [vp] + [vp] * 6
         L.orc_get_ghosts.argtypes = [vp, vp, vp]
         L.orc_get_pairs.argtypes = [vp, vp]
+        # in.chain additions
+        L.orc_enable_sort.argtypes = [vp, C.c_int]
+        L.orc_sort_atoms.argtypes = [vp]
+        L.orc_set_bonds.argtypes = [vp, C.c_int, vp, vp, vp]
+        L.orc_bond_fene.argtypes = [vp, C.c_int, vp, vp, vp, vp]
+        L.orc_fix_langevin.argtypes = [vp, C.c_double, C.c_double, C.c_double, C.c_int]
+        L.orc_thermo_bond.argtypes = [vp, vp]
+        L.orc_nbondlist.restype = C.c_int
+        L.orc_nbondlist.argtypes = [vp]
         _lib = L
     return _lib
 
@@ -188,6 +197,57 @@ class OracleSystem:
         special = np.ascontiguousarray(special, dtype=np.int32)
         sl = np.ascontiguousarray(special_lj, dtype=np.float64)
         self.L.orc_set_special(self.h, special.shape[1], _p(nspecial), _p(special), _p(sl))
+
+    # ---- in.chain additions (atom_style bond, special_bonds fene, bond_style fene, fix langevin) ----
+    def enable_sort(self, flag=True):
+        """Atom::sort at setup, as the reference does (fixes the local order fix langevin draws its numbers in)."""
+        self.L.orc_enable_sort(self.h, int(flag))
+
+    def set_bonds(self, bonds):
+        """bonds: (nbonds, 3) int rows `type a1 a2` as in a data file; stored on a1 (newton_bond on).  Also sets the
+        1-2 special partners both ways; with `special_bonds fene` (lj 0 1 1) they are excluded from the pair list."""
+        bonds = np.asarray(bonds, dtype=np.int64)
+        a = self.atoms()
+        n = self.nlocal
+        where = {int(t): i for i, t in enumerate(a["tag"])}
+        per = [[] for _ in range(n)]
+        spec = [[] for _ in range(n)]
+        for t, a1, a2 in bonds:
+            per[where[int(a1)]].append((int(t), int(a2)))
+            spec[where[int(a1)]].append(int(a2))
+            spec[where[int(a2)]].append(int(a1))
+        bpa = max(1, max(len(p) for p in per))
+        num = np.array([len(p) for p in per], dtype=np.int32)
+        btype = np.zeros((n, bpa), dtype=np.int32)
+        batom = np.zeros((n, bpa), dtype=np.int32)
+        for i, p in enumerate(per):
+            for m, (t, a2) in enumerate(p):
+                btype[i, m], batom[i, m] = t, a2
+        self.L.orc_set_bonds(self.h, bpa, _p(num), _p(btype), _p(batom))
+        ms = max(1, max(len(p) for p in spec))
+        nspecial = np.zeros((n, 3), dtype=np.int32)
+        special = np.zeros((n, ms), dtype=np.int32)
+        for i, p in enumerate(spec):
+            nspecial[i, :] = len(p)  # Special::build stops after 1-2 when the 1-3/1-4 weights are 1.0 (src/special.cpp)
+            special[i, :len(p)] = p
+        self.set_special(nspecial, special, [1.0, 0.0, 1.0, 1.0])
+
+    def bond_fene(self, coeffs):
+        """coeffs: {bondtype: (K, R0, epsilon, sigma)} like `bond_coeff`"""
+        nt = max(coeffs)
+        arr = np.zeros((4, nt + 1))
+        for t, c in coeffs.items():
+            arr[:, t] = c
+        k, r0, e, sg = (np.ascontiguousarray(arr[q]) for q in range(4))
+        self.L.orc_bond_fene(self.h, nt, _p(k), _p(r0), _p(e), _p(sg))
+
+    def fix_langevin(self, t_start, t_stop, damp, seed):
+        self.L.orc_fix_langevin(self.h, t_start, t_stop, damp, seed)
+
+    def thermo_bond(self):
+        out = np.zeros(7)
+        self.L.orc_thermo_bond(self.h, _p(out))
+        return dict(e_bond=out[0], virial_bond=out[1:].copy())
 
     def pair_lj_cut(self, epsilon, sigma, cut, offset_flag=False):
         """epsilon/sigma/cut: (ntypes+1)x(ntypes+1) tables (row/col 0 unused), already mixed."""

@@ -88,6 +88,19 @@ typedef struct {
   int *special;               /* [nlocal][maxspecial] partner tags */
   int maxspecial;
   int special_flag[4];        /* src/neighbor.cpp: 0 = exclude, 1 = keep plain, 2 = keep with bits */
+  /* ---- in.chain additions: Atom::sort, bonds, bond_style fene, fix langevin ---- */
+  int sort_enabled;           /* spatial re-ordering of owned atoms at setup (src/atom.cpp:2246-2345) */
+  int bond_per_atom;          /* atom->bond_per_atom */
+  int *num_bond, *bond_type, *bond_atom; /* [nlocal], [nlocal][bond_per_atom] (partner tags), like src/atom.h */
+  int nbondtypes;
+  double *fene_k, *fene_r0, *fene_eps, *fene_sigma; /* [nbondtypes+1] src/MOLECULE/bond_fene.h */
+  int nbondlist, maxbondlist, *bondlist; /* [nbondlist][3]: i1, i2, type (src/ntopo_bond_all.cpp) */
+  int *tag2local, maxtag, *sametag;      /* Atom::map_set (array style) for Domain::closest_image */
+  double eng_bond, virial_bond[6];
+  int langevin;               /* fix langevin (src/fix_langevin.cpp), constant target, per-type mass */
+  double lang_tstart, lang_tstop, lang_period;
+  double mars_u[98], mars_c, mars_cd, mars_cm; int mars_i97, mars_j97; /* RanMars (src/random_mars.cpp) */
+  int64_t beginstep, endstep;
   /* ---- results ---- */
   double eng_vdwl, virial[6];
   int eflag, vflag;
@@ -96,6 +109,9 @@ typedef struct {
 /* ------------------------------------------------------------------------------------ */
 static void *xmalloc(size_t n) { void *p = malloc(n ? n : 1); if (!p) { fprintf(stderr, "oracle: out of memory\n"); abort(); } return p; }
 static void *xcalloc(size_t n, size_t s) { void *p = calloc(n ? n : 1, s); if (!p) { fprintf(stderr, "oracle: out of memory\n"); abort(); } return p; }
+static int build_bondlist(orc_sys *s);
+static int bond_fene_compute(orc_sys *s);
+static void langevin_post_force(orc_sys *s, int64_t ntimestep);
 #define MIN(a,b) ((a) < (b) ? (a) : (b))
 #define MAX(a,b) ((a) > (b) ? (a) : (b))
 
@@ -839,6 +855,7 @@ void orc_neighbor_build(orc_sys *s)
   memcpy(s->xhold, s->x, sizeof(double) * 3 * s->nlocal);
   orc_bin_atoms(s);
   orc_neigh_build(s);
+  if (build_bondlist(s) > 0) { fprintf(stderr, "oracle: Bond atoms missing\n"); abort(); }  /* Neighbor::build_topology */
 }
 
 /* Neighbor::decide / check_distance src/neighbor.cpp:2293-2374 */
@@ -1010,9 +1027,260 @@ void orc_compute_forces(orc_sys *s, int eflag, int vflag)
   s->eflag = eflag; s->vflag = vflag;
   s->eng_vdwl = 0.0;
   for (int k = 0; k < 6; k++) s->virial[k] = 0.0;
+  s->eng_bond = 0.0;
+  for (int k = 0; k < 6; k++) s->virial_bond[k] = 0.0;
   if (s->pair_style == 1) pair_lj_compute(s);
   else if (s->pair_style == 2) pair_eam_compute(s);
+  if (s->nbondtypes && bond_fene_compute(s) < 0) { fprintf(stderr, "oracle: Bad FENE bond\n"); abort(); }  /* src/verlet.cpp:327-332 */
   orc_reverse_comm(s);
+}
+
+/* =====================================================================================
+ * in.chain additions.  Atom::sort (src/atom.cpp:2246-2345, setup_sort_bins :2351-2405):
+ * stable counting sort of owned atoms by sort bin (binsize = 0.5*cutneighmax), x fastest.
+ * The reference does this in Verlet::setup; it fixes the local atom order, which matters
+ * here because fix langevin draws its random numbers in local-index order.
+ * ===================================================================================== */
+void orc_enable_sort(orc_sys *s, int flag) { s->sort_enabled = flag; }
+
+static void permute_int(int *a, const int *perm, int n, int w)
+{
+  int *t = (int *) xmalloc(sizeof(int) * (size_t) n * w);
+  for (int i = 0; i < n; i++) memcpy(t + (size_t) i * w, a + (size_t) perm[i] * w, sizeof(int) * w);
+  memcpy(a, t, sizeof(int) * (size_t) n * w);
+  free(t);
+}
+static void permute_dbl(double *a, const int *perm, int n, int w)
+{
+  double *t = (double *) xmalloc(sizeof(double) * (size_t) n * w);
+  for (int i = 0; i < n; i++) memcpy(t + (size_t) i * w, a + (size_t) perm[i] * w, sizeof(double) * w);
+  memcpy(a, t, sizeof(double) * (size_t) n * w);
+  free(t);
+}
+
+void orc_sort_atoms(orc_sys *s)
+{
+  double binsize = 0.5 * s->cutneighmax;
+  if (binsize <= 0.0) return;
+  double bininv = 1.0 / binsize;
+  int nb[3]; double inv[3];
+  for (int d = 0; d < 3; d++) {
+    nb[d] = (int) ((s->boxhi[d] - s->boxlo[d]) * bininv);
+    if (nb[d] == 0) nb[d] = 1;
+    inv[d] = nb[d] / (s->boxhi[d] - s->boxlo[d]);
+  }
+  int nbins = nb[0] * nb[1] * nb[2];
+  if (nbins == 1) return;
+  int n = s->nlocal;
+  int *binhead = (int *) xmalloc(sizeof(int) * nbins), *next = (int *) xmalloc(sizeof(int) * n);
+  int *perm = (int *) xmalloc(sizeof(int) * n);
+  for (int b = 0; b < nbins; b++) binhead[b] = -1;
+  for (int i = n - 1; i >= 0; i--) {
+    int ix = (int) ((s->x[3 * i] - s->boxlo[0]) * inv[0]);
+    int iy = (int) ((s->x[3 * i + 1] - s->boxlo[1]) * inv[1]);
+    int iz = (int) ((s->x[3 * i + 2] - s->boxlo[2]) * inv[2]);
+    ix = MIN(MAX(ix, 0), nb[0] - 1); iy = MIN(MAX(iy, 0), nb[1] - 1); iz = MIN(MAX(iz, 0), nb[2] - 1);
+    int ibin = iz * nb[1] * nb[0] + iy * nb[0] + ix;
+    next[i] = binhead[ibin];
+    binhead[ibin] = i;
+  }
+  int m = 0;
+  for (int b = 0; b < nbins; b++)
+    for (int i = binhead[b]; i >= 0; i = next[i]) perm[m++] = i;   /* perm[I] = J: new atom I is old atom J */
+  permute_dbl(s->x, perm, n, 3); permute_dbl(s->v, perm, n, 3);
+  permute_int(s->type, perm, n, 1); permute_int(s->tag, perm, n, 1); permute_int(s->image, perm, n, 1);
+  if (s->have_special) { permute_int(s->nspecial, perm, n, 3); permute_int(s->special, perm, n, s->maxspecial); }
+  if (s->bond_per_atom) {
+    permute_int(s->num_bond, perm, n, 1);
+    permute_int(s->bond_type, perm, n, s->bond_per_atom); permute_int(s->bond_atom, perm, n, s->bond_per_atom);
+  }
+  free(binhead); free(next); free(perm);
+}
+
+/* bonds as Atom::data_bonds stores them with newton_bond on (src/atom.cpp: each bond lives on its first atom):
+ * num_bond[i], bond_type[i][m], bond_atom[i][m] = partner TAG */
+void orc_set_bonds(orc_sys *s, int bond_per_atom, const int *num_bond, const int *bond_type, const int *bond_atom)
+{
+  int n = s->nlocal;
+  s->bond_per_atom = bond_per_atom;
+  free(s->num_bond); free(s->bond_type); free(s->bond_atom);
+  s->num_bond = (int *) xmalloc(sizeof(int) * n); memcpy(s->num_bond, num_bond, sizeof(int) * n);
+  s->bond_type = (int *) xmalloc(sizeof(int) * (size_t) n * bond_per_atom);
+  s->bond_atom = (int *) xmalloc(sizeof(int) * (size_t) n * bond_per_atom);
+  memcpy(s->bond_type, bond_type, sizeof(int) * (size_t) n * bond_per_atom);
+  memcpy(s->bond_atom, bond_atom, sizeof(int) * (size_t) n * bond_per_atom);
+}
+
+/* bond_style fene + bond_coeff (src/MOLECULE/bond_fene.cpp:142-165); arrays are 1-based [nbondtypes+1] */
+void orc_bond_fene(orc_sys *s, int nbondtypes, const double *k, const double *r0, const double *eps, const double *sigma)
+{
+  s->nbondtypes = nbondtypes;
+  size_t b = sizeof(double) * (nbondtypes + 1);
+  free(s->fene_k); free(s->fene_r0); free(s->fene_eps); free(s->fene_sigma);
+  s->fene_k = (double *) xmalloc(b); s->fene_r0 = (double *) xmalloc(b); s->fene_eps = (double *) xmalloc(b); s->fene_sigma = (double *) xmalloc(b);
+  memcpy(s->fene_k, k, b); memcpy(s->fene_r0, r0, b); memcpy(s->fene_eps, eps, b); memcpy(s->fene_sigma, sigma, b);
+}
+
+/* Atom::map_set, array style (src/atom_map.cpp:167-199): map[tag] = lowest local index carrying the tag (the
+ * owned atom), sametag[i] = next higher index with the same tag (its ghost images) */
+static void map_set(orc_sys *s)
+{
+  int nall = s->nlocal + s->nghost, maxtag = 0;
+  for (int i = 0; i < nall; i++) maxtag = MAX(maxtag, s->tag[i]);
+  if (maxtag > s->maxtag || !s->tag2local) {
+    s->maxtag = maxtag;
+    s->tag2local = (int *) realloc(s->tag2local, sizeof(int) * ((size_t) maxtag + 1));
+  }
+  for (int t = 0; t <= s->maxtag; t++) s->tag2local[t] = -1;
+  s->sametag = (int *) realloc(s->sametag, sizeof(int) * (size_t) (nall ? nall : 1));
+  for (int i = nall - 1; i >= 0; i--) {
+    s->sametag[i] = s->tag2local[s->tag[i]];
+    s->tag2local[s->tag[i]] = i;
+  }
+}
+
+/* Domain::closest_image (src/domain.cpp:1054-1082) */
+static int closest_image(orc_sys *s, int i, int j)
+{
+  if (j < 0) return j;
+  const double *x = s->x, *xi = &s->x[3 * i];
+  int closest = j;
+  double delx = xi[0] - x[3 * j], dely = xi[1] - x[3 * j + 1], delz = xi[2] - x[3 * j + 2];
+  double rsqmin = delx * delx + dely * dely + delz * delz;
+  while (s->sametag[j] >= 0) {
+    j = s->sametag[j];
+    delx = xi[0] - x[3 * j]; dely = xi[1] - x[3 * j + 1]; delz = xi[2] - x[3 * j + 2];
+    double rsq = delx * delx + dely * dely + delz * delz;
+    if (rsq < rsqmin) { rsqmin = rsq; closest = j; }
+  }
+  return closest;
+}
+
+/* NTopoBondAll::build (src/ntopo_bond_all.cpp:37-76), newton_bond on; returns the number of missing partners */
+static int build_bondlist(orc_sys *s)
+{
+  int nmissing = 0;
+  s->nbondlist = 0;
+  if (!s->bond_per_atom) return 0;
+  map_set(s);
+  for (int i = 0; i < s->nlocal; i++)
+    for (int m = 0; m < s->num_bond[i]; m++) {
+      int t = s->bond_atom[i * s->bond_per_atom + m];
+      int atom1 = (t >= 0 && t <= s->maxtag) ? s->tag2local[t] : -1;
+      if (atom1 == -1) { nmissing++; continue; }
+      atom1 = closest_image(s, i, atom1);
+      if (s->nbondlist == s->maxbondlist) {
+        s->maxbondlist = s->maxbondlist ? 2 * s->maxbondlist : 16384;
+        s->bondlist = (int *) realloc(s->bondlist, sizeof(int) * 3 * (size_t) s->maxbondlist);
+      }
+      int *b = &s->bondlist[3 * s->nbondlist++];
+      b[0] = i; b[1] = atom1; b[2] = s->bond_type[i * s->bond_per_atom + m];
+    }
+  return nmissing;
+}
+
+/* BondFENE::compute (src/MOLECULE/bond_fene.cpp:52-127) with Bond::ev_tally (src/bond.cpp:220-282), newton_bond on.
+ * Returns -1 on "Bad FENE bond". */
+static int bond_fene_compute(orc_sys *s)
+{
+  const double CUBEROOT2 = 1.25992104989487316476; /* MY_CUBEROOT2, src/math_const.h */
+  const double *x = s->x; double *f = s->f;
+  for (int n = 0; n < s->nbondlist; n++) {
+    int i1 = s->bondlist[3 * n], i2 = s->bondlist[3 * n + 1], type = s->bondlist[3 * n + 2];
+    double delx = x[3 * i1] - x[3 * i2], dely = x[3 * i1 + 1] - x[3 * i2 + 1], delz = x[3 * i1 + 2] - x[3 * i2 + 2];
+    double rsq = delx * delx + dely * dely + delz * delz;
+    double r0sq = s->fene_r0[type] * s->fene_r0[type];
+    double rlogarg = 1.0 - rsq / r0sq;
+    if (rlogarg < 0.1) {
+      if (rlogarg <= -3.0) return -1;
+      rlogarg = 0.1;
+    }
+    double fbond = -s->fene_k[type] / rlogarg, sr6 = 0.0, ebond = 0.0;
+    if (rsq < CUBEROOT2 * s->fene_sigma[type] * s->fene_sigma[type]) {
+      double sr2 = s->fene_sigma[type] * s->fene_sigma[type] / rsq;
+      sr6 = sr2 * sr2 * sr2;
+      fbond += 48.0 * s->fene_eps[type] * sr6 * (sr6 - 0.5) / rsq;
+    }
+    if (s->eflag) {
+      ebond = -0.5 * s->fene_k[type] * r0sq * log(rlogarg);
+      if (rsq < CUBEROOT2 * s->fene_sigma[type] * s->fene_sigma[type])
+        ebond += 4.0 * s->fene_eps[type] * sr6 * (sr6 - 1.0) + s->fene_eps[type];
+    }
+    f[3 * i1] += delx * fbond; f[3 * i1 + 1] += dely * fbond; f[3 * i1 + 2] += delz * fbond;
+    f[3 * i2] -= delx * fbond; f[3 * i2 + 1] -= dely * fbond; f[3 * i2 + 2] -= delz * fbond;
+    if (s->eflag) s->eng_bond += ebond;
+    if (s->vflag) {
+      s->virial_bond[0] += delx * delx * fbond; s->virial_bond[1] += dely * dely * fbond; s->virial_bond[2] += delz * delz * fbond;
+      s->virial_bond[3] += delx * dely * fbond; s->virial_bond[4] += delx * delz * fbond; s->virial_bond[5] += dely * delz * fbond;
+    }
+  }
+  return 0;
+}
+
+/* RanMars (src/random_mars.cpp:30-100): constructor and uniform() */
+static double mars_uniform(orc_sys *s)
+{
+  double uni = s->mars_u[s->mars_i97] - s->mars_u[s->mars_j97];
+  if (uni < 0.0) uni += 1.0;
+  s->mars_u[s->mars_i97] = uni;
+  s->mars_i97--; if (s->mars_i97 == 0) s->mars_i97 = 97;
+  s->mars_j97--; if (s->mars_j97 == 0) s->mars_j97 = 97;
+  s->mars_c -= s->mars_cd;
+  if (s->mars_c < 0.0) s->mars_c += s->mars_cm;
+  uni -= s->mars_c;
+  if (uni < 0.0) uni += 1.0;
+  return uni;
+}
+static void mars_init(orc_sys *s, int seed)
+{
+  memset(s->mars_u, 0, sizeof s->mars_u);
+  int ij = (seed - 1) / 30082, kl = (seed - 1) - 30082 * ij;
+  int i = (ij / 177) % 177 + 2, j = ij % 177 + 2, k = (kl / 169) % 178 + 1, l = kl % 169;
+  for (int ii = 1; ii <= 97; ii++) {
+    double sum = 0.0, t = 0.5;
+    for (int jj = 1; jj <= 24; jj++) {
+      int m = ((i * j) % 179) * k % 179;
+      i = j; j = k; k = m;
+      l = (53 * l + 1) % 169;
+      if ((l * m) % 64 >= 32) sum = sum + t;
+      t = 0.5 * t;
+    }
+    s->mars_u[ii] = sum;
+  }
+  s->mars_c = 362436.0 / 16777216.0; s->mars_cd = 7654321.0 / 16777216.0; s->mars_cm = 16777213.0 / 16777216.0;
+  s->mars_i97 = 97; s->mars_j97 = 33;
+  mars_uniform(s);
+}
+
+/* fix ID all langevin Tstart Tstop damp seed (src/fix_langevin.cpp:55-190): RanMars(seed + me), me = 0 */
+void orc_fix_langevin(orc_sys *s, double t_start, double t_stop, double t_period, int seed)
+{
+  s->langevin = 1; s->lang_tstart = t_start; s->lang_tstop = t_stop; s->lang_period = t_period;
+  mars_init(s, seed);
+}
+
+/* FixLangevin::post_force, the plain template instance (no gjf/tally/bias/rmass/zero; src/fix_langevin.cpp:583-716,
+ * gfactor1/2 :284-298, compute_target :773-787) */
+static void langevin_post_force(orc_sys *s, int64_t ntimestep)
+{
+  double delta = (double) (ntimestep - s->beginstep);
+  if (delta != 0.0) delta /= (double) (s->endstep - s->beginstep);
+  double t_target = s->lang_tstart + delta * (s->lang_tstop - s->lang_tstart);
+  double tsqrt = sqrt(t_target);
+  for (int i = 0; i < s->nlocal; i++) {
+    double m = s->mass[s->type[i]];
+    double gamma1 = -m / s->lang_period / s->ftm2v;
+    double gamma2 = sqrt(m) / s->ftm2v;
+    gamma2 *= sqrt(24.0 * s->boltz / s->lang_period / s->dt / s->mvv2e);
+    gamma1 *= 1.0 / 1.0;            /* ratio[type] = 1 */
+    gamma2 *= 1.0 / sqrt(1.0);
+    gamma2 = gamma2 * tsqrt;
+    double fran0 = gamma2 * (mars_uniform(s) - 0.5);
+    double fran1 = gamma2 * (mars_uniform(s) - 0.5);
+    double fran2 = gamma2 * (mars_uniform(s) - 0.5);
+    double fdrag0 = gamma1 * s->v[3 * i], fdrag1 = gamma1 * s->v[3 * i + 1], fdrag2 = gamma1 * s->v[3 * i + 2];
+    s->f[3 * i] += fdrag0 + fran0; s->f[3 * i + 1] += fdrag1 + fran1; s->f[3 * i + 2] += fdrag2 + fran2;
+  }
 }
 
 /* =====================================================================================
@@ -1046,16 +1314,19 @@ void orc_setup(orc_sys *s)
   /* cutghost needed by setup_bins */
   s->cutghost = s->cutneighmax;
   orc_setup_bins(s);
+  if (s->sort_enabled) orc_sort_atoms(s);       /* Verlet::setup: if (atom->sortfreq > 0) atom->sort() (src/verlet.cpp:121) */
   orc_borders(s);
   orc_neighbor_build(s);
   s->ncalls = 0; s->ndanger = 0;                /* build at setup is not counted (src/neighbor.cpp:2382 called with 1 -> ncalls reset in init) */
   orc_compute_forces(s, 1, 1);
+  if (s->langevin) langevin_post_force(s, s->beginstep);  /* modify->setup -> FixLangevin::setup -> post_force (src/fix_langevin.cpp:359) */
 }
 
 /* eflag/vflag: energy+virial only on steps in thermo_every multiples and the last step
  * (Integrate::ev_set src/integrate.cpp:138-183) */
 void orc_run(orc_sys *s, int nsteps, int thermo_every, int step0)
 {
+  s->beginstep = step0; s->endstep = (int64_t) step0 + nsteps;   /* Run::command (src/run.cpp:172-176) */
   for (int istep = 1; istep <= nsteps; istep++) {
     int ntimestep = step0 + istep;
     int ev = (istep == nsteps) || (thermo_every > 0 && ntimestep % thermo_every == 0);
@@ -1068,6 +1339,7 @@ void orc_run(orc_sys *s, int nsteps, int thermo_every, int step0)
       orc_neighbor_build(s);
     }
     orc_compute_forces(s, ev, ev);
+    if (s->langevin) langevin_post_force(s, ntimestep);  /* modify->post_force, before final_integrate (src/verlet.cpp:345-347) */
     orc_nve_final(s);
   }
 }
@@ -1083,13 +1355,23 @@ void orc_thermo(orc_sys *s, double *out)
   double tfactor = s->mvv2e / (dof * s->boltz);
   double temp = t * tfactor;
   double inv_volume = 1.0 / (s->prd[0] * s->prd[1] * s->prd[2]);
-  double press = (dof * s->boltz * temp + s->virial[0] + s->virial[1] + s->virial[2]) / 3.0 * inv_volume * s->nktv2p;
+  /* ComputePressure::virial_compute sums pair and bond virials (src/compute_pressure.cpp:314-341) */
+  double press = (dof * s->boltz * temp + (s->virial[0] + s->virial_bond[0]) + (s->virial[1] + s->virial_bond[1]) +
+                  (s->virial[2] + s->virial_bond[2])) / 3.0 * inv_volume * s->nktv2p;
   out[0] = s->eng_vdwl;
   out[1] = 0.5 * dof * s->boltz * temp;
   out[2] = temp;
   out[3] = press;
   for (int k = 0; k < 6; k++) out[4 + k] = s->virial[k];
 }
+
+/* bond energy (thermo E_mol) and bond virial */
+void orc_thermo_bond(orc_sys *s, double *out)
+{
+  out[0] = s->eng_bond;
+  for (int k = 0; k < 6; k++) out[1 + k] = s->virial_bond[k];
+}
+int orc_nbondlist(orc_sys *s) { return s->nbondlist; }
 
 /* ---- getters ---- */
 int orc_nlocal(orc_sys *s) { return s->nlocal; }

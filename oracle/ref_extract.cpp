@@ -102,6 +102,7 @@ int main(int argc, char **argv)
   fprintf(fm, "pxx %.17g\npyy %.17g\npzz %.17g\npxy %.17g\npxz %.17g\npyz %.17g\n",
           lammps_get_thermo(lmp, "pxx"), lammps_get_thermo(lmp, "pyy"), lammps_get_thermo(lmp, "pzz"),
           lammps_get_thermo(lmp, "pxy"), lammps_get_thermo(lmp, "pxz"), lammps_get_thermo(lmp, "pyz"));
+  fprintf(fm, "evdwl %.17g\nebond %.17g\n", lammps_get_thermo(lmp, "evdwl"), lammps_get_thermo(lmp, "ebond"));
   fprintf(fm, "npairs %ld\n", npairs);
   fclose(fm);
   lammps_close(lmp);

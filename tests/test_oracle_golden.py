@@ -115,3 +115,54 @@ def test_oracle_reference_unittest_eam_yaml(oracle, name, units):
         assert np.abs(a["f"][o] - f_ref).max() <= 5 * eps * scale, phase
         assert abs(t["pe"] - float(g[f"{phase}_vdwl"])) <= eps * abs(float(g[f"{phase}_vdwl"])), phase
         assert np.abs(t["virial"] - g[f"{phase}_stress"]).max() <= eps * np.abs(g[f"{phase}_stress"]).max(), phase
+
+
+def make_chain_oracle(oracle, g):
+    """bench/in.chain on the oracle: atom_style bond, special_bonds fene, lj/cut 1.12 shifted, bond fene,
+    fix nve + fix langevin 1.0 1.0 10.0 904297, neighbor 0.4 / every 1 delay 1, dt 0.012"""
+    s = oracle.OracleSystem(1, "lj")
+    s.set_dt(0.012)
+    s.set_box(g["in_boxlo"], g["in_boxhi"])
+    s.set_mass(1, 1.0)
+    s.set_neighbor(0.4, every=1, delay=1, check=1)
+    e = np.zeros((2, 2))
+    e[1, 1] = 1.0
+    c = np.zeros((2, 2))
+    c[1, 1] = 1.12
+    s.pair_lj_cut(e, e, c, offset_flag=True)
+    s.set_atoms(g["in_x"], g["in_v"], g["in_type"], g["in_tag"])
+    s.set_bonds(g["in_bonds"])
+    s.bond_fene({1: (30.0, 1.5, 1.0, 1.0)})
+    s.fix_langevin(1.0, 1.0, 10.0, 904297)
+    s.enable_sort()
+    return s
+
+
+def test_oracle_bench_chain_vs_reference(oracle):
+    """BASELINE configs[2], bench/in.chain (32 000-bead FENE melt): the restatement of Atom::sort, NPairHalfBinNewton
+    with special-bond exclusion, BondFENE, NTopoBondAll/closest_image and FixLangevin (RanMars replayed in the
+    reference's local atom order) against tests/golden/chain_32k.npz, minted from the unmodified reference by
+    tests/golden/make_chain_golden.py: per-atom x, v, f (every 16th tag), E_pair, E_mol, KE, T, P at step 0 and
+    after the 100 steps of the benchmark, and the shipped log bench/log.6Oct16.chain.fixed.icc.1 (8 digits)."""
+    g = load_golden("chain_32k")
+    n = len(g["in_tag"])
+    s = make_chain_oracle(oracle, g)
+    s.setup()
+    log = {"a": (0.97029772, 0.44484087, 20.494523, 22.394765, 4.6721833), "b": (0.9729966, 0.4361122, 20.507698, 22.40326, 4.6548819)}
+    for state in ("a", "b"):
+        if state == "b":
+            s.run(100)
+        t, b = s.thermo(), s.thermo_bond()
+        got = np.array([t["pe"], b["e_bond"], t["ke"], t["temp"], t["press"]])
+        ref = g[f"{state}_thermo"]
+        np.testing.assert_allclose(got, ref, rtol=1e-12)
+        a = s.atoms()
+        where = {int(tg): i for i, tg in enumerate(a["tag"])}
+        sel = np.array([where[int(tg)] for tg in g[f"{state}_tag"]])
+        for k in ("x", "v", "f"):
+            assert np.abs(a[k][sel] - g[f"{state}_{k}"]).max() <= 1e-10 * np.abs(g[f"{state}_{k}"]).max(), (state, k)
+        assert s.L.orc_npairs(s.h) == int(g[f"{state}_npairs"][0])
+        temp, epair, emol, tot, press = log[state]  # thermo normalises by N in lj units
+        assert abs(t["temp"] - temp) < 5e-8 and abs(t["pe"] / n - epair) < 5e-8 and abs(b["e_bond"] / n - emol) < 5e-6
+        assert abs((t["pe"] + b["e_bond"] + t["ke"]) / n - tot) < 5e-6 and abs(t["press"] - press) < 5e-7
+    assert s.ncalls == 25  # "Neighbor list builds = 25" in the shipped log
