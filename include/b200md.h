@@ -198,6 +198,45 @@ int b200md_host_eam_rho(b200md_ctx *ctx, int eflag, double *rho, double *fp, dou
 int b200md_host_eam_force(b200md_ctx *ctx, const double *fp_all, int eflag, int vflag, double *eng_pair,
                           double *virial);
 
+/* ---- bench/in.chain additions: bond_style fene, special_bonds fene, fix langevin -------------------
+ * One-rank contexts only for now; they take effect inside b200md_setup / b200md_run (Verlet::setup / run order:
+ * pair force, bond force, post_force fixes, final_integrate; src/verlet.cpp:106-160,232-360).
+ *
+ * b200md_set_bonds: the molecular atom style's per-atom bond arrays in the caller's local order -- num_bond[n],
+ * bond_type[n][bond_per_atom], bond_atom[n][bond_per_atom] = partner tag (src/atom.h:108-110), tag[n]; newton_bond
+ * says whether each bond is stored once (on, the data-file default) or on both atoms (src/atom.cpp data_bonds).
+ * Replaces NTopoBondAll::build (src/ntopo_bond_all.cpp:37-76): the partner's closest image
+ * (Domain::closest_image) is resolved inside the neighbor build, which also leaves 1-2 partners out of the pair
+ * list (special_bonds fene = lj 0.0 1.0 1.0, src/npair.h:125-158).  A partner farther than the neighbor cutoff
+ * is "Bond atoms missing" (B200MD_ERR_LOST_ATOMS at the next build).  Up to 4 bonds per atom.  n = 0 removes them. */
+int b200md_set_bonds(b200md_ctx *ctx, int n, const int *tag, int bond_per_atom, const int *num_bond,
+                     const int *bond_type, const int *bond_atom, int newton_bond);
+/* bond_style fene + bond_coeff K R0 epsilon sigma, arrays [nbondtypes+1] indexed by bond type
+ * (BondFENE::coeff / compute, src/MOLECULE/bond_fene.cpp:52-165).  "Bad FENE bond" is reported at the
+ * next neighbor build as B200MD_ERR_ARG. */
+int b200md_bond_fene(b200md_ctx *ctx, int nbondtypes, const double *k, const double *r0, const double *epsilon,
+                     const double *sigma);
+/* bond energy (thermo E_bond) and bond virial[6] of the last force evaluation that tallied them
+ * (Bond::energy / Bond::virial, src/bond.h:33-35); b200md_thermo's pressure already includes the bond virial */
+int b200md_thermo_bond(b200md_ctx *ctx, double *eng_bond, double *virial);
+/* fix langevin t_start t_stop damp seed, plain instance (no zero / tally / gjf / omega / per-type scale;
+ * FixLangevin::post_force_templated<0,0,0,0,0,0>, src/fix_langevin.cpp:583-716), dt = update->dt.
+ * The random stream is the reference's RanMars(seed + rank) (src/random_mars.cpp) and is consumed in the
+ * reference's local atom order, which the caller states with b200md_langevin_order, so a run reproduces the
+ * reference's trajectory.  t_period <= 0 with seed 0 removes the fix. */
+int b200md_fix_langevin(b200md_ctx *ctx, double t_start, double t_stop, double t_period, int seed, double dt);
+/* tag[n] = the owned atoms in the reference's current local order (atom->tag[0..nlocal)); sortfreq / userbinsize
+ * = atom_modify sort (defaults 1000, 0.0): the library replays Atom::sort (src/atom.cpp:2203-2290) on that
+ * order at setup and every sortfreq steps, as Verlet does */
+int b200md_langevin_order(b200md_ctx *ctx, int n, const int *tag, int sortfreq, double userbinsize);
+/* update->beginstep / endstep of the run the following b200md_run calls are pieces of (the fix langevin
+ * temperature ramp, FixLangevin::compute_target :773-787); unset = each b200md_run call is a whole run */
+int b200md_run_bounds(b200md_ctx *ctx, int64_t beginstep, int64_t endstep);
+
+/* RanMars(seed)->uniform() x n (src/random_mars.cpp:30-100): the stream b200md_fix_langevin draws from.
+ * Host only: needs neither a context nor a device. */
+int b200md_ranmars(int seed, int n, double *out);
+
 /* ---- instrumentation: device time per section in ms since the last reset, named like the
  * reference's Timer (src/timer.h:23-42): [0]=Pair [1]=Neigh [2]=Comm [3]=Modify [4]=Other;
  * counts kernels launched by this library since the last reset. */

@@ -86,6 +86,7 @@ extern "C" int b200md_destroy(b200md_ctx *c)
   dev_free(c, c->send_idx); dev_free(c, c->border_blockcnt); dev_free(c, c->border_total); dev_free(c, c->send_dir);
   dev_free(c, c->sendbuf_i); dev_free(c, c->allcounts); dev_free(c, c->sendbuf4); dev_free(c, c->recvbuf4); dev_free(c, c->sendbuf1);
   dev_free(c, c->partials); dev_free(c, c->stage);
+  bond_release(c);
   if (c->lj.d) cudaFree(c->lj.d);
   if (c->eam.frho) cudaFree(c->eam.frho);
   if (c->eam.rhor) cudaFree(c->eam.rhor);
@@ -670,6 +671,9 @@ extern "C" int b200md_thermo(b200md_ctx *c, double natoms_total, double *out)
     CU(cudaMemcpyAsync(loc, c->red_d + 16, sizeof(loc), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
   }
+  // ComputePressure::virial_compute adds the bond virial to the pair virial (src/compute_pressure.cpp:314-341);
+  // bonded contexts are one-rank (b200md_set_bonds), so no reduction
+  const double vbond = c->bonds.maxb ? c->bonds.virial_bond[0] + c->bonds.virial_bond[1] + c->bonds.virial_bond[2] : 0.0;
   // ComputeTemp (src/compute_temp.cpp:55-100): dof = 3N - 3; ComputePressure (src/compute_pressure.cpp:228-260);
   // KE = 0.5*dof*boltz*T (src/thermo.cpp:1712-1717)
   const double dof = 3.0 * natoms_total - 3.0;
@@ -679,7 +683,7 @@ extern "C" int b200md_thermo(b200md_ctx *c, double natoms_total, double *out)
   out[0] = loc[0];
   out[1] = 0.5 * dof * c->boltz * temp;
   out[2] = temp;
-  out[3] = (dof * c->boltz * temp + loc[2] + loc[3] + loc[4]) / 3.0 * inv_volume * c->nktv2p;
+  out[3] = (dof * c->boltz * temp + loc[2] + loc[3] + loc[4] + vbond) / 3.0 * inv_volume * c->nktv2p;
   for (int k = 0; k < 6; k++) out[4 + k] = loc[2 + k];
   return B200MD_OK;
 }
@@ -699,6 +703,8 @@ extern "C" int b200md_last_ev(b200md_ctx *c, double *eng_vdwl, double *virial)
 extern "C" int b200md_setup(b200md_ctx *c)
 {
   NEED_CTX();
+  if (c->bonds.maxb && !c->bonds.fene_set) return b200md_fail(c, B200MD_ERR_ARG, "All bond coeffs are not set");
+  c->langevin.nextsort = c->ntimestep;  // Verlet::setup sorts unconditionally (src/verlet.cpp:121)
   {
     Sect s(c, SECT_NEIGH);
     TRY(neigh_rebuild(c));
@@ -708,6 +714,12 @@ extern "C" int b200md_setup(b200md_ctx *c)
   {
     Sect s(c, SECT_PAIR);
     TRY(force_compute(c, 1, 1));
+    TRY(bond_compute(c, 1));
+  }
+  if (c->langevin.on) {  // modify->setup -> FixLangevin::setup -> post_force (src/fix_langevin.cpp:359)
+    Sect s(c, SECT_MODIFY);
+    if (!c->langevin.bounds_set) c->langevin.beginstep = c->langevin.endstep = c->ntimestep;
+    TRY(langevin_apply(c, c->ntimestep));
   }
   c->setup_done = true;
   return B200MD_OK;
@@ -719,6 +731,14 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
   if (!c->setup_done) TRY(b200md_setup(c));
   const double dtv = dt, dtf = 0.5 * dt * c->ftm2v;  // FixNVE::init (src/fix_nve.cpp:51-58)
   bool pending_final = false;                         // final_integrate of the previous step still to do
+  const bool extras = c->bonds.maxb > 0 || c->langevin.on;  // in.chain: bond forces / fix langevin after the pair force
+  if (c->langevin.on) {
+    if (!c->langevin.bounds_set) {  // Run::command (src/run.cpp:172-176): this call is the whole run
+      c->langevin.beginstep = c->ntimestep;
+      c->langevin.endstep = c->ntimestep + nsteps;
+    }
+    c->langevin.dt = dt;
+  }
   for (int istep = 1; istep <= nsteps; istep++) {
     c->ntimestep++;
     // Integrate::ev_set (src/integrate.cpp:138-183): energy/virial on thermo steps and on the last step
@@ -747,6 +767,10 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
       }
       Sect s(c, SECT_PAIR);
       TRY(force_compute(c, ev, ev));
+    }
+    if (extras) {  // Verlet::run: force->bond->compute, then modify->post_force (src/verlet.cpp:325-347)
+      TRY(bond_compute(c, ev));
+      TRY(langevin_apply(c, c->ntimestep));
     }
     if (ev || istep == nsteps) {
       Sect s(c, SECT_MODIFY);
@@ -871,6 +895,8 @@ extern "C" int b200md_step_host(b200md_ctx *c, double dt, int eflag, int vflag, 
   NEED_CTX();
   if (!c->setup_done) return b200md_fail(c, B200MD_ERR_ARG, "step_host needs b200md_setup first");
   if (!x || !v || !f) return b200md_fail(c, B200MD_ERR_ARG, "step_host: x, v, f are required");
+  if (c->bonds.maxb > 0 || c->langevin.on)
+    return b200md_fail(c, B200MD_ERR_ARG, "step_host: bonded / fix langevin systems run through b200md_setup + b200md_run");
   int n = c->nlocal;
   if (capacity < n) return b200md_fail(c, B200MD_ERR_ARG, "step_host: capacity %d < nlocal %d", capacity, n);
   // B200MD_HOST_PIPELINE=1 selects the three-stream chunk pipeline below (written in round 1 after the GPU budget
@@ -970,6 +996,7 @@ extern "C" int b200md_host_atoms(b200md_ctx *c, int nlocal, int nghost, const do
   NEED_CTX();
   if (nlocal <= 0 || nghost < 0 || !x || !type) return b200md_fail(c, B200MD_ERR_ARG, "host_atoms: nlocal, x, type are required");
   if (!c->have_neigh) return b200md_fail(c, B200MD_ERR_ARG, "host_atoms before b200md_neigh_config");
+  if (c->bonds.maxb > 0) return b200md_fail(c, B200MD_ERR_ARG, "host_atoms: bonded systems run through b200md_setup + b200md_run");
   const int nall = nlocal + nghost;
   if (nlocal != c->nlocal || nghost != c->nghost || !c->host_ghosts) rebuild = 1;
   TRY(dev_ensure(c, c->pos, (size_t) nall));
@@ -993,7 +1020,7 @@ extern "C" int b200md_host_atoms(b200md_ctx *c, int nlocal, int nghost, const do
   if (rebuild) {
     Sect s(c, SECT_NEIGH);
     TRY(neigh_setup_bins(c));
-    CU(cudaMemsetAsync(c->flags_d, 0, 4 * sizeof(int), c->stream));
+    CU(cudaMemsetAsync(c->flags_d, 0, 6 * sizeof(int), c->stream));
     TRY(neigh_build_lists(c));
   }
   return B200MD_OK;

@@ -75,6 +75,45 @@ struct EAMTables {            // what PairEAM::array2spline produces (src/MANYBO
   int h_type2frho[B200MD_MAXTYPES + 1];
 };
 
+// ---- in.chain additions (bond.cu) ----
+#define B200MD_MAXBONDTYPES 8
+#define B200MD_MAXBONDS 4        // bond slots per atom (both directions), held in registers by the neighbor build
+struct FeneParams {           // bond_coeff K R0 epsilon sigma (src/MOLECULE/bond_fene.cpp:142-165), 1-based
+  double k[B200MD_MAXBONDTYPES + 1], r0[B200MD_MAXBONDTYPES + 1], epsilon[B200MD_MAXBONDTYPES + 1], sigma[B200MD_MAXBONDTYPES + 1];
+};
+struct BondState {
+  int maxb = 0;               // bond slots per atom (both directions stored); 0 = no bonds
+  int ntags = 0;              // the tables below have ntags rows (tags 1..ntags)
+  DevBuf<int> partner_by_tag; // [ntags][maxb] partner tag, 0 = empty slot
+  DevBuf<int> type_by_tag;    // [ntags][maxb] bond type
+  DevBuf<int> idx;            // [nlocal][maxb] device index of each partner's closest image (neighbor build), -1 = empty
+  DevBuf<unsigned long long> best;  // [nlocal][maxb] scratch of the build: (rsq bits << 32 | index) minimum
+  bool idx_valid = false;
+  bool fene_set = false;
+  FeneParams fene;
+  double eng_bond = 0.0, virial_bond[6] = {0, 0, 0, 0, 0, 0};
+};
+struct RanMarsHost {          // src/random_mars.cpp
+  double u[98], c, cd, cm;
+  int i97, j97;
+  void init(int seed);
+  double uniform();
+};
+struct LangevinState {
+  bool on = false;
+  double t_start = 0, t_stop = 0, t_period = 1, dt = 0;
+  int64_t beginstep = 0, endstep = 0;
+  RanMarsHost rng;
+  std::vector<int> order;     // tags of the owned atoms in the REFERENCE's local order (the order RanMars is consumed in)
+  int sortfreq = 0;           // atom_modify sort: the reference's local order changes at every Atom::sort
+  double userbinsize = 0.0;
+  int64_t nextsort = 0;
+  bool bounds_set = false;    // b200md_run_bounds given (a run split into several b200md_run calls)
+  double *rand_h = nullptr;   // pinned [ntags][3]
+  int ntags = 0;
+  DevBuf<double> rand_d, gamma_d;
+};
+
 // kernel classes for the event timers (b200md_kernel_times)
 enum { KC_PAIR = 0, KC_EAM_RHO = 1, KC_NEIGH = 2, KC_NVE = 3, KC_HALO = 4, KC_SORT = 5, KC_N = 6 };
 struct KEvent { cudaEvent_t a, b; int cls; };
@@ -123,6 +162,7 @@ struct b200md_ctx {
   BinGeom bg;
   DevBuf<int> bin_count, bin_start, atom_bin, cell_list, perm, scan_tmp;
   DevBuf<unsigned char> atom_sub;
+  DevBuf<int> binrec_tag;     // tags in cell_list order (bonded systems only)
   DevBuf<double> binrec;      // BinRec[nall] (16 B each): FP32 candidate records in cell_list order (neigh.cu)
 
   // neighbor list
@@ -158,6 +198,10 @@ struct b200md_ctx {
   int *flags_h = nullptr;   // pinned mirror
   double eng_vdwl = 0, virial[6] = {0, 0, 0, 0, 0, 0};
   bool have_ev = false;
+
+  // in.chain additions
+  BondState bonds;
+  LangevinState langevin;
 
   // run state
   int64_t ntimestep = 0;
@@ -317,3 +361,7 @@ __device__ __forceinline__ double rcp_pos(double x)
 __device__ __forceinline__ int pos_type(const double4 &p) { return __double2loint(p.w); }
 __device__ __forceinline__ double type_as_w(int t) { return __hiloint2double(0, t); }
 int nve_final_initial(b200md_ctx *c, double dtv, double dtf);
+int bond_compute(b200md_ctx *c, int ev);                   // bond.cu
+int langevin_apply(b200md_ctx *c, int64_t ntimestep);     // bond.cu
+int langevin_resort(b200md_ctx *c);                        // bond.cu: Atom::sort replayed on the reference's local order
+void bond_release(b200md_ctx *c);                          // bond.cu

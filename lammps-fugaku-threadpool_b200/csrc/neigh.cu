@@ -399,7 +399,7 @@ struct BinRec { float x, y, z; int jt; };
 #define BR_JMASK 0x0FFFFFFF
 
 __global__ void k_binrec_fill(const double4 *__restrict__ pos, const int *__restrict__ cell_list, int nall, double ox, double oy,
-                              double oz, BinRec *__restrict__ rec)
+                              double oz, BinRec *__restrict__ rec, const int *__restrict__ tag, int *__restrict__ rec_tag)
 {
   int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= nall) return;
@@ -411,6 +411,7 @@ __global__ void k_binrec_fill(const double4 *__restrict__ pos, const int *__rest
   r.z = (float) (p.z - oz);
   r.jt = j | ((pos_type(p) - 1) << 28);
   rec[k] = r;
+  if (rec_tag) rec_tag[k] = tag[j];  // bonded systems: the candidate's tag, for the special-partner test
 }
 
 __device__ __forceinline__ BinRec ld_rec(const BinRec *__restrict__ p)
@@ -424,11 +425,22 @@ __device__ __forceinline__ BinRec ld_rec(const BinRec *__restrict__ p)
 #define BUILD_WARPS 4
 // STAGE: each warp collects its lanes' lists in shared memory ([k][lane], conflict free) and writes them out row by
 // row, so a store instruction covers one contiguous piece of a 128-byte list row instead of 32 different rows
-template <int ONETYPE, int STAGE>
+// BONDED (in.chain): a candidate within the cutoff whose tag is one of the atom's 1-2 partners is NOT listed
+// (special_bonds lj weight 0, NPair::find_special src/npair.h:125-158 -> -1) but recorded as the device index of that
+// bond partner; of several periodic images the closest wins (Domain::closest_image).
+struct BondBuild {
+  const int *rec_tag;          // [nall] tag of each record, cell_list order
+  const int *tag;              // [nall]
+  const int *partner_by_tag;   // [ntags][maxb], 0 = empty
+  int *bond_idx;               // [nlocal][maxb] out
+  int maxb;
+};
+template <int ONETYPE, int STAGE, int BONDED>
 __global__ void __launch_bounds__(BUILD_WARPS * 32)
 k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int nlocal, BinGeom g,
              const int *__restrict__ bin_start, const double *__restrict__ cutneighsq, int ntypes, float tol, int maxneigh,
-             int *__restrict__ numneigh, int *__restrict__ neigh, int *__restrict__ flags, int *__restrict__ tile_ghost)
+             int *__restrict__ numneigh, int *__restrict__ neigh, int *__restrict__ flags, int *__restrict__ tile_ghost,
+             BondBuild bb)
 {
   __shared__ double s_cut[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
   __shared__ float s_cutf[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
@@ -461,6 +473,17 @@ k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, in
     const size_t base = (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
     int n = 0;
     bool ghost_seen = false;  // overlap mode: does this atom's list hold a ghost?
+    int ptag[B200MD_MAXBONDS], pbest[B200MD_MAXBONDS];
+    float prsq[B200MD_MAXBONDS];
+    if (BONDED) {
+      const int ti = owned ? bb.tag[i] : 1;
+#pragma unroll
+      for (int m = 0; m < B200MD_MAXBONDS; m++) {
+        ptag[m] = (owned && m < bb.maxb) ? bb.partner_by_tag[(size_t) (ti - 1) * bb.maxb + m] : 0;
+        pbest[m] = -1;
+        prsq[m] = 3.0e38f;
+      }
+    }
     for (int dz = -1; dz <= 1; dz++)
       for (int dy = -1; dy <= 1; dy++) {
         const int cell = ((bz + dz) * g.mbin[1] + (by + dy)) * g.mbin[0] + bx - 1;
@@ -480,6 +503,15 @@ k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, in
             accept = r2 <= s_cut[(ONETYPE ? nt1 : trow) + (ONETYPE ? 1 : ((unsigned) c.jt >> 28) + 1)];
           }
           const int j = c.jt & BR_JMASK;
+          if (BONDED && accept && owned && j != i) {
+            const int tj = __ldg(bb.rec_tag + k);
+#pragma unroll
+            for (int m = 0; m < B200MD_MAXBONDS; m++)
+              if (ptag[m] != 0 && tj == ptag[m]) {
+                accept = false;
+                if (rsq < prsq[m]) { prsq[m] = rsq; pbest[m] = j; }
+              }
+          }
           if (accept && owned && j != i) {
             ghost_seen |= j >= nlocal;
             if (n < maxneigh) {
@@ -497,6 +529,15 @@ k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, in
       __syncwarp();
     }
     if (owned) numneigh[i] = n;
+    if (BONDED && owned) {
+#pragma unroll
+      for (int m = 0; m < B200MD_MAXBONDS; m++)
+        if (m < bb.maxb) {
+          bb.bond_idx[(size_t) i * bb.maxb + m] = pbest[m];
+          if (ptag[m] != 0 && pbest[m] < 0) flags[5] = 1;  // "Bond atoms missing" (src/ntopo_bond_all.cpp:56-61)
+          ghost_seen |= pbest[m] >= nlocal;
+        }
+    }
     if (tile_ghost && owned && ghost_seen) atomicOr(&tile_ghost[i >> 5], 1);
     nmax = max(nmax, owned ? n : 0);
   }
@@ -572,7 +613,12 @@ int neigh_rebuild(b200md_ctx *c)
   PhaseTimer ph(c);
   if (c->nlocal <= 0) return b200md_fail(c, B200MD_ERR_ARG, "no atoms uploaded");
   TRY(neigh_setup_bins(c));
-  CU(cudaMemsetAsync(c->flags_d, 0, 4 * sizeof(int), c->stream));
+  if (c->bonds.maxb) {  // "Bad FENE bond" raised by k_bond_fene since the last build (bond_fene.cpp:88)
+    CU(cudaMemcpyAsync(c->flags_h + 4, c->flags_d + 4, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (c->flags_h[4]) return b200md_fail(c, B200MD_ERR_ARG, "Bad FENE bond");
+  }
+  CU(cudaMemsetAsync(c->flags_d, 0, 6 * sizeof(int), c->stream));
   int n = c->nlocal;
 
   // Domain::pbc
@@ -587,6 +633,9 @@ int neigh_rebuild(b200md_ctx *c)
   TRY(comm_exchange(c));
   ph.mark("exchange");
   n = c->nlocal;
+  // fix langevin replay: the reference's own Atom::sort reorders the atoms its random stream is consumed over
+  // (Verlet::setup src/verlet.cpp:121, Verlet::run :291)
+  if (c->langevin.on && c->langevin.sortfreq > 0 && c->ntimestep >= c->langevin.nextsort) TRY(langevin_resort(c));
 
   // spatial sort of owned atoms (Atom::sort) by neighbor bin
   TRY(dev_ensure(c, c->perm, (size_t) n));
@@ -657,8 +706,14 @@ int neigh_build_lists(b200md_ctx *c)
       TRY(dev_ensure(c, c->binrec, (size_t) nall * 2));  // 16-byte records held as double pairs
       KProf kp(c, KC_NEIGH);
       BinRec *rec = reinterpret_cast<BinRec *>(c->binrec.p);
+      int *rec_tag = nullptr;
+      if (c->bonds.maxb > 0) {
+        TRY(dev_ensure(c, c->binrec_tag, (size_t) nall));
+        rec_tag = c->binrec_tag.p;
+      }
       k_binrec_fill<<<cdiv(nall, 256), 256, 0, c->stream>>>(c->pos.p, c->cell_list.p, nall, g.lo[0] - BIN_MARGIN / g.inv[0],
-                                                            g.lo[1] - BIN_MARGIN / g.inv[1], g.lo[2] - BIN_MARGIN / g.inv[2], rec);
+                                                            g.lo[1] - BIN_MARGIN / g.inv[1], g.lo[2] - BIN_MARGIN / g.inv[2], rec,
+                                                            c->tag.p, rec_tag);
       LAUNCH_CHECK();
       const int nown = g.nbin[0] * g.nbin[1] * g.nbin[2];
       const size_t stage_bytes = (size_t) BUILD_WARPS * c->maxneigh * 32 * sizeof(int);
@@ -666,8 +721,8 @@ int neigh_build_lists(b200md_ctx *c)
       const bool stage = stage_bytes <= 96 * 1024 && getenv("B200MD_BUILD_STAGE") != nullptr;
       static bool attr_done = false;
       if (!attr_done) {
-        CU(cudaFuncSetAttribute(k_build_bins<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-        CU(cudaFuncSetAttribute(k_build_bins<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        CU(cudaFuncSetAttribute(k_build_bins<1, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        CU(cudaFuncSetAttribute(k_build_bins<0, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
         attr_done = true;
       }
       int *tile_ghost = nullptr;
@@ -677,18 +732,33 @@ int neigh_build_lists(b200md_ctx *c)
         tile_ghost = c->tile_ghost.p;
       }
       c->tiles_valid = tile_ghost != nullptr;
-#define BB_ARGS c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d, tile_ghost
+      BondBuild bb = {nullptr, nullptr, nullptr, nullptr, 0};
+      const bool bonded = c->bonds.maxb > 0;
+      if (bonded) {
+        TRY(dev_ensure(c, c->bonds.idx, (size_t) n * c->bonds.maxb));
+        bb.rec_tag = c->binrec_tag.p;
+        bb.tag = c->tag.p;
+        bb.partner_by_tag = c->bonds.partner_by_tag.p;
+        bb.bond_idx = c->bonds.idx.p;
+        bb.maxb = c->bonds.maxb;
+      }
+#define BB_ARGS c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d, tile_ghost, bb
       const int bgrid = cdiv(nown, BUILD_WARPS), bthr = BUILD_WARPS * 32;
-      if (c->ntypes == 1) {
-        if (stage) k_build_bins<1, 1><<<bgrid, bthr, stage_bytes, c->stream>>>(BB_ARGS);
-        else k_build_bins<1, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+      if (bonded) {
+        if (c->ntypes == 1) k_build_bins<1, 0, 1><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+        else k_build_bins<0, 0, 1><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+      } else if (c->ntypes == 1) {
+        if (stage) k_build_bins<1, 1, 0><<<bgrid, bthr, stage_bytes, c->stream>>>(BB_ARGS);
+        else k_build_bins<1, 0, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
       } else {
-        if (stage) k_build_bins<0, 1><<<bgrid, bthr, stage_bytes, c->stream>>>(BB_ARGS);
-        else k_build_bins<0, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+        if (stage) k_build_bins<0, 1, 0><<<bgrid, bthr, stage_bytes, c->stream>>>(BB_ARGS);
+        else k_build_bins<0, 0, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
       }
 #undef BB_ARGS
       LAUNCH_CHECK();
     } else {
+      if (c->bonds.maxb > 0)
+        return b200md_fail(c, B200MD_ERR_ARG, "bonded systems are built by the bin-per-warp kernel only (cluster size 1, FP32 prefilter)");
       c->tiles_valid = false;
       KProf kp(c, KC_NEIGH);
 #define BUILD_ARGS c->pos.p, n, c->bg, c->bin_start.p, c->cell_list.p, c->cutneighsq_d.p, c->ntypes, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d
@@ -698,9 +768,11 @@ int neigh_build_lists(b200md_ctx *c)
 #undef BUILD_ARGS
       LAUNCH_CHECK();
     }
-    CU(cudaMemcpyAsync(c->flags_h, c->flags_d, 4 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(c->flags_h, c->flags_d, 6 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     if (c->flags_h[0]) return b200md_fail(c, B200MD_ERR_NONFINITE, "Non-numeric positions - simulation unstable");
+    if (c->flags_h[5]) return b200md_fail(c, B200MD_ERR_LOST_ATOMS, "Bond atoms missing: a bond partner is not within the neighbor cutoff");
+    c->bonds.idx_valid = c->bonds.maxb > 0;
     c->maxneigh_seen = c->flags_h[1];
     if (c->flags_h[1] > c->maxneigh) {  // "Neighbor list overflow": grow and redo instead of aborting
       c->maxneigh = (c->flags_h[1] + c->flags_h[1] / 8 + 7) / 8 * 8;

@@ -55,6 +55,13 @@ PROTOTYPES = {
     "b200md_host_forces": (_i, [_vp, _vp, _i]),
     "b200md_host_eam_rho": (_i, [_vp, _i, _vp, _vp, _vp]),
     "b200md_host_eam_force": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
+    "b200md_set_bonds": (_i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _i]),
+    "b200md_bond_fene": (_i, [_vp, _i, _vp, _vp, _vp, _vp]),
+    "b200md_thermo_bond": (_i, [_vp, _vp, _vp]),
+    "b200md_fix_langevin": (_i, [_vp, _d, _d, _d, _i, _d]),
+    "b200md_langevin_order": (_i, [_vp, _i, _vp, _i, _d]),
+    "b200md_run_bounds": (_i, [_vp, _i64, _i64]),
+    "b200md_ranmars": (_i, [_i, _i, _vp]),
     "b200md_timers": (_i, [_vp, _vp, _vp, _i]),
     "b200md_profile": (_i, [_vp, _i]),
     "b200md_kernel_times": (_i, [_vp, _vp, _vp, _i]),

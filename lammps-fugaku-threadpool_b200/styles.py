@@ -8,6 +8,8 @@ Same names, argument meaning and error behaviour as the reference's script comma
     neighbor SKIN bin ; neigh_modify every N delay M check yes|no
                                               -> NeighborB200.set / modify                 (src/neighbor.cpp:2556-2700)
     fix ID all nve                            -> FixNVEB200                                (src/fix_nve.cpp)
+    bond_style fene ; bond_coeff ; special_bonds fene ; fix ID all langevin T T damp seed   (bench/in.chain)
+                                              -> BondFENEB200, B200MD.bonds / fix("langevin", ...)
     timestep DT ; run N ; thermo N            -> B200MD.timestep / run                     (src/verlet.cpp:229-360)
 
 The C++ versions of these classes for a LAMMPS build (suffix ``b200``) are described in INTEGRATION.md; this
@@ -189,6 +191,45 @@ class FixNVEB200:
         self.o.ctx.call("b200md_nve_final", self.dtf)
 
 
+class BondFENEB200:
+    """bond_style fene ; bond_coeff N K R0 epsilon sigma (src/MOLECULE/bond_fene.cpp:129-165)."""
+
+    def __init__(self, owner: "B200MD", nbondtypes: int):
+        self.o = owner
+        self.n = int(nbondtypes)
+        self.k = np.zeros(self.n + 1)
+        self.r0 = np.zeros(self.n + 1)
+        self.epsilon = np.zeros(self.n + 1)
+        self.sigma = np.zeros(self.n + 1)
+        self.setflag = np.zeros(self.n + 1, dtype=bool)
+
+    def coeff(self, itype: int, k: float, r0: float, epsilon: float, sigma: float):
+        if not 1 <= itype <= self.n:
+            raise ValueError("Incorrect args for bond coefficients")
+        self.k[itype], self.r0[itype], self.epsilon[itype], self.sigma[itype] = k, r0, epsilon, sigma
+        self.setflag[itype] = True
+
+    def init(self):
+        if not self.setflag[1:].all():
+            raise ValueError("All bond coeffs are not set")
+        self.o.ctx.call("b200md_bond_fene", self.n, lib.ptr(self.k), lib.ptr(self.r0), lib.ptr(self.epsilon), lib.ptr(self.sigma))
+
+
+class FixLangevinB200:
+    """fix ID all langevin Tstart Tstop damp seed (src/fix_langevin.cpp:55-160), plain instance."""
+
+    def __init__(self, owner: "B200MD", t_start: float, t_stop: float, damp: float, seed: int):
+        if damp <= 0.0:
+            raise ValueError("Fix langevin period must be > 0.0")
+        if seed <= 0:
+            raise ValueError("Illegal fix langevin command")
+        self.o = owner
+        self.t_start, self.t_stop, self.damp, self.seed = float(t_start), float(t_stop), float(damp), int(seed)
+
+    def init(self):
+        self.o.ctx.call("b200md_fix_langevin", self.t_start, self.t_stop, self.damp, self.seed, self.o.dt)
+
+
 class B200MD:
     """The slice of a LAMMPS instance the hot path needs: box, atoms, one pair style, neighbor, fix nve, run."""
 
@@ -209,6 +250,10 @@ class B200MD:
         self.natoms_total = 0
         self._initialized = False
         self.thermo_log: list[dict] = []
+        self.bond = None            # bond_style fene (bench/in.chain)
+        self.fix_langevin = None
+        self.sortfreq, self.sort_binsize = 1000, 0.0   # atom_modify sort defaults (src/atom.cpp:119-120)
+        self._order = None
 
     # -- script-command analogues ---------------------------------------------------------------
     def box(self, lo, hi, periodic=(1, 1, 1)):
@@ -226,9 +271,50 @@ class B200MD:
         type_ = np.ascontiguousarray(type_, dtype=np.int32)
         tag = np.ascontiguousarray(tag, dtype=np.int32)
         image = None if image is None else np.ascontiguousarray(image, dtype=np.int32)
+        if self._order is None or self._order.shape[0] != tag.shape[0]:
+            self._order = tag.copy()
         self.ctx.call("b200md_upload_atoms", x.shape[0], lib.ptr(x), lib.ptr(v), lib.ptr(type_), lib.ptr(tag), lib.ptr(image))
         self.natoms_total = int(natoms_total if natoms_total is not None else x.shape[0])
         self._initialized = False
+
+    def bonds(self, tag, num_bond, bond_type, bond_atom, newton_bond: bool = True):
+        """The molecular atom style's bond arrays in the caller's local order (read_data Bonds section ->
+        Atom::data_bonds, src/atom.cpp:1380-1460)."""
+        tag = np.ascontiguousarray(tag, dtype=np.int32)
+        num_bond = np.ascontiguousarray(num_bond, dtype=np.int32)
+        bond_type = np.ascontiguousarray(bond_type, dtype=np.int32).reshape(tag.shape[0], -1)
+        bond_atom = np.ascontiguousarray(bond_atom, dtype=np.int32).reshape(tag.shape[0], -1)
+        self.ctx.call("b200md_set_bonds", tag.shape[0], lib.ptr(tag), bond_type.shape[1], lib.ptr(num_bond), lib.ptr(bond_type),
+                      lib.ptr(bond_atom), int(newton_bond))
+
+    def bond_style(self, name: str, nbondtypes: int = 1):
+        if name not in ("fene", "fene/b200"):
+            raise ValueError(f"Unrecognized bond style '{name}' is not on the B200 hot path")
+        self.bond = BondFENEB200(self, nbondtypes)
+        self._initialized = False
+        return self.bond
+
+    def special_bonds(self, keyword: str):
+        """Only `special_bonds fene` (lj 0.0 1.0 1.0): what the bonded neighbor build implements."""
+        if keyword != "fene":
+            raise ValueError("special_bonds: only the fene setting (lj 0.0 1.0 1.0) is on the B200 hot path")
+
+    def fix(self, style: str, *args):
+        if style in ("langevin", "langevin/b200"):
+            self.fix_langevin = FixLangevinB200(self, *args)
+            self._initialized = False
+            return self.fix_langevin
+        if style in ("nve", "nve/b200"):
+            return self.fix_nve
+        raise ValueError(f"Unrecognized fix style '{style}' is not on the B200 hot path")
+
+    def atom_modify_sort(self, freq: int, binsize: float = 0.0):
+        self.sortfreq, self.sort_binsize = int(freq), float(binsize)
+
+    def local_order(self, tag):
+        """atom->tag[0..nlocal) of the reference at this point of the script: the order fix langevin's random
+        stream is consumed in (defaults to the order atoms were handed to create_atoms)."""
+        self._order = np.ascontiguousarray(tag, dtype=np.int32)
 
     def pair_style(self, name: str, *args):
         if name in ("lj/cut", "lj/cut/b200"):
@@ -253,6 +339,11 @@ class B200MD:
         self.ctx.call("b200md_set_mass", self.ntypes, lib.ptr(self.mass))
         self.neighbor.init(cut)
         self.fix_nve.init()
+        if self.bond is not None:
+            self.bond.init()
+        if self.fix_langevin is not None:
+            self.fix_langevin.init()
+            self.ctx.call("b200md_langevin_order", self._order.shape[0], lib.ptr(self._order), self.sortfreq, self.sort_binsize)
         self._initialized = True
 
     def setup(self):
@@ -268,6 +359,9 @@ class B200MD:
         if int(self.ctx.L.b200md_timestep(self.ctx.h)) == 0 and not self.thermo_log:
             self.setup()
         done = 0
+        step0 = int(self.ctx.L.b200md_timestep(self.ctx.h))
+        if self.fix_langevin is not None:   # update->beginstep / endstep of this `run` (src/run.cpp:172-176)
+            self.ctx.call("b200md_run_bounds", step0, step0 + nsteps)
         while done < nsteps:
             step = int(self.ctx.L.b200md_timestep(self.ctx.h))
             chunk = nsteps - done
@@ -280,8 +374,13 @@ class B200MD:
     def thermo(self) -> dict:
         out = np.zeros(10)
         self.ctx.call("b200md_thermo", float(self.natoms_total), lib.ptr(out))
-        return dict(step=int(self.ctx.L.b200md_timestep(self.ctx.h)), pe=out[0], ke=out[1], temp=out[2], press=out[3],
-                    virial=out[4:10].copy())
+        th = dict(step=int(self.ctx.L.b200md_timestep(self.ctx.h)), pe=out[0], ke=out[1], temp=out[2], press=out[3],
+                  virial=out[4:10].copy())
+        if self.bond is not None:
+            eb, vb = np.zeros(1), np.zeros(6)
+            self.ctx.call("b200md_thermo_bond", lib.ptr(eb), lib.ptr(vb))
+            th.update(evdwl=out[0], ebond=float(eb[0]), pe=out[0] + float(eb[0]), virial_bond=vb)
+        return th
 
     # -- data access --------------------------------------------------------------------------------
     @property

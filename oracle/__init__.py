@@ -106,6 +106,7 @@ def lib() -> C.CDLL:
         L.orc_thermo_bond.argtypes = [vp, vp]
         L.orc_nbondlist.restype = C.c_int
         L.orc_nbondlist.argtypes = [vp]
+        L.orc_ranmars.argtypes = [C.c_int, C.c_int, vp]
         _lib = L
     return _lib
 

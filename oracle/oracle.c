@@ -1252,6 +1252,15 @@ static void mars_init(orc_sys *s, int seed)
   mars_uniform(s);
 }
 
+/* the first n numbers of RanMars(seed)->uniform(), for checking another restatement of the generator */
+void orc_ranmars(int seed, int n, double *out)
+{
+  orc_sys *s = (orc_sys *) calloc(1, sizeof(orc_sys));
+  mars_init(s, seed);
+  for (int i = 0; i < n; i++) out[i] = mars_uniform(s);
+  free(s);
+}
+
 /* fix ID all langevin Tstart Tstop damp seed (src/fix_langevin.cpp:55-190): RanMars(seed + me), me = 0 */
 void orc_fix_langevin(orc_sys *s, double t_start, double t_stop, double t_period, int seed)
 {

@@ -104,3 +104,20 @@ def test_inputs_match_oracle_lattice_and_velocities(pkg, oracle):
     v = inp.velocity_create_geom(x, m, 1.44, 87287, "lj")
     vo = oracle.velocity_create_geom(x, np.ones(len(x), dtype=np.int32), np.array([0.0, 1.0]), 1.44, 87287, "lj")
     np.testing.assert_allclose(v, vo, rtol=1e-13, atol=1e-15)
+
+
+def test_ranmars_stream_equals_oracle(pkg, oracle):
+    """fix langevin's generator is host code: the library's RanMars restatement against the oracle's (which the
+    in.chain golden pins to the reference, tests/test_oracle_golden.py) -- bit-exact, several seeds, 10^5 numbers
+    (more than one wrap of the 97-entry lag table and of the c/cd/cm counter)"""
+    import ctypes as C
+
+    L, O = pkg.lib.load(), oracle.lib()
+    for seed in (1, 904297, 904298, 30082, 900000000):
+        a, b = np.empty(100000), np.empty(100000)
+        assert L.b200md_ranmars(seed, len(a), a.ctypes.data_as(C.c_void_p)) == 0
+        O.orc_ranmars(seed, len(b), b.ctypes.data_as(C.c_void_p))
+        assert np.array_equal(a, b)
+        assert 0.0 <= a.min() and a.max() < 1.0
+    assert L.b200md_ranmars(0, 1, a.ctypes.data_as(C.c_void_p)) == 5      # "Invalid seed for Marsaglia random # generator"
+    assert L.b200md_ranmars(900000001, 1, a.ctypes.data_as(C.c_void_p)) == 5

@@ -1,0 +1,140 @@
+"""bench/in.chain on the device: bonded neighbor build (special_bonds fene), BondFENE,
+fix langevin with the reference's RanMars stream, through the C ABI, against tests/golden/chain_32k.npz minted from
+the unmodified reference by tests/golden/make_chain_golden.py and against the shipped log
+bench/log.6Oct16.chain.fixed.icc.1.  The file sorts last on purpose: these kernels were written after the round's GPU
+budget was spent and have not run on hardware yet, so they go after everything that has."""
+from __future__ import annotations
+
+import numpy as np
+import pytest
+
+from conftest import FIRST_RUN, load_golden
+
+pytestmark = pytest.mark.gpu
+F_RTOL = 1e-10
+THERMO_RTOL = 1e-6
+N = 32000
+
+
+def bond_arrays(tag, bonds):
+    """data-file `Bonds` rows (type a1 a2) -> num_bond / bond_type / bond_atom in the local order of `tag`,
+    each bond stored on a1 (newton_bond on; Atom::data_bonds)"""
+    where = {int(t): i for i, t in enumerate(tag)}
+    per = [[] for _ in tag]
+    for t, a1, a2 in np.asarray(bonds):
+        per[where[int(a1)]].append((int(t), int(a2)))
+    bpa = max(1, max(len(p) for p in per))
+    num = np.array([len(p) for p in per], dtype=np.int32)
+    btype = np.zeros((len(per), bpa), dtype=np.int32)
+    batom = np.zeros((len(per), bpa), dtype=np.int32)
+    for i, p in enumerate(per):
+        for m, (t, a2) in enumerate(p):
+            btype[i, m], batom[i, m] = t, a2
+    return num, btype, batom
+
+
+def make_chain_device(pkg, g, langevin=True):
+    md = pkg.B200MD(units="lj", ntypes=1)
+    md.box(g["in_boxlo"], g["in_boxhi"])
+    md.set_mass(1, 1.0)
+    p = md.pair_style("lj/cut", 1.12)
+    p.coeff(1, 1, 1.0, 1.0, 1.12)
+    p.modify(shift=True)
+    md.neighbor.set(0.4, "bin")
+    md.neighbor.modify(every=1, delay=1, check=True)
+    md.timestep(0.012)
+    md.create_atoms(g["in_x"], g["in_v"], g["in_type"], g["in_tag"])
+    md.special_bonds("fene")
+    md.bonds(g["in_tag"], *bond_arrays(g["in_tag"], g["in_bonds"]))
+    md.bond_style("fene", 1).coeff(1, 30.0, 1.5, 1.0, 1.0)
+    if langevin:
+        md.fix("langevin", 1.0, 1.0, 10.0, 904297)
+    return md
+
+
+def check_state(md, g, state, x_atol):
+    t = md.thermo_log[-1]
+    got = np.array([t["evdwl"], t["ebond"], t["ke"], t["temp"], t["press"]])
+    np.testing.assert_allclose(got, g[f"{state}_thermo"], rtol=THERMO_RTOL)
+    a = md.gather()
+    sel = np.searchsorted(a["tag"], g[f"{state}_tag"])
+    assert np.array_equal(a["tag"][sel], g[f"{state}_tag"])
+    box = g["in_boxhi"] - g["in_boxlo"]
+    dx = a["x"][sel] - g[f"{state}_x"]
+    dx -= box * np.round(dx / box)
+    assert np.abs(dx).max() <= x_atol
+    return a, sel
+
+
+@FIRST_RUN
+def test_chain_setup_forces_vs_reference(pkg):
+    """step 0: pair list without the 1-2 partners (count = 2 x the reference's half list), E_pair, E_bond, P and
+    per-atom forces (pair + FENE + the langevin kick of FixLangevin::setup) <= 1e-10 relative"""
+    g = load_golden("chain_32k")
+    md = make_chain_device(pkg, g)
+    md.setup()
+    a, sel = check_state(md, g, "a", 1e-12)
+    fmax = np.abs(g["a_f"]).max()
+    assert np.abs(a["f"][sel] - g["a_f"]).max() <= F_RTOL * fmax
+    numneigh, _ = md.neighbor_list()
+    assert int(numneigh.sum()) == 2 * int(g["a_npairs"][0])
+    md.close()
+
+
+@FIRST_RUN
+def test_chain_100_steps_vs_reference_and_shipped_log(pkg):
+    """the benchmark itself: 100 steps, thermo <= 1e-6 of the reference run here and of the shipped log
+    (bench/log.6Oct16.chain.fixed.icc.1: T, E_pair/N, E_mol/N, TotEng/N, P at step 100; 25 neighbor builds)"""
+    g = load_golden("chain_32k")
+    md = make_chain_device(pkg, g)
+    md.run(100)
+    check_state(md, g, "b", 1e-7)
+    t = md.thermo_log[-1]
+    temp, epair, emol, tot, press = 0.9729966, 0.4361122, 20.507698, 22.40326, 4.6548819
+    assert abs(t["temp"] - temp) < 5e-7 and abs(t["evdwl"] / N - epair) < 5e-7 and abs(t["ebond"] / N - emol) < 5e-5
+    assert abs((t["pe"] + t["ke"]) / N - tot) < 5e-5 and abs(t["press"] - press) < 5e-6
+    assert md.neigh_stats()["builds"] == 25
+    md.close()
+
+
+@FIRST_RUN
+def test_chain_nve_conserves_energy_and_is_reproducible(pkg):
+    """without the thermostat: pair + FENE forces are conservative, so E_total drifts by < 1e-4 relative over 200
+    steps; two runs are bitwise identical (no atomics on the bond path either)"""
+    g = load_golden("chain_32k")
+    out = []
+    for _ in range(2):
+        md = make_chain_device(pkg, g, langevin=False)
+        md.run(200, thermo_every=100)
+        e = [t["pe"] + t["ke"] for t in md.thermo_log]
+        assert abs(e[-1] - e[0]) <= 1e-4 * abs(e[0])
+        out.append(md.gather())
+        md.close()
+    assert np.array_equal(out[0]["x"], out[1]["x"]) and np.array_equal(out[0]["f"], out[1]["f"])
+
+
+@FIRST_RUN
+def test_chain_error_paths(pkg):
+    """"Bond atoms missing" when a partner is beyond the neighbor cutoff; more than 4 bonds per atom refused;
+    bond coeffs required at setup"""
+    g = load_golden("chain_32k")
+    md = make_chain_device(pkg, g, langevin=False)
+    tag = g["in_tag"]
+    bonds = np.array(g["in_bonds"])
+    far = bonds.copy()
+    far[0] = (1, 1, 17001)  # two beads of different chains
+    md.bonds(tag, *bond_arrays(tag, far))
+    with pytest.raises(pkg.lib.B200MDError) as e:
+        md.setup()
+    assert "Bond atoms missing" in str(e.value)
+    star = np.concatenate([bonds, [(1, 5, k) for k in (100, 200, 300, 400)]])
+    with pytest.raises(pkg.lib.B200MDError) as e:
+        md.bonds(tag, *bond_arrays(tag, star))
+    assert "bonds" in str(e.value)
+    md.close()
+    md = make_chain_device(pkg, g, langevin=False)
+    md.bond = None  # bond_style never given
+    with pytest.raises(pkg.lib.B200MDError) as e:
+        md.setup()
+    assert "bond coeffs" in str(e.value)
+    md.close()
