@@ -168,6 +168,9 @@ int b200md_last_ev(b200md_ctx *ctx, double *eng_vdwl, double *virial);
 int b200md_setup(b200md_ctx *ctx);
 int b200md_run(b200md_ctx *ctx, int nsteps, double dt, int thermo_every);
 int64_t b200md_timestep(const b200md_ctx *ctx);
+/* update->ntimestep of the caller (reset_timestep, or a context attached in the middle of a script): the thermo
+ * schedule of b200md_run and the Atom::sort schedule of the langevin replay count in these steps */
+int b200md_set_timestep(b200md_ctx *ctx, int64_t ntimestep);
 
 /* ---- host-buffer mode: one whole timestep with the atoms handed over in HOST arrays every step -- the GPU
  * package's traffic model (x up, results down every step, src/GPU/pair_lj_cut_gpu.cpp:85-118) applied to the
@@ -223,7 +226,8 @@ int b200md_thermo_bond(b200md_ctx *ctx, double *eng_bond, double *virial);
  * FixLangevin::post_force_templated<0,0,0,0,0,0>, src/fix_langevin.cpp:583-716), dt = update->dt.
  * The random stream is the reference's RanMars(seed + rank) (src/random_mars.cpp) and is consumed in the
  * reference's local atom order, which the caller states with b200md_langevin_order, so a run reproduces the
- * reference's trajectory.  t_period <= 0 with seed 0 removes the fix. */
+ * reference's trajectory.  Calling it again with the same seed (every `run`) updates the parameters and keeps
+ * the stream where it is, like the fix's own generator; t_period <= 0 with seed 0 removes the fix. */
 int b200md_fix_langevin(b200md_ctx *ctx, double t_start, double t_stop, double t_period, int seed, double dt);
 /* tag[n] = the owned atoms in the reference's current local order (atom->tag[0..nlocal)); sortfreq / userbinsize
  * = atom_modify sort (defaults 1000, 0.0): the library replays Atom::sort (src/atom.cpp:2203-2290) on that

@@ -380,6 +380,7 @@ extern "C" int b200md_fix_langevin(b200md_ctx *c, double t_start, double t_stop,
   LangevinState &L = c->langevin;
   if (t_period <= 0.0 && seed == 0) {  // unfix
     L.on = false;
+    L.seed = 0;
     return B200MD_OK;
   }
   if (t_period <= 0.0) return b200md_fail(c, B200MD_ERR_ARG, "Fix langevin period must be > 0.0");
@@ -387,7 +388,10 @@ extern "C" int b200md_fix_langevin(b200md_ctx *c, double t_start, double t_stop,
   if (seed > 900000000) return b200md_fail(c, B200MD_ERR_ARG, "Invalid seed for Marsaglia random # generator");
   if (c->nranks > 1) return b200md_fail(c, B200MD_ERR_ARG, "fix langevin replay mode supports one rank (RanMars(seed + me) per rank)");
   L.t_start = t_start; L.t_stop = t_stop; L.t_period = t_period; L.dt = dt;
-  L.rng.init(seed + c->rank);
+  // the fix owns one generator for its whole life (created in the constructor, fix_langevin.cpp:160): a repeated
+  // call for the same fix (same seed, e.g. at the start of every `run`) keeps the stream where it is
+  if (!L.on || L.seed != seed) L.rng.init(seed + c->rank);
+  L.seed = seed;
   L.on = true;
   c->setup_done = false;
   return B200MD_OK;

@@ -783,6 +783,13 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
 }
 
 extern "C" int64_t b200md_timestep(const b200md_ctx *c) { return c ? c->ntimestep : 0; }
+extern "C" int b200md_set_timestep(b200md_ctx *c, int64_t ntimestep)
+{
+  if (!c) return b200md_fail(nullptr, B200MD_ERR_ARG, "NULL context");
+  if (ntimestep < 0) return b200md_fail(c, B200MD_ERR_ARG, "Timestep must be >= 0");  // reset_timestep (src/update.cpp:470)
+  c->ntimestep = ntimestep;
+  return B200MD_OK;
+}
 
 // ---- host-buffer mode ------------------------------------------------------------------------------
 // One whole timestep with HOST x, v in and x, v, f out.  PCIe is the bound (120 B/atom against about 4.6 ms of

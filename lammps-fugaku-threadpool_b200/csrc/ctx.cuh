@@ -103,6 +103,7 @@ struct LangevinState {
   bool on = false;
   double t_start = 0, t_stop = 0, t_period = 1, dt = 0;
   int64_t beginstep = 0, endstep = 0;
+  int seed = 0;
   RanMarsHost rng;
   std::vector<int> order;     // tags of the owned atoms in the REFERENCE's local order (the order RanMars is consumed in)
   int sortfreq = 0;           // atom_modify sort: the reference's local order changes at every Atom::sort

@@ -33,6 +33,13 @@ B200Device *B200Device::instance(LAMMPS *lmp)
   return it->second;
 }
 
+B200Device *B200Device::peek(LAMMPS *lmp)
+{
+  auto &r = registry();
+  auto it = r.find(lmp);
+  return it == r.end() ? nullptr : it->second;
+}
+
 void B200Device::release(LAMMPS *lmp)
 {
   auto &r = registry();

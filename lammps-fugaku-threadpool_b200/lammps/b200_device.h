@@ -1,5 +1,5 @@
 /* b200_device.h -- the one device context a LAMMPS instance (one MPI rank, one GPU) owns, shared by the
-   `b200` styles: PairLJCutB200, PairEAMB200, FixNVEB200, VerletB200.  Plays the role FixGPU plays for the GPU
+   `b200` styles: PairLJCutB200, PairEAMB200, FixNVEB200, BondFENEB200, FixLangevinB200, VerletB200.  Plays the role FixGPU plays for the GPU
    package (src/GPU/fix_gpu.cpp:43-51, lmp_init_device / lmp_clear_device) and the KokkosLMP object plays for
    KOKKOS: create the device library context once, translate its status codes into error->one like
    GPU_EXTRA::check_flag (src/GPU/gpu_extra.h) does. */
@@ -17,6 +17,7 @@ class B200Device : protected Pointers {
   // the context of `lmp` (created on first use; device = local rank modulo visible GPUs, as `package gpu` picks)
   static B200Device *instance(LAMMPS *lmp);
   static void release(LAMMPS *lmp);    // drop one reference; the last one destroys the context
+  static B200Device *peek(LAMMPS *lmp);    // the context if one exists, without creating or referencing it
 
   b200md_ctx *ctx;
   int resident;       // 1 while VerletB200::run owns the atoms on the device (pair/fix host hooks are idle)

@@ -13,6 +13,7 @@
 #include "suffix.h"
 #include "update.h"
 
+#include <cstring>
 #include <vector>
 
 using namespace LAMMPS_NS;
@@ -32,8 +33,9 @@ PairLJCutB200::~PairLJCutB200()
 void PairLJCutB200::init_style()
 {
   if (!force->newton_pair && comm_forward) {}    // newton on/off both fine: the device list is a full list
-  if (atom->molecular != Atom::ATOMIC)
-    error->all(FLERR, "Pair style lj/cut/b200 currently requires atom_style atomic (no special bonds)");
+  // bonded systems (special-bond exclusion in the neighbor build) run inside the device-resident loop only
+  if (atom->molecular != Atom::ATOMIC && strcmp(update->integrate_style, "verlet/b200") != 0)
+    error->all(FLERR, "Pair style lj/cut/b200 with a bonded atom style requires run_style verlet/b200");
   // no host NeighList is requested: Neighbor still runs decide/exchange/borders, the list lives on the device
   tables_loaded = 0;
 }
@@ -59,6 +61,8 @@ void PairLJCutB200::compute(int eflag, int vflag)
   ev_init(eflag, vflag);
   if (dev->resident) return;
   if (eflag_atom || vflag_atom) error->all(FLERR, "Pair style lj/cut/b200 does not tally per-atom energy/virial");
+  if (atom->molecular != Atom::ATOMIC)
+    error->all(FLERR, "Pair style lj/cut/b200: bonded systems are served by the device-resident loop only");
   if (!tables_loaded) device_tables(dev);
 
   const int nlocal = atom->nlocal, nghost = atom->nghost;

@@ -4,9 +4,11 @@
 #include "atom.h"
 #include "atom_vec.h"
 #include "b200_device.h"
+#include "bond_fene_b200.h"
 #include "comm.h"
 #include "domain.h"
 #include "error.h"
+#include "fix_langevin_b200.h"
 #include "fix_nve_b200.h"
 #include "force.h"
 #include "modify.h"
@@ -23,7 +25,8 @@
 
 using namespace LAMMPS_NS;
 
-VerletB200::VerletB200(LAMMPS *lmp, int narg, char **arg) : Verlet(lmp, narg, arg), dev(nullptr), nve(nullptr)
+VerletB200::VerletB200(LAMMPS *lmp, int narg, char **arg) :
+    Verlet(lmp, narg, arg), dev(nullptr), nve(nullptr), bond(nullptr), langevin(nullptr), device_setup_step(-1)
 {
   dev = B200Device::instance(lmp);
 }
@@ -37,18 +40,46 @@ void VerletB200::init()
 {
   Verlet::init();
   if (domain->triclinic) error->all(FLERR, "Run style verlet/b200 requires an orthogonal box");
-  if (atom->molecular != Atom::ATOMIC) error->all(FLERR, "Run style verlet/b200 requires atom_style atomic");
   if (!force->pair || !dynamic_cast<B200PairTables *>(force->pair))
     error->all(FLERR, "Run style verlet/b200 requires a pair style with suffix b200 (lj/cut/b200, eam/b200)");
-  if (force->kspace || force->bond || force->angle) error->all(FLERR, "Run style verlet/b200: only pair interactions run on the device");
-  // exactly one time-integration fix, nve/b200 on group all; nothing else may touch atoms between output steps
+  if (force->kspace || force->angle || force->dihedral || force->improper)
+    error->all(FLERR, "Run style verlet/b200: only pair and fene bond interactions run on the device");
+  // atom_style atomic, or a bonded style whose only topology is fene/b200 bonds with special_bonds fene (in.chain)
+  bond = nullptr;
+  if (atom->molecular == Atom::TEMPLATE) error->all(FLERR, "Run style verlet/b200 does not support atom_style template");
+  if (atom->molecular == Atom::MOLECULAR) {
+    bond = dynamic_cast<BondFENEB200 *>(force->bond);
+    if (force->bond && !bond) error->all(FLERR, "Run style verlet/b200 requires bond style fene/b200");
+    if (atom->nangles || atom->ndihedrals || atom->nimpropers)
+      error->all(FLERR, "Run style verlet/b200: angles, dihedrals and impropers do not run on the device");
+    if (atom->nbonds && !bond) error->all(FLERR, "Run style verlet/b200: the system has bonds but no bond style fene/b200");
+    if (bond) {
+      const double *sl = force->special_lj;
+      if (sl[1] != 0.0 || sl[2] != 1.0 || sl[3] != 1.0)
+        error->all(FLERR, "Run style verlet/b200 requires special_bonds fene (lj 0.0 1.0 1.0) with bond style fene/b200");
+      if (!bond->all_set()) error->all(FLERR, "All bond coeffs are not set");
+      if (atom->bond_per_atom > 4) error->all(FLERR, "Run style verlet/b200 holds up to 4 bonds per atom");
+    }
+  } else if (force->bond)
+    error->all(FLERR, "Run style verlet/b200: bond style without a bonded atom style");
+  // one time-integration fix, nve/b200 on group all, and optionally one langevin/b200 thermostat; nothing else may
+  // touch atoms between output steps
   nve = nullptr;
+  langevin = nullptr;
   for (const auto &fix : modify->get_fix_list()) {
     auto *f = dynamic_cast<FixNVEB200 *>(fix);
+    auto *l = dynamic_cast<FixLangevinB200 *>(fix);
     if (f && f->igroup == 0 && !nve) nve = f;
-    else error->all(FLERR, "Run style verlet/b200 supports exactly one fix, nve/b200 on group all (found fix {} {})", fix->id, fix->style);
+    else if (l && !langevin) {
+      langevin = l;
+      if (const char *why = l->device_unsupported())
+        error->all(FLERR, "Fix langevin/b200 under run style verlet/b200 does not support {}", why);
+    } else
+      error->all(FLERR, "Run style verlet/b200 supports fix nve/b200 on group all plus one fix langevin/b200 (found fix {} {})", fix->id, fix->style);
   }
   if (!nve) error->all(FLERR, "Run style verlet/b200 requires fix nve/b200 on group all");
+  if ((bond || langevin) && comm->nprocs > 1)
+    error->all(FLERR, "Run style verlet/b200: bond style fene/b200 and fix langevin/b200 run on one rank only for now");
   if (comm->nprocs > 1) {
     // the device library places rank r at grid location (r % px, (r / px) % py, r / (px*py)) (include/b200md.h)
     const int *pg = comm->procgrid;
@@ -66,6 +97,69 @@ void VerletB200::upload()
   tables->device_tables(dev);    // also units, masses and neighbor settings
   const int n = atom->nlocal;
   B200_CHECK(dev, b200md_upload_atoms(dev->ctx, n, &atom->x[0][0], &atom->v[0][0], atom->type, atom->tag, atom->image));
+  B200_CHECK(dev, b200md_set_timestep(dev->ctx, update->ntimestep));
+  if (bond && n > 0) {
+    // Atom's bond arrays are contiguous n x bond_per_atom blocks (Memory::create); tagint is int (LAMMPS_SMALLBIG)
+    B200_CHECK(dev, b200md_set_bonds(dev->ctx, n, atom->tag, atom->bond_per_atom, atom->num_bond, &atom->bond_type[0][0],
+                                     &atom->bond_atom[0][0], force->newton_bond));
+    B200_CHECK(dev, b200md_bond_fene(dev->ctx, atom->nbondtypes, bond->dev_k(), bond->dev_r0(), bond->dev_epsilon(), bond->dev_sigma()));
+  } else
+    B200_CHECK(dev, b200md_set_bonds(dev->ctx, 0, nullptr, 0, nullptr, nullptr, nullptr, 1));
+  if (langevin) {
+    B200_CHECK(dev, b200md_fix_langevin(dev->ctx, langevin->dev_t_start(), langevin->dev_t_stop(), langevin->dev_t_period(),
+                                        langevin->dev_seed(), update->dt));
+    if (!langevin->order_sent) {
+      B200_CHECK(dev, b200md_langevin_order(dev->ctx, n, atom->tag, atom->sortfreq, atom->userbinsize));
+      langevin->order_sent = true;
+    }
+    B200_CHECK(dev, b200md_run_bounds(dev->ctx, update->beginstep, update->endstep));
+  } else
+    B200_CHECK(dev, b200md_fix_langevin(dev->ctx, 0.0, 0.0, 0.0, 0, 0.0));
+}
+
+// pair (and bond) energy / virial of the device's last tallied force evaluation -> the style objects the
+// reference's computes read (compute pe, compute pressure)
+void VerletB200::fetch_energies()
+{
+  double e = 0.0, vir[6] = {0, 0, 0, 0, 0, 0};
+  Pair *pair = force->pair;
+  B200_CHECK(dev, b200md_last_ev(dev->ctx, &e, vir));
+  pair->eng_vdwl = e;
+  pair->eng_coul = 0.0;
+  for (int k = 0; k < 6; k++) pair->virial[k] = vir[k];
+  if (bond) {
+    B200_CHECK(dev, b200md_thermo_bond(dev->ctx, &e, vir));
+    bond->energy = e;
+    for (int k = 0; k < 6; k++) bond->virial[k] = vir[k];
+  }
+  update->eflag_global = update->vflag_global = update->ntimestep;
+}
+
+// Verlet::setup (src/verlet.cpp:90-160).  Atomic systems: the stock routine.  Bonded / thermostatted systems: the
+// device does the whole setup (pbc, sort, ghosts, build, pair + bond forces, FixLangevin::setup's post_force) and the
+// result comes back for the step-0 output.
+void VerletB200::setup(int flag)
+{
+  device_setup_step = -1;
+  if (!bond && !langevin) {
+    Verlet::setup(flag);
+    return;
+  }
+  if (comm->me == 0 && screen) fputs("Setting up Verlet/b200 run on the device ...\n", screen);
+  update->setupflag = 1;
+  atom->setup();
+  ev_set(update->ntimestep);
+  upload();
+  dev->resident = 1;
+  B200_CHECK(dev, b200md_setup(dev->ctx));
+  download();
+  fetch_energies();
+  neighbor->ncalls = 0;
+  modify->setup(vflag);    // fix langevin/b200 and nve/b200 do nothing here while the device is resident
+  dev->resident = 0;
+  device_setup_step = update->ntimestep;
+  output->setup(flag);
+  update->setupflag = 0;
 }
 
 void VerletB200::download()
@@ -119,10 +213,15 @@ void VerletB200::download()
 void VerletB200::run(int n)
 {
   if (n <= 0) return;
-  upload();
-  dev->resident = 1;
-  B200_CHECK(dev, b200md_setup(dev->ctx));
-  Pair *pair = force->pair;
+  if (device_setup_step == update->ntimestep) {
+    // setup() above already put this state on the device: do not set up twice (the langevin stream would advance)
+    dev->resident = 1;
+  } else {
+    upload();
+    dev->resident = 1;
+    B200_CHECK(dev, b200md_setup(dev->ctx));
+  }
+  device_setup_step = -1;
 
   bigint done = 0;
   while (done < n) {
@@ -140,13 +239,8 @@ void VerletB200::run(int n)
     update->ntimestep += chunk;
 
     if (update->ntimestep == output->next || done == n) {
-      double e = 0.0, vir[6] = {0, 0, 0, 0, 0, 0};
       download();
-      B200_CHECK(dev, b200md_last_ev(dev->ctx, &e, vir));
-      pair->eng_vdwl = e;
-      pair->eng_coul = 0.0;
-      for (int k = 0; k < 6; k++) pair->virial[k] = vir[k];
-      update->eflag_global = update->vflag_global = update->ntimestep;
+      fetch_energies();
       timer->stamp(Timer::COMM);
       if (update->ntimestep == output->next) {
         output->write(update->ntimestep);

@@ -50,6 +50,7 @@ PROTOTYPES = {
     "b200md_setup": (_i, [_vp]),
     "b200md_run": (_i, [_vp, _i, _d, _i]),
     "b200md_timestep": (_i64, [_vp]),
+    "b200md_set_timestep": (_i, [_vp, _i64]),
     "b200md_step_host": (_i, [_vp, _d, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "b200md_host_atoms": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _i]),
     "b200md_host_forces": (_i, [_vp, _vp, _i]),

@@ -256,3 +256,104 @@ def test_thin_box_is_refused_by_the_resident_loop(tmp_path):
     r = run_lmp(LMP_B200, text, tmp_path, ["-sf", "b200"])
     assert r.returncode != 0
     assert "thinner than the ghost cutoff" in (r.stdout + r.stderr)
+
+
+# ---- bench/in.chain (BASELINE configs[2]) through the reference hosting the b200 styles ----
+IN_CHAIN = """units lj
+atom_style bond
+special_bonds fene
+read_data data.chain
+neighbor 0.4 bin
+neigh_modify every 1 delay 1
+bond_style {bond}
+bond_coeff 1 30.0 1.5 1.0 1.0
+pair_style lj/cut 1.12
+pair_modify shift yes
+pair_coeff 1 1 1.0 1.0 1.12
+fix 1 all {nve}
+fix 2 all {langevin} 1.0 1.0 10.0 904297
+thermo {thermo}
+thermo_modify format float %.15g
+timestep 0.012
+run {steps}
+"""
+
+
+def write_data_chain(g, path):
+    """tests/golden/chain_32k.npz (the reference's read_data of bench/data.chain, dumped by
+    tests/golden/make_chain_golden.py) back into a data file, 17 significant digits"""
+    n, nb = len(g["in_tag"]), len(g["in_bonds"])
+    lines = ["LAMMPS data file (tests/golden/chain_32k.npz <- bench/data.chain)", "", f"{n} atoms", f"{nb} bonds", "",
+             "1 atom types", "1 bond types", ""]
+    for k, ax in enumerate("xyz"):
+        lines.append(f"{g['in_boxlo'][k]:.17g} {g['in_boxhi'][k]:.17g} {ax}lo {ax}hi")
+    lines += ["", "Masses", "", "1 1.0", "", "Atoms # bond", ""]
+    for i in range(n):
+        x, im = g["in_x"][i], g["in_image"][i]
+        lines.append(f"{g['in_tag'][i]} {g['in_mol'][i]} {g['in_type'][i]} {x[0]:.17g} {x[1]:.17g} {x[2]:.17g} {im[0]} {im[1]} {im[2]}")
+    lines += ["", "Velocities", ""]
+    for i in range(n):
+        v = g["in_v"][i]
+        lines.append(f"{g['in_tag'][i]} {v[0]:.17g} {v[1]:.17g} {v[2]:.17g}")
+    lines += ["", "Bonds", ""]
+    for k, (t, a, b) in enumerate(g["in_bonds"]):
+        lines.append(f"{k + 1} {t} {a} {b}")
+    path.write_text("\n".join(lines) + "\n")
+
+
+def test_chain_data_file_round_trip_and_b200_host_styles(tmp_path):
+    """(1) the data file regenerated from the golden reproduces the golden's own reference thermo (minted from
+    bench/data.chain itself) digit for digit, so GPU-box runs need no /root/reference; (2) bond fene/b200,
+    fix langevin/b200 and fix nve/b200 under the stock loop with a host pair style ARE the reference's classes:
+    identical thermo over 20 steps"""
+    build_host()
+    g = dict(np.load(ROOT / "tests" / "golden" / "chain_32k.npz"))
+    write_data_chain(g, tmp_path / "data.chain")
+    plain = dict(bond="fene", nve="nve", langevin="langevin")
+    ref0 = run_lmp(LMP_REF, IN_CHAIN.format(thermo=100, steps=0, **plain), tmp_path)
+    assert ref0.returncode == 0, ref0.stdout[-2000:]
+    r0 = thermo_rows(ref0.stdout)[0]   # Step Temp E_pair E_mol TotEng Press, per atom in lj units
+    n = len(g["in_tag"])
+    evdwl, ebond, ke, temp, press = g["a_thermo"]
+    np.testing.assert_allclose(r0[1:], [temp, evdwl / n, ebond / n, (evdwl + ebond + ke) / n, press], rtol=2e-14)
+    ref = run_lmp(LMP_REF, IN_CHAIN.format(thermo=10, steps=20, **plain), tmp_path)
+    got = run_lmp(LMP_B200, IN_CHAIN.format(thermo=10, steps=20, bond="fene/b200", nve="nve/b200", langevin="langevin/b200"), tmp_path)
+    assert ref.returncode == 0 and got.returncode == 0, got.stdout[-2000:] + got.stderr[-2000:]
+    R, G = thermo_rows(ref.stdout), thermo_rows(got.stdout)
+    assert R.shape == (3, 6)
+    np.testing.assert_array_equal(R, G)
+
+
+def test_chain_with_suffix_fails_loudly_without_device(tmp_path):
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    build_host()
+    g = dict(np.load(ROOT / "tests" / "golden" / "chain_32k.npz"))
+    write_data_chain(g, tmp_path / "data.chain")
+    r = run_lmp(LMP_B200, IN_CHAIN.format(thermo=100, steps=100, bond="fene", nve="nve", langevin="langevin"), tmp_path, ["-sf", "b200"])
+    assert r.returncode != 0
+    assert "no CPU fallback" in (r.stdout + r.stderr)
+
+
+@FIRST_RUN
+@pytest.mark.gpu
+def test_chain_thermo_matches_reference(tmp_path):
+    """bench/in.chain as shipped with `-sf b200`: pair lj/cut/b200 + bond fene/b200 + fix nve/b200 + fix
+    langevin/b200 inside run_style verlet/b200 (bonded neighbor build, FENE kernel, RanMars replay) against
+    lmp_ref on the same data file: Temp, E_pair, E_mol, TotEng, Press at steps 0 and 100 within 1e-6"""
+    if not LMP_B200.exists() or not LMP_REF.exists():
+        pytest.skip("oracle/_ref host binaries not shipped")
+    g = dict(np.load(ROOT / "tests" / "golden" / "chain_32k.npz"))
+    write_data_chain(g, tmp_path / "data.chain")
+    text = IN_CHAIN.format(thermo=100, steps=100, bond="fene", nve="nve", langevin="langevin")
+    ref = run_lmp(LMP_REF, text, tmp_path)
+    got = run_lmp(LMP_B200, text, tmp_path, ["-sf", "b200"])
+    assert ref.returncode == 0, ref.stdout[-2000:]
+    assert got.returncode == 0, got.stdout[-3000:] + got.stderr[-2000:]
+    R, G = thermo_rows(ref.stdout), thermo_rows(got.stdout)
+    assert R.shape == G.shape == (2, 6), (R.shape, G.shape, got.stdout[-2000:])
+    np.testing.assert_allclose(G[:, 1:], R[:, 1:], rtol=1e-6)
+    np.testing.assert_allclose(G[0, 1:], R[0, 1:], rtol=1e-10)
+    assert "Neighbor list builds = 25" in got.stdout
