@@ -36,6 +36,7 @@ void PairLJCutB200::init_style()
   // bonded systems (special-bond exclusion in the neighbor build) run inside the device-resident loop only
   if (atom->molecular != Atom::ATOMIC && strcmp(update->integrate_style, "verlet/b200") != 0)
     error->all(FLERR, "Pair style lj/cut/b200 with a bonded atom style requires run_style verlet/b200");
+  cut_respa = nullptr;    // PairLJCut::init_style sets it (its constructor does not); init_one reads it
   // no host NeighList is requested: Neighbor still runs decide/exchange/borders, the list lives on the device
   tables_loaded = 0;
 }

@@ -71,9 +71,7 @@ void VerletB200::init()
     auto *l = dynamic_cast<FixLangevinB200 *>(fix);
     if (f && f->igroup == 0 && !nve) nve = f;
     else if (l && !langevin) {
-      langevin = l;
-      if (const char *why = l->device_unsupported())
-        error->all(FLERR, "Fix langevin/b200 under run style verlet/b200 does not support {}", why);
+      langevin = l;    // its keywords are checked in upload(): FixLangevin::init has not run yet (Update before Modify)
     } else
       error->all(FLERR, "Run style verlet/b200 supports fix nve/b200 on group all plus one fix langevin/b200 (found fix {} {})", fix->id, fix->style);
   }
@@ -106,6 +104,8 @@ void VerletB200::upload()
   } else
     B200_CHECK(dev, b200md_set_bonds(dev->ctx, 0, nullptr, 0, nullptr, nullptr, nullptr, 1));
   if (langevin) {
+    if (const char *why = langevin->device_unsupported())
+      error->all(FLERR, "Fix langevin/b200 under run style verlet/b200 does not support {}", why);
     B200_CHECK(dev, b200md_fix_langevin(dev->ctx, langevin->dev_t_start(), langevin->dev_t_stop(), langevin->dev_t_period(),
                                         langevin->dev_seed(), update->dt));
     if (!langevin->order_sent) {

@@ -6,6 +6,7 @@
 #undef blockDim
 #undef gridDim
 
+#include <execinfo.h>
 #include <signal.h>
 #include <stdio.h>
 #include <sys/mman.h>
@@ -28,6 +29,8 @@ static void on_segv(int, siginfo_t *si, void *)
   char msg[160];
   int n = snprintf(msg, sizeof msg, "\ncudaemu: invalid memory access at %p (out-of-bounds device access or a host bug)\n", si->si_addr);
   if (write(2, msg, n) < 0) {}
+  void *bt[48];
+  backtrace_symbols_fd(bt, backtrace(bt, 48), 2);
   _exit(139);
 }
 

@@ -253,6 +253,8 @@ def test_thin_box_is_refused_by_the_resident_loop(tmp_path):
     write_data_metal(g, tmp_path / "data.metal")
     text = IN_UNITTEST_EAM.format(units="metal", al=ROOT / "tests" / "golden" / "Al_jnp.eam",
                                   cu=ROOT / "tests" / "golden" / "Cu_u3_units.eam", runstyle="")
+    # the resident loop wants its integration fix from the first run on
+    text = text.replace("run 0 post no", "fix 0 all nve\nrun 0 post no\nunfix 0", 1)
     r = run_lmp(LMP_B200, text, tmp_path, ["-sf", "b200"])
     assert r.returncode != 0
     assert "thinner than the ghost cutoff" in (r.stdout + r.stderr)
