@@ -15,6 +15,7 @@ ROOT = HERE.parents[1]
 CSRC = ROOT / "lammps-fugaku-threadpool_b200" / "csrc"
 OUT = HERE / "_build"
 LIB = OUT / "libb200md_emu.so"
+FAKE_NCCL = OUT / "libnccl_emu.so"
 
 
 def _match_back(text: str, end: int) -> int:
@@ -108,13 +109,15 @@ def rewrite(text: str, name: str) -> str:
     text = re.sub(r'asm\("rcp\.approx\.ftz\.f64[^;]*;"[^;]*;', "y = 1.0 / x;", text)
     if "asm(" in text or "asm volatile" in text:
         raise RuntimeError(f"{name}: inline PTX the emulation does not know")
+    # comm.cu binds NCCL by dlopen: hand it the in-process stand-in for emulated ranks (threads) instead
+    text = text.replace('{"libnccl.so.2", "libnccl.so"}', '{"%s", "%s"}' % (FAKE_NCCL, FAKE_NCCL))
     return rewrite_launches(text)
 
 
 def build(verbose: bool = False) -> Path:
     OUT.mkdir(exist_ok=True)
     srcs = sorted(CSRC.glob("*.cu"))
-    deps = srcs + sorted(CSRC.glob("*.cuh")) + [HERE / "cuda_runtime.h", HERE / "emu.cpp", HERE / "nccl.h", Path(__file__),
+    deps = srcs + sorted(CSRC.glob("*.cuh")) + [HERE / "cuda_runtime.h", HERE / "emu.cpp", HERE / "nccl.h", HERE / "fake_nccl.cpp", Path(__file__),
                                                 ROOT / "include" / "b200md.h"]
     if LIB.exists() and all(LIB.stat().st_mtime > d.stat().st_mtime for d in deps):
         return LIB
@@ -147,7 +150,8 @@ def build(verbose: bool = False) -> Path:
             print(out)
     if bad:
         raise RuntimeError("cudaemu build failed")
-    subprocess.check_call(["g++", "-shared", "-o", str(LIB), *map(str, objs), str(emu_o), "-ldl"])
+    subprocess.check_call(["g++", "-O1", "-g", "-std=c++17", "-fPIC", "-shared", "-pthread", str(HERE / "fake_nccl.cpp"), "-o", str(FAKE_NCCL)])
+    subprocess.check_call(["g++", "-shared", "-pthread", "-o", str(LIB), *map(str, objs), str(emu_o), "-ldl"])
     return LIB
 
 

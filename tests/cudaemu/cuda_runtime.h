@@ -7,7 +7,7 @@
 // GPU tests run on the box.  It says nothing about performance and is not bit-identical to the device (no FMA
 // contraction here, exact reciprocal instead of the MUFU seed); parity claims rest on the -m gpu tests only.
 //
-// Execution model: one OS thread; every CUDA thread of a block is a fiber (emu.cpp); blocks run one after the
+// Execution model: per host thread (= per emulated rank) one scheduler; every CUDA thread of a block is a fiber (emu.cpp); blocks run one after the
 // other.  __syncthreads and the *_sync warp primitives are real rendezvous between fibers, exited threads count as
 // arrived.  "Device" memory is host memory between PROT_NONE guard pages (end-aligned), so an out-of-bounds device
 // access faults instead of passing silently.  Streams and events are no-ops: every call completes before it returns.
@@ -26,7 +26,7 @@
 #define __host__
 #define __forceinline__ inline
 #define __launch_bounds__(...)
-#define __shared__ static
+#define __shared__ static thread_local   /* one block at a time per host thread (= per emulated rank) */
 #ifndef __restrict__
 #define __restrict__ __restrict
 #endif
@@ -67,11 +67,11 @@ void launch(dim3 grid, dim3 block, size_t smem, const std::function<void()> &bod
 void block_barrier();
 void warp_barrier();
 struct ThreadState { uint3 threadIdx, blockIdx; dim3 blockDim, gridDim; int lane, warp; };
-extern ThreadState *cur;
+extern thread_local ThreadState *cur;
 extern unsigned long long *warp_scratch();   // [32] of the running thread's warp
 extern unsigned warp_livemask();             // lanes of the running thread's warp that have not exited
-extern void *dyn_smem;
-extern int launches;
+extern thread_local void *dyn_smem;
+extern thread_local int launches;
 }    // namespace emu
 
 #define threadIdx (emu::cur->threadIdx)
@@ -81,7 +81,7 @@ extern int launches;
 
 static inline const char *cudaGetErrorString(cudaError_t e) { return e == cudaSuccess ? "no error" : "emulated CUDA error"; }
 static inline cudaError_t cudaGetLastError() { return cudaSuccess; }
-static inline cudaError_t cudaGetDeviceCount(int *n) { *n = 1; return cudaSuccess; }
+static inline cudaError_t cudaGetDeviceCount(int *n) { *n = 64; return cudaSuccess; }   // one emulated device per host thread
 static inline cudaError_t cudaSetDevice(int) { return cudaSuccess; }
 static inline cudaError_t cudaGetDeviceProperties(cudaDeviceProp *p, int)
 {

@@ -14,13 +14,15 @@
 #include <unistd.h>
 
 #include <map>
+#include <mutex>
 #include <vector>
 
 namespace emu {
 
 // ---- guarded "device" memory: [PROT_NONE page][ ... payload, end-aligned ][PROT_NONE page] -------------------
 struct Alloc { char *base; size_t map_bytes; };
-static std::map<void *, Alloc> g_allocs;
+static std::map<void *, Alloc> g_allocs;   // shared by the emulated ranks (a context may be closed from another thread)
+static std::mutex g_alloc_mutex;
 static const size_t PAGE = 4096;
 static bool g_handler = false;
 
@@ -36,6 +38,8 @@ static void on_segv(int, siginfo_t *si, void *)
 
 void *dev_alloc(size_t bytes)
 {
+  static std::mutex handler_mutex;
+  std::unique_lock<std::mutex> hl(handler_mutex);
   if (!g_handler) {
     // the handler runs on a fiber's stack; give it its own so a fiber stack overflow is reported too
     static char altstack[1 << 16];
@@ -51,6 +55,7 @@ void *dev_alloc(size_t bytes)
     sigaction(SIGSEGV, &sa, nullptr);
     g_handler = true;
   }
+  hl.unlock();
   if (bytes == 0) bytes = 1;
   const size_t payload = (bytes + 7) / 8 * 8;                 // keep 8-byte alignment of the start
   const size_t pages = (payload + PAGE - 1) / PAGE;
@@ -61,6 +66,7 @@ void *dev_alloc(size_t bytes)
   mprotect(base + (pages + 1) * PAGE, PAGE, PROT_NONE);
   char *p = base + (pages + 1) * PAGE - payload;
   memset(p, 0xCD, payload);                                   // uninitialised device memory is not zero
+  std::lock_guard<std::mutex> lock(g_alloc_mutex);
   g_allocs[p] = {base, map_bytes};
   return p;
 }
@@ -68,6 +74,7 @@ void *dev_alloc(size_t bytes)
 void dev_free(void *p)
 {
   if (!p) return;
+  std::lock_guard<std::mutex> lock(g_alloc_mutex);
   auto it = g_allocs.find(p);
   if (it == g_allocs.end()) {
     fprintf(stderr, "cudaemu: cudaFree of a pointer cudaMalloc did not return (%p)\n", p);
@@ -123,9 +130,9 @@ struct Fiber {
   unsigned wait_val = 0;
 };
 static const size_t STACK = 128 * 1024;
-static std::vector<Fiber *> g_fibers;
-static ucontext_t g_sched;
-static void *g_sched_sp = nullptr;
+static thread_local std::vector<Fiber *> g_fibers;
+static thread_local ucontext_t g_sched;
+static thread_local void *g_sched_sp = nullptr;
 static inline void to_sched(Fiber *f)
 {
 #if EMU_ASM_SWITCH
@@ -142,16 +149,16 @@ static inline void to_fiber(Fiber *f)
   swapcontext(&g_sched, &f->ctx);
 #endif
 }
-static Warp g_warps[32];
-static int g_block_live = 0, g_block_count = 0;
-static unsigned g_block_gen = 0;
-static const std::function<void()> *g_body = nullptr;
-static Fiber *g_cur = nullptr;
-static ThreadState g_host_ts;
-ThreadState *cur = &g_host_ts;
-void *dyn_smem = nullptr;
-int launches = 0;
-static std::vector<char> g_smem;
+static thread_local Warp g_warps[32];
+static thread_local int g_block_live = 0, g_block_count = 0;
+static thread_local unsigned g_block_gen = 0;
+static thread_local const std::function<void()> *g_body = nullptr;
+static thread_local Fiber *g_cur = nullptr;
+static thread_local ThreadState g_host_ts;
+thread_local ThreadState *cur = nullptr;   // the host thread's own state until a kernel thread runs
+thread_local void *dyn_smem = nullptr;
+thread_local int launches = 0;
+static thread_local std::vector<char> g_smem;
 
 unsigned long long *warp_scratch() { return g_warps[cur->warp].scratch; }
 unsigned warp_livemask() { return g_warps[cur->warp].livemask; }
@@ -205,7 +212,7 @@ static void trampoline()
 
 void launch(dim3 grid, dim3 block, size_t smem, const std::function<void()> &body)
 {
-  if (cur != &g_host_ts) {
+  if (cur != nullptr && cur != &g_host_ts) {
     fprintf(stderr, "cudaemu: kernel launch from inside a kernel\n");
     abort();
   }

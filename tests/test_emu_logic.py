@@ -180,3 +180,138 @@ def test_emu_lammps_chain(emu_lmp, tmp_path):
     """bench/in.chain with -sf b200 end to end through the glue: VerletB200::setup on the device, bond fene/b200,
     fix langevin/b200, energies published to the reference's computes"""
     lh.test_chain_thermo_matches_reference(tmp_path)
+
+
+# ---- several ranks: threads of this process, one emulated device each, NCCL stand-in (tests/cudaemu/fake_nccl.cpp) ----
+import threading  # noqa: E402
+
+
+class _AllSum:
+    def __init__(self, n):
+        self.n, self.bar, self.parts, self.lock = n, threading.Barrier(n, timeout=300), {}, threading.Lock()
+
+    def __call__(self, rank, a):
+        a = np.ascontiguousarray(a, dtype=np.float64)
+        with self.lock:
+            self.parts[rank] = a
+        self.bar.wait()
+        tot = sum(self.parts[r] for r in range(self.n))
+        self.bar.wait()
+        return tot
+
+
+def run_decomposed_emu(pkg, world, grid, kind, cells, steps, host_steps=0):
+    """tests/multirank_util._worker with threads for ranks; optionally `host_steps` more steps through
+    b200md_step_host (the bench's e2e leg: atoms migrate between ranks at its rebuilds)"""
+    import bench
+
+    allsum, res, errs = _AllSum(world), [None] * world, []
+    nccl_id = pkg.lib.nccl_unique_id()
+
+    def worker(rank):
+        try:
+            loc = (rank % grid[0], (rank // grid[0]) % grid[1], rank // (grid[0] * grid[1]))
+            x, v, tag, box, natoms = bench.make_atoms(pkg, kind, cells, grid, loc, lambda a: allsum(rank, a))
+            md = bench.make_system(pkg, kind, rank, world, rank, nccl_id, grid)
+            md.box([0, 0, 0], box)
+            md.create_atoms(x, v, np.ones(len(x), dtype=np.int32), tag, natoms_total=natoms)
+            md.setup()
+            t0 = md.thermo_log[-1]
+            numneigh, _ = md.neighbor_list()
+            out = dict(box=np.array(box), nneigh0=int(numneigh.sum()), thermo0=np.array([t0["pe"], t0["ke"], t0["press"]]))
+            md.run(steps)
+            t1 = md.thermo_log[-1]
+            g = md.gather()
+            st = md.neigh_stats()
+            out.update(thermo1=np.array([t1["pe"], t1["ke"], t1["press"]]), x1=g["x"], tag1=g["tag"], builds=st["builds"],
+                       nlocal1=md.nlocal)
+            if host_steps:
+                n = md.nlocal
+                cap = n + n // 8 + 64
+                hx, hv, hf = np.zeros((cap, 3)), np.zeros((cap, 3)), np.zeros((cap, 3))
+                htag = np.zeros(cap, dtype=np.int32)
+                vp = lambda a: a.ctypes.data_as(C.c_void_p)
+                md.ctx.call("b200md_download_atoms", vp(hx), vp(hv), None, None, None, None)
+                nout, seen = C.c_int(0), set()
+                for _ in range(host_steps):
+                    md.ctx.call("b200md_step_host", md.dt, 0, 0, cap, vp(hx), vp(hv), vp(hf), vp(htag), C.byref(nout), None, None)
+                    seen.add(nout.value)
+                out.update(hx=hx[:nout.value].copy(), htag=htag[:nout.value].copy(), nlocal_seen=sorted(seen),
+                           builds2=md.neigh_stats()["builds"])
+            md.close()
+            res[rank] = out
+        except BaseException as e:  # noqa: BLE001
+            errs.append((rank, e))
+            allsum.bar.abort()
+            raise
+
+    th = [threading.Thread(target=worker, args=(r,)) for r in range(world)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not errs, errs
+    return res
+
+
+@pytest.mark.parametrize("kind,world,grid,cells,steps", [
+    ("lj", 2, (2, 1, 1), 6, 60),
+    ("eam", 2, (2, 1, 1), 6, 40),
+    ("lj", 4, (2, 2, 1), 6, 60),
+    ("eam", 8, (2, 2, 2), 5, 40),
+])
+def test_emu_decomposed_equals_single(emu, kind, world, grid, cells, steps):
+    """the body of tests/test_gpu_multirank.py::test_decomposed_equals_single_gpu on emulated ranks"""
+    import test_gpu_multirank as mr
+
+    res = run_decomposed_emu(emu, world, grid, kind, cells, steps)
+    tot = tuple(cells * g for g in grid)
+    t0, t1, g, nn, st = mr._single(emu, kind, tot, steps)
+    assert sum(r["nneigh0"] for r in res) == nn
+    np.testing.assert_allclose(res[0]["thermo0"], [t0["pe"], t0["ke"], t0["press"]], rtol=1e-10)
+    np.testing.assert_allclose(res[0]["thermo1"], [t1["pe"], t1["ke"], t1["press"]], rtol=1e-6)
+    assert all(r["builds"] == st["builds"] for r in res)
+    tag = np.concatenate([r["tag1"] for r in res])
+    x = np.concatenate([r["x1"] for r in res])
+    assert sorted(tag.tolist()) == list(range(1, len(g["tag"]) + 1))
+    o = np.argsort(tag)
+    dx = x[o] - g["x"]
+    dx -= res[0]["box"] * np.round(dx / res[0]["box"])
+    assert np.abs(dx).max() < 1e-6
+
+
+@pytest.mark.parametrize("kind,world,grid,cells,steps,host_steps", [
+    ("eam", 4, (2, 2, 1), 5, 10, 40),
+    ("eam", 8, (2, 2, 2), 5, 10, 40),
+    ("lj", 8, (2, 2, 2), 5, 10, 50),
+])
+def test_emu_host_buffer_step_with_migration(emu, kind, world, grid, cells, steps, host_steps):
+    """bench.py's e2e leg on several ranks: b200md_step_host through rebuilds at which atoms change rank (the leg that
+    failed on 4 and 8 B200s in round 1 with stale atom counts).  The owned count must really change on some rank,
+    no atom may be lost or doubled, and the trajectory must follow the single-rank run of the same total length."""
+    import test_gpu_multirank as mr
+
+    res = run_decomposed_emu(emu, world, grid, kind, cells, steps, host_steps=host_steps)
+    tot = tuple(cells * g for g in grid)
+    _, _, g, _, st = mr._single(emu, kind, tot, steps + host_steps)
+    tag = np.concatenate([r["htag"] for r in res])
+    x = np.concatenate([r["hx"] for r in res])
+    assert sorted(tag.tolist()) == list(range(1, len(g["tag"]) + 1))
+    assert any(len(r["nlocal_seen"]) > 1 for r in res), "no migration happened: the case does not test what it claims"
+    assert all(r["builds2"] == st["builds"] for r in res)
+    o = np.argsort(tag)
+    dx = x[o] - g["x"]
+    dx -= res[0]["box"] * np.round(dx / res[0]["box"])
+    assert np.abs(dx).max() < 1e-6
+
+
+@pytest.mark.parametrize("kind,world,grid,cells,steps", [("lj", 4, (2, 2, 1), 6, 45), ("eam", 8, (2, 2, 2), 5, 30)])
+def test_emu_decomposed_overlap_equals_plain(emu, kind, world, grid, cells, steps, monkeypatch):
+    """B200MD_OVERLAP=1 on several ranks (where the halo it hides is an NCCL exchange): same trajectory, bit for bit"""
+    monkeypatch.delenv("B200MD_OVERLAP", raising=False)
+    a = run_decomposed_emu(emu, world, grid, kind, cells, steps)
+    monkeypatch.setenv("B200MD_OVERLAP", "1")
+    b = run_decomposed_emu(emu, world, grid, kind, cells, steps)
+    for ra, rb in zip(a, b):
+        assert np.array_equal(ra["tag1"], rb["tag1"]) and np.array_equal(ra["x1"], rb["x1"])
+        assert np.array_equal(ra["thermo1"], rb["thermo1"]) and ra["builds"] == rb["builds"]
