@@ -130,7 +130,13 @@ struct Fiber {
   unsigned wait_val = 0;
 };
 static const size_t STACK = 128 * 1024;
-static thread_local std::vector<Fiber *> g_fibers;
+// fiber stacks are mappings: give them back when the emulated rank's thread ends (the map count of a process is limited)
+struct FiberPool {
+  std::vector<Fiber *> v;
+  ~FiberPool();
+};
+static thread_local FiberPool g_pool;
+#define g_fibers (g_pool.v)
 static thread_local ucontext_t g_sched;
 static thread_local void *g_sched_sp = nullptr;
 static inline void to_sched(Fiber *f)
@@ -210,6 +216,14 @@ static void trampoline()
   abort();    // a finished fiber is never resumed
 }
 
+FiberPool::~FiberPool()
+{
+  for (Fiber *f : v) {
+    if (f->stack) munmap(f->stack, STACK + PAGE);
+    delete f;
+  }
+}
+
 void launch(dim3 grid, dim3 block, size_t smem, const std::function<void()> &body)
 {
   if (cur != nullptr && cur != &g_host_ts) {
@@ -229,6 +243,10 @@ void launch(dim3 grid, dim3 block, size_t smem, const std::function<void()> &bod
   while ((int) g_fibers.size() < nthreads) {
     Fiber *f = new Fiber();
     f->stack = (char *) mmap(nullptr, STACK + PAGE, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0);
+    if (f->stack == MAP_FAILED) {
+      fprintf(stderr, "cudaemu: cannot map a fiber stack\n");
+      abort();
+    }
     mprotect(f->stack, PAGE, PROT_NONE);   // stack overflow faults
     g_fibers.push_back(f);
   }

@@ -29,20 +29,25 @@ struct Shared {
   unsigned gen = 0;
   std::map<std::pair<int, int>, std::deque<std::vector<char>>> mail;   // (src, dst) -> messages in posting order
   std::vector<std::vector<char>> stage;
-  void barrier()
+  bool broken = false;
+  // false = the communicator is broken (a rank failed, or did not show up): every caller gets an error, nobody hangs
+  bool barrier()
   {
     std::unique_lock<std::mutex> l(m);
+    if (broken) return false;
     const unsigned g = gen;
     if (++arrived == nranks) {
       arrived = 0;
       gen++;
       cv.notify_all();
-      return;
+      return true;
     }
-    if (!cv.wait_for(l, std::chrono::seconds(120), [&] { return gen != g; })) {
+    if (!cv.wait_for(l, std::chrono::seconds(120), [&] { return gen != g || broken; })) {
       fprintf(stderr, "fake nccl: %d of %d ranks reached a collective within 120 s -- another rank failed or took a different path\n", arrived, nranks);
-      abort();
+      broken = true;
+      cv.notify_all();
     }
+    return !broken;
   }
 };
 struct Comm { Shared *s; int rank; };
@@ -64,7 +69,7 @@ ncclResult_t flush()
     for (const Op &o : t_ops)
       if (o.send) s->mail[{me, o.peer}].emplace_back((const char *) o.buf, (const char *) o.buf + o.bytes);
   }
-  s->barrier();
+  if (!s->barrier()) return ncclUnhandledCudaError;
   {
     std::lock_guard<std::mutex> l(s->m);
     for (const Op &o : t_ops)
@@ -73,13 +78,16 @@ ncclResult_t flush()
         if (q.empty() || q.front().size() != o.bytes) {
           fprintf(stderr, "fake nccl: rank %d expects %zu bytes from rank %d, %s\n", me, o.bytes, o.peer,
                   q.empty() ? "nothing was sent" : "a message of another size was sent");
-          abort();
+          s->broken = true;
+          s->cv.notify_all();
+          t_ops.clear();
+          return ncclUnhandledCudaError;
         }
         memcpy(o.buf, q.front().data(), o.bytes);
         q.pop_front();
       }
   }
-  s->barrier();
+  if (!s->barrier()) return ncclUnhandledCudaError;
   t_ops.clear();
   return ncclSuccess;
 }
@@ -111,11 +119,21 @@ ncclResult_t ncclCommInitRank(Comm **comm, int nranks, ncclUniqueId id, int rank
   }
   if (s->nranks != nranks || rank < 0 || rank >= nranks) return ncclInvalidArgument;
   *comm = new Comm{s, rank};
-  s->barrier();
+  if (!s->barrier()) return ncclUnhandledCudaError;
   return ncclSuccess;
 }
 ncclResult_t ncclCommDestroy(Comm *c) { delete c; return ncclSuccess; }
-const char *ncclGetErrorString(ncclResult_t r) { return r == ncclSuccess ? "no error" : "fake nccl error"; }
+const char *ncclGetErrorString(ncclResult_t r) { return r == ncclSuccess ? "no error" : "fake nccl: communicator broken (a rank failed or did not arrive)"; }
+// test harness: a rank died outside the library; release everybody who waits for it
+void fake_nccl_break_all()
+{
+  std::lock_guard<std::mutex> l(g_m);
+  for (auto &kv : g_comms) {
+    std::lock_guard<std::mutex> l2(kv.second->m);
+    kv.second->broken = true;
+    kv.second->cv.notify_all();
+  }
+}
 ncclResult_t ncclGroupStart() { t_depth++; return ncclSuccess; }
 ncclResult_t ncclGroupEnd() { return --t_depth == 0 ? flush() : ncclSuccess; }
 ncclResult_t ncclSend(const void *buf, size_t count, ncclDataType_t t, int peer, Comm *c, cudaStream_t)
@@ -136,12 +154,12 @@ ncclResult_t ncclAllGather(const void *sbuf, void *rbuf, size_t count, ncclDataT
     std::lock_guard<std::mutex> l(s->m);
     s->stage[c->rank].assign((const char *) sbuf, (const char *) sbuf + bytes);
   }
-  s->barrier();
+  if (!s->barrier()) return ncclUnhandledCudaError;
   for (int r = 0; r < s->nranks; r++) {
-    if (s->stage[r].size() != bytes) { fprintf(stderr, "fake nccl: all-gather sizes differ between ranks\n"); abort(); }
+    if (s->stage[r].size() != bytes) { fprintf(stderr, "fake nccl: all-gather sizes differ between ranks\n"); return ncclUnhandledCudaError; }
     memcpy((char *) rbuf + (size_t) r * bytes, s->stage[r].data(), bytes);
   }
-  s->barrier();
+  if (!s->barrier()) return ncclUnhandledCudaError;
   return ncclSuccess;
 }
 ncclResult_t ncclAllReduce(const void *sbuf, void *rbuf, size_t count, ncclDataType_t t, ncclRedOp_t op, Comm *c, cudaStream_t)
@@ -153,7 +171,7 @@ ncclResult_t ncclAllReduce(const void *sbuf, void *rbuf, size_t count, ncclDataT
     std::lock_guard<std::mutex> l(s->m);
     s->stage[c->rank].assign((const char *) sbuf, (const char *) sbuf + bytes);
   }
-  s->barrier();
+  if (!s->barrier()) return ncclUnhandledCudaError;
   for (size_t k = 0; k < count; k++) {
     if (t == ncclDouble) {
       double acc = 0.0;   // rank order, the same on every rank
@@ -165,7 +183,7 @@ ncclResult_t ncclAllReduce(const void *sbuf, void *rbuf, size_t count, ncclDataT
       ((int *) rbuf)[k] = acc;
     }
   }
-  s->barrier();
+  if (!s->barrier()) return ncclUnhandledCudaError;
   return ncclSuccess;
 }
 }

@@ -186,6 +186,12 @@ def test_emu_lammps_chain(emu_lmp, tmp_path):
 import threading  # noqa: E402
 
 
+def emu_build_dir():
+    import build as emu_build
+
+    return emu_build.OUT
+
+
 class _AllSum:
     def __init__(self, n):
         self.n, self.bar, self.parts, self.lock = n, threading.Barrier(n, timeout=300), {}, threading.Lock()
@@ -242,7 +248,9 @@ def run_decomposed_emu(pkg, world, grid, kind, cells, steps, host_steps=0):
             res[rank] = out
         except BaseException as e:  # noqa: BLE001
             errs.append((rank, e))
+            print(f"emulated rank {rank} failed: {e!r}", file=sys.stderr, flush=True)  # the others will time out in a collective
             allsum.bar.abort()
+            C.CDLL(str(Path(emu_build_dir()) / "libnccl_emu.so")).fake_nccl_break_all()
             raise
 
     th = [threading.Thread(target=worker, args=(r,)) for r in range(world)]
