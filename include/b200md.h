@@ -237,6 +237,15 @@ int b200md_langevin_order(b200md_ctx *ctx, int n, const int *tag, int sortfreq, 
  * temperature ramp, FixLangevin::compute_target :773-787); unset = each b200md_run call is a whole run */
 int b200md_run_bounds(b200md_ctx *ctx, int64_t beginstep, int64_t endstep);
 
+/* random numbers of the thermostat: 0 (default) = the reference's RanMars stream replayed on the host in the
+ * reference's atom order (one rank; reproduces the reference's trajectory), 1 = counter-based on the device:
+ * Philox4x32-10 keyed by the seed with counter (tag, timestep) -- any number of ranks, no per-step host work,
+ * results independent of rank count and atom order; statistically equivalent, not stream-compatible. */
+int b200md_langevin_rng(b200md_ctx *ctx, int mode);
+/* host only (no context, no device): u[3] of atom `tag` on timestep `step` in counter mode; a raw
+ * Philox4x32-10 block for known-answer tests */
+int b200md_langevin_counter_uniforms(int seed, int tag, int64_t step, double *u);
+int b200md_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]);
 /* RanMars(seed)->uniform() x n (src/random_mars.cpp:30-100): the stream b200md_fix_langevin draws from.
  * Host only: needs neither a context nor a device. */
 int b200md_ranmars(int seed, int n, double *out);

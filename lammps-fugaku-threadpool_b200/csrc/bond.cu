@@ -109,6 +109,51 @@ __global__ void k_langevin(const double4 *__restrict__ pos, const int *__restric
   fz[i] = __dadd_rn(fz[i], __dadd_rn(fdrag2, fran2));
 }
 
+// ---- counter-based mode: Philox4x32-10 (Salmon et al., SC'11) keyed by the fix's seed, counter = (tag, timestep) ----
+// The three numbers of an atom depend on nothing but (seed, tag, step): independent of the rank count, of the atom
+// order and of how a run is split into calls; no host work and no copy per step.  Statistically equivalent to the
+// reference's thermostat, not stream-compatible with it (that is what the replay mode above is for).
+__host__ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1,
+                                                       uint32_t out[4])
+{
+#pragma unroll
+  for (int r = 0; r < 10; r++) {
+    const uint64_t p0 = (uint64_t) 0xD2511F53u * c0, p1 = (uint64_t) 0xCD9E8D57u * c2;
+    const uint32_t n0 = (uint32_t) (p1 >> 32) ^ c1 ^ k0, n1 = (uint32_t) p1, n2 = (uint32_t) (p0 >> 32) ^ c3 ^ k1, n3 = (uint32_t) p0;
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+// uniform in (0,1) with 32 random bits, symmetric about 1/2 (so u - 0.5 has exactly zero mean over the 2^32 values)
+__host__ __device__ __forceinline__ double u01_32(uint32_t x) { return ((double) x + 0.5) * 2.3283064365386963e-10; }
+__host__ __device__ __forceinline__ void langevin_counter_uniforms(int seed, int tag, int64_t step, double u[3])
+{
+  uint32_t r[4];
+  philox4x32_10((uint32_t) tag, (uint32_t) (uint64_t) step, (uint32_t) ((uint64_t) step >> 32), 0x4c616e67u /* "Lang" */, (uint32_t) seed,
+                0x62323030u /* "b200" */, r);
+  u[0] = u01_32(r[0]);
+  u[1] = u01_32(r[1]);
+  u[2] = u01_32(r[2]);
+}
+
+struct LangevinGamma { double g1[B200MD_MAXTYPES + 1], g2[B200MD_MAXTYPES + 1]; };
+__global__ void k_langevin_counter(const double4 *__restrict__ pos, const int *__restrict__ tag, int nlocal, const double *__restrict__ vx,
+                                   const double *__restrict__ vy, const double *__restrict__ vz, int seed, int64_t step, LangevinGamma G,
+                                   double *__restrict__ fx, double *__restrict__ fy, double *__restrict__ fz)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nlocal) return;
+  const int type = pos_type(pos[i]);
+  const double g1 = G.g1[type], g2 = G.g2[type];
+  double u[3];
+  langevin_counter_uniforms(seed, tag[i], step, u);
+  fx[i] += g1 * vx[i] + g2 * (u[0] - 0.5);
+  fy[i] += g1 * vy[i] + g2 * (u[1] - 0.5);
+  fz[i] += g1 * vz[i] + g2 * (u[2] - 0.5);
+}
+
 int bond_compute(b200md_ctx *c, int ev)
 {
   if (!c->bonds.maxb) return B200MD_OK;
@@ -179,9 +224,12 @@ int langevin_apply(b200md_ctx *c, int64_t ntimestep)
 {
   LangevinState &L = c->langevin;
   if (!L.on) return B200MD_OK;
-  if (c->nranks > 1) return b200md_fail(c, B200MD_ERR_ARG, "fix langevin replay mode supports one rank (RanMars(seed + me) per rank)");
   const int n = c->nlocal;
-  if ((int) L.order.size() != n) return b200md_fail(c, B200MD_ERR_ARG, "fix langevin: b200md_langevin_order must list every owned atom");
+  if (L.rng_mode == 0) {
+    if (c->nranks > 1)
+      return b200md_fail(c, B200MD_ERR_ARG, "fix langevin replay mode supports one rank (RanMars(seed + me) per rank); use the counter mode (b200md_langevin_rng)");
+    if ((int) L.order.size() != n) return b200md_fail(c, B200MD_ERR_ARG, "fix langevin: b200md_langevin_order must list every owned atom");
+  }
   double delta = (double) (ntimestep - L.beginstep);
   if (delta != 0.0) delta /= (double) (L.endstep - L.beginstep);
   const double t_target = L.t_start + delta * (L.t_stop - L.t_start);
@@ -197,6 +245,14 @@ int langevin_apply(b200md_ctx *c, int64_t ntimestep)
     g2[t] = b * tsqrt;
   }
   g1[0] = g2[0] = 0.0;
+  if (L.rng_mode == 1) {
+    LangevinGamma G;
+    for (int t = 0; t <= B200MD_MAXTYPES; t++) { G.g1[t] = t <= c->ntypes ? g1[t] : 0.0; G.g2[t] = t <= c->ntypes ? g2[t] : 0.0; }
+    k_langevin_counter<<<cdiv(n, 256), 256, 0, c->stream>>>(c->pos.p, c->tag.p, n, c->v[0].p, c->v[1].p, c->v[2].p, L.seed, ntimestep, G,
+                                                            c->f[0].p, c->f[1].p, c->f[2].p);
+    LAUNCH_CHECK();
+    return B200MD_OK;
+  }
   // three numbers per atom, drawn in the reference's local-index order, stored by tag
   for (int k = 0; k < n; k++) {
     double *u = L.rand_h + (size_t) (L.order[k] - 1) * 3;
@@ -386,7 +442,6 @@ extern "C" int b200md_fix_langevin(b200md_ctx *c, double t_start, double t_stop,
   if (t_period <= 0.0) return b200md_fail(c, B200MD_ERR_ARG, "Fix langevin period must be > 0.0");
   if (seed <= 0) return b200md_fail(c, B200MD_ERR_ARG, "Illegal fix langevin command");  // fix_langevin.cpp:84-85
   if (seed > 900000000) return b200md_fail(c, B200MD_ERR_ARG, "Invalid seed for Marsaglia random # generator");
-  if (c->nranks > 1) return b200md_fail(c, B200MD_ERR_ARG, "fix langevin replay mode supports one rank (RanMars(seed + me) per rank)");
   L.t_start = t_start; L.t_stop = t_stop; L.t_period = t_period; L.dt = dt;
   // the fix owns one generator for its whole life (created in the constructor, fix_langevin.cpp:160): a repeated
   // call for the same fix (same seed, e.g. at the start of every `run`) keeps the stream where it is
@@ -439,5 +494,28 @@ extern "C" int b200md_ranmars(int seed, int n, double *out)
   RanMarsHost r;
   r.init(seed);
   for (int i = 0; i < n; i++) out[i] = r.uniform();
+  return B200MD_OK;
+}
+
+extern "C" int b200md_langevin_rng(b200md_ctx *c, int mode)
+{
+  NEED_CTX();
+  if (mode != 0 && mode != 1) return b200md_fail(c, B200MD_ERR_ARG, "langevin_rng: 0 = RanMars replay, 1 = counter-based");
+  c->langevin.rng_mode = mode;
+  return B200MD_OK;
+}
+
+// host only: the three uniforms the counter mode gives atom `tag` on timestep `step` (same function as the kernel's)
+extern "C" int b200md_langevin_counter_uniforms(int seed, int tag, int64_t step, double *u)
+{
+  if (!u) return b200md_fail(nullptr, B200MD_ERR_ARG, "langevin_counter_uniforms: u[3] is required");
+  langevin_counter_uniforms(seed, tag, step, u);
+  return B200MD_OK;
+}
+// host only: raw Philox4x32-10 block, for known-answer tests
+extern "C" int b200md_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4])
+{
+  if (!ctr || !key || !out) return b200md_fail(nullptr, B200MD_ERR_ARG, "philox4x32_10: ctr[4], key[2], out[4]");
+  philox4x32_10(ctr[0], ctr[1], ctr[2], ctr[3], key[0], key[1], out);
   return B200MD_OK;
 }

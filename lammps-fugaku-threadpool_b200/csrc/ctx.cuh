@@ -110,6 +110,7 @@ struct LangevinState {
   double userbinsize = 0.0;
   int64_t nextsort = 0;
   bool bounds_set = false;    // b200md_run_bounds given (a run split into several b200md_run calls)
+  int rng_mode = 0;           // 0 = the reference's RanMars stream replayed on the host, 1 = counter-based on the device
   double *rand_h = nullptr;   // pinned [ntags][3]
   int ntags = 0;
   DevBuf<double> rand_d, gamma_d;

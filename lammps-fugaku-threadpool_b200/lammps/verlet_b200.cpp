@@ -19,6 +19,8 @@
 #include "update.h"
 
 #include <algorithm>
+#include <cstdlib>
+#include <cstring>
 #include <mpi.h>
 #include <utility>
 #include <vector>
@@ -76,8 +78,7 @@ void VerletB200::init()
       error->all(FLERR, "Run style verlet/b200 supports fix nve/b200 on group all plus one fix langevin/b200 (found fix {} {})", fix->id, fix->style);
   }
   if (!nve) error->all(FLERR, "Run style verlet/b200 requires fix nve/b200 on group all");
-  if ((bond || langevin) && comm->nprocs > 1)
-    error->all(FLERR, "Run style verlet/b200: bond style fene/b200 and fix langevin/b200 run on one rank only for now");
+  if (bond && comm->nprocs > 1) error->all(FLERR, "Run style verlet/b200: bond style fene/b200 runs on one rank only for now");
   if (comm->nprocs > 1) {
     // the device library places rank r at grid location (r % px, (r / px) % py, r / (px*py)) (include/b200md.h)
     const int *pg = comm->procgrid;
@@ -106,6 +107,13 @@ void VerletB200::upload()
   if (langevin) {
     if (const char *why = langevin->device_unsupported())
       error->all(FLERR, "Fix langevin/b200 under run style verlet/b200 does not support {}", why);
+    // one rank: the reference's own RanMars stream in the reference's atom order (same trajectory as `fix langevin`);
+    // several ranks, or B200MD_LANGEVIN_RNG=counter: the counter-based device generator (same statistics)
+    const char *rng = getenv("B200MD_LANGEVIN_RNG");
+    const int counter = comm->nprocs > 1 || (rng && strcmp(rng, "counter") == 0);
+    if (counter && comm->nprocs > 1 && comm->me == 0)
+      error->warning(FLERR, "Fix langevin/b200 on several ranks uses the counter-based device generator, not the RanMars streams of fix langevin");
+    B200_CHECK(dev, b200md_langevin_rng(dev->ctx, counter));
     B200_CHECK(dev, b200md_fix_langevin(dev->ctx, langevin->dev_t_start(), langevin->dev_t_stop(), langevin->dev_t_period(),
                                         langevin->dev_seed(), update->dt));
     if (!langevin->order_sent) {

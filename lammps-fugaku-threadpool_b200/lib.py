@@ -63,6 +63,9 @@ PROTOTYPES = {
     "b200md_langevin_order": (_i, [_vp, _i, _vp, _i, _d]),
     "b200md_run_bounds": (_i, [_vp, _i64, _i64]),
     "b200md_ranmars": (_i, [_i, _i, _vp]),
+    "b200md_langevin_rng": (_i, [_vp, _i]),
+    "b200md_langevin_counter_uniforms": (_i, [_i, _i, _i64, _vp]),
+    "b200md_philox4x32_10": (_i, [_vp, _vp, _vp]),
     "b200md_timers": (_i, [_vp, _vp, _vp, _i]),
     "b200md_profile": (_i, [_vp, _i]),
     "b200md_kernel_times": (_i, [_vp, _vp, _vp, _i]),

@@ -218,7 +218,10 @@ class BondFENEB200:
 class FixLangevinB200:
     """fix ID all langevin Tstart Tstop damp seed (src/fix_langevin.cpp:55-160), plain instance."""
 
-    def __init__(self, owner: "B200MD", t_start: float, t_stop: float, damp: float, seed: int):
+    def __init__(self, owner: "B200MD", t_start: float, t_stop: float, damp: float, seed: int, rng: str = "mars"):
+        if rng not in ("mars", "counter"):
+            raise ValueError("fix langevin: rng is 'mars' (the reference's stream, one rank) or 'counter' (device, any ranks)")
+        self.rng = rng
         if damp <= 0.0:
             raise ValueError("Fix langevin period must be > 0.0")
         if seed <= 0:
@@ -227,6 +230,7 @@ class FixLangevinB200:
         self.t_start, self.t_stop, self.damp, self.seed = float(t_start), float(t_stop), float(damp), int(seed)
 
     def init(self):
+        self.o.ctx.call("b200md_langevin_rng", 1 if self.rng == "counter" else 0)
         self.o.ctx.call("b200md_fix_langevin", self.t_start, self.t_stop, self.damp, self.seed, self.o.dt)
 
 
@@ -299,9 +303,9 @@ class B200MD:
         if keyword != "fene":
             raise ValueError("special_bonds: only the fene setting (lj 0.0 1.0 1.0) is on the B200 hot path")
 
-    def fix(self, style: str, *args):
+    def fix(self, style: str, *args, **kw):
         if style in ("langevin", "langevin/b200"):
-            self.fix_langevin = FixLangevinB200(self, *args)
+            self.fix_langevin = FixLangevinB200(self, *args, **kw)
             self._initialized = False
             return self.fix_langevin
         if style in ("nve", "nve/b200"):

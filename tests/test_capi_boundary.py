@@ -121,3 +121,33 @@ def test_ranmars_stream_equals_oracle(pkg, oracle):
         assert 0.0 <= a.min() and a.max() < 1.0
     assert L.b200md_ranmars(0, 1, a.ctypes.data_as(C.c_void_p)) == 5      # "Invalid seed for Marsaglia random # generator"
     assert L.b200md_ranmars(900000001, 1, a.ctypes.data_as(C.c_void_p)) == 5
+
+
+def test_philox_known_answers_and_counter_uniforms(pkg):
+    """the device thermostat's counter-based generator is one __host__ __device__ function: Random123's published
+    known-answer vectors for Philox4x32-10, and the moments / independence of the uniforms it feeds k_langevin_counter"""
+    import ctypes as C
+
+    L = pkg.lib.load()
+    kat = [([0, 0, 0, 0], [0, 0], "6627e8d5 e169c58d bc57ac4c 9b00dbd8"),
+           ([0xffffffff] * 4, [0xffffffff] * 2, "408f276d 41c83b0e a20bc7c6 6d5451fd"),
+           ([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0], "d16cfe09 94fdcceb 5001e420 24126ea1")]
+    for ctr, key, want in kat:
+        c, k, o = np.array(ctr, dtype=np.uint32), np.array(key, dtype=np.uint32), np.zeros(4, dtype=np.uint32)
+        assert L.b200md_philox4x32_10(pkg.lib.ptr(c), pkg.lib.ptr(k), pkg.lib.ptr(o)) == 0
+        assert " ".join(f"{x:08x}" for x in o) == want
+    u = np.zeros((20000, 3))
+    row = np.zeros(3)
+    for t in range(len(u)):
+        assert L.b200md_langevin_counter_uniforms(904297, t + 1, 17, pkg.lib.ptr(row)) == 0
+        u[t] = row
+    assert 0.0 < u.min() and u.max() < 1.0
+    assert abs(u.mean() - 0.5) < 4 * np.sqrt(1 / 12 / u.size)                 # 4 sigma
+    assert abs(u.var() - 1 / 12) < 0.002
+    assert abs(np.corrcoef(u[:, 0], u[:, 1])[0, 1]) < 0.03 and abs(np.corrcoef(u[:-1, 0], u[1:, 0])[0, 1]) < 0.03
+    a, b = np.zeros(3), np.zeros(3)
+    L.b200md_langevin_counter_uniforms(904297, 5, 17, pkg.lib.ptr(a))
+    L.b200md_langevin_counter_uniforms(904297, 5, 18, pkg.lib.ptr(b))
+    assert not np.array_equal(a, b) and np.array_equal(a, u[4])               # a function of (seed, tag, step) only
+    L.b200md_langevin_counter_uniforms(904298, 5, 17, pkg.lib.ptr(b))
+    assert not np.array_equal(a, b)

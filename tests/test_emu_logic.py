@@ -206,7 +206,7 @@ class _AllSum:
         return tot
 
 
-def run_decomposed_emu(pkg, world, grid, kind, cells, steps, host_steps=0):
+def run_decomposed_emu(pkg, world, grid, kind, cells, steps, host_steps=0, configure=None):
     """tests/multirank_util._worker with threads for ranks; optionally `host_steps` more steps through
     b200md_step_host (the bench's e2e leg: atoms migrate between ranks at its rebuilds)"""
     import bench
@@ -221,6 +221,8 @@ def run_decomposed_emu(pkg, world, grid, kind, cells, steps, host_steps=0):
             md = bench.make_system(pkg, kind, rank, world, rank, nccl_id, grid)
             md.box([0, 0, 0], box)
             md.create_atoms(x, v, np.ones(len(x), dtype=np.int32), tag, natoms_total=natoms)
+            if configure:
+                configure(md)
             md.setup()
             t0 = md.thermo_log[-1]
             numneigh, _ = md.neighbor_list()
@@ -230,7 +232,7 @@ def run_decomposed_emu(pkg, world, grid, kind, cells, steps, host_steps=0):
             g = md.gather()
             st = md.neigh_stats()
             out.update(thermo1=np.array([t1["pe"], t1["ke"], t1["press"]]), x1=g["x"], tag1=g["tag"], builds=st["builds"],
-                       nlocal1=md.nlocal)
+                       nlocal1=md.nlocal, temp0=t0["temp"], temp1=t1["temp"])
             if host_steps:
                 n = md.nlocal
                 cap = n + n // 8 + 64
@@ -323,3 +325,41 @@ def test_emu_decomposed_overlap_equals_plain(emu, kind, world, grid, cells, step
     for ra, rb in zip(a, b):
         assert np.array_equal(ra["tag1"], rb["tag1"]) and np.array_equal(ra["x1"], rb["x1"])
         assert np.array_equal(ra["thermo1"], rb["thermo1"]) and ra["builds"] == rb["builds"]
+
+
+def test_emu_langevin_counter_mode_is_rank_count_independent(emu):
+    """fix langevin with the counter-based device generator (Philox keyed by seed, counter = tag, step) on an LJ melt:
+    1 rank and 4 ranks follow the same trajectory (the numbers depend on nothing but seed, tag and step), and the
+    thermostat pulls the temperature from 1.44 toward its 0.3 target"""
+    kind, cells, steps = "lj", 6, 60
+
+    def thermostat(md):
+        md.fix("langevin", 0.3, 0.3, 0.1, 48279, rng="counter")
+
+    one = run_decomposed_emu(emu, 1, (1, 1, 1), kind, cells * 2, steps, configure=thermostat)[0]
+    plain = run_decomposed_emu(emu, 1, (1, 1, 1), kind, cells * 2, steps)[0]
+    assert one["temp1"] < 0.75 * plain["temp1"]          # visibly thermostatted toward 0.3
+    res = run_decomposed_emu(emu, 8, (2, 2, 2), kind, cells, steps, configure=thermostat)
+    np.testing.assert_allclose(res[0]["thermo1"], one["thermo1"], rtol=1e-6)
+    tag = np.concatenate([r["tag1"] for r in res])
+    x = np.concatenate([r["x1"] for r in res])
+    o = np.argsort(tag)
+    dx = x[o] - one["x1"]
+    dx -= one["box"] * np.round(dx / one["box"])
+    assert np.abs(dx).max() < 1e-6
+
+
+def test_emu_chain_with_counter_thermostat(emu):
+    """in.chain with the device generator instead of the RanMars replay: runs through the bonded rebuilds, keeps the
+    melt at its temperature (T = 1 +- a few %), reproducible run to run"""
+    g = load_golden("chain_32k")
+    out = []
+    for _ in range(2):
+        md = chain.make_chain_device(emu, g, langevin=False)
+        md.fix("langevin", 1.0, 1.0, 10.0, 904297, rng="counter")
+        md.run(30)
+        out.append((md.thermo_log[-1], md.gather()))
+        md.close()
+    (ta, ga), (tb, gb) = out
+    assert abs(ta["temp"] - 1.0) < 0.05 and ta["ebond"] > 0
+    assert np.array_equal(ga["x"], gb["x"]) and ta["pe"] == tb["pe"]
