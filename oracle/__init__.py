@@ -107,6 +107,7 @@ def lib() -> C.CDLL:
         L.orc_nbondlist.restype = C.c_int
         L.orc_nbondlist.argtypes = [vp]
         L.orc_ranmars.argtypes = [C.c_int, C.c_int, vp]
+        L.orc_pair_eam_setfl.argtypes = [vp, C.c_char_p, C.c_int, vp]
         _lib = L
     return _lib
 
@@ -268,6 +269,15 @@ class OracleSystem:
                 loaded[fn] = k
             self.L.orc_eam_map_type(self.h, itype, loaded[fn])
         self.L.orc_pair_eam_init(self.h)
+
+    def pair_eam_setfl(self, filename, elements, fs=False):
+        """pair_style eam/alloy (fs=False) or eam/fs; pair_coeff * * filename elements[0] elements[1] ... (one name per
+        atom type, "NULL" allowed)"""
+        assert len(elements) == self.ntypes
+        arr = (C.c_char_p * (self.ntypes + 1))(None, *[e.encode() for e in elements])
+        rc = self.L.orc_pair_eam_setfl(self.h, str(filename).encode(), int(fs), arr)
+        if rc != 0:
+            raise OSError(f"cannot use setfl/fs file {filename} ({rc})")
 
     def eam_tables(self):
         dims = np.zeros(5, dtype=np.int32)

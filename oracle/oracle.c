@@ -538,6 +538,131 @@ void orc_pair_eam_init(orc_sys *s)
   s->cutneighmax = c;
 }
 
+/* -------------------------------------------------------------------------------------
+ * pair_style eam/alloy (DYNAMO setfl) and eam/fs (Finnis-Sinclair):
+ *   pair_coeff * * file El1 El2 ...   PairEAMAlloy::coeff / read_file / file2array
+ *   (src/MANYBODY/pair_eam_alloy.cpp:55-337), PairEAMFS (src/MANYBODY/pair_eam_fs.cpp:55-345);
+ *   array2spline and init_one are PairEAM's (src/MANYBODY/pair_eam.cpp:720-765, 435-456).
+ * The tables are used on the file's own grid (no re-gridding).  elements[i] (i = 1..ntypes) = element name of atom
+ * type i, or "NULL".  Unit conversion as the reference does it, INCLUDING its loop bounds: the setfl reader converts
+ * frho[1..nrho-1] and z2r[1..nr-1] (the last knot keeps the file's units, pair_eam_alloy.cpp:181,189), the fs reader
+ * converts all knots (pair_eam_fs.cpp:165,177).
+ * ------------------------------------------------------------------------------------- */
+static int next_content_line(FILE *fp, char *line, int n)
+{
+  while (fgets(line, n, fp)) {
+    const char *q = line;
+    while (*q == ' ' || *q == '\t' || *q == '\r' || *q == '\n') q++;
+    if (*q) return 1;
+  }
+  return 0;
+}
+static int read_dvector(FILE *fp, double *dst, int n)
+{
+  for (int i = 0; i < n; i++) if (fscanf(fp, "%lg", &dst[i]) != 1) return 0;
+  return 1;
+}
+int orc_pair_eam_setfl(orc_sys *s, const char *filename, int fs, const char *const *elements)
+{
+  FILE *fp = fopen(filename, "r");
+  if (!fp) return -1;
+  char line[4096], first[4096];
+  if (!fgets(first, sizeof first, fp) || !fgets(line, sizeof line, fp) || !fgets(line, sizeof line, fp)) { fclose(fp); return -2; }
+  double conv = 1.0;
+  {
+    int sys_real = fabs(s->boltz - 0.0019872067) < 1e-12, sys_metal = fabs(s->boltz - 8.617343e-5) < 1e-15;
+    if (strstr(first, "UNITS: metal") && sys_real) conv = 23.060549;
+    else if (strstr(first, "UNITS: real") && sys_metal) conv = 1.0 / 23.060549;
+  }
+  if (!next_content_line(fp, line, sizeof line)) { fclose(fp); return -2; }
+  int nel = 0, off = 0;
+  char names[16][32];
+  if (sscanf(line, "%d%n", &nel, &off) != 1 || nel < 1 || nel > 16) { fclose(fp); return -2; }
+  {
+    const char *q = line + off;
+    for (int e = 0; e < nel; e++) {
+      int used = 0;
+      if (sscanf(q, "%31s%n", names[e], &used) != 1) { fclose(fp); return -2; }   /* "Incorrect element names" */
+      q += used;
+    }
+  }
+  int nrho, nr; double drho, dr, cut;
+  if (!next_content_line(fp, line, sizeof line) || sscanf(line, "%d %lg %d %lg %lg", &nrho, &drho, &nr, &dr, &cut) != 5 ||
+      nrho <= 0 || nr <= 0 || dr <= 0.0) { fclose(fp); return -2; }
+  int nrhor_file = fs ? nel * nel : nel, npair = nel * (nel + 1) / 2;
+  double *mass = (double *) xcalloc(nel, sizeof(double));
+  double *frho = (double *) xcalloc((size_t) (nel + 1) * (nrho + 1), sizeof(double));    /* + the all-zero table */
+  double *rhor = (double *) xcalloc((size_t) nrhor_file * (nr + 1), sizeof(double));
+  double *z2r = (double *) xcalloc((size_t) npair * (nr + 1), sizeof(double));
+  int ok = 1;
+  for (int e = 0; e < nel && ok; e++) {
+    int iz;
+    ok = next_content_line(fp, line, sizeof line) && sscanf(line, "%d %lg", &iz, &mass[e]) == 2 &&
+         read_dvector(fp, &frho[(size_t) e * (nrho + 1) + 1], nrho);
+    if (!ok) break;
+    if (fs) {
+      for (int j = 0; j < nel && ok; j++) ok = read_dvector(fp, &rhor[(size_t) (e * nel + j) * (nr + 1) + 1], nr);
+      if (conv != 1.0) for (int m = 1; m <= nrho; m++) frho[(size_t) e * (nrho + 1) + m] *= conv;
+    } else {
+      ok = read_dvector(fp, &rhor[(size_t) e * (nr + 1) + 1], nr);
+      if (conv != 1.0) for (int m = 1; m < nrho; m++) frho[(size_t) e * (nrho + 1) + m] *= conv;
+    }
+  }
+  int n = 0;
+  for (int i = 0; i < nel && ok; i++)
+    for (int j = 0; j <= i && ok; j++, n++) {
+      ok = read_dvector(fp, &z2r[(size_t) n * (nr + 1) + 1], nr);
+      if (conv != 1.0) for (int m = 1; m < nr + (fs ? 1 : 0); m++) z2r[(size_t) n * (nr + 1) + m] *= conv;
+    }
+  fclose(fp);
+  if (!ok) { free(mass); free(frho); free(rhor); free(z2r); return -3; }
+
+  int nt = s->ntypes, ld = nt + 1, count = 0;
+  for (int i = 1; i <= nt; i++) {
+    s->map[i] = -1;
+    if (!elements[i] || strcmp(elements[i], "NULL") == 0) continue;
+    for (int e = 0; e < nel; e++) if (strcmp(elements[i], names[e]) == 0) s->map[i] = e;
+    if (s->map[i] < 0) { free(mass); free(frho); free(rhor); free(z2r); return -4; }   /* "No matching element in EAM potential file" */
+    s->mass[i] = mass[s->map[i]];
+    count++;
+  }
+  free(mass);
+  if (!count) { free(frho); free(rhor); free(z2r); return -5; }
+  s->pair_style = 2;
+  s->nrho = nrho; s->nr = nr; s->drho = drho; s->dr = dr; s->rhomax = (nrho - 1) * drho;
+  s->nfrho = nel + 1; s->nrhor = nrhor_file; s->nz2r = npair;
+  free(s->type2frho); s->type2frho = (int *) xcalloc(ld, sizeof(int));
+  free(s->type2rhor); s->type2rhor = (int *) xcalloc(ld * ld, sizeof(int));
+  free(s->type2z2r); s->type2z2r = (int *) xcalloc(ld * ld, sizeof(int));
+  for (int i = 1; i <= nt; i++) {
+    s->type2frho[i] = s->map[i] >= 0 ? s->map[i] : s->nfrho - 1;
+    for (int j = 1; j <= nt; j++) {
+      s->type2rhor[i * ld + j] = fs ? s->map[i] * nel + s->map[j] : s->map[i];
+      int irow = s->map[i], icol = s->map[j];
+      if (irow == -1 || icol == -1) { s->type2z2r[i * ld + j] = 0; if (fs) s->type2rhor[i * ld + j] = 0; continue; }
+      if (irow < icol) { irow = s->map[j]; icol = s->map[i]; }
+      int k = 0;
+      for (int m = 0; m < irow; m++) k += m + 1;
+      s->type2z2r[i * ld + j] = k + icol;
+    }
+  }
+  s->rdr = 1.0 / dr; s->rdrho = 1.0 / drho;
+  free(s->frho_spline); free(s->rhor_spline); free(s->z2r_spline);
+  s->frho_spline = (double *) xcalloc((size_t) s->nfrho * (nrho + 1) * 7, sizeof(double));
+  s->rhor_spline = (double *) xcalloc((size_t) s->nrhor * (nr + 1) * 7, sizeof(double));
+  s->z2r_spline = (double *) xcalloc((size_t) s->nz2r * (nr + 1) * 7, sizeof(double));
+  for (int i = 0; i < s->nfrho; i++) interpolate(nrho, drho, &frho[(size_t) i * (nrho + 1)], &s->frho_spline[(size_t) i * (nrho + 1) * 7]);
+  for (int i = 0; i < s->nrhor; i++) interpolate(nr, dr, &rhor[(size_t) i * (nr + 1)], &s->rhor_spline[(size_t) i * (nr + 1) * 7]);
+  for (int i = 0; i < s->nz2r; i++) interpolate(nr, dr, &z2r[(size_t) i * (nr + 1)], &s->z2r_spline[(size_t) i * (nr + 1) * 7]);
+  free(frho); free(rhor); free(z2r);
+  s->cutmax = cut;                                   /* init_one: cutmax = setfl->cut (pair_eam.cpp:446-450) */
+  s->cutforcesq = cut * cut; s->cutforce = cut;
+  double c = cut + s->skin;
+  for (int i = 1; i <= nt; i++) for (int j = 1; j <= nt; j++) { s->cutsq[i * ld + j] = s->cutforcesq; s->cutneighsq[i * ld + j] = c * c; }
+  s->cutneighmax = c;
+  return 0;
+}
+
 /* table accessors for tests (sizes, then raw copies) */
 void orc_eam_dims(orc_sys *s, int *out) { out[0] = s->nrho; out[1] = s->nr; out[2] = s->nfrho; out[3] = s->nrhor; out[4] = s->nz2r; }
 void orc_eam_scalars(orc_sys *s, double *out) { out[0] = s->rdr; out[1] = s->rdrho; out[2] = s->rhomax; out[3] = s->cutforcesq; out[4] = s->cutmax; }

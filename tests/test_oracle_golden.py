@@ -117,6 +117,47 @@ def test_oracle_reference_unittest_eam_yaml(oracle, name, units):
         assert np.abs(t["virial"] - g[f"{phase}_stress"]).max() <= eps * np.abs(g[f"{phase}_stress"]).max(), phase
 
 
+def unpack_fs(tmp_path):
+    import lzma
+
+    p = tmp_path / "AlFe_mm.eam.fs"
+    p.write_bytes(lzma.decompress((GOLDEN / "AlFe_mm.eam.fs.xz").read_bytes()))
+    return p
+
+
+@pytest.mark.parametrize("name,units,fs", [("unittest_atomic_pair_eam_alloy", "metal", False),
+                                           ("unittest_atomic_pair_eam_alloy_real", "real", False),
+                                           ("unittest_atomic_pair_eam_fs", "metal", True),
+                                           ("unittest_atomic_pair_eam_fs_real", "real", True)])
+def test_oracle_reference_unittest_eam_alloy_fs_yaml(oracle, name, units, fs, tmp_path):
+    """The reference's known-answer tests for pair eam/alloy (CuNi.eam.alloy, setfl) and eam/fs (AlFe_mm.eam.fs,
+    Finnis-Sinclair: the density function depends on both elements) in metal and real units
+    (unittest/force-styles/tests/atomic-pair-eam_{alloy,fs}{,_real}.yaml): same 32 atoms and run protocol as the
+    funcfl case above, held to the yaml's own epsilon.  The real-units cases pin the reader's unit conversion,
+    including the setfl reader's habit of leaving the last knot of F(rho) and z2r unconverted."""
+    g = load_golden(name)
+    eps = float(g["epsilon"])
+    s = oracle.OracleSystem(2, units)
+    s.set_dt(0.0001)
+    s.set_box(g["boxlo"], g["boxhi"])
+    s.set_neighbor(2.0, every=2, delay=2, check=0)
+    if fs:
+        s.pair_eam_setfl(unpack_fs(tmp_path), ["Al", "Fe"], fs=True)
+    else:
+        s.pair_eam_setfl(GOLDEN / "CuNi.eam.alloy", ["Cu", "Ni"])
+    s.set_atoms(g["x"], g["v"], g["type"], g["tag"])
+    s.setup()
+    for phase in ("init", "run"):
+        if phase == "run":
+            s.run(4)
+        a, t = s.atoms(), s.thermo()
+        o = np.argsort(a["tag"])
+        f_ref = g[f"{phase}_forces"]
+        assert np.abs(a["f"][o] - f_ref).max() <= 5 * eps * np.abs(f_ref).max(), phase
+        assert abs(t["pe"] - float(g[f"{phase}_vdwl"])) <= eps * abs(float(g[f"{phase}_vdwl"])), phase
+        assert np.abs(t["virial"] - g[f"{phase}_stress"]).max() <= eps * np.abs(g[f"{phase}_stress"]).max(), phase
+
+
 def make_chain_oracle(oracle, g):
     """bench/in.chain on the oracle: atom_style bond, special_bonds fene, lj/cut 1.12 shifted, bond fene,
     fix nve + fix langevin 1.0 1.0 10.0 904297, neighbor 0.4 / every 1 delay 1, dt 0.012"""
