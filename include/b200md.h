@@ -103,6 +103,14 @@ int b200md_eam_init(b200md_ctx *ctx, int ntypes, int nrho, int nr, double rdrho,
  * :404), *cutmax_out the force cutoff.  Ends by calling b200md_eam_init. */
 int b200md_eam_init_funcfl(b200md_ctx *ctx, int ntypes, int nfiles, const char *const *files, const int *map,
                            double *mass_out, double *cutmax_out);
+/* pair_style eam/alloy (fs = 0, DYNAMO setfl file) and eam/fs (fs = 1, Finnis-Sinclair file: the density
+ * function depends on both elements): PairEAMAlloy / PairEAMFS ::coeff + read_file + file2array
+ * (src/MANYBODY/pair_eam_alloy.cpp:55-337, pair_eam_fs.cpp:55-345) + PairEAM::array2spline + init_one, i.e.
+ * `pair_coeff * * file El1 El2 ...`: elements[1..ntypes] = element name of each atom type or "NULL".  The file's
+ * energies are converted between metal and real units as the reference's readers do.  mass_out / cutmax_out as
+ * above.  Ends by calling b200md_eam_init; the force kernels are the same multi-type ones. */
+int b200md_eam_init_setfl(b200md_ctx *ctx, int ntypes, const char *file, int fs, const char *const *elements,
+                          double *mass_out, double *cutmax_out);
 /* per-atom EAM intermediates of owned atoms, device order (PairEAM::extract / rho, fp members) */
 int b200md_eam_download(b200md_ctx *ctx, double *rho, double *fp);
 

@@ -8,4 +8,4 @@ thin host side: ``lib`` binds the C ABI with ctypes, ``styles`` mirrors the refe
 """
 from .build import build, LIB  # noqa: F401
 from . import lib, inputs, styles  # noqa: F401
-from .styles import B200MD, PairLJCutB200, PairEAMB200, NeighborB200, FixNVEB200, BondFENEB200, FixLangevinB200  # noqa: F401
+from .styles import B200MD, PairLJCutB200, PairEAMB200, PairEAMAlloyB200, NeighborB200, FixNVEB200, BondFENEB200, FixLangevinB200  # noqa: F401

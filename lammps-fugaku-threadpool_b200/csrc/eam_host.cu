@@ -164,3 +164,109 @@ extern "C" int b200md_eam_init_funcfl(b200md_ctx *c, int ntypes, int nfiles, con
   return b200md_eam_init(c, ntypes, nrho, nr, 1.0 / drho, 1.0 / dr, rhomax, cutmax * cutmax, nfrho, frho_s.data(),
                          nrhor, rhor_s.data(), nz2r, z2r_s.data(), t2f.data(), t2r.data(), t2z.data());
 }
+
+// ---- pair_style eam/alloy (DYNAMO setfl) and eam/fs (Finnis-Sinclair) -----------------------------------------
+// pair_coeff * * file El1 El2 ...: PairEAMAlloy::coeff / read_file / file2array (src/MANYBODY/pair_eam_alloy.cpp:55-337)
+// and PairEAMFS (src/MANYBODY/pair_eam_fs.cpp:55-345).  The tables are used on the file's own grid; splines and
+// cutoff as PairEAM (array2spline, init_one).  The device kernels are the multi-type ones the funcfl path uses:
+// type2rhor is a full [type][type] map, which is all eam/fs needs.
+namespace {
+
+bool content_line(FILE *fp, char *line, int n)
+{
+  while (fgets(line, n, fp)) {
+    const char *q = line;
+    while (*q == ' ' || *q == '\t' || *q == '\r' || *q == '\n') q++;
+    if (*q) return true;
+  }
+  return false;
+}
+
+bool read_into(FILE *fp, double *dst, int n)
+{
+  for (int k = 0; k < n; k++)
+    if (fscanf(fp, "%lg", &dst[k]) != 1) return false;
+  return true;
+}
+
+}  // namespace
+
+extern "C" int b200md_eam_init_setfl(b200md_ctx *c, int ntypes, const char *file, int fs, const char *const *elements,
+                                     double *mass_out, double *cutmax_out)
+{
+  if (!c) return b200md_fail(nullptr, B200MD_ERR_ARG, "NULL context");
+  if (ntypes < 1 || ntypes > B200MD_MAXTYPES || !file || !elements) return b200md_fail(c, B200MD_ERR_ARG, "eam: bad ntypes / file / elements");
+  FILE *fp = fopen(file, "r");
+  if (!fp) return b200md_fail(c, B200MD_ERR_ARG, "Cannot open EAM potential file %s", file);
+  struct Closer { FILE *f; ~Closer() { fclose(f); } } closer{fp};
+  char first[4096], line[4096];
+  if (!fgets(first, sizeof first, fp) || !fgets(line, sizeof line, fp) || !fgets(line, sizeof line, fp) || !content_line(fp, line, sizeof line))
+    return b200md_fail(c, B200MD_ERR_ARG, "Invalid EAM potential file %s", file);
+  // PotentialFileReader's transparent metal <-> real conversion of energies (src/utils.cpp:1488-1506)
+  const bool system_real = fabs(c->boltz - 0.0019872067) < 1e-12;
+  double conv = 1.0;
+  if (strstr(first, "UNITS: metal") && system_real) conv = 23.060549;
+  else if (strstr(first, "UNITS: real") && !system_real) conv = 1.0 / 23.060549;
+  int nel = 0, off = 0;
+  if (sscanf(line, "%d%n", &nel, &off) != 1 || nel < 1 || nel > B200MD_MAXTYPES) return b200md_fail(c, B200MD_ERR_ARG, "Invalid EAM potential file %s", file);
+  std::vector<std::string> names;
+  for (const char *q = line + off; (int) names.size() < nel;) {
+    char buf[64];
+    int used = 0;
+    if (sscanf(q, "%63s%n", buf, &used) != 1) return b200md_fail(c, B200MD_ERR_ARG, "Incorrect element names in EAM potential file");
+    names.push_back(buf);
+    q += used;
+  }
+  int nrho = 0, nr = 0;
+  double drho = 0, dr = 0, cut = 0;
+  if (!content_line(fp, line, sizeof line) || sscanf(line, "%d %lg %d %lg %lg", &nrho, &drho, &nr, &dr, &cut) != 5 || nrho <= 4 || nr <= 4 ||
+      dr <= 0.0 || drho <= 0.0)
+    return b200md_fail(c, B200MD_ERR_ARG, "Invalid EAM potential file %s", file);
+  const int nfrho = nel + 1, nrhor = fs ? nel * nel : nel, nz2r = nel * (nel + 1) / 2, nt1 = ntypes + 1;
+  std::vector<double> mass(nel), frho((size_t) nfrho * (nrho + 1), 0.0), rhor((size_t) nrhor * (nr + 1), 0.0), z2r((size_t) nz2r * (nr + 1), 0.0);
+  for (int e = 0; e < nel; e++) {
+    int iz = 0;
+    if (!content_line(fp, line, sizeof line) || sscanf(line, "%d %lg", &iz, &mass[e]) != 2 || !read_into(fp, &frho[(size_t) e * (nrho + 1) + 1], nrho))
+      return b200md_fail(c, B200MD_ERR_ARG, "Invalid EAM potential file %s", file);
+    for (int j = 0; j < (fs ? nel : 1); j++)
+      if (!read_into(fp, &rhor[(size_t) (fs ? e * nel + j : e) * (nr + 1) + 1], nr)) return b200md_fail(c, B200MD_ERR_ARG, "Invalid EAM potential file %s", file);
+    // the setfl reader converts knots 1..nrho-1 (pair_eam_alloy.cpp:181), the fs reader all of them (pair_eam_fs.cpp:165)
+    if (conv != 1.0)
+      for (int m = 1; m < nrho + (fs ? 1 : 0); m++) frho[(size_t) e * (nrho + 1) + m] *= conv;
+  }
+  for (int t = 0; t < nz2r; t++) {
+    if (!read_into(fp, &z2r[(size_t) t * (nr + 1) + 1], nr)) return b200md_fail(c, B200MD_ERR_ARG, "Invalid EAM potential file %s", file);
+    if (conv != 1.0)
+      for (int m = 1; m < nr + (fs ? 1 : 0); m++) z2r[(size_t) t * (nr + 1) + m] *= conv;   // pair_eam_alloy.cpp:189 / pair_eam_fs.cpp:177
+  }
+  std::vector<int> map(nt1, -1);
+  int count = 0;
+  for (int i = 1; i <= ntypes; i++) {
+    if (!elements[i] || strcmp(elements[i], "NULL") == 0) continue;
+    for (int e = 0; e < nel; e++)
+      if (names[e] == elements[i]) map[i] = e;
+    if (map[i] < 0) return b200md_fail(c, B200MD_ERR_ARG, "No matching element in EAM potential file");
+    count++;
+  }
+  if (!count) return b200md_fail(c, B200MD_ERR_ARG, "Incorrect args for pair coefficients");
+
+  std::vector<double> frho_s((size_t) nfrho * (nrho + 1) * 7, 0.0), rhor_s((size_t) nrhor * (nr + 1) * 7, 0.0), z2r_s((size_t) nz2r * (nr + 1) * 7, 0.0);
+  for (int k = 0; k < nfrho; k++) cubic_rows(nrho, drho, &frho[(size_t) k * (nrho + 1)], &frho_s[(size_t) k * (nrho + 1) * 7]);
+  for (int k = 0; k < nrhor; k++) cubic_rows(nr, dr, &rhor[(size_t) k * (nr + 1)], &rhor_s[(size_t) k * (nr + 1) * 7]);
+  for (int k = 0; k < nz2r; k++) cubic_rows(nr, dr, &z2r[(size_t) k * (nr + 1)], &z2r_s[(size_t) k * (nr + 1) * 7]);
+  std::vector<int> t2f(nt1, 0), t2r((size_t) nt1 * nt1, 0), t2z((size_t) nt1 * nt1, 0);
+  for (int i = 1; i <= ntypes; i++) {
+    t2f[i] = map[i] >= 0 ? map[i] : nfrho - 1;
+    for (int j = 1; j <= ntypes; j++) {
+      if (map[i] < 0 || map[j] < 0) continue;   // pair hybrid's non-EAM types: never looked up
+      t2r[(size_t) i * nt1 + j] = fs ? map[i] * nel + map[j] : map[i];
+      const int hi = std::max(map[i], map[j]), lo = std::min(map[i], map[j]);
+      t2z[(size_t) i * nt1 + j] = hi * (hi + 1) / 2 + lo;
+    }
+  }
+  if (mass_out)
+    for (int i = 1; i <= ntypes; i++) mass_out[i] = map[i] >= 0 ? mass[map[i]] : 0.0;
+  if (cutmax_out) *cutmax_out = cut;
+  return b200md_eam_init(c, ntypes, nrho, nr, 1.0 / drho, 1.0 / dr, (nrho - 1) * drho, cut * cut, nfrho, frho_s.data(), nrhor, rhor_s.data(),
+                         nz2r, z2r_s.data(), t2f.data(), t2r.data(), t2z.data());
+}

@@ -8,6 +8,7 @@
 #include "input.h"
 #include "lammps.h"
 #include "modify.h"
+#include "pair_eam_alloy_b200.h"
 #include "pair_eam_b200.h"
 #include "pair_lj_cut_b200.h"
 #include "update.h"
@@ -19,6 +20,8 @@ namespace LAMMPS_NS {
 
 static Pair *make_lj(LAMMPS *lmp) { return new PairLJCutB200(lmp); }
 static Pair *make_eam(LAMMPS *lmp) { return new PairEAMB200(lmp); }
+static Pair *make_eam_alloy(LAMMPS *lmp) { return new PairEAMAlloyB200(lmp); }
+static Pair *make_eam_fs(LAMMPS *lmp) { return new PairEAMFSB200(lmp); }
 static Fix *make_nve(LAMMPS *lmp, int narg, char **arg) { return new FixNVEB200(lmp, narg, arg); }
 static Fix *make_langevin(LAMMPS *lmp, int narg, char **arg) { return new FixLangevinB200(lmp, narg, arg); }
 static Bond *make_fene(LAMMPS *lmp) { return new BondFENEB200(lmp); }
@@ -28,6 +31,8 @@ void b200_register_styles(LAMMPS *lmp)
 {
   (*lmp->force->pair_map)["lj/cut/b200"] = &make_lj;
   (*lmp->force->pair_map)["eam/b200"] = &make_eam;
+  (*lmp->force->pair_map)["eam/alloy/b200"] = &make_eam_alloy;
+  (*lmp->force->pair_map)["eam/fs/b200"] = &make_eam_fs;
   (*lmp->modify->fix_map)["nve/b200"] = &make_nve;
   (*lmp->modify->fix_map)["langevin/b200"] = &make_langevin;
   (*lmp->force->bond_map)["fene/b200"] = &make_fene;

@@ -7,6 +7,7 @@
 
 #include "fix_nve_b200.h"
 #include "lammps.h"
+#include "pair_eam_alloy_b200.h"
 #include "pair_eam_b200.h"
 #include "pair_lj_cut_b200.h"
 #include "version.h"
@@ -15,6 +16,8 @@ using namespace LAMMPS_NS;
 
 static Pair *lj_creator(LAMMPS *lmp) { return new PairLJCutB200(lmp); }
 static Pair *eam_creator(LAMMPS *lmp) { return new PairEAMB200(lmp); }
+static Pair *eam_alloy_creator(LAMMPS *lmp) { return new PairEAMAlloyB200(lmp); }
+static Pair *eam_fs_creator(LAMMPS *lmp) { return new PairEAMFSB200(lmp); }
 static Fix *nve_creator(LAMMPS *lmp, int argc, char **argv) { return new FixNVEB200(lmp, argc, argv); }
 
 extern "C" void lammpsplugin_init(void *lmp, void *handle, void *regfunc)
@@ -34,6 +37,16 @@ extern "C" void lammpsplugin_init(void *lmp, void *handle, void *regfunc)
   plugin.name = "eam/b200";
   plugin.info = "eam (funcfl) on the B200 device library (libb200md.so)";
   plugin.creator.v1 = (lammpsplugin_factory1 *) &eam_creator;
+  (*register_plugin)(&plugin, lmp);
+
+  plugin.name = "eam/alloy/b200";
+  plugin.info = "eam/alloy (setfl) on the B200 device library (libb200md.so)";
+  plugin.creator.v1 = (lammpsplugin_factory1 *) &eam_alloy_creator;
+  (*register_plugin)(&plugin, lmp);
+
+  plugin.name = "eam/fs/b200";
+  plugin.info = "eam/fs (Finnis-Sinclair) on the B200 device library (libb200md.so)";
+  plugin.creator.v1 = (lammpsplugin_factory1 *) &eam_fs_creator;
   (*register_plugin)(&plugin, lmp);
 
   plugin.style = "fix";

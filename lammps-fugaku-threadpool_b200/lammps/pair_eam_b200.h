@@ -15,7 +15,8 @@ PairStyle(eam/b200,PairEAMB200);
 
 namespace LAMMPS_NS {
 
-class PairEAMB200 : public PairEAM, public B200PairTables {
+// `virtual`: PairEAMAlloy / PairEAMFS derive virtually from PairEAM, and eam/alloy/b200, eam/fs/b200 combine them with this class
+class PairEAMB200 : virtual public PairEAM, public B200PairTables {
  public:
   PairEAMB200(LAMMPS *lmp);
   ~PairEAMB200() override;

@@ -33,6 +33,7 @@ PROTOTYPES = {
     "b200md_lj_init": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "b200md_eam_init": (_i, [_vp, _i, _i, _i, _d, _d, _d, _d, _i, _vp, _i, _vp, _i, _vp, _vp, _vp, _vp]),
     "b200md_eam_init_funcfl": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp]),
+    "b200md_eam_init_setfl": (_i, [_vp, _i, C.c_char_p, _i, _vp, _vp, _vp]),
     "b200md_eam_download": (_i, [_vp, _vp, _vp]),
     "b200md_neigh_config": (_i, [_vp, _i, _vp, _d, _d, _i, _i, _i, _d]),
     "b200md_neigh_decide": (_i, [_vp, _vp]),

@@ -5,6 +5,8 @@ Same names, argument meaning and error behaviour as the reference's script comma
     pair_style lj/cut Rc ; pair_coeff I J eps sigma [cut] ; pair_modify shift yes mix arithmetic
                                               -> PairLJCutB200.settings / coeff / modify   (src/pair_lj_cut.cpp:428-557)
     pair_style eam ; pair_coeff I I file      -> PairEAMB200.coeff                         (src/MANYBODY/pair_eam.cpp:372-412)
+    pair_style eam/alloy | eam/fs ; pair_coeff * * file El1 El2 ...
+                                              -> PairEAMAlloyB200.coeff                    (src/MANYBODY/pair_eam_alloy.cpp:55-110)
     neighbor SKIN bin ; neigh_modify every N delay M check yes|no
                                               -> NeighborB200.set / modify                 (src/neighbor.cpp:2556-2700)
     fix ID all nve                            -> FixNVEB200                                (src/fix_nve.cpp)
@@ -127,6 +129,41 @@ class PairEAMB200:
         self.o.ctx.call("b200md_eam_init_funcfl", nt, len(self.files), arr, lib.ptr(self.map), lib.ptr(mass), C.byref(cut))
         for i in range(1, nt + 1):
             if self.map[i] >= 0:
+                self.o.mass[i] = mass[i]
+        self.cutmax = cut.value
+        return np.full((nt + 1, nt + 1), self.cutmax)
+
+
+class PairEAMAlloyB200:
+    """pair_style eam/alloy (setfl) and eam/fs (src/MANYBODY/pair_eam_alloy.cpp, pair_eam_fs.cpp):
+    coeff("*", "*", file, El1, El2, ...) with one element name (or "NULL") per atom type; sets the type masses."""
+
+    def __init__(self, owner: "B200MD", fs: bool = False):
+        self.o = owner
+        self.fs = fs
+        self.file = None
+        self.elements: list[str] = []
+        self.cutmax = 0.0
+
+    def settings(self):
+        pass
+
+    def coeff(self, i, j, filename: str, *elements: str):
+        if str(i) != "*" or str(j) != "*" or len(elements) != self.o.ntypes:
+            raise ValueError("Incorrect args for pair coefficients")
+        self.file = str(filename)
+        self.elements = [str(e) for e in elements]
+
+    def init(self):
+        nt = self.o.ntypes
+        if self.file is None:
+            raise ValueError("All pair coeffs are not set")
+        arr = (C.c_char_p * (nt + 1))(None, *[e.encode() for e in self.elements])
+        mass = np.zeros(nt + 1)
+        cut = C.c_double(0.0)
+        self.o.ctx.call("b200md_eam_init_setfl", nt, self.file.encode(), int(self.fs), arr, lib.ptr(mass), C.byref(cut))
+        for i in range(1, nt + 1):
+            if self.elements[i - 1] != "NULL":
                 self.o.mass[i] = mass[i]
         self.cutmax = cut.value
         return np.full((nt + 1, nt + 1), self.cutmax)
@@ -326,6 +363,10 @@ class B200MD:
             self.pair.settings(*args)
         elif name in ("eam", "eam/b200"):
             self.pair = PairEAMB200(self)
+        elif name in ("eam/alloy", "eam/alloy/b200"):
+            self.pair = PairEAMAlloyB200(self, fs=False)
+        elif name in ("eam/fs", "eam/fs/b200"):
+            self.pair = PairEAMAlloyB200(self, fs=True)
         else:
             raise ValueError(f"Unrecognized pair style '{name}' is not on the B200 hot path")
         self._initialized = False

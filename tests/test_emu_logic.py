@@ -363,3 +363,24 @@ def test_emu_chain_with_counter_thermostat(emu):
     (ta, ga), (tb, gb) = out
     assert abs(ta["temp"] - 1.0) < 0.05 and ta["ebond"] > 0
     assert np.array_equal(ga["x"], gb["x"]) and ta["pe"] == tb["pe"]
+
+
+# ---- eam/alloy and eam/fs (the library's setfl / fs readers + the multi-type EAM kernels) ----
+import test_zz_gpu_eam_alloy as alloy  # noqa: E402
+
+
+@pytest.mark.parametrize("kind,units", [("alloy", "metal"), ("alloy", "real"), ("fs", "metal"), ("fs", "real")])
+def test_emu_eam_alloy_fs_vs_oracle(emu, oracle, kind, units, tmp_path):
+    alloy.test_eam_alloy_fs_vs_oracle(emu, oracle, kind, units, tmp_path)
+
+
+def test_emu_eam_alloy_error_paths(emu, tmp_path):
+    alloy.test_eam_alloy_error_paths(emu, tmp_path)
+
+
+@pytest.mark.parametrize("name,units,style", [("unittest_atomic_pair_eam_alloy", "metal", "eam/alloy"),
+                                              ("unittest_atomic_pair_eam_alloy_real", "real", "eam/alloy"),
+                                              ("unittest_atomic_pair_eam_fs", "metal", "eam/fs"),
+                                              ("unittest_atomic_pair_eam_fs_real", "real", "eam/fs")])
+def test_emu_lammps_unittest_eam_alloy_fs_yaml(emu_lmp, name, units, style, tmp_path):
+    lh.test_reference_unittest_eam_alloy_fs_yaml_through_lammps(name, units, style, tmp_path)

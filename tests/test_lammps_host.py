@@ -172,10 +172,9 @@ neigh_modify delay 2 every 2 check no
 units {units}
 timestep 0.0001
 newton on on
-pair_style eam
+pair_style {style}
 read_data data.metal
-pair_coeff 1 1 {al}
-pair_coeff 2 2 {cu}
+{coeffs}
 {runstyle}
 thermo_style custom step pe
 thermo_modify format float %.17g
@@ -186,6 +185,10 @@ thermo 2
 run 4 post no
 write_dump all custom run.txt id fx fy fz modify sort id format float %.17g
 """
+
+
+FUNCFL_COEFFS = (f"pair_coeff 1 1 {ROOT / 'tests' / 'golden' / 'Al_jnp.eam'}\n"
+                 f"pair_coeff 2 2 {ROOT / 'tests' / 'golden' / 'Cu_u3_units.eam'}")
 
 
 def write_data_metal(g, path):
@@ -229,8 +232,7 @@ def test_reference_unittest_eam_yaml_through_lammps(name, units, tmp_path):
         pytest.skip("oracle/_ref host binaries not shipped")
     g = dict(np.load(ROOT / "tests" / "golden" / f"{name}.npz"))
     write_data_metal(g, tmp_path / "data.metal")
-    text = IN_UNITTEST_EAM.format(units=units, al=ROOT / "tests" / "golden" / "Al_jnp.eam",
-                                  cu=ROOT / "tests" / "golden" / "Cu_u3_units.eam", runstyle=STOCK_LOOP)
+    text = IN_UNITTEST_EAM.format(units=units, style="eam", coeffs=FUNCFL_COEFFS, runstyle=STOCK_LOOP)
     r = run_lmp(LMP_B200, text, tmp_path, ["-sf", "b200"])
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert "eam/b200" in r.stdout or True
@@ -251,8 +253,7 @@ def test_thin_box_is_refused_by_the_resident_loop(tmp_path):
         pytest.skip("oracle/_ref host binaries not shipped")
     g = dict(np.load(ROOT / "tests" / "golden" / "unittest_atomic_pair_eam.npz"))
     write_data_metal(g, tmp_path / "data.metal")
-    text = IN_UNITTEST_EAM.format(units="metal", al=ROOT / "tests" / "golden" / "Al_jnp.eam",
-                                  cu=ROOT / "tests" / "golden" / "Cu_u3_units.eam", runstyle="")
+    text = IN_UNITTEST_EAM.format(units="metal", style="eam", coeffs=FUNCFL_COEFFS, runstyle="")
     # the resident loop wants its integration fix from the first run on
     text = text.replace("run 0 post no", "fix 0 all nve\nrun 0 post no\nunfix 0", 1)
     r = run_lmp(LMP_B200, text, tmp_path, ["-sf", "b200"])
@@ -359,3 +360,35 @@ def test_chain_thermo_matches_reference(tmp_path):
     np.testing.assert_allclose(G[:, 1:], R[:, 1:], rtol=1e-6)
     np.testing.assert_allclose(G[0, 1:], R[0, 1:], rtol=1e-10)
     assert "Neighbor list builds = 25" in got.stdout
+
+
+@FIRST_RUN
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,units,style", [("unittest_atomic_pair_eam_alloy", "metal", "eam/alloy"),
+                                              ("unittest_atomic_pair_eam_alloy_real", "real", "eam/alloy"),
+                                              ("unittest_atomic_pair_eam_fs", "metal", "eam/fs"),
+                                              ("unittest_atomic_pair_eam_fs_real", "real", "eam/fs")])
+def test_reference_unittest_eam_alloy_fs_yaml_through_lammps(name, units, style, tmp_path):
+    """atomic-pair-eam_alloy{,_real}.yaml and atomic-pair-eam_fs{,_real}.yaml through `lmp_b200 -sf b200` under the
+    stock loop: pair eam/alloy/b200 and eam/fs/b200 = the reference's own file readers + the device compute in
+    host-ghost mode (eam/fs: the density table is looked up per element PAIR).  Forces 1e-10 of max|f|, energy 1e-10."""
+    import lzma
+
+    if not LMP_B200.exists():
+        pytest.skip("oracle/_ref host binaries not shipped")
+    g = dict(np.load(ROOT / "tests" / "golden" / f"{name}.npz"))
+    write_data_metal(g, tmp_path / "data.metal")
+    if style == "eam/fs":
+        (tmp_path / "AlFe_mm.eam.fs").write_bytes(lzma.decompress((ROOT / "tests" / "golden" / "AlFe_mm.eam.fs.xz").read_bytes()))
+        coeffs = "pair_coeff * * AlFe_mm.eam.fs Al Fe"
+    else:
+        coeffs = f"pair_coeff * * {ROOT / 'tests' / 'golden' / 'CuNi.eam.alloy'} Cu Ni"
+    text = IN_UNITTEST_EAM.format(units=units, style=style, coeffs=coeffs, runstyle=STOCK_LOOP)
+    r = run_lmp(LMP_B200, text, tmp_path, ["-sf", "b200"])
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    pe = [row[1] for row in thermo_rows_generic(r.stdout, "Step", "PotEng")]
+    for phase, fn, e in (("init", "init.txt", pe[0]), ("run", "run.txt", pe[-1])):
+        f = read_forces(tmp_path / fn)
+        ref = g[f"{phase}_forces"]
+        assert np.abs(f - ref).max() <= 1e-10 * np.abs(ref).max(), phase
+        assert abs(e - float(g[f"{phase}_vdwl"])) <= 1e-10 * abs(float(g[f"{phase}_vdwl"])), phase
