@@ -210,7 +210,7 @@ int b200md_host_eam_force(b200md_ctx *ctx, const double *fp_all, int eflag, int 
                           double *virial);
 
 /* ---- bench/in.chain additions: bond_style fene, special_bonds fene, fix langevin -------------------
- * One-rank contexts only for now; they take effect inside b200md_setup / b200md_run (Verlet::setup / run order:
+ * They take effect inside b200md_setup / b200md_run (Verlet::setup / run order:
  * pair force, bond force, post_force fixes, final_integrate; src/verlet.cpp:106-160,232-360).
  *
  * b200md_set_bonds: the molecular atom style's per-atom bond arrays in the caller's local order -- num_bond[n],
@@ -219,7 +219,10 @@ int b200md_host_eam_force(b200md_ctx *ctx, const double *fp_all, int eflag, int 
  * Replaces NTopoBondAll::build (src/ntopo_bond_all.cpp:37-76): the partner's closest image
  * (Domain::closest_image) is resolved inside the neighbor build, which also leaves 1-2 partners out of the pair
  * list (special_bonds fene = lj 0.0 1.0 1.0, src/npair.h:125-158).  A partner farther than the neighbor cutoff
- * is "Bond atoms missing" (B200MD_ERR_LOST_ATOMS at the next build).  Up to 4 bonds per atom.  n = 0 removes them. */
+ * is "Bond atoms missing" (B200MD_ERR_LOST_ATOMS at the next build).  Up to 4 bonds per atom.  n = 0 removes them.
+ * The library keeps the topology as a table by atom TAG, so on several ranks every rank passes the COMPLETE
+ * topology (all atoms of the system, any order), not only the bonds of the atoms it owns; the table then needs no
+ * update when atoms migrate. */
 int b200md_set_bonds(b200md_ctx *ctx, int n, const int *tag, int bond_per_atom, const int *num_bond,
                      const int *bond_type, const int *bond_atom, int newton_bond);
 /* bond_style fene + bond_coeff K R0 epsilon sigma, arrays [nbondtypes+1] indexed by bond type
@@ -227,8 +230,9 @@ int b200md_set_bonds(b200md_ctx *ctx, int n, const int *tag, int bond_per_atom, 
  * next neighbor build as B200MD_ERR_ARG. */
 int b200md_bond_fene(b200md_ctx *ctx, int nbondtypes, const double *k, const double *r0, const double *epsilon,
                      const double *sigma);
-/* bond energy (thermo E_bond) and bond virial[6] of the last force evaluation that tallied them
- * (Bond::energy / Bond::virial, src/bond.h:33-35); b200md_thermo's pressure already includes the bond virial */
+/* bond energy (thermo E_bond) and bond virial[6] of the last force evaluation that tallied them, summed over
+ * the ranks (collective, like b200md_thermo) (Bond::energy / Bond::virial, src/bond.h:33-35 -> compute pe /
+ * pressure); b200md_thermo's pressure already includes the bond virial */
 int b200md_thermo_bond(b200md_ctx *ctx, double *eng_bond, double *virial);
 /* fix langevin t_start t_stop damp seed, plain instance (no zero / tally / gjf / omega / per-type scale;
  * FixLangevin::post_force_templated<0,0,0,0,0,0>, src/fix_langevin.cpp:583-716), dt = update->dt.

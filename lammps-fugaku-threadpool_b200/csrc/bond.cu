@@ -359,7 +359,6 @@ extern "C" int b200md_set_bonds(b200md_ctx *c, int n, const int *tag, int bond_p
   }
   if (n < 0 || bond_per_atom < 0 || !tag || !num_bond || !bond_type || !bond_atom)
     return b200md_fail(c, B200MD_ERR_ARG, "set_bonds: tag, num_bond, bond_type, bond_atom are required");
-  if (c->nranks > 1) return b200md_fail(c, B200MD_ERR_ARG, "set_bonds: every rank needs the whole topology table; one-rank contexts only for now");
   int ntags = 0;
   for (int i = 0; i < n; i++) ntags = std::max(ntags, tag[i]);
   std::vector<int> deg((size_t) ntags + 1, 0);
@@ -425,8 +424,16 @@ extern "C" int b200md_thermo_bond(b200md_ctx *c, double *eng_bond, double *viria
   NEED_CTX();
   if (!c->bonds.maxb) return b200md_fail(c, B200MD_ERR_ARG, "thermo_bond: no bonds defined");
   if (!c->have_ev) return b200md_fail(c, B200MD_ERR_ARG, "no force evaluation has tallied energy/virial yet");
-  if (eng_bond) *eng_bond = c->bonds.eng_bond;
-  if (virial) for (int k = 0; k < 6; k++) virial[k] = c->bonds.virial_bond[k];
+  double loc[7] = {c->bonds.eng_bond, c->bonds.virial_bond[0], c->bonds.virial_bond[1], c->bonds.virial_bond[2],
+                   c->bonds.virial_bond[3], c->bonds.virial_bond[4], c->bonds.virial_bond[5]};
+  if (c->nranks > 1) {  // collective, like b200md_thermo: Bond::energy / virial summed over the ranks (compute pe, pressure)
+    CU(cudaMemcpyAsync(c->red_d + 16, loc, sizeof(loc), cudaMemcpyHostToDevice, c->stream));
+    TRY(comm_allreduce_sum(c, c->red_d + 16, 7));
+    CU(cudaMemcpyAsync(loc, c->red_d + 16, sizeof(loc), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+  }
+  if (eng_bond) *eng_bond = loc[0];
+  if (virial) for (int k = 0; k < 6; k++) virial[k] = loc[1 + k];
   return B200MD_OK;
 }
 

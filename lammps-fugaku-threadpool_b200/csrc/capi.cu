@@ -671,9 +671,14 @@ extern "C" int b200md_thermo(b200md_ctx *c, double natoms_total, double *out)
     CU(cudaMemcpyAsync(loc, c->red_d + 16, sizeof(loc), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
   }
-  // ComputePressure::virial_compute adds the bond virial to the pair virial (src/compute_pressure.cpp:314-341);
-  // bonded contexts are one-rank (b200md_set_bonds), so no reduction
-  const double vbond = c->bonds.maxb ? c->bonds.virial_bond[0] + c->bonds.virial_bond[1] + c->bonds.virial_bond[2] : 0.0;
+  // ComputePressure::virial_compute adds the bond virial to the pair virial (src/compute_pressure.cpp:314-341)
+  double vbond = c->bonds.maxb ? c->bonds.virial_bond[0] + c->bonds.virial_bond[1] + c->bonds.virial_bond[2] : 0.0;
+  if (c->bonds.maxb && c->nranks > 1) {
+    CU(cudaMemcpyAsync(c->red_d + 16, &vbond, sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    TRY(comm_allreduce_sum(c, c->red_d + 16, 1));
+    CU(cudaMemcpyAsync(&vbond, c->red_d + 16, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+  }
   // ComputeTemp (src/compute_temp.cpp:55-100): dof = 3N - 3; ComputePressure (src/compute_pressure.cpp:228-260);
   // KE = 0.5*dof*boltz*T (src/thermo.cpp:1712-1717)
   const double dof = 3.0 * natoms_total - 3.0;

@@ -384,3 +384,68 @@ def test_emu_eam_alloy_error_paths(emu, tmp_path):
                                               ("unittest_atomic_pair_eam_fs_real", "real", "eam/fs")])
 def test_emu_lammps_unittest_eam_alloy_fs_yaml(emu_lmp, name, units, style, tmp_path):
     lh.test_reference_unittest_eam_alloy_fs_yaml_through_lammps(name, units, style, tmp_path)
+
+
+def test_emu_chain_decomposed_equals_single(emu):
+    """in.chain on 8 emulated ranks (every rank holds the complete bond table by tag, its own atoms, the counter-based
+    thermostat) == the same run on one rank: bonds whose partner lives on another rank resolve through ghost tags,
+    tables need no update when beads migrate, bond energy / virial are summed over the ranks"""
+    g = load_golden("chain_32k")
+    steps, world, grid = 30, 8, (2, 2, 2)
+    lo, hi = g["in_boxlo"], g["in_boxhi"]
+    num, btype, batom = chain.bond_arrays(g["in_tag"], g["in_bonds"])
+
+    def build(rank, nranks, nccl_id, procgrid, sel):
+        md = emu.B200MD(units="lj", ntypes=1, device=rank, nranks=nranks, rank=rank, nccl_id=nccl_id, procgrid=procgrid)
+        md.box(lo, hi)
+        md.set_mass(1, 1.0)
+        p = md.pair_style("lj/cut", 1.12)
+        p.coeff(1, 1, 1.0, 1.0, 1.12)
+        p.modify(shift=True)
+        md.neighbor.set(0.4, "bin")
+        md.neighbor.modify(every=1, delay=1, check=True)
+        md.timestep(0.012)
+        md.create_atoms(g["in_x"][sel], g["in_v"][sel], g["in_type"][sel], g["in_tag"][sel], natoms_total=len(g["in_tag"]))
+        md.bonds(g["in_tag"], num, btype, batom)          # the COMPLETE topology on every rank
+        md.bond_style("fene", 1).coeff(1, 30.0, 1.5, 1.0, 1.0)
+        md.fix("langevin", 1.0, 1.0, 10.0, 904297, rng="counter")
+        return md
+
+    one = build(0, 1, None, (1, 1, 1), slice(None))
+    one.run(steps)
+    t1, g1 = one.thermo_log[-1], one.gather()
+    one.close()
+
+    frac = (g["in_x"] - lo) / (hi - lo)
+    cell = np.minimum((frac * np.array(grid)).astype(int), np.array(grid) - 1)
+    owner = cell[:, 0] + grid[0] * (cell[:, 1] + grid[1] * cell[:, 2])
+    nccl_id, res, errs = emu.lib.nccl_unique_id(), [None] * world, []
+
+    def worker(rank):
+        try:
+            md = build(rank, world, nccl_id, grid, owner == rank)
+            md.run(steps)
+            res[rank] = (md.thermo_log[-1], md.gather(), md.neigh_stats()["builds"])
+            md.close()
+        except BaseException as e:  # noqa: BLE001
+            errs.append((rank, e))
+            print(f"emulated rank {rank} failed: {e!r}", file=sys.stderr, flush=True)
+            C.CDLL(str(Path(emu_build_dir()) / "libnccl_emu.so")).fake_nccl_break_all()
+            raise
+
+    th = [threading.Thread(target=worker, args=(r,)) for r in range(world)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not errs, errs
+    t8 = res[0][0]
+    for k in ("evdwl", "ebond", "ke", "temp", "press"):
+        assert abs(t8[k] - t1[k]) <= 1e-6 * abs(t1[k]), k
+    tag = np.concatenate([r[1]["tag"] for r in res])
+    x = np.concatenate([r[1]["x"] for r in res])
+    assert sorted(tag.tolist()) == list(range(1, len(g["in_tag"]) + 1))
+    o = np.argsort(tag)
+    dx = x[o] - g1["x"]
+    dx -= (hi - lo) * np.round(dx / (hi - lo))
+    assert np.abs(dx).max() < 1e-6
