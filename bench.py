@@ -52,6 +52,9 @@ def parse_args():
     ap.add_argument("--cells", type=int, default=160, help="fcc cells per GPU per dimension for LJ (160 -> 16.384 M atoms)")
     ap.add_argument("--eam-cells", type=int, default=100, help="fcc cells per GPU per dimension for EAM (100 -> 4 M atoms)")
     ap.add_argument("--no-eam", action="store_true")
+    ap.add_argument("--chain", type=int, default=0, metavar="R",
+                    help="also run bench/in.chain replicated R x R x R (32 000 R^3 beads; one GPU only; opt-in: the bonded "
+                         "path has not run on hardware yet)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -255,6 +258,47 @@ def run_workload(torch, dist, pkg, kind, cells, args, device, nranks, rank, nccl
     return out, md
 
 
+def run_chain(torch, dist, pkg, r, args, device):
+    """BASELINE configs[2]: bench/in.chain (FENE bead-spring melt, special_bonds fene, fix nve + fix langevin) replicated
+    r^3 times like `replicate r r r`, on one GPU.  The thermostat draws from the counter-based device generator (the
+    RanMars replay that reproduces the reference's trajectory is a one-rank parity mode with a host draw per step)."""
+    g = dict(np.load(ROOT / "tests" / "golden" / "chain_32k.npz"))
+    R = pkg.inputs.replicate_chain(g, r)
+    md = pkg.B200MD(units="lj", ntypes=1, device=device)
+    md.box(R["boxlo"], R["boxhi"])
+    md.set_mass(1, 1.0)
+    p = md.pair_style("lj/cut", 1.12)
+    p.coeff(1, 1, 1.0, 1.0, 1.12)
+    p.modify(shift=True)
+    md.neighbor.set(0.4, "bin")
+    md.neighbor.modify(every=1, delay=1, check=True)
+    md.timestep(0.012)
+    md.create_atoms(R["x"], R["v"], R["type"], R["tag"])
+    md.special_bonds("fene")
+    md.bonds(R["tag"], *pkg.inputs.bond_arrays(R["tag"], R["bonds"]))
+    md.bond_style("fene", 1).coeff(1, 30.0, 1.5, 1.0, 1.0)
+    md.fix("langevin", 1.0, 1.0, 10.0, 904297, rng="counter")
+    natoms = len(R["tag"])
+    del R
+    md.setup()
+    out = dict(natoms=natoms, thermo0=md.thermo_log[-1])
+    md.timers(reset=True)
+    ms = time_resident(torch, dist, md, args.steps, args.warmup, device, 1)
+    out["ms"] = ms
+    out["value"] = natoms * args.steps / (ms * 1e-3) / 1e6
+    out["launches"] = int(round(md.timers()["launches"] * args.steps / (args.steps + args.warmup)))
+    md.ctx.call("b200md_profile", 1)
+    kernel_times(md, reset=True)
+    time_resident(torch, dist, md, args.steps, 0, device, 1)
+    kms, kcnt = kernel_times(md, reset=True)
+    md.ctx.call("b200md_profile", 0)
+    out["kernel_ms"] = {k: (float(kms[i]), int(kcnt[i])) for i, k in enumerate(["pair+bond", "eam_rho", "neigh", "nve", "halo", "sort"])}
+    out["thermo1"] = md.thermo()
+    out["neigh"] = md.neigh_stats()
+    md.close()
+    return out
+
+
 def run_e2e(torch, dist, md, out, args, device, nranks):
     """End to end through host buffers: every rank moves its own atoms over its own PCIe link every step."""
     k = max(3, min(args.steps, 20))
@@ -445,6 +489,13 @@ def main():
     if not args.no_eam:
         eam, md_eam = run_workload(torch, dist, pkg, "eam", args.eam_cells, args, local, world, rank, nccl_id, grid, loc, allsum)
 
+    chain = None
+    if args.chain > 0 and world == 1:
+        try:
+            chain = run_chain(torch, dist, pkg, args.chain, args, local)
+        except Exception as e:  # noqa: BLE001  (opt-in extra: never lose the headline line over it)
+            chain = {"error": repr(e)}
+
     def emit(e2e_error=None):
         if rank != 0:
             return
@@ -497,6 +548,12 @@ def main():
                            "step_frac_of_hbm_peak": BYTES_EAM_STEP * eam["atoms_per_gpu"] / (eam["ms"] / args.steps * 1e-3) / 1e9 / peak,
                            "kernel_ms": eam["kernel_ms"], "gpu_launches": eam["launches"], "clocks": eam["clocks"],
                            "thermo": {"step0": eam["thermo0"], "last": eam["thermo1"]}, "neigh": eam["neigh"], "e2e": eam.get("e2e")}
+        if chain is not None:
+            line["chain"] = chain if "error" in chain else {
+                "value": chain["value"], "unit": "Matom-steps/s", "ms_per_step": chain["ms"] / args.steps,
+                "workload": f"bench/in.chain replicated {args.chain}^3 = {chain['natoms']} beads on one GPU, counter-based thermostat",
+                "kernel_ms": chain["kernel_ms"], "gpu_launches": chain["launches"], "neigh": chain["neigh"],
+                "thermo": {"step0": chain["thermo0"], "last": chain["thermo1"]}}
         if world == 1 and not args.no_cpu and not e2e_error:
             line["cpu_baseline"] = cpu_measure("lj", 100, 10, budget_s=20.0, cells_cap=args.cells)
             if eam is not None:

@@ -99,3 +99,51 @@ def velocity_finish(v: np.ndarray, mass_per_atom: np.ndarray, t_desired: float, 
 
 def velocity_create_geom(x, mass_per_atom, t_desired, seed, units="lj"):
     return velocity_finish(velocity_loop_geom_raw(x, seed), mass_per_atom, t_desired, units)
+
+
+def replicate_chain(g: dict, r: int) -> dict:
+    """`replicate r r r` (src/replicate.cpp) of the bench/data.chain system as tests/golden/chain_32k.npz holds it
+    (in_x, in_v, in_type, in_tag, in_image, in_bonds, in_boxlo, in_boxhi): every replica is the UNWRAPPED molecule set
+    (x + image * L) shifted by whole box lengths, tags and bond partners offset by replica * natoms, then wrapped into
+    the r-times larger box -- so chains that cross the periodic boundary of the small box stay connected.
+    Returns x, v, type, tag, bonds (type, a, b), boxlo, boxhi."""
+    lo, hi = np.asarray(g["in_boxlo"], dtype=np.float64), np.asarray(g["in_boxhi"], dtype=np.float64)
+    L = hi - lo
+    n = len(g["in_tag"])
+    xu = np.asarray(g["in_x"], dtype=np.float64) + np.asarray(g["in_image"], dtype=np.float64) * L
+    xs, vs, tags, bonds = [], [], [], []
+    for k in range(r):
+        for j in range(r):
+            for i in range(r):
+                rep = (k * r + j) * r + i
+                xs.append(xu + np.array([i, j, k]) * L)
+                vs.append(g["in_v"])
+                tags.append(np.asarray(g["in_tag"], dtype=np.int64) + rep * n)
+                b = np.array(g["in_bonds"], dtype=np.int64)
+                b[:, 1:] += rep * n
+                bonds.append(b)
+    x = np.concatenate(xs)
+    big = L * r
+    x = lo + np.mod(x - lo, big)
+    x = np.where(x >= lo + big, lo, x)   # mod() can round up to the upper face
+    return dict(x=x, v=np.concatenate(vs), type=np.tile(np.asarray(g["in_type"], dtype=np.int32), r ** 3),
+                tag=np.concatenate(tags).astype(np.int32), bonds=np.concatenate(bonds).astype(np.int32), boxlo=lo, boxhi=lo + big)
+
+
+def bond_arrays(tag, bonds):
+    """data-file `Bonds` rows (type a1 a2) -> num_bond[n], bond_type[n][bpa], bond_atom[n][bpa] in the local order of
+    `tag`, each bond stored on a1 (newton_bond on; Atom::data_bonds src/atom.cpp:1380-1460).  Vectorised: the chain
+    benchmark replicates to millions of bonds."""
+    tag = np.asarray(tag)
+    bonds = np.asarray(bonds)
+    order = np.argsort(tag, kind="stable")
+    where = order[np.searchsorted(tag[order], bonds[:, 1])]
+    num = np.bincount(where, minlength=len(tag)).astype(np.int32)
+    bpa = max(1, int(num.max()))
+    o = np.argsort(where, kind="stable")
+    slot = np.arange(len(o)) - np.repeat(np.cumsum(num) - num, num)
+    btype = np.zeros((len(tag), bpa), dtype=np.int32)
+    batom = np.zeros((len(tag), bpa), dtype=np.int32)
+    btype[where[o], slot] = bonds[o, 0]
+    batom[where[o], slot] = bonds[o, 2]
+    return num, btype, batom

@@ -449,3 +449,42 @@ def test_emu_chain_decomposed_equals_single(emu):
     dx = x[o] - g1["x"]
     dx -= (hi - lo) * np.round(dx / (hi - lo))
     assert np.abs(dx).max() < 1e-6
+
+
+def test_emu_replicated_chain_and_bench_leg(emu, monkeypatch):
+    """(1) inputs.replicate_chain(2): 256 000 beads whose step-0 energies are exactly 8 x the reference's for the 32 000
+    (a periodic system replicated is the same physics), same pressure, no bond longer than R0; (2) bench.py's opt-in
+    chain leg wired end to end (the CUDA-event timer replaced by a plain run)"""
+    import types
+
+    import bench
+
+    g = load_golden("chain_32k")
+    R = emu.inputs.replicate_chain(g, 2)
+    md = emu.B200MD(units="lj", ntypes=1)
+    md.box(R["boxlo"], R["boxhi"])
+    md.set_mass(1, 1.0)
+    p = md.pair_style("lj/cut", 1.12)
+    p.coeff(1, 1, 1.0, 1.0, 1.12)
+    p.modify(shift=True)
+    md.neighbor.set(0.4, "bin")
+    md.neighbor.modify(every=1, delay=1, check=True)
+    md.timestep(0.012)
+    md.create_atoms(R["x"], R["v"], R["type"], R["tag"])
+    md.bonds(R["tag"], *emu.inputs.bond_arrays(R["tag"], R["bonds"]))
+    md.bond_style("fene", 1).coeff(1, 30.0, 1.5, 1.0, 1.0)
+    md.setup()
+    t = md.thermo_log[-1]
+    evdwl, ebond, ke, temp, press = g["a_thermo"]
+    np.testing.assert_allclose([t["evdwl"], t["ebond"], t["ke"]], [8 * evdwl, 8 * ebond, 8 * ke], rtol=1e-10)
+    np.testing.assert_allclose(t["press"], press, rtol=1e-10)
+    md.close()
+
+    def plain_timer(torch, dist, md, steps, warmup, device, nranks):
+        md.ctx.call("b200md_run", warmup + steps, md.dt, 0)
+        return 1.0
+
+    monkeypatch.setattr(bench, "time_resident", plain_timer)
+    out = bench.run_chain(None, None, emu, 1, types.SimpleNamespace(steps=3, warmup=1), 0)
+    assert out["natoms"] == 32000 and out["neigh"]["builds"] >= 1 and out["launches"] > 0
+    assert abs(out["thermo1"]["temp"] - 1.0) < 0.05 and out["kernel_ms"]["neigh"][1] >= 0

@@ -138,3 +138,32 @@ def test_chain_error_paths(pkg):
         md.setup()
     assert "bond coeffs" in str(e.value)
     md.close()
+
+
+@FIRST_RUN
+def test_replicated_chain_energies_scale(pkg):
+    """size-independent property at a size the oracle would take minutes for: bench/in.chain replicated 4^3 (2.05 M
+    beads) has exactly 64 x the reference's step-0 energies and the same pressure"""
+    g = load_golden("chain_32k")
+    R = pkg.inputs.replicate_chain(g, 4)
+    md = pkg.B200MD(units="lj", ntypes=1)
+    md.box(R["boxlo"], R["boxhi"])
+    md.set_mass(1, 1.0)
+    p = md.pair_style("lj/cut", 1.12)
+    p.coeff(1, 1, 1.0, 1.0, 1.12)
+    p.modify(shift=True)
+    md.neighbor.set(0.4, "bin")
+    md.neighbor.modify(every=1, delay=1, check=True)
+    md.timestep(0.012)
+    md.create_atoms(R["x"], R["v"], R["type"], R["tag"])
+    md.bonds(R["tag"], *pkg.inputs.bond_arrays(R["tag"], R["bonds"]))
+    md.bond_style("fene", 1).coeff(1, 30.0, 1.5, 1.0, 1.0)
+    md.fix("langevin", 1.0, 1.0, 10.0, 904297, rng="counter")
+    md.setup()
+    t = md.thermo_log[-1]
+    evdwl, ebond, ke, temp, press = g["a_thermo"]
+    np.testing.assert_allclose([t["evdwl"], t["ebond"], t["ke"]], [64 * evdwl, 64 * ebond, 64 * ke], rtol=1e-10)
+    np.testing.assert_allclose(t["press"], press, rtol=1e-10)
+    md.run(20)
+    assert abs(md.thermo_log[-1]["temp"] - 1.0) < 0.02
+    md.close()
