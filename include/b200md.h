@@ -156,6 +156,13 @@ int b200md_pair_compute(b200md_ctx *ctx, int eflag, int vflag, double *eng_vdwl,
 
 /* ---- fix nve : FixNVE::initial_integrate/final_integrate (src/fix_nve.cpp:64-141) ---------
  * dtv = dt, dtf = 0.5*dt*ftm2v (src/fix_nve.cpp:51-58) */
+/* eflag_atom / vflag_atom (Pair::ev_tally per-atom tallies, src/pair.cpp:1037-1097; what compute pe/atom and
+ * compute stress/atom read from Pair::eatom / vatom): call after a force evaluation at the current positions.
+ * The tallies are a pass of their own over the same list (the timestep kernels carry no per-atom stores).
+ * b200md_peratom_download: eatom[nlocal], vatom[nlocal][6] (xx yy zz xy xz yz), either may be NULL, in the
+ * order of b200md_download_atoms (host-ghost mode: the caller's own order).  Pair contributions only. */
+int b200md_pair_peratom(b200md_ctx *ctx);
+int b200md_peratom_download(b200md_ctx *ctx, double *eatom, double *vatom);
 int b200md_nve_initial(b200md_ctx *ctx, double dtv, double dtf);
 int b200md_nve_final(b200md_ctx *ctx, double dtf);
 

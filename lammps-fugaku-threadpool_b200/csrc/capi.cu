@@ -85,7 +85,7 @@ extern "C" int b200md_destroy(b200md_ctx *c)
   dev_free(c, c->perm); dev_free(c, c->scan_tmp); dev_free(c, c->binrec); dev_free(c, c->atom_sub); dev_free(c, c->numneigh); dev_free(c, c->neigh); dev_free(c, c->tile_ghost);
   dev_free(c, c->send_idx); dev_free(c, c->border_blockcnt); dev_free(c, c->border_total); dev_free(c, c->send_dir);
   dev_free(c, c->sendbuf_i); dev_free(c, c->allcounts); dev_free(c, c->sendbuf4); dev_free(c, c->recvbuf4); dev_free(c, c->sendbuf1);
-  dev_free(c, c->partials); dev_free(c, c->stage);
+  dev_free(c, c->partials); dev_free(c, c->stage); dev_free(c, c->peratom);
   bond_release(c);
   if (c->lj.d) cudaFree(c->lj.d);
   if (c->eam.frho) cudaFree(c->eam.frho);
@@ -203,6 +203,14 @@ __global__ void k_update_pos(const double *__restrict__ x3, double4 *__restrict_
   double4 p = pos[i];
   p.x = x3[3 * i]; p.y = x3[3 * i + 1]; p.z = x3[3 * i + 2];
   pos[i] = p;
+}
+
+__global__ void k_soa6_to_aos(const double *__restrict__ src, size_t stride, double *__restrict__ dst, int n)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+#pragma unroll
+  for (int k = 0; k < 6; k++) dst[(size_t) i * 6 + k] = src[(size_t) k * stride + i];
 }
 
 static int stage_bytes(b200md_ctx *c, size_t bytes)
@@ -641,6 +649,44 @@ extern "C" int b200md_pair_compute(b200md_ctx *c, int eflag, int vflag, double *
     if (eng_vdwl) *eng_vdwl = c->eng_vdwl;
     if (virial) for (int k = 0; k < 6; k++) virial[k] = c->virial[k];
   }
+  return B200MD_OK;
+}
+
+// eflag_atom / vflag_atom: a pass of its own after the force evaluation (pair_lj.cu, pair_eam.cu)
+extern "C" int b200md_pair_peratom(b200md_ctx *c)
+{
+  NEED_CTX();
+  if (!c->list_valid) return b200md_fail(c, B200MD_ERR_ARG, "pair_peratom before the first neighbor build");
+  if (c->cl != 1) return b200md_fail(c, B200MD_ERR_ARG, "per-atom tallies need the per-atom list (cluster size 1)");
+  const int n = c->nlocal;
+  const size_t stride = ((size_t) n + 31) / 32 * 32;
+  TRY(dev_ensure(c, c->peratom, 7 * stride));
+  c->peratom_stride = stride;
+  c->peratom_n = 0;
+  {
+    Sect s(c, SECT_PAIR);
+    if (c->pair_style == 1) TRY(pair_lj_peratom(c, c->peratom.p, stride));
+    else if (c->pair_style == 2) TRY(pair_eam_peratom(c, c->peratom.p, stride));
+    else return b200md_fail(c, B200MD_ERR_ARG, "no pair style defined");
+  }
+  c->peratom_n = n;
+  return B200MD_OK;
+}
+
+extern "C" int b200md_peratom_download(b200md_ctx *c, double *eatom, double *vatom)
+{
+  NEED_CTX();
+  const int n = c->peratom_n;
+  if (n <= 0 || n != c->nlocal) return b200md_fail(c, B200MD_ERR_ARG, "peratom_download: call b200md_pair_peratom after the force evaluation first");
+  if (eatom) CU(cudaMemcpyAsync(eatom, c->peratom.p, (size_t) n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  if (vatom) {
+    // device [6][stride] -> host [n][6] through the staging buffer
+    TRY(stage_bytes(c, (size_t) n * 48));
+    k_soa6_to_aos<<<cdiv(n, 256), 256, 0, c->stream>>>(c->peratom.p + c->peratom_stride, c->peratom_stride, c->stage.p, n);
+    LAUNCH_CHECK();
+    CU(cudaMemcpyAsync(vatom, c->stage.p, (size_t) n * 48, cudaMemcpyDeviceToHost, c->stream));
+  }
+  CU(cudaStreamSynchronize(c->stream));
   return B200MD_OK;
 }
 

@@ -194,6 +194,9 @@ struct b200md_ctx {
 
   // reductions / flags
   DevBuf<double> partials;  // [nblocks][8]
+  DevBuf<double> peratom;   // [7][peratom_stride]: eatom, vatom xx yy zz xy xz yz of the owned atoms (b200md_pair_peratom)
+  size_t peratom_stride = 0;
+  int peratom_n = 0;        // owned atoms the tallies are valid for, 0 = none
   double *red_d = nullptr;  // [16] device results
   double *red_h = nullptr;  // pinned mirror
   int *flags_d = nullptr;   // [8]: 0 nonfinite, 1 overflow(max count), 2 moved, 3 lost
@@ -337,6 +340,8 @@ int nve_initial(b200md_ctx *c, double dtv, double dtf);
 int nve_final(b200md_ctx *c, double dtf);
 int thermo_ke(b200md_ctx *c, double *sum_mv2);
 int reduce_partials(b200md_ctx *c, int nblocks, int ncomp, int dst);  // partials -> red_d[dst..]
+int pair_lj_peratom(b200md_ctx *c, double *out, size_t stride);       // eatom / vatom pass, out = [7][stride]
+int pair_eam_peratom(b200md_ctx *c, double *out, size_t stride);
 
 // device helpers
 // one 32-byte gather of a position record: sm_100 has 256-bit global loads (LDG.E.ENL2.256), which halves the

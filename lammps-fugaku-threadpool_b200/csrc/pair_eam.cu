@@ -559,3 +559,80 @@ int pair_eam_force_part(b200md_ctx *c, int part)
   LAUNCH_CHECK();
   return B200MD_OK;
 }
+
+// ---- per-atom tallies (see pair_lj.cu): eatom = F(rho_i) + half of each pair's phi, vatom = half of each pair's
+// del x del * fpair (pair_eam.cpp:240-246, 300-323 with eflag_atom / vflag_atom).  Runs after a force evaluation at
+// the current positions: rho of the owned atoms and fp of owned + ghost atoms are in place.
+__global__ void __launch_bounds__(128)
+k_eam_peratom(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
+              int nlocal, EAMParams P, const double *__restrict__ rho, const double *__restrict__ fp, const double4 *__restrict__ posfp,
+              double *__restrict__ out, size_t stride)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nlocal) return;
+  const int nt1 = P.ntypes + 1;
+  const double4 pi = pos[i];
+  const int it = pos_type(pi);
+  const double fpi = posfp ? posfp[i].w : fp[i];
+  double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  {  // embedding energy of atom i (pass B)
+    double p = rho[i] * P.rdrho + 1.0;
+    int m = (int) p;
+    m = max(1, min(m, P.nrho - 1));
+    p -= m;
+    p = fmin(p, 1.0);
+    const double *cf = P.frho + ((size_t) P.type2frho[it] * (P.nrho + 1) + m) * 7;
+    double phi = ((__ldg(cf + 3) * p + __ldg(cf + 4)) * p + __ldg(cf + 5)) * p + __ldg(cf + 6);
+    if (rho[i] > P.rhomax) phi += fpi * (rho[i] - P.rhomax);
+    acc[0] = phi;
+  }
+  const int n = numneigh[i];
+  const int *nb = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
+  for (int k = 0; k < n; k++) {
+    const int j = __ldg(nb + (size_t) k * TILE) & CLJMASK;
+    const double4 pj = pos[j];
+    const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+    const double rsq = dx * dx + dy * dy + dz * dz;
+    if (rsq >= P.cutforcesq) continue;
+    const int jt = pos_type(pj);
+    const double fpj = posfp ? posfp[j].w : fp[j];
+    const double r = sqrt(rsq);
+    double p = r * P.rdr + 1.0;
+    int m = (int) p;
+    m = min(m, P.nr - 1);
+    p -= m;
+    p = fmin(p, 1.0);
+    const double *c1 = P.rhor + ((size_t) P.type2rhor[it * nt1 + jt] * (P.nr + 1) + m) * 7;
+    const double *c2 = P.rhor + ((size_t) P.type2rhor[jt * nt1 + it] * (P.nr + 1) + m) * 7;
+    const double *c3 = P.z2r + ((size_t) P.type2z2r[it * nt1 + jt] * (P.nr + 1) + m) * 7;
+    const double rhoip = (__ldg(c1) * p + __ldg(c1 + 1)) * p + __ldg(c1 + 2);
+    const double rhojp = (__ldg(c2) * p + __ldg(c2 + 1)) * p + __ldg(c2 + 2);
+    const double z2p = (__ldg(c3) * p + __ldg(c3 + 1)) * p + __ldg(c3 + 2);
+    const double z2 = ((__ldg(c3 + 3) * p + __ldg(c3 + 4)) * p + __ldg(c3 + 5)) * p + __ldg(c3 + 6);
+    const double recip = 1.0 / r;
+    const double phi = z2 * recip;
+    const double phip = z2p * recip - phi * recip;
+    const double psip = fpi * rhojp + fpj * rhoip + phip;
+    const double hf = -0.5 * psip * recip;
+    acc[0] += 0.5 * phi;
+    acc[1] += dx * dx * hf;
+    acc[2] += dy * dy * hf;
+    acc[3] += dz * dz * hf;
+    acc[4] += dx * dy * hf;
+    acc[5] += dx * dz * hf;
+    acc[6] += dy * dz * hf;
+  }
+#pragma unroll
+  for (int c = 0; c < 7; c++) out[(size_t) c * stride + i] = acc[c];
+}
+
+int pair_eam_peratom(b200md_ctx *c, double *out, size_t stride)
+{
+  const int n = c->nlocal;
+  const EAMParams P = eam_params(c);
+  // single-type path: fp of owned and ghost atoms lives in the {x,y,z,fp} records; generic path: in fp[nall]
+  const double4 *posfp = eam_use_1t(c) ? c->posfp.p : nullptr;
+  k_eam_peratom<<<cdiv(n, 128), 128, 0, c->stream>>>(c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, c->rho.p, c->fp.p, posfp, out, stride);
+  LAUNCH_CHECK();
+  return B200MD_OK;
+}

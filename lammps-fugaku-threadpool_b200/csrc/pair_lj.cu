@@ -317,3 +317,50 @@ int pair_lj_compute_part(b200md_ctx *c, int part)
   LAUNCH_CHECK();
   return B200MD_OK;
 }
+
+// ---- per-atom tallies (eflag_atom / vflag_atom: Pair::ev_tally, src/pair.cpp:1037-1097) ----------------------
+// A pass of its own over the same list, so the timestep kernels above carry no extra stores or registers: per-atom
+// energy and virial are wanted on dump / thermo steps only (compute pe/atom, compute stress/atom).  With the full
+// list every atom takes half of each of its pairs -- exactly what the reference's half list gives both partners.
+// out = [7][stride]: energy, then the virial components xx yy zz xy xz yz.
+__global__ void __launch_bounds__(128)
+k_lj_peratom(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
+             int nlocal, const double *__restrict__ tables, int ntypes, double *__restrict__ out, size_t stride)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nlocal) return;
+  const int nt1 = ntypes + 1, nt2 = nt1 * nt1;
+  const double4 pi = pos[i];
+  const int trow = pos_type(pi) * nt1;
+  const int n = numneigh[i];
+  const int *nb = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
+  double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  for (int k = 0; k < n; k++) {
+    const int j = __ldg(nb + (size_t) k * TILE) & CLJMASK;
+    const double4 pj = pos[j];
+    const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+    const double rsq = dx * dx + dy * dy + dz * dz;
+    const int t = trow + pos_type(pj);
+    if (rsq >= __ldg(tables + t)) continue;
+    const double r2inv = 1.0 / rsq, r6inv = r2inv * r2inv * r2inv;
+    const double fpair = r6inv * (__ldg(tables + nt2 + t) * r6inv - __ldg(tables + 2 * nt2 + t)) * r2inv;
+    acc[0] += 0.5 * (r6inv * (__ldg(tables + 3 * nt2 + t) * r6inv - __ldg(tables + 4 * nt2 + t)) - __ldg(tables + 5 * nt2 + t));
+    const double hf = 0.5 * fpair;
+    acc[1] += dx * dx * hf;
+    acc[2] += dy * dy * hf;
+    acc[3] += dz * dz * hf;
+    acc[4] += dx * dy * hf;
+    acc[5] += dx * dz * hf;
+    acc[6] += dy * dz * hf;
+  }
+#pragma unroll
+  for (int c = 0; c < 7; c++) out[(size_t) c * stride + i] = acc[c];
+}
+
+int pair_lj_peratom(b200md_ctx *c, double *out, size_t stride)
+{
+  const int n = c->nlocal;
+  k_lj_peratom<<<cdiv(n, 128), 128, 0, c->stream>>>(c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, c->lj.d, c->lj.ntypes, out, stride);
+  LAUNCH_CHECK();
+  return B200MD_OK;
+}

@@ -101,3 +101,17 @@ void B200Device::sync_settings()
     B200_CHECK(this, b200md_set_mass(ctx, nt, m.data()));
   }
 }
+
+void B200Device::peratom_to_host(int nlocal, double *eatom, double **vatom)
+{
+  std::vector<double> e, v;
+  if (eatom) e.resize(nlocal);
+  if (vatom) v.resize((size_t) 6 * nlocal);
+  check(b200md_pair_peratom(ctx), FLERR);
+  check(b200md_peratom_download(ctx, eatom ? e.data() : nullptr, vatom ? v.data() : nullptr), FLERR);
+  for (int i = 0; i < nlocal; i++) {
+    if (eatom) eatom[i] += e[i];
+    if (vatom)
+      for (int k = 0; k < 6; k++) vatom[i][k] += v[(size_t) 6 * i + k];
+  }
+}

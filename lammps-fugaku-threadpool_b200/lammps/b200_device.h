@@ -27,6 +27,9 @@ class B200Device : protected Pointers {
   void check(int status, const char *file, int line);
   // units, neighbor settings and per-type cutoffs from the LAMMPS objects (Update, Neighbor, Force)
   void sync_settings();
+  // eflag_atom / vflag_atom under the stock loop: run the per-atom pass and ADD the owned atoms' tallies to the pair
+  // style's eatom / vatom (host order == device order in host-ghost mode)
+  void peratom_to_host(int nlocal, double *eatom, double **vatom);
 
  private:
   B200Device(LAMMPS *);

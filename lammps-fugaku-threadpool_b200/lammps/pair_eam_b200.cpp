@@ -62,7 +62,6 @@ void PairEAMB200::compute(int eflag, int vflag)
 {
   ev_init(eflag, vflag);
   if (dev->resident) return;
-  if (eflag_atom || vflag_atom) error->all(FLERR, "Pair style eam/b200 does not tally per-atom energy/virial");
   if (!tables_loaded) device_tables(dev);
 
   const int nlocal = atom->nlocal, nghost = atom->nghost;
@@ -87,6 +86,7 @@ void PairEAMB200::compute(int eflag, int vflag)
   if (eflag_global) eng_vdwl += e_embed + e_pair;
   if (vflag_global)
     for (int k = 0; k < 6; k++) virial[k] += v[k];
+  if (eflag_atom || vflag_atom) dev->peratom_to_host(nlocal, eflag_atom ? eatom : nullptr, vflag_atom ? vatom : nullptr);
 }
 
 double PairEAMB200::memory_usage()

@@ -61,7 +61,6 @@ void PairLJCutB200::compute(int eflag, int vflag)
 {
   ev_init(eflag, vflag);
   if (dev->resident) return;
-  if (eflag_atom || vflag_atom) error->all(FLERR, "Pair style lj/cut/b200 does not tally per-atom energy/virial");
   if (atom->molecular != Atom::ATOMIC)
     error->all(FLERR, "Pair style lj/cut/b200: bonded systems are served by the device-resident loop only");
   if (!tables_loaded) device_tables(dev);
@@ -76,6 +75,7 @@ void PairLJCutB200::compute(int eflag, int vflag)
   if (eflag_global) eng_vdwl += e;
   if (vflag_global)
     for (int k = 0; k < 6; k++) virial[k] += v[k];
+  if (eflag_atom || vflag_atom) dev->peratom_to_host(nlocal, eflag_atom ? eatom : nullptr, vflag_atom ? vatom : nullptr);
 }
 
 double PairLJCutB200::memory_usage()

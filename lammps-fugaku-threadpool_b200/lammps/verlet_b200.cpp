@@ -131,6 +131,10 @@ void VerletB200::fetch_energies()
 {
   double e = 0.0, vir[6] = {0, 0, 0, 0, 0, 0};
   Pair *pair = force->pair;
+  // what the computes of this step want (Integrate::ev_set); while the device is resident the pair style's compute()
+  // only does its ev_init: sizes and clears eatom / vatom and sets the eflag_* / vflag_* members
+  ev_set(update->ntimestep);
+  pair->compute(eflag, vflag);
   B200_CHECK(dev, b200md_last_ev(dev->ctx, &e, vir));
   pair->eng_vdwl = e;
   pair->eng_coul = 0.0;
@@ -141,6 +145,28 @@ void VerletB200::fetch_energies()
     for (int k = 0; k < 6; k++) bond->virial[k] = vir[k];
   }
   update->eflag_global = update->vflag_global = update->ntimestep;
+  // per-atom tallies if a compute wants them on this step: the device pass, scattered by tag
+  if ((eflag & ENERGY_ATOM) || (vflag & VIRIAL_ATOM)) {
+    if (comm->nprocs > 1) error->all(FLERR, "Run style verlet/b200: per-atom energy/virial on one rank only for now");
+    const int n = b200md_nlocal(dev->ctx);
+    std::vector<double> e(n), v((size_t) 6 * n);
+    std::vector<int> tag(n);
+    B200_CHECK(dev, b200md_pair_peratom(dev->ctx));
+    B200_CHECK(dev, b200md_peratom_download(dev->ctx, e.data(), v.data()));
+    B200_CHECK(dev, b200md_download_atoms(dev->ctx, nullptr, nullptr, nullptr, nullptr, tag.data(), nullptr));
+    std::vector<std::pair<tagint, int>> where(atom->nlocal);
+    for (int i = 0; i < atom->nlocal; i++) where[i] = {atom->tag[i], i};
+    std::sort(where.begin(), where.end());
+    for (int s = 0; s < n; s++) {
+      auto it = std::lower_bound(where.begin(), where.end(), std::make_pair((tagint) tag[s], -1));
+      if (it == where.end() || it->first != tag[s]) error->one(FLERR, "Run style verlet/b200: unknown atom tag {} came back", tag[s]);
+      const int i = it->second;
+      if (pair->eflag_atom) pair->eatom[i] = e[s];
+      if (pair->vflag_atom)
+        for (int k = 0; k < 6; k++) pair->vatom[i][k] = v[(size_t) 6 * s + k];
+    }
+    update->eflag_atom = update->vflag_atom = update->ntimestep;
+  }
 }
 
 // Verlet::setup (src/verlet.cpp:90-160).  Atomic systems: the stock routine.  Bonded / thermostatted systems: the

@@ -44,6 +44,8 @@ PROTOTYPES = {
     "b200md_halo_forward": (_i, [_vp]),
     "b200md_plan_peers": (_i, [_vp, _vp, _i, _vp, _vp]),
     "b200md_pair_compute": (_i, [_vp, _i, _i, _vp, _vp]),
+    "b200md_pair_peratom": (_i, [_vp]),
+    "b200md_peratom_download": (_i, [_vp, _vp, _vp]),
     "b200md_nve_initial": (_i, [_vp, _d, _d]),
     "b200md_nve_final": (_i, [_vp, _d]),
     "b200md_thermo": (_i, [_vp, _d, _vp]),

@@ -446,6 +446,19 @@ class B200MD:
             x, v, f, t, tag, img = x[o], v[o], f[o], t[o], tag[o], img[o]
         return dict(x=x, v=v, f=f, type=t, tag=tag, image=img)
 
+    def peratom(self, sort_by_tag: bool = True) -> dict:
+        """compute pe/atom + compute stress/atom NULL pair: per-atom pair energy and virial (xx yy zz xy xz yz, energy
+        units: stress/atom multiplies by -nktv2p) of the current configuration"""
+        n = self.nlocal
+        self.ctx.call("b200md_pair_peratom")
+        e, v = np.empty(n), np.empty((n, 6))
+        self.ctx.call("b200md_peratom_download", lib.ptr(e), lib.ptr(v))
+        tag = self.gather(sort_by_tag=False)["tag"]
+        if sort_by_tag:
+            o = np.argsort(tag)
+            e, v, tag = e[o], v[o], tag[o]
+        return dict(eatom=e, vatom=v, tag=tag)
+
     def all_positions(self):
         n = self.nlocal + self.nghost
         x, tag = np.empty((n, 3)), np.empty(n, dtype=np.int32)

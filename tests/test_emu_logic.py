@@ -488,3 +488,21 @@ def test_emu_replicated_chain_and_bench_leg(emu, monkeypatch):
     out = bench.run_chain(None, None, emu, 1, types.SimpleNamespace(steps=3, warmup=1), 0)
     assert out["natoms"] == 32000 and out["neigh"]["builds"] >= 1 and out["launches"] > 0
     assert abs(out["thermo1"]["temp"] - 1.0) < 0.05 and out["kernel_ms"]["neigh"][1] >= 0
+
+
+@pytest.mark.parametrize("kind", ["lj", "eam"])
+@pytest.mark.parametrize("loop", ["verlet/b200", "verlet"])
+def test_emu_lammps_peratom(emu_lmp, kind, loop, tmp_path):
+    lh.test_peratom_energy_and_stress_match_reference(kind, loop, tmp_path)
+
+
+import test_zz_gpu_peratom as pa  # noqa: E402
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_emu_peratom_sums(emu, name):
+    pa.test_peratom_sums_are_the_global_tallies(emu, name)
+
+
+def test_emu_peratom_needs_a_list(emu):
+    pa.test_peratom_needs_a_list(emu)
