@@ -254,9 +254,14 @@ void launch(dim3 grid, dim3 block, size_t smem, const std::function<void()> &bod
   dyn_smem = g_smem.data();
   g_body = &body;
   const int nwarps = (nthreads + 31) / 32;
-  for (unsigned bz = 0; bz < grid.z; bz++)
-    for (unsigned by = 0; by < grid.y; by++)
-      for (unsigned bx = 0; bx < grid.x; bx++) {
+  // CUDAEMU_ORDER=reverse runs the blocks of every launch last-to-first and resumes the threads of a block
+  // last-to-first: CUDA promises no order, so results that change under it point at an ordering assumption
+  // (a block reading what another block of the same launch writes, a thread relying on an earlier one)
+  static const bool reverse = getenv("CUDAEMU_ORDER") && strcmp(getenv("CUDAEMU_ORDER"), "reverse") == 0;
+  for (unsigned bz_ = 0; bz_ < grid.z; bz_++)
+    for (unsigned by_ = 0; by_ < grid.y; by_++)
+      for (unsigned bx_ = 0; bx_ < grid.x; bx_++) {
+        const unsigned bx = reverse ? grid.x - 1 - bx_ : bx_, by = reverse ? grid.y - 1 - by_ : by_, bz = reverse ? grid.z - 1 - bz_ : bz_;
         for (int w = 0; w < nwarps; w++) {
           g_warps[w].live = std::min(32, nthreads - 32 * w);
           g_warps[w].count = 0;
@@ -295,7 +300,8 @@ void launch(dim3 grid, dim3 block, size_t smem, const std::function<void()> &bod
         int remaining = nthreads;
         while (remaining > 0) {
           bool progressed = false;
-          for (int t = 0; t < nthreads; t++) {
+          for (int t_ = 0; t_ < nthreads; t_++) {
+            const int t = reverse ? nthreads - 1 - t_ : t_;
             Fiber *f = g_fibers[t];
             if (f->done) continue;
             if (f->wait_gen) {
