@@ -520,3 +520,7 @@ def test_emu_results_do_not_depend_on_block_or_thread_order():
                        cwd=ROOT, env=env, capture_output=True, text=True)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert " passed" in r.stdout and "failed" not in r.stdout
+
+
+def test_emu_lammps_restart_and_data_round_trip(emu_lmp, tmp_path):
+    lh.test_restart_and_data_round_trip_under_suffix_b200(tmp_path)

@@ -449,3 +449,70 @@ def test_peratom_energy_and_stress_match_reference(kind, loop, tmp_path):
         for cols in ([1], [2, 3, 4, 5, 6, 7]):
             scale = max(np.abs(R[k][:, cols]).max(), term if cols[0] > 1 else 0.0)
             assert np.abs(G[k][:, cols] - R[k][:, cols]).max() <= rtol * scale, (k, cols)
+
+
+# ---- restart / data-file round trips through the b200 pair style (the restart and data legs of the reference's
+# ---- test_pair_style.cpp: write_restart / read_restart, write_data / read_data, then the same energies) ----
+IN_ROUNDTRIP = """units lj
+atom_style atomic
+lattice fcc 0.8442
+region box block 0 5 0 5 0 5
+create_box 2 box
+create_atoms 1 box
+set group all type/fraction 2 0.3 12345
+mass 1 1.0
+mass 2 1.5
+velocity all create 1.44 87287 loop geom
+pair_style lj/cut 2.5
+pair_coeff 1 1 1.0 1.0 2.5
+pair_coeff 2 2 0.8 1.1 2.5
+pair_modify shift yes mix arithmetic
+neighbor 0.3 bin
+fix 1 all nve
+thermo_style custom step pe press
+thermo_modify format float %.15g
+run 10
+write_restart rt.restart
+write_data rt.data
+clear
+read_restart rt.restart
+fix 1 all nve
+thermo_style custom step pe press
+thermo_modify format float %.15g
+run 0
+clear
+units lj
+atom_style atomic
+pair_style lj/cut 2.5
+read_data rt.data
+pair_modify shift yes mix arithmetic
+neighbor 0.3 bin
+fix 1 all nve
+thermo_style custom step pe press
+thermo_modify format float %.15g
+run 0
+"""
+
+
+@FIRST_RUN
+@pytest.mark.gpu
+def test_restart_and_data_round_trip_under_suffix_b200(tmp_path):
+    """pair lj/cut/b200 inherits PairLJCut's write_restart / read_restart / write_data (src/pair_lj_cut.cpp:563-656):
+    a restart written under -sf b200 restores the b200 style with its coefficients, a data file restores them through
+    `Pair Coeffs`, and both reproduce the energy and pressure the first run ended with; lmp_ref beside it gives the
+    same three rows"""
+    if not LMP_B200.exists() or not LMP_REF.exists():
+        pytest.skip("oracle/_ref host binaries not shipped")
+    ref = run_lmp(LMP_REF, IN_ROUNDTRIP, tmp_path)
+    assert ref.returncode == 0, ref.stdout[-2000:]
+    got = run_lmp(LMP_B200, IN_ROUNDTRIP, tmp_path, ["-sf", "b200"])
+    assert got.returncode == 0, got.stdout[-3000:] + got.stderr[-2000:]
+    assert "lj/cut/b200" in got.stdout     # "restoring pair style lj/cut/b200 from restart"
+    R = np.array(thermo_rows_generic(ref.stdout, "Step", "PotEng"))
+    G = np.array(thermo_rows_generic(got.stdout, "Step", "PotEng"))
+    assert R.shape == G.shape == (4, 3), (R.shape, G.shape)
+    # rows: step 0, step 10, after read_restart (step 10), after read_data (step 0 of a new run)
+    np.testing.assert_allclose(G[1, 1:], G[2, 1:], rtol=1e-12)
+    np.testing.assert_allclose(G[1, 1:], G[3, 1:], rtol=1e-10)
+    np.testing.assert_allclose(G[:, 1:], R[:, 1:], rtol=1e-6)
+    np.testing.assert_allclose(G[0, 1:], R[0, 1:], rtol=1e-10)
