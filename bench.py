@@ -514,7 +514,7 @@ def main():
 
         def roof(w, cls, bytes_per_atom, dram_key=None):
             kms, kc = w["kernel_ms"][cls]
-            if kc == 0:
+            if kc == 0 or kms <= 0.0:
                 return None
             avg_ms = kms / kc
             ach = bytes_per_atom * w["atoms_per_gpu"] / (avg_ms * 1e-3) / 1e9

@@ -151,3 +151,21 @@ def test_philox_known_answers_and_counter_uniforms(pkg):
     assert not np.array_equal(a, b) and np.array_equal(a, u[4])               # a function of (seed, tag, step) only
     L.b200md_langevin_counter_uniforms(904298, 5, 17, pkg.lib.ptr(b))
     assert not np.array_equal(a, b)
+
+
+def test_bench_reference_arm_prints_the_contract_line():
+    """bench.py --impl reference (the unmodified reference's OpenMP build on the host cores, oracle/_ref/lmp_ref): one
+    JSON line with the reference-arm keys, on a tiny sample"""
+    import json
+    import subprocess
+    import sys
+
+    if not (ROOT / "oracle" / "_ref" / "lmp_ref").exists():
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    r = subprocess.run([sys.executable, "bench.py", "--impl", "reference", "--steps", "3", "--warmup", "1", "--cells", "8", "--eam-cells", "8"],
+                       cwd=ROOT, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
+    assert line["impl"] == "reference" and line["value"] > 0 and line["unit"] == "Matom-steps/s" and line["higher_is_better"] is True
+    assert line["cpu_baseline"]["kind"] == "reference" and line["cpu_baseline"]["cores"] >= 1 and line["cpu_baseline"]["value"] == line["value"]
+    assert line["e2e"] == {"value": line["value"], "unit": line["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}

@@ -524,3 +524,120 @@ def test_emu_results_do_not_depend_on_block_or_thread_order():
 
 def test_emu_lammps_restart_and_data_round_trip(emu_lmp, tmp_path):
     lh.test_restart_and_data_round_trip_under_suffix_b200(tmp_path)
+
+
+def test_emu_graft_entry_smoke(emu):
+    """__graft_entry__.smoke() as the driver runs it at round end, on the emulation build"""
+    import __graft_entry__ as ge
+
+    ge.smoke()
+
+
+class _FakeTorch:
+    """the slice of torch.cuda bench.py uses for timing and pinned buffers, on the host: lets bench.main() run end to
+    end against the emulation build so that its control flow and its JSON line are exercised before the GPU run"""
+
+    float64 = np.float64
+    uint8 = np.uint8
+
+    class _T:
+        def __init__(self, a):
+            self.a = np.ascontiguousarray(a)
+
+        def pin_memory(self):
+            return self
+
+        def data_ptr(self):
+            return self.a.ctypes.data
+
+        def item(self):
+            return self.a.reshape(-1)[0].item()
+
+        def __getitem__(self, k):
+            return _FakeTorch._T(self.a[k:k + 1]) if isinstance(k, int) else _FakeTorch._T(self.a[k])
+
+        def clone(self):
+            return _FakeTorch._T(self.a.copy())
+
+    class _Event:
+        def __init__(self, enable_timing=False):
+            self.t = 0.0
+
+        def record(self):
+            import time
+            self.t = time.perf_counter()
+
+        def elapsed_time(self, other):
+            return (other.t - self.t) * 1e3
+
+    class _Ctx:
+        def __enter__(self):
+            return self
+
+        def __exit__(self, *a):
+            return False
+
+    class cuda:  # noqa: N801
+        Event = None
+
+        @staticmethod
+        def is_available():
+            return True
+
+        @staticmethod
+        def set_device(i):
+            pass
+
+        @staticmethod
+        def synchronize(device=None):
+            pass
+
+        @staticmethod
+        def ExternalStream(ptr, device=None):  # noqa: N802
+            return object()
+
+        @staticmethod
+        def stream(s):
+            return _FakeTorch._Ctx()
+
+    @staticmethod
+    def empty(shape, dtype=None):
+        return _FakeTorch._T(np.zeros(shape, dtype=dtype or np.float64))
+
+    @staticmethod
+    def tensor(v, dtype=None, device=None):
+        return _FakeTorch._T(np.array(v, dtype=dtype or np.float64))
+
+
+_FakeTorch.cuda.Event = _FakeTorch._Event
+
+
+def test_emu_bench_main_prints_the_contract_line(emu, monkeypatch, capsys):
+    """bench.py, b200 arm, N = 1, reduced sizes: both workloads' resident phases, the e2e phase under its watchdog, the
+    cpu_baseline leg (the oracle/_ref reference run), one JSON line with every key the contract names"""
+    import json
+    import types
+
+    import bench
+
+    fake_dist = types.ModuleType("torch.distributed")
+    monkeypatch.setattr(_FakeTorch, "distributed", fake_dist, raising=False)
+    monkeypatch.setitem(sys.modules, "torch", _FakeTorch)
+    monkeypatch.setitem(sys.modules, "torch.distributed", fake_dist)
+    monkeypatch.setattr(sys, "argv", ["bench.py", "--steps", "6", "--warmup", "3", "--cells", "6", "--eam-cells", "6", "--chain", "1"])
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        monkeypatch.delenv(k, raising=False)
+    bench.main()
+    lines = [l for l in capsys.readouterr().out.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    line = json.loads(lines[0])
+    for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline",
+                "dtype", "data", "config", "roofline", "cpu_baseline", "e2e", "gpu_launches", "clocks"):
+        assert key in line, key
+    assert line["n_gpus"] == 1 and line["steps"] == 6 and line["warmup"] == 3 and line["value"] > 0
+    assert line["config"]["workload"] and line["dtype"] == "f64" and line["gpu_launches"] > 0
+    assert {"bound", "achieved", "peak", "unit", "frac", "traffic"} <= set(line["roofline"])
+    assert line["e2e"]["value"] > 0 and line["e2e"]["h2d_bytes_per_step"] == 2 * 864 * 24 and line["e2e"]["d2h_bytes_per_step"] == 3 * 864 * 24
+    assert {"value", "unit", "cores", "kind", "sample"} <= set(line["cpu_baseline"])
+    assert line["eam"]["value"] > 0 and line["eam"]["e2e"]["value"] > 0
+    assert line["chain"]["value"] > 0 and line["chain"]["neigh"]["builds"] >= 1
