@@ -283,6 +283,8 @@ int b200md_kernel_times(b200md_ctx *ctx, double *ms, int64_t *count, int reset);
 /* the cudaStream_t all of this context's work is issued on (for callers that record their own events
  * or order their own kernels against the library's, as KOKKOS styles do with their execution space) */
 void *b200md_stream(b200md_ctx *ctx);
+/* 1 when the opt-in shared-memory tiled lj/cut kernel (B200MD_LJ_TILED=1) serves the current neighbor list */
+int b200md_tiled_active(const b200md_ctx *ctx);
 
 #ifdef __cplusplus
 }

@@ -58,6 +58,12 @@ extern "C" int b200md_create(b200md_ctx **out, int device, int nranks, int rank,
   // opt-in: run the per-step halo on its own stream under the force kernels of the ghost-free tiles (written in
   // round 1 after the GPU budget was spent: not yet run on hardware)
   c->overlap = getenv("B200MD_OVERLAP") != nullptr;
+  // opt-in, same status: shared-memory tiled lj/cut kernel (pair_lj.cu); B200MD_TILED_G = bins per block along x
+  c->tiled = getenv("B200MD_LJ_TILED") != nullptr;
+  if (const char *e = getenv("B200MD_TILED_G")) {
+    int v = atoi(e);
+    if (v >= 1 && v <= 64) c->tiled_g = v;
+  }
   *out = c;
   CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CU(cudaMalloc((void **) &c->red_d, 32 * sizeof(double)));
@@ -85,7 +91,7 @@ extern "C" int b200md_destroy(b200md_ctx *c)
   dev_free(c, c->perm); dev_free(c, c->scan_tmp); dev_free(c, c->binrec); dev_free(c, c->atom_sub); dev_free(c, c->numneigh); dev_free(c, c->neigh); dev_free(c, c->tile_ghost);
   dev_free(c, c->send_idx); dev_free(c, c->border_blockcnt); dev_free(c, c->border_total); dev_free(c, c->send_dir);
   dev_free(c, c->sendbuf_i); dev_free(c, c->allcounts); dev_free(c, c->sendbuf4); dev_free(c, c->recvbuf4); dev_free(c, c->sendbuf1);
-  dev_free(c, c->partials); dev_free(c, c->stage); dev_free(c, c->peratom);
+  dev_free(c, c->partials); dev_free(c, c->stage); dev_free(c, c->peratom); dev_free(c, c->neigh16); dev_free(c, c->cell_pos);
   bond_release(c);
   if (c->lj.d) cudaFree(c->lj.d);
   if (c->eam.frho) cudaFree(c->eam.frho);
@@ -1184,4 +1190,5 @@ extern "C" int b200md_profile(b200md_ctx *c, int level)
   return B200MD_OK;
 }
 
+extern "C" int b200md_tiled_active(const b200md_ctx *c) { return c && c->tiled_valid ? 1 : 0; }
 extern "C" void *b200md_stream(b200md_ctx *c) { return c ? (void *) c->stream : nullptr; }

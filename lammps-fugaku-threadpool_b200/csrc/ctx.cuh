@@ -194,6 +194,13 @@ struct b200md_ctx {
 
   // reductions / flags
   DevBuf<double> partials;  // [nblocks][8]
+  // opt-in shared-memory tiled lj/cut (B200MD_LJ_TILED=1, pair_lj.cu): a block = TG consecutive bins of one x-row; the
+  // atoms of its 3 x 3 x (TG+2) bin neighbourhood are staged in shared memory once per step and the list entries are
+  // 16-bit slots of that staging area
+  DevBuf<unsigned short> neigh16;   // same blocked-transposed layout as neigh
+  DevBuf<int> cell_pos;             // [nall] slot of each atom in cell_list (inverse permutation)
+  bool tiled = false, tiled_valid = false;
+  int tiled_g = 6, tiled_nseg = 0, tiled_max_staged = 0;
   DevBuf<double> peratom;   // [7][peratom_stride]: eatom, vatom xx yy zz xy xz yz of the owned atoms (b200md_pair_peratom)
   size_t peratom_stride = 0;
   int peratom_n = 0;        // owned atoms the tallies are valid for, 0 = none
@@ -340,6 +347,7 @@ int nve_initial(b200md_ctx *c, double dtv, double dtf);
 int nve_final(b200md_ctx *c, double dtf);
 int thermo_ke(b200md_ctx *c, double *sum_mv2);
 int reduce_partials(b200md_ctx *c, int nblocks, int ncomp, int dst);  // partials -> red_d[dst..]
+int pair_lj_tiled_prepare(b200md_ctx *c);   // after a list build: 16-bit staged-slot lists (no-op unless opted in)
 int pair_lj_peratom(b200md_ctx *c, double *out, size_t stride);       // eatom / vatom pass, out = [7][stride]
 int pair_eam_peratom(b200md_ctx *c, double *out, size_t stride);
 

@@ -792,5 +792,7 @@ int neigh_build_lists(b200md_ctx *c)
   c->ago = 0;
   c->nbuilds++;
   c->list_valid = true;
+  TRY(pair_lj_tiled_prepare(c));   // B200MD_LJ_TILED=1 only
+  ph.mark("tiled lists");
   return B200MD_OK;
 }

@@ -276,8 +276,11 @@ template <int CL> static void launch_lj(b200md_ctx *c, int blocks, int threads, 
 #undef LJ_ARGS
 }
 
+static int pair_lj_compute_tiled(b200md_ctx *c, int ev);
+
 int pair_lj_compute(b200md_ctx *c, int eflag, int vflag)
 {
+  if (c->tiled_valid) return pair_lj_compute_tiled(c, (eflag || vflag) ? 1 : 0);
   const int n = c->nlocal;
   const bool lanes = c->cl == 1 ? getenv("B200MD_LJ_PLAIN") == nullptr : getenv("B200MD_LANES") != nullptr;
   const int nclus = lanes ? n : cdiv(n, c->cl);
@@ -362,5 +365,225 @@ int pair_lj_peratom(b200md_ctx *c, double *out, size_t stride)
   const int n = c->nlocal;
   k_lj_peratom<<<cdiv(n, 128), 128, 0, c->stream>>>(c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, c->lj.d, c->lj.ntypes, out, stride);
   LAUNCH_CHECK();
+  return B200MD_OK;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// Shared-memory tiled lj/cut (opt-in: B200MD_LJ_TILED=1; written after round 1's GPU budget was spent, validated under
+// the CPU emulation only).  ncu on k_lj_lanes: the L1 LSU data pipe is the limiter -- every gathered neighbor is a
+// distinct 32-byte sector, 26 wavefronts per warp step -- while DRAM sits at 19 % and the FP64 pipe at 36 %.
+// Here a block owns TG consecutive bins of one x-row.  Bins are >= the neighbor cutoff wide, so every neighbor of its
+// atoms lies in the 3 x 3 x (TG + 2) bins around it, and those are 9 CONTIGUOUS ranges of cell_list (bins of an
+// x-row are consecutive).  The block gathers that neighbourhood once per step into shared memory (each atom once
+// per block instead of once per pair: about 6 x fewer global gathers for lj at rc 2.5) and the inner loop reads
+// neighbors from shared memory through 16-bit slot numbers (which also halves the list traffic, the largest DRAM
+// term of the step).  List order, arithmetic and summation order are those of k_lj_lanes: forces are bit-identical.
+// ------------------------------------------------------------------------------------------------------------
+struct TileGeom {
+  BinGeom g;
+  int tg, nsegx;   // bins per segment along x, segments per x-row
+};
+
+// the 9 cell_list ranges (dz, dy rows) of segment `seg` and the prefix offsets of their staged copies
+__device__ __forceinline__ void tile_rows(const TileGeom &T, const int *__restrict__ bin_start, int seg, int ks[9], int off[10],
+                                          int &own_s, int &own_e, int &by, int &bz)
+{
+  const int sx = seg % T.nsegx, oby = (seg / T.nsegx) % T.g.nbin[1], obz = seg / (T.nsegx * T.g.nbin[1]);
+  const int gx = min(T.tg, T.g.nbin[0] - sx * T.tg);
+  const int bx0 = BIN_MARGIN + sx * T.tg;
+  by = oby + BIN_MARGIN;
+  bz = obz + BIN_MARGIN;
+  off[0] = 0;
+#pragma unroll
+  for (int r = 0; r < 9; r++) {
+    const int dz = r / 3 - 1, dy = r % 3 - 1;
+    const int first = ((bz + dz) * T.g.mbin[1] + (by + dy)) * T.g.mbin[0] + bx0 - 1;
+    ks[r] = bin_start[first];
+    off[r + 1] = off[r] + bin_start[first + gx + 2] - ks[r];
+    if (r == 4) {
+      own_s = bin_start[first + 1];
+      own_e = bin_start[first + 1 + gx];
+    }
+  }
+}
+
+__global__ void k_cell_pos(const int *__restrict__ cell_list, int nall, int *__restrict__ cell_pos)
+{
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < nall) cell_pos[cell_list[k]] = k;
+}
+
+// list entries (global atom index) -> slots of the owning segment's staging area; flags[6] = largest staging area
+__global__ void __launch_bounds__(128)
+k_tile_convert(TileGeom T, const int *__restrict__ bin_start, const int *__restrict__ cell_list, const int *__restrict__ atom_bin,
+               const int *__restrict__ cell_pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh, int nlocal,
+               unsigned short *__restrict__ neigh16, int *__restrict__ flags)
+{
+  int ks[9], off[10], own_s, own_e, by, bz;
+  tile_rows(T, bin_start, blockIdx.x, ks, off, own_s, own_e, by, bz);
+  if (threadIdx.x == 0) atomicMax(&flags[6], off[9]);
+  for (int slot = own_s + threadIdx.x; slot < own_e; slot += blockDim.x) {
+    const int i = cell_list[slot];
+    if (i >= nlocal) continue;   // a ghost that rounding put into an owned bin
+    const int n = numneigh[i];
+    const size_t base = (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
+    for (int k = 0; k < n; k++) {
+      const int j = neigh[base + (size_t) k * TILE] & CLJMASK;
+      const int bj = atom_bin[j];
+      const int bjy = (bj / T.g.mbin[0]) % T.g.mbin[1], bjz = bj / (T.g.mbin[0] * T.g.mbin[1]);
+      const int r = (bjz - bz + 1) * 3 + (bjy - by + 1);
+      int local = 0xFFFF;
+      if (r >= 0 && r < 9) {
+        const int l = off[r] + cell_pos[j] - ks[r];
+        if (l >= off[r] && l < off[r + 1] && l < 0xFFFF) local = l;
+      }
+      if (local == 0xFFFF) flags[7] = 1;   // outside the staged neighbourhood: the tiled path must not be used
+      neigh16[base + (size_t) k * TILE] = (unsigned short) local;
+    }
+  }
+}
+
+template <int EVFLAG, int ONETYPE>
+__global__ void __launch_bounds__(128)
+k_lj_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__restrict__ cell_list, const double4 *__restrict__ pos,
+           const int *__restrict__ numneigh, const unsigned short *__restrict__ neigh16, int maxneigh, int nlocal, int max_staged,
+           LJOne one, const double *__restrict__ tables, int ntypes, double *__restrict__ fx, double *__restrict__ fy,
+           double *__restrict__ fz, double *__restrict__ partials)
+{
+  extern __shared__ double4 s_tile[];   // [max_staged] staged atoms, then 6 tables of (ntypes+1)^2 when !ONETYPE
+  double *s_tab = reinterpret_cast<double *>(s_tile + max_staged);
+  const int nt1 = ntypes + 1, nt2 = nt1 * nt1;
+  int ks[9], off[10], own_s, own_e, by, bz;
+  tile_rows(T, bin_start, blockIdx.x, ks, off, own_s, own_e, by, bz);
+  if (!ONETYPE)
+    for (int k = threadIdx.x; k < 6 * nt2; k += blockDim.x) s_tab[k] = tables[k];
+#pragma unroll
+  for (int r = 0; r < 9; r++) {
+    const int len = off[r + 1] - off[r];
+    for (int k = threadIdx.x; k < len; k += blockDim.x) s_tile[off[r] + k] = ld_pos256(pos + cell_list[ks[r] + k]);
+  }
+  __syncthreads();
+  double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  for (int slot = own_s + threadIdx.x; slot < own_e; slot += blockDim.x) {
+    const int i = cell_list[slot];
+    if (i >= nlocal) continue;
+    const double4 pi = pos[i];
+    const int trow = ONETYPE ? 0 : pos_type(pi) * nt1;
+    const int n = numneigh[i];
+    const unsigned short *nb = neigh16 + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
+    double fxi = 0.0, fyi = 0.0, fzi = 0.0;
+#pragma unroll 4
+    for (int k = 0; k < n; k++) {
+      const double4 pj = s_tile[__ldcs(nb + (size_t) k * TILE)];
+      const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+      const double rsq = dx * dx + dy * dy + dz * dz;
+      double cutsq, lj1, lj2;
+      if (ONETYPE) {
+        cutsq = one.cutsq; lj1 = one.lj1; lj2 = one.lj2;
+      } else {
+        const int t = trow + pos_type(pj);
+        cutsq = s_tab[t]; lj1 = s_tab[nt2 + t]; lj2 = s_tab[2 * nt2 + t];
+      }
+      const bool in = rsq < cutsq;
+      const double r2inv = rcp_pos(rsq);
+      const double r6inv = r2inv * r2inv * r2inv;
+      const double forcelj = r6inv * (lj1 * r6inv - lj2);
+      const double fpair = in ? forcelj * r2inv : 0.0;
+      fxi += dx * fpair;
+      fyi += dy * fpair;
+      fzi += dz * fpair;
+      if (EVFLAG) {
+        double lj3, lj4, offs;
+        if (ONETYPE) {
+          lj3 = one.lj3; lj4 = one.lj4; offs = one.offset;
+        } else {
+          const int t = trow + pos_type(pj);
+          lj3 = s_tab[3 * nt2 + t]; lj4 = s_tab[4 * nt2 + t]; offs = s_tab[5 * nt2 + t];
+        }
+        acc[0] += in ? 0.5 * (r6inv * (lj3 * r6inv - lj4) - offs) : 0.0;
+        const double hf = 0.5 * fpair;
+        acc[1] += dx * dx * hf;
+        acc[2] += dy * dy * hf;
+        acc[3] += dz * dz * hf;
+        acc[4] += dx * dy * hf;
+        acc[5] += dx * dz * hf;
+        acc[6] += dy * dz * hf;
+      }
+    }
+    fx[i] = fxi;
+    fy[i] = fyi;
+    fz[i] = fzi;
+  }
+  if (EVFLAG) block_partials<7>(acc, partials);
+}
+
+static TileGeom tile_geom(const b200md_ctx *c)
+{
+  TileGeom T;
+  T.g = c->bg;
+  T.tg = c->tiled_g;
+  T.nsegx = cdiv(c->bg.nbin[0], c->tiled_g);
+  return T;
+}
+
+int pair_lj_tiled_prepare(b200md_ctx *c)
+{
+  c->tiled_valid = false;
+  if (!c->tiled || c->pair_style != 1 || c->cl != 1 || c->host_ghosts) return B200MD_OK;
+  const int n = c->nlocal, nall = n + c->nghost;
+  const TileGeom T = tile_geom(c);
+  const int nseg = T.nsegx * c->bg.nbin[1] * c->bg.nbin[2];
+  TRY(dev_ensure(c, c->cell_pos, (size_t) nall));
+  TRY(dev_ensure(c, c->neigh16, (size_t) cdiv(n, TILE) * TILE * c->maxneigh));
+  CU(cudaMemsetAsync(c->flags_d + 6, 0, 2 * sizeof(int), c->stream));
+  {
+    KProf kp(c, KC_NEIGH);
+    k_cell_pos<<<cdiv(nall, 256), 256, 0, c->stream>>>(c->cell_list.p, nall, c->cell_pos.p);
+    LAUNCH_CHECK();
+    k_tile_convert<<<nseg, 128, 0, c->stream>>>(T, c->bin_start.p, c->cell_list.p, c->atom_bin.p, c->cell_pos.p, c->numneigh.p, c->neigh.p,
+                                                c->maxneigh, n, c->neigh16.p, c->flags_d);
+    LAUNCH_CHECK();
+  }
+  CU(cudaMemcpyAsync(c->flags_h + 6, c->flags_d + 6, 2 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  c->tiled_nseg = nseg;
+  c->tiled_max_staged = c->flags_h[6];
+  const size_t nt2 = (size_t) (c->lj.ntypes + 1) * (c->lj.ntypes + 1);
+  const size_t smem = (size_t) c->tiled_max_staged * sizeof(double4) + (c->lj.ntypes == 1 ? 0 : 6 * nt2 * sizeof(double));
+  // usable only when every neighbor was found in its segment's neighbourhood and the staging area fits
+  c->tiled_valid = !c->flags_h[7] && c->tiled_max_staged > 0 && c->tiled_max_staged < 0xFFFF && smem <= 200 * 1024;
+  return B200MD_OK;
+}
+
+static int pair_lj_compute_tiled(b200md_ctx *c, int ev)
+{
+  const TileGeom T = tile_geom(c);
+  const int nseg = c->tiled_nseg, onetype = (c->lj.ntypes == 1);
+  const size_t nt2 = (size_t) (c->lj.ntypes + 1) * (c->lj.ntypes + 1);
+  const size_t smem = (size_t) c->tiled_max_staged * sizeof(double4) + (onetype ? 0 : 6 * nt2 * sizeof(double));
+  LJOne one = {c->lj.h_onetype[0], c->lj.h_onetype[1], c->lj.h_onetype[2], c->lj.h_onetype[3], c->lj.h_onetype[4], c->lj.h_onetype[5]};
+  if (ev) TRY(dev_ensure(c, c->partials, (size_t) nseg * 8));
+  static bool attr_done = false;
+  if (!attr_done) {
+    CU(cudaFuncSetAttribute(k_lj_tiled<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU(cudaFuncSetAttribute(k_lj_tiled<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU(cudaFuncSetAttribute(k_lj_tiled<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU(cudaFuncSetAttribute(k_lj_tiled<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr_done = true;
+  }
+  {
+    KProf kp(c, KC_PAIR);
+#define T_ARGS T, c->bin_start.p, c->cell_list.p, c->pos.p, c->numneigh.p, c->neigh16.p, c->maxneigh, c->nlocal, c->tiled_max_staged, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p
+    if (ev) {
+      if (onetype) k_lj_tiled<1, 1><<<nseg, 128, smem, c->stream>>>(T_ARGS);
+      else k_lj_tiled<1, 0><<<nseg, 128, smem, c->stream>>>(T_ARGS);
+    } else {
+      if (onetype) k_lj_tiled<0, 1><<<nseg, 128, smem, c->stream>>>(T_ARGS);
+      else k_lj_tiled<0, 0><<<nseg, 128, smem, c->stream>>>(T_ARGS);
+    }
+#undef T_ARGS
+    LAUNCH_CHECK();
+  }
+  if (ev) TRY(reduce_partials(c, nseg, 7, 0));
   return B200MD_OK;
 }

@@ -641,3 +641,39 @@ def test_emu_bench_main_prints_the_contract_line(emu, monkeypatch, capsys):
     assert {"value", "unit", "cores", "kind", "sample"} <= set(line["cpu_baseline"])
     assert line["eam"]["value"] > 0 and line["eam"]["e2e"]["value"] > 0
     assert line["chain"]["value"] > 0 and line["chain"]["neigh"]["builds"] >= 1
+
+
+# ---- shared-memory tiled lj/cut (B200MD_LJ_TILED=1, opt-in) ----
+@pytest.mark.parametrize("g_bins", ["1", "3", "6", "64"])
+@pytest.mark.parametrize("name,steps", [("lj_500", 45), ("lj2_864", 25)])
+def test_emu_tiled_lj_equals_plain(emu, name, steps, g_bins, monkeypatch):
+    """k_lj_tiled (neighbourhood of a bin segment staged in shared memory, 16-bit slot lists) == k_lj_lanes bit for bit:
+    same list order, same arithmetic (forces and trajectory; the energy / virial sums agree to round-off); one and two atom types, segments of 1 / 3 / 6 / a whole row of bins, through
+    rebuilds, energies and virial included"""
+    g = load_golden(name)
+    monkeypatch.delenv("B200MD_LJ_TILED", raising=False)
+    a = make_device_system(emu, name, g)
+    a.run(steps, thermo_every=10)
+    monkeypatch.setenv("B200MD_LJ_TILED", "1")
+    monkeypatch.setenv("B200MD_TILED_G", g_bins)
+    b = make_device_system(emu, name, g)
+    b.run(steps, thermo_every=10)
+    assert emu.lib.load().b200md_tiled_active(b.ctx.h) == 1
+    ga, gb = a.gather(), b.gather()
+    assert np.array_equal(ga["x"], gb["x"]) and np.array_equal(ga["v"], gb["v"]) and np.array_equal(ga["f"], gb["f"])
+    for ta, tb in zip(a.thermo_log, b.thermo_log):   # the per-block partial sums group the atoms differently: last bits
+        assert abs(ta["pe"] - tb["pe"]) <= 1e-13 * abs(ta["pe"]) and abs(ta["press"] - tb["press"]) <= 1e-12 * abs(ta["press"])
+    a.close()
+    b.close()
+
+
+def test_emu_tiled_lj_decomposed_and_chain(emu, monkeypatch):
+    """the tiled kernel where ghosts come from other ranks (4 emulated ranks == the plain kernel, bit for bit) and on the
+    bonded in.chain system (lists without the 1-2 partners; the reference's setup forces)"""
+    monkeypatch.delenv("B200MD_LJ_TILED", raising=False)
+    a = run_decomposed_emu(emu, 4, (2, 2, 1), "lj", 6, 45)
+    monkeypatch.setenv("B200MD_LJ_TILED", "1")
+    b = run_decomposed_emu(emu, 4, (2, 2, 1), "lj", 6, 45)
+    for ra, rb in zip(a, b):
+        assert np.array_equal(ra["tag1"], rb["tag1"]) and np.array_equal(ra["x1"], rb["x1"]) and ra["builds"] == rb["builds"]
+    chain.test_chain_setup_forces_vs_reference(emu)

@@ -318,3 +318,27 @@ def test_large_lj_properties(pkg):
     assert abs(e1 - e0) < 2e-2  # the 32k reference drifts -4.6134 -> -4.6224 over the same 100 steps
     assert abs(e1 - (-4.6223613)) < 2e-3  # intensive quantity: same ensemble as the 32k log
     md.close()
+
+
+@pytest.mark.skipif(not os.environ.get("B200MD_TEST_TILED"),
+                    reason="shared-memory tiled lj/cut (B200MD_LJ_TILED=1) was written after round 1's GPU budget was spent: opt-in "
+                           "(B200MD_TEST_TILED=1) until it has run on hardware")
+@pytest.mark.parametrize("g_bins", ["3", "6", "12"])
+@pytest.mark.parametrize("name,steps", [("lj_500", 45), ("lj2_864", 25)])
+def test_tiled_lj_equals_plain(pkg, name, steps, g_bins, monkeypatch):
+    """B200MD_LJ_TILED=1 (k_lj_tiled: a bin segment's neighbourhood staged in shared memory, 16-bit slot lists) follows
+    the plain kernel's trajectory bit for bit; energies agree to round-off"""
+    g = load_golden(name)
+    monkeypatch.delenv("B200MD_LJ_TILED", raising=False)
+    a = make_device_system(pkg, name, g)
+    a.run(steps)
+    monkeypatch.setenv("B200MD_LJ_TILED", "1")
+    monkeypatch.setenv("B200MD_TILED_G", g_bins)
+    b = make_device_system(pkg, name, g)
+    b.run(steps)
+    assert pkg.lib.load().b200md_tiled_active(b.ctx.h) == 1
+    ga, gb = a.gather(), b.gather()
+    assert np.array_equal(ga["x"], gb["x"]) and np.array_equal(ga["v"], gb["v"]) and np.array_equal(ga["f"], gb["f"])
+    assert abs(a.thermo_log[-1]["pe"] - b.thermo_log[-1]["pe"]) <= 1e-13 * abs(a.thermo_log[-1]["pe"])
+    a.close()
+    b.close()
