@@ -375,6 +375,43 @@ __device__ __forceinline__ double rcp_pos(double x)
 }
 __device__ __forceinline__ int pos_type(const double4 &p) { return __double2loint(p.w); }
 __device__ __forceinline__ double type_as_w(int t) { return __hiloint2double(0, t); }
+// ---- geometry of the shared-memory tiled kernels (pair_lj.cu, pair_eam.cu; B200MD_LJ_TILED=1) ----
+struct TileGeom {
+  BinGeom g;
+  int tg, nsegx;   // bins per segment along x, segments per x-row
+};
+
+// the 9 cell_list ranges (dz, dy rows) of segment `seg` and the prefix offsets of their staged copies
+__device__ __forceinline__ void tile_rows(const TileGeom &T, const int *__restrict__ bin_start, int seg, int ks[9], int off[10],
+                                          int &own_s, int &own_e, int &by, int &bz)
+{
+  const int sx = seg % T.nsegx, oby = (seg / T.nsegx) % T.g.nbin[1], obz = seg / (T.nsegx * T.g.nbin[1]);
+  const int gx = min(T.tg, T.g.nbin[0] - sx * T.tg);
+  const int bx0 = BIN_MARGIN + sx * T.tg;
+  by = oby + BIN_MARGIN;
+  bz = obz + BIN_MARGIN;
+  off[0] = 0;
+#pragma unroll
+  for (int r = 0; r < 9; r++) {
+    const int dz = r / 3 - 1, dy = r % 3 - 1;
+    const int first = ((bz + dz) * T.g.mbin[1] + (by + dy)) * T.g.mbin[0] + bx0 - 1;
+    ks[r] = bin_start[first];
+    off[r + 1] = off[r] + bin_start[first + gx + 2] - ks[r];
+    if (r == 4) {
+      own_s = bin_start[first + 1];
+      own_e = bin_start[first + 1 + gx];
+    }
+  }
+}
+
+static inline TileGeom tile_geom(const b200md_ctx *c)
+{
+  TileGeom T;
+  T.g = c->bg;
+  T.tg = c->tiled_g;
+  T.nsegx = (c->bg.nbin[0] + c->tiled_g - 1) / c->tiled_g;
+  return T;
+}
 int nve_final_initial(b200md_ctx *c, double dtv, double dtf);
 int bond_compute(b200md_ctx *c, int ev);                   // bond.cu
 int langevin_apply(b200md_ctx *c, int64_t ntimestep);     // bond.cu

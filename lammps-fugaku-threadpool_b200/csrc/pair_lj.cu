@@ -379,34 +379,6 @@ int pair_lj_peratom(b200md_ctx *c, double *out, size_t stride)
 // neighbors from shared memory through 16-bit slot numbers (which also halves the list traffic, the largest DRAM
 // term of the step).  List order, arithmetic and summation order are those of k_lj_lanes: forces are bit-identical.
 // ------------------------------------------------------------------------------------------------------------
-struct TileGeom {
-  BinGeom g;
-  int tg, nsegx;   // bins per segment along x, segments per x-row
-};
-
-// the 9 cell_list ranges (dz, dy rows) of segment `seg` and the prefix offsets of their staged copies
-__device__ __forceinline__ void tile_rows(const TileGeom &T, const int *__restrict__ bin_start, int seg, int ks[9], int off[10],
-                                          int &own_s, int &own_e, int &by, int &bz)
-{
-  const int sx = seg % T.nsegx, oby = (seg / T.nsegx) % T.g.nbin[1], obz = seg / (T.nsegx * T.g.nbin[1]);
-  const int gx = min(T.tg, T.g.nbin[0] - sx * T.tg);
-  const int bx0 = BIN_MARGIN + sx * T.tg;
-  by = oby + BIN_MARGIN;
-  bz = obz + BIN_MARGIN;
-  off[0] = 0;
-#pragma unroll
-  for (int r = 0; r < 9; r++) {
-    const int dz = r / 3 - 1, dy = r % 3 - 1;
-    const int first = ((bz + dz) * T.g.mbin[1] + (by + dy)) * T.g.mbin[0] + bx0 - 1;
-    ks[r] = bin_start[first];
-    off[r + 1] = off[r] + bin_start[first + gx + 2] - ks[r];
-    if (r == 4) {
-      own_s = bin_start[first + 1];
-      own_e = bin_start[first + 1 + gx];
-    }
-  }
-}
-
 __global__ void k_cell_pos(const int *__restrict__ cell_list, int nall, int *__restrict__ cell_pos)
 {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
@@ -517,19 +489,12 @@ k_lj_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__restrict_
   if (EVFLAG) block_partials<7>(acc, partials);
 }
 
-static TileGeom tile_geom(const b200md_ctx *c)
-{
-  TileGeom T;
-  T.g = c->bg;
-  T.tg = c->tiled_g;
-  T.nsegx = cdiv(c->bg.nbin[0], c->tiled_g);
-  return T;
-}
-
 int pair_lj_tiled_prepare(b200md_ctx *c)
 {
   c->tiled_valid = false;
-  if (!c->tiled || c->pair_style != 1 || c->cl != 1 || c->host_ghosts) return B200MD_OK;
+  if (!c->tiled || c->cl != 1 || c->host_ghosts) return B200MD_OK;
+  if (c->pair_style == 2 && !pair_eam_can_split(c)) return B200MD_OK;   // eam: the single-type kernels only
+  if (c->pair_style != 1 && c->pair_style != 2) return B200MD_OK;
   const int n = c->nlocal, nall = n + c->nghost;
   const TileGeom T = tile_geom(c);
   const int nseg = T.nsegx * c->bg.nbin[1] * c->bg.nbin[2];
@@ -549,7 +514,8 @@ int pair_lj_tiled_prepare(b200md_ctx *c)
   c->tiled_nseg = nseg;
   c->tiled_max_staged = c->flags_h[6];
   const size_t nt2 = (size_t) (c->lj.ntypes + 1) * (c->lj.ntypes + 1);
-  const size_t smem = (size_t) c->tiled_max_staged * sizeof(double4) + (c->lj.ntypes == 1 ? 0 : 6 * nt2 * sizeof(double));
+  const size_t extra = c->pair_style == 2 ? (size_t) 7 * (c->eam.nr + 1) * sizeof(double) : (c->lj.ntypes == 1 ? 0 : 6 * nt2 * sizeof(double));
+  const size_t smem = (size_t) c->tiled_max_staged * sizeof(double4) + extra;
   // usable only when every neighbor was found in its segment's neighbourhood and the staging area fits
   c->tiled_valid = !c->flags_h[7] && c->tiled_max_staged > 0 && c->tiled_max_staged < 0xFFFF && smem <= 200 * 1024;
   return B200MD_OK;

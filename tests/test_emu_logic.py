@@ -677,3 +677,36 @@ def test_emu_tiled_lj_decomposed_and_chain(emu, monkeypatch):
     for ra, rb in zip(a, b):
         assert np.array_equal(ra["tag1"], rb["tag1"]) and np.array_equal(ra["x1"], rb["x1"]) and ra["builds"] == rb["builds"]
     chain.test_chain_setup_forces_vs_reference(emu)
+
+
+@pytest.mark.parametrize("g_bins", ["1", "4", "64"])
+def test_emu_tiled_eam_equals_plain(emu, oracle, g_bins, monkeypatch):
+    """the tiled single-type EAM passes (k_eam_rho_fp_tiled, k_eam_force_tiled) == the default ones bit for bit, on the
+    reference-minted Cu case and on a 12^3-cell block through its check-yes rebuilds; 8 emulated ranks likewise"""
+    g = load_golden("eam_500")
+    out = []
+    for tiled in (False, True):
+        if tiled:
+            monkeypatch.setenv("B200MD_LJ_TILED", "1")
+            monkeypatch.setenv("B200MD_TILED_G", g_bins)
+        else:
+            monkeypatch.delenv("B200MD_LJ_TILED", raising=False)
+        md = make_device_system(emu, "eam_500", g)
+        md.run(30, thermo_every=10)
+        assert emu.lib.load().b200md_tiled_active(md.ctx.h) == int(tiled)
+        big, _ = gp._bench_system(emu, oracle, "eam", 8)
+        big.run(25)
+        out.append((md.gather(), md.thermo_log, big.gather(), big.neigh_stats()["builds"]))
+        md.close()
+        big.close()
+    (a, ta, ba, na), (b, tb, bb, nb_) = out
+    assert np.array_equal(a["x"], b["x"]) and np.array_equal(a["f"], b["f"]) and np.array_equal(ba["x"], bb["x"]) and na == nb_ >= 2
+    for x, y in zip(ta, tb):
+        assert abs(x["pe"] - y["pe"]) <= 1e-13 * abs(x["pe"]) and abs(x["press"] - y["press"]) <= 1e-11 * abs(x["press"])
+    if g_bins == "4":
+        monkeypatch.delenv("B200MD_LJ_TILED", raising=False)
+        p = run_decomposed_emu(emu, 8, (2, 2, 2), "eam", 5, 30)
+        monkeypatch.setenv("B200MD_LJ_TILED", "1")
+        q = run_decomposed_emu(emu, 8, (2, 2, 2), "eam", 5, 30)
+        for rp, rq in zip(p, q):
+            assert np.array_equal(rp["tag1"], rq["tag1"]) and np.array_equal(rp["x1"], rq["x1"]) and rp["builds"] == rq["builds"]

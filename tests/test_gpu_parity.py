@@ -324,7 +324,7 @@ def test_large_lj_properties(pkg):
                     reason="shared-memory tiled lj/cut (B200MD_LJ_TILED=1) was written after round 1's GPU budget was spent: opt-in "
                            "(B200MD_TEST_TILED=1) until it has run on hardware")
 @pytest.mark.parametrize("g_bins", ["3", "6", "12"])
-@pytest.mark.parametrize("name,steps", [("lj_500", 45), ("lj2_864", 25)])
+@pytest.mark.parametrize("name,steps", [("lj_500", 45), ("lj2_864", 25), ("eam_500", 30)])
 def test_tiled_lj_equals_plain(pkg, name, steps, g_bins, monkeypatch):
     """B200MD_LJ_TILED=1 (k_lj_tiled: a bin segment's neighbourhood staged in shared memory, 16-bit slot lists) follows
     the plain kernel's trajectory bit for bit; energies agree to round-off"""

@@ -9,8 +9,8 @@ timeout 900 python -m pytest tests -m gpu -q -rxX > gpurun_out/r2j1_pytest.log 2
 B200MD_TEST_PIPELINE=1 B200MD_TEST_OVERLAP=1 B200MD_TEST_TILED=1 timeout 300 python -m pytest tests/test_gpu_parity.py -m gpu -q -rxX -k "host_buffer or overlapped or tiled" > gpurun_out/r2j1_optin.log 2>&1; echo "optin rc=$?"; tail -5 gpurun_out/r2j1_optin.log
 timeout 120 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r2j1_smoke.log 2>&1; echo "smoke rc=$?"
 timeout 420 python bench.py --steps 100 --warmup 20 --chain 8 > gpurun_out/r2j1_bench.log 2>&1; echo "bench rc=$?"; tail -1 gpurun_out/r2j1_bench.log | cut -c1-600
-# the shared-memory tiled lj/cut kernel against the default one, bins per block swept (LJ only, no CPU / e2e legs)
+# the shared-memory tiled lj/cut and eam kernels against the default ones, bins per block swept (no CPU / e2e legs)
 for g in 4 6 8 12; do
-  B200MD_LJ_TILED=1 B200MD_TILED_G=$g timeout 200 python bench.py --steps 100 --warmup 20 --no-eam --no-cpu --no-e2e > gpurun_out/r2j1_tiled_g$g.log 2>&1
-  echo "tiled G=$g rc=$?"; tail -1 gpurun_out/r2j1_tiled_g$g.log | cut -c1-300
+  B200MD_LJ_TILED=1 B200MD_TILED_G=$g timeout 300 python bench.py --steps 100 --warmup 20 --no-cpu --no-e2e > gpurun_out/r2j1_tiled_g$g.log 2>&1
+  echo "tiled G=$g rc=$?"; tail -1 gpurun_out/r2j1_tiled_g$g.log | python -c "import sys,json; l=json.loads(sys.stdin.read()); print(l['value'], l['ms_per_step'], l.get('eam',{}).get('value'))"
 done
