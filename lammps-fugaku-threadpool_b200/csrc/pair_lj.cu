@@ -444,9 +444,21 @@ k_lj_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__restrict_
     const int n = numneigh[i];
     const unsigned short *nb = neigh16 + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
     double fxi = 0.0, fyi = 0.0, fzi = 0.0;
-#pragma unroll 4
-    for (int k = 0; k < n; k++) {
-      const double4 pj = s_tile[__ldcs(nb + (size_t) k * TILE)];
+    // the list entries of the NEXT batch are in flight (global memory) while this batch is computed from shared memory
+    constexpr int PF = 4;
+    const int nlast = max(n - 1, 0);
+    unsigned short enx[PF];
+#pragma unroll
+    for (int u = 0; u < PF; u++) enx[u] = __ldcs(nb + (size_t) min(u, nlast) * TILE);
+    for (int k0 = 0; k0 < n; k0 += PF) {
+      unsigned short ent[PF];
+#pragma unroll
+      for (int u = 0; u < PF; u++) ent[u] = enx[u];
+#pragma unroll
+      for (int u = 0; u < PF; u++) enx[u] = __ldcs(nb + (size_t) min(k0 + PF + u, nlast) * TILE);
+#pragma unroll
+      for (int u = 0; u < PF; u++) {
+      const double4 pj = s_tile[ent[u]];
       const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
       const double rsq = dx * dx + dy * dy + dz * dz;
       double cutsq, lj1, lj2;
@@ -456,7 +468,7 @@ k_lj_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__restrict_
         const int t = trow + pos_type(pj);
         cutsq = s_tab[t]; lj1 = s_tab[nt2 + t]; lj2 = s_tab[2 * nt2 + t];
       }
-      const bool in = rsq < cutsq;
+      const bool in = rsq < cutsq && (k0 + u < n);
       const double r2inv = rcp_pos(rsq);
       const double r6inv = r2inv * r2inv * r2inv;
       const double forcelj = r6inv * (lj1 * r6inv - lj2);
@@ -480,6 +492,7 @@ k_lj_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__restrict_
         acc[4] += dx * dy * hf;
         acc[5] += dx * dz * hf;
         acc[6] += dy * dz * hf;
+      }
       }
     }
     fx[i] = fxi;
