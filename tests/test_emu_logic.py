@@ -710,3 +710,21 @@ def test_emu_tiled_eam_equals_plain(emu, oracle, g_bins, monkeypatch):
         q = run_decomposed_emu(emu, 8, (2, 2, 2), "eam", 5, 30)
         for rp, rq in zip(p, q):
             assert np.array_equal(rp["tag1"], rq["tag1"]) and np.array_equal(rp["x1"], rq["x1"]) and rp["builds"] == rq["builds"]
+
+
+@pytest.mark.parametrize("env", [{"B200MD_CLUSTER": "2"}, {"B200MD_CLUSTER": "4"}, {"B200MD_CLUSTER": "2", "B200MD_LANES": "1"},
+                                 {"B200MD_LJ_PLAIN": "1"}, {"B200MD_EAM_GENERIC": "1"}, {"B200MD_BUILD_FP64": "1"}])
+@pytest.mark.parametrize("name", ["lj2_864", "eam_500"])
+def test_emu_tuning_knobs_keep_the_physics(emu, name, env, monkeypatch):
+    """the alternative kernels behind the tuning knobs (cluster lists of 2 / 4 atoms, lane clusters, the plain lj kernel,
+    the generic multi-type eam kernels, the all-FP64 build) still reproduce the reference goldens"""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    g = load_golden(name)
+    md = make_device_system(emu, name, g)
+    md.setup()
+    a = md.gather()
+    assert np.abs(a["f"] - g["a_f"]).max() <= F_RTOL * np.abs(g["a_f"]).max()
+    md.run(int(g["nmore"][0]))
+    np.testing.assert_allclose(thermo_vec(md.thermo_log[-1]), g["b_thermo"][:3], rtol=THERMO_RTOL)
+    md.close()
