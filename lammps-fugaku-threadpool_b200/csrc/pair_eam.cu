@@ -655,8 +655,9 @@ k_eam_rho_fp_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__r
                    EAMParams P, const double *__restrict__ tab1, double *__restrict__ rho_out, double *__restrict__ fp_out,
                    double4 *__restrict__ posfp, double *__restrict__ partials)
 {
-  extern __shared__ double4 s_tile[];   // [max_staged] positions, then [4][n1] rhor c3..c6
-  double *s_t = reinterpret_cast<double *>(s_tile + max_staged);
+  extern __shared__ double4 s_tile[];   // x[], y[], z[], (unused) of max_staged doubles each (see k_lj_tiled), then [4][n1] rhor c3..c6
+  double *s_x = reinterpret_cast<double *>(s_tile), *s_y = s_x + max_staged, *s_z = s_y + max_staged;
+  double *s_t = s_z + 2 * max_staged;
   const int n1 = P.nr + 1;
   int ks[9], off[10], own_s, own_e, by, bz;
   tile_rows(T, bin_start, blockIdx.x, ks, off, own_s, own_e, by, bz);
@@ -664,7 +665,10 @@ k_eam_rho_fp_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__r
 #pragma unroll
   for (int r = 0; r < 9; r++) {
     const int len = off[r + 1] - off[r];
-    for (int k = threadIdx.x; k < len; k += blockDim.x) s_tile[off[r] + k] = ld_pos256(pos + cell_list[ks[r] + k]);
+    for (int k = threadIdx.x; k < len; k += blockDim.x) {
+      const double4 q = ld_pos256(pos + cell_list[ks[r] + k]);
+      s_x[off[r] + k] = q.x; s_y[off[r] + k] = q.y; s_z[off[r] + k] = q.z;
+    }
   }
   __syncthreads();
   double acc[1] = {0.0};
@@ -677,8 +681,8 @@ k_eam_rho_fp_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__r
     double rho = 0.0;
 #pragma unroll 4
     for (int k = 0; k < n; k++) {
-      const double4 pj = s_tile[__ldcs(nb + (size_t) k * TILE)];
-      const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+      const int e = __ldcs(nb + (size_t) k * TILE);
+      const double dx = pi.x - s_x[e], dy = pi.y - s_y[e], dz = pi.z - s_z[e];
       const double rsq = dx * dx + dy * dy + dz * dz;
       if (rsq < P.cutforcesq) {
         double p = rsq * rsqrt(rsq) * P.rdr + 1.0;
@@ -715,8 +719,9 @@ k_eam_force_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__re
                   EAMParams P, const double *__restrict__ tab1, double *__restrict__ fx, double *__restrict__ fy, double *__restrict__ fz,
                   double *__restrict__ partials)
 {
-  extern __shared__ double4 s_tile[];   // [max_staged] {x,y,z,fp}, then [7][n1]: rhor c0..c2, z2r c3..c6
-  double *s_t = reinterpret_cast<double *>(s_tile + max_staged);
+  extern __shared__ double4 s_tile[];   // x[], y[], z[], fp[] of max_staged doubles each, then [7][n1]: rhor c0..c2, z2r c3..c6
+  double *s_x = reinterpret_cast<double *>(s_tile), *s_y = s_x + max_staged, *s_z = s_y + max_staged, *s_w = s_z + max_staged;
+  double *s_t = s_w + max_staged;
   const int n1 = P.nr + 1;
   int ks[9], off[10], own_s, own_e, by, bz;
   tile_rows(T, bin_start, blockIdx.x, ks, off, own_s, own_e, by, bz);
@@ -724,7 +729,10 @@ k_eam_force_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__re
 #pragma unroll
   for (int r = 0; r < 9; r++) {
     const int len = off[r + 1] - off[r];
-    for (int k = threadIdx.x; k < len; k += blockDim.x) s_tile[off[r] + k] = ld_pos256(posfp + cell_list[ks[r] + k]);
+    for (int k = threadIdx.x; k < len; k += blockDim.x) {
+      const double4 q = ld_pos256(posfp + cell_list[ks[r] + k]);
+      s_x[off[r] + k] = q.x; s_y[off[r] + k] = q.y; s_z[off[r] + k] = q.z; s_w[off[r] + k] = q.w;
+    }
   }
   __syncthreads();
   double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
@@ -737,10 +745,11 @@ k_eam_force_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__re
     double fxi = 0.0, fyi = 0.0, fzi = 0.0;
 #pragma unroll 2
     for (int k = 0; k < n; k++) {
-      const double4 pj = s_tile[__ldcs(nb + (size_t) k * TILE)];
-      const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+      const int e = __ldcs(nb + (size_t) k * TILE);
+      const double dx = pi.x - s_x[e], dy = pi.y - s_y[e], dz = pi.z - s_z[e];
       const double rsq = dx * dx + dy * dy + dz * dz;
       if (rsq < P.cutforcesq) {
+        const double pjw = s_w[e];
         const double recip = rsqrt(rsq);
         const double r = rsq * recip;
         double p = r * P.rdr + 1.0;
@@ -754,7 +763,7 @@ k_eam_force_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__re
         const double z2p = ((3.0 * z3 * p + 2.0 * z4) * p + z5) * P.rdr;
         const double phi = z2 * recip;
         const double phip = z2p * recip - phi * recip;
-        const double psip = (pi.w + pj.w) * rhoip + phip;
+        const double psip = (pi.w + pjw) * rhoip + phip;
         const double fpair = -psip * recip;
         fxi += dx * fpair;
         fyi += dy * fpair;

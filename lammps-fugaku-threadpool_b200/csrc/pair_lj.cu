@@ -422,8 +422,12 @@ k_lj_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__restrict_
            LJOne one, const double *__restrict__ tables, int ntypes, double *__restrict__ fx, double *__restrict__ fy,
            double *__restrict__ fz, double *__restrict__ partials)
 {
-  extern __shared__ double4 s_tile[];   // [max_staged] staged atoms, then 6 tables of (ntypes+1)^2 when !ONETYPE
-  double *s_tab = reinterpret_cast<double *>(s_tile + max_staged);
+  // staged atoms as four arrays x[], y[], z[], w[] of max_staged doubles (the lists are sorted by slot, so the lanes
+  // of a warp read NEARBY slots at the same step: 8-byte elements then fall into different banks, where 32-byte
+  // records would use only a quarter of them), then 6 tables of (ntypes+1)^2 when !ONETYPE
+  extern __shared__ double4 s_tile[];
+  double *s_x = reinterpret_cast<double *>(s_tile), *s_y = s_x + max_staged, *s_z = s_y + max_staged, *s_w = s_z + max_staged;
+  double *s_tab = s_w + max_staged;
   const int nt1 = ntypes + 1, nt2 = nt1 * nt1;
   int ks[9], off[10], own_s, own_e, by, bz;
   tile_rows(T, bin_start, blockIdx.x, ks, off, own_s, own_e, by, bz);
@@ -432,7 +436,11 @@ k_lj_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__restrict_
 #pragma unroll
   for (int r = 0; r < 9; r++) {
     const int len = off[r + 1] - off[r];
-    for (int k = threadIdx.x; k < len; k += blockDim.x) s_tile[off[r] + k] = ld_pos256(pos + cell_list[ks[r] + k]);
+    for (int k = threadIdx.x; k < len; k += blockDim.x) {
+      const double4 q = ld_pos256(pos + cell_list[ks[r] + k]);
+      s_x[off[r] + k] = q.x; s_y[off[r] + k] = q.y; s_z[off[r] + k] = q.z;
+      if (!ONETYPE) s_w[off[r] + k] = q.w;
+    }
   }
   __syncthreads();
   double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
@@ -458,7 +466,9 @@ k_lj_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__restrict_
       for (int u = 0; u < PF; u++) enx[u] = __ldcs(nb + (size_t) min(k0 + PF + u, nlast) * TILE);
 #pragma unroll
       for (int u = 0; u < PF; u++) {
-      const double4 pj = s_tile[ent[u]];
+      double4 pj;
+      pj.x = s_x[ent[u]]; pj.y = s_y[ent[u]]; pj.z = s_z[ent[u]];
+      pj.w = ONETYPE ? 0.0 : s_w[ent[u]];
       const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
       const double rsq = dx * dx + dy * dy + dz * dz;
       double cutsq, lj1, lj2;
