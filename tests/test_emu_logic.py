@@ -357,7 +357,7 @@ def test_emu_chain_with_counter_thermostat(emu):
     for _ in range(2):
         md = chain.make_chain_device(emu, g, langevin=False)
         md.fix("langevin", 1.0, 1.0, 10.0, 904297, rng="counter")
-        md.run(30)
+        md.run(8)
         out.append((md.thermo_log[-1], md.gather()))
         md.close()
     (ta, ga), (tb, gb) = out
