@@ -62,7 +62,7 @@ extern "C" int b200md_create(b200md_ctx **out, int device, int nranks, int rank,
   c->tiled = getenv("B200MD_LJ_TILED") != nullptr;
   if (const char *e = getenv("B200MD_TILED_G")) {
     int v = atoi(e);
-    if (v >= 1 && v <= 64) c->tiled_g = v;
+    if (v >= 1 && v <= 4096) c->tiled_g_user = v;
   }
   *out = c;
   CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));

@@ -200,7 +200,7 @@ struct b200md_ctx {
   DevBuf<unsigned short> neigh16;   // same blocked-transposed layout as neigh
   DevBuf<int> cell_pos;             // [nall] slot of each atom in cell_list (inverse permutation)
   bool tiled = false, tiled_valid = false;
-  int tiled_g = 6, tiled_nseg = 0, tiled_max_staged = 0;
+  int tiled_g = 6, tiled_g_user = 0, tiled_nseg = 0, tiled_max_staged = 0;   // tiled_g_user: B200MD_TILED_G, 0 = choose by bin population
   DevBuf<double> peratom;   // [7][peratom_stride]: eatom, vatom xx yy zz xy xz yz of the owned atoms (b200md_pair_peratom)
   size_t peratom_stride = 0;
   int peratom_n = 0;        // owned atoms the tallies are valid for, 0 = none

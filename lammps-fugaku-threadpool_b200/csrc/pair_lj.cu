@@ -519,6 +519,13 @@ int pair_lj_tiled_prepare(b200md_ctx *c)
   if (c->pair_style == 2 && !pair_eam_can_split(c)) return B200MD_OK;   // eam: the single-type kernels only
   if (c->pair_style != 1 && c->pair_style != 2) return B200MD_OK;
   const int n = c->nlocal, nall = n + c->nghost;
+  if (c->tiled_g_user <= 0) {
+    // bins per block: about 112 atoms per 128-thread block (lj melt: 18.5 atoms per bin -> 6; chain: 3 per bin -> 37)
+    const double per_bin = (double) n / ((double) c->bg.nbin[0] * c->bg.nbin[1] * c->bg.nbin[2]);
+    int g = (int) (112.0 / (per_bin > 0.1 ? per_bin : 0.1) + 0.5);
+    c->tiled_g = g < 1 ? 1 : (g > c->bg.nbin[0] ? c->bg.nbin[0] : g);
+  } else
+    c->tiled_g = c->tiled_g_user;
   const TileGeom T = tile_geom(c);
   const int nseg = T.nsegx * c->bg.nbin[1] * c->bg.nbin[2];
   TRY(dev_ensure(c, c->cell_pos, (size_t) nall));

@@ -644,7 +644,7 @@ def test_emu_bench_main_prints_the_contract_line(emu, monkeypatch, capsys):
 
 
 # ---- shared-memory tiled lj/cut (B200MD_LJ_TILED=1, opt-in) ----
-@pytest.mark.parametrize("g_bins", ["1", "3", "6", "64"])
+@pytest.mark.parametrize("g_bins", ["1", "3", "auto", "64"])
 @pytest.mark.parametrize("name,steps", [("lj_500", 45), ("lj2_864", 25)])
 def test_emu_tiled_lj_equals_plain(emu, name, steps, g_bins, monkeypatch):
     """k_lj_tiled (neighbourhood of a bin segment staged in shared memory, 16-bit slot lists) == k_lj_lanes bit for bit:
@@ -655,7 +655,10 @@ def test_emu_tiled_lj_equals_plain(emu, name, steps, g_bins, monkeypatch):
     a = make_device_system(emu, name, g)
     a.run(steps, thermo_every=10)
     monkeypatch.setenv("B200MD_LJ_TILED", "1")
-    monkeypatch.setenv("B200MD_TILED_G", g_bins)
+    if g_bins == "auto":
+        monkeypatch.delenv("B200MD_TILED_G", raising=False)
+    else:
+        monkeypatch.setenv("B200MD_TILED_G", g_bins)
     b = make_device_system(emu, name, g)
     b.run(steps, thermo_every=10)
     assert emu.lib.load().b200md_tiled_active(b.ctx.h) == 1

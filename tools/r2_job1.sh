@@ -10,7 +10,7 @@ B200MD_TEST_PIPELINE=1 B200MD_TEST_OVERLAP=1 B200MD_TEST_TILED=1 timeout 300 pyt
 timeout 120 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r2j1_smoke.log 2>&1; echo "smoke rc=$?"
 timeout 420 python bench.py --steps 100 --warmup 20 --chain 8 > gpurun_out/r2j1_bench.log 2>&1; echo "bench rc=$?"; tail -1 gpurun_out/r2j1_bench.log | cut -c1-600
 # the shared-memory tiled lj/cut and eam kernels against the default ones, bins per block swept (no CPU / e2e legs)
-for g in 4 6 8 12; do
+for g in 0 4 8 12; do   # 0 = automatic (about 112 atoms per block)
   B200MD_LJ_TILED=1 B200MD_TILED_G=$g timeout 300 python bench.py --steps 100 --warmup 20 --no-cpu --no-e2e > gpurun_out/r2j1_tiled_g$g.log 2>&1
   echo "tiled G=$g rc=$?"; tail -1 gpurun_out/r2j1_tiled_g$g.log | python -c "import sys,json; l=json.loads(sys.stdin.read()); print(l['value'], l['ms_per_step'], l.get('eam',{}).get('value'))"
 done
