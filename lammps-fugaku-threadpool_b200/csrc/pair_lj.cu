@@ -401,13 +401,13 @@ k_tile_convert(TileGeom T, const int *__restrict__ bin_start, const int *__restr
     const size_t base = (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
     for (int k = 0; k < n; k++) {
       const int j = neigh[base + (size_t) k * TILE] & CLJMASK;
-      const int bj = atom_bin[j];
-      const int bjy = (bj / T.g.mbin[0]) % T.g.mbin[1], bjz = bj / (T.g.mbin[0] * T.g.mbin[1]);
-      const int r = (bjz - bz + 1) * 3 + (bjy - by + 1);
+      // the staged rows are disjoint slot ranges of cell_list: the neighbor's slot alone says which row it is in
+      const int sj = cell_pos[j];
       int local = 0xFFFF;
-      if (r >= 0 && r < 9) {
-        const int l = off[r] + cell_pos[j] - ks[r];
-        if (l >= off[r] && l < off[r + 1] && l < 0xFFFF) local = l;
+#pragma unroll
+      for (int r = 0; r < 9; r++) {
+        const int l = off[r] + sj - ks[r];
+        if (sj >= ks[r] && l < off[r + 1] && l < 0xFFFF) local = l;
       }
       if (local == 0xFFFF) flags[7] = 1;   // outside the staged neighbourhood: the tiled path must not be used
       neigh16[base + (size_t) k * TILE] = (unsigned short) local;
