@@ -198,8 +198,7 @@ struct b200md_ctx {
   // atoms of its 3 x 3 x (TG+2) bin neighbourhood are staged in shared memory once per step and the list entries are
   // 16-bit slots of that staging area
   DevBuf<unsigned short> neigh16;   // same blocked-transposed layout as neigh
-  DevBuf<int> cell_pos;             // [nall] slot of each atom in cell_list (inverse permutation)
-  bool tiled = false, tiled_valid = false;
+  bool tiled = false, tiled_valid = false, tiled_emitted = false;   // emitted: the last build wrote neigh16
   int tiled_g = 6, tiled_g_user = 0, tiled_nseg = 0, tiled_max_staged = 0;   // tiled_g_user: B200MD_TILED_G, 0 = choose by bin population
   DevBuf<double> peratom;   // [7][peratom_stride]: eatom, vatom xx yy zz xy xz yz of the owned atoms (b200md_pair_peratom)
   size_t peratom_stride = 0;
@@ -347,7 +346,8 @@ int nve_initial(b200md_ctx *c, double dtv, double dtf);
 int nve_final(b200md_ctx *c, double dtf);
 int thermo_ke(b200md_ctx *c, double *sum_mv2);
 int reduce_partials(b200md_ctx *c, int nblocks, int ncomp, int dst);  // partials -> red_d[dst..]
-int pair_lj_tiled_prepare(b200md_ctx *c);   // after a list build: 16-bit staged-slot lists (no-op unless opted in)
+bool pair_tiled_wanted(b200md_ctx *c);      // before a list build: emit 16-bit staged-slot lists? (B200MD_LJ_TILED=1)
+int pair_lj_tiled_prepare(b200md_ctx *c);   // after it: can the tiled kernels serve this list?
 int pair_lj_peratom(b200md_ctx *c, double *out, size_t stride);       // eatom / vatom pass, out = [7][stride]
 int pair_eam_peratom(b200md_ctx *c, double *out, size_t stride);
 

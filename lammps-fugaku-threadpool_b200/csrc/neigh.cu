@@ -435,12 +435,20 @@ struct BondBuild {
   int *bond_idx;               // [nlocal][maxb] out
   int maxb;
 };
-template <int ONETYPE, int STAGE, int BONDED>
+// TILED16 (B200MD_LJ_TILED=1, pair_lj.cu): next to every list entry its 16-bit slot in the staging area of the bin
+// segment the atom belongs to -- the candidate loop already walks the segment's rows in staging order, so the slot is
+// the running row offset plus the candidate's position in its row.  flags[6] = largest staging area, flags[7] = a slot
+// did not fit 16 bits.
+struct TileEmit {
+  unsigned short *neigh16;
+  int tg;   // bins per segment along x
+};
+template <int ONETYPE, int STAGE, int BONDED, int TILED16>
 __global__ void __launch_bounds__(BUILD_WARPS * 32)
 k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int nlocal, BinGeom g,
              const int *__restrict__ bin_start, const double *__restrict__ cutneighsq, int ntypes, float tol, int maxneigh,
              int *__restrict__ numneigh, int *__restrict__ neigh, int *__restrict__ flags, int *__restrict__ tile_ghost,
-             BondBuild bb)
+             BondBuild bb, TileEmit te)
 {
   __shared__ double s_cut[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
   __shared__ float s_cutf[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
@@ -484,10 +492,19 @@ k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, in
         prsq[m] = 3.0e38f;
       }
     }
+    int toff = 0;   // TILED16: staging offset of the current row of this bin's segment
     for (int dz = -1; dz <= 1; dz++)
       for (int dy = -1; dy <= 1; dy++) {
         const int cell = ((bz + dz) * g.mbin[1] + (by + dy)) * g.mbin[0] + bx - 1;
         const int ks = bin_start[cell], ke = bin_start[cell + 3];
+        int tbase = 0;
+        if (TILED16) {
+          const int sx = obx / te.tg, gx = min(te.tg, g.nbin[0] - sx * te.tg);
+          const int first = cell - (obx - sx * te.tg);           // the row's first staged bin: bx0 - 1
+          const int tks = bin_start[first];
+          tbase = toff - tks;
+          toff += bin_start[first + gx + 2] - tks;
+        }
 #pragma unroll 4
         for (int k = ks; k < ke; k++) {
           const BinRec c = ld_rec(rec + k);
@@ -517,6 +534,11 @@ k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, in
             if (n < maxneigh) {
               if (STAGE) s_mine[n * 32] = j | (1 << CLBITS);
               else neigh[base + (size_t) n * TILE] = j | (1 << CLBITS);
+              if (TILED16) {
+                const int slot = tbase + k;
+                if (slot >= 0xFFFF) flags[7] = 1;
+                te.neigh16[base + (size_t) n * TILE] = (unsigned short) slot;
+              }
             }
             n++;
           }
@@ -538,6 +560,7 @@ k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, in
           ghost_seen |= pbest[m] >= nlocal;
         }
     }
+    if (TILED16 && lane == 0 && gbase == s0) atomicMax(&flags[6], toff);
     if (tile_ghost && owned && ghost_seen) atomicOr(&tile_ghost[i >> 5], 1);
     nmax = max(nmax, owned ? n : 0);
   }
@@ -721,8 +744,8 @@ int neigh_build_lists(b200md_ctx *c)
       const bool stage = stage_bytes <= 96 * 1024 && getenv("B200MD_BUILD_STAGE") != nullptr;
       static bool attr_done = false;
       if (!attr_done) {
-        CU(cudaFuncSetAttribute(k_build_bins<1, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-        CU(cudaFuncSetAttribute(k_build_bins<0, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        CU(cudaFuncSetAttribute(k_build_bins<1, 1, 0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        CU(cudaFuncSetAttribute(k_build_bins<0, 1, 0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
         attr_done = true;
       }
       int *tile_ghost = nullptr;
@@ -742,17 +765,34 @@ int neigh_build_lists(b200md_ctx *c)
         bb.bond_idx = c->bonds.idx.p;
         bb.maxb = c->bonds.maxb;
       }
-#define BB_ARGS c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d, tile_ghost, bb
+      TileEmit te = {nullptr, 1};
+      const bool tiled16 = pair_tiled_wanted(c);
+      if (tiled16) {
+        TRY(dev_ensure(c, c->neigh16, (size_t) ntiles * TILE * c->maxneigh));
+        CU(cudaMemsetAsync(c->flags_d + 6, 0, 2 * sizeof(int), c->stream));
+        te.neigh16 = c->neigh16.p;
+        te.tg = c->tiled_g;
+      }
+#define BB_ARGS c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d, tile_ghost, bb, te
       const int bgrid = cdiv(nown, BUILD_WARPS), bthr = BUILD_WARPS * 32;
-      if (bonded) {
-        if (c->ntypes == 1) k_build_bins<1, 0, 1><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
-        else k_build_bins<0, 0, 1><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+      c->tiled_emitted = tiled16;
+      if (tiled16) {
+        if (bonded) {
+          if (c->ntypes == 1) k_build_bins<1, 0, 1, 1><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+          else k_build_bins<0, 0, 1, 1><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+        } else {
+          if (c->ntypes == 1) k_build_bins<1, 0, 0, 1><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+          else k_build_bins<0, 0, 0, 1><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+        }
+      } else if (bonded) {
+        if (c->ntypes == 1) k_build_bins<1, 0, 1, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+        else k_build_bins<0, 0, 1, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
       } else if (c->ntypes == 1) {
-        if (stage) k_build_bins<1, 1, 0><<<bgrid, bthr, stage_bytes, c->stream>>>(BB_ARGS);
-        else k_build_bins<1, 0, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+        if (stage) k_build_bins<1, 1, 0, 0><<<bgrid, bthr, stage_bytes, c->stream>>>(BB_ARGS);
+        else k_build_bins<1, 0, 0, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
       } else {
-        if (stage) k_build_bins<0, 1, 0><<<bgrid, bthr, stage_bytes, c->stream>>>(BB_ARGS);
-        else k_build_bins<0, 0, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+        if (stage) k_build_bins<0, 1, 0, 0><<<bgrid, bthr, stage_bytes, c->stream>>>(BB_ARGS);
+        else k_build_bins<0, 0, 0, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
       }
 #undef BB_ARGS
       LAUNCH_CHECK();
@@ -768,7 +808,7 @@ int neigh_build_lists(b200md_ctx *c)
 #undef BUILD_ARGS
       LAUNCH_CHECK();
     }
-    CU(cudaMemcpyAsync(c->flags_h, c->flags_d, 6 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(c->flags_h, c->flags_d, 8 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     if (c->flags_h[0]) return b200md_fail(c, B200MD_ERR_NONFINITE, "Non-numeric positions - simulation unstable");
     if (c->flags_h[5]) return b200md_fail(c, B200MD_ERR_LOST_ATOMS, "Bond atoms missing: a bond partner is not within the neighbor cutoff");

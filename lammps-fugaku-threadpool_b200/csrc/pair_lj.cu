@@ -379,42 +379,6 @@ int pair_lj_peratom(b200md_ctx *c, double *out, size_t stride)
 // neighbors from shared memory through 16-bit slot numbers (which also halves the list traffic, the largest DRAM
 // term of the step).  List order, arithmetic and summation order are those of k_lj_lanes: forces are bit-identical.
 // ------------------------------------------------------------------------------------------------------------
-__global__ void k_cell_pos(const int *__restrict__ cell_list, int nall, int *__restrict__ cell_pos)
-{
-  const int k = blockIdx.x * blockDim.x + threadIdx.x;
-  if (k < nall) cell_pos[cell_list[k]] = k;
-}
-
-// list entries (global atom index) -> slots of the owning segment's staging area; flags[6] = largest staging area
-__global__ void __launch_bounds__(128)
-k_tile_convert(TileGeom T, const int *__restrict__ bin_start, const int *__restrict__ cell_list, const int *__restrict__ atom_bin,
-               const int *__restrict__ cell_pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh, int nlocal,
-               unsigned short *__restrict__ neigh16, int *__restrict__ flags)
-{
-  int ks[9], off[10], own_s, own_e, by, bz;
-  tile_rows(T, bin_start, blockIdx.x, ks, off, own_s, own_e, by, bz);
-  if (threadIdx.x == 0) atomicMax(&flags[6], off[9]);
-  for (int slot = own_s + threadIdx.x; slot < own_e; slot += blockDim.x) {
-    const int i = cell_list[slot];
-    if (i >= nlocal) continue;   // a ghost that rounding put into an owned bin
-    const int n = numneigh[i];
-    const size_t base = (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
-    for (int k = 0; k < n; k++) {
-      const int j = neigh[base + (size_t) k * TILE] & CLJMASK;
-      // the staged rows are disjoint slot ranges of cell_list: the neighbor's slot alone says which row it is in
-      const int sj = cell_pos[j];
-      int local = 0xFFFF;
-#pragma unroll
-      for (int r = 0; r < 9; r++) {
-        const int l = off[r] + sj - ks[r];
-        if (sj >= ks[r] && l < off[r + 1] && l < 0xFFFF) local = l;
-      }
-      if (local == 0xFFFF) flags[7] = 1;   // outside the staged neighbourhood: the tiled path must not be used
-      neigh16[base + (size_t) k * TILE] = (unsigned short) local;
-    }
-  }
-}
-
 template <int EVFLAG, int ONETYPE>
 __global__ void __launch_bounds__(128)
 k_lj_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__restrict__ cell_list, const double4 *__restrict__ pos,
@@ -512,41 +476,36 @@ k_lj_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__restrict_
   if (EVFLAG) block_partials<7>(acc, partials);
 }
 
-int pair_lj_tiled_prepare(b200md_ctx *c)
+// does this context want (and qualify for) the tiled kernels at the coming list build?  Also fixes the segment length.
+bool pair_tiled_wanted(b200md_ctx *c)
 {
-  c->tiled_valid = false;
-  if (!c->tiled || c->cl != 1 || c->host_ghosts) return B200MD_OK;
-  if (c->pair_style == 2 && !pair_eam_can_split(c)) return B200MD_OK;   // eam: the single-type kernels only
-  if (c->pair_style != 1 && c->pair_style != 2) return B200MD_OK;
-  const int n = c->nlocal, nall = n + c->nghost;
+  if (!c->tiled || c->cl != 1 || c->host_ghosts) return false;
+  if (c->pair_style == 2 && !pair_eam_can_split(c)) return false;   // eam: the single-type kernels only
+  if (c->pair_style != 1 && c->pair_style != 2) return false;
   if (c->tiled_g_user <= 0) {
     // bins per block: about 112 atoms per 128-thread block (lj melt: 18.5 atoms per bin -> 6; chain: 3 per bin -> 37)
-    const double per_bin = (double) n / ((double) c->bg.nbin[0] * c->bg.nbin[1] * c->bg.nbin[2]);
+    const double per_bin = (double) c->nlocal / ((double) c->bg.nbin[0] * c->bg.nbin[1] * c->bg.nbin[2]);
     int g = (int) (112.0 / (per_bin > 0.1 ? per_bin : 0.1) + 0.5);
     c->tiled_g = g < 1 ? 1 : (g > c->bg.nbin[0] ? c->bg.nbin[0] : g);
   } else
     c->tiled_g = c->tiled_g_user;
+  return true;
+}
+
+// after a list build that emitted the 16-bit slot lists (k_build_bins<..., TILED16>; flags_h[6..7] are its verdict)
+int pair_lj_tiled_prepare(b200md_ctx *c)
+{
+  const bool emitted = c->tiled_emitted;
+  c->tiled_emitted = false;
+  c->tiled_valid = false;
+  if (!emitted) return B200MD_OK;
   const TileGeom T = tile_geom(c);
-  const int nseg = T.nsegx * c->bg.nbin[1] * c->bg.nbin[2];
-  TRY(dev_ensure(c, c->cell_pos, (size_t) nall));
-  TRY(dev_ensure(c, c->neigh16, (size_t) cdiv(n, TILE) * TILE * c->maxneigh));
-  CU(cudaMemsetAsync(c->flags_d + 6, 0, 2 * sizeof(int), c->stream));
-  {
-    KProf kp(c, KC_NEIGH);
-    k_cell_pos<<<cdiv(nall, 256), 256, 0, c->stream>>>(c->cell_list.p, nall, c->cell_pos.p);
-    LAUNCH_CHECK();
-    k_tile_convert<<<nseg, 128, 0, c->stream>>>(T, c->bin_start.p, c->cell_list.p, c->atom_bin.p, c->cell_pos.p, c->numneigh.p, c->neigh.p,
-                                                c->maxneigh, n, c->neigh16.p, c->flags_d);
-    LAUNCH_CHECK();
-  }
-  CU(cudaMemcpyAsync(c->flags_h + 6, c->flags_d + 6, 2 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaStreamSynchronize(c->stream));
-  c->tiled_nseg = nseg;
+  c->tiled_nseg = T.nsegx * c->bg.nbin[1] * c->bg.nbin[2];
   c->tiled_max_staged = c->flags_h[6];
   const size_t nt2 = (size_t) (c->lj.ntypes + 1) * (c->lj.ntypes + 1);
   const size_t extra = c->pair_style == 2 ? (size_t) 7 * (c->eam.nr + 1) * sizeof(double) : (c->lj.ntypes == 1 ? 0 : 6 * nt2 * sizeof(double));
   const size_t smem = (size_t) c->tiled_max_staged * sizeof(double4) + extra;
-  // usable only when every neighbor was found in its segment's neighbourhood and the staging area fits
+  // usable only when every slot fits 16 bits and the staging area fits shared memory; else the default kernels run
   c->tiled_valid = !c->flags_h[7] && c->tiled_max_staged > 0 && c->tiled_max_staged < 0xFFFF && smem <= 200 * 1024;
   return B200MD_OK;
 }
