@@ -855,6 +855,8 @@ extern "C" int b200md_set_timestep(b200md_ctx *c, int64_t ntimestep)
 //   main : k_hs_in(c) = unpack + FixNVE::initial_integrate + pack of the new x; then decide / halo|rebuild / force;
 //          then k_hs_out(c) = FixNVE::final_integrate + pack of v, f
 //   s_out: D2H of the new x of chunk c (runs while later chunks still upload: PCIe is full duplex), later v, f
+// On steps without an energy/virial tally the force kernel is launched per chunk as well, k_hs_out(c) right behind
+// it, so v, f of chunk c go down while the forces of chunk c+1 are computed.
 // A reneighboring step permutes the owned atoms (spatial sort), which invalidates the x that already went down in
 // the old order: those steps send x again after the rebuild.
 #define HS_CHUNKS 8
@@ -971,7 +973,8 @@ extern "C" int b200md_step_host(b200md_ctx *c, double dt, int eflag, int vflag, 
   TRY(stage_bytes(c, (size_t) capacity * 120));
   const size_t cap3 = (size_t) 3 * capacity;
   double *sx = c->stage.p, *sv = sx + cap3, *xo = sv + cap3, *vo = xo + cap3, *fo = vo + cap3;
-  const int nch = n >= 65536 ? HS_CHUNKS : 1;
+  const char *minc = getenv("B200MD_HS_MIN_CHUNK");  // test knob: chunk smaller systems too
+  const int nch = n >= (minc ? atoi(minc) : 65536) ? HS_CHUNKS : 1;
   const int per = cdiv(cdiv(n, nch), 256) * 256;
   cudaEvent_t *e_in = c->hs_ev, *e_x = c->hs_ev + HS_CHUNKS, *e_o = c->hs_ev + 2 * HS_CHUNKS;
   cudaEvent_t e_start = c->hs_ev[3 * HS_CHUNKS], e_mid = c->hs_ev[3 * HS_CHUNKS + 1];
@@ -1015,13 +1018,22 @@ extern "C" int b200md_step_host(b200md_ctx *c, double dt, int eflag, int vflag, 
     CU(cudaStreamWaitEvent(c->s_out, e_mid, 0));
     CU(cudaMemcpyAsync(x, xo, (size_t) n * 24, cudaMemcpyDeviceToHost, c->s_out));
   }
-  TRY(force_compute(c, eflag, vflag));
-  const int per2 = cdiv(cdiv(n, nch), 256) * 256;  // n may have changed at the rebuild
+  // without a tally the force kernel runs range by range too, so that the download of one range's v, f is under the
+  // force kernel of the next (EAM: passes A+B and the fp halo need all atoms; pass C is ranged)
+  const bool ranged = !eflag && !vflag && nch > 1 && c->list_valid &&
+                      (c->pair_style == 1 ? pair_lj_range_usable(c) : c->pair_style == 2 && pair_eam_range_usable(c));
+  if (!ranged) TRY(force_compute(c, eflag, vflag));
+  else if (c->pair_style == 2) TRY(pair_eam_before_ranges(c));
+  const int per2 = cdiv(cdiv(n, nch), 512) * 512;  // n may have changed at the rebuild; a multiple of the force kernels' blocks
   {
-    Sect s(c, SECT_MODIFY);
     for (int ch = 0; ch < nch; ch++) {
       const int first = ch * per2, m = min(per2, n - first);
       if (m <= 0) break;
+      if (ranged) {
+        Sect s(c, SECT_PAIR);
+        TRY(c->pair_style == 1 ? pair_lj_compute_range(c, first, m) : pair_eam_force_range(c, first, m));
+      }
+      Sect s(c, SECT_MODIFY);
       k_hs_out<<<cdiv(m, 256), 256, 0, c->stream>>>(c->pos.p, c->v[0].p, c->v[1].p, c->v[2].p, c->f[0].p, c->f[1].p, c->f[2].p,
                                                      c->mass_d.p, vo, fo, first, m, dtf);
       LAUNCH_CHECK();

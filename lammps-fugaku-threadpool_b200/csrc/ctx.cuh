@@ -338,6 +338,11 @@ int pair_lj_compute(b200md_ctx *c, int eflag, int vflag);
 int pair_lj_compute_part(b200md_ctx *c, int part);            // overlap mode: part 0 = ghost-free tiles, 1 = the rest
 int pair_eam_rho_part(b200md_ctx *c, int part);
 int pair_eam_force_part(b200md_ctx *c, int part);
+bool pair_lj_range_usable(const b200md_ctx *c);                 // host-buffer pipeline: forces of an atom range
+int pair_lj_compute_range(b200md_ctx *c, int first, int count);
+bool pair_eam_range_usable(const b200md_ctx *c);
+int pair_eam_before_ranges(b200md_ctx *c);                      // passes A+B and the fp halo
+int pair_eam_force_range(b200md_ctx *c, int first, int count);
 bool pair_eam_can_split(const b200md_ctx *c);
 int pair_eam_compute(b200md_ctx *c, int eflag, int vflag);
 int pair_eam_rho(b200md_ctx *c, int ev);

@@ -245,7 +245,7 @@ k_eam_rho_fp_1t(const double4 *__restrict__ pos, const int *__restrict__ numneig
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   double acc[1] = {0.0};
   bool active = i < nlocal;
-  if (SPLIT && active) active = (tile_ghost[i >> 5] != 0) == (part != 0);  // overlap mode, see k_lj_lanes
+  if (SPLIT == 1 && active) active = (tile_ghost[i >> 5] != 0) == (part != 0);  // overlap mode, see k_lj_lanes
   if (active) {
     const double4 pi = pos[i];
     const int n = numneigh[i];
@@ -306,10 +306,10 @@ k_eam_force_1t(const double4 *__restrict__ posfp, const int *__restrict__ numnei
   const int n1 = P.nr + 1;
   for (int k = threadIdx.x; k < 7 * n1; k += blockDim.x) s_t[k] = tab1[4 * n1 + k];
   __syncthreads();
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = (SPLIT == 2 ? part : 0) + blockIdx.x * blockDim.x + threadIdx.x;  // 2: range mode, see k_lj_lanes
   double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
   bool active = i < nlocal;
-  if (SPLIT && active) active = (tile_ghost[i >> 5] != 0) == (part != 0);
+  if (SPLIT == 1 && active) active = (tile_ghost[i >> 5] != 0) == (part != 0);
   if (active) {
     const double4 pi = posfp[i];
     const int n = numneigh[i];
@@ -421,6 +421,7 @@ static int eam_attrs_1t(b200md_ctx *c)
     CU(cudaFuncSetAttribute(k_eam_rho_fp_1t<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CU(cudaFuncSetAttribute(k_eam_rho_fp_1t<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CU(cudaFuncSetAttribute(k_eam_force_1t<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CU(cudaFuncSetAttribute(k_eam_force_1t<0, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     attr_done = true;
   }
   return B200MD_OK;
@@ -561,6 +562,30 @@ int pair_eam_force_part(b200md_ctx *c, int part)
   KProf kp(c, KC_PAIR);
   k_eam_force_1t<0, 1><<<blocks, threads, smemC, c->stream>>>(c->posfp.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->f[0].p,
                                                                c->f[1].p, c->f[2].p, c->partials.p, c->tile_ghost.p, part);
+  LAUNCH_CHECK();
+  return B200MD_OK;
+}
+
+// ---- host-buffer pipeline (capi.cu): passes A+B and the fp halo for all atoms, then pass C range by range ----
+bool pair_eam_range_usable(const b200md_ctx *c) { return eam_use_1t(c) && !c->tiled_valid; }
+
+int pair_eam_before_ranges(b200md_ctx *c)
+{
+  TRY(pair_eam_rho(c, 0));
+  return halo_forward_vec4(c, c->posfp.p);
+}
+
+int pair_eam_force_range(b200md_ctx *c, int first, int count)
+{
+  const EAMTables &T = c->eam;
+  const EAMParams P = eam_params(c);
+  const int threads = EAM1T_THREADS, blocks = cdiv(count, threads);
+  if (first % threads) return b200md_fail(c, B200MD_ERR_ARG, "pair range must start at a multiple of %d", threads);
+  const size_t n1 = (size_t) T.nr + 1, smemC = 7 * n1 * 8;
+  TRY(eam_attrs_1t(c));
+  KProf kp(c, KC_PAIR);
+  k_eam_force_1t<0, 2><<<blocks, threads, smemC, c->stream>>>(c->posfp.p, c->numneigh.p, c->neigh.p, c->maxneigh, first + count, P, T.tab1,
+                                                               c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, first);
   LAUNCH_CHECK();
   return B200MD_OK;
 }

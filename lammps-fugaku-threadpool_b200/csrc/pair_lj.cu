@@ -151,10 +151,11 @@ k_lj_lanes(const double4 *__restrict__ pos, const int *__restrict__ numneigh, co
     for (int k = threadIdx.x; k < 6 * nt2; k += blockDim.x) s_tab[k] = tables[k];
     __syncthreads();
   }
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  // SPLIT == 2 (host-buffer pipeline): the atom range [part, nlocal), part a multiple of the block size
+  const int i = (SPLIT == 2 ? part : 0) + blockIdx.x * blockDim.x + threadIdx.x;
   double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
   bool active = i < nlocal;
-  if (SPLIT && active) active = (tile_ghost[i >> 5] != 0) == (part != 0);
+  if (SPLIT == 1 && active) active = (tile_ghost[i >> 5] != 0) == (part != 0);
   if (active) {
     const int q = i / CL, a = i % CL;
     const double4 pi = pos[i];
@@ -316,6 +317,26 @@ int pair_lj_compute_part(b200md_ctx *c, int part)
 #define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, c->tile_ghost.p, part
   if (onetype) k_lj_lanes<1, 0, 1, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
   else k_lj_lanes<1, 0, 0, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+#undef LJ_ARGS
+  LAUNCH_CHECK();
+  return B200MD_OK;
+}
+
+// host-buffer pipeline (capi.cu): forces of the owned atoms [first, first + count) only, no energy/virial tally, so
+// the download of one range's results runs under the force kernel of the next
+bool pair_lj_range_usable(const b200md_ctx *c) { return c->cl == 1 && !c->tiled_valid && getenv("B200MD_LJ_PLAIN") == nullptr; }
+
+int pair_lj_compute_range(b200md_ctx *c, int first, int count)
+{
+  const int threads = 128, blocks = cdiv(count, threads);
+  if (first % threads) return b200md_fail(c, B200MD_ERR_ARG, "pair range must start at a multiple of %d", threads);
+  LJOne one = {c->lj.h_onetype[0], c->lj.h_onetype[1], c->lj.h_onetype[2], c->lj.h_onetype[3], c->lj.h_onetype[4], c->lj.h_onetype[5]};
+  const int onetype = (c->lj.ntypes == 1);
+  size_t smem = onetype ? 0 : (size_t) 6 * (c->lj.ntypes + 1) * (c->lj.ntypes + 1) * sizeof(double);
+  KProf kp(c, KC_PAIR);
+#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, first + count, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, first
+  if (onetype) k_lj_lanes<1, 0, 1, 2><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+  else k_lj_lanes<1, 0, 0, 2><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
 #undef LJ_ARGS
   LAUNCH_CHECK();
   return B200MD_OK;

@@ -90,6 +90,11 @@ def test_emu_host_buffer_step(emu, name, steps, pipeline, monkeypatch):
     gp.test_host_buffer_step_equals_device_loop(emu, name, steps, pipeline, monkeypatch)
 
 
+@pytest.mark.parametrize("kind,steps", [("lj", 45), ("eam", 25)])
+def test_emu_host_buffer_pipeline_chunked(emu, oracle, kind, steps, monkeypatch):
+    gp.test_host_buffer_pipeline_chunked(emu, oracle, kind, steps, monkeypatch)
+
+
 @pytest.mark.parametrize("name,steps", [("lj_500", 45), ("eam_500", 30)])
 def test_emu_overlapped_halo(emu, name, steps, monkeypatch):
     """B200MD_OVERLAP=1: interior / boundary tile split of the force kernels (tile_ghost flags from the build)"""

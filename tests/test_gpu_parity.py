@@ -230,6 +230,40 @@ def test_host_buffer_step_equals_device_loop(pkg, name, steps, pipeline, monkeyp
     b.close()
 
 
+@pytest.mark.skipif(not os.environ.get("B200MD_TEST_PIPELINE"),
+                    reason="three-stream pipeline: opt-in (B200MD_TEST_PIPELINE=1) until it has run on hardware")
+@pytest.mark.parametrize("kind,steps", [("lj", 45), ("eam", 25)])
+def test_host_buffer_pipeline_chunked(pkg, oracle, kind, steps, monkeypatch):
+    """the pipeline with its chunking on (8 ranges of 512 atoms of a 4000-atom bench system): uploads, ranged force
+    kernels (pair_lj_compute_range / pair_eam_force_range) and downloads per range, through rebuilds that re-order
+    the atoms, == b200md_run bit for bit; the last step takes the tally path (whole-system force kernel)"""
+    import ctypes as C
+
+    monkeypatch.setenv("B200MD_HOST_PIPELINE", "1")
+    monkeypatch.setenv("B200MD_HS_MIN_CHUNK", "1000")
+    a, _ = _bench_system(pkg, oracle, kind, 10)
+    b, _ = _bench_system(pkg, oracle, kind, 10)
+    a.run(steps)
+    b.setup()
+    n = b.nlocal
+    hx, hv, hf = np.zeros((n, 3)), np.zeros((n, 3)), np.zeros((n, 3))
+    tag = np.zeros(n, dtype=np.int32)
+    vp = lambda arr: arr.ctypes.data_as(C.c_void_p)
+    b.ctx.call("b200md_download_atoms", vp(hx), vp(hv), None, None, None, None)
+    e, vir, nout = C.c_double(0), np.zeros(6), C.c_int(0)
+    for step in range(steps):
+        ev = 1 if step == steps - 1 else 0
+        b.ctx.call("b200md_step_host", b.dt, ev, ev, n, vp(hx), vp(hv), vp(hf), vp(tag), C.byref(nout), C.byref(e), vp(vir))
+    assert b.neigh_stats()["builds"] == a.neigh_stats()["builds"] >= 2
+    ga = a.gather()
+    o = np.argsort(tag)
+    assert np.array_equal(tag[o], ga["tag"])
+    assert np.array_equal(hx[o], ga["x"]) and np.array_equal(hv[o], ga["v"]) and np.array_equal(hf[o], ga["f"])
+    assert e.value == a.thermo_log[-1]["pe"]
+    a.close()
+    b.close()
+
+
 @pytest.mark.skipif(not os.environ.get("B200MD_TEST_OVERLAP"),
                     reason="halo/compute overlap (B200MD_OVERLAP=1) was written after round 1's GPU budget was spent: opt-in "
                            "(B200MD_TEST_OVERLAP=1) until it has run on hardware")
