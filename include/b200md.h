@@ -285,6 +285,9 @@ int b200md_kernel_times(b200md_ctx *ctx, double *ms, int64_t *count, int reset);
 void *b200md_stream(b200md_ctx *ctx);
 /* 1 when the opt-in shared-memory tiled lj/cut kernel (B200MD_LJ_TILED=1) serves the current neighbor list */
 int b200md_tiled_active(const b200md_ctx *ctx);
+/* bins of an x-row one warp of the last neighbor build handled (1 for dense bins such as in.lj / in.eam; about
+ * 26 / <atoms per bin> for sparse ones such as in.chain; B200MD_BUILD_GB overrides) */
+int b200md_build_bins_per_warp(const b200md_ctx *ctx);
 
 #ifdef __cplusplus
 }

@@ -1203,4 +1203,5 @@ extern "C" int b200md_profile(b200md_ctx *c, int level)
 }
 
 extern "C" int b200md_tiled_active(const b200md_ctx *c) { return c && c->tiled_valid ? 1 : 0; }
+extern "C" int b200md_build_bins_per_warp(const b200md_ctx *c) { return c ? c->build_gb : 0; }
 extern "C" void *b200md_stream(b200md_ctx *c) { return c ? (void *) c->stream : nullptr; }

@@ -198,6 +198,7 @@ struct b200md_ctx {
   // atoms of its 3 x 3 x (TG+2) bin neighbourhood are staged in shared memory once per step and the list entries are
   // 16-bit slots of that staging area
   DevBuf<unsigned short> neigh16;   // same blocked-transposed layout as neigh
+  int build_gb = 1;          // bins per warp of the last list build (k_build_bins)
   bool tiled = false, tiled_valid = false, tiled_emitted = false;   // emitted: the last build wrote neigh16
   int tiled_g = 6, tiled_g_user = 0, tiled_nseg = 0, tiled_max_staged = 0;   // tiled_g_user: B200MD_TILED_G, 0 = choose by bin population
   DevBuf<double> peratom;   // [7][peratom_stride]: eatom, vatom xx yy zz xy xz yz of the owned atoms (b200md_pair_peratom)

@@ -448,7 +448,7 @@ __global__ void __launch_bounds__(BUILD_WARPS * 32)
 k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int nlocal, BinGeom g,
              const int *__restrict__ bin_start, const double *__restrict__ cutneighsq, int ntypes, float tol, int maxneigh,
              int *__restrict__ numneigh, int *__restrict__ neigh, int *__restrict__ flags, int *__restrict__ tile_ghost,
-             BondBuild bb, TileEmit te)
+             BondBuild bb, TileEmit te, int gb)
 {
   __shared__ double s_cut[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
   __shared__ float s_cutf[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
@@ -458,16 +458,20 @@ k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, in
   extern __shared__ int s_stage[];                                   // [BUILD_WARPS][maxneigh][32] when STAGE
   const int lane = threadIdx.x & 31;
   int *s_mine = s_stage + (size_t) (threadIdx.x >> 5) * maxneigh * 32 + lane;
-  const int wb = blockIdx.x * BUILD_WARPS + (threadIdx.x >> 5);      // owned-bin number, x fastest
-  const int nown = g.nbin[0] * g.nbin[1] * g.nbin[2];
-  if (wb >= nown) return;
-  const int obx = wb % g.nbin[0], oby = (wb / g.nbin[0]) % g.nbin[1], obz = wb / (g.nbin[0] * g.nbin[1]);
+  // a warp owns gb consecutive bins of an x-row (gb = 1 unless the bins are sparse, e.g. 3 atoms per bin in
+  // bench/in.chain: the bins' records are contiguous in cell_list, so are the gb + 2 bins of every candidate row, and
+  // the distance test alone decides membership -- same lists, same entry order, more lanes at work)
+  const int wb = blockIdx.x * BUILD_WARPS + (threadIdx.x >> 5);      // owned-segment number, x fastest
+  const int nsegx = (g.nbin[0] + gb - 1) / gb;
+  if (wb >= nsegx * g.nbin[1] * g.nbin[2]) return;
+  const int obx = (wb % nsegx) * gb, oby = (wb / nsegx) % g.nbin[1], obz = wb / (nsegx * g.nbin[1]);
+  const int gx = min(gb, g.nbin[0] - obx);
   const int bx = obx + BIN_MARGIN, by = oby + BIN_MARGIN, bz = obz + BIN_MARGIN;
   const int b = (bz * g.mbin[1] + by) * g.mbin[0] + bx;
-  const int s0 = bin_start[b], e0 = bin_start[b + 1];
+  const int s0 = bin_start[b], e0 = bin_start[b + gx];
   const float cut1 = s_cutf[nt1 + 1];
   int nmax = 0;
-  // owned atoms come first in a bin's segment (cell_list is index-ordered within a bin, ghosts have index >= nlocal)
+  // owned atoms come first in a bin's records (cell_list is index-ordered within a bin, ghosts have index >= nlocal)
   for (int gbase = s0; gbase < e0; gbase += 32) {
     const int kk = gbase + lane;
     BinRec me;
@@ -476,7 +480,10 @@ k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, in
     if (kk < e0) me = ld_rec(rec + kk);
     const int i = me.jt & BR_JMASK;
     const bool owned = (kk < e0) && i < nlocal;
-    if (!__any_sync(0xffffffffu, owned)) break;
+    if (!__any_sync(0xffffffffu, owned)) {
+      if (gb == 1) break;
+      continue;
+    }
     const int trow = ONETYPE ? 0 : (((unsigned) me.jt >> 28) + 1) * nt1;
     const size_t base = (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
     int n = 0;
@@ -496,7 +503,7 @@ k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, in
     for (int dz = -1; dz <= 1; dz++)
       for (int dy = -1; dy <= 1; dy++) {
         const int cell = ((bz + dz) * g.mbin[1] + (by + dy)) * g.mbin[0] + bx - 1;
-        const int ks = bin_start[cell], ke = bin_start[cell + 3];
+        const int ks = bin_start[cell], ke = bin_start[cell + gx + 2];
         int tbase = 0;
         if (TILED16) {
           const int sx = obx / te.tg, gx = min(te.tg, g.nbin[0] - sx * te.tg);
@@ -773,8 +780,17 @@ int neigh_build_lists(b200md_ctx *c)
         te.neigh16 = c->neigh16.p;
         te.tg = c->tiled_g;
       }
-#define BB_ARGS c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d, tile_ghost, bb, te
-      const int bgrid = cdiv(nown, BUILD_WARPS), bthr = BUILD_WARPS * 32;
+      // bins per warp: about 26 owned atoms, leaving room for density fluctuations below the 32 lanes (a second
+      // batch of a few lanes costs a whole pass over the candidates); B200MD_BUILD_GB overrides
+      int gb = 1;
+      if (!tiled16 && !stage) {
+        const char *e = getenv("B200MD_BUILD_GB");
+        gb = e ? atoi(e) : (int) (26.0 * nown / (n > 0 ? n : 1));
+        gb = gb < 1 ? 1 : gb > 16 ? 16 : gb;
+      }
+      c->build_gb = gb;
+#define BB_ARGS c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d, tile_ghost, bb, te, gb
+      const int bgrid = cdiv(cdiv(g.nbin[0], gb) * g.nbin[1] * g.nbin[2], BUILD_WARPS), bthr = BUILD_WARPS * 32;
       c->tiled_emitted = tiled16;
       if (tiled16) {
         if (bonded) {

@@ -107,8 +107,29 @@ def test_emu_neighbor_list_bit_exact(emu, name, monkeypatch):
     monkeypatch.setenv("B200MD_BUILD_STAGE", "1")   # shared-memory row staging of the list stores (opt-in)
     gp.test_neighbor_list_bit_exact(emu, name)
     monkeypatch.delenv("B200MD_BUILD_STAGE")
+    for gb in ("2", "5"):                            # several bins of an x-row per warp (sparse-bin form)
+        monkeypatch.setenv("B200MD_BUILD_GB", gb)
+        gp.test_neighbor_list_bit_exact(emu, name)
+    monkeypatch.delenv("B200MD_BUILD_GB")
     monkeypatch.setenv("B200MD_BUILD_FP64", "1")    # the all-FP64 build kernel
     gp.test_neighbor_list_bit_exact(emu, name)
+
+
+@pytest.mark.parametrize("kind,steps", [("lj", 45), ("eam", 25)])
+def test_emu_bins_per_warp_same_list_order(emu, oracle, kind, steps, monkeypatch):
+    """k_build_bins with 1, 3 and 7 bins per warp (3 and 7 do not divide the bin count; 7 needs several 32-lane
+    batches per segment) writes the same lists in the same entry order: trajectories are bit-identical"""
+    out = []
+    for gb in ("1", "3", "7"):
+        monkeypatch.setenv("B200MD_BUILD_GB", gb)
+        md, _ = gp._bench_system(emu, oracle, kind, 8)
+        md.run(steps)
+        assert emu.lib.load().b200md_build_bins_per_warp(md.ctx.h) == int(gb)
+        out.append((md.gather(), md.thermo_log[-1]["pe"], md.neigh_stats()))
+        md.close()
+    for g, pe, st in out[1:]:
+        assert st == out[0][2] and st["builds"] >= 2 and pe == out[0][1]
+        assert np.array_equal(g["x"], out[0][0]["x"]) and np.array_equal(g["f"], out[0][0]["f"])
 
 
 def test_emu_piecewise_api_and_error_paths(emu):

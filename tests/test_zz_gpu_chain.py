@@ -78,6 +78,8 @@ def test_chain_setup_forces_vs_reference(pkg):
     assert np.abs(a["f"][sel] - g["a_f"]).max() <= F_RTOL * fmax
     numneigh, _ = md.neighbor_list()
     assert int(numneigh.sum()) == 2 * int(g["a_npairs"][0])
+    L = pkg.lib.load()   # 3 beads per bin: 8 bins of an x-row per warp (one when the build also emits tiled slot lists)
+    assert L.b200md_build_bins_per_warp(md.ctx.h) == (1 if L.b200md_tiled_active(md.ctx.h) else 8)
     md.close()
 
 

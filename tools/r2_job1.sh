@@ -14,3 +14,6 @@ for g in 0 4 8 12; do   # 0 = automatic (about 112 atoms per block)
   B200MD_LJ_TILED=1 B200MD_TILED_G=$g timeout 300 python bench.py --steps 100 --warmup 20 --no-cpu --no-e2e > gpurun_out/r2j1_tiled_g$g.log 2>&1
   echo "tiled G=$g rc=$?"; tail -1 gpurun_out/r2j1_tiled_g$g.log | python -c "import sys,json; l=json.loads(sys.stdin.read()); print(l['value'], l['ms_per_step'], l.get('eam',{}).get('value'))"
 done
+# the e2e leg through the three-stream pipeline (ranged force kernels), against r2j1_bench.log's serial e2e
+B200MD_HOST_PIPELINE=1 timeout 300 python bench.py --steps 20 --warmup 5 --no-cpu --no-eam > gpurun_out/r2j1_pipeline.log 2>&1
+echo "pipeline rc=$?"; tail -1 gpurun_out/r2j1_pipeline.log | python -c "import sys,json; l=json.loads(sys.stdin.read()); print(l['value'], l['e2e'])"
