@@ -536,13 +536,14 @@ def test_emu_peratom_needs_a_list(emu):
 
 def test_emu_results_do_not_depend_on_block_or_thread_order():
     """CUDA promises no execution order between blocks, nor between the threads of a block outside its barriers: a
-    subset of the cases above (reference goldens, bit-exact lists, the bonded build, host-buffer steps) once more with
+    subset of the cases (reference goldens, bit-exact lists, the bonded build, host-buffer steps, the tiled kernels) once more with
     the emulator running blocks and threads last-to-first (CUDAEMU_ORDER=reverse, read once per process)"""
     import subprocess
 
     env = dict(os.environ, CUDAEMU_ORDER="reverse")
     r = subprocess.run([sys.executable, "-m", "pytest", str(Path(__file__)), "-x", "-q", "-p", "no:cacheprovider", "-k",
-                        "forces_and_trajectory or neighbor_list_bit_exact or chain_setup or emu_host_buffer_step or emu_peratom_sums"],
+                        "forces_and_trajectory or neighbor_list_bit_exact or chain_setup or emu_host_buffer_step or emu_peratom_sums "
+                        "or tiled or bins_per_warp or pipeline_chunked"],
                        cwd=ROOT, env=env, capture_output=True, text=True)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert " passed" in r.stdout and "failed" not in r.stdout
