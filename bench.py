@@ -304,7 +304,8 @@ def run_e2e(torch, dist, md, out, args, device, nranks):
     k = max(3, min(args.steps, 20))
     ems, bi, bo = time_host_buffers(torch, dist, md, k, 3, device, nranks)
     out["e2e"] = dict(value=out["natoms"] * k / (ems * 1e-3) / 1e6, unit="Matom-steps/s", h2d_bytes_per_step=bi,
-                      d2h_bytes_per_step=bo, steps=k, api="b200md_step_host (pinned host x,v in; x,v,f out every step)")
+                      d2h_bytes_per_step=bo, steps=k, api="b200md_step_host (pinned host x,v in; x,v,f out every step)",
+                      form="three-stream pipeline" if os.environ.get("B200MD_HOST_PIPELINE") else "serial")
 
 
 class Watchdog:
