@@ -34,7 +34,10 @@ def pytest_collection_modifyitems(config, items):
         return
     for item in items:
         if item.get_closest_marker("gpu") and not item.get_closest_marker("timeout"):
-            item.add_marker(pytest.mark.timeout(900, method="thread"))
+            # a FIRST_RUN test has never met the hardware: a hang there should cost 5 minutes, not 15
+            xf = item.get_closest_marker("xfail")
+            first_run = xf is not None and str(xf.kwargs.get("reason", "")).startswith("first hardware run")
+            item.add_marker(pytest.mark.timeout(300 if first_run else 900, method="thread"))
 
 
 @pytest.fixture(scope="session")
