@@ -749,11 +749,11 @@ int neigh_build_lists(b200md_ctx *c)
       const size_t stage_bytes = (size_t) BUILD_WARPS * c->maxneigh * 32 * sizeof(int);
       // opt-in: written in round 1 after the GPU budget was spent, not yet run on hardware
       const bool stage = stage_bytes <= 96 * 1024 && getenv("B200MD_BUILD_STAGE") != nullptr;
-      static bool attr_done = false;
-      if (!attr_done) {
+      static bool attr_done[64] = {};  // per device: a process may hold contexts on several GPUs
+      if (!attr_done[c->device & 63]) {
         CU(cudaFuncSetAttribute(k_build_bins<1, 1, 0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
         CU(cudaFuncSetAttribute(k_build_bins<0, 1, 0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-        attr_done = true;
+        attr_done[c->device & 63] = true;
       }
       int *tile_ghost = nullptr;
       if (c->overlap) {  // B200MD_OVERLAP=1: tile flags for the interior / boundary split of the force kernels

@@ -413,8 +413,8 @@ static EAMParams eam_params(const b200md_ctx *c)
 
 static int eam_attrs_1t(b200md_ctx *c)
 {
-  static bool attr_done = false;
-  if (!attr_done) {
+  static bool attr_done[64] = {};  // per device: a process may hold contexts on several GPUs
+  if (!attr_done[c->device & 63]) {
     CU(cudaFuncSetAttribute(k_eam_force_1t<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CU(cudaFuncSetAttribute(k_eam_force_1t<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CU(cudaFuncSetAttribute(k_eam_rho_fp_1t<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
@@ -422,7 +422,7 @@ static int eam_attrs_1t(b200md_ctx *c)
     CU(cudaFuncSetAttribute(k_eam_rho_fp_1t<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CU(cudaFuncSetAttribute(k_eam_force_1t<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CU(cudaFuncSetAttribute(k_eam_force_1t<0, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    attr_done = true;
+    attr_done[c->device & 63] = true;
   }
   return B200MD_OK;
 }
@@ -812,9 +812,10 @@ k_eam_force_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__re
   if (EVFLAG) block_partials_e<7>(acc, partials);
 }
 
-static int eam_tiled_attrs()
+static int eam_tiled_attrs(int device)
 {
-  static bool done = false;
+  static bool done_dev[64] = {};  // per device: a process may hold contexts on several GPUs
+  bool &done = done_dev[device & 63];
   if (done) return 0;
   if (cudaFuncSetAttribute(k_eam_rho_fp_tiled<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess ||
       cudaFuncSetAttribute(k_eam_rho_fp_tiled<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess ||
@@ -834,7 +835,7 @@ static int pair_eam_rho_tiled(b200md_ctx *c, int ev)
   const size_t smem = (size_t) c->tiled_max_staged * sizeof(double4) + (size_t) 4 * (E.nr + 1) * sizeof(double);
   TRY(dev_ensure(c, c->posfp, (size_t) n + c->nghost));
   if (ev) TRY(dev_ensure(c, c->partials, (size_t) nseg * 8));
-  if (eam_tiled_attrs()) return b200md_fail(c, B200MD_ERR_CUDA, "cudaFuncSetAttribute (tiled eam) failed");
+  if (eam_tiled_attrs(c->device)) return b200md_fail(c, B200MD_ERR_CUDA, "cudaFuncSetAttribute (tiled eam) failed");
   {
     KProf kp(c, KC_EAM_RHO);
 #define R_ARGS T, c->bin_start.p, c->cell_list.p, c->pos.p, c->numneigh.p, c->neigh16.p, c->maxneigh, n, c->tiled_max_staged, P, E.tab1, c->rho.p, c->fp.p, c->posfp.p, c->partials.p

@@ -539,13 +539,13 @@ static int pair_lj_compute_tiled(b200md_ctx *c, int ev)
   const size_t smem = (size_t) c->tiled_max_staged * sizeof(double4) + (onetype ? 0 : 6 * nt2 * sizeof(double));
   LJOne one = {c->lj.h_onetype[0], c->lj.h_onetype[1], c->lj.h_onetype[2], c->lj.h_onetype[3], c->lj.h_onetype[4], c->lj.h_onetype[5]};
   if (ev) TRY(dev_ensure(c, c->partials, (size_t) nseg * 8));
-  static bool attr_done = false;
-  if (!attr_done) {
+  static bool attr_done[64] = {};  // per device: a process may hold contexts on several GPUs
+  if (!attr_done[c->device & 63]) {
     CU(cudaFuncSetAttribute(k_lj_tiled<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CU(cudaFuncSetAttribute(k_lj_tiled<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CU(cudaFuncSetAttribute(k_lj_tiled<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CU(cudaFuncSetAttribute(k_lj_tiled<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    attr_done = true;
+    attr_done[c->device & 63] = true;
   }
   {
     KProf kp(c, KC_PAIR);
