@@ -305,7 +305,7 @@ def run_e2e(torch, dist, md, out, args, device, nranks):
     ems, bi, bo = time_host_buffers(torch, dist, md, k, 3, device, nranks)
     out["e2e"] = dict(value=out["natoms"] * k / (ems * 1e-3) / 1e6, unit="Matom-steps/s", h2d_bytes_per_step=bi,
                       d2h_bytes_per_step=bo, steps=k, api="b200md_step_host (pinned host x,v in; x,v,f out every step)",
-                      form="three-stream pipeline" if os.environ.get("B200MD_HOST_PIPELINE") else "serial")
+                      form="three-stream pipeline")
 
 
 class Watchdog:

@@ -132,9 +132,6 @@ int b200md_neigh_build(b200md_ctx *ctx);
  * Call with neighbors == NULL to get numneigh and *total only. */
 int b200md_neigh_export(b200md_ctx *ctx, int *numneigh, int *neighbors, int64_t *total);
 int b200md_neigh_stats(b200md_ctx *ctx, int64_t *nbuilds, int64_t *ndanger, int *maxneigh);
-/* storage form of the device list: owned atoms are grouped in clusters of `cluster_size` consecutive atoms that
- * share one list of `entries` (summed over clusters) neighbor indices, each with a per-atom membership mask */
-int b200md_neigh_cluster_stats(b200md_ctx *ctx, int *cluster_size, int64_t *nclusters, int64_t *entries);
 
 /* ---- Comm : CommBrick::forward_comm (src/comm_brick.cpp:538-591) -------------------------
  * ghost positions from their owners (self copy, peer copy over NVLink/NCCL).  The device list is
@@ -283,11 +280,19 @@ int b200md_kernel_times(b200md_ctx *ctx, double *ms, int64_t *count, int reset);
 /* the cudaStream_t all of this context's work is issued on (for callers that record their own events
  * or order their own kernels against the library's, as KOKKOS styles do with their execution space) */
 void *b200md_stream(b200md_ctx *ctx);
-/* 1 when the opt-in shared-memory tiled lj/cut kernel (B200MD_LJ_TILED=1) serves the current neighbor list */
-int b200md_tiled_active(const b200md_ctx *ctx);
 /* bins of an x-row one warp of the last neighbor build handled (1 for dense bins such as in.lj / in.eam; about
- * 26 / <atoms per bin> for sparse ones such as in.chain; B200MD_BUILD_GB overrides) */
+ * 26 / <atoms per bin> for sparse ones such as in.chain) */
 int b200md_build_bins_per_warp(const b200md_ctx *ctx);
+/* execution knobs of this context -- the analogue of the reference's `package` command options
+ * (src/GPU/fix_gpu.cpp:43-51 `package gpu ... neigh/split/...`, src/input.cpp package()).  Defaults are the variants
+ * that measured fastest on B200; nothing is read from the environment.
+ *   "overlap"        0/1  per-step halo exchange on its own stream under the force kernels of the tiles whose lists
+ *                         hold no ghost (default 1 on several ranks, 0 on one); applies from the next list build
+ *   "host_pipeline"  0/1  b200md_step_host as a three-stream chunk pipeline (default 1) or serial copy-compute-copy
+ *   "hs_min_chunk"   n    smallest system the pipeline splits into ranges (default 65536)
+ *   "build_gb" n, "build_fp64" 0/1   test knobs of the list build (bins per warp; force the all-FP64 fallback kernel)
+ * Unknown key: B200MD_ERR_ARG. */
+int b200md_tune(b200md_ctx *ctx, const char *key, int value);
 
 #ifdef __cplusplus
 }

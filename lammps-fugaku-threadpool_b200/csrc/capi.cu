@@ -51,19 +51,10 @@ extern "C" int b200md_create(b200md_ctx **out, int device, int nranks, int rank,
   c->rank = rank;
   for (int k = 0; k <= B200MD_MAXTYPES; k++) c->mass_h[k] = 0.0;
   strcpy(c->err, "no error");
-  if (const char *e = getenv("B200MD_CLUSTER")) {  // tuning knob: atoms per neighbor-list cluster
-    int v = atoi(e);
-    if (v == 1 || v == 2 || v == 4) c->cl = v;
-  }
-  // opt-in: run the per-step halo on its own stream under the force kernels of the ghost-free tiles (written in
-  // round 1 after the GPU budget was spent: not yet run on hardware)
-  c->overlap = getenv("B200MD_OVERLAP") != nullptr;
-  // opt-in, same status: shared-memory tiled lj/cut kernel (pair_lj.cu); B200MD_TILED_G = bins per block along x
-  c->tiled = getenv("B200MD_LJ_TILED") != nullptr;
-  if (const char *e = getenv("B200MD_TILED_G")) {
-    int v = atoi(e);
-    if (v >= 1 && v <= 4096) c->tiled_g_user = v;
-  }
+  // defaults chosen from hardware measurements; b200md_tune changes them per context
+  c->overlap = nranks > 1;           // halo on its own stream under the ghost-free tiles' force kernels
+  c->host_pipeline = 1;
+  c->debug_timing = getenv("B200MD_DEBUG_TIMING") != nullptr;   // diagnostic only, read once
   *out = c;
   CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CU(cudaMalloc((void **) &c->red_d, 32 * sizeof(double)));
@@ -91,7 +82,7 @@ extern "C" int b200md_destroy(b200md_ctx *c)
   dev_free(c, c->perm); dev_free(c, c->scan_tmp); dev_free(c, c->binrec); dev_free(c, c->atom_sub); dev_free(c, c->numneigh); dev_free(c, c->neigh); dev_free(c, c->tile_ghost);
   dev_free(c, c->send_idx); dev_free(c, c->border_blockcnt); dev_free(c, c->border_total); dev_free(c, c->send_dir);
   dev_free(c, c->sendbuf_i); dev_free(c, c->allcounts); dev_free(c, c->sendbuf4); dev_free(c, c->recvbuf4); dev_free(c, c->sendbuf1);
-  dev_free(c, c->partials); dev_free(c, c->stage); dev_free(c, c->peratom); dev_free(c, c->neigh16);
+  dev_free(c, c->partials); dev_free(c, c->stage); dev_free(c, c->peratom);
   bond_release(c);
   if (c->lj.d) cudaFree(c->lj.d);
   if (c->eam.frho) cudaFree(c->eam.frho);
@@ -454,35 +445,16 @@ extern "C" int b200md_neigh_build(b200md_ctx *c)
   return neigh_rebuild(c);
 }
 
-// per-atom view of the cluster list: atom i = cluster q, slot a; its neighbors are the cluster's entries whose
-// mask (top 4 bits of the entry) has bit a
-__global__ void k_list_count(const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh, int nlocal, int cl,
-                             int *__restrict__ count)
-{
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= nlocal) return;
-  const int q = i / cl, a = i % cl;
-  const int *nb = neigh + (size_t) (q >> 5) * TILE * maxneigh + (q & 31);
-  const int n = numneigh[q];
-  int m = 0;
-  for (int k = 0; k < n; k++) m += ((unsigned) nb[(size_t) k * TILE] >> (CLBITS + a)) & 1u;
-  count[i] = m;
-}
-
-__global__ void k_list_to_csr(const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh, int nlocal, int cl,
+// blocked-transposed device list -> the reference's per-atom rows (firstneigh[i][0..numneigh[i]), src/neigh_list.h:52-61)
+__global__ void k_list_to_csr(const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh, int nlocal,
                               const long long *__restrict__ first, int *__restrict__ out)
 {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nlocal) return;
-  const int q = i / cl, a = i % cl;
-  const int *nb = neigh + (size_t) (q >> 5) * TILE * maxneigh + (q & 31);
+  const int *nb = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
   int *o = out + first[i];
-  const int n = numneigh[q];
-  int m = 0;
-  for (int k = 0; k < n; k++) {
-    const unsigned e = (unsigned) nb[(size_t) k * TILE];
-    if ((e >> (CLBITS + a)) & 1u) o[m++] = (int) (e & CLJMASK);
-  }
+  const int n = numneigh[i];
+  for (int k = 0; k < n; k++) o[k] = nb[(size_t) k * TILE] & CLJMASK;
 }
 
 extern "C" int b200md_neigh_export(b200md_ctx *c, int *numneigh, int *neighbors, int64_t *total)
@@ -491,13 +463,8 @@ extern "C" int b200md_neigh_export(b200md_ctx *c, int *numneigh, int *neighbors,
   if (!c->list_valid) return b200md_fail(c, B200MD_ERR_ARG, "no neighbor list built");
   const int n = c->nlocal;
   std::vector<int> nn((size_t) n);
-  int *cnt_d = nullptr;
-  CU(cudaMalloc((void **) &cnt_d, (size_t) n * 4));
-  k_list_count<<<cdiv(n, 128), 128, 0, c->stream>>>(c->numneigh.p, c->neigh.p, c->maxneigh, n, c->cl, cnt_d);
-  LAUNCH_CHECK();
-  CU(cudaMemcpyAsync(nn.data(), cnt_d, (size_t) n * 4, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemcpyAsync(nn.data(), c->numneigh.p, (size_t) n * 4, cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
-  cudaFree(cnt_d);
   std::vector<long long> first((size_t) n + 1);
   first[0] = 0;
   for (int i = 0; i < n; i++) first[i + 1] = first[i] + nn[i];
@@ -509,29 +476,13 @@ extern "C" int b200md_neigh_export(b200md_ctx *c, int *numneigh, int *neighbors,
     CU(cudaMalloc((void **) &first_d, ((size_t) n + 1) * 8));
     CU(cudaMalloc((void **) &out_d, (size_t) first[n] * 4));
     CU(cudaMemcpyAsync(first_d, first.data(), ((size_t) n + 1) * 8, cudaMemcpyHostToDevice, c->stream));
-    k_list_to_csr<<<cdiv(n, 128), 128, 0, c->stream>>>(c->numneigh.p, c->neigh.p, c->maxneigh, n, c->cl, first_d, out_d);
+    k_list_to_csr<<<cdiv(n, 128), 128, 0, c->stream>>>(c->numneigh.p, c->neigh.p, c->maxneigh, n, first_d, out_d);
     LAUNCH_CHECK();
     CU(cudaMemcpyAsync(neighbors, out_d, (size_t) first[n] * 4, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     cudaFree(first_d);
     cudaFree(out_d);
   }
-  return B200MD_OK;
-}
-
-extern "C" int b200md_neigh_cluster_stats(b200md_ctx *c, int *cluster_size, int64_t *nclusters, int64_t *entries)
-{
-  NEED_CTX();
-  if (!c->list_valid) return b200md_fail(c, B200MD_ERR_ARG, "no neighbor list built");
-  const int nclus = cdiv(c->nlocal, c->cl);
-  std::vector<int> nn((size_t) nclus);
-  CU(cudaMemcpyAsync(nn.data(), c->numneigh.p, (size_t) nclus * 4, cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaStreamSynchronize(c->stream));
-  int64_t t = 0;
-  for (int q = 0; q < nclus; q++) t += nn[q];
-  if (cluster_size) *cluster_size = c->cl;
-  if (nclusters) *nclusters = nclus;
-  if (entries) *entries = t;
   return B200MD_OK;
 }
 
@@ -591,7 +542,7 @@ static int overlap_streams(b200md_ctx *c)
 
 static bool overlap_usable(const b200md_ctx *c)
 {
-  if (!c->overlap || !c->tiles_valid || !c->list_valid || c->cl != 1 || c->host_ghosts) return false;
+  if (!c->overlap || !c->tiles_valid || !c->list_valid || c->host_ghosts) return false;
   if (c->pair_style == 2) return pair_eam_can_split(c);
   return c->pair_style == 1;
 }
@@ -663,7 +614,6 @@ extern "C" int b200md_pair_peratom(b200md_ctx *c)
 {
   NEED_CTX();
   if (!c->list_valid) return b200md_fail(c, B200MD_ERR_ARG, "pair_peratom before the first neighbor build");
-  if (c->cl != 1) return b200md_fail(c, B200MD_ERR_ARG, "per-atom tallies need the per-atom list (cluster size 1)");
   const int n = c->nlocal;
   const size_t stride = ((size_t) n + 31) / 32 * 32;
   TRY(dev_ensure(c, c->peratom, 7 * stride));
@@ -761,6 +711,12 @@ extern "C" int b200md_setup(b200md_ctx *c)
 {
   NEED_CTX();
   if (c->bonds.maxb && !c->bonds.fene_set) return b200md_fail(c, B200MD_ERR_ARG, "All bond coeffs are not set");
+  // the bonded neighbor build implements `special_bonds fene` only: 1-2 partners excluded, 1-3 and 1-4 at full weight
+  // (src/npair.h:125-158 with special_flag 0 1 1); any other weights given to b200md_lj_init would be silently ignored
+  if (c->bonds.maxb && c->pair_style == 1 &&
+      (c->lj.special_lj[1] != 0.0 || c->lj.special_lj[2] != 1.0 || c->lj.special_lj[3] != 1.0))
+    return b200md_fail(c, B200MD_ERR_ARG, "bonded systems need special_bonds fene (special_lj = {1, 0, 1, 1}), got {%g, %g, %g, %g}",
+                       c->lj.special_lj[0], c->lj.special_lj[1], c->lj.special_lj[2], c->lj.special_lj[3]);
   c->langevin.nextsort = c->ntimestep;  // Verlet::setup sorts unconditionally (src/verlet.cpp:121)
   {
     Sect s(c, SECT_NEIGH);
@@ -835,7 +791,10 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
     } else
       pending_final = true;
   }
+  if (c->bonds.maxb)  // "Bad FENE bond" of the run's last steps (k_bond_fene raises flags_d[4]; BondFENE::compute :88 aborts)
+    CU(cudaMemcpyAsync(c->flags_h + 4, c->flags_d + 4, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
+  if (c->bonds.maxb && c->flags_h[4]) return b200md_fail(c, B200MD_ERR_ARG, "Bad FENE bond");
   return B200MD_OK;
 }
 
@@ -965,16 +924,14 @@ extern "C" int b200md_step_host(b200md_ctx *c, double dt, int eflag, int vflag, 
     return b200md_fail(c, B200MD_ERR_ARG, "step_host: bonded / fix langevin systems run through b200md_setup + b200md_run");
   int n = c->nlocal;
   if (capacity < n) return b200md_fail(c, B200MD_ERR_ARG, "step_host: capacity %d < nlocal %d", capacity, n);
-  // B200MD_HOST_PIPELINE=1 selects the three-stream chunk pipeline below (written in round 1 after the GPU budget
-  // was spent: not yet run on hardware, hence opt-in)
-  if (!getenv("B200MD_HOST_PIPELINE")) return step_host_serial(c, dt, eflag, vflag, capacity, x, v, f, tag, nlocal_out, eng_vdwl, virial);
+  // default: the three-stream chunk pipeline below (B200, 16.4 M atoms: 527 against 405 Matom-steps/s serial)
+  if (!c->host_pipeline) return step_host_serial(c, dt, eflag, vflag, capacity, x, v, f, tag, nlocal_out, eng_vdwl, virial);
   const double dtv = dt, dtf = 0.5 * dt * c->ftm2v;
   TRY(hs_streams(c));
   TRY(stage_bytes(c, (size_t) capacity * 120));
   const size_t cap3 = (size_t) 3 * capacity;
   double *sx = c->stage.p, *sv = sx + cap3, *xo = sv + cap3, *vo = xo + cap3, *fo = vo + cap3;
-  const char *minc = getenv("B200MD_HS_MIN_CHUNK");  // test knob: chunk smaller systems too
-  const int nch = n >= (minc ? atoi(minc) : 65536) ? HS_CHUNKS : 1;
+  const int nch = n >= c->hs_min_chunk ? HS_CHUNKS : 1;
   const int per = cdiv(cdiv(n, nch), 256) * 256;
   cudaEvent_t *e_in = c->hs_ev, *e_x = c->hs_ev + HS_CHUNKS, *e_o = c->hs_ev + 2 * HS_CHUNKS;
   cudaEvent_t e_start = c->hs_ev[3 * HS_CHUNKS], e_mid = c->hs_ev[3 * HS_CHUNKS + 1];
@@ -1202,6 +1159,22 @@ extern "C" int b200md_profile(b200md_ctx *c, int level)
   return B200MD_OK;
 }
 
-extern "C" int b200md_tiled_active(const b200md_ctx *c) { return c && c->tiled_valid ? 1 : 0; }
+// execution knobs, per context; defaults are the measured winners.  Unknown key: B200MD_ERR_ARG.
+//   "overlap"       0/1  halo exchange on its own stream under the force kernels of the ghost-free tiles
+//   "host_pipeline" 0/1  b200md_step_host as a three-stream chunk pipeline (0: serial copy - compute - copy)
+//   "hs_min_chunk"  n    smallest system the pipeline splits into ranges (tests lower it)
+//   "build_gb" n, "build_fp64" 0/1   test knobs of the list build: bins per warp; force the all-FP64 fallback kernel
+extern "C" int b200md_tune(b200md_ctx *c, const char *key, int value)
+{
+  NEED_CTX();
+  if (!key) return b200md_fail(c, B200MD_ERR_ARG, "b200md_tune: key == NULL");
+  if (!strcmp(key, "overlap")) c->overlap = value != 0;   // takes effect with the next list build (tile flags)
+  else if (!strcmp(key, "host_pipeline")) c->host_pipeline = value != 0;
+  else if (!strcmp(key, "hs_min_chunk")) c->hs_min_chunk = value > 0 ? value : 65536;
+  else if (!strcmp(key, "build_gb")) c->build_gb_user = value > 0 ? value : 0;     // test knob
+  else if (!strcmp(key, "build_fp64")) c->build_fp64 = value != 0;                 // test knob
+  else return b200md_fail(c, B200MD_ERR_ARG, "b200md_tune: unknown key '%s'", key);
+  return B200MD_OK;
+}
 extern "C" int b200md_build_bins_per_warp(const b200md_ctx *c) { return c ? c->build_gb : 0; }
 extern "C" void *b200md_stream(b200md_ctx *c) { return c ? (void *) c->stream : nullptr; }

@@ -22,11 +22,10 @@
 
 #define NEIGHMASK 0x1FFFFFFF  // src/lmptype.h:61-65 (what b200md_neigh_export hands out)
 #define SBBITS 30
-// device list entry: neighbor index in the low 28 bits, membership mask of the (up to 4) atoms of the cluster
-// in the top 4 bits -- bit a set <=> j is in the reference's list of atom a of the cluster
+// device list entry: neighbor index in the low 28 bits; the top 4 bits are free for per-entry flags (special-bond
+// class of a molecular system, as the reference keeps in the top 2 bits of its own entries, src/lmptype.h:61-65)
 #define CLBITS 28
 #define CLJMASK 0x0FFFFFFF
-#define CLMAX 4
 #define IMGMASK 1023          // src/lmptype.h (LAMMPS_SMALLBIG)
 #define IMGBITS 10
 #define IMG2BITS 20
@@ -168,7 +167,6 @@ struct b200md_ctx {
   DevBuf<double> binrec;      // BinRec[nall] (16 B each): FP32 candidate records in cell_list order (neigh.cu)
 
   // neighbor list
-  int cl = 1;                 // cluster size of the neighbor list (1, 2 or 4 atoms per list), env B200MD_CLUSTER
   int maxneigh = 0;
   DevBuf<int> numneigh, neigh;
   DevBuf<int> tile_ghost;     // [ntiles]: != 0 if any atom of the 32-atom tile has a ghost in its list (overlap mode)
@@ -176,8 +174,8 @@ struct b200md_ctx {
   int maxneigh_seen = 0;
 
   // halo / exchange (comm.cu)
-  // opt-in (B200MD_OVERLAP=1): the per-step halo runs on s_comm while the main stream computes the tiles whose lists
-  // hold no ghost; hstream != nullptr redirects the halo kernels and NCCL calls to that stream
+  // overlap (default on several ranks, b200md_tune "overlap"): the per-step halo runs on s_comm while the main stream
+  // computes the tiles whose lists hold no ghost; hstream != nullptr redirects the halo kernels and NCCL calls there
   int overlap = 0;
   cudaStream_t s_comm = nullptr, hstream = nullptr;
   cudaEvent_t ev_main = nullptr, ev_halo = nullptr;
@@ -194,13 +192,7 @@ struct b200md_ctx {
 
   // reductions / flags
   DevBuf<double> partials;  // [nblocks][8]
-  // opt-in shared-memory tiled lj/cut (B200MD_LJ_TILED=1, pair_lj.cu): a block = TG consecutive bins of one x-row; the
-  // atoms of its 3 x 3 x (TG+2) bin neighbourhood are staged in shared memory once per step and the list entries are
-  // 16-bit slots of that staging area
-  DevBuf<unsigned short> neigh16;   // same blocked-transposed layout as neigh
   int build_gb = 1;          // bins per warp of the last list build (k_build_bins)
-  bool tiled = false, tiled_valid = false, tiled_emitted = false;   // emitted: the last build wrote neigh16
-  int tiled_g = 6, tiled_g_user = 0, tiled_nseg = 0, tiled_max_staged = 0;   // tiled_g_user: B200MD_TILED_G, 0 = choose by bin population
   DevBuf<double> peratom;   // [7][peratom_stride]: eatom, vatom xx yy zz xy xz yz of the owned atoms (b200md_pair_peratom)
   size_t peratom_stride = 0;
   int peratom_n = 0;        // owned atoms the tallies are valid for, 0 = none
@@ -229,6 +221,13 @@ struct b200md_ctx {
   double kc_ms[KC_N] = {0, 0, 0, 0, 0, 0};
   int64_t kc_count[KC_N] = {0, 0, 0, 0, 0, 0};
   double bytes_held = 0;
+
+  // knobs (b200md_tune; defaults chosen from hardware measurements)
+  int host_pipeline = 1;      // b200md_step_host: three-stream chunk pipeline (0 = serial copy-compute-copy)
+  int hs_min_chunk = 65536;   // smallest system the pipeline splits into ranges
+  int build_gb_user = 0;      // test knob: bins of an x-row per warp in the list build (0 = by bin population)
+  int build_fp64 = 0;         // test knob: force the all-FP64 build kernel (otherwise only huge boxes with tiny cutoffs use it)
+  int debug_timing = 0;       // per-phase wall times of every rebuild on stderr (B200MD_DEBUG_TIMING, read at create)
 
   // host-buffer mode staging and its copy streams (b200md_step_host)
   DevBuf<double> stage;
@@ -352,8 +351,6 @@ int nve_initial(b200md_ctx *c, double dtv, double dtf);
 int nve_final(b200md_ctx *c, double dtf);
 int thermo_ke(b200md_ctx *c, double *sum_mv2);
 int reduce_partials(b200md_ctx *c, int nblocks, int ncomp, int dst);  // partials -> red_d[dst..]
-bool pair_tiled_wanted(b200md_ctx *c);      // before a list build: emit 16-bit staged-slot lists? (B200MD_LJ_TILED=1)
-int pair_lj_tiled_prepare(b200md_ctx *c);   // after it: can the tiled kernels serve this list?
 int pair_lj_peratom(b200md_ctx *c, double *out, size_t stride);       // eatom / vatom pass, out = [7][stride]
 int pair_eam_peratom(b200md_ctx *c, double *out, size_t stride);
 
@@ -381,43 +378,6 @@ __device__ __forceinline__ double rcp_pos(double x)
 }
 __device__ __forceinline__ int pos_type(const double4 &p) { return __double2loint(p.w); }
 __device__ __forceinline__ double type_as_w(int t) { return __hiloint2double(0, t); }
-// ---- geometry of the shared-memory tiled kernels (pair_lj.cu, pair_eam.cu; B200MD_LJ_TILED=1) ----
-struct TileGeom {
-  BinGeom g;
-  int tg, nsegx;   // bins per segment along x, segments per x-row
-};
-
-// the 9 cell_list ranges (dz, dy rows) of segment `seg` and the prefix offsets of their staged copies
-__device__ __forceinline__ void tile_rows(const TileGeom &T, const int *__restrict__ bin_start, int seg, int ks[9], int off[10],
-                                          int &own_s, int &own_e, int &by, int &bz)
-{
-  const int sx = seg % T.nsegx, oby = (seg / T.nsegx) % T.g.nbin[1], obz = seg / (T.nsegx * T.g.nbin[1]);
-  const int gx = min(T.tg, T.g.nbin[0] - sx * T.tg);
-  const int bx0 = BIN_MARGIN + sx * T.tg;
-  by = oby + BIN_MARGIN;
-  bz = obz + BIN_MARGIN;
-  off[0] = 0;
-#pragma unroll
-  for (int r = 0; r < 9; r++) {
-    const int dz = r / 3 - 1, dy = r % 3 - 1;
-    const int first = ((bz + dz) * T.g.mbin[1] + (by + dy)) * T.g.mbin[0] + bx0 - 1;
-    ks[r] = bin_start[first];
-    off[r + 1] = off[r] + bin_start[first + gx + 2] - ks[r];
-    if (r == 4) {
-      own_s = bin_start[first + 1];
-      own_e = bin_start[first + 1 + gx];
-    }
-  }
-}
-
-static inline TileGeom tile_geom(const b200md_ctx *c)
-{
-  TileGeom T;
-  T.g = c->bg;
-  T.tg = c->tiled_g;
-  T.nsegx = (c->bg.nbin[0] + c->tiled_g - 1) / c->tiled_g;
-  return T;
-}
 int nve_final_initial(b200md_ctx *c, double dtv, double dtf);
 int bond_compute(b200md_ctx *c, int ev);                   // bond.cu
 int langevin_apply(b200md_ctx *c, int64_t ntimestep);     // bond.cu

@@ -11,8 +11,6 @@
 // owned atoms are physically re-ordered by bin at every rebuild, ghosts are made in ONE stage from the
 // 26 direction masks instead of the reference's 6 staged swaps (same ghost set when every sub-domain is
 // at least one ghost cutoff wide), and the list is a full list in a blocked-transposed layout.
-#include <stdlib.h>
-
 #include <utility>
 
 #include "ctx.cuh"
@@ -295,86 +293,47 @@ int neigh_setup_bins(b200md_ctx *c)
 }
 
 // ------------------------------------------------------------------------------------------------
-// neighbor build: FULL list stored per CLUSTER of CL consecutive (spatially compact) owned atoms.
-// One thread per cluster scans the bins around the cluster's bounding box; a candidate j is stored once for the
-// cluster if it is a neighbor of ANY of its atoms, with a CL-bit mask saying of which.  The mask is decided
-// exactly as the reference decides list membership: rsq = delx*delx + dely*dely + delz*delz (no FMA), keep if
-// rsq <= cutneighsq[itype][jtype] (src/npair_half_bin_atomonly_newton.cpp:80-87), so the per-atom lists the
-// masks define are bit-identical to the reference's as tag-pair sets.  The force kernels gather x_j once per
-// entry and serve up to CL atoms with it (fewer L1 look-ups and list bytes per pair than a per-atom list).
-// Layout: entry k of cluster q at [(q>>5)*32*maxneigh + k*32 + (q&31)] (one coalesced 128-byte row per k per warp).
+// neighbor build, all-FP64 form (fallback: boxes so large relative to the cutoff that the FP32 prefilter's error
+// band would exceed 1 % of cutneighsq, see build_tolerance): one thread per owned atom scans its 27-bin stencil.
+// Membership is decided exactly as the reference decides it: rsq = delx*delx + dely*dely + delz*delz (no FMA), keep if
+// rsq <= cutneighsq[itype][jtype] (src/npair_half_bin_atomonly_newton.cpp:80-87), so the lists are bit-identical to
+// the reference's as tag-pair sets.
+// Layout: entry k of atom i at [(i>>5)*32*maxneigh + k*32 + (i&31)] (one coalesced 128-byte row per k per warp).
 // ------------------------------------------------------------------------------------------------
-template <int CL>
 __global__ void __launch_bounds__(128)
-k_build_cluster(const double4 *__restrict__ pos, int nlocal, BinGeom g, const int *__restrict__ bin_start,
-                const int *__restrict__ cell_list, const double *__restrict__ cutneighsq, int ntypes, int maxneigh,
-                int *__restrict__ numneigh, int *__restrict__ neigh, int *__restrict__ flags)
+k_build_fp64(const double4 *__restrict__ pos, int nlocal, BinGeom g, const int *__restrict__ bin_start,
+             const int *__restrict__ cell_list, const double *__restrict__ cutneighsq, int ntypes, int maxneigh,
+             int *__restrict__ numneigh, int *__restrict__ neigh, int *__restrict__ flags)
 {
   extern __shared__ double s_cut[];
   const int nt1 = ntypes + 1;
   for (int k = threadIdx.x; k < nt1 * nt1; k += blockDim.x) s_cut[k] = cutneighsq[k];
   __syncthreads();
-  const int q = blockIdx.x * blockDim.x + threadIdx.x;
-  const int i0 = q * CL;
-  if (i0 >= nlocal) return;
-  double xi[CL], yi[CL], zi[CL];
-  int trow[CL], bx[CL], by[CL], bz[CL];
-#pragma unroll
-  for (int a = 0; a < CL; a++) {
-    if (i0 + a < nlocal) {
-      const double4 p = pos[i0 + a];
-      xi[a] = p.x; yi[a] = p.y; zi[a] = p.z;
-      trow[a] = pos_type(p) * nt1;
-      bx[a] = min(max((int) floor((p.x - g.lo[0]) * g.inv[0]) + BIN_MARGIN, 1), g.mbin[0] - 2);
-      by[a] = min(max((int) floor((p.y - g.lo[1]) * g.inv[1]) + BIN_MARGIN, 1), g.mbin[1] - 2);
-      bz[a] = min(max((int) floor((p.z - g.lo[2]) * g.inv[2]) + BIN_MARGIN, 1), g.mbin[2] - 2);
-    } else {
-      xi[a] = yi[a] = zi[a] = 1e150;  // padding atom of the last cluster: never within any cutoff
-      trow[a] = nt1;
-      bx[a] = bx[0]; by[a] = by[0]; bz[a] = bz[0];
-    }
-  }
-  const size_t base = (size_t) (q >> 5) * TILE * maxneigh + (q & 31);
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nlocal) return;
+  const double4 p = pos[i];
+  const int trow = pos_type(p) * nt1;
+  const int bx = min(max((int) floor((p.x - g.lo[0]) * g.inv[0]) + BIN_MARGIN, 1), g.mbin[0] - 2);
+  const int by = min(max((int) floor((p.y - g.lo[1]) * g.inv[1]) + BIN_MARGIN, 1), g.mbin[1] - 2);
+  const int bz = min(max((int) floor((p.z - g.lo[2]) * g.inv[2]) + BIN_MARGIN, 1), g.mbin[2] - 2);
+  const size_t base = (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
   int n = 0;
-  // candidates = union of the 27-bin stencils of the cluster's atoms: walk each atom's stencil, skipping every
-  // bin an earlier atom of the cluster already covered (consecutive atoms mostly share their bin)
-#pragma unroll
-  for (int a = 0; a < CL; a++) {
-    bool same = false;
-#pragma unroll
-    for (int b = 0; b < a; b++) same |= (bx[b] == bx[a] && by[b] == by[a] && bz[b] == bz[a]);
-    if (same) continue;
-    for (int dz = -1; dz <= 1; dz++)
-      for (int dy = -1; dy <= 1; dy++) {
-        const int cy = by[a] + dy, cz = bz[a] + dz;
-        const int row = (cz * g.mbin[1] + cy) * g.mbin[0];
-        for (int dx = -1; dx <= 1; dx++) {
-          const int cx = bx[a] + dx;
-          bool covered = false;
-#pragma unroll
-          for (int b = 0; b < a; b++) covered |= (abs(cx - bx[b]) <= 1 && abs(cy - by[b]) <= 1 && abs(cz - bz[b]) <= 1);
-          if (covered) continue;
-          const int s = bin_start[row + cx], e = bin_start[row + cx + 1];
-          for (int k = s; k < e; k++) {
-            const int j = cell_list[k];
-            const double4 pj = ld_pos256(pos + j);
-            const int jt = pos_type(pj);
-            unsigned m = 0;
-#pragma unroll
-            for (int c = 0; c < CL; c++) {
-              const double ddx = __dsub_rn(xi[c], pj.x), ddy = __dsub_rn(yi[c], pj.y), ddz = __dsub_rn(zi[c], pj.z);
-              const double rsq = __dadd_rn(__dadd_rn(__dmul_rn(ddx, ddx), __dmul_rn(ddy, ddy)), __dmul_rn(ddz, ddz));
-              if (rsq <= s_cut[trow[c] + jt] && j != i0 + c) m |= 1u << c;
-            }
-            if (m) {
-              if (n < maxneigh) neigh[base + (size_t) n * TILE] = j | (int) (m << CLBITS);
-              n++;
-            }
-          }
+  for (int dz = -1; dz <= 1; dz++)
+    for (int dy = -1; dy <= 1; dy++) {
+      const int row = ((bz + dz) * g.mbin[1] + by + dy) * g.mbin[0] + bx - 1;
+      const int s = bin_start[row], e = bin_start[row + 3];   // the 3 bins of an x-row are contiguous in cell_list
+      for (int k = s; k < e; k++) {
+        const int j = cell_list[k];
+        const double4 pj = ld_pos256(pos + j);
+        const double ddx = __dsub_rn(p.x, pj.x), ddy = __dsub_rn(p.y, pj.y), ddz = __dsub_rn(p.z, pj.z);
+        const double rsq = __dadd_rn(__dadd_rn(__dmul_rn(ddx, ddx), __dmul_rn(ddy, ddy)), __dmul_rn(ddz, ddz));
+        if (rsq <= s_cut[trow + pos_type(pj)] && j != i) {
+          if (n < maxneigh) neigh[base + (size_t) n * TILE] = j;
+          n++;
         }
       }
-  }
-  numneigh[q] = n;
+    }
+  numneigh[i] = n;
   unsigned am = __activemask();
   int nmax = __reduce_max_sync(am, n);
   if ((threadIdx.x & 31) == (__ffs(am) - 1)) atomicMax(&flags[1], nmax);  // flags[1] = longest list seen
@@ -423,8 +382,6 @@ __device__ __forceinline__ BinRec ld_rec(const BinRec *__restrict__ p)
 }
 
 #define BUILD_WARPS 4
-// STAGE: each warp collects its lanes' lists in shared memory ([k][lane], conflict free) and writes them out row by
-// row, so a store instruction covers one contiguous piece of a 128-byte list row instead of 32 different rows
 // BONDED (in.chain): a candidate within the cutoff whose tag is one of the atom's 1-2 partners is NOT listed
 // (special_bonds lj weight 0, NPair::find_special src/npair.h:125-158 -> -1) but recorded as the device index of that
 // bond partner; of several periodic images the closest wins (Domain::closest_image).
@@ -435,29 +392,19 @@ struct BondBuild {
   int *bond_idx;               // [nlocal][maxb] out
   int maxb;
 };
-// TILED16 (B200MD_LJ_TILED=1, pair_lj.cu): next to every list entry its 16-bit slot in the staging area of the bin
-// segment the atom belongs to -- the candidate loop already walks the segment's rows in staging order, so the slot is
-// the running row offset plus the candidate's position in its row.  flags[6] = largest staging area, flags[7] = a slot
-// did not fit 16 bits.
-struct TileEmit {
-  unsigned short *neigh16;
-  int tg;   // bins per segment along x
-};
-template <int ONETYPE, int STAGE, int BONDED, int TILED16>
+template <int ONETYPE, int BONDED>
 __global__ void __launch_bounds__(BUILD_WARPS * 32)
 k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int nlocal, BinGeom g,
              const int *__restrict__ bin_start, const double *__restrict__ cutneighsq, int ntypes, float tol, int maxneigh,
              int *__restrict__ numneigh, int *__restrict__ neigh, int *__restrict__ flags, int *__restrict__ tile_ghost,
-             BondBuild bb, TileEmit te, int gb)
+             BondBuild bb, int gb)
 {
   __shared__ double s_cut[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
   __shared__ float s_cutf[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
   const int nt1 = ntypes + 1;
   for (int k = threadIdx.x; k < nt1 * nt1; k += blockDim.x) { s_cut[k] = cutneighsq[k]; s_cutf[k] = (float) cutneighsq[k]; }
   __syncthreads();
-  extern __shared__ int s_stage[];                                   // [BUILD_WARPS][maxneigh][32] when STAGE
   const int lane = threadIdx.x & 31;
-  int *s_mine = s_stage + (size_t) (threadIdx.x >> 5) * maxneigh * 32 + lane;
   // a warp owns gb consecutive bins of an x-row (gb = 1 unless the bins are sparse, e.g. 3 atoms per bin in
   // bench/in.chain: the bins' records are contiguous in cell_list, so are the gb + 2 bins of every candidate row, and
   // the distance test alone decides membership -- same lists, same entry order, more lanes at work)
@@ -499,19 +446,10 @@ k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, in
         prsq[m] = 3.0e38f;
       }
     }
-    int toff = 0;   // TILED16: staging offset of the current row of this bin's segment
     for (int dz = -1; dz <= 1; dz++)
       for (int dy = -1; dy <= 1; dy++) {
         const int cell = ((bz + dz) * g.mbin[1] + (by + dy)) * g.mbin[0] + bx - 1;
         const int ks = bin_start[cell], ke = bin_start[cell + gx + 2];
-        int tbase = 0;
-        if (TILED16) {
-          const int sx = obx / te.tg, gx = min(te.tg, g.nbin[0] - sx * te.tg);
-          const int first = cell - (obx - sx * te.tg);           // the row's first staged bin: bx0 - 1
-          const int tks = bin_start[first];
-          tbase = toff - tks;
-          toff += bin_start[first + gx + 2] - tks;
-        }
 #pragma unroll 4
         for (int k = ks; k < ke; k++) {
           const BinRec c = ld_rec(rec + k);
@@ -538,25 +476,11 @@ k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, in
           }
           if (accept && owned && j != i) {
             ghost_seen |= j >= nlocal;
-            if (n < maxneigh) {
-              if (STAGE) s_mine[n * 32] = j | (1 << CLBITS);
-              else neigh[base + (size_t) n * TILE] = j | (1 << CLBITS);
-              if (TILED16) {
-                const int slot = tbase + k;
-                if (slot >= 0xFFFF) flags[7] = 1;
-                te.neigh16[base + (size_t) n * TILE] = (unsigned short) slot;
-              }
-            }
+            if (n < maxneigh) neigh[base + (size_t) n * TILE] = j;
             n++;
           }
         }
       }
-    if (STAGE) {
-      const int nrows = min(__reduce_max_sync(0xffffffffu, owned ? n : 0), maxneigh);
-      for (int k = 0; k < nrows; k++)
-        if (owned && k < n) neigh[base + (size_t) k * TILE] = s_mine[k * 32];
-      __syncwarp();
-    }
     if (owned) numneigh[i] = n;
     if (BONDED && owned) {
 #pragma unroll
@@ -567,7 +491,6 @@ k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, in
           ghost_seen |= pbest[m] >= nlocal;
         }
     }
-    if (TILED16 && lane == 0 && gbase == s0) atomicMax(&flags[6], toff);
     if (tile_ghost && owned && ghost_seen) atomicOr(&tile_ghost[i >> 5], 1);
     nmax = max(nmax, owned ? n : 0);
   }
@@ -627,7 +550,7 @@ struct PhaseTimer {
   b200md_ctx *c;
   bool on;
   std::chrono::steady_clock::time_point t0;
-  PhaseTimer(b200md_ctx *ctx) : c(ctx), on(getenv("B200MD_DEBUG_TIMING") != nullptr), t0(std::chrono::steady_clock::now()) {}
+  PhaseTimer(b200md_ctx *ctx) : c(ctx), on(ctx->debug_timing != 0), t0(std::chrono::steady_clock::now()) {}
   void mark(const char *what)
   {
     if (!on) return;
@@ -665,7 +588,8 @@ int neigh_rebuild(b200md_ctx *c)
   n = c->nlocal;
   // fix langevin replay: the reference's own Atom::sort reorders the atoms its random stream is consumed over
   // (Verlet::setup src/verlet.cpp:121, Verlet::run :291)
-  if (c->langevin.on && c->langevin.sortfreq > 0 && c->ntimestep >= c->langevin.nextsort) TRY(langevin_resort(c));
+  // (counter mode draws by (tag, timestep): no order to replay, and after a migration the order list would be stale)
+  if (c->langevin.on && c->langevin.rng_mode == 0 && c->langevin.sortfreq > 0 && c->ntimestep >= c->langevin.nextsort) TRY(langevin_resort(c));
 
   // spatial sort of owned atoms (Atom::sort) by neighbor bin
   TRY(dev_ensure(c, c->perm, (size_t) n));
@@ -714,24 +638,20 @@ int neigh_build_lists(b200md_ctx *c)
     TRY(dev_ensure(c, c->fp, (size_t) nall));
   }
 
-  const int CLs = c->cl;
-  const int nclus = cdiv(n, CLs);
   if (c->maxneigh == 0) {
     double vol = 1.0;
     for (int k = 0; k < 3; k++) vol *= c->subhi[k] - c->sublo[k];
     double expect = 4.18879020478639 * c->cutneighmax * c->cutneighmax * c->cutneighmax * n / vol;
-    // a cluster's list is the union of its atoms' lists (measured on an LJ melt: x1.4 / x1.9 / x2.6 for 2 / 4 / 8)
-    const double f = CLs == 1 ? 1.0 : CLs == 2 ? 1.5 : 2.0;
-    int m = (int) (expect * f * 1.2) + 24;
+    int m = (int) (expect * 1.2) + 24;
     c->maxneigh = (m + 7) / 8 * 8;
   }
-  const int ntiles = cdiv(nclus, TILE);
+  const int ntiles = cdiv(n, TILE);
   for (int attempt = 0; attempt < 8; attempt++) {
     TRY(dev_ensure(c, c->neigh, (size_t) ntiles * TILE * c->maxneigh));
     size_t smem = (size_t) (c->ntypes + 1) * (c->ntypes + 1) * sizeof(double);
     double cutsq_min = 0.0;
     const double tol = build_tolerance(c, &cutsq_min);
-    if (CLs == 1 && tol < 0.01 * cutsq_min && !getenv("B200MD_BUILD_FP64")) {
+    if (tol < 0.01 * cutsq_min && !c->build_fp64) {
       const BinGeom &g = c->bg;
       TRY(dev_ensure(c, c->binrec, (size_t) nall * 2));  // 16-byte records held as double pairs
       KProf kp(c, KC_NEIGH);
@@ -746,17 +666,8 @@ int neigh_build_lists(b200md_ctx *c)
                                                             c->tag.p, rec_tag);
       LAUNCH_CHECK();
       const int nown = g.nbin[0] * g.nbin[1] * g.nbin[2];
-      const size_t stage_bytes = (size_t) BUILD_WARPS * c->maxneigh * 32 * sizeof(int);
-      // opt-in: written in round 1 after the GPU budget was spent, not yet run on hardware
-      const bool stage = stage_bytes <= 96 * 1024 && getenv("B200MD_BUILD_STAGE") != nullptr;
-      static bool attr_done[64] = {};  // per device: a process may hold contexts on several GPUs
-      if (!attr_done[c->device & 63]) {
-        CU(cudaFuncSetAttribute(k_build_bins<1, 1, 0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-        CU(cudaFuncSetAttribute(k_build_bins<0, 1, 0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-        attr_done[c->device & 63] = true;
-      }
       int *tile_ghost = nullptr;
-      if (c->overlap) {  // B200MD_OVERLAP=1: tile flags for the interior / boundary split of the force kernels
+      if (c->overlap) {  // tile flags for the interior / boundary split of the force kernels
         TRY(dev_ensure(c, c->tile_ghost, (size_t) ntiles));
         CU(cudaMemsetAsync(c->tile_ghost.p, 0, (size_t) ntiles * sizeof(int), c->stream));
         tile_ghost = c->tile_ghost.p;
@@ -772,43 +683,19 @@ int neigh_build_lists(b200md_ctx *c)
         bb.bond_idx = c->bonds.idx.p;
         bb.maxb = c->bonds.maxb;
       }
-      TileEmit te = {nullptr, 1};
-      const bool tiled16 = pair_tiled_wanted(c);
-      if (tiled16) {
-        TRY(dev_ensure(c, c->neigh16, (size_t) ntiles * TILE * c->maxneigh));
-        CU(cudaMemsetAsync(c->flags_d + 6, 0, 2 * sizeof(int), c->stream));
-        te.neigh16 = c->neigh16.p;
-        te.tg = c->tiled_g;
-      }
       // bins per warp: about 26 owned atoms, leaving room for density fluctuations below the 32 lanes (a second
-      // batch of a few lanes costs a whole pass over the candidates); B200MD_BUILD_GB overrides
-      int gb = 1;
-      if (!tiled16 && !stage) {
-        const char *e = getenv("B200MD_BUILD_GB");
-        gb = e ? atoi(e) : (int) (26.0 * nown / (n > 0 ? n : 1));
-        gb = gb < 1 ? 1 : gb > 16 ? 16 : gb;
-      }
+      // batch of a few lanes costs a whole pass over the candidates)
+      int gb = c->build_gb_user > 0 ? c->build_gb_user : (int) (26.0 * nown / (n > 0 ? n : 1));
+      gb = gb < 1 ? 1 : gb > 16 ? 16 : gb;
       c->build_gb = gb;
-#define BB_ARGS c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d, tile_ghost, bb, te, gb
+#define BB_ARGS c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d, tile_ghost, bb, gb
       const int bgrid = cdiv(cdiv(g.nbin[0], gb) * g.nbin[1] * g.nbin[2], BUILD_WARPS), bthr = BUILD_WARPS * 32;
-      c->tiled_emitted = tiled16;
-      if (tiled16) {
-        if (bonded) {
-          if (c->ntypes == 1) k_build_bins<1, 0, 1, 1><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
-          else k_build_bins<0, 0, 1, 1><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
-        } else {
-          if (c->ntypes == 1) k_build_bins<1, 0, 0, 1><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
-          else k_build_bins<0, 0, 0, 1><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
-        }
-      } else if (bonded) {
-        if (c->ntypes == 1) k_build_bins<1, 0, 1, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
-        else k_build_bins<0, 0, 1, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
-      } else if (c->ntypes == 1) {
-        if (stage) k_build_bins<1, 1, 0, 0><<<bgrid, bthr, stage_bytes, c->stream>>>(BB_ARGS);
-        else k_build_bins<1, 0, 0, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+      if (bonded) {
+        if (c->ntypes == 1) k_build_bins<1, 1><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+        else k_build_bins<0, 1><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
       } else {
-        if (stage) k_build_bins<0, 1, 0, 0><<<bgrid, bthr, stage_bytes, c->stream>>>(BB_ARGS);
-        else k_build_bins<0, 0, 0, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+        if (c->ntypes == 1) k_build_bins<1, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+        else k_build_bins<0, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
       }
 #undef BB_ARGS
       LAUNCH_CHECK();
@@ -817,11 +704,8 @@ int neigh_build_lists(b200md_ctx *c)
         return b200md_fail(c, B200MD_ERR_ARG, "bonded systems are built by the bin-per-warp kernel only (cluster size 1, FP32 prefilter)");
       c->tiles_valid = false;
       KProf kp(c, KC_NEIGH);
-#define BUILD_ARGS c->pos.p, n, c->bg, c->bin_start.p, c->cell_list.p, c->cutneighsq_d.p, c->ntypes, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d
-      if (CLs == 1) k_build_cluster<1><<<cdiv(nclus, 128), 128, smem, c->stream>>>(BUILD_ARGS);
-      else if (CLs == 2) k_build_cluster<2><<<cdiv(nclus, 128), 128, smem, c->stream>>>(BUILD_ARGS);
-      else k_build_cluster<4><<<cdiv(nclus, 128), 128, smem, c->stream>>>(BUILD_ARGS);
-#undef BUILD_ARGS
+      k_build_fp64<<<cdiv(n, 128), 128, smem, c->stream>>>(c->pos.p, n, c->bg, c->bin_start.p, c->cell_list.p, c->cutneighsq_d.p,
+                                                          c->ntypes, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d);
       LAUNCH_CHECK();
     }
     CU(cudaMemcpyAsync(c->flags_h, c->flags_d, 8 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
@@ -848,7 +732,5 @@ int neigh_build_lists(b200md_ctx *c)
   c->ago = 0;
   c->nbuilds++;
   c->list_valid = true;
-  TRY(pair_lj_tiled_prepare(c));   // B200MD_LJ_TILED=1 only
-  ph.mark("tiled lists");
   return B200MD_OK;
 }

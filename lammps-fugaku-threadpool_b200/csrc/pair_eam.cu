@@ -10,8 +10,6 @@
 // PairEAM::interpolate :769-797), 1-based knots m = 1..n, re-packed at init into 32-byte aligned pieces:
 //   rhoA[t][m]  = {c3,c4,c5,c6} of rhor_spline            (pass A reads one double4)
 //   tabC[t][m]  = {r0,r1,r2,-} {z0,z1,z2,z3} {z4,z5,z6,-}  only for the single-type fast path
-#include <stdlib.h>
-
 #include "ctx.cuh"
 
 __device__ __forceinline__ double4 ld4(const double4 *__restrict__ p)
@@ -57,11 +55,12 @@ struct EAMParams {
   const int *type2frho, *type2rhor, *type2z2r;
 };
 
-template <int CL, int EFLAG, int ONETYPE>
+template <int EFLAG, int ONETYPE>
 __global__ void __launch_bounds__(128)
 k_eam_rho_fp(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
              int nlocal, EAMParams P, double *__restrict__ rho_out, double *__restrict__ fp_out, double *__restrict__ partials)
 {
+  constexpr int CL = 1;   // one list per atom (lists per cluster of 2 / 4 atoms measured slower)
   const int q = blockIdx.x * blockDim.x + threadIdx.x;
   const int i0 = q * CL;
   double acc[1] = {0.0};
@@ -93,7 +92,7 @@ k_eam_rho_fp(const double4 *__restrict__ pos, const int *__restrict__ numneigh, 
       for (int a = 0; a < CL; a++) {
         const double dx = xi[a] - pj.x, dy = yi[a] - pj.y, dz = zi[a] - pj.z;
         const double rsq = dx * dx + dy * dy + dz * dz;
-        if (rsq < P.cutforcesq && ((ent >> (CLBITS + a)) & 1u)) {
+        if (rsq < P.cutforcesq) {
           double p = sqrt(rsq) * P.rdr + 1.0;
           int m = (int) p;
           m = min(m, P.nr - 1);
@@ -128,12 +127,13 @@ k_eam_rho_fp(const double4 *__restrict__ pos, const int *__restrict__ numneigh, 
   if (EFLAG) block_partials_e<1>(acc, partials);
 }
 
-template <int CL, int EVFLAG, int ONETYPE>
+template <int EVFLAG, int ONETYPE>
 __global__ void __launch_bounds__(128)
 k_eam_force(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
             int nlocal, EAMParams P, const double *__restrict__ fp, double *__restrict__ fx, double *__restrict__ fy,
             double *__restrict__ fz, double *__restrict__ partials)
 {
+  constexpr int CL = 1;   // one list per atom (lists per cluster of 2 / 4 atoms measured slower)
   const int q = blockIdx.x * blockDim.x + threadIdx.x;
   const int i0 = q * CL;
   double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
@@ -167,7 +167,7 @@ k_eam_force(const double4 *__restrict__ pos, const int *__restrict__ numneigh, c
       for (int a = 0; a < CL; a++) {
         const double dx = xi[a] - pj.x, dy = yi[a] - pj.y, dz = zi[a] - pj.z;
         const double rsq = dx * dx + dy * dy + dz * dz;
-        if (rsq < P.cutforcesq && ((ent >> (CLBITS + a)) & 1u)) {
+        if (rsq < P.cutforcesq) {
           const double r = sqrt(rsq);
           double p = r * P.rdr + 1.0;
           int m = (int) p;
@@ -245,13 +245,13 @@ k_eam_rho_fp_1t(const double4 *__restrict__ pos, const int *__restrict__ numneig
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   double acc[1] = {0.0};
   bool active = i < nlocal;
-  if (SPLIT == 1 && active) active = (tile_ghost[i >> 5] != 0) == (part != 0);  // overlap mode, see k_lj_lanes
+  if (SPLIT == 1 && active) active = (tile_ghost[i >> 5] != 0) == (part != 0);  // overlap mode, see k_lj_force
   if (active) {
     const double4 pi = pos[i];
     const int n = numneigh[i];
     const int *nb = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
     double rho = 0.0;
-    // software pipeline (see k_lj_lanes): next batch of list entries in flight while PF gathers are issued together
+    // software pipeline (see k_lj_force): next batch of list entries in flight while PF gathers are issued together
     constexpr int PF = 4;
     const int nlast = max(n - 1, 0);
     unsigned enx[PF];
@@ -306,7 +306,7 @@ k_eam_force_1t(const double4 *__restrict__ posfp, const int *__restrict__ numnei
   const int n1 = P.nr + 1;
   for (int k = threadIdx.x; k < 7 * n1; k += blockDim.x) s_t[k] = tab1[4 * n1 + k];
   __syncthreads();
-  const int i = (SPLIT == 2 ? part : 0) + blockIdx.x * blockDim.x + threadIdx.x;  // 2: range mode, see k_lj_lanes
+  const int i = (SPLIT == 2 ? part : 0) + blockIdx.x * blockDim.x + threadIdx.x;  // 2: range mode, see k_lj_force
   double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
   bool active = i < nlocal;
   if (SPLIT == 1 && active) active = (tile_ghost[i >> 5] != 0) == (part != 0);
@@ -370,28 +370,28 @@ k_eam_force_1t(const double4 *__restrict__ posfp, const int *__restrict__ numnei
   if (EVFLAG) block_partials_e<7>(acc, partials);
 }
 
-template <int CL> static void launch_eam_rho(b200md_ctx *c, int blocks, int threads, int ev, int onetype, const EAMParams &P, int n)
+static void launch_eam_rho(b200md_ctx *c, int blocks, int threads, int ev, int onetype, const EAMParams &P, int n)
 {
 #define A_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, c->rho.p, c->fp.p, c->partials.p
   if (ev) {
-    if (onetype) k_eam_rho_fp<CL, 1, 1><<<blocks, threads, 0, c->stream>>>(A_ARGS);
-    else k_eam_rho_fp<CL, 1, 0><<<blocks, threads, 0, c->stream>>>(A_ARGS);
+    if (onetype) k_eam_rho_fp<1, 1><<<blocks, threads, 0, c->stream>>>(A_ARGS);
+    else k_eam_rho_fp<1, 0><<<blocks, threads, 0, c->stream>>>(A_ARGS);
   } else {
-    if (onetype) k_eam_rho_fp<CL, 0, 1><<<blocks, threads, 0, c->stream>>>(A_ARGS);
-    else k_eam_rho_fp<CL, 0, 0><<<blocks, threads, 0, c->stream>>>(A_ARGS);
+    if (onetype) k_eam_rho_fp<0, 1><<<blocks, threads, 0, c->stream>>>(A_ARGS);
+    else k_eam_rho_fp<0, 0><<<blocks, threads, 0, c->stream>>>(A_ARGS);
   }
 #undef A_ARGS
 }
 
-template <int CL> static void launch_eam_force(b200md_ctx *c, int blocks, int threads, int ev, int onetype, const EAMParams &P, int n)
+static void launch_eam_force(b200md_ctx *c, int blocks, int threads, int ev, int onetype, const EAMParams &P, int n)
 {
 #define C_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, c->fp.p, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p
   if (ev) {
-    if (onetype) k_eam_force<CL, 1, 1><<<blocks, threads, 0, c->stream>>>(C_ARGS);
-    else k_eam_force<CL, 1, 0><<<blocks, threads, 0, c->stream>>>(C_ARGS);
+    if (onetype) k_eam_force<1, 1><<<blocks, threads, 0, c->stream>>>(C_ARGS);
+    else k_eam_force<1, 0><<<blocks, threads, 0, c->stream>>>(C_ARGS);
   } else {
-    if (onetype) k_eam_force<CL, 0, 1><<<blocks, threads, 0, c->stream>>>(C_ARGS);
-    else k_eam_force<CL, 0, 0><<<blocks, threads, 0, c->stream>>>(C_ARGS);
+    if (onetype) k_eam_force<0, 1><<<blocks, threads, 0, c->stream>>>(C_ARGS);
+    else k_eam_force<0, 0><<<blocks, threads, 0, c->stream>>>(C_ARGS);
   }
 #undef C_ARGS
 }
@@ -400,7 +400,7 @@ static bool eam_use_1t(const b200md_ctx *c)
 {
   const EAMTables &T = c->eam;
   const int onetype = (T.ntypes == 1 && T.nrhor == 1 && T.nz2r == 1);
-  return onetype && c->cl == 1 && (size_t) 7 * (T.nr + 1) * 8 <= 96 * 1024 && !getenv("B200MD_EAM_GENERIC");
+  return onetype && (size_t) 7 * (T.nr + 1) * 8 <= 96 * 1024;
 }
 
 static EAMParams eam_params(const b200md_ctx *c)
@@ -439,12 +439,8 @@ __global__ void k_posfp_fill(const double4 *__restrict__ pos, const double *__re
 }
 
 // passes A+B (pair_eam.cpp:187-247): rho, fp and the embedding energy (-> red_d[8]) of the owned atoms
-static int pair_eam_rho_tiled(b200md_ctx *c, int ev);
-static int pair_eam_force_tiled(b200md_ctx *c, int ev);
-
 int pair_eam_rho(b200md_ctx *c, int ev)
 {
-  if (c->tiled_valid && eam_use_1t(c)) return pair_eam_rho_tiled(c, ev);
   const int n = c->nlocal;
   const EAMTables &T = c->eam;
   const EAMParams P = eam_params(c);
@@ -465,15 +461,12 @@ int pair_eam_rho(b200md_ctx *c, int ev)
     if (ev) TRY(reduce_partials(c, blocks, 1, 8));
     return B200MD_OK;
   }
-  const int nclus = cdiv(n, c->cl);
-  const int threads = 128, blocks = cdiv(nclus, threads);
+  const int threads = 128, blocks = cdiv(n, threads);
   if (ev) TRY(dev_ensure(c, c->partials, (size_t) blocks * 8));
   const int onetype = (T.ntypes == 1 && T.nrhor == 1 && T.nz2r == 1);
   {
     KProf kp(c, KC_EAM_RHO);
-    if (c->cl == 1) launch_eam_rho<1>(c, blocks, threads, ev, onetype, P, n);
-    else if (c->cl == 2) launch_eam_rho<2>(c, blocks, threads, ev, onetype, P, n);
-    else launch_eam_rho<4>(c, blocks, threads, ev, onetype, P, n);
+    launch_eam_rho(c, blocks, threads, ev, onetype, P, n);
     LAUNCH_CHECK();
   }
   if (ev) TRY(reduce_partials(c, blocks, 1, 8));  // embedding energy -> red_d[8]
@@ -484,7 +477,6 @@ int pair_eam_rho(b200md_ctx *c, int ev)
 // {x,y,z,fp} records of the single-type path from pos + fp instead of expecting them from the halo)
 int pair_eam_force(b200md_ctx *c, int ev, bool ghost_from_fp)
 {
-  if (c->tiled_valid && eam_use_1t(c) && !ghost_from_fp) return pair_eam_force_tiled(c, ev);
   const int n = c->nlocal;
   const EAMTables &T = c->eam;
   const EAMParams P = eam_params(c);
@@ -507,15 +499,12 @@ int pair_eam_force(b200md_ctx *c, int ev, bool ghost_from_fp)
     if (ev) TRY(reduce_partials(c, blocks, 7, 0));
     return B200MD_OK;
   }
-  const int nclus = cdiv(n, c->cl);
-  const int threads = 128, blocks = cdiv(nclus, threads);
+  const int threads = 128, blocks = cdiv(n, threads);
   if (ev) TRY(dev_ensure(c, c->partials, (size_t) blocks * 8));
   const int onetype = (T.ntypes == 1 && T.nrhor == 1 && T.nz2r == 1);
   {
     KProf kp(c, KC_PAIR);
-    if (c->cl == 1) launch_eam_force<1>(c, blocks, threads, ev, onetype, P, n);
-    else if (c->cl == 2) launch_eam_force<2>(c, blocks, threads, ev, onetype, P, n);
-    else launch_eam_force<4>(c, blocks, threads, ev, onetype, P, n);
+    launch_eam_force(c, blocks, threads, ev, onetype, P, n);
     LAUNCH_CHECK();
   }
   if (ev) TRY(reduce_partials(c, blocks, 7, 0));  // pair energy + virial -> red_d[0..6]; eng = red[0] + red[8]
@@ -567,7 +556,7 @@ int pair_eam_force_part(b200md_ctx *c, int part)
 }
 
 // ---- host-buffer pipeline (capi.cu): passes A+B and the fp halo for all atoms, then pass C range by range ----
-bool pair_eam_range_usable(const b200md_ctx *c) { return eam_use_1t(c) && !c->tiled_valid; }
+bool pair_eam_range_usable(const b200md_ctx *c) { return eam_use_1t(c); }
 
 int pair_eam_before_ranges(b200md_ctx *c)
 {
@@ -664,206 +653,5 @@ int pair_eam_peratom(b200md_ctx *c, double *out, size_t stride)
   const double4 *posfp = eam_use_1t(c) ? c->posfp.p : nullptr;
   k_eam_peratom<<<cdiv(n, 128), 128, 0, c->stream>>>(c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, c->rho.p, c->fp.p, posfp, out, stride);
   LAUNCH_CHECK();
-  return B200MD_OK;
-}
-
-// ------------------------------------------------------------------------------------------------------------
-// Shared-memory tiled single-type EAM passes (opt-in with B200MD_LJ_TILED=1, see k_lj_tiled in pair_lj.cu): a block =
-// TG bins of an x-row; its 3 x 3 x (TG+2)-bin neighbourhood is gathered once per pass into shared memory (positions
-// in the rho pass, {x,y,z,fp} records in the force pass) next to the spline table, and the loops read neighbors
-// through the 16-bit slot lists.  Arithmetic and list order are those of k_eam_rho_fp_1t / k_eam_force_1t.
-// ------------------------------------------------------------------------------------------------------------
-template <int EFLAG>
-__global__ void __launch_bounds__(128)
-k_eam_rho_fp_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__restrict__ cell_list, const double4 *__restrict__ pos,
-                   const int *__restrict__ numneigh, const unsigned short *__restrict__ neigh16, int maxneigh, int nlocal, int max_staged,
-                   EAMParams P, const double *__restrict__ tab1, double *__restrict__ rho_out, double *__restrict__ fp_out,
-                   double4 *__restrict__ posfp, double *__restrict__ partials)
-{
-  extern __shared__ double4 s_tile[];   // x[], y[], z[], (unused) of max_staged doubles each (see k_lj_tiled), then [4][n1] rhor c3..c6
-  double *s_x = reinterpret_cast<double *>(s_tile), *s_y = s_x + max_staged, *s_z = s_y + max_staged;
-  double *s_t = s_z + 2 * max_staged;
-  const int n1 = P.nr + 1;
-  int ks[9], off[10], own_s, own_e, by, bz;
-  tile_rows(T, bin_start, blockIdx.x, ks, off, own_s, own_e, by, bz);
-  for (int k = threadIdx.x; k < 4 * n1; k += blockDim.x) s_t[k] = tab1[k];
-#pragma unroll
-  for (int r = 0; r < 9; r++) {
-    const int len = off[r + 1] - off[r];
-    for (int k = threadIdx.x; k < len; k += blockDim.x) {
-      const double4 q = ld_pos256(pos + cell_list[ks[r] + k]);
-      s_x[off[r] + k] = q.x; s_y[off[r] + k] = q.y; s_z[off[r] + k] = q.z;
-    }
-  }
-  __syncthreads();
-  double acc[1] = {0.0};
-  for (int slot = own_s + threadIdx.x; slot < own_e; slot += blockDim.x) {
-    const int i = cell_list[slot];
-    if (i >= nlocal) continue;
-    const double4 pi = pos[i];
-    const int n = numneigh[i];
-    const unsigned short *nb = neigh16 + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
-    double rho = 0.0;
-#pragma unroll 4
-    for (int k = 0; k < n; k++) {
-      const int e = __ldcs(nb + (size_t) k * TILE);
-      const double dx = pi.x - s_x[e], dy = pi.y - s_y[e], dz = pi.z - s_z[e];
-      const double rsq = dx * dx + dy * dy + dz * dz;
-      if (rsq < P.cutforcesq) {
-        double p = rsq * rsqrt(rsq) * P.rdr + 1.0;
-        int m = (int) p;
-        m = min(m, P.nr - 1);
-        p -= m;
-        p = fmin(p, 1.0);
-        rho += ((s_t[m] * p + s_t[n1 + m]) * p + s_t[2 * n1 + m]) * p + s_t[3 * n1 + m];
-      }
-    }
-    double p = rho * P.rdrho + 1.0;
-    int m = (int) p;
-    m = max(1, min(m, P.nrho - 1));
-    p -= m;
-    p = fmin(p, 1.0);
-    const double *cf = P.frho + (size_t) m * 7;
-    const double fpi = (__ldg(cf) * p + __ldg(cf + 1)) * p + __ldg(cf + 2);
-    rho_out[i] = rho;
-    fp_out[i] = fpi;
-    posfp[i] = make_double4(pi.x, pi.y, pi.z, fpi);
-    if (EFLAG) {
-      double phi = ((__ldg(cf + 3) * p + __ldg(cf + 4)) * p + __ldg(cf + 5)) * p + __ldg(cf + 6);
-      if (rho > P.rhomax) phi += fpi * (rho - P.rhomax);
-      acc[0] += phi;
-    }
-  }
-  if (EFLAG) block_partials_e<1>(acc, partials);
-}
-
-template <int EVFLAG>
-__global__ void __launch_bounds__(128)
-k_eam_force_tiled(TileGeom T, const int *__restrict__ bin_start, const int *__restrict__ cell_list, const double4 *__restrict__ posfp,
-                  const int *__restrict__ numneigh, const unsigned short *__restrict__ neigh16, int maxneigh, int nlocal, int max_staged,
-                  EAMParams P, const double *__restrict__ tab1, double *__restrict__ fx, double *__restrict__ fy, double *__restrict__ fz,
-                  double *__restrict__ partials)
-{
-  extern __shared__ double4 s_tile[];   // x[], y[], z[], fp[] of max_staged doubles each, then [7][n1]: rhor c0..c2, z2r c3..c6
-  double *s_x = reinterpret_cast<double *>(s_tile), *s_y = s_x + max_staged, *s_z = s_y + max_staged, *s_w = s_z + max_staged;
-  double *s_t = s_w + max_staged;
-  const int n1 = P.nr + 1;
-  int ks[9], off[10], own_s, own_e, by, bz;
-  tile_rows(T, bin_start, blockIdx.x, ks, off, own_s, own_e, by, bz);
-  for (int k = threadIdx.x; k < 7 * n1; k += blockDim.x) s_t[k] = tab1[4 * n1 + k];
-#pragma unroll
-  for (int r = 0; r < 9; r++) {
-    const int len = off[r + 1] - off[r];
-    for (int k = threadIdx.x; k < len; k += blockDim.x) {
-      const double4 q = ld_pos256(posfp + cell_list[ks[r] + k]);
-      s_x[off[r] + k] = q.x; s_y[off[r] + k] = q.y; s_z[off[r] + k] = q.z; s_w[off[r] + k] = q.w;
-    }
-  }
-  __syncthreads();
-  double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-  for (int slot = own_s + threadIdx.x; slot < own_e; slot += blockDim.x) {
-    const int i = cell_list[slot];
-    if (i >= nlocal) continue;
-    const double4 pi = posfp[i];
-    const int n = numneigh[i];
-    const unsigned short *nb = neigh16 + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
-    double fxi = 0.0, fyi = 0.0, fzi = 0.0;
-#pragma unroll 2
-    for (int k = 0; k < n; k++) {
-      const int e = __ldcs(nb + (size_t) k * TILE);
-      const double dx = pi.x - s_x[e], dy = pi.y - s_y[e], dz = pi.z - s_z[e];
-      const double rsq = dx * dx + dy * dy + dz * dz;
-      if (rsq < P.cutforcesq) {
-        const double pjw = s_w[e];
-        const double recip = rsqrt(rsq);
-        const double r = rsq * recip;
-        double p = r * P.rdr + 1.0;
-        int m = (int) p;
-        m = min(m, P.nr - 1);
-        p -= m;
-        p = fmin(p, 1.0);
-        const double rhoip = (s_t[m] * p + s_t[n1 + m]) * p + s_t[2 * n1 + m];
-        const double z3 = s_t[3 * n1 + m], z4 = s_t[4 * n1 + m], z5 = s_t[5 * n1 + m], z6 = s_t[6 * n1 + m];
-        const double z2 = ((z3 * p + z4) * p + z5) * p + z6;
-        const double z2p = ((3.0 * z3 * p + 2.0 * z4) * p + z5) * P.rdr;
-        const double phi = z2 * recip;
-        const double phip = z2p * recip - phi * recip;
-        const double psip = (pi.w + pjw) * rhoip + phip;
-        const double fpair = -psip * recip;
-        fxi += dx * fpair;
-        fyi += dy * fpair;
-        fzi += dz * fpair;
-        if (EVFLAG) {
-          acc[0] += 0.5 * phi;
-          const double hf = 0.5 * fpair;
-          acc[1] += dx * dx * hf;
-          acc[2] += dy * dy * hf;
-          acc[3] += dz * dz * hf;
-          acc[4] += dx * dy * hf;
-          acc[5] += dx * dz * hf;
-          acc[6] += dy * dz * hf;
-        }
-      }
-    }
-    fx[i] = fxi;
-    fy[i] = fyi;
-    fz[i] = fzi;
-  }
-  if (EVFLAG) block_partials_e<7>(acc, partials);
-}
-
-static int eam_tiled_attrs(int device)
-{
-  static bool done_dev[64] = {};  // per device: a process may hold contexts on several GPUs
-  bool &done = done_dev[device & 63];
-  if (done) return 0;
-  if (cudaFuncSetAttribute(k_eam_rho_fp_tiled<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess ||
-      cudaFuncSetAttribute(k_eam_rho_fp_tiled<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess ||
-      cudaFuncSetAttribute(k_eam_force_tiled<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess ||
-      cudaFuncSetAttribute(k_eam_force_tiled<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess)
-    return 1;
-  done = true;
-  return 0;
-}
-
-static int pair_eam_rho_tiled(b200md_ctx *c, int ev)
-{
-  const EAMTables &E = c->eam;
-  const EAMParams P = eam_params(c);
-  const TileGeom T = tile_geom(c);
-  const int nseg = c->tiled_nseg, n = c->nlocal;
-  const size_t smem = (size_t) c->tiled_max_staged * sizeof(double4) + (size_t) 4 * (E.nr + 1) * sizeof(double);
-  TRY(dev_ensure(c, c->posfp, (size_t) n + c->nghost));
-  if (ev) TRY(dev_ensure(c, c->partials, (size_t) nseg * 8));
-  if (eam_tiled_attrs(c->device)) return b200md_fail(c, B200MD_ERR_CUDA, "cudaFuncSetAttribute (tiled eam) failed");
-  {
-    KProf kp(c, KC_EAM_RHO);
-#define R_ARGS T, c->bin_start.p, c->cell_list.p, c->pos.p, c->numneigh.p, c->neigh16.p, c->maxneigh, n, c->tiled_max_staged, P, E.tab1, c->rho.p, c->fp.p, c->posfp.p, c->partials.p
-    if (ev) k_eam_rho_fp_tiled<1><<<nseg, 128, smem, c->stream>>>(R_ARGS);
-    else k_eam_rho_fp_tiled<0><<<nseg, 128, smem, c->stream>>>(R_ARGS);
-#undef R_ARGS
-    LAUNCH_CHECK();
-  }
-  if (ev) TRY(reduce_partials(c, nseg, 1, 8));
-  return B200MD_OK;
-}
-
-static int pair_eam_force_tiled(b200md_ctx *c, int ev)
-{
-  const EAMTables &E = c->eam;
-  const EAMParams P = eam_params(c);
-  const TileGeom T = tile_geom(c);
-  const int nseg = c->tiled_nseg, n = c->nlocal;
-  const size_t smem = (size_t) c->tiled_max_staged * sizeof(double4) + (size_t) 7 * (E.nr + 1) * sizeof(double);
-  if (ev) TRY(dev_ensure(c, c->partials, (size_t) nseg * 8));
-  {
-    KProf kp(c, KC_PAIR);
-#define F_ARGS T, c->bin_start.p, c->cell_list.p, c->posfp.p, c->numneigh.p, c->neigh16.p, c->maxneigh, n, c->tiled_max_staged, P, E.tab1, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p
-    if (ev) k_eam_force_tiled<1><<<nseg, 128, smem, c->stream>>>(F_ARGS);
-    else k_eam_force_tiled<0><<<nseg, 128, smem, c->stream>>>(F_ARGS);
-#undef F_ARGS
-    LAUNCH_CHECK();
-  }
-  if (ev) TRY(reduce_partials(c, nseg, 7, 0));
   return B200MD_OK;
 }

@@ -67,6 +67,7 @@ B200Device::B200Device(LAMMPS *lmp) : Pointers(lmp), ctx(nullptr), resident(0), 
   if (const char *e = getenv("B200MD_DEVICE")) device = atoi(e);
   else if (const char *l = getenv("OMPI_COMM_WORLD_LOCAL_RANK")) device = atoi(l);
   else if (const char *l2 = getenv("SLURM_LOCALID")) device = atoi(l2);
+  device_id = device;
   int st = b200md_create(&ctx, device, nprocs, me, nprocs > 1 ? id : nullptr);
   if (st != B200MD_OK)
     error->one(FLERR, "b200: cannot create the device context (there is no CPU fallback): {}", b200md_last_error(ctx));
@@ -75,6 +76,11 @@ B200Device::B200Device(LAMMPS *lmp) : Pointers(lmp), ctx(nullptr), resident(0), 
 B200Device::~B200Device()
 {
   if (ctx) b200md_destroy(ctx);
+}
+
+void B200Device::announce(const char *what)
+{
+  if (comm->me == 0) utils::logmesg(lmp, "b200: {} on CUDA device {} (libb200md, sm_100a)\n", what, device_id);
 }
 
 void B200Device::check(int status, const char *file, int line)

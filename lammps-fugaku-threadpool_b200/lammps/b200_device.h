@@ -20,6 +20,7 @@ class B200Device : protected Pointers {
   static B200Device *peek(LAMMPS *lmp);    // the context if one exists, without creating or referencing it
 
   b200md_ctx *ctx;
+  int device_id;      // CUDA device of this rank
   int resident;       // 1 while VerletB200::run owns the atoms on the device (pair/fix host hooks are idle)
   bigint resident_step;
 
@@ -30,6 +31,9 @@ class B200Device : protected Pointers {
   // eflag_atom / vflag_atom under the stock loop: run the per-atom pass and ADD the owned atoms' tallies to the pair
   // style's eatom / vatom (host order == device order in host-ghost mode)
   void peratom_to_host(int nlocal, double *eatom, double **vatom);
+  // one log line per style per init ("b200: pair lj/cut/b200 on CUDA device 0"): the evidence in a run's output that
+  // the suffix resolved to the device style and not to the reference's own class (LAMMPS falls back silently)
+  void announce(const char *what);
 
  private:
   B200Device(LAMMPS *);

@@ -38,6 +38,7 @@ void PairEAMB200::init_style()
   embedstep = -1;
   if (atom->molecular != Atom::ATOMIC) error->all(FLERR, "Pair style eam/b200 requires atom_style atomic");
   tables_loaded = 0;
+  dev->announce("pair eam/b200");
 }
 
 void PairEAMB200::device_tables(B200Device *d)

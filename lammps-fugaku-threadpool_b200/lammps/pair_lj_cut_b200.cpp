@@ -39,6 +39,7 @@ void PairLJCutB200::init_style()
   cut_respa = nullptr;    // PairLJCut::init_style sets it (its constructor does not); init_one reads it
   // no host NeighList is requested: Neighbor still runs decide/exchange/borders, the list lives on the device
   tables_loaded = 0;
+  dev->announce("pair lj/cut/b200");
 }
 
 void PairLJCutB200::device_tables(B200Device *d)

@@ -87,6 +87,7 @@ void VerletB200::init()
     MPI_Allreduce(&bad, &anybad, 1, MPI_INT, MPI_MAX, world);
     if (anybad) error->all(FLERR, "Run style verlet/b200 needs x-fastest rank placement: use 'processors * * * map xyz'");
   }
+  dev->announce("run_style verlet/b200 (device-resident loop)");
 }
 
 void VerletB200::upload()

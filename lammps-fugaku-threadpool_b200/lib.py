@@ -40,7 +40,6 @@ PROTOTYPES = {
     "b200md_neigh_build": (_i, [_vp]),
     "b200md_neigh_export": (_i, [_vp, _vp, _vp, _vp]),
     "b200md_neigh_stats": (_i, [_vp, _vp, _vp, _vp]),
-    "b200md_neigh_cluster_stats": (_i, [_vp, _vp, _vp, _vp]),
     "b200md_halo_forward": (_i, [_vp]),
     "b200md_plan_peers": (_i, [_vp, _vp, _i, _vp, _vp]),
     "b200md_pair_compute": (_i, [_vp, _i, _i, _vp, _vp]),
@@ -73,7 +72,7 @@ PROTOTYPES = {
     "b200md_profile": (_i, [_vp, _i]),
     "b200md_kernel_times": (_i, [_vp, _vp, _vp, _i]),
     "b200md_stream": (_vp, [_vp]),
-    "b200md_tiled_active": (_i, [_vp]),
+    "b200md_tune": (_i, [_vp, C.c_char_p, _i]),
     "b200md_build_bins_per_warp": (_i, [_vp]),
 }
 

@@ -295,6 +295,7 @@ class B200MD:
         self.fix_langevin = None
         self.sortfreq, self.sort_binsize = 1000, 0.0   # atom_modify sort defaults (src/atom.cpp:119-120)
         self._order = None
+        self._special_lj = None
 
     # -- script-command analogues ---------------------------------------------------------------
     def box(self, lo, hi, periodic=(1, 1, 1)):
@@ -339,6 +340,12 @@ class B200MD:
         """Only `special_bonds fene` (lj 0.0 1.0 1.0): what the bonded neighbor build implements."""
         if keyword != "fene":
             raise ValueError("special_bonds: only the fene setting (lj 0.0 1.0 1.0) is on the B200 hot path")
+        # Force::special_lj as `special_bonds fene` sets it (src/force.cpp: special_lj[1..3] = 0, 1, 1); the library
+        # refuses a bonded system whose pair style was initialised with any other weights
+        self._special_lj = np.array([1.0, 0.0, 1.0, 1.0])
+        if getattr(self, "pair", None) is not None and hasattr(self.pair, "special_lj"):
+            self.pair.special_lj[:] = self._special_lj
+            self._initialized = False
 
     def fix(self, style: str, *args, **kw):
         if style in ("langevin", "langevin/b200"):
@@ -361,6 +368,8 @@ class B200MD:
         if name in ("lj/cut", "lj/cut/b200"):
             self.pair = PairLJCutB200(self)
             self.pair.settings(*args)
+            if getattr(self, "_special_lj", None) is not None:
+                self.pair.special_lj[:] = self._special_lj
         elif name in ("eam", "eam/b200"):
             self.pair = PairEAMB200(self)
         elif name in ("eam/alloy", "eam/alloy/b200"):
@@ -374,6 +383,10 @@ class B200MD:
 
     def timestep(self, dt: float):
         self.dt = float(dt)
+
+    def tune(self, key: str, value: int):
+        """`package`-style execution knobs of the device context (include/b200md.h b200md_tune): overlap, host_pipeline, hs_min_chunk."""
+        self.ctx.call("b200md_tune", key.encode(), int(value))
 
     # -- init / setup / run -------------------------------------------------------------------------
     def init(self):

@@ -17,27 +17,18 @@ GOLDEN = ROOT / "tests" / "golden"
 POT = ROOT / "lammps-fugaku-threadpool_b200" / "data" / "Cu_u3.eam"
 
 
-# GPU tests written after round 1's GPU budget was spent: their first hardware run is the round-end suite.  They are
-# non-strict xfail so that a surprise there is reported (x / X in the summary) without masking the verified tests
-# behind `-x`; round 2 promotes them to plain tests.
-FIRST_RUN = pytest.mark.xfail(strict=False, reason="first hardware run (written after round 1's GPU budget was spent)")
-
-
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a B200 (run with -m gpu on the GPU box)")
 
 
 def pytest_collection_modifyitems(config, items):
     """A GPU test that hangs (a kernel that never ends) must end the run, not sit there until the box is taken away:
-    pytest-timeout's thread method dumps the stacks and exits the process after 15 minutes in one test."""
+    pytest-timeout's thread method dumps the stacks and exits the process after 10 minutes in one test."""
     if not config.pluginmanager.hasplugin("timeout"):
         return
     for item in items:
         if item.get_closest_marker("gpu") and not item.get_closest_marker("timeout"):
-            # a FIRST_RUN test has never met the hardware: a hang there should cost 5 minutes, not 15
-            xf = item.get_closest_marker("xfail")
-            first_run = xf is not None and str(xf.kwargs.get("reason", "")).startswith("first hardware run")
-            item.add_marker(pytest.mark.timeout(300 if first_run else 900, method="thread"))
+            item.add_marker(pytest.mark.timeout(600, method="thread"))
 
 
 @pytest.fixture(scope="session")

@@ -84,45 +84,39 @@ import test_gpu_parity as gp  # noqa: E402
 
 @pytest.mark.parametrize("pipeline", [False, True])
 @pytest.mark.parametrize("name,steps", [("lj2_864", 25), ("eam_500", 30)])
-def test_emu_host_buffer_step(emu, name, steps, pipeline, monkeypatch):
-    """b200md_step_host, serial form (default) and the three-stream chunk pipeline (B200MD_HOST_PIPELINE=1; the
-    emulation runs streams in issue order, so this checks its indexing and chunking, not its event protocol)"""
-    gp.test_host_buffer_step_equals_device_loop(emu, name, steps, pipeline, monkeypatch)
+def test_emu_host_buffer_step(emu, name, steps, pipeline):
+    """b200md_step_host, serial form and the three-stream chunk pipeline (the default; the emulation runs streams in
+    issue order, so this checks its indexing and chunking, not its event protocol)"""
+    gp.test_host_buffer_step_equals_device_loop(emu, name, steps, pipeline)
 
 
 @pytest.mark.parametrize("kind,steps", [("lj", 45), ("eam", 25)])
-def test_emu_host_buffer_pipeline_chunked(emu, oracle, kind, steps, monkeypatch):
-    gp.test_host_buffer_pipeline_chunked(emu, oracle, kind, steps, monkeypatch)
+def test_emu_host_buffer_pipeline_chunked(emu, oracle, kind, steps):
+    gp.test_host_buffer_pipeline_chunked(emu, oracle, kind, steps)
 
 
 @pytest.mark.parametrize("name,steps", [("lj_500", 45), ("eam_500", 30)])
-def test_emu_overlapped_halo(emu, name, steps, monkeypatch):
-    """B200MD_OVERLAP=1: interior / boundary tile split of the force kernels (tile_ghost flags from the build)"""
-    gp.test_overlapped_halo_equals_plain(emu, name, steps, monkeypatch)
+def test_emu_overlapped_halo(emu, name, steps):
+    """overlap mode: interior / boundary tile split of the force kernels (tile_ghost flags from the build)"""
+    gp.test_overlapped_halo_equals_plain(emu, name, steps)
 
 
 @pytest.mark.parametrize("name", list(CASES))
-def test_emu_neighbor_list_bit_exact(emu, name, monkeypatch):
+def test_emu_neighbor_list_bit_exact(emu, name):
     gp.test_neighbor_list_bit_exact(emu, name)
-    monkeypatch.setenv("B200MD_BUILD_STAGE", "1")   # shared-memory row staging of the list stores (opt-in)
-    gp.test_neighbor_list_bit_exact(emu, name)
-    monkeypatch.delenv("B200MD_BUILD_STAGE")
-    for gb in ("2", "5"):                            # several bins of an x-row per warp (sparse-bin form)
-        monkeypatch.setenv("B200MD_BUILD_GB", gb)
-        gp.test_neighbor_list_bit_exact(emu, name)
-    monkeypatch.delenv("B200MD_BUILD_GB")
-    monkeypatch.setenv("B200MD_BUILD_FP64", "1")    # the all-FP64 build kernel
-    gp.test_neighbor_list_bit_exact(emu, name)
+    for gb in (2, 5):                                # several bins of an x-row per warp (sparse-bin form)
+        gp.test_neighbor_list_bit_exact(emu, name, tune={"build_gb": gb})
+    gp.test_neighbor_list_bit_exact(emu, name, tune={"build_fp64": 1})   # the all-FP64 fallback kernel
 
 
 @pytest.mark.parametrize("kind,steps", [("lj", 45), ("eam", 25)])
-def test_emu_bins_per_warp_same_list_order(emu, oracle, kind, steps, monkeypatch):
+def test_emu_bins_per_warp_same_list_order(emu, oracle, kind, steps):
     """k_build_bins with 1, 3 and 7 bins per warp (3 and 7 do not divide the bin count; 7 needs several 32-lane
     batches per segment) writes the same lists in the same entry order: trajectories are bit-identical"""
     out = []
-    for gb in ("1", "3", "7"):
-        monkeypatch.setenv("B200MD_BUILD_GB", gb)
+    for gb in (1, 3, 7):
         md, _ = gp._bench_system(emu, oracle, kind, 8)
+        md.tune("build_gb", gb)
         md.run(steps)
         assert emu.lib.load().b200md_build_bins_per_warp(md.ctx.h) == int(gb)
         out.append((md.gather(), md.thermo_log[-1]["pe"], md.neigh_stats()))
@@ -139,16 +133,13 @@ def test_emu_piecewise_api_and_error_paths(emu):
 
 
 @pytest.mark.parametrize("kind,n,steps", [("lj", 12, 45), ("eam", 12, 25)])
-def test_emu_overlap_with_interior_tiles(emu, oracle, kind, n, steps, monkeypatch):
+def test_emu_overlap_with_interior_tiles(emu, oracle, kind, n, steps):
     """a box wide enough (12^3 cells) that many 32-atom tiles have no ghost in their lists, so the interior part of
     the split really runs under the halo: overlap == plain, bit for bit, through rebuilds"""
     out = []
     for overlap in (False, True):
-        if overlap:
-            monkeypatch.setenv("B200MD_OVERLAP", "1")
-        else:
-            monkeypatch.delenv("B200MD_OVERLAP", raising=False)
         md, _ = gp._bench_system(emu, oracle, kind, n)
+        md.tune("overlap", int(overlap))
         md.run(steps)
         out.append((md.gather(), md.thermo_log[-1]["pe"], md.neigh_stats()["builds"]))
         md.close()
@@ -232,7 +223,7 @@ class _AllSum:
         return tot
 
 
-def run_decomposed_emu(pkg, world, grid, kind, cells, steps, host_steps=0, configure=None):
+def run_decomposed_emu(pkg, world, grid, kind, cells, steps, host_steps=0, configure=None, tune=None):
     """tests/multirank_util._worker with threads for ranks; optionally `host_steps` more steps through
     b200md_step_host (the bench's e2e leg: atoms migrate between ranks at its rebuilds)"""
     import bench
@@ -249,6 +240,8 @@ def run_decomposed_emu(pkg, world, grid, kind, cells, steps, host_steps=0, confi
             md.create_atoms(x, v, np.ones(len(x), dtype=np.int32), tag, natoms_total=natoms)
             if configure:
                 configure(md)
+            for k, val in (tune or {}).items():
+                md.tune(k, val)
             md.setup()
             t0 = md.thermo_log[-1]
             numneigh, _ = md.neighbor_list()
@@ -342,12 +335,11 @@ def test_emu_host_buffer_step_with_migration(emu, kind, world, grid, cells, step
 
 
 @pytest.mark.parametrize("kind,world,grid,cells,steps", [("lj", 4, (2, 2, 1), 6, 45), ("eam", 8, (2, 2, 2), 5, 30)])
-def test_emu_decomposed_overlap_equals_plain(emu, kind, world, grid, cells, steps, monkeypatch):
-    """B200MD_OVERLAP=1 on several ranks (where the halo it hides is an NCCL exchange): same trajectory, bit for bit"""
-    monkeypatch.delenv("B200MD_OVERLAP", raising=False)
-    a = run_decomposed_emu(emu, world, grid, kind, cells, steps)
-    monkeypatch.setenv("B200MD_OVERLAP", "1")
-    b = run_decomposed_emu(emu, world, grid, kind, cells, steps)
+def test_emu_decomposed_overlap_equals_plain(emu, kind, world, grid, cells, steps):
+    """overlap mode on several ranks (its default there; the halo it hides is an NCCL exchange) against the serialized
+    halo: same trajectory, bit for bit"""
+    a = run_decomposed_emu(emu, world, grid, kind, cells, steps, tune={"overlap": 0})
+    b = run_decomposed_emu(emu, world, grid, kind, cells, steps, tune={"overlap": 1})
     for ra, rb in zip(a, b):
         assert np.array_equal(ra["tag1"], rb["tag1"]) and np.array_equal(ra["x1"], rb["x1"])
         assert np.array_equal(ra["thermo1"], rb["thermo1"]) and ra["builds"] == rb["builds"]
@@ -373,6 +365,35 @@ def test_emu_langevin_counter_mode_is_rank_count_independent(emu):
     dx = x[o] - one["x1"]
     dx -= one["box"] * np.round(dx / one["box"])
     assert np.abs(dx).max() < 1e-6
+
+
+def test_emu_langevin_counter_mode_runs_past_a_sort_step_with_migration(emu):
+    """counter-mode thermostat on 2 ranks with `atom_modify sort 10`: atoms migrate between the ranks before the first
+    rebuild at a sort step.  The RanMars replay order (sized for the initial owned atoms) must not be consulted in
+    counter mode -- it would be stale after the first migration (round-1 advisor finding)."""
+    def thermostat(md):
+        md.fix("langevin", 1.44, 1.44, 0.5, 48279, rng="counter")
+        md.atom_modify_sort(10)
+
+    res = run_decomposed_emu(emu, 2, (2, 1, 1), "lj", 6, 45, configure=thermostat, host_steps=0)
+    assert sum(r["nlocal1"] for r in res) == 2 * 4 * 6 ** 3
+    assert res[0]["builds"] >= 2 and len({r["nlocal1"] for r in res}) > 1 or res[0]["nlocal1"] != 4 * 6 ** 3
+
+
+def test_emu_tune_and_special_bonds_errors(emu):
+    """b200md_tune refuses unknown keys; a bonded system whose pair style was given special_lj other than the fene
+    weights is refused at setup (the bonded build implements exactly lj 0 1 1)"""
+    g = load_golden("chain_32k")
+    md = chain.make_chain_device(emu, g, langevin=False)
+    with pytest.raises(emu.lib.B200MDError) as e:
+        md.tune("no_such_knob", 1)
+    assert "unknown key" in str(e.value)
+    md.pair.special_lj[:] = [1.0, 0.0, 0.0, 0.0]   # the LAMMPS default, not `special_bonds fene`
+    md._initialized = False
+    with pytest.raises(emu.lib.B200MDError) as e:
+        md.setup()
+    assert "special_bonds fene" in str(e.value)
+    md.close()
 
 
 def test_emu_chain_with_counter_thermostat(emu):
@@ -432,6 +453,7 @@ def test_emu_chain_decomposed_equals_single(emu):
         md.neighbor.modify(every=1, delay=1, check=True)
         md.timestep(0.012)
         md.create_atoms(g["in_x"][sel], g["in_v"][sel], g["in_type"][sel], g["in_tag"][sel], natoms_total=len(g["in_tag"]))
+        md.special_bonds("fene")
         md.bonds(g["in_tag"], num, btype, batom)          # the COMPLETE topology on every rank
         md.bond_style("fene", 1).coeff(1, 30.0, 1.5, 1.0, 1.0)
         md.fix("langevin", 1.0, 1.0, 10.0, 904297, rng="counter")
@@ -497,6 +519,7 @@ def test_emu_replicated_chain_and_bench_leg(emu, monkeypatch):
     md.neighbor.modify(every=1, delay=1, check=True)
     md.timestep(0.012)
     md.create_atoms(R["x"], R["v"], R["type"], R["tag"])
+    md.special_bonds("fene")
     md.bonds(R["tag"], *emu.inputs.bond_arrays(R["tag"], R["bonds"]))
     md.bond_style("fene", 1).coeff(1, 30.0, 1.5, 1.0, 1.0)
     md.setup()
@@ -536,14 +559,14 @@ def test_emu_peratom_needs_a_list(emu):
 
 def test_emu_results_do_not_depend_on_block_or_thread_order():
     """CUDA promises no execution order between blocks, nor between the threads of a block outside its barriers: a
-    subset of the cases (reference goldens, bit-exact lists, the bonded build, host-buffer steps, the tiled kernels) once more with
+    subset of the cases (reference goldens, bit-exact lists, the bonded build, host-buffer steps) once more with
     the emulator running blocks and threads last-to-first (CUDAEMU_ORDER=reverse, read once per process)"""
     import subprocess
 
     env = dict(os.environ, CUDAEMU_ORDER="reverse")
     r = subprocess.run([sys.executable, "-m", "pytest", str(Path(__file__)), "-x", "-q", "-p", "no:cacheprovider", "-k",
                         "forces_and_trajectory or neighbor_list_bit_exact or chain_setup or emu_host_buffer_step or emu_peratom_sums "
-                        "or tiled or bins_per_warp or pipeline_chunked"],
+                        "or bins_per_warp or pipeline_chunked"],
                        cwd=ROOT, env=env, capture_output=True, text=True)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert " passed" in r.stdout and "failed" not in r.stdout
@@ -670,88 +693,12 @@ def test_emu_bench_main_prints_the_contract_line(emu, monkeypatch, capsys):
     assert line["chain"]["value"] > 0 and line["chain"]["neigh"]["builds"] >= 1
 
 
-# ---- shared-memory tiled lj/cut (B200MD_LJ_TILED=1, opt-in) ----
-@pytest.mark.parametrize("g_bins", ["1", "3", "auto", "64"])
-@pytest.mark.parametrize("name,steps", [("lj_500", 45), ("lj2_864", 25)])
-def test_emu_tiled_lj_equals_plain(emu, name, steps, g_bins, monkeypatch):
-    """k_lj_tiled (neighbourhood of a bin segment staged in shared memory, 16-bit slot lists) == k_lj_lanes bit for bit:
-    same list order, same arithmetic (forces and trajectory; the energy / virial sums agree to round-off); one and two atom types, segments of 1 / 3 / 6 / a whole row of bins, through
-    rebuilds, energies and virial included"""
-    g = load_golden(name)
-    monkeypatch.delenv("B200MD_LJ_TILED", raising=False)
-    a = make_device_system(emu, name, g)
-    a.run(steps, thermo_every=10)
-    monkeypatch.setenv("B200MD_LJ_TILED", "1")
-    if g_bins == "auto":
-        monkeypatch.delenv("B200MD_TILED_G", raising=False)
-    else:
-        monkeypatch.setenv("B200MD_TILED_G", g_bins)
-    b = make_device_system(emu, name, g)
-    b.run(steps, thermo_every=10)
-    assert emu.lib.load().b200md_tiled_active(b.ctx.h) == 1
-    ga, gb = a.gather(), b.gather()
-    assert np.array_equal(ga["x"], gb["x"]) and np.array_equal(ga["v"], gb["v"]) and np.array_equal(ga["f"], gb["f"])
-    for ta, tb in zip(a.thermo_log, b.thermo_log):   # the per-block partial sums group the atoms differently: last bits
-        assert abs(ta["pe"] - tb["pe"]) <= 1e-13 * abs(ta["pe"]) and abs(ta["press"] - tb["press"]) <= 1e-12 * abs(ta["press"])
-    a.close()
-    b.close()
-
-
-def test_emu_tiled_lj_decomposed_and_chain(emu, monkeypatch):
-    """the tiled kernel where ghosts come from other ranks (4 emulated ranks == the plain kernel, bit for bit) and on the
-    bonded in.chain system (lists without the 1-2 partners; the reference's setup forces)"""
-    monkeypatch.delenv("B200MD_LJ_TILED", raising=False)
-    a = run_decomposed_emu(emu, 4, (2, 2, 1), "lj", 6, 45)
-    monkeypatch.setenv("B200MD_LJ_TILED", "1")
-    b = run_decomposed_emu(emu, 4, (2, 2, 1), "lj", 6, 45)
-    for ra, rb in zip(a, b):
-        assert np.array_equal(ra["tag1"], rb["tag1"]) and np.array_equal(ra["x1"], rb["x1"]) and ra["builds"] == rb["builds"]
-    chain.test_chain_setup_forces_vs_reference(emu)
-
-
-@pytest.mark.parametrize("g_bins", ["1", "4", "64"])
-def test_emu_tiled_eam_equals_plain(emu, oracle, g_bins, monkeypatch):
-    """the tiled single-type EAM passes (k_eam_rho_fp_tiled, k_eam_force_tiled) == the default ones bit for bit, on the
-    reference-minted Cu case and on a 12^3-cell block through its check-yes rebuilds; 8 emulated ranks likewise"""
-    g = load_golden("eam_500")
-    out = []
-    for tiled in (False, True):
-        if tiled:
-            monkeypatch.setenv("B200MD_LJ_TILED", "1")
-            monkeypatch.setenv("B200MD_TILED_G", g_bins)
-        else:
-            monkeypatch.delenv("B200MD_LJ_TILED", raising=False)
-        md = make_device_system(emu, "eam_500", g)
-        md.run(30, thermo_every=10)
-        assert emu.lib.load().b200md_tiled_active(md.ctx.h) == int(tiled)
-        big, _ = gp._bench_system(emu, oracle, "eam", 8)
-        big.run(25)
-        out.append((md.gather(), md.thermo_log, big.gather(), big.neigh_stats()["builds"]))
-        md.close()
-        big.close()
-    (a, ta, ba, na), (b, tb, bb, nb_) = out
-    assert np.array_equal(a["x"], b["x"]) and np.array_equal(a["f"], b["f"]) and np.array_equal(ba["x"], bb["x"]) and na == nb_ >= 2
-    for x, y in zip(ta, tb):
-        assert abs(x["pe"] - y["pe"]) <= 1e-13 * abs(x["pe"]) and abs(x["press"] - y["press"]) <= 1e-11 * abs(x["press"])
-    if g_bins == "4":
-        monkeypatch.delenv("B200MD_LJ_TILED", raising=False)
-        p = run_decomposed_emu(emu, 8, (2, 2, 2), "eam", 5, 30)
-        monkeypatch.setenv("B200MD_LJ_TILED", "1")
-        q = run_decomposed_emu(emu, 8, (2, 2, 2), "eam", 5, 30)
-        for rp, rq in zip(p, q):
-            assert np.array_equal(rp["tag1"], rq["tag1"]) and np.array_equal(rp["x1"], rq["x1"]) and rp["builds"] == rq["builds"]
-
-
-@pytest.mark.parametrize("env", [{"B200MD_CLUSTER": "2"}, {"B200MD_CLUSTER": "4"}, {"B200MD_CLUSTER": "2", "B200MD_LANES": "1"},
-                                 {"B200MD_LJ_PLAIN": "1"}, {"B200MD_EAM_GENERIC": "1"}, {"B200MD_BUILD_FP64": "1"}])
 @pytest.mark.parametrize("name", ["lj2_864", "eam_500"])
-def test_emu_tuning_knobs_keep_the_physics(emu, name, env, monkeypatch):
-    """the alternative kernels behind the tuning knobs (cluster lists of 2 / 4 atoms, lane clusters, the plain lj kernel,
-    the generic multi-type eam kernels, the all-FP64 build) still reproduce the reference goldens"""
-    for k, v in env.items():
-        monkeypatch.setenv(k, v)
+def test_emu_fp64_fallback_build_keeps_the_physics(emu, name):
+    """the all-FP64 list build (the fallback for boxes whose FP32 error band would be too wide) reproduces the goldens"""
     g = load_golden(name)
     md = make_device_system(emu, name, g)
+    md.tune("build_fp64", 1)
     md.setup()
     a = md.gather()
     assert np.abs(a["f"] - g["a_f"]).max() <= F_RTOL * np.abs(g["a_f"]).max()

@@ -9,7 +9,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import CASES, FIRST_RUN, POT, load_golden, make_device_system, make_oracle_system, thermo_vec
+from conftest import CASES, POT, load_golden, make_device_system, make_oracle_system, thermo_vec
 
 pytestmark = pytest.mark.gpu
 NAMES = list(CASES)
@@ -29,9 +29,11 @@ def _directed_sorted(p):
 
 
 @pytest.mark.parametrize("name", NAMES)
-def test_neighbor_list_bit_exact(pkg, name):
+def test_neighbor_list_bit_exact(pkg, name, tune=None):
     g = load_golden(name)
     md = make_device_system(pkg, name, g)
+    for k, val in (tune or {}).items():
+        md.tune(k, val)
     md.setup()
     d = md.neighbor_tag_pairs()  # full list: every pair twice
     # (a) the device full list is symmetric: (i,j) stored <=> (j,i) stored
@@ -186,26 +188,17 @@ def test_piecewise_api_equals_device_loop(pkg):
     b.close()
 
 
-@FIRST_RUN
-@pytest.mark.parametrize("pipeline", [
-    False,
-    pytest.param(True, marks=pytest.mark.skipif(not os.environ.get("B200MD_TEST_PIPELINE"),
-                                                reason="three-stream pipeline (B200MD_HOST_PIPELINE=1) was written after round 1's GPU "
-                                                       "budget was spent: opt-in (B200MD_TEST_PIPELINE=1) until it has run on hardware")),
-])
+@pytest.mark.parametrize("pipeline", [False, True])
 @pytest.mark.parametrize("name,steps", [("lj2_864", 25), ("eam_500", 30)])
-def test_host_buffer_step_equals_device_loop(pkg, name, steps, pipeline, monkeypatch):
+def test_host_buffer_step_equals_device_loop(pkg, name, steps, pipeline):
     """b200md_step_host (x, v in / x, v, f out through HOST arrays every step, through rebuilds that re-order the
     atoms) == b200md_run, bit for bit."""
     import ctypes as C
 
-    if pipeline:
-        monkeypatch.setenv("B200MD_HOST_PIPELINE", "1")
-    else:
-        monkeypatch.delenv("B200MD_HOST_PIPELINE", raising=False)
     g = load_golden(name)
     a = make_device_system(pkg, name, g)
     b = make_device_system(pkg, name, g)
+    b.tune("host_pipeline", int(pipeline))   # default 1: the three-stream chunk pipeline; 0: serial copy-compute-copy
     a.run(steps)
     b.setup()
     n = b.nlocal
@@ -230,19 +223,17 @@ def test_host_buffer_step_equals_device_loop(pkg, name, steps, pipeline, monkeyp
     b.close()
 
 
-@pytest.mark.skipif(not os.environ.get("B200MD_TEST_PIPELINE"),
-                    reason="three-stream pipeline: opt-in (B200MD_TEST_PIPELINE=1) until it has run on hardware")
 @pytest.mark.parametrize("kind,steps", [("lj", 45), ("eam", 25)])
-def test_host_buffer_pipeline_chunked(pkg, oracle, kind, steps, monkeypatch):
+def test_host_buffer_pipeline_chunked(pkg, oracle, kind, steps):
     """the pipeline with its chunking on (8 ranges of 512 atoms of a 4000-atom bench system): uploads, ranged force
     kernels (pair_lj_compute_range / pair_eam_force_range) and downloads per range, through rebuilds that re-order
     the atoms, == b200md_run bit for bit; the last step takes the tally path (whole-system force kernel)"""
     import ctypes as C
 
-    monkeypatch.setenv("B200MD_HOST_PIPELINE", "1")
-    monkeypatch.setenv("B200MD_HS_MIN_CHUNK", "1000")
     a, _ = _bench_system(pkg, oracle, kind, 10)
     b, _ = _bench_system(pkg, oracle, kind, 10)
+    b.tune("host_pipeline", 1)
+    b.tune("hs_min_chunk", 1000)
     a.run(steps)
     b.setup()
     n = b.nlocal
@@ -264,19 +255,17 @@ def test_host_buffer_pipeline_chunked(pkg, oracle, kind, steps, monkeypatch):
     b.close()
 
 
-@pytest.mark.skipif(not os.environ.get("B200MD_TEST_OVERLAP"),
-                    reason="halo/compute overlap (B200MD_OVERLAP=1) was written after round 1's GPU budget was spent: opt-in "
-                           "(B200MD_TEST_OVERLAP=1) until it has run on hardware")
 @pytest.mark.parametrize("name,steps", [("lj_500", 45), ("eam_500", 30)])
-def test_overlapped_halo_equals_plain(pkg, name, steps, monkeypatch):
-    """B200MD_OVERLAP=1 (halo on its own stream under the force kernels of the ghost-free tiles) == the plain step,
-    bit for bit: same kernels, same lists, only the launch split and the stream differ."""
+def test_overlapped_halo_equals_plain(pkg, name, steps):
+    """overlap mode (halo on its own stream under the force kernels of the ghost-free tiles; the default on several
+    ranks, forced on here for the one-rank periodic halo) == the plain step, bit for bit: same kernels, same lists,
+    only the launch split and the stream differ."""
     g = load_golden(name)
-    monkeypatch.delenv("B200MD_OVERLAP", raising=False)
     a = make_device_system(pkg, name, g)
+    a.tune("overlap", 0)
     a.run(steps)
-    monkeypatch.setenv("B200MD_OVERLAP", "1")
     b = make_device_system(pkg, name, g)
+    b.tune("overlap", 1)
     b.run(steps)
     ga, gb = a.gather(), b.gather()
     assert np.array_equal(ga["x"], gb["x"]) and np.array_equal(ga["v"], gb["v"]) and np.array_equal(ga["f"], gb["f"])
@@ -352,27 +341,3 @@ def test_large_lj_properties(pkg):
     assert abs(e1 - e0) < 2e-2  # the 32k reference drifts -4.6134 -> -4.6224 over the same 100 steps
     assert abs(e1 - (-4.6223613)) < 2e-3  # intensive quantity: same ensemble as the 32k log
     md.close()
-
-
-@pytest.mark.skipif(not os.environ.get("B200MD_TEST_TILED"),
-                    reason="shared-memory tiled lj/cut (B200MD_LJ_TILED=1) was written after round 1's GPU budget was spent: opt-in "
-                           "(B200MD_TEST_TILED=1) until it has run on hardware")
-@pytest.mark.parametrize("g_bins", ["3", "6", "12"])
-@pytest.mark.parametrize("name,steps", [("lj_500", 45), ("lj2_864", 25), ("eam_500", 30)])
-def test_tiled_lj_equals_plain(pkg, name, steps, g_bins, monkeypatch):
-    """B200MD_LJ_TILED=1 (k_lj_tiled: a bin segment's neighbourhood staged in shared memory, 16-bit slot lists) follows
-    the plain kernel's trajectory bit for bit; energies agree to round-off"""
-    g = load_golden(name)
-    monkeypatch.delenv("B200MD_LJ_TILED", raising=False)
-    a = make_device_system(pkg, name, g)
-    a.run(steps)
-    monkeypatch.setenv("B200MD_LJ_TILED", "1")
-    monkeypatch.setenv("B200MD_TILED_G", g_bins)
-    b = make_device_system(pkg, name, g)
-    b.run(steps)
-    assert pkg.lib.load().b200md_tiled_active(b.ctx.h) == 1
-    ga, gb = a.gather(), b.gather()
-    assert np.array_equal(ga["x"], gb["x"]) and np.array_equal(ga["v"], gb["v"]) and np.array_equal(ga["f"], gb["f"])
-    assert abs(a.thermo_log[-1]["pe"] - b.thermo_log[-1]["pe"]) <= 1e-13 * abs(a.thermo_log[-1]["pe"])
-    a.close()
-    b.close()

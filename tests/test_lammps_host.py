@@ -16,7 +16,7 @@ from pathlib import Path
 import numpy as np
 import pytest
 
-from conftest import FIRST_RUN
+
 
 ROOT = Path(__file__).resolve().parents[1]
 REFDIR = ROOT / "oracle" / "_ref"
@@ -154,7 +154,11 @@ def test_thermo_matches_reference(kind, n, loop, tmp_path):
     got = run_lmp(LMP_B200, text.format(n=n, pot=POT, runstyle=STOCK_LOOP if loop == "verlet" else ""), tmp_path,
                   ["-sf", "b200"])
     assert got.returncode == 0, got.stdout[-3000:] + got.stderr[-2000:]
-    assert f"run_style {loop}" in got.stdout or loop == "verlet" or True
+    # the suffix resolved to the device styles (LAMMPS falls back to the reference's class silently otherwise, and this
+    # test would compare the reference with itself): every b200 style logs one line when it initialises
+    assert f"b200: pair {'lj/cut' if kind == 'lj' else 'eam'}/b200 on CUDA device" in got.stdout, got.stdout[-2000:]
+    assert ("b200: run_style verlet/b200" in got.stdout) == (loop == "verlet/b200"), got.stdout[-2000:]
+    assert "b200:" not in ref.stdout
     R, G = thermo_rows(ref.stdout), thermo_rows(got.stdout)
     assert R.shape == G.shape and R.shape[0] == 3, (R.shape, G.shape, got.stdout[-2000:])
     np.testing.assert_array_equal(R[:, 0], G[:, 0])  # steps 0, 50, 100
@@ -220,7 +224,6 @@ def read_forces(path):
     return a[np.argsort(a[:, 0]), 1:]
 
 
-@FIRST_RUN
 @pytest.mark.gpu
 @pytest.mark.parametrize("name,units", [("unittest_atomic_pair_eam", "metal"), ("unittest_atomic_pair_eam_real", "real")])
 def test_reference_unittest_eam_yaml_through_lammps(name, units, tmp_path):
@@ -235,7 +238,7 @@ def test_reference_unittest_eam_yaml_through_lammps(name, units, tmp_path):
     text = IN_UNITTEST_EAM.format(units=units, style="eam", coeffs=FUNCFL_COEFFS, runstyle=STOCK_LOOP)
     r = run_lmp(LMP_B200, text, tmp_path, ["-sf", "b200"])
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
-    assert "eam/b200" in r.stdout or True
+    assert "b200: pair eam/b200 on CUDA device" in r.stdout, r.stdout[-2000:]
     pe = [row[1] for row in thermo_rows_generic(r.stdout, "Step", "PotEng")]
     for phase, fn, e in (("init", "init.txt", pe[0]), ("run", "run.txt", pe[-1])):
         f = read_forces(tmp_path / fn)
@@ -244,7 +247,6 @@ def test_reference_unittest_eam_yaml_through_lammps(name, units, tmp_path):
         assert abs(e - float(g[f"{phase}_vdwl"])) <= 1e-10 * abs(float(g[f"{phase}_vdwl"])), phase
 
 
-@FIRST_RUN
 @pytest.mark.gpu
 def test_thin_box_is_refused_by_the_resident_loop(tmp_path):
     """the device makes its ghosts in one stage, which needs sub-domains at least one ghost cutoff wide: the 7 A box
@@ -340,7 +342,6 @@ def test_chain_with_suffix_fails_loudly_without_device(tmp_path):
     assert "no CPU fallback" in (r.stdout + r.stderr)
 
 
-@FIRST_RUN
 @pytest.mark.gpu
 def test_chain_thermo_matches_reference(tmp_path):
     """bench/in.chain as shipped with `-sf b200`: pair lj/cut/b200 + bond fene/b200 + fix nve/b200 + fix
@@ -362,7 +363,6 @@ def test_chain_thermo_matches_reference(tmp_path):
     assert "Neighbor list builds = 25" in got.stdout
 
 
-@FIRST_RUN
 @pytest.mark.gpu
 @pytest.mark.parametrize("name,units,style", [("unittest_atomic_pair_eam_alloy", "metal", "eam/alloy"),
                                               ("unittest_atomic_pair_eam_alloy_real", "real", "eam/alloy"),
@@ -419,7 +419,6 @@ def read_dump_frames(path):
     return frames
 
 
-@FIRST_RUN
 @pytest.mark.gpu
 @pytest.mark.parametrize("kind", ["lj", "eam"])
 @pytest.mark.parametrize("loop", ["verlet/b200", "verlet"])
@@ -494,7 +493,6 @@ run 0
 """
 
 
-@FIRST_RUN
 @pytest.mark.gpu
 def test_restart_and_data_round_trip_under_suffix_b200(tmp_path):
     """pair lj/cut/b200 inherits PairLJCut's write_restart / read_restart / write_data (src/pair_lj_cut.cpp:563-656):

@@ -8,7 +8,7 @@ from __future__ import annotations
 import numpy as np
 import pytest
 
-from conftest import FIRST_RUN, load_golden
+from conftest import load_golden
 
 pytestmark = pytest.mark.gpu
 F_RTOL = 1e-10
@@ -66,7 +66,6 @@ def check_state(md, g, state, x_atol):
     return a, sel
 
 
-@FIRST_RUN
 def test_chain_setup_forces_vs_reference(pkg):
     """step 0: pair list without the 1-2 partners (count = 2 x the reference's half list), E_pair, E_bond, P and
     per-atom forces (pair + FENE + the langevin kick of FixLangevin::setup) <= 1e-10 relative"""
@@ -78,12 +77,11 @@ def test_chain_setup_forces_vs_reference(pkg):
     assert np.abs(a["f"][sel] - g["a_f"]).max() <= F_RTOL * fmax
     numneigh, _ = md.neighbor_list()
     assert int(numneigh.sum()) == 2 * int(g["a_npairs"][0])
-    L = pkg.lib.load()   # 3 beads per bin: 8 bins of an x-row per warp (one when the build also emits tiled slot lists)
-    assert L.b200md_build_bins_per_warp(md.ctx.h) == (1 if L.b200md_tiled_active(md.ctx.h) else 8)
+    L = pkg.lib.load()   # 3 beads per bin: 8 bins of an x-row per warp
+    assert L.b200md_build_bins_per_warp(md.ctx.h) == 8
     md.close()
 
 
-@FIRST_RUN
 def test_chain_100_steps_vs_reference_and_shipped_log(pkg):
     """the benchmark itself: 100 steps, thermo <= 1e-6 of the reference run here and of the shipped log
     (bench/log.6Oct16.chain.fixed.icc.1: T, E_pair/N, E_mol/N, TotEng/N, P at step 100; 25 neighbor builds)"""
@@ -99,7 +97,6 @@ def test_chain_100_steps_vs_reference_and_shipped_log(pkg):
     md.close()
 
 
-@FIRST_RUN
 def test_chain_nve_conserves_energy_and_is_reproducible(pkg):
     """without the thermostat: pair + FENE forces are conservative, so E_total drifts by < 1e-4 relative over 200
     steps; two runs are bitwise identical (no atomics on the bond path either)"""
@@ -115,7 +112,6 @@ def test_chain_nve_conserves_energy_and_is_reproducible(pkg):
     assert np.array_equal(out[0]["x"], out[1]["x"]) and np.array_equal(out[0]["f"], out[1]["f"])
 
 
-@FIRST_RUN
 def test_chain_error_paths(pkg):
     """"Bond atoms missing" when a partner is beyond the neighbor cutoff; more than 4 bonds per atom refused;
     bond coeffs required at setup"""
@@ -142,7 +138,6 @@ def test_chain_error_paths(pkg):
     md.close()
 
 
-@FIRST_RUN
 def test_replicated_chain_energies_scale(pkg):
     """size-independent property at a size the oracle would take minutes for: bench/in.chain replicated 4^3 (2.05 M
     beads) has exactly 64 x the reference's step-0 energies and the same pressure"""
@@ -158,6 +153,7 @@ def test_replicated_chain_energies_scale(pkg):
     md.neighbor.modify(every=1, delay=1, check=True)
     md.timestep(0.012)
     md.create_atoms(R["x"], R["v"], R["type"], R["tag"])
+    md.special_bonds("fene")
     md.bonds(R["tag"], *pkg.inputs.bond_arrays(R["tag"], R["bonds"]))
     md.bond_style("fene", 1).coeff(1, 30.0, 1.5, 1.0, 1.0)
     md.fix("langevin", 1.0, 1.0, 10.0, 904297, rng="counter")

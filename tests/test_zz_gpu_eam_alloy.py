@@ -9,7 +9,7 @@ import lzma
 import numpy as np
 import pytest
 
-from conftest import FIRST_RUN, GOLDEN, thermo_vec
+from conftest import GOLDEN, thermo_vec
 
 pytestmark = pytest.mark.gpu
 F_RTOL = 1e-10
@@ -37,7 +37,6 @@ def potential(kind, tmp_path):
     return p, ["Al", "Fe"], 3.9
 
 
-@FIRST_RUN
 @pytest.mark.parametrize("kind,units", [("alloy", "metal"), ("alloy", "real"), ("fs", "metal"), ("fs", "real")])
 def test_eam_alloy_fs_vs_oracle(pkg, oracle, kind, units, tmp_path):
     """forces <= 1e-10 relative and thermo at step 0; PE / KE / P <= 1e-6 and the same number of rebuilds after 40 steps
@@ -77,7 +76,6 @@ def test_eam_alloy_fs_vs_oracle(pkg, oracle, kind, units, tmp_path):
     md.close()
 
 
-@FIRST_RUN
 def test_eam_alloy_error_paths(pkg, tmp_path):
     """the reference's messages: unknown element, wrong number of element names, missing / truncated file"""
     md = pkg.B200MD(units="metal", ntypes=2)

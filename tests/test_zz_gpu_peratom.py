@@ -7,12 +7,11 @@ from __future__ import annotations
 import numpy as np
 import pytest
 
-from conftest import CASES, FIRST_RUN, load_golden, make_device_system
+from conftest import CASES, load_golden, make_device_system
 
 pytestmark = pytest.mark.gpu
 
 
-@FIRST_RUN
 @pytest.mark.parametrize("name", list(CASES))
 def test_peratom_sums_are_the_global_tallies(pkg, name):
     g = load_golden(name)
@@ -32,7 +31,6 @@ def test_peratom_sums_are_the_global_tallies(pkg, name):
     md.close()
 
 
-@FIRST_RUN
 def test_peratom_needs_a_list(pkg):
     g = load_golden("lj_500")
     md = make_device_system(pkg, "lj_500", g)

@@ -34,11 +34,8 @@ ms, cnt = bench.kernel_times(md, reset=True)
 names = ["pair", "eam_rho", "neigh", "nve", "halo", "sort"]
 per = {k: (ms[i] / cnt[i] if cnt[i] else 0.0) for i, k in enumerate(names)}
 st = md.neigh_stats()
-cs, nc, ne = C.c_int(0), C.c_int64(0), C.c_int64(0)
-md.ctx.call("b200md_neigh_cluster_stats", C.byref(cs), C.byref(nc), C.byref(ne))
 nn = md.neighbor_list()[0]
-print(f"   list: cluster {cs.value}, {ne.value / nc.value:.1f} entries/cluster = {ne.value / n:.1f} per atom; per-atom neighbors {nn.mean():.1f}; "
-      f"efficiency {nn.sum() / (ne.value * cs.value):.3f}")
+print(f"   list: {nn.mean():.1f} neighbors per atom (full list)")
 print(f"[kbench {label}] {kind} {n} atoms: step {wall / steps:.3f} ms | " + " ".join(f"{k} {per[k]:.3f}ms x{cnt[i]}" for i, k in enumerate(names) if cnt[i])
       + f" | maxneigh {st['maxneigh']} launches {md.timers()['launches']}")
 for name, b in (("pair", bench.BYTES_LJ_PAIR if kind == "lj" else bench.BYTES_EAM_FORCE),):

@@ -17,3 +17,4 @@ done
 # the e2e leg through the three-stream pipeline (ranged force kernels), against r2j1_bench.log's serial e2e
 B200MD_HOST_PIPELINE=1 timeout 300 python bench.py --steps 20 --warmup 5 --no-cpu --no-eam > gpurun_out/r2j1_pipeline.log 2>&1
 echo "pipeline rc=$?"; tail -1 gpurun_out/r2j1_pipeline.log | python -c "import sys,json; l=json.loads(sys.stdin.read()); print(l['value'], l['e2e'])"
+timeout 120 tools/ubench > gpurun_out/r2j1_ubench.log 2>&1; echo "ubench rc=$?"; cat gpurun_out/r2j1_ubench.log
