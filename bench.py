@@ -39,6 +39,8 @@ NBAR_LJ, NBAR_EAM = 37.59, 37.74
 BYTES_LJ_PAIR = 52 + 4 * NBAR_LJ            # 202.4 B / atom / launch of the lj/cut force kernel
 BYTES_EAM_RHO = 28 + 4 * NBAR_EAM + 8 + 16  # pass A + B fused: x_i,type + ids + rho write + fp
 BYTES_EAM_FORCE = 28 + 8 + 4 * NBAR_EAM + 24
+BYTES_NEIGH_CHAIN = 28 + 4 * 4.87 + 4      # neighbor build of in.chain (4.87 stored half-list neighbors per bead), per build
+BYTES_CHAIN_PAIR = 52 + 4 * 4.87            # its lj/cut 1.12 force kernel
 BYTES_LJ_STEP = 394.0                       # pair 202 + nve 192 (no rebuild)
 BYTES_EAM_STEP = 606.0
 
@@ -52,9 +54,10 @@ def parse_args():
     ap.add_argument("--cells", type=int, default=160, help="fcc cells per GPU per dimension for LJ (160 -> 16.384 M atoms)")
     ap.add_argument("--eam-cells", type=int, default=100, help="fcc cells per GPU per dimension for EAM (100 -> 4 M atoms)")
     ap.add_argument("--no-eam", action="store_true")
-    ap.add_argument("--chain", type=int, default=0, metavar="R",
-                    help="also run bench/in.chain replicated R x R x R (32 000 R^3 beads; one GPU only; opt-in: the bonded "
-                         "path has not run on hardware yet)")
+    ap.add_argument("--chain", type=int, default=8, metavar="R",
+                    help="bench/in.chain replicated R x R x R (32 000 R^3 beads; BASELINE configs[2]; one GPU only; 0 = skip)")
+    ap.add_argument("--no-parity", action="store_true", help="skip the parity legs (reference thermo at the quoted sizes)")
+    ap.add_argument("--parity-steps", type=int, default=0, help="steps of the full-size parity leg (default min(W+K, 50))")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -110,6 +113,15 @@ WORK = {
 }
 
 
+def workload_config(cells, ngpus):
+    """config of the headline line -- the SAME text from both arms (the CPU arm's bounded sample is described in its
+    cpu_baseline.sample, not here)"""
+    per = 4 * cells ** 3
+    return {"workload": f"LJ melt {per} atoms per GPU ({per * ngpus} total; bench/in.lj scaled, fcc 0.8442, T=1.44 loop geom, "
+                        f"lj/cut 2.5, skin 0.3, rebuild every 20 check no, fix nve, dt 0.005); inputs larger than L2",
+            "grid": list(proc_grid(ngpus))}
+
+
 def make_atoms(pkg, kind, cells, grid, loc, allsum):
     """This rank's block of the global fcc lattice (cells^3 cells per rank, grid ranks): positions, tags,
     velocities exactly as `create_atoms` + `velocity all create T seed loop geom` give them (inputs.py)."""
@@ -159,25 +171,28 @@ def kernel_times(md, reset=False):
 # ---------------------------------------------------------------------------------------------------------
 def time_resident(torch, dist, md, steps, warmup, device, nranks):
     """W untimed + K timed Verlet steps on device-resident atoms (b200md_run), CUDA events on the library's own
-    stream, barrier + synchronize on both sides, max over ranks.  Returns ms for the K steps."""
+    stream, barrier + synchronize on both sides, max over ranks.  Returns (ms for the K steps, kernel launches in them)."""
     ext = torch.cuda.ExternalStream(md.ctx.L.b200md_stream(md.ctx.h), device=device)
-    md.ctx.call("b200md_run", warmup, md.dt, 0)
+    if warmup > 0:
+        md.ctx.call("b200md_run", warmup, md.dt, 0)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize(device)
     if nranks > 1:
         dist.barrier()
+    launches0 = md.timers()["launches"]
     with torch.cuda.stream(ext):
         e0.record()
     md.ctx.call("b200md_run", steps, md.dt, 0)
     with torch.cuda.stream(ext):
         e1.record()
     torch.cuda.synchronize(device)
+    launches = md.timers()["launches"] - launches0   # this library's kernel launches INSIDE the timed region
     if nranks > 1:
         dist.barrier()
     ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
     if nranks > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    return float(ms.item())
+    return float(ms.item()), int(launches)
 
 
 def time_host_buffers(torch, dist, md, steps, warmup, device, nranks):
@@ -229,22 +244,28 @@ def run_workload(torch, dist, pkg, kind, cells, args, device, nranks, rank, nccl
     md.setup()
     out = dict(natoms=natoms_total, atoms_per_gpu=md.nlocal, thermo0=md.thermo_log[-1])
 
+    # ---- parity leg (untimed, before the warm-up): thermo at step 0 and after P steps against the unmodified reference
+    # on the SAME input at the SAME size (N = 1), or against closed forms of the perfect lattice (any N)
+    if not args.no_parity:
+        psteps = args.parity_steps or min(args.steps + args.warmup, 50)
+        md.run(psteps)
+        out["parity_run"] = dict(steps=psteps, thermo=md.thermo_log[-1], builds=md.neigh_stats()["builds"])
+
     # ---- timed region: device-resident steps ---------------------------------------------------------
     md.timers(reset=True)
     clocks = Clocks(device)
     if rank == 0:
         clocks.start()
-    ms = time_resident(torch, dist, md, args.steps, args.warmup, device, nranks)
+    ms, launches = time_resident(torch, dist, md, args.steps, args.warmup, device, nranks)
     out["clocks"] = clocks.stop() if rank == 0 else None
-    launches_total = md.timers()["launches"]
     out["ms"] = ms
-    out["launches"] = int(round(launches_total * args.steps / (args.steps + args.warmup)))
+    out["launches"] = launches
     out["value"] = natoms_total * args.steps / (ms * 1e-3) / 1e6
 
     # ---- second pass with per-kernel CUDA events (no host syncs added) for the roofline ---------------
     md.ctx.call("b200md_profile", 1)
     kernel_times(md, reset=True)
-    ms2 = time_resident(torch, dist, md, args.steps, 0, device, nranks)
+    ms2, _ = time_resident(torch, dist, md, args.steps, 0, device, nranks)
     kms, kcnt = kernel_times(md, reset=True)
     md.ctx.call("b200md_profile", 0)
     out["ms_profiled_pass"] = ms2
@@ -281,12 +302,12 @@ def run_chain(torch, dist, pkg, r, args, device):
     natoms = len(R["tag"])
     del R
     md.setup()
-    out = dict(natoms=natoms, thermo0=md.thermo_log[-1])
+    out = dict(natoms=natoms, atoms_per_gpu=natoms, thermo0=md.thermo_log[-1], builds0=md.neigh_stats()["builds"])
     md.timers(reset=True)
-    ms = time_resident(torch, dist, md, args.steps, args.warmup, device, 1)
+    ms, launches = time_resident(torch, dist, md, args.steps, args.warmup, device, 1)
     out["ms"] = ms
     out["value"] = natoms * args.steps / (ms * 1e-3) / 1e6
-    out["launches"] = int(round(md.timers()["launches"] * args.steps / (args.steps + args.warmup)))
+    out["launches"] = launches
     md.ctx.call("b200md_profile", 1)
     kernel_times(md, reset=True)
     time_resident(torch, dist, md, args.steps, 0, device, 1)
@@ -297,6 +318,36 @@ def run_chain(torch, dist, pkg, r, args, device):
     out["neigh"] = md.neigh_stats()
     md.close()
     return out
+
+
+def run_decomposed_parity(torch, dist, pkg, kind, device, nranks, rank, nccl_id, grid, loc, allsum, steps=60, cells=None):
+    """N > 1: a small decomposed system (24^3 fcc cells per rank for lj, 20^3 for eam) run for `steps` steps before the
+    timed workload -- migration, borders, halo and the rebuild votes all exercised -- and compared on rank 0 with the
+    unmodified reference run on the host on the same global box: thermo at step 0 and `steps`, the rebuild count, and
+    the atoms themselves (every tag 1..N owned exactly once: count, sum and a weighted sum of the owned tags)."""
+    cells = cells or (24 if kind == "lj" else 20)
+    x, v, tag, box, natoms = make_atoms(pkg, kind, cells, grid, loc, allsum)
+    md = make_system(pkg, kind, device, nranks, rank, nccl_id(), grid)
+    md.box([0, 0, 0], box)
+    md.create_atoms(x, v, np.ones(len(x), dtype=np.int32), tag, natoms_total=natoms)
+    md.setup()
+    t0 = md.thermo_log[-1]
+    md.run(steps)
+    t1 = md.thermo_log[-1]
+    builds = md.neigh_stats()["builds"]
+    tg = md.gather(sort_by_tag=False)["tag"].astype(np.int64)
+    chk = allsum(np.array([len(tg), tg.sum(), (tg * (tg % 4099)).sum()], dtype=np.float64))   # all exact below 2^53
+    nmig = md.nlocal != len(x)
+    md.close()
+    allt = np.arange(1, natoms + 1, dtype=np.int64)
+    tags_ok = bool(chk[0] == natoms and chk[1] == allt.sum() and chk[2] == (allt * (allt % 4099)).sum())
+    if rank != 0:
+        return None
+    dims = tuple(cells * g for g in grid)
+    ref = ref_thermo(kind, dims, steps, os.cpu_count() or 1)
+    return parity_block(f"oracle/_ref/lmp_ref (unmodified reference, OPENMP styles) on the host, same {dims[0]}x{dims[1]}x{dims[2]}-cell box, "
+                        f"{nranks} ranks on the device side", t0, t1, builds, ref,
+                        extra={"tags": {"owned_exactly_once": tags_ok, "count": int(chk[0])}, "rank0_atom_count_changed": bool(nmig)})
 
 
 def run_e2e(torch, dist, md, out, args, device, nranks):
@@ -338,11 +389,11 @@ class Watchdog:
 # ---------------------------------------------------------------------------------------------------------
 # CPU arm: the unmodified reference (oracle/_ref/lmp_ref, OPENMP package) or, failing that, the oracle port
 # ---------------------------------------------------------------------------------------------------------
-REF_IN = {
+REF_HEAD = {
     "lj": """units lj
 atom_style atomic
 lattice fcc 0.8442
-region box block 0 {n} 0 {n} 0 {n}
+region box block 0 {nx} 0 {ny} 0 {nz}
 create_box 1 box
 create_atoms 1 box
 mass 1 1.0
@@ -352,14 +403,11 @@ pair_coeff 1 1 1.0 1.0 2.5
 neighbor 0.3 bin
 neigh_modify delay 0 every 20 check no
 fix 1 all nve
-thermo 0
-run {w}
-run {k}
 """,
     "eam": """units metal
 atom_style atomic
 lattice fcc 3.615
-region box block 0 {n} 0 {n} 0 {n}
+region box block 0 {nx} 0 {ny} 0 {nz}
 create_box 1 box
 create_atoms 1 box
 pair_style eam
@@ -369,29 +417,124 @@ neighbor 1.0 bin
 neigh_modify every 1 delay 5 check yes
 fix 1 all nve
 timestep 0.005
-thermo 0
-run {w}
-run {k}
+""",
+    # bench/in.chain on the data file regenerated from tests/golden/chain_32k.npz, replicated like in.chain.scaled
+    "chain": """units lj
+atom_style bond
+special_bonds fene
+read_data data.chain
+replicate {nx} {ny} {nz}
+neighbor 0.4 bin
+neigh_modify every 1 delay 1
+bond_style fene
+bond_coeff 1 30.0 1.5 1.0 1.0
+pair_style lj/cut 1.12
+pair_modify shift yes
+pair_coeff 1 1 1.0 1.0 1.12
+fix 1 all nve
+fix 2 all langevin 1.0 1.0 10.0 904297
+timestep 0.012
 """,
 }
+REF_TIMED = "thermo 0\nrun {w}\nrun {k}\n"
+# totals, 15 digits: what the parity legs compare (src/thermo.cpp:182-189 keywords; norm no = extensive values)
+REF_THERMO = "thermo_style custom step temp pe ke press evdwl ebond\nthermo_modify format float %.15g norm no\nthermo {t}\nrun {p}\n"
 
 
-def ref_run(kind, n, steps, warmup, threads):
-    """One launch of the unmodified reference on an n^3-cell sample: `run W` then `run K`; returns
-    (Matom-steps/s of the K-step loop as Finish prints it, loop seconds)."""
+def write_data_chain(g, path):
+    """tests/golden/chain_32k.npz (the reference's own read_data of bench/data.chain, tests/golden/make_chain_golden.py)
+    back into a data file, 17 significant digits -- /root/reference does not exist on the GPU box"""
+    n, nb = len(g["in_tag"]), len(g["in_bonds"])
+    lines = ["LAMMPS data file (tests/golden/chain_32k.npz <- bench/data.chain)", "", f"{n} atoms", f"{nb} bonds", "",
+             "1 atom types", "1 bond types", ""]
+    for k, ax in enumerate("xyz"):
+        lines.append(f"{g['in_boxlo'][k]:.17g} {g['in_boxhi'][k]:.17g} {ax}lo {ax}hi")
+    lines += ["", "Masses", "", "1 1.0", "", "Atoms # bond", ""]
+    X, IM, T, M, TY = g["in_x"], g["in_image"], g["in_tag"], g["in_mol"], g["in_type"]
+    lines += [f"{T[i]} {M[i]} {TY[i]} {X[i][0]:.17g} {X[i][1]:.17g} {X[i][2]:.17g} {IM[i][0]} {IM[i][1]} {IM[i][2]}" for i in range(n)]
+    lines += ["", "Velocities", ""]
+    V = g["in_v"]
+    lines += [f"{T[i]} {V[i][0]:.17g} {V[i][1]:.17g} {V[i][2]:.17g}" for i in range(n)]
+    lines += ["", "Bonds", ""]
+    lines += [f"{k + 1} {t} {a} {b}" for k, (t, a, b) in enumerate(g["in_bonds"])]
+    Path(path).write_text("\n".join(lines) + "\n")
+
+
+def ref_launch(kind, dims, tail, threads):
+    """one launch of the UNMODIFIED reference (oracle/_ref/lmp_ref, OPENMP styles when threads > 1) on the workload
+    `kind` with dims = (nx, ny, nz) fcc cells (lj, eam) or replication factors (chain); returns its stdout"""
     import oracle
 
     with tempfile.TemporaryDirectory() as tmp:
+        if kind == "chain":
+            write_data_chain(dict(np.load(ROOT / "tests" / "golden" / "chain_32k.npz")), Path(tmp) / "data.chain")
         inp = Path(tmp) / "in.bench"
-        inp.write_text(REF_IN[kind].format(n=n, w=warmup, k=steps, pot=POT))
+        inp.write_text(REF_HEAD[kind].format(nx=dims[0], ny=dims[1], nz=dims[2], pot=POT) + tail)
         cmd = [str(oracle.LMP_REF), "-in", str(inp), "-log", "none", "-echo", "none"]
         if threads > 1:
             cmd += ["-sf", "omp", "-pk", "omp", str(threads)]
         env = dict(os.environ, OMP_NUM_THREADS=str(threads), OMP_PROC_BIND="true")
-        txt = subprocess.run(cmd, cwd=tmp, env=env, capture_output=True, text=True, check=True).stdout
+        return subprocess.run(cmd, cwd=tmp, env=env, capture_output=True, text=True, check=True).stdout
+
+
+def ref_run(kind, n, steps, warmup, threads):
+    """timing launch on an n^3 sample: `run W` then `run K`; returns (Matom-steps/s of the K-step loop as Finish prints
+    it, loop seconds)"""
+    txt = ref_launch(kind, (n, n, n), REF_TIMED.format(w=warmup, k=steps), threads)
     loops = re.findall(r"Loop time of ([0-9.eE+-]+) on \d+ procs for (\d+) steps with (\d+) atoms", txt)
     sec, st, na = loops[-1]
     return int(na) * int(st) / float(sec) / 1e6, float(sec)
+
+
+def ref_thermo(kind, dims, steps, threads):
+    """parity launch: the reference's own thermo (totals, 15 digits) at step 0 and at step `steps`, its neighbor-build
+    count and atom count, on exactly the GPU arm's input"""
+    txt = ref_launch(kind, dims, REF_THERMO.format(t=max(1, steps), p=steps), threads)
+    rows, on = [], False
+    for line in txt.splitlines():
+        t = line.split()
+        if t[:2] == ["Step", "Temp"]:
+            on = True
+            continue
+        if on:
+            try:
+                rows.append([float(v) for v in t])
+            except ValueError:
+                on = False
+    keys = ("step", "temp", "pe", "ke", "press", "evdwl", "ebond")
+    m = re.search(r"Loop time of ([0-9.eE+-]+) on \d+ procs for (\d+) steps with (\d+) atoms", txt)
+    b = re.search(r"Neighbor list builds = (\d+)", txt)
+    d = re.search(r"Dangerous builds = (\d+)", txt)
+    return dict(step0=dict(zip(keys, rows[0])), last=dict(zip(keys, rows[-1])), builds=int(b.group(1)) if b else None,
+                dangerous=int(d.group(1)) if d else None, natoms=int(m.group(3)) if m else None,
+                loop_s=float(m.group(1)) if m else None)
+
+
+PARITY_TOL = 1e-6   # north_star: thermo (PE, KE, pressure) within 1e-6 relative of the reference's CPU path
+
+
+def parity_block(label, got0, got1, builds, ref, extra=None):
+    """relative errors of the device thermo against the reference's at step 0 and at the last parity step"""
+    def rel(g, r):
+        return abs(g - r) / max(abs(r), 1e-300)
+
+    out = {"against": label, "steps": int(ref["last"]["step"]), "natoms": ref["natoms"], "tolerance": PARITY_TOL}
+    worst = 0.0
+    for name, g in (("step0", got0), ("last", got1)):
+        r = ref[name]
+        e = {k: rel(g[k], r[k]) for k in ("pe", "ke", "press")}
+        if "ebond" in g:
+            e["ebond"] = rel(g["ebond"], r["ebond"])
+        out[name] = e
+        worst = max(worst, *e.values())
+    out["pe"], out["ke"], out["press"] = (max(out["step0"][k], out["last"][k]) for k in ("pe", "ke", "press"))
+    out["builds"] = {"b200": int(builds), "reference": ref["builds"], "equal": int(builds) == ref["builds"]}
+    out["reference_thermo_last"] = {k: ref["last"][k] for k in ("pe", "ke", "press")}
+    out["b200_thermo_last"] = {k: float(got1[k]) for k in ("pe", "ke", "press")}
+    out["ok"] = bool(worst <= PARITY_TOL and out["builds"]["equal"])
+    if extra:
+        out.update(extra)
+    return out
 
 
 def port_run(kind, n, steps, warmup):
@@ -408,23 +551,36 @@ def port_run(kind, n, steps, warmup):
 
 
 def cpu_measure(kind, steps, warmup, budget_s, cells_cap):
-    """Size an n^3-cell sample of the workload so that W+K steps take about `budget_s` on this host, run it."""
+    """Size an n^3 sample of the workload (fcc cells for lj / eam, replicas of the 32 000-bead melt for chain) so that
+    W+K steps take about `budget_s` on this host, run it."""
     import oracle
 
     cores = os.cpu_count() or 1
     have_ref = oracle.ref_available()
+    per_cell = 32000 if kind == "chain" else 4
     if have_ref:
-        rate, _ = ref_run(kind, 20, 10, 2, cores)  # calibration: the shipped 32k case, 10 steps
+        # calibration on the shipped 32k case, 10 steps: all host threads (OPENMP styles) against one thread -- the
+        # reference arm gets whichever is faster here (in.chain's many short parallel regions can lose to one thread)
+        n0 = 1 if kind == "chain" else 20
+        rate, _ = ref_run(kind, n0, 10, 2, cores)
+        if cores > 1:
+            rate1, _ = ref_run(kind, n0, 10, 2, 1)
+            if rate1 > rate:
+                rate, cores = rate1, 1
         kindname = "reference"
+    elif kind == "chain":
+        return None   # the scalar port of in.chain is a parity tool, not a timing baseline
     else:
         oracle.build()
         rate, _ = port_run(kind, 10, 5, 1)
         cores, kindname = 1, "port"
     atoms = rate * 1e6 * budget_s / max(1, steps + warmup)
-    n = int(max(10, min(cells_cap, round((atoms / 4) ** (1 / 3)))))
+    n = int(max(1 if kind == "chain" else 10, min(cells_cap, round((atoms / per_cell) ** (1 / 3)))))
     val, sec = ref_run(kind, n, steps, warmup, cores) if have_ref else port_run(kind, n, steps, warmup)
-    sample = (f"{'bench/in.' + kind} scaled to {n}^3 fcc cells = {4 * n ** 3} atoms, {steps} steps after {warmup} warm-up, "
-              + (f"oracle/_ref/lmp_ref -sf omp -pk omp {cores}" if have_ref else "oracle/oracle.c port, 1 thread")
+    what = f"bench/in.chain replicated {n}^3 = {per_cell * n ** 3} beads" if kind == "chain" else f"bench/in.{kind} scaled to {n}^3 fcc cells = {4 * n ** 3} atoms"
+    sample = (f"{what}, {steps} steps after {warmup} warm-up, "
+              + ((f"oracle/_ref/lmp_ref -sf omp -pk omp {cores}" if cores > 1 else "oracle/_ref/lmp_ref, 1 thread (faster than the OPENMP styles "
+                  "on this host for this input)") if have_ref else "oracle/oracle.c port, 1 thread")
               + f", loop time {sec:.2f} s")
     return dict(value=val, unit="Matom-steps/s", cores=cores, kind=kindname, sample=sample)
 
@@ -438,8 +594,7 @@ def main_reference(args, rank):
     line = {"impl": "reference", "metric": "Matom-steps/s (LJ melt, bench/in.lj scaled)", "value": cb["value"], "unit": "Matom-steps/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"LJ melt 16.384 M atoms per GPU (bench/in.lj -var x 8 -var y 8 -var z 8), rc=2.5, skin 0.3, "
-                                   f"rebuild every 20; CPU arm timed on a bounded sample: {cb['sample']}"},
+            "config": workload_config(args.cells, args.gpus),
             "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": "Matom-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     if not args.no_eam:
@@ -485,6 +640,21 @@ def main():
             dist.all_reduce(t)
             return t.cpu().numpy()
 
+    have_ref = False
+    if rank == 0 and not args.no_parity:
+        import oracle  # the checker: only the parity / cpu_baseline legs touch it
+
+        have_ref = oracle.ref_available()
+    # ---- N > 1: decomposed parity on a small system first (the driver's pytest box has one GPU) ----
+    parity_small = {}
+    if world > 1 and not args.no_parity:
+        for kind in ("lj",) if args.no_eam else ("lj", "eam"):
+            try:
+                r = run_decomposed_parity(torch, dist, pkg, kind, local, world, rank, nccl_id, grid, loc, allsum) if (have_ref or rank != 0) else None
+            except Exception as e:  # noqa: BLE001
+                r = {"error": repr(e), "ok": False}
+            parity_small[kind] = r
+
     lj, md_lj = run_workload(torch, dist, pkg, "lj", args.cells, args, local, world, rank, nccl_id, grid, loc, allsum)
     eam, md_eam = None, None
     if not args.no_eam:
@@ -494,8 +664,55 @@ def main():
     if args.chain > 0 and world == 1:
         try:
             chain = run_chain(torch, dist, pkg, args.chain, args, local)
-        except Exception as e:  # noqa: BLE001  (opt-in extra: never lose the headline line over it)
+        except Exception as e:  # noqa: BLE001  (never lose the headline line over the third config)
             chain = {"error": repr(e)}
+
+    # ---- parity at the quoted sizes: the reference's own thermo on the same input (rank 0, host cores) ----
+    def lattice_check(w, kind):
+        """size-independent step-0 facts of the perfect fcc lattice: potential energy per atom equals the 32 000-atom
+        reference value (BASELINE.md, 15 digits) and the temperature is the `velocity create` target exactly"""
+        pe_atom = {"lj": -6.77336805323422, "eam": -113280.000077752 / 32000.0}[kind]
+        t_target = {"lj": 1.44, "eam": 1600.0}[kind]
+        t0 = w["thermo0"]
+        return {"pe_per_atom_rel": abs(t0["pe"] / w["natoms"] - pe_atom) / abs(pe_atom), "temp_rel": abs(t0["temp"] - t_target) / t_target,
+                "natoms": w["natoms"]}
+
+    parity = {}
+    if rank == 0 and not args.no_parity:
+        cores = os.cpu_count() or 1
+        for kind, w, cells in (("lj", lj, args.cells), ("eam", eam, args.eam_cells)):
+            if w is None:
+                continue
+            blk = {"lattice_step0": lattice_check(w, kind)}
+            if world == 1 and have_ref and "parity_run" in w:
+                try:
+                    pr = w["parity_run"]
+                    ref = ref_thermo(kind, (cells,) * 3, pr["steps"], cores)
+                    blk.update(parity_block(f"oracle/_ref/lmp_ref (unmodified reference, OPENMP styles, {cores} threads) on the same "
+                                            f"{cells}^3-cell input = {w['natoms']} atoms", w["thermo0"], pr["thermo"], pr["builds"], ref))
+                except Exception as e:  # noqa: BLE001
+                    blk.update({"error": repr(e), "ok": False})
+            elif world > 1:
+                small = parity_small.get(kind)
+                if small is not None:
+                    blk.update(small)
+                blk["note"] = ("full size: lattice_step0 only (the reference cannot run the %d-atom box in bench time); decomposed parity "
+                               "on the small system above" % w["natoms"])
+            else:
+                blk["note"] = "oracle/_ref/lmp_ref not available on this box"
+            if "ok" in blk:
+                blk["ok"] = bool(blk["ok"] and blk["lattice_step0"]["pe_per_atom_rel"] <= PARITY_TOL)
+            parity[kind] = blk
+        if chain is not None and "error" not in chain and have_ref:
+            try:   # the thermostat generators differ after step 0 (counter-based on the device): setup state only
+                ref = ref_thermo("chain", (args.chain,) * 3, 0, cores)
+                t0 = dict(chain["thermo0"])
+                parity["chain"] = parity_block(f"oracle/_ref/lmp_ref on bench/data.chain replicated {args.chain}^3, step 0 (setup forces: pair + "
+                                               f"FENE; later steps differ by the thermostat's random stream)", t0, t0, 0, ref)
+                parity["chain"]["builds"] = None
+                parity["chain"]["ok"] = bool(max(parity["chain"]["step0"].values()) <= PARITY_TOL)
+            except Exception as e:  # noqa: BLE001
+                parity["chain"] = {"error": repr(e), "ok": False}
 
     def emit(e2e_error=None):
         if rank != 0:
@@ -530,16 +747,17 @@ def main():
         line = {"metric": "Matom-steps/s (LJ melt, bench/in.lj scaled)", "value": lj["value"], "unit": "Matom-steps/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": lj["ms"] / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": f"LJ melt {lj['atoms_per_gpu']} atoms per GPU ({lj['natoms']} total; bench/in.lj scaled, fcc 0.8442, "
-                                       f"T=1.44 loop geom, lj/cut 2.5, skin 0.3, rebuild every 20 check no, fix nve, dt 0.005)",
-                           "grid": list(grid), "l2": "inputs larger than L2 (per-GPU working set %.1f GB)" % lj["mem_gb"]},
-                "clocks": lj["clocks"], "gpu_launches": lj["launches"],
+                "config": workload_config(args.cells, world),
+                "working_set_gb": lj["mem_gb"], "clocks": lj["clocks"], "gpu_launches": lj["launches"],
                 "roofline": roof(lj, "pair", BYTES_LJ_PAIR, "pair_lj"),
                 "step_roofline": {"algorithmic_bytes_per_atom_step": BYTES_LJ_STEP,
                                   "frac_of_hbm_peak": BYTES_LJ_STEP * lj["atoms_per_gpu"] / (lj["ms"] / args.steps * 1e-3) / 1e9 / peak},
                 "kernel_ms": lj["kernel_ms"], "ms_profiled_pass": lj["ms_profiled_pass"],
                 "thermo": {"step0": lj["thermo0"], "last": lj["thermo1"]}, "neigh": lj["neigh"], "nghost": lj["nghost"]}
         line["e2e"] = lj.get("e2e")
+        if parity:
+            line["parity"] = parity.get("lj")
+            line["parity_all_ok"] = bool(all(v.get("ok", True) for v in parity.values()))
         if e2e_error:
             line["e2e_error"] = e2e_error
         if eam is not None:
@@ -548,17 +766,21 @@ def main():
                            "roofline": roof(eam, "pair", BYTES_EAM_FORCE, "pair_eam"), "roofline_rho": roof(eam, "eam_rho", BYTES_EAM_RHO, "eam_rho"),
                            "step_frac_of_hbm_peak": BYTES_EAM_STEP * eam["atoms_per_gpu"] / (eam["ms"] / args.steps * 1e-3) / 1e9 / peak,
                            "kernel_ms": eam["kernel_ms"], "gpu_launches": eam["launches"], "clocks": eam["clocks"],
-                           "thermo": {"step0": eam["thermo0"], "last": eam["thermo1"]}, "neigh": eam["neigh"], "e2e": eam.get("e2e")}
+                           "thermo": {"step0": eam["thermo0"], "last": eam["thermo1"]}, "neigh": eam["neigh"], "e2e": eam.get("e2e"),
+                           "parity": parity.get("eam")}
         if chain is not None:
             line["chain"] = chain if "error" in chain else {
                 "value": chain["value"], "unit": "Matom-steps/s", "ms_per_step": chain["ms"] / args.steps,
                 "workload": f"bench/in.chain replicated {args.chain}^3 = {chain['natoms']} beads on one GPU, counter-based thermostat",
                 "kernel_ms": chain["kernel_ms"], "gpu_launches": chain["launches"], "neigh": chain["neigh"],
-                "thermo": {"step0": chain["thermo0"], "last": chain["thermo1"]}}
+                "roofline": roof(chain, "neigh", BYTES_NEIGH_CHAIN), "roofline_pair": roof(chain, "pair+bond", BYTES_CHAIN_PAIR),
+                "thermo": {"step0": chain["thermo0"], "last": chain["thermo1"]}, "parity": parity.get("chain")}
         if world == 1 and not args.no_cpu and not e2e_error:
             line["cpu_baseline"] = cpu_measure("lj", 100, 10, budget_s=20.0, cells_cap=args.cells)
             if eam is not None:
                 line["eam"]["cpu_baseline"] = cpu_measure("eam", 100, 10, budget_s=15.0, cells_cap=args.eam_cells)
+            if chain is not None and "error" not in chain:
+                line["chain"]["cpu_baseline"] = cpu_measure("chain", 100, 10, budget_s=15.0, cells_cap=args.chain)
 
         def clean(o):
             if isinstance(o, dict):

@@ -345,6 +345,37 @@ def test_emu_decomposed_overlap_equals_plain(emu, kind, world, grid, cells, step
         assert np.array_equal(ra["thermo1"], rb["thermo1"]) and ra["builds"] == rb["builds"]
 
 
+@pytest.mark.parametrize("kind,world,grid", [("lj", 2, (2, 1, 1)), ("eam", 4, (2, 2, 1))])
+def test_emu_bench_decomposed_parity_leg(emu, kind, world, grid):
+    """bench.py's N > 1 parity leg (a small decomposed system against the unmodified reference on the host: thermo at
+    step 0 and after 45 steps within 1e-6, same rebuild count, every tag owned exactly once), ranks as threads"""
+    import bench
+
+    if not __import__("oracle").ref_available():
+        pytest.skip("oracle/_ref not built")
+    allsum, res, errs = _AllSum(world), [None] * world, []
+    nccl_id = emu.lib.nccl_unique_id()
+
+    def worker(rank):
+        try:
+            loc = (rank % grid[0], (rank // grid[0]) % grid[1], rank // (grid[0] * grid[1]))
+            res[rank] = bench.run_decomposed_parity(None, None, emu, kind, rank, world, rank, lambda: nccl_id, grid, loc,
+                                                    lambda a: allsum(rank, a), steps=45, cells=6)
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+            allsum.bar.abort()
+
+    th = [threading.Thread(target=worker, args=(r,)) for r in range(world)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errs, errs
+    blk = res[0]
+    assert all(r is None for r in res[1:])
+    assert blk["ok"], blk
+    assert blk["tags"]["owned_exactly_once"] and blk["builds"]["equal"] and blk["builds"]["b200"] >= 2
+    assert max(blk["pe"], blk["ke"], blk["press"]) <= 1e-6
+
+
 def test_emu_langevin_counter_mode_is_rank_count_independent(emu):
     """fix langevin with the counter-based device generator (Philox keyed by seed, counter = tag, step) on an LJ melt:
     1 rank and 4 ranks follow the same trajectory (the numbers depend on nothing but seed, tag and step), and the
@@ -530,8 +561,9 @@ def test_emu_replicated_chain_and_bench_leg(emu, monkeypatch):
     md.close()
 
     def plain_timer(torch, dist, md, steps, warmup, device, nranks):
+        l0 = md.timers()["launches"]
         md.ctx.call("b200md_run", warmup + steps, md.dt, 0)
-        return 1.0
+        return 1.0, md.timers()["launches"] - l0
 
     monkeypatch.setattr(bench, "time_resident", plain_timer)
     out = bench.run_chain(None, None, emu, 1, types.SimpleNamespace(steps=3, warmup=1), 0)
@@ -662,7 +694,7 @@ class _FakeTorch:
 _FakeTorch.cuda.Event = _FakeTorch._Event
 
 
-def test_emu_bench_main_prints_the_contract_line(emu, monkeypatch, capsys):
+def test_emu_bench_main_prints_the_contract_line(emu, monkeypatch, capsys, tmp_path):
     """bench.py, b200 arm, N = 1, reduced sizes: both workloads' resident phases, the e2e phase under its watchdog, the
     cpu_baseline leg (the oracle/_ref reference run), one JSON line with every key the contract names"""
     import json
@@ -675,6 +707,7 @@ def test_emu_bench_main_prints_the_contract_line(emu, monkeypatch, capsys):
     monkeypatch.setitem(sys.modules, "torch", _FakeTorch)
     monkeypatch.setitem(sys.modules, "torch.distributed", fake_dist)
     monkeypatch.setattr(sys, "argv", ["bench.py", "--steps", "6", "--warmup", "3", "--cells", "6", "--eam-cells", "6", "--chain", "1"])
+    monkeypatch.chdir(tmp_path)
     for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
         monkeypatch.delenv(k, raising=False)
     bench.main()
@@ -691,6 +724,13 @@ def test_emu_bench_main_prints_the_contract_line(emu, monkeypatch, capsys):
     assert {"value", "unit", "cores", "kind", "sample"} <= set(line["cpu_baseline"])
     assert line["eam"]["value"] > 0 and line["eam"]["e2e"]["value"] > 0
     assert line["chain"]["value"] > 0 and line["chain"]["neigh"]["builds"] >= 1
+    # parity at the sizes the numbers are quoted on: the unmodified reference's thermo on the same input, step 0 and
+    # after the parity steps, and its rebuild count (here 6^3 cells; 16.4 M / 4 M atoms on the GPU box)
+    for blk in (line["parity"], line["eam"]["parity"]):
+        assert blk["ok"] and blk["builds"]["equal"] and blk["steps"] == 9
+        assert max(blk["pe"], blk["ke"], blk["press"]) <= 1e-6 and blk["lattice_step0"]["pe_per_atom_rel"] < 1e-9
+    assert line["chain"]["parity"]["ok"] and line["parity_all_ok"]
+    assert line["chain"]["cpu_baseline"]["value"] > 0
 
 
 @pytest.mark.parametrize("name", ["lj2_864", "eam_500"])
