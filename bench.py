@@ -510,6 +510,28 @@ def ref_thermo(kind, dims, steps, threads):
                 loop_s=float(m.group(1)) if m else None)
 
 
+def lammps_host_leg(kind, cells, steps, warmup):
+    """What a user of the drop-in sees: the UNMODIFIED reference hosting the b200 style classes (oracle/_ref/lmp_b200,
+    lammps-fugaku-threadpool_b200/lammps/) on the same input script with `-sf b200` -- LAMMPS creates the atoms on the host,
+    run_style verlet/b200 keeps them on the device, Finish prints the loop time of the K-step run."""
+    exe = ROOT / "oracle" / "_ref" / "lmp_b200"
+    if not exe.exists():
+        return None
+    with tempfile.TemporaryDirectory() as tmp:
+        inp = Path(tmp) / "in.bench"
+        inp.write_text(REF_HEAD[kind].format(nx=cells, ny=cells, nz=cells, pot=POT) + REF_TIMED.format(w=warmup, k=steps))
+        t = time.perf_counter()
+        r = subprocess.run([str(exe), "-in", str(inp), "-log", "none", "-echo", "none", "-sf", "b200"], cwd=tmp,
+                           env=dict(os.environ, OMP_NUM_THREADS="1"), capture_output=True, text=True)
+        wall = time.perf_counter() - t
+    if r.returncode != 0 or "b200: run_style verlet/b200" not in r.stdout:
+        return {"error": (r.stdout[-300:] + r.stderr[-300:]).strip()}
+    loops = re.findall(r"Loop time of ([0-9.eE+-]+) on \d+ procs for (\d+) steps with (\d+) atoms", r.stdout)
+    sec, st, na = loops[-1]
+    return {"value": int(na) * int(st) / float(sec) / 1e6, "unit": "Matom-steps/s", "loop_s": float(sec), "steps": int(st), "natoms": int(na),
+            "process_wall_s": wall, "api": "lmp_b200 -sf b200 -in <bench/in.%s scaled> (run_style verlet/b200, Loop time as Finish prints it)" % kind}
+
+
 PARITY_TOL = 1e-6   # north_star: thermo (PE, KE, pressure) within 1e-6 relative of the reference's CPU path
 
 
@@ -775,6 +797,11 @@ def main():
                 "kernel_ms": chain["kernel_ms"], "gpu_launches": chain["launches"], "neigh": chain["neigh"],
                 "roofline": roof(chain, "neigh", BYTES_NEIGH_CHAIN), "roofline_pair": roof(chain, "pair+bond", BYTES_CHAIN_PAIR),
                 "thermo": {"step0": chain["thermo0"], "last": chain["thermo1"]}, "parity": parity.get("chain")}
+        if world == 1 and not args.no_e2e and not e2e_error and line["e2e"]:
+            try:   # beside e2e: the loop time LAMMPS itself prints for the drop-in on the same input
+                line["e2e"]["lammps_host"] = lammps_host_leg("lj", args.cells, args.steps, args.warmup)
+            except Exception as ex:  # noqa: BLE001
+                line["e2e"]["lammps_host"] = {"error": repr(ex)}
         if world == 1 and not args.no_cpu and not e2e_error:
             line["cpu_baseline"] = cpu_measure("lj", 100, 10, budget_s=20.0, cells_cap=args.cells)
             if eam is not None:

@@ -280,9 +280,9 @@ int b200md_kernel_times(b200md_ctx *ctx, double *ms, int64_t *count, int reset);
 /* the cudaStream_t all of this context's work is issued on (for callers that record their own events
  * or order their own kernels against the library's, as KOKKOS styles do with their execution space) */
 void *b200md_stream(b200md_ctx *ctx);
-/* bins of an x-row one warp of the last neighbor build handled (1 for dense bins such as in.lj / in.eam; about
- * 26 / <atoms per bin> for sparse ones such as in.chain) */
-int b200md_build_bins_per_warp(const b200md_ctx *ctx);
+/* bins of an x-row one thread block of the last neighbor build handled (about 112 / <atoms per bin>: 6 for in.lj
+ * and in.eam, 37 for in.chain) */
+int b200md_build_bins_per_block(const b200md_ctx *ctx);
 /* execution knobs of this context -- the analogue of the reference's `package` command options
  * (src/GPU/fix_gpu.cpp:43-51 `package gpu ... neigh/split/...`, src/input.cpp package()).  Defaults are the variants
  * that measured fastest on B200; nothing is read from the environment.
@@ -290,7 +290,7 @@ int b200md_build_bins_per_warp(const b200md_ctx *ctx);
  *                         hold no ghost (default 1 on several ranks, 0 on one); applies from the next list build
  *   "host_pipeline"  0/1  b200md_step_host as a three-stream chunk pipeline (default 1) or serial copy-compute-copy
  *   "hs_min_chunk"   n    smallest system the pipeline splits into ranges (default 65536)
- *   "build_gb" n, "build_fp64" 0/1   test knobs of the list build (bins per warp; force the all-FP64 fallback kernel)
+ *   "build_gb" n, "build_fp64" 0/1   test knobs of the list build (bins per block; force the all-FP64 fallback kernel)
  * Unknown key: B200MD_ERR_ARG. */
 int b200md_tune(b200md_ctx *ctx, const char *key, int value);
 

@@ -7,7 +7,7 @@
 // directions are stored), so there are no atomics and no reverse_comm of ghost forces; energy and virial are tallied
 // half per visit like Pair::ev_tally_full.  The bond topology is a table indexed by atom TAG (partner tags and bond
 // types, b200md_set_bond_topology), so it needs no permutation when atoms are re-sorted or migrate.  The device index
-// of each partner's closest image is resolved inside the neighbor build (k_build_bins, BONDED): a 1-2 partner always
+// of each partner's closest image is resolved inside the neighbor build (k_build_seg, BONDED): a 1-2 partner always
 // lies within the neighbor cutoff (FENE: r < R0), is dropped from the pair list there (special_bonds lj weight 0) and
 // recorded in bond_idx instead.
 #include "ctx.cuh"

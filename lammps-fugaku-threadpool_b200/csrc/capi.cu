@@ -1163,7 +1163,7 @@ extern "C" int b200md_profile(b200md_ctx *c, int level)
 //   "overlap"       0/1  halo exchange on its own stream under the force kernels of the ghost-free tiles
 //   "host_pipeline" 0/1  b200md_step_host as a three-stream chunk pipeline (0: serial copy - compute - copy)
 //   "hs_min_chunk"  n    smallest system the pipeline splits into ranges (tests lower it)
-//   "build_gb" n, "build_fp64" 0/1   test knobs of the list build: bins per warp; force the all-FP64 fallback kernel
+//   "build_gb" n, "build_fp64" 0/1   test knobs of the list build: bins per block; force the all-FP64 fallback kernel
 extern "C" int b200md_tune(b200md_ctx *c, const char *key, int value)
 {
   NEED_CTX();
@@ -1173,8 +1173,9 @@ extern "C" int b200md_tune(b200md_ctx *c, const char *key, int value)
   else if (!strcmp(key, "hs_min_chunk")) c->hs_min_chunk = value > 0 ? value : 65536;
   else if (!strcmp(key, "build_gb")) c->build_gb_user = value > 0 ? value : 0;     // test knob
   else if (!strcmp(key, "build_fp64")) c->build_fp64 = value != 0;                 // test knob
+  else if (!strcmp(key, "build_seg_cap")) { c->seg_cap_user = value > 0 ? value : 0; c->seg_cap = 0; }   // test knob
   else return b200md_fail(c, B200MD_ERR_ARG, "b200md_tune: unknown key '%s'", key);
   return B200MD_OK;
 }
-extern "C" int b200md_build_bins_per_warp(const b200md_ctx *c) { return c ? c->build_gb : 0; }
+extern "C" int b200md_build_bins_per_block(const b200md_ctx *c) { return c ? c->build_gb : 0; }
 extern "C" void *b200md_stream(b200md_ctx *c) { return c ? (void *) c->stream : nullptr; }

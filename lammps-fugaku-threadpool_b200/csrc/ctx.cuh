@@ -192,7 +192,8 @@ struct b200md_ctx {
 
   // reductions / flags
   DevBuf<double> partials;  // [nblocks][8]
-  int build_gb = 1;          // bins per warp of the last list build (k_build_bins)
+  int build_gb = 1;          // bins of an x-row per block (segment) of the last list build (k_build_seg)
+  int seg_cap = 0, seg_cap_tg = 0;   // its staging capacity in records (grown on demand) and the segment length it was sized for
   DevBuf<double> peratom;   // [7][peratom_stride]: eatom, vatom xx yy zz xy xz yz of the owned atoms (b200md_pair_peratom)
   size_t peratom_stride = 0;
   int peratom_n = 0;        // owned atoms the tallies are valid for, 0 = none
@@ -225,7 +226,8 @@ struct b200md_ctx {
   // knobs (b200md_tune; defaults chosen from hardware measurements)
   int host_pipeline = 1;      // b200md_step_host: three-stream chunk pipeline (0 = serial copy-compute-copy)
   int hs_min_chunk = 65536;   // smallest system the pipeline splits into ranges
-  int build_gb_user = 0;      // test knob: bins of an x-row per warp in the list build (0 = by bin population)
+  int build_gb_user = 0;      // test knob: bins of an x-row per block in the list build (0 = by bin population)
+  int seg_cap_user = 0;       // test knob: initial staging capacity of the list build (records)
   int build_fp64 = 0;         // test knob: force the all-FP64 build kernel (otherwise only huge boxes with tiny cutoffs use it)
   int debug_timing = 0;       // per-phase wall times of every rebuild on stderr (B200MD_DEBUG_TIMING, read at create)
 

@@ -340,19 +340,26 @@ k_build_fp64(const double4 *__restrict__ pos, int nlocal, BinGeom g, const int *
 }
 
 // ------------------------------------------------------------------------------------------------
-// neighbor build, warp-cooperative form (the default, per-atom lists): ONE WARP PER BIN.
+// neighbor build, the default: ONE THREAD PER OWNED ATOM over candidates staged in shared memory.
 //   * k_binrec_fill stages every binned atom (owned + ghost, in cell_list order) as a 16-byte record
-//     {float x, y, z relative to the bin-grid origin; j | (type-1) << 28}: the candidates of a bin's 27-bin stencil
-//     are then 9 CONTIGUOUS record ranges (3 bins of an x-row each), read as warp-uniform (broadcast) 128-bit loads
-//     -- no per-lane gathers, no per-lane trip counts.
-//   * lanes = the owned atoms of the bin.  Every lane tests every candidate in FP32 (6 flops); the decision is
-//     final when |rsq_f - cutneighsq| > tol, where tol rigorously bounds the FP32 error (derivation at
-//     build_tolerance()).  Inside the band (about 1 candidate in 10^4) the reference's own FP64 expression decides:
+//     {float x, y, z relative to the bin-grid origin; j | (type-1) << 28}.
+//   * a block owns a SEGMENT of tg consecutive bins of one x-row (about 112 owned atoms).  Bins are >= the neighbor
+//     cutoff wide, so every candidate of its atoms lies in the 3 x 3 x (tg + 2) bins around it: 9 CONTIGUOUS record
+//     ranges, copied once into shared memory with coalesced 16-byte loads.
+//   * every thread then walks the 27 bins around ITS atom's bin (9 sub-ranges of the staged rows) with LDS.128 --
+//     the lanes of a warp sit in 2 or 3 bins, so a step reads 2 or 3 distinct addresses (broadcast) -- two candidates
+//     per iteration through the packed FP32 pipe (fadd2 / fmul2 / ffma2).  The decision is final when
+//     |rsq_f - cutneighsq| > tol, where tol rigorously bounds the FP32 error (derivation at build_tolerance()).  Inside
+//     the band (about 1 candidate in 10^4) the reference's own FP64 expression decides:
 //     rsq = delx*delx + dely*dely + delz*delz without FMA contraction, keep if rsq <= cutneighsq[itype][jtype]
 //     (src/npair_half_bin_atomonly_newton.cpp:80-87).  List membership is therefore bit-identical to the all-FP64
 //     kernel above and to the reference's list as tag-pair sets.
-//   * entry order per atom = (dz, dy) rows, then cell_list order -- the same order k_build_cluster<1> emits, so the
-//     force summation order (and every bit of the forces) is unchanged.
+//   * entry order per atom = (dz, dy) rows, then cell_list order -- what every earlier form of this kernel emitted, so
+//     the force summation order (and every bit of the forces) is unchanged.
+// Why this form (ncu, profiles/r02_ncu_build.md): the warp-per-bin kernel of round 1 (lanes = the 18.5 atoms of a bin,
+// candidates broadcast from global memory) was ISSUE-bound -- 81 % issue-slot utilisation, 757 warp instructions per
+// atom: 27 candidate steps per atom (500 candidates over 18.5 useful lanes) at 28 instructions each.  Here a lane
+// scans its own 500 candidates (15.6 steps per atom at 32 lanes) at about 14 instructions per candidate.
 // ------------------------------------------------------------------------------------------------
 struct BinRec { float x, y, z; int jt; };
 #define BR_JMASK 0x0FFFFFFF
@@ -381,7 +388,6 @@ __device__ __forceinline__ BinRec ld_rec(const BinRec *__restrict__ p)
   return r;
 }
 
-#define BUILD_WARPS 4
 // BONDED (in.chain): a candidate within the cutoff whose tag is one of the atom's 1-2 partners is NOT listed
 // (special_bonds lj weight 0, NPair::find_special src/npair.h:125-158 -> -1) but recorded as the device index of that
 // bond partner; of several periodic images the closest wins (Domain::closest_image).
@@ -392,113 +398,224 @@ struct BondBuild {
   int *bond_idx;               // [nlocal][maxb] out
   int maxb;
 };
+#define SEG_THREADS 128
+// shared-memory plan of a segment: SoA candidate arrays of `cap` elements (cap a multiple of 4, every staged bin padded
+// to a multiple of 4 with records that can never be accepted), so a thread reads four candidates with one LDS.128 per
+// array and every bin range is 4-aligned: no per-candidate range tests
+//   float x[cap], y[cap], z[cap]; int jt[cap] (index | (type-1) << 28); int tag[cap] (BONDED);
+//   int bs[9][tg+3]  cell_list position of each staged bin's first record (+ the end);
+//   int po[9][tg+3]  staged (padded) offset of each staged bin (+ the end)
+#define SEG_FAR 1.0e18f   /* coordinate of a padding record: rsq = inf, never <= any cutoff */
 template <int ONETYPE, int BONDED>
-__global__ void __launch_bounds__(BUILD_WARPS * 32)
-k_build_bins(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int nlocal, BinGeom g,
-             const int *__restrict__ bin_start, const double *__restrict__ cutneighsq, int ntypes, float tol, int maxneigh,
-             int *__restrict__ numneigh, int *__restrict__ neigh, int *__restrict__ flags, int *__restrict__ tile_ghost,
-             BondBuild bb, int gb)
+__global__ void __launch_bounds__(SEG_THREADS)
+k_build_seg(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int nlocal, BinGeom g,
+            const int *__restrict__ bin_start, const double *__restrict__ cutneighsq, int ntypes, float tol, int maxneigh,
+            int *__restrict__ numneigh, int *__restrict__ neigh, int *__restrict__ flags, int *__restrict__ tile_ghost,
+            BondBuild bb, int tg, int cap)
 {
+  extern __shared__ int4 s_dyn[];
+  float *s_x = reinterpret_cast<float *>(s_dyn), *s_y = s_x + cap, *s_z = s_y + cap;
+  int *s_jt = reinterpret_cast<int *>(s_z + cap);
+  int *s_tag = s_jt + cap;                                           // BONDED only
+  int *s_bs = s_tag + (BONDED ? cap : 0);
+  const int W = tg + 3;
+  int *s_po = s_bs + 9 * W;
   __shared__ double s_cut[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
   __shared__ float s_cutf[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
+  __shared__ int s_total;
   const int nt1 = ntypes + 1;
   for (int k = threadIdx.x; k < nt1 * nt1; k += blockDim.x) { s_cut[k] = cutneighsq[k]; s_cutf[k] = (float) cutneighsq[k]; }
+  const int nsegx = (g.nbin[0] + tg - 1) / tg;
+  const int seg = blockIdx.x;
+  const int sx = seg % nsegx, oby = (seg / nsegx) % g.nbin[1], obz = seg / (nsegx * g.nbin[1]);
+  const int gx = min(tg, g.nbin[0] - sx * tg);
+  const int bx0 = BIN_MARGIN + sx * tg, by = oby + BIN_MARGIN, bz = obz + BIN_MARGIN;
+  const int nq = gx + 3;   // bin starts per row: bins bx0-1 .. bx0+gx, plus the end of the last
+  for (int idx = threadIdx.x; idx < 9 * nq; idx += blockDim.x) {
+    const int r = idx / nq, q = idx - r * nq;
+    const int first = ((bz + r / 3 - 1) * g.mbin[1] + (by + r % 3 - 1)) * g.mbin[0] + bx0 - 1;
+    s_bs[r * W + q] = bin_start[first + q];
+  }
   __syncthreads();
-  const int lane = threadIdx.x & 31;
-  // a warp owns gb consecutive bins of an x-row (gb = 1 unless the bins are sparse, e.g. 3 atoms per bin in
-  // bench/in.chain: the bins' records are contiguous in cell_list, so are the gb + 2 bins of every candidate row, and
-  // the distance test alone decides membership -- same lists, same entry order, more lanes at work)
-  const int wb = blockIdx.x * BUILD_WARPS + (threadIdx.x >> 5);      // owned-segment number, x fastest
-  const int nsegx = (g.nbin[0] + gb - 1) / gb;
-  if (wb >= nsegx * g.nbin[1] * g.nbin[2]) return;
-  const int obx = (wb % nsegx) * gb, oby = (wb / nsegx) % g.nbin[1], obz = wb / (nsegx * g.nbin[1]);
-  const int gx = min(gb, g.nbin[0] - obx);
-  const int bx = obx + BIN_MARGIN, by = oby + BIN_MARGIN, bz = obz + BIN_MARGIN;
-  const int b = (bz * g.mbin[1] + by) * g.mbin[0] + bx;
-  const int s0 = bin_start[b], e0 = bin_start[b + gx];
-  const float cut1 = s_cutf[nt1 + 1];
-  int nmax = 0;
-  // owned atoms come first in a bin's records (cell_list is index-ordered within a bin, ghosts have index >= nlocal)
-  for (int gbase = s0; gbase < e0; gbase += 32) {
-    const int kk = gbase + lane;
-    BinRec me;
-    me.x = me.y = me.z = 0.f;
-    me.jt = BR_JMASK;
-    if (kk < e0) me = ld_rec(rec + kk);
-    const int i = me.jt & BR_JMASK;
-    const bool owned = (kk < e0) && i < nlocal;
-    if (!__any_sync(0xffffffffu, owned)) {
-      if (gb == 1) break;
-      continue;
+  // padded staging offsets: exclusive scan of roundup4(bin population) over the 9 x (gx + 2) staged bins (warp 0)
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x, nb = 9 * (gx + 2);
+    int carry = 0;
+    for (int b0 = 0; b0 < nb; b0 += 32) {
+      const int b = b0 + lane;
+      int cnt = 0, r = 0, q = 0;
+      if (b < nb) {
+        r = b / (gx + 2);
+        q = b - r * (gx + 2);
+        cnt = (s_bs[r * W + q + 1] - s_bs[r * W + q] + 3) & ~3;
+      }
+      int incl = cnt;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += y;
+      }
+      if (b < nb) {
+        s_po[r * W + q] = carry + incl - cnt;
+        if (q == gx + 1) s_po[r * W + q + 1] = carry + incl;   // end of the row = start of the next row's first bin
+      }
+      carry += __shfl_sync(0xffffffffu, incl, 31);
     }
-    const int trow = ONETYPE ? 0 : (((unsigned) me.jt >> 28) + 1) * nt1;
-    const size_t base = (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
+    if (lane == 0) s_total = carry;
+  }
+  __syncthreads();
+  const int total = s_total;
+  if (total > cap) {   // denser than the staging area allows: report the size wanted, the host grows it and redoes the build
+    if (threadIdx.x == 0) atomicMax(&flags[6], total);
+    return;
+  }
+  // stage: coalesced 16-byte record loads, scattered into the SoA arrays at the padded offset of the record's bin
+#pragma unroll 1
+  for (int r = 0; r < 9; r++) {
+    const int ks = s_bs[r * W], len = s_bs[r * W + gx + 2] - ks;
+    const int4 *src = reinterpret_cast<const int4 *>(rec + ks);
+    for (int k = threadIdx.x; k < len; k += blockDim.x) {
+      const int4 v = __ldg(src + k);
+      const int gk = ks + k;
+      int qlo = 0, qhi = gx + 1;   // the bin holding cell_list position gk: largest q with bs[q] <= gk
+      while (qlo < qhi) {
+        const int mid = (qlo + qhi + 1) >> 1;
+        if (s_bs[r * W + mid] <= gk) qlo = mid;
+        else qhi = mid - 1;
+      }
+      const int d = s_po[r * W + qlo] + gk - s_bs[r * W + qlo];
+      s_x[d] = __int_as_float(v.x); s_y[d] = __int_as_float(v.y); s_z[d] = __int_as_float(v.z);
+      s_jt[d] = v.w;
+      if (BONDED) s_tag[d] = __ldg(bb.rec_tag + gk);
+    }
+  }
+  for (int idx = threadIdx.x; idx < 9 * (gx + 2); idx += blockDim.x) {   // the padding records of every bin
+    const int r = idx / (gx + 2), q = idx - r * (gx + 2);
+    const int cnt = s_bs[r * W + q + 1] - s_bs[r * W + q];
+    for (int d = s_po[r * W + q] + cnt; d < s_po[r * W + q + 1]; d++) {
+      s_x[d] = s_y[d] = s_z[d] = SEG_FAR;
+      s_jt[d] = BR_JMASK;
+      if (BONDED) s_tag[d] = 0;
+    }
+  }
+  __syncthreads();
+  const float cut1 = s_cutf[nt1 + 1];
+  const int own_s = s_bs[4 * W + 1], own_e = s_bs[4 * W + 1 + gx];
+  int nmax = 0;
+  // the segment's own records (centre row, bins 1..gx); owned atoms come first in every bin's records (cell_list is
+  // index-ordered within a bin, ghosts have index >= nlocal)
+  for (int slot = own_s + threadIdx.x; slot < own_e; slot += blockDim.x) {
+    int bl = 0;   // my bin inside the segment, from my position in cell_list (exact; a float coordinate is not)
+    while (slot >= s_bs[4 * W + bl + 2]) bl++;
+    const int mine = s_po[4 * W + bl + 1] + slot - s_bs[4 * W + bl + 1];
+    const int myjt = s_jt[mine];
+    const int i = myjt & BR_JMASK;
+    if (i >= nlocal) continue;
+    const int trow = ONETYPE ? 0 : (((unsigned) myjt >> 28) + 1) * nt1;
+    int *const nbp = neigh + ((size_t) (i >> 5) * TILE * maxneigh + (i & 31));
+    const int nlastrow = maxneigh - 1;
+    const float mx = s_x[mine], my = s_y[mine], mz = s_z[mine];
+    const float2 nx = make_float2(-mx, -mx), ny = make_float2(-my, -my), nz = make_float2(-mz, -mz);
     int n = 0;
-    bool ghost_seen = false;  // overlap mode: does this atom's list hold a ghost?
+    bool ghost_near = false;   // overlap mode: a ghost record among my candidates (a superset of "a ghost in my list")
     int ptag[B200MD_MAXBONDS], pbest[B200MD_MAXBONDS];
     float prsq[B200MD_MAXBONDS];
     if (BONDED) {
-      const int ti = owned ? bb.tag[i] : 1;
+      const int ti = bb.tag[i];
 #pragma unroll
       for (int m = 0; m < B200MD_MAXBONDS; m++) {
-        ptag[m] = (owned && m < bb.maxb) ? bb.partner_by_tag[(size_t) (ti - 1) * bb.maxb + m] : 0;
+        ptag[m] = (m < bb.maxb) ? bb.partner_by_tag[(size_t) (ti - 1) * bb.maxb + m] : 0;
         pbest[m] = -1;
         prsq[m] = 3.0e38f;
       }
     }
-    for (int dz = -1; dz <= 1; dz++)
-      for (int dy = -1; dy <= 1; dy++) {
-        const int cell = ((bz + dz) * g.mbin[1] + (by + dy)) * g.mbin[0] + bx - 1;
-        const int ks = bin_start[cell], ke = bin_start[cell + gx + 2];
-#pragma unroll 4
-        for (int k = ks; k < ke; k++) {
-          const BinRec c = ld_rec(rec + k);
-          const float dx = me.x - c.x, dyy = me.y - c.y, dzz = me.z - c.z;
-          const float rsq = fmaf(dzz, dzz, fmaf(dyy, dyy, dx * dx));
-          const float cut = ONETYPE ? cut1 : s_cutf[trow + ((unsigned) c.jt >> 28) + 1];
-          bool accept = rsq <= cut - tol;
-          if (!accept && rsq <= cut + tol) {   // ambiguity band: the reference's FP64 expression decides
-            const int j = c.jt & BR_JMASK;
-            const double4 pi = pos[min(i, nlocal - 1)], pj = pos[j];
-            const double ddx = __dsub_rn(pi.x, pj.x), ddy = __dsub_rn(pi.y, pj.y), ddz = __dsub_rn(pi.z, pj.z);
-            const double r2 = __dadd_rn(__dadd_rn(__dmul_rn(ddx, ddx), __dmul_rn(ddy, ddy)), __dmul_rn(ddz, ddz));
-            accept = r2 <= s_cut[(ONETYPE ? nt1 : trow) + (ONETYPE ? 1 : ((unsigned) c.jt >> 28) + 1)];
-          }
-          const int j = c.jt & BR_JMASK;
-          if (BONDED && accept && owned && j != i) {
-            const int tj = __ldg(bb.rec_tag + k);
+    const float cut_lo1 = cut1 - tol, cut_hi1 = cut1 + tol;
+    // a candidate's verdict from its FP32 distance: 1 = inside for sure, 0 = outside for sure, 2 = in the ambiguity band
+    auto classify = [&](const int jt, const float rsq) -> int {
+      float cut_lo = cut_lo1, cut_hi = cut_hi1;
+      if (!ONETYPE) {
+        const float cut = s_cutf[trow + ((unsigned) jt >> 28) + 1];
+        cut_lo = cut - tol;
+        cut_hi = cut + tol;
+      }
+      return rsq <= cut_lo ? 1 : (rsq <= cut_hi ? 2 : 0);
+    };
+    // the band (about 1 candidate in 10^4): the reference's FP64 expression decides
+    auto exact = [&](const int jt) -> int {
+      const double4 pi = pos[i], pj = pos[jt & BR_JMASK];
+      const double ddx = __dsub_rn(pi.x, pj.x), ddy = __dsub_rn(pi.y, pj.y), ddz = __dsub_rn(pi.z, pj.z);
+      const double r2 = __dadd_rn(__dadd_rn(__dmul_rn(ddx, ddx), __dmul_rn(ddy, ddy)), __dmul_rn(ddz, ddz));
+      return r2 <= s_cut[(ONETYPE ? nt1 : trow) + (ONETYPE ? 1 : ((unsigned) jt >> 28) + 1)] ? 1 : 0;
+    };
+    // predicated append.  Entries beyond maxneigh pile up in the last row: the count flags the overflow and the host
+    // redoes the build with longer rows.
+    auto append = [&](const int jt, const float rsq, const int k, int verdict) {
+      const int j = ONETYPE ? jt : (jt & BR_JMASK);   // one type: the type bits are zero
+      bool accept = verdict != 0 && j != i;
+      if (BONDED && accept) {
+        const int tj = s_tag[k];
 #pragma unroll
-            for (int m = 0; m < B200MD_MAXBONDS; m++)
-              if (ptag[m] != 0 && tj == ptag[m]) {
-                accept = false;
-                if (rsq < prsq[m]) { prsq[m] = rsq; pbest[m] = j; }
-              }
+        for (int m = 0; m < B200MD_MAXBONDS; m++)
+          if (ptag[m] != 0 && tj == ptag[m]) {
+            accept = false;
+            if (rsq < prsq[m]) { prsq[m] = rsq; pbest[m] = j; }
           }
-          if (accept && owned && j != i) {
-            ghost_seen |= j >= nlocal;
-            if (n < maxneigh) neigh[base + (size_t) n * TILE] = j;
-            n++;
-          }
+      }
+      if (accept) nbp[(size_t) min(n, nlastrow) * TILE] = j;
+      n += accept ? 1 : 0;
+    };
+#pragma unroll 1
+    for (int r = 0; r < 9; r++) {
+      const int lo = s_po[r * W + bl], hi = s_po[r * W + bl + 3];   // both multiples of 4
+      if (tile_ghost) {   // ghosts are the last records of a bin: one look per stencil bin
+#pragma unroll
+        for (int q = 0; q < 3; q++) {
+          const int cnt = s_bs[r * W + bl + q + 1] - s_bs[r * W + bl + q];
+          if (cnt > 0) ghost_near |= (s_jt[s_po[r * W + bl + q] + cnt - 1] & BR_JMASK) >= nlocal;
         }
       }
-    if (owned) numneigh[i] = n;
-    if (BONDED && owned) {
+      for (int k = lo; k < hi; k += 4) {
+        const float4 X = *reinterpret_cast<const float4 *>(s_x + k), Y = *reinterpret_cast<const float4 *>(s_y + k),
+                     Z = *reinterpret_cast<const float4 *>(s_z + k);
+        const int4 J = *reinterpret_cast<const int4 *>(s_jt + k);
+        // packed FP32 (fadd2 / fmul2 / ffma2): four squared distances in 12 instructions; same operations and rounding
+        // as the scalar form rsq = fma(dz, dz, fma(dy, dy, dx * dx)) that build_tolerance() bounds
+        const float2 dxa = __fadd2_rn(make_float2(X.x, X.y), nx), dxb = __fadd2_rn(make_float2(X.z, X.w), nx);
+        const float2 dya = __fadd2_rn(make_float2(Y.x, Y.y), ny), dyb = __fadd2_rn(make_float2(Y.z, Y.w), ny);
+        const float2 dza = __fadd2_rn(make_float2(Z.x, Z.y), nz), dzb = __fadd2_rn(make_float2(Z.z, Z.w), nz);
+        const float2 ra = __ffma2_rn(dza, dza, __ffma2_rn(dya, dya, __fmul2_rn(dxa, dxa)));
+        const float2 rb = __ffma2_rn(dzb, dzb, __ffma2_rn(dyb, dyb, __fmul2_rn(dxb, dxb)));
+        int v0 = classify(J.x, ra.x), v1 = classify(J.y, ra.y), v2 = classify(J.z, rb.x), v3 = classify(J.w, rb.y);
+        if (__builtin_expect(((v0 | v1 | v2 | v3) & 2) != 0, 0)) {   // one rare branch per four candidates
+          if (v0 == 2) v0 = exact(J.x);
+          if (v1 == 2) v1 = exact(J.y);
+          if (v2 == 2) v2 = exact(J.z);
+          if (v3 == 2) v3 = exact(J.w);
+        }
+        append(J.x, ra.x, k, v0);
+        append(J.y, ra.y, k + 1, v1);
+        append(J.z, rb.x, k + 2, v2);
+        append(J.w, rb.y, k + 3, v3);
+      }
+    }
+    numneigh[i] = n;
+    if (BONDED) {
 #pragma unroll
       for (int m = 0; m < B200MD_MAXBONDS; m++)
         if (m < bb.maxb) {
           bb.bond_idx[(size_t) i * bb.maxb + m] = pbest[m];
           if (ptag[m] != 0 && pbest[m] < 0) flags[5] = 1;  // "Bond atoms missing" (src/ntopo_bond_all.cpp:56-61)
-          ghost_seen |= pbest[m] >= nlocal;
         }
     }
-    if (tile_ghost && owned && ghost_seen) atomicOr(&tile_ghost[i >> 5], 1);
-    nmax = max(nmax, owned ? n : 0);
+    if (tile_ghost && ghost_near) tile_ghost[i >> 5] = 1;   // several lanes may write the same 1
+    nmax = max(nmax, n);
   }
   nmax = __reduce_max_sync(0xffffffffu, nmax);
-  if (lane == 0 && nmax > 0) atomicMax(&flags[1], nmax);
+  // flags[1] = longest list seen; the plain read only skips atomics that could not raise it
+  if ((threadIdx.x & 31) == 0 && nmax > flags[1]) atomicMax(&flags[1], nmax);
 }
 
-// Rigorous bound on |rsq_f - rsq| of k_build_bins for any pair with r <= 2*rc (pairs farther apart differ from the
+// Rigorous bound on |rsq_f - rsq| of k_build_seg for any pair with r <= 2*rc (pairs farther apart differ from the
 // cutoff by more than 3*rc^2, far outside any band): coordinates are stored relative to the bin-grid origin, so
 // |x_f - x| <= u*M with u = 2^-24 and M the grid extent; dx_f carries both conversion errors plus one rounding:
 // |dx_f - dx| <= 2u(M + r); three squared terms and three roundings give
@@ -571,7 +688,7 @@ int neigh_rebuild(b200md_ctx *c)
     CU(cudaStreamSynchronize(c->stream));
     if (c->flags_h[4]) return b200md_fail(c, B200MD_ERR_ARG, "Bad FENE bond");
   }
-  CU(cudaMemsetAsync(c->flags_d, 0, 6 * sizeof(int), c->stream));
+  CU(cudaMemsetAsync(c->flags_d, 0, 8 * sizeof(int), c->stream));
   int n = c->nlocal;
 
   // Domain::pbc
@@ -646,6 +763,7 @@ int neigh_build_lists(b200md_ctx *c)
     c->maxneigh = (m + 7) / 8 * 8;
   }
   const int ntiles = cdiv(n, TILE);
+  CU(cudaMemsetAsync(c->flags_d + 6, 0, 2 * sizeof(int), c->stream));
   for (int attempt = 0; attempt < 8; attempt++) {
     TRY(dev_ensure(c, c->neigh, (size_t) ntiles * TILE * c->maxneigh));
     size_t smem = (size_t) (c->ntypes + 1) * (c->ntypes + 1) * sizeof(double);
@@ -683,19 +801,46 @@ int neigh_build_lists(b200md_ctx *c)
         bb.bond_idx = c->bonds.idx.p;
         bb.maxb = c->bonds.maxb;
       }
-      // bins per warp: about 26 owned atoms, leaving room for density fluctuations below the 32 lanes (a second
-      // batch of a few lanes costs a whole pass over the candidates)
-      int gb = c->build_gb_user > 0 ? c->build_gb_user : (int) (26.0 * nown / (n > 0 ? n : 1));
-      gb = gb < 1 ? 1 : gb > 16 ? 16 : gb;
-      c->build_gb = gb;
-#define BB_ARGS c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d, tile_ghost, bb, gb
-      const int bgrid = cdiv(cdiv(g.nbin[0], gb) * g.nbin[1] * g.nbin[2], BUILD_WARPS), bthr = BUILD_WARPS * 32;
+      // bins per block: about 112 owned atoms on 128 threads (lj melt: 18.5 atoms per bin -> 6 bins; chain melt: 3 per
+      // bin -> 37); "build_gb" overrides (tests)
+      const double per_bin = (double) n / (nown > 0 ? nown : 1);
+      int tg = c->build_gb_user > 0 ? c->build_gb_user : (int) (112.0 / (per_bin > 0.1 ? per_bin : 0.1) + 0.5);
+      tg = tg < 1 ? 1 : (tg > g.nbin[0] ? g.nbin[0] : tg);
+      // staging area: the 3 x 3 x (tg + 2) bins of a segment with 20 % head room; a denser segment reports its size
+      // through flags[6] and the build is redone with room for it (like the maxneigh retry below)
+      const size_t rec_bytes = bonded ? 20 : 16;
+      auto seg_smem = [&](int t, int cap) { return (size_t) cap * rec_bytes + (size_t) (2 * 9 * (t + 3)) * sizeof(int); };
+      if (c->seg_cap_tg != tg) { c->seg_cap = 0; c->seg_cap_tg = tg; }
+      if (c->seg_cap == 0 && c->seg_cap_user > 0) c->seg_cap = (c->seg_cap_user + 3) & ~3;   // test knob: start too small, exercise the retry
+      // (every staged bin is padded to a multiple of 4 records: + 1.5 on average, at most + 3)
+      if (c->seg_cap == 0) c->seg_cap = (int) (1.2 * 9.0 * (tg + 2) * ((double) nall / (nown > 0 ? nown : 1) + 1.5)) + 64;
+      if (c->seg_cap > nall + 27 * (tg + 2)) c->seg_cap = nall + 27 * (tg + 2);   // no segment can stage more than exists
+      c->seg_cap = (c->seg_cap + 3) & ~3;
+      while (tg > 1 && seg_smem(tg, c->seg_cap) > 160 * 1024) {   // never needed for liquids; a guard for pathological density
+        tg = (tg + 1) / 2;
+        c->seg_cap = (c->seg_cap + 1) / 2 + 64;
+        c->seg_cap_tg = tg;
+      }
+      if (seg_smem(tg, c->seg_cap) > 200 * 1024)
+        return b200md_fail(c, B200MD_ERR_NEIGH_OVERFLOW, "neighbor build: %d atoms in the 27 bins around one bin do not fit shared memory", c->seg_cap);
+      c->build_gb = tg;
+      static bool attr_done[64] = {};  // per device: a process may hold contexts on several GPUs
+      if (!attr_done[c->device & 63]) {
+        CU(cudaFuncSetAttribute(k_build_seg<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(cudaFuncSetAttribute(k_build_seg<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(cudaFuncSetAttribute(k_build_seg<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(cudaFuncSetAttribute(k_build_seg<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_done[c->device & 63] = true;
+      }
+      const size_t bsmem = seg_smem(tg, c->seg_cap);
+#define BB_ARGS c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d, tile_ghost, bb, tg, c->seg_cap
+      const int bgrid = cdiv(g.nbin[0], tg) * g.nbin[1] * g.nbin[2];
       if (bonded) {
-        if (c->ntypes == 1) k_build_bins<1, 1><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
-        else k_build_bins<0, 1><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+        if (c->ntypes == 1) k_build_seg<1, 1><<<bgrid, SEG_THREADS, bsmem, c->stream>>>(BB_ARGS);
+        else k_build_seg<0, 1><<<bgrid, SEG_THREADS, bsmem, c->stream>>>(BB_ARGS);
       } else {
-        if (c->ntypes == 1) k_build_bins<1, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
-        else k_build_bins<0, 0><<<bgrid, bthr, 0, c->stream>>>(BB_ARGS);
+        if (c->ntypes == 1) k_build_seg<1, 0><<<bgrid, SEG_THREADS, bsmem, c->stream>>>(BB_ARGS);
+        else k_build_seg<0, 0><<<bgrid, SEG_THREADS, bsmem, c->stream>>>(BB_ARGS);
       }
 #undef BB_ARGS
       LAUNCH_CHECK();
@@ -714,6 +859,12 @@ int neigh_build_lists(b200md_ctx *c)
     if (c->flags_h[5]) return b200md_fail(c, B200MD_ERR_LOST_ATOMS, "Bond atoms missing: a bond partner is not within the neighbor cutoff");
     c->bonds.idx_valid = c->bonds.maxb > 0;
     c->maxneigh_seen = c->flags_h[1];
+    if (c->flags_h[6] > c->seg_cap) {   // a segment's candidates did not fit the staging area: make room and redo
+      c->seg_cap = (c->flags_h[6] + c->flags_h[6] / 8 + 64 + 3) & ~3;
+      CU(cudaMemsetAsync(c->flags_d + 6, 0, sizeof(int), c->stream));
+      CU(cudaMemsetAsync(c->flags_d + 1, 0, sizeof(int), c->stream));
+      continue;
+    }
     if (c->flags_h[1] > c->maxneigh) {  // "Neighbor list overflow": grow and redo instead of aborting
       c->maxneigh = (c->flags_h[1] + c->flags_h[1] / 8 + 7) / 8 * 8;
       CU(cudaMemsetAsync(c->flags_d + 1, 0, sizeof(int), c->stream));

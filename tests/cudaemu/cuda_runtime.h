@@ -41,6 +41,8 @@ struct int2 { int x, y; };
 struct int4 { int x, y, z, w; };
 struct float4 { float x, y, z, w; };
 struct double2 { double x, y; };
+struct float2 { float x, y; };
+static inline float2 make_float2(float x, float y) { return {x, y}; }
 struct double3 { double x, y, z; };
 struct double4 { double x, y, z, w; };
 static inline double3 make_double3(double x, double y, double z) { return {x, y, z}; }
@@ -196,6 +198,10 @@ static inline unsigned __ballot_sync(unsigned, int pred)
   emu::warp_barrier();
   return r;
 }
+// packed FP32 pair arithmetic of sm_100 (crt/sm_100_rt.h): two independent IEEE operations
+static inline float2 __fadd2_rn(float2 a, float2 b) { return {a.x + b.x, a.y + b.y}; }
+static inline float2 __fmul2_rn(float2 a, float2 b) { return {a.x * b.x, a.y * b.y}; }
+static inline float2 __ffma2_rn(float2 a, float2 b, float2 c) { return {fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y)}; }
 static inline int __any_sync(unsigned m, int pred) { return __ballot_sync(m, pred) != 0; }
 static inline int __all_sync(unsigned m, int pred) { return __ballot_sync(m, !pred) == 0; }
 static inline int __reduce_max_sync(unsigned, int v)

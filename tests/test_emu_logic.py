@@ -107,18 +107,20 @@ def test_emu_neighbor_list_bit_exact(emu, name):
     for gb in (2, 5):                                # several bins of an x-row per warp (sparse-bin form)
         gp.test_neighbor_list_bit_exact(emu, name, tune={"build_gb": gb})
     gp.test_neighbor_list_bit_exact(emu, name, tune={"build_fp64": 1})   # the all-FP64 fallback kernel
+    gp.test_neighbor_list_bit_exact(emu, name, tune={"build_seg_cap": 8})  # staging area too small: grow-and-redo path
 
 
 @pytest.mark.parametrize("kind,steps", [("lj", 45), ("eam", 25)])
 def test_emu_bins_per_warp_same_list_order(emu, oracle, kind, steps):
-    """k_build_bins with 1, 3 and 7 bins per warp (3 and 7 do not divide the bin count; 7 needs several 32-lane
-    batches per segment) writes the same lists in the same entry order: trajectories are bit-identical"""
+    """k_build_seg with segments of 1, 3 and 7 bins per block (the box has 4 bins per x-row: 3 leaves a remainder
+    segment, 7 is clamped to the whole row and needs several passes of the 128 threads) writes the same lists in the
+    same entry order: trajectories are bit-identical"""
     out = []
     for gb in (1, 3, 7):
         md, _ = gp._bench_system(emu, oracle, kind, 8)
         md.tune("build_gb", gb)
         md.run(steps)
-        assert emu.lib.load().b200md_build_bins_per_warp(md.ctx.h) == int(gb)
+        assert emu.lib.load().b200md_build_bins_per_block(md.ctx.h) == min(int(gb), 4)
         out.append((md.gather(), md.thermo_log[-1]["pe"], md.neigh_stats()))
         md.close()
     for g, pe, st in out[1:]:

@@ -77,8 +77,8 @@ def test_chain_setup_forces_vs_reference(pkg):
     assert np.abs(a["f"][sel] - g["a_f"]).max() <= F_RTOL * fmax
     numneigh, _ = md.neighbor_list()
     assert int(numneigh.sum()) == 2 * int(g["a_npairs"][0])
-    L = pkg.lib.load()   # 3 beads per bin: 8 bins of an x-row per warp
-    assert L.b200md_build_bins_per_warp(md.ctx.h) == 8
+    L = pkg.lib.load()   # 3 beads per bin: a block of the list build takes a whole 22-bin x-row of the 32k box (37 on big ones)
+    assert L.b200md_build_bins_per_block(md.ctx.h) == 22
     md.close()
 
 
