@@ -400,13 +400,14 @@ struct BondBuild {
 };
 #define SEG_THREADS 128
 // shared-memory plan of a segment: SoA candidate arrays of `cap` elements (cap a multiple of 4, every staged bin padded
-// to a multiple of 4 with records that can never be accepted), so a thread reads four candidates with one LDS.128 per
-// array and every bin range is 4-aligned: no per-candidate range tests
+// to a multiple of VW with records that can never be accepted), so a thread reads VW candidates with one LDS.128 (VW = 4,
+// dense bins) or LDS.64 (VW = 2, sparse bins such as in.chain's 3 beads per bin, where padding to 4 would add a third
+// more candidates) per array and every bin range is VW-aligned: no per-candidate range tests
 //   float x[cap], y[cap], z[cap]; int jt[cap] (index | (type-1) << 28); int tag[cap] (BONDED);
 //   int bs[9][tg+3]  cell_list position of each staged bin's first record (+ the end);
 //   int po[9][tg+3]  staged (padded) offset of each staged bin (+ the end)
 #define SEG_FAR 1.0e18f   /* coordinate of a padding record: rsq = inf, never <= any cutoff */
-template <int ONETYPE, int BONDED>
+template <int ONETYPE, int BONDED, int VW>
 __global__ void __launch_bounds__(SEG_THREADS)
 k_build_seg(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int nlocal, BinGeom g,
             const int *__restrict__ bin_start, const double *__restrict__ cutneighsq, int ntypes, float tol, int maxneigh,
@@ -447,7 +448,7 @@ k_build_seg(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int
       if (b < nb) {
         r = b / (gx + 2);
         q = b - r * (gx + 2);
-        cnt = (s_bs[r * W + q + 1] - s_bs[r * W + q] + 3) & ~3;
+        cnt = (s_bs[r * W + q + 1] - s_bs[r * W + q] + VW - 1) & ~(VW - 1);
       }
       int incl = cnt;
 #pragma unroll
@@ -530,28 +531,18 @@ k_build_seg(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int
       }
     }
     const float cut_lo1 = cut1 - tol, cut_hi1 = cut1 + tol;
-    // a candidate's verdict from its FP32 distance: 1 = inside for sure, 0 = outside for sure, 2 = in the ambiguity band
-    auto classify = [&](const int jt, const float rsq) -> int {
-      float cut_lo = cut_lo1, cut_hi = cut_hi1;
-      if (!ONETYPE) {
-        const float cut = s_cutf[trow + ((unsigned) jt >> 28) + 1];
-        cut_lo = cut - tol;
-        cut_hi = cut + tol;
-      }
-      return rsq <= cut_lo ? 1 : (rsq <= cut_hi ? 2 : 0);
-    };
-    // the band (about 1 candidate in 10^4): the reference's FP64 expression decides
-    auto exact = [&](const int jt) -> int {
+    // the ambiguity band (about 1 candidate in 10^4): the reference's FP64 expression decides
+    auto exact = [&](const int jt) -> bool {
       const double4 pi = pos[i], pj = pos[jt & BR_JMASK];
       const double ddx = __dsub_rn(pi.x, pj.x), ddy = __dsub_rn(pi.y, pj.y), ddz = __dsub_rn(pi.z, pj.z);
       const double r2 = __dadd_rn(__dadd_rn(__dmul_rn(ddx, ddx), __dmul_rn(ddy, ddy)), __dmul_rn(ddz, ddz));
-      return r2 <= s_cut[(ONETYPE ? nt1 : trow) + (ONETYPE ? 1 : ((unsigned) jt >> 28) + 1)] ? 1 : 0;
+      return r2 <= s_cut[(ONETYPE ? nt1 : trow) + (ONETYPE ? 1 : ((unsigned) jt >> 28) + 1)];
     };
     // predicated append.  Entries beyond maxneigh pile up in the last row: the count flags the overflow and the host
     // redoes the build with longer rows.
-    auto append = [&](const int jt, const float rsq, const int k, int verdict) {
+    auto append = [&](const int jt, const float rsq, const int k, bool accept) {
       const int j = ONETYPE ? jt : (jt & BR_JMASK);   // one type: the type bits are zero
-      bool accept = verdict != 0 && j != i;
+      accept = accept && j != i;
       if (BONDED && accept) {
         const int tj = s_tag[k];
 #pragma unroll
@@ -566,7 +557,7 @@ k_build_seg(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int
     };
 #pragma unroll 1
     for (int r = 0; r < 9; r++) {
-      const int lo = s_po[r * W + bl], hi = s_po[r * W + bl + 3];   // both multiples of 4
+      const int lo = s_po[r * W + bl], hi = s_po[r * W + bl + 3];   // both multiples of VW
       if (tile_ghost) {   // ghosts are the last records of a bin: one look per stencil bin
 #pragma unroll
         for (int q = 0; q < 3; q++) {
@@ -574,28 +565,69 @@ k_build_seg(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int
           if (cnt > 0) ghost_near |= (s_jt[s_po[r * W + bl + q] + cnt - 1] & BR_JMASK) >= nlocal;
         }
       }
-      for (int k = lo; k < hi; k += 4) {
-        const float4 X = *reinterpret_cast<const float4 *>(s_x + k), Y = *reinterpret_cast<const float4 *>(s_y + k),
-                     Z = *reinterpret_cast<const float4 *>(s_z + k);
-        const int4 J = *reinterpret_cast<const int4 *>(s_jt + k);
-        // packed FP32 (fadd2 / fmul2 / ffma2): four squared distances in 12 instructions; same operations and rounding
-        // as the scalar form rsq = fma(dz, dz, fma(dy, dy, dx * dx)) that build_tolerance() bounds
-        const float2 dxa = __fadd2_rn(make_float2(X.x, X.y), nx), dxb = __fadd2_rn(make_float2(X.z, X.w), nx);
-        const float2 dya = __fadd2_rn(make_float2(Y.x, Y.y), ny), dyb = __fadd2_rn(make_float2(Y.z, Y.w), ny);
-        const float2 dza = __fadd2_rn(make_float2(Z.x, Z.y), nz), dzb = __fadd2_rn(make_float2(Z.z, Z.w), nz);
-        const float2 ra = __ffma2_rn(dza, dza, __ffma2_rn(dya, dya, __fmul2_rn(dxa, dxa)));
-        const float2 rb = __ffma2_rn(dzb, dzb, __ffma2_rn(dyb, dyb, __fmul2_rn(dxb, dxb)));
-        int v0 = classify(J.x, ra.x), v1 = classify(J.y, ra.y), v2 = classify(J.z, rb.x), v3 = classify(J.w, rb.y);
-        if (__builtin_expect(((v0 | v1 | v2 | v3) & 2) != 0, 0)) {   // one rare branch per four candidates
-          if (v0 == 2) v0 = exact(J.x);
-          if (v1 == 2) v1 = exact(J.y);
-          if (v2 == 2) v2 = exact(J.z);
-          if (v3 == 2) v3 = exact(J.w);
+      // VW verdicts from VW FP32 distances: one compare each on the common path (provisionally inside iff
+      // rsq <= cut + tol), then ONE rare branch for the group: taken iff the largest provisionally-inside distance
+      // lies above cut - tol, i.e. some candidate sits in the ambiguity band
+      auto group = [&](const float (&rs)[VW], const int (&js)[VW], const int k0) {
+        bool acc[VW];
+        if (ONETYPE) {
+          float worst = 0.f;
+#pragma unroll
+          for (int u = 0; u < VW; u++) {
+            acc[u] = rs[u] <= cut_hi1;
+            worst = fmaxf(worst, acc[u] ? rs[u] : 0.f);
+          }
+          if (__builtin_expect(worst > cut_lo1, 0)) {
+#pragma unroll
+            for (int u = 0; u < VW; u++)
+              if (acc[u] && rs[u] > cut_lo1) acc[u] = exact(js[u]);
+          }
+        } else {
+          bool band = false;
+          float cl[VW];
+#pragma unroll
+          for (int u = 0; u < VW; u++) {
+            const float cut = s_cutf[trow + ((unsigned) js[u] >> 28) + 1];
+            cl[u] = cut - tol;
+            acc[u] = rs[u] <= cut + tol;
+            band |= acc[u] && rs[u] > cl[u];
+          }
+          if (__builtin_expect(band, 0)) {
+#pragma unroll
+            for (int u = 0; u < VW; u++)
+              if (acc[u] && rs[u] > cl[u]) acc[u] = exact(js[u]);
+          }
         }
-        append(J.x, ra.x, k, v0);
-        append(J.y, ra.y, k + 1, v1);
-        append(J.z, rb.x, k + 2, v2);
-        append(J.w, rb.y, k + 3, v3);
+#pragma unroll
+        for (int u = 0; u < VW; u++) append(js[u], rs[u], k0 + u, acc[u]);
+      };
+      // packed FP32 (fadd2 / fmul2 / ffma2): two squared distances per instruction triple; same operations and rounding
+      // as the scalar form rsq = fma(dz, dz, fma(dy, dy, dx * dx)) that build_tolerance() bounds
+      if constexpr (VW == 4) {
+        for (int k = lo; k < hi; k += 4) {
+          const float4 X = *reinterpret_cast<const float4 *>(s_x + k), Y = *reinterpret_cast<const float4 *>(s_y + k),
+                       Z = *reinterpret_cast<const float4 *>(s_z + k);
+          const int4 J = *reinterpret_cast<const int4 *>(s_jt + k);
+          const float2 dxa = __fadd2_rn(make_float2(X.x, X.y), nx), dxb = __fadd2_rn(make_float2(X.z, X.w), nx);
+          const float2 dya = __fadd2_rn(make_float2(Y.x, Y.y), ny), dyb = __fadd2_rn(make_float2(Y.z, Y.w), ny);
+          const float2 dza = __fadd2_rn(make_float2(Z.x, Z.y), nz), dzb = __fadd2_rn(make_float2(Z.z, Z.w), nz);
+          const float2 ra = __ffma2_rn(dza, dza, __ffma2_rn(dya, dya, __fmul2_rn(dxa, dxa)));
+          const float2 rb = __ffma2_rn(dzb, dzb, __ffma2_rn(dyb, dyb, __fmul2_rn(dxb, dxb)));
+          const float rs[VW] = {ra.x, ra.y, rb.x, rb.y};
+          const int js[VW] = {J.x, J.y, J.z, J.w};
+          group(rs, js, k);
+        }
+      } else {
+        for (int k = lo; k < hi; k += 2) {
+          const float2 X = *reinterpret_cast<const float2 *>(s_x + k), Y = *reinterpret_cast<const float2 *>(s_y + k),
+                       Z = *reinterpret_cast<const float2 *>(s_z + k);
+          const int2 J = *reinterpret_cast<const int2 *>(s_jt + k);
+          const float2 dxa = __fadd2_rn(X, nx), dya = __fadd2_rn(Y, ny), dza = __fadd2_rn(Z, nz);
+          const float2 ra = __ffma2_rn(dza, dza, __ffma2_rn(dya, dya, __fmul2_rn(dxa, dxa)));
+          const float rs[VW] = {ra.x, ra.y};
+          const int js[VW] = {J.x, J.y};
+          group(rs, js, k);
+        }
       }
     }
     numneigh[i] = n;
@@ -806,14 +838,15 @@ int neigh_build_lists(b200md_ctx *c)
       const double per_bin = (double) n / (nown > 0 ? nown : 1);
       int tg = c->build_gb_user > 0 ? c->build_gb_user : (int) (112.0 / (per_bin > 0.1 ? per_bin : 0.1) + 0.5);
       tg = tg < 1 ? 1 : (tg > g.nbin[0] ? g.nbin[0] : tg);
-      // staging area: the 3 x 3 x (tg + 2) bins of a segment with 20 % head room; a denser segment reports its size
+      // staging area: the 3 x 3 x (tg + 2) bins of a segment with 8 % head room; a denser segment reports its size
       // through flags[6] and the build is redone with room for it (like the maxneigh retry below)
       const size_t rec_bytes = bonded ? 20 : 16;
       auto seg_smem = [&](int t, int cap) { return (size_t) cap * rec_bytes + (size_t) (2 * 9 * (t + 3)) * sizeof(int); };
       if (c->seg_cap_tg != tg) { c->seg_cap = 0; c->seg_cap_tg = tg; }
       if (c->seg_cap == 0 && c->seg_cap_user > 0) c->seg_cap = (c->seg_cap_user + 3) & ~3;   // test knob: start too small, exercise the retry
-      // (every staged bin is padded to a multiple of 4 records: + 1.5 on average, at most + 3)
-      if (c->seg_cap == 0) c->seg_cap = (int) (1.2 * 9.0 * (tg + 2) * ((double) nall / (nown > 0 ? nown : 1) + 1.5)) + 64;
+      // (every staged bin is padded to a multiple of vw records: + (vw - 1) / 2 on average)
+      const int vw = per_bin >= 8.0 ? 4 : 2;
+      if (c->seg_cap == 0) c->seg_cap = (int) (1.08 * 9.0 * (tg + 2) * ((double) nall / (nown > 0 ? nown : 1) + 0.5 * (vw - 1))) + 64;
       if (c->seg_cap > nall + 27 * (tg + 2)) c->seg_cap = nall + 27 * (tg + 2);   // no segment can stage more than exists
       c->seg_cap = (c->seg_cap + 3) & ~3;
       while (tg > 1 && seg_smem(tg, c->seg_cap) > 160 * 1024) {   // never needed for liquids; a guard for pathological density
@@ -826,22 +859,29 @@ int neigh_build_lists(b200md_ctx *c)
       c->build_gb = tg;
       static bool attr_done[64] = {};  // per device: a process may hold contexts on several GPUs
       if (!attr_done[c->device & 63]) {
-        CU(cudaFuncSetAttribute(k_build_seg<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        CU(cudaFuncSetAttribute(k_build_seg<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        CU(cudaFuncSetAttribute(k_build_seg<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        CU(cudaFuncSetAttribute(k_build_seg<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(cudaFuncSetAttribute(k_build_seg<1, 0, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(cudaFuncSetAttribute(k_build_seg<0, 0, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(cudaFuncSetAttribute(k_build_seg<1, 1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(cudaFuncSetAttribute(k_build_seg<0, 1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(cudaFuncSetAttribute(k_build_seg<1, 0, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(cudaFuncSetAttribute(k_build_seg<0, 0, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(cudaFuncSetAttribute(k_build_seg<1, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(cudaFuncSetAttribute(k_build_seg<0, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr_done[c->device & 63] = true;
       }
       const size_t bsmem = seg_smem(tg, c->seg_cap);
 #define BB_ARGS c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d, tile_ghost, bb, tg, c->seg_cap
+#define BB_LAUNCH(OT, BD, V) k_build_seg<OT, BD, V><<<bgrid, SEG_THREADS, bsmem, c->stream>>>(BB_ARGS)
       const int bgrid = cdiv(g.nbin[0], tg) * g.nbin[1] * g.nbin[2];
-      if (bonded) {
-        if (c->ntypes == 1) k_build_seg<1, 1><<<bgrid, SEG_THREADS, bsmem, c->stream>>>(BB_ARGS);
-        else k_build_seg<0, 1><<<bgrid, SEG_THREADS, bsmem, c->stream>>>(BB_ARGS);
+      const int ot = c->ntypes == 1;
+      if (vw == 4) {
+        if (bonded) { if (ot) BB_LAUNCH(1, 1, 4); else BB_LAUNCH(0, 1, 4); }
+        else { if (ot) BB_LAUNCH(1, 0, 4); else BB_LAUNCH(0, 0, 4); }
       } else {
-        if (c->ntypes == 1) k_build_seg<1, 0><<<bgrid, SEG_THREADS, bsmem, c->stream>>>(BB_ARGS);
-        else k_build_seg<0, 0><<<bgrid, SEG_THREADS, bsmem, c->stream>>>(BB_ARGS);
+        if (bonded) { if (ot) BB_LAUNCH(1, 1, 2); else BB_LAUNCH(0, 1, 2); }
+        else { if (ot) BB_LAUNCH(1, 0, 2); else BB_LAUNCH(0, 0, 2); }
       }
+#undef BB_LAUNCH
 #undef BB_ARGS
       LAUNCH_CHECK();
     } else {
