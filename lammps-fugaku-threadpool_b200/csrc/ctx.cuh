@@ -169,7 +169,9 @@ struct b200md_ctx {
   // neighbor list
   int maxneigh = 0;
   DevBuf<int> numneigh, neigh;
-  DevBuf<int> tile_ghost;     // [ntiles]: != 0 if any atom of the 32-atom tile has a ghost in its list (overlap mode)
+  DevBuf<int> tile_ghost;     // [ntiles]: != 0 if an atom of the 32-atom tile has a ghost among its candidates (overlap mode)
+  DevBuf<int> tile_list, tile_pos;   // tile numbers, ghost-free tiles first (ascending), then the others; scan scratch
+  int ntiles_ghost = 0;       // tiles in the second part
   bool tiles_valid = false;
   int maxneigh_seen = 0;
 

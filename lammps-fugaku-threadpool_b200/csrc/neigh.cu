@@ -647,6 +647,20 @@ k_build_seg(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int
   if ((threadIdx.x & 31) == 0 && nmax > flags[1]) atomicMax(&flags[1], nmax);
 }
 
+// overlap mode: the tiles as two compact lists, ghost-free tiles first (ascending), then the others (ascending), from
+// the flags the build left and their exclusive scan; flags[7] = number of tiles in the second list
+__global__ void k_tile_lists(const int *__restrict__ flag, const int *__restrict__ pos, int ntiles, int *__restrict__ list,
+                             int *__restrict__ flags)
+{
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= ntiles) return;
+  const int nghost = pos[ntiles - 1] + (flag[ntiles - 1] != 0);
+  const int gflag = flag[t] != 0, p = pos[t];
+  if (gflag) list[ntiles - nghost + p] = t;
+  else list[t - p] = t;
+  if (t == 0) flags[7] = nghost;
+}
+
 // Rigorous bound on |rsq_f - rsq| of k_build_seg for any pair with r <= 2*rc (pairs farther apart differ from the
 // cutoff by more than 3*rc^2, far outside any band): coordinates are stored relative to the bin-grid origin, so
 // |x_f - x| <= u*M with u = 2^-24 and M the grid extent; dx_f carries both conversion errors plus one rounding:
@@ -882,6 +896,13 @@ int neigh_build_lists(b200md_ctx *c)
         else { if (ot) BB_LAUNCH(1, 0, 2); else BB_LAUNCH(0, 0, 2); }
       }
 #undef BB_LAUNCH
+      if (tile_ghost) {   // (the flags are 0 / 1, so their scan counts the ghost tiles before each tile)
+        TRY(dev_ensure(c, c->tile_list, (size_t) ntiles));
+        TRY(dev_ensure(c, c->tile_pos, (size_t) ntiles));
+        TRY(exclusive_scan(c, tile_ghost, c->tile_pos.p, ntiles));
+        k_tile_lists<<<cdiv(ntiles, 256), 256, 0, c->stream>>>(tile_ghost, c->tile_pos.p, ntiles, c->tile_list.p, c->flags_d);
+        c->launches++;
+      }
 #undef BB_ARGS
       LAUNCH_CHECK();
     } else {
@@ -899,6 +920,7 @@ int neigh_build_lists(b200md_ctx *c)
     if (c->flags_h[5]) return b200md_fail(c, B200MD_ERR_LOST_ATOMS, "Bond atoms missing: a bond partner is not within the neighbor cutoff");
     c->bonds.idx_valid = c->bonds.maxb > 0;
     c->maxneigh_seen = c->flags_h[1];
+    c->ntiles_ghost = c->tiles_valid ? c->flags_h[7] : 0;
     if (c->flags_h[6] > c->seg_cap) {   // a segment's candidates did not fit the staging area: make room and redo
       c->seg_cap = (c->flags_h[6] + c->flags_h[6] / 8 + 64 + 3) & ~3;
       CU(cudaMemsetAsync(c->flags_d + 6, 0, sizeof(int), c->stream));

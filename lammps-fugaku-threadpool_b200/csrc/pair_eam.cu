@@ -236,16 +236,19 @@ __global__ void __launch_bounds__(EAM1T_THREADS, 2)
 k_eam_rho_fp_1t(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
                 int nlocal, EAMParams P, const double *__restrict__ tab1, double *__restrict__ rho_out,
                 double *__restrict__ fp_out, double4 *__restrict__ posfp, double *__restrict__ partials,
-                const int *__restrict__ tile_ghost, int part)
+                const int *__restrict__ tile_list, int part)
 {
   extern __shared__ double s_t[];  // [4][n1]: rhor c3..c6
   const int n1 = P.nr + 1;
   for (int k = threadIdx.x; k < 4 * n1; k += blockDim.x) s_t[k] = tab1[k];
   __syncthreads();
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (SPLIT == 1) {   // overlap mode, see k_lj_force: warp w takes tile tile_list[w], w < part
+    const int w = i >> 5;
+    i = w < part ? tile_list[w] * TILE + (threadIdx.x & 31) : nlocal;
+  }
   double acc[1] = {0.0};
-  bool active = i < nlocal;
-  if (SPLIT == 1 && active) active = (tile_ghost[i >> 5] != 0) == (part != 0);  // overlap mode, see k_lj_force
+  const bool active = i < nlocal;
   if (active) {
     const double4 pi = pos[i];
     const int n = numneigh[i];
@@ -300,16 +303,19 @@ template <int EVFLAG, int SPLIT>
 __global__ void __launch_bounds__(EAM1T_THREADS, 2)
 k_eam_force_1t(const double4 *__restrict__ posfp, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
                int nlocal, EAMParams P, const double *__restrict__ tab1, double *__restrict__ fx, double *__restrict__ fy,
-               double *__restrict__ fz, double *__restrict__ partials, const int *__restrict__ tile_ghost, int part)
+               double *__restrict__ fz, double *__restrict__ partials, const int *__restrict__ tile_list, int part)
 {
   extern __shared__ double s_t[];  // [7][n1]: rhor c0..c2 (derivative), z2r c3..c6 (value; derivative derived)
   const int n1 = P.nr + 1;
   for (int k = threadIdx.x; k < 7 * n1; k += blockDim.x) s_t[k] = tab1[4 * n1 + k];
   __syncthreads();
-  const int i = (SPLIT == 2 ? part : 0) + blockIdx.x * blockDim.x + threadIdx.x;  // 2: range mode, see k_lj_force
+  int i = (SPLIT == 2 ? part : 0) + blockIdx.x * blockDim.x + threadIdx.x;  // 2: range mode, see k_lj_force
+  if (SPLIT == 1) {
+    const int w = i >> 5;
+    i = w < part ? tile_list[w] * TILE + (threadIdx.x & 31) : nlocal;
+  }
   double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-  bool active = i < nlocal;
-  if (SPLIT == 1 && active) active = (tile_ghost[i >> 5] != 0) == (part != 0);
+  const bool active = i < nlocal;
   if (active) {
     const double4 pi = posfp[i];
     const int n = numneigh[i];
@@ -529,13 +535,16 @@ int pair_eam_rho_part(b200md_ctx *c, int part)
   const int n = c->nlocal;
   const EAMTables &T = c->eam;
   const EAMParams P = eam_params(c);
-  const int threads = EAM1T_THREADS, blocks = cdiv(n, threads);
+  const int ntiles = cdiv(n, TILE), cnt = part ? c->ntiles_ghost : ntiles - c->ntiles_ghost;
+  const int *list = c->tile_list.p + (part ? ntiles - c->ntiles_ghost : 0);
+  const int threads = EAM1T_THREADS, blocks = cdiv(cnt * TILE, threads);
   const size_t n1 = (size_t) T.nr + 1, smemA = 4 * n1 * 8;
   TRY(dev_ensure(c, c->posfp, (size_t) n + c->nghost));
+  if (cnt == 0) return B200MD_OK;
   TRY(eam_attrs_1t(c));
   KProf kp(c, KC_EAM_RHO);
   k_eam_rho_fp_1t<0, 1><<<blocks, threads, smemA, c->stream>>>(c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->rho.p,
-                                                                c->fp.p, c->posfp.p, c->partials.p, c->tile_ghost.p, part);
+                                                                c->fp.p, c->posfp.p, c->partials.p, list, cnt);
   LAUNCH_CHECK();
   return B200MD_OK;
 }
@@ -545,12 +554,15 @@ int pair_eam_force_part(b200md_ctx *c, int part)
   const int n = c->nlocal;
   const EAMTables &T = c->eam;
   const EAMParams P = eam_params(c);
-  const int threads = EAM1T_THREADS, blocks = cdiv(n, threads);
+  const int ntiles = cdiv(n, TILE), cnt = part ? c->ntiles_ghost : ntiles - c->ntiles_ghost;
+  if (cnt == 0) return B200MD_OK;
+  const int *list = c->tile_list.p + (part ? ntiles - c->ntiles_ghost : 0);
+  const int threads = EAM1T_THREADS, blocks = cdiv(cnt * TILE, threads);
   const size_t n1 = (size_t) T.nr + 1, smemC = 7 * n1 * 8;
   TRY(eam_attrs_1t(c));
   KProf kp(c, KC_PAIR);
   k_eam_force_1t<0, 1><<<blocks, threads, smemC, c->stream>>>(c->posfp.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->f[0].p,
-                                                               c->f[1].p, c->f[2].p, c->partials.p, c->tile_ghost.p, part);
+                                                               c->f[1].p, c->f[2].p, c->partials.p, list, cnt);
   LAUNCH_CHECK();
   return B200MD_OK;
 }

@@ -45,14 +45,15 @@ template <int NC> __device__ __forceinline__ void block_partials(double (&acc)[N
 // LDS.64 gathers conflict 2.4-way: 15.9 wavefronts per step, and occupancy falls to 26 %), register tiles with
 // indexed shuffles (25-31 % lane efficiency), a Newton-3 half list (no native 64-bit shared-memory atomic add on
 // sm_100: ATOMS.CAST.SPIN loops at 104 cycles per warp step).
-// SPLIT 1 (overlap mode): only the warps (= 32-atom tiles) whose ghost flag equals `part` work, so the ghost-free
-// tiles can run while the halo is still in flight.  SPLIT 2 (host-buffer pipeline): the atom range [part, nlocal).
+// SPLIT 1 (overlap mode): warp w works on the 32-atom tile tile_list[w], w < part -- the launch covers either the
+// ghost-free tiles (they run while the halo is still in flight) or the others, each as a compact list made at the
+// rebuild, so neither launch carries idle blocks.  SPLIT 2 (host-buffer pipeline): the atom range [part, nlocal).
 template <int EVFLAG, int ONETYPE, int SPLIT>
 __global__ void __launch_bounds__(128)
 k_lj_force(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
            int nlocal, LJOne one, const double *__restrict__ tables, int ntypes, double *__restrict__ fx,
            double *__restrict__ fy, double *__restrict__ fz, double *__restrict__ partials,
-           const int *__restrict__ tile_ghost, int part)
+           const int *__restrict__ tile_list, int part)
 {
   extern __shared__ double s_tab[];
   const int nt1 = ntypes + 1, nt2 = nt1 * nt1;
@@ -61,10 +62,13 @@ k_lj_force(const double4 *__restrict__ pos, const int *__restrict__ numneigh, co
     __syncthreads();
   }
   // SPLIT == 2 (host-buffer pipeline): the atom range [part, nlocal), part a multiple of the block size
-  const int i = (SPLIT == 2 ? part : 0) + blockIdx.x * blockDim.x + threadIdx.x;
+  int i = (SPLIT == 2 ? part : 0) + blockIdx.x * blockDim.x + threadIdx.x;
+  if (SPLIT == 1) {
+    const int w = i >> 5;
+    i = w < part ? tile_list[w] * TILE + (threadIdx.x & 31) : nlocal;
+  }
   double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-  bool active = i < nlocal;
-  if (SPLIT == 1 && active) active = (tile_ghost[i >> 5] != 0) == (part != 0);
+  const bool active = i < nlocal;
   if (active) {
     const double4 pi = pos[i];
     const int trow = ONETYPE ? 0 : pos_type(pi) * nt1;
@@ -185,16 +189,19 @@ int pair_lj_compute(b200md_ctx *c, int eflag, int vflag)
   return B200MD_OK;
 }
 
-// overlap mode (capi.cu): forces of the tiles whose ghost flag equals `part`, no energy/virial tally
+// overlap mode (capi.cu): forces of the ghost-free tiles (part 0) or of the others (part 1), no energy/virial tally
 int pair_lj_compute_part(b200md_ctx *c, int part)
 {
   const int n = c->nlocal;
-  const int threads = 128, blocks = cdiv(n, threads);
+  const int ntiles = cdiv(n, TILE), cnt = part ? c->ntiles_ghost : ntiles - c->ntiles_ghost;
+  if (cnt == 0) return B200MD_OK;
+  const int *list = c->tile_list.p + (part ? ntiles - c->ntiles_ghost : 0);
+  const int threads = 128, blocks = cdiv(cnt * TILE, threads);
   LJOne one = {c->lj.h_onetype[0], c->lj.h_onetype[1], c->lj.h_onetype[2], c->lj.h_onetype[3], c->lj.h_onetype[4], c->lj.h_onetype[5]};
   const int onetype = (c->lj.ntypes == 1);
   size_t smem = onetype ? 0 : (size_t) 6 * (c->lj.ntypes + 1) * (c->lj.ntypes + 1) * sizeof(double);
   KProf kp(c, KC_PAIR);
-#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, c->tile_ghost.p, part
+#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, list, cnt
   if (onetype) k_lj_force<0, 1, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
   else k_lj_force<0, 0, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
 #undef LJ_ARGS
