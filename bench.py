@@ -748,7 +748,7 @@ def main():
         peak_src = "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "B200_PROFILING.md fallback 6650 GB/s (of fallback)"
 
         try:  # measured DRAM bytes per atom of each kernel (one ncu --set full capture, committed under profiles/)
-            dram = json.loads((ROOT / "profiles" / "r01_dram_traffic.json").read_text())
+            dram = json.loads((ROOT / "profiles" / "r02_dram_traffic.json").read_text())
         except Exception:
             dram = {}
 
@@ -763,7 +763,7 @@ def main():
             if dram_key in dram:
                 r["traffic"] = dram[dram_key]["bytes_per_atom"] * w["atoms_per_gpu"]
                 r["traffic_source"] = (f"ncu dram__bytes_read+write = {dram[dram_key]['bytes_per_atom']} B/atom on "
-                                       f"{dram[dram_key]['capture_atoms']} atoms (profiles/r01_ncu_pair_kernels.md), scaled to this launch")
+                                       f"{dram[dram_key]['capture_atoms']} atoms ({dram[dram_key].get('source', 'profiles/')}), scaled to this launch")
             return r
 
         line = {"metric": "Matom-steps/s (LJ melt, bench/in.lj scaled)", "value": lj["value"], "unit": "Matom-steps/s", "n_gpus": world,

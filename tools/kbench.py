@@ -21,6 +21,9 @@ x, v, tag, box, n = bench.make_atoms(pkg, kind, cells, (1, 1, 1), (0, 0, 0), lam
 md = bench.make_system(pkg, kind, 0, 1, 0, None, (1, 1, 1))
 md.box([0, 0, 0], box)
 md.create_atoms(x, v, np.ones(len(x), dtype=np.int32), tag)
+for kv in (sys.argv[4].split(",") if len(sys.argv) > 4 else []):   # e.g. overlap=1,build_gb=4
+    k, val = kv.split("=")
+    md.tune(k, int(val))
 md.setup()
 md.ctx.call("b200md_run", 60, md.dt, 0)  # thermalise: melt / heat the lattice
 md.ctx.call("b200md_profile", 1)
