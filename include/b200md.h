@@ -204,6 +204,14 @@ int b200md_step_host(b200md_ctx *ctx, double dt, int eflag, int vflag, int capac
  * b200md_pair_compute (lj/cut) or the two EAM passes below, then b200md_host_forces. */
 int b200md_host_atoms(b200md_ctx *ctx, int nlocal, int nghost, const double *x, const int *type,
                       const double sublo[3], const double subhi[3], int rebuild);
+/* molecular systems in host-ghost mode: the special-bond lists LAMMPS keeps on the host -- Atom::nspecial[nlocal][3]
+ * (cumulative counts of 1-2, 1-3, 1-4 partners), Atom::special[nlocal][maxspecial] (their tags), Atom::tag[nall]
+ * (src/atom.h:93-95) and Neighbor::special_flag[4] (src/neighbor.h:82; 0 drop, 1 ordinary, 2 keep with the class
+ * in the entry).  Call before the b200md_host_atoms that rebuilds the list.  The list build then follows
+ * NPair::find_special (src/npair.h:125-158) and pair lj/cut applies factor_lj = special_lj[class]
+ * (src/pair_lj_cut.cpp:103-105; the weights given to b200md_lj_init).  maxspecial == 0 turns it off. */
+int b200md_host_special(b200md_ctx *ctx, int nlocal, int nall, const int *tag, int maxspecial, const int *nspecial,
+                        const int *special, const int special_flag[4]);
 /* f[nlocal][3] = (accumulate ? f : 0) + device forces of the owned atoms, host order */
 int b200md_host_forces(b200md_ctx *ctx, double *f, int accumulate);
 /* PairEAM::compute split at its forward_comm (src/MANYBODY/pair_eam.cpp:251), which stays on the host like in

@@ -82,7 +82,7 @@ extern "C" int b200md_destroy(b200md_ctx *c)
   dev_free(c, c->perm); dev_free(c, c->scan_tmp); dev_free(c, c->binrec); dev_free(c, c->atom_sub); dev_free(c, c->numneigh); dev_free(c, c->neigh); dev_free(c, c->tile_ghost); dev_free(c, c->tile_list); dev_free(c, c->tile_pos);
   dev_free(c, c->send_idx); dev_free(c, c->border_blockcnt); dev_free(c, c->border_total); dev_free(c, c->send_dir);
   dev_free(c, c->sendbuf_i); dev_free(c, c->allcounts); dev_free(c, c->sendbuf4); dev_free(c, c->recvbuf4); dev_free(c, c->sendbuf1);
-  dev_free(c, c->partials); dev_free(c, c->stage); dev_free(c, c->peratom);
+  dev_free(c, c->partials); dev_free(c, c->stage); dev_free(c, c->peratom); dev_free(c, c->special.n3); dev_free(c, c->special.tags);
   bond_release(c);
   if (c->lj.d) cudaFree(c->lj.d);
   if (c->eam.frho) cudaFree(c->eam.frho);
@@ -318,19 +318,22 @@ extern "C" int b200md_lj_init(b200md_ctx *c, int ntypes, const double *cutsq, co
   NEED_CTX();
   if (ntypes < 1 || ntypes > B200MD_MAXTYPES) return b200md_fail(c, B200MD_ERR_ARG, "ntypes %d out of range", ntypes);
   const int nt2 = (ntypes + 1) * (ntypes + 1);
-  std::vector<double> h((size_t) 6 * nt2);
+  std::vector<double> h((size_t) 6 * nt2 + 4);   // + the four special_lj weights ([0] = 1: an ordinary neighbor)
   const double *src[6] = {cutsq, lj1, lj2, lj3, lj4, offset};
   double cutmax = 0.0;
   for (int t = 0; t < 6; t++)
     for (int k = 0; k < nt2; k++) h[(size_t) t * nt2 + k] = src[t][k];
   for (int i = 1; i <= ntypes; i++)
     for (int j = 1; j <= ntypes; j++) cutmax = fmax(cutmax, sqrt(cutsq[i * (ntypes + 1) + j]));
+  h[(size_t) 6 * nt2] = 1.0;
+  for (int k = 1; k < 4; k++) h[(size_t) 6 * nt2 + k] = special_lj ? special_lj[k] : 1.0;
   if (c->lj.d) CU(cudaFree(c->lj.d));
   CU(cudaMalloc((void **) &c->lj.d, h.size() * sizeof(double)));
   CU(cudaMemcpy(c->lj.d, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice));
   c->lj.ntypes = ntypes;
   for (int t = 0; t < 6; t++) c->lj.h_onetype[t] = src[t][(ntypes + 1) + 1];
   for (int k = 0; k < 4; k++) c->lj.special_lj[k] = special_lj ? special_lj[k] : 1.0;
+  c->lj.special_lj[0] = 1.0;
   c->pair_style = 1;
   c->cutforce = cutmax;
   if (c->ntypes == 0) c->ntypes = ntypes;
@@ -1056,6 +1059,42 @@ extern "C" int b200md_host_atoms(b200md_ctx *c, int nlocal, int nghost, const do
     CU(cudaMemsetAsync(c->flags_d, 0, 6 * sizeof(int), c->stream));
     TRY(neigh_build_lists(c));
   }
+  return B200MD_OK;
+}
+
+// host-ghost mode, molecular systems: the special-bond lists of the owned atoms and the tags of owned + ghost atoms,
+// as LAMMPS holds them (Atom::nspecial / special / tag, Neighbor::special_flag).  Call before the b200md_host_atoms that
+// rebuilds the list; maxspecial == 0 turns the special handling off.  The list build then treats a neighbor whose tag
+// is in the atom's lists exactly as NPair::find_special does (src/npair.h:125-158): dropped (flag 0), kept as an
+// ordinary neighbor (flag 1) or kept with its class in bits 28-29 of the entry (flag 2), which the lj/cut kernel
+// turns into the factor_lj of src/pair_lj_cut.cpp:103-105.
+extern "C" int b200md_host_special(b200md_ctx *c, int nlocal, int nall, const int *tag, int maxspecial, const int *nspecial,
+                                   const int *special, const int special_flag[4])
+{
+  NEED_CTX();
+  SpecialState &S = c->special;
+  if (maxspecial <= 0) {
+    S.on = false;
+    S.maxspecial = 0;
+    return B200MD_OK;
+  }
+  if (nlocal <= 0 || nall < nlocal || !tag || !nspecial || !special || !special_flag)
+    return b200md_fail(c, B200MD_ERR_ARG, "host_special: tag, nspecial, special and special_flag are required");
+  if (c->bonds.maxb > 0) return b200md_fail(c, B200MD_ERR_ARG, "host_special: the context holds device-resident bonds (b200md_set_bonds)");
+  for (int k = 1; k < 4; k++)
+    if (special_flag[k] < 0 || special_flag[k] > 2) return b200md_fail(c, B200MD_ERR_ARG, "host_special: special_flag[%d] = %d", k, special_flag[k]);
+  TRY(dev_ensure(c, c->tag, (size_t) nall));
+  TRY(dev_ensure(c, S.n3, (size_t) nlocal * 3));
+  TRY(dev_ensure(c, S.tags, (size_t) nlocal * maxspecial));
+  CU(cudaMemcpyAsync(c->tag.p, tag, (size_t) nall * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(S.n3.p, nspecial, (size_t) nlocal * 3 * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(S.tags.p, special, (size_t) nlocal * maxspecial * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaStreamSynchronize(c->stream));   // the host arrays are LAMMPS's and may move
+  S.maxspecial = maxspecial;
+  S.flag[0] = 1;
+  for (int k = 1; k < 4; k++) S.flag[k] = special_flag[k];
+  S.on = true;
+  c->list_valid = false;
   return B200MD_OK;
 }
 

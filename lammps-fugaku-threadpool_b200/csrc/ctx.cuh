@@ -92,6 +92,15 @@ struct BondState {
   FeneParams fene;
   double eng_bond = 0.0, virial_bond[6] = {0, 0, 0, 0, 0, 0};
 };
+// general special-bond lists of a molecular system whose atoms LAMMPS keeps on the host (host-ghost mode): what
+// Atom::nspecial / Atom::special hold (src/atom.h:93-95) and Neighbor::special_flag (src/neighbor.h:82)
+struct SpecialState {
+  bool on = false;
+  int maxspecial = 0;
+  int flag[4] = {1, 1, 1, 1};       // 0 exclude, 1 ordinary neighbor, 2 keep with the class in the entry's bits 28-29
+  DevBuf<int> n3;                   // [nlocal][3] cumulative counts of 1-2, 1-3, 1-4 partners
+  DevBuf<int> tags;                 // [nlocal][maxspecial] partner tags
+};
 struct RanMarsHost {          // src/random_mars.cpp
   double u[98], c, cd, cm;
   int i97, j97;
@@ -208,6 +217,7 @@ struct b200md_ctx {
 
   // in.chain additions
   BondState bonds;
+  SpecialState special;
   LangevinState langevin;
 
   // run state

@@ -388,7 +388,7 @@ __device__ __forceinline__ BinRec ld_rec(const BinRec *__restrict__ p)
   return r;
 }
 
-// BONDED (in.chain): a candidate within the cutoff whose tag is one of the atom's 1-2 partners is NOT listed
+// BONDED == 1 (in.chain): a candidate within the cutoff whose tag is one of the atom's 1-2 partners is NOT listed
 // (special_bonds lj weight 0, NPair::find_special src/npair.h:125-158 -> -1) but recorded as the device index of that
 // bond partner; of several periodic images the closest wins (Domain::closest_image).
 struct BondBuild {
@@ -397,6 +397,11 @@ struct BondBuild {
   const int *partner_by_tag;   // [ntags][maxb], 0 = empty
   int *bond_idx;               // [nlocal][maxb] out
   int maxb;
+  // BONDED == 2 (host-ghost molecular systems): the general special-bond lists, NPair::find_special (src/npair.h:125-158)
+  const int *spec_n3;          // [nlocal][3] cumulative counts of 1-2, 1-3, 1-4 partners
+  const int *spec_tags;        // [nlocal][maxspecial]
+  int maxspecial;
+  int flag[4];                 // 0 drop, 1 ordinary neighbor, 2 keep with the class in bits 28-29 of the entry
 };
 #define SEG_THREADS 128
 // shared-memory plan of a segment: SoA candidate arrays of `cap` elements (cap a multiple of 4, every staged bin padded
@@ -521,7 +526,7 @@ k_build_seg(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int
     bool ghost_near = false;   // overlap mode: a ghost record among my candidates (a superset of "a ghost in my list")
     int ptag[B200MD_MAXBONDS], pbest[B200MD_MAXBONDS];
     float prsq[B200MD_MAXBONDS];
-    if (BONDED) {
+    if (BONDED == 1) {
       const int ti = bb.tag[i];
 #pragma unroll
       for (int m = 0; m < B200MD_MAXBONDS; m++) {
@@ -543,7 +548,8 @@ k_build_seg(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int
     auto append = [&](const int jt, const float rsq, const int k, bool accept) {
       const int j = ONETYPE ? jt : (jt & BR_JMASK);   // one type: the type bits are zero
       accept = accept && j != i;
-      if (BONDED && accept) {
+      int entry = j;
+      if (BONDED == 1 && accept) {
         const int tj = s_tag[k];
 #pragma unroll
         for (int m = 0; m < B200MD_MAXBONDS; m++)
@@ -552,7 +558,19 @@ k_build_seg(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int
             if (rsq < prsq[m]) { prsq[m] = rsq; pbest[m] = j; }
           }
       }
-      if (accept) nbp[(size_t) min(n, nlastrow) * TILE] = j;
+      if (BONDED == 2 && accept) {   // NPair::find_special: first match in the atom's 1-2 | 1-3 | 1-4 list decides
+        const int tj = s_tag[k];
+        const int n1 = bb.spec_n3[3 * i], n2 = bb.spec_n3[3 * i + 1], n3 = bb.spec_n3[3 * i + 2];
+        const int *sp = bb.spec_tags + (size_t) i * bb.maxspecial;
+        for (int m = 0; m < n3; m++)
+          if (sp[m] == tj) {
+            const int which = m < n1 ? 1 : (m < n2 ? 2 : 3);
+            if (bb.flag[which] == 0) accept = false;
+            else if (bb.flag[which] == 2) entry = j | (which << CLBITS);
+            break;
+          }
+      }
+      if (accept) nbp[(size_t) min(n, nlastrow) * TILE] = entry;
       n += accept ? 1 : 0;
     };
 #pragma unroll 1
@@ -631,7 +649,7 @@ k_build_seg(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int
       }
     }
     numneigh[i] = n;
-    if (BONDED) {
+    if (BONDED == 1) {
 #pragma unroll
       for (int m = 0; m < B200MD_MAXBONDS; m++)
         if (m < bb.maxb) {
@@ -821,7 +839,7 @@ int neigh_build_lists(b200md_ctx *c)
       KProf kp(c, KC_NEIGH);
       BinRec *rec = reinterpret_cast<BinRec *>(c->binrec.p);
       int *rec_tag = nullptr;
-      if (c->bonds.maxb > 0) {
+      if (c->bonds.maxb > 0 || c->special.on) {
         TRY(dev_ensure(c, c->binrec_tag, (size_t) nall));
         rec_tag = c->binrec_tag.p;
       }
@@ -837,8 +855,16 @@ int neigh_build_lists(b200md_ctx *c)
         tile_ghost = c->tile_ghost.p;
       }
       c->tiles_valid = tile_ghost != nullptr;
-      BondBuild bb = {nullptr, nullptr, nullptr, nullptr, 0};
-      const bool bonded = c->bonds.maxb > 0;
+      BondBuild bb = {nullptr, nullptr, nullptr, nullptr, 0, nullptr, nullptr, 0, {1, 1, 1, 1}};
+      const bool bonded = c->bonds.maxb > 0, special = c->special.on && !bonded;
+      if (special) {
+        if (!c->host_ghosts) return b200md_fail(c, B200MD_ERR_ARG, "general special-bond lists are a host-ghost mode feature (b200md_host_special)");
+        bb.rec_tag = c->binrec_tag.p;
+        bb.spec_n3 = c->special.n3.p;
+        bb.spec_tags = c->special.tags.p;
+        bb.maxspecial = c->special.maxspecial;
+        for (int k = 0; k < 4; k++) bb.flag[k] = c->special.flag[k];
+      }
       if (bonded) {
         TRY(dev_ensure(c, c->bonds.idx, (size_t) n * c->bonds.maxb));
         bb.rec_tag = c->binrec_tag.p;
@@ -854,12 +880,12 @@ int neigh_build_lists(b200md_ctx *c)
       tg = tg < 1 ? 1 : (tg > g.nbin[0] ? g.nbin[0] : tg);
       // staging area: the 3 x 3 x (tg + 2) bins of a segment with 8 % head room; a denser segment reports its size
       // through flags[6] and the build is redone with room for it (like the maxneigh retry below)
-      const size_t rec_bytes = bonded ? 20 : 16;
+      const size_t rec_bytes = (bonded || special) ? 20 : 16;
       auto seg_smem = [&](int t, int cap) { return (size_t) cap * rec_bytes + (size_t) (2 * 9 * (t + 3)) * sizeof(int); };
       if (c->seg_cap_tg != tg) { c->seg_cap = 0; c->seg_cap_tg = tg; }
       if (c->seg_cap == 0 && c->seg_cap_user > 0) c->seg_cap = (c->seg_cap_user + 3) & ~3;   // test knob: start too small, exercise the retry
       // (every staged bin is padded to a multiple of vw records: + (vw - 1) / 2 on average)
-      const int vw = per_bin >= 8.0 ? 4 : 2;
+      const int vw = (per_bin >= 8.0 && !(c->special.on && c->bonds.maxb == 0)) ? 4 : 2;
       if (c->seg_cap == 0) c->seg_cap = (int) (1.08 * 9.0 * (tg + 2) * ((double) nall / (nown > 0 ? nown : 1) + 0.5 * (vw - 1))) + 64;
       if (c->seg_cap > nall + 27 * (tg + 2)) c->seg_cap = nall + 27 * (tg + 2);   // no segment can stage more than exists
       c->seg_cap = (c->seg_cap + 3) & ~3;
@@ -881,6 +907,7 @@ int neigh_build_lists(b200md_ctx *c)
         CU(cudaFuncSetAttribute(k_build_seg<0, 0, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(cudaFuncSetAttribute(k_build_seg<1, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(cudaFuncSetAttribute(k_build_seg<0, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(cudaFuncSetAttribute(k_build_seg<0, 2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr_done[c->device & 63] = true;
       }
       const size_t bsmem = seg_smem(tg, c->seg_cap);
@@ -888,7 +915,9 @@ int neigh_build_lists(b200md_ctx *c)
 #define BB_LAUNCH(OT, BD, V) k_build_seg<OT, BD, V><<<bgrid, SEG_THREADS, bsmem, c->stream>>>(BB_ARGS)
       const int bgrid = cdiv(g.nbin[0], tg) * g.nbin[1] * g.nbin[2];
       const int ot = c->ntypes == 1;
-      if (vw == 4) {
+      if (special) {   // molecular systems under the stock loop: the multi-type kernel, narrow vectors (small systems)
+        BB_LAUNCH(0, 2, 2);
+      } else if (vw == 4) {
         if (bonded) { if (ot) BB_LAUNCH(1, 1, 4); else BB_LAUNCH(0, 1, 4); }
         else { if (ot) BB_LAUNCH(1, 0, 4); else BB_LAUNCH(0, 0, 4); }
       } else {

@@ -55,10 +55,10 @@ k_lj_force(const double4 *__restrict__ pos, const int *__restrict__ numneigh, co
            double *__restrict__ fy, double *__restrict__ fz, double *__restrict__ partials,
            const int *__restrict__ tile_list, int part)
 {
-  extern __shared__ double s_tab[];
+  extern __shared__ double s_tab[];   // 6 tables of (ntypes+1)^2, then special_lj[4] ([0] = 1), when !ONETYPE
   const int nt1 = ntypes + 1, nt2 = nt1 * nt1;
   if (!ONETYPE) {
-    for (int k = threadIdx.x; k < 6 * nt2; k += blockDim.x) s_tab[k] = tables[k];
+    for (int k = threadIdx.x; k < 6 * nt2 + 4; k += blockDim.x) s_tab[k] = tables[k];
     __syncthreads();
   }
   // SPLIT == 2 (host-buffer pipeline): the atom range [part, nlocal), part a multiple of the block size
@@ -105,10 +105,13 @@ k_lj_force(const double4 *__restrict__ pos, const int *__restrict__ numneigh, co
           cutsq = s_tab[t]; lj1 = s_tab[nt2 + t]; lj2 = s_tab[2 * nt2 + t];
         }
         const bool in = rsq < cutsq && (k0 + u < n);
+        // factor_lj of src/pair_lj_cut.cpp:103-105: the special-bond class sits in bits 28-29 of the entry (0 = ordinary
+        // neighbor, weight 1); single-type systems are atomic, their entries carry no class
+        const double factor_lj = ONETYPE ? 1.0 : s_tab[6 * nt2 + ((ent[u] >> CLBITS) & 3u)];
         const double r2inv = rcp_pos(rsq);
         const double r6inv = r2inv * r2inv * r2inv;
         const double forcelj = r6inv * (lj1 * r6inv - lj2);
-        const double fpair = in ? forcelj * r2inv : 0.0;
+        const double fpair = in ? factor_lj * forcelj * r2inv : 0.0;
         fxi += dx * fpair;
         fyi += dy * fpair;
         fzi += dz * fpair;
@@ -120,7 +123,7 @@ k_lj_force(const double4 *__restrict__ pos, const int *__restrict__ numneigh, co
             const int t = trow + pos_type(pj[u]);
             lj3 = s_tab[3 * nt2 + t]; lj4 = s_tab[4 * nt2 + t]; off = s_tab[5 * nt2 + t];
           }
-          acc[0] += in ? 0.5 * (r6inv * (lj3 * r6inv - lj4) - off) : 0.0;
+          acc[0] += in ? 0.5 * factor_lj * (r6inv * (lj3 * r6inv - lj4) - off) : 0.0;
           const double hf = 0.5 * fpair;
           acc[1] += dx * dx * hf;
           acc[2] += dy * dy * hf;
@@ -170,8 +173,8 @@ int pair_lj_compute(b200md_ctx *c, int eflag, int vflag)
   const int ev = (eflag || vflag) ? 1 : 0;
   if (ev) TRY(dev_ensure(c, c->partials, (size_t) blocks * 8));
   LJOne one = {c->lj.h_onetype[0], c->lj.h_onetype[1], c->lj.h_onetype[2], c->lj.h_onetype[3], c->lj.h_onetype[4], c->lj.h_onetype[5]};
-  const int onetype = (c->lj.ntypes == 1);
-  size_t smem = onetype ? 0 : (size_t) 6 * (c->lj.ntypes + 1) * (c->lj.ntypes + 1) * sizeof(double);
+  const int onetype = (c->lj.ntypes == 1) && !c->special.on;
+  size_t smem = onetype ? 0 : ((size_t) 6 * (c->lj.ntypes + 1) * (c->lj.ntypes + 1) + 4) * sizeof(double);
   {
     KProf kp(c, KC_PAIR);
 #define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, -1
@@ -198,8 +201,8 @@ int pair_lj_compute_part(b200md_ctx *c, int part)
   const int *list = c->tile_list.p + (part ? ntiles - c->ntiles_ghost : 0);
   const int threads = 128, blocks = cdiv(cnt * TILE, threads);
   LJOne one = {c->lj.h_onetype[0], c->lj.h_onetype[1], c->lj.h_onetype[2], c->lj.h_onetype[3], c->lj.h_onetype[4], c->lj.h_onetype[5]};
-  const int onetype = (c->lj.ntypes == 1);
-  size_t smem = onetype ? 0 : (size_t) 6 * (c->lj.ntypes + 1) * (c->lj.ntypes + 1) * sizeof(double);
+  const int onetype = (c->lj.ntypes == 1) && !c->special.on;
+  size_t smem = onetype ? 0 : ((size_t) 6 * (c->lj.ntypes + 1) * (c->lj.ntypes + 1) + 4) * sizeof(double);
   KProf kp(c, KC_PAIR);
 #define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, list, cnt
   if (onetype) k_lj_force<0, 1, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
@@ -218,8 +221,8 @@ int pair_lj_compute_range(b200md_ctx *c, int first, int count)
   const int threads = 128, blocks = cdiv(count, threads);
   if (first % threads) return b200md_fail(c, B200MD_ERR_ARG, "pair range must start at a multiple of %d", threads);
   LJOne one = {c->lj.h_onetype[0], c->lj.h_onetype[1], c->lj.h_onetype[2], c->lj.h_onetype[3], c->lj.h_onetype[4], c->lj.h_onetype[5]};
-  const int onetype = (c->lj.ntypes == 1);
-  size_t smem = onetype ? 0 : (size_t) 6 * (c->lj.ntypes + 1) * (c->lj.ntypes + 1) * sizeof(double);
+  const int onetype = (c->lj.ntypes == 1) && !c->special.on;
+  size_t smem = onetype ? 0 : ((size_t) 6 * (c->lj.ntypes + 1) * (c->lj.ntypes + 1) + 4) * sizeof(double);
   KProf kp(c, KC_PAIR);
 #define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, first + count, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, first
   if (onetype) k_lj_force<0, 1, 2><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
@@ -247,15 +250,17 @@ k_lj_peratom(const double4 *__restrict__ pos, const int *__restrict__ numneigh, 
   const int *nb = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
   double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
   for (int k = 0; k < n; k++) {
-    const int j = __ldg(nb + (size_t) k * TILE) & CLJMASK;
+    const unsigned ent = (unsigned) __ldg(nb + (size_t) k * TILE);
+    const int j = (int) (ent & CLJMASK);
+    const double factor_lj = __ldg(tables + 6 * nt2 + ((ent >> CLBITS) & 3u));
     const double4 pj = pos[j];
     const double dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
     const double rsq = dx * dx + dy * dy + dz * dz;
     const int t = trow + pos_type(pj);
     if (rsq >= __ldg(tables + t)) continue;
     const double r2inv = 1.0 / rsq, r6inv = r2inv * r2inv * r2inv;
-    const double fpair = r6inv * (__ldg(tables + nt2 + t) * r6inv - __ldg(tables + 2 * nt2 + t)) * r2inv;
-    acc[0] += 0.5 * (r6inv * (__ldg(tables + 3 * nt2 + t) * r6inv - __ldg(tables + 4 * nt2 + t)) - __ldg(tables + 5 * nt2 + t));
+    const double fpair = factor_lj * r6inv * (__ldg(tables + nt2 + t) * r6inv - __ldg(tables + 2 * nt2 + t)) * r2inv;
+    acc[0] += 0.5 * factor_lj * (r6inv * (__ldg(tables + 3 * nt2 + t) * r6inv - __ldg(tables + 4 * nt2 + t)) - __ldg(tables + 5 * nt2 + t));
     const double hf = 0.5 * fpair;
     acc[1] += dx * dx * hf;
     acc[2] += dy * dy * hf;

@@ -33,9 +33,10 @@ PairLJCutB200::~PairLJCutB200()
 void PairLJCutB200::init_style()
 {
   if (!force->newton_pair && comm_forward) {}    // newton on/off both fine: the device list is a full list
-  // bonded systems (special-bond exclusion in the neighbor build) run inside the device-resident loop only
-  if (atom->molecular != Atom::ATOMIC && strcmp(update->integrate_style, "verlet/b200") != 0)
-    error->all(FLERR, "Pair style lj/cut/b200 with a bonded atom style requires run_style verlet/b200");
+  // molecular systems: under the stock loop the device list build applies the host's special-bond lists
+  // (b200md_host_special: any special_bonds weights); the device-resident loop serves fene bonds with
+  // special_bonds fene only (VerletB200::init checks)
+  if (atom->molecular == Atom::TEMPLATE) error->all(FLERR, "Pair style lj/cut/b200 does not support atom_style template");
   cut_respa = nullptr;    // PairLJCut::init_style sets it (its constructor does not); init_one reads it
   // no host NeighList is requested: Neighbor still runs decide/exchange/borders, the list lives on the device
   tables_loaded = 0;
@@ -62,12 +63,19 @@ void PairLJCutB200::compute(int eflag, int vflag)
 {
   ev_init(eflag, vflag);
   if (dev->resident) return;
-  if (atom->molecular != Atom::ATOMIC)
-    error->all(FLERR, "Pair style lj/cut/b200: bonded systems are served by the device-resident loop only");
   if (!tables_loaded) device_tables(dev);
 
   const int nlocal = atom->nlocal, nghost = atom->nghost;
   if (nlocal == 0) return;
+  if (neighbor->ago == 0) {
+    // the special-bond lists as Neighbor would hand them to NPair::find_special (src/npair.h:125-158); tagint is int
+    // (LAMMPS_SMALLBIG) and Atom's 2-d arrays are contiguous (Memory::create)
+    if (atom->molecular == Atom::MOLECULAR && atom->maxspecial > 0)
+      B200_CHECK(dev, b200md_host_special(dev->ctx, nlocal, nlocal + nghost, atom->tag, atom->maxspecial, &atom->nspecial[0][0],
+                                          &atom->special[0][0], neighbor->special_flag));
+    else
+      B200_CHECK(dev, b200md_host_special(dev->ctx, nlocal, nlocal + nghost, nullptr, 0, nullptr, nullptr, nullptr));
+  }
   B200_CHECK(dev, b200md_host_atoms(dev->ctx, nlocal, nghost, &atom->x[0][0], atom->type, domain->sublo, domain->subhi,
                                     neighbor->ago == 0));
   double e = 0.0, v[6] = {0, 0, 0, 0, 0, 0};

@@ -73,6 +73,7 @@ PROTOTYPES = {
     "b200md_kernel_times": (_i, [_vp, _vp, _vp, _i]),
     "b200md_stream": (_vp, [_vp]),
     "b200md_tune": (_i, [_vp, C.c_char_p, _i]),
+    "b200md_host_special": (_i, [_vp, _i, _i, _vp, _i, _vp, _vp, _vp]),
     "b200md_build_bins_per_block": (_i, [_vp]),
 }
 

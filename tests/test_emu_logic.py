@@ -191,6 +191,12 @@ def test_emu_lammps_unittest_eam_yaml(emu_lmp, name, units, tmp_path):
     lh.test_reference_unittest_eam_yaml_through_lammps(name, units, tmp_path)
 
 
+def test_emu_lammps_unittest_mol_pair_lj_cut_yaml(emu_lmp, tmp_path):
+    """molecular system under the stock loop: special-bond lists from the host applied in the device list build, factor_lj
+    in the multi-type lj kernel -- the reference's mol-pair-lj_cut.yaml"""
+    lh.test_reference_unittest_mol_pair_lj_cut_yaml_through_lammps(tmp_path)
+
+
 def test_emu_lammps_thin_box_refused(emu_lmp, tmp_path):
     lh.test_thin_box_is_refused_by_the_resident_loop(tmp_path)
 

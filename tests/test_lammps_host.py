@@ -247,6 +247,91 @@ def test_reference_unittest_eam_yaml_through_lammps(name, units, tmp_path):
         assert abs(e - float(g[f"{phase}_vdwl"])) <= 1e-10 * abs(float(g[f"{phase}_vdwl"])), phase
 
 
+# ---- the reference's own known-answer test for pair lj/cut on a MOLECULAR system (special_bonds weights) ----
+IN_FOURMOL = """atom_style full
+atom_modify map array
+neigh_modify delay 2 every 2 check no
+units real
+timestep 0.1
+newton on on
+special_bonds lj/coul 0.1 0.25 0.5
+pair_style lj/cut 8.0
+bond_style zero
+read_data data.fourmol
+bond_coeff *
+{coeffs}
+pair_modify mix arithmetic
+pair_modify shift yes
+{runstyle}
+thermo_style custom step pe evdwl
+thermo_modify format float %.17g
+run 0 post no
+write_dump all custom init.txt id fx fy fz modify sort id format float %.17g
+fix 1 all nve
+thermo 2
+run 4 post no
+write_dump all custom run.txt id fx fy fz modify sort id format float %.17g
+"""
+
+
+def write_data_fourmol(g, path):
+    """tests/golden/unittest_mol_pair_lj_cut.npz back into a data file: the atoms, velocities and BONDS of
+    unittest/force-styles/tests/data.fourmol.  Its angles / dihedrals / impropers are left out: with the default
+    `special_bonds ... angle no dihedral no` the 1-2 / 1-3 / 1-4 lists follow from the bond graph alone (the reference
+    run on this file reproduces the YAML's forces to 3e-16, tests/golden/make_unittest_golden.py)."""
+    n, nb = len(g["tag"]), len(g["bonds"])
+    L = ["LAMMPS data file (tests/golden/unittest_mol_pair_lj_cut.npz <- unittest/force-styles/tests/data.fourmol)", "",
+         f"{n} atoms", f"{len(g['mass']) - 1} atom types", f"{nb} bonds", f"{int(g['bonds'][:, 0].max())} bond types", ""]
+    for k, ax in enumerate("xyz"):
+        L.append(f"{g['boxlo'][k]:.17g} {g['boxhi'][k]:.17g} {ax}lo {ax}hi")
+    L += ["", "Masses", ""] + [f"{t} {g['mass'][t]:.17g}" for t in range(1, len(g["mass"]))] + ["", "Atoms # full", ""]
+    for i in range(n):
+        x, im = g["x"][i], g["image"][i]
+        L.append(f"{g['tag'][i]} {g['mol'][i]} {g['type'][i]} {g['q'][i]:.17g} {x[0]:.17g} {x[1]:.17g} {x[2]:.17g} {im[0]} {im[1]} {im[2]}")
+    L += ["", "Velocities", ""] + [f"{g['tag'][i]} {g['v'][i][0]:.17g} {g['v'][i][1]:.17g} {g['v'][i][2]:.17g}" for i in range(n)]
+    L += ["", "Bonds", ""] + [f"{k + 1} {t} {a} {b}" for k, (t, a, b) in enumerate(g["bonds"])]
+    path.write_text("\n".join(L) + "\n")
+
+
+def fourmol_input(g, runstyle):
+    coeffs = "\n".join(f"pair_coeff {int(a)} {int(b)} {e:.17g} {s:.17g}" for a, b, e, s in g["pair_coeff"])
+    return IN_FOURMOL.format(coeffs=coeffs, runstyle=runstyle)
+
+
+def test_fourmol_data_file_reproduces_the_yaml_with_the_reference(tmp_path):
+    """CPU: the regenerated data file (atoms + bonds only) through the UNMODIFIED reference gives the YAML's forces and
+    energies -- so the GPU-side test below needs nothing from /root/reference"""
+    build_host()
+    g = dict(np.load(ROOT / "tests" / "golden" / "unittest_mol_pair_lj_cut.npz"))
+    write_data_fourmol(g, tmp_path / "data.fourmol")
+    r = run_lmp(LMP_REF, fourmol_input(g, ""), tmp_path)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    for phase in ("init", "run"):
+        f = read_forces(tmp_path / f"{phase}.txt")
+        assert np.abs(f - g[f"{phase}_forces"]).max() <= 1e-13 * np.abs(g[f"{phase}_forces"]).max()
+
+
+@pytest.mark.gpu
+def test_reference_unittest_mol_pair_lj_cut_yaml_through_lammps(tmp_path):
+    """mol-pair-lj_cut.yaml (29 atoms, 5 types, arithmetic mixing, shifted, special_bonds lj/coul 0.1 0.25 0.5, a 15 A
+    box under an 8 A cutoff) through `lmp_b200 -sf b200` under the stock Verlet loop: pair lj/cut/b200 in host-ghost mode
+    with the host's special-bond lists applied inside the device list build (NPair::find_special) and factor_lj in the
+    multi-type force kernel.  Tolerance: forces 1e-10 of max|f| (north_star), energy 1e-10 relative."""
+    if not LMP_B200.exists():
+        pytest.skip("oracle/_ref host binaries not shipped")
+    g = dict(np.load(ROOT / "tests" / "golden" / "unittest_mol_pair_lj_cut.npz"))
+    write_data_fourmol(g, tmp_path / "data.fourmol")
+    r = run_lmp(LMP_B200, fourmol_input(g, STOCK_LOOP), tmp_path, ["-sf", "b200"])
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert "b200: pair lj/cut/b200 on CUDA device" in r.stdout, r.stdout[-2000:]
+    pe = [row[1] for row in thermo_rows_generic(r.stdout, "Step", "PotEng")]
+    for phase, e in (("init", pe[0]), ("run", pe[-1])):
+        f = read_forces(tmp_path / f"{phase}.txt")
+        ref = g[f"{phase}_forces"]
+        assert np.abs(f - ref).max() <= 1e-10 * np.abs(ref).max(), phase
+        assert abs(e - float(g[f"{phase}_vdwl"])) <= 1e-10 * abs(float(g[f"{phase}_vdwl"])), phase
+
+
 @pytest.mark.gpu
 def test_thin_box_is_refused_by_the_resident_loop(tmp_path):
     """the device makes its ghosts in one stage, which needs sub-domains at least one ghost cutoff wide: the 7 A box
