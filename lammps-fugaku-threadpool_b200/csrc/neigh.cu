@@ -549,14 +549,21 @@ k_build_seg(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int
       const int j = ONETYPE ? jt : (jt & BR_JMASK);   // one type: the type bits are zero
       accept = accept && j != i;
       int entry = j;
-      if (BONDED == 1 && accept) {
+      if (BONDED == 1) {
+        // branch-free: with 2 bonds per bead some lane of a warp meets a partner at most steps, and a divergent body
+        // run by 3-4 lanes was a fifth of this kernel's instructions (ncu source view, profiles/r02_ncu_build.md).
+        // Empty slots hold tag 0, padding records carry tag 0 but are never accepted.
         const int tj = s_tag[k];
+        bool partner = false;
 #pragma unroll
-        for (int m = 0; m < B200MD_MAXBONDS; m++)
-          if (ptag[m] != 0 && tj == ptag[m]) {
-            accept = false;
-            if (rsq < prsq[m]) { prsq[m] = rsq; pbest[m] = j; }
-          }
+        for (int m = 0; m < B200MD_MAXBONDS; m++) {
+          const bool hit = accept && tj == ptag[m];
+          const bool closer = hit && rsq < prsq[m];
+          partner |= hit;
+          prsq[m] = closer ? rsq : prsq[m];
+          pbest[m] = closer ? j : pbest[m];
+        }
+        accept = accept && !partner;
       }
       if (BONDED == 2 && accept) {   // NPair::find_special: first match in the atom's 1-2 | 1-3 | 1-4 list decides
         const int tj = s_tag[k];

@@ -341,3 +341,90 @@ def test_large_lj_properties(pkg):
     assert abs(e1 - e0) < 2e-2  # the 32k reference drifts -4.6134 -> -4.6224 over the same 100 steps
     assert abs(e1 - (-4.6223613)) < 2e-3  # intensive quantity: same ensemble as the 32k log
     md.close()
+
+
+def test_host_ghost_special_bonds_vs_direct_sum(pkg):
+    """b200md_host_special through the C ABI alone (no LAMMPS host): a 96-atom chain molecule in an open box, two types,
+    special_lj = (-, 0.0, 0.3, 0.7) with flags (1, 0, 2, 2).  Forces and energy against a direct O(N^2) sum with the
+    same weights (NPair::find_special semantics: first match in the 1-2 | 1-3 | 1-4 list decides; src/npair.h:125-158,
+    factor_lj src/pair_lj_cut.cpp:103-105); the exported list has no 1-2 pairs."""
+    import ctypes as C
+
+    rng = np.random.default_rng(7)
+    n, cutoff, skin = 96, 3.0, 0.3
+    x = np.zeros((n, 3))
+    x[0] = 8.0
+    for i in range(1, n):   # a self-avoiding-ish random walk of step 1.05
+        for _ in range(200):
+            d = rng.normal(size=3)
+            cand = x[i - 1] + 1.05 * d / np.linalg.norm(d)
+            if (np.linalg.norm(x[:i - 1] - cand, axis=1) > 0.95).all() if i > 1 else True:
+                break
+        x[i] = cand
+    typ = (1 + (np.arange(n) % 2)).astype(np.int32)
+    tag = np.arange(1, n + 1, dtype=np.int32)
+    lo, hi = x.min(0) - 4.0, x.max(0) + 4.0
+    md = pkg.B200MD("lj", 2)
+    md.box(lo, hi, periodic=(0, 0, 0))
+    md.set_mass(1, 1.0)
+    md.set_mass(2, 1.0)
+    p = md.pair_style("lj/cut", cutoff)
+    p.coeff(1, 1, 1.0, 1.0, cutoff)
+    p.coeff(2, 2, 0.7, 1.1, cutoff)
+    p.modify(shift=True, mix="arithmetic")
+    special_lj = np.array([1.0, 0.0, 0.3, 0.7])
+    p.special_lj[:] = special_lj
+    md.neighbor.set(skin, "bin")
+    md.init()
+    # Atom::nspecial (cumulative) / Atom::special as LAMMPS holds them for a linear chain
+    maxsp = 6
+    nsp = np.zeros((n, 3), dtype=np.int32)
+    sp = np.zeros((n, maxsp), dtype=np.int32)
+    for i in range(n):
+        m = 0
+        for k, dist in enumerate((1, 2, 3)):
+            for j in (i - dist, i + dist):
+                if 0 <= j < n:
+                    sp[i, m] = tag[j]
+                    m += 1
+            nsp[i, k] = m
+    flag = np.array([1, 0, 2, 2], dtype=np.int32)
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)
+    md.ctx.call("b200md_host_special", n, n, vp(tag), maxsp, vp(nsp), vp(sp), vp(flag))
+    md.ctx.call("b200md_host_atoms", n, 0, vp(x), vp(typ), vp(np.asarray(lo, dtype=np.float64)), vp(np.asarray(hi, dtype=np.float64)), 1)
+    e, vir = C.c_double(0), np.zeros(6)
+    md.ctx.call("b200md_pair_compute", 1, 1, C.byref(e), vp(vir))
+    f = np.zeros((n, 3))
+    md.ctx.call("b200md_host_forces", vp(f), 0)
+    # direct sum
+    t = p.tables
+    fr, er = np.zeros((n, 3)), 0.0
+    for i in range(n):
+        for j in range(n):
+            if i == j:
+                continue
+            d = abs(i - j)
+            w = special_lj[d] if d <= 3 else 1.0
+            if w == 0.0:
+                continue
+            a, b = typ[i], typ[j]
+            dx = x[i] - x[j]
+            rsq = dx @ dx
+            if rsq >= t["cutsq"][a, b]:
+                continue
+            r2 = 1.0 / rsq
+            r6 = r2 ** 3
+            fr[i] += dx * (w * r6 * (t["lj1"][a, b] * r6 - t["lj2"][a, b]) * r2)
+            er += 0.5 * w * (r6 * (t["lj3"][a, b] * r6 - t["lj4"][a, b]) - t["offset"][a, b])
+    assert np.abs(f - fr).max() <= 1e-11 * np.abs(fr).max()
+    assert abs(e.value - er) <= 1e-11 * abs(er)
+    numneigh, neigh = md.neighbor_list()
+    first = np.concatenate([[0], np.cumsum(numneigh)])
+    for i in range(n):
+        nb = neigh[first[i]:first[i + 1]]
+        assert not ({i - 1, i + 1} & set(nb.tolist())), i   # 1-2 partners (weight 0) are not listed
+    md.ctx.call("b200md_host_special", n, n, None, 0, None, None, None)   # off again: an atomic system
+    md.ctx.call("b200md_host_atoms", n, 0, vp(x), vp(typ), vp(np.asarray(lo, dtype=np.float64)), vp(np.asarray(hi, dtype=np.float64)), 1)
+    numneigh2, _ = md.neighbor_list()
+    assert numneigh2.sum() > numneigh.sum()
+    md.close()
