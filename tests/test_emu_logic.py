@@ -128,6 +128,15 @@ def test_emu_bins_per_warp_same_list_order(emu, oracle, kind, steps):
         assert np.array_equal(g["x"], out[0][0]["x"]) and np.array_equal(g["f"], out[0][0]["f"])
 
 
+@pytest.mark.parametrize("ntypes", [1, 3])
+def test_emu_dilute_gas_and_special_bonds_direct_sums(emu, ntypes):
+    """oracle-independent checks: a dilute gas (empty and ragged bins, vector width 2, one and three types) and, once,
+    the special-bond path through the C ABI, each against a direct O(N^2) sum"""
+    gp.test_dilute_gas_vs_direct_sum(emu, ntypes)
+    if ntypes == 1:
+        gp.test_host_ghost_special_bonds_vs_direct_sum(emu)
+
+
 def test_emu_piecewise_api_and_error_paths(emu):
     gp.test_piecewise_api_equals_device_loop(emu)
     gp.test_error_paths(emu)

@@ -428,3 +428,58 @@ def test_host_ghost_special_bonds_vs_direct_sum(pkg):
     numneigh2, _ = md.neighbor_list()
     assert numneigh2.sum() > numneigh.sum()
     md.close()
+
+
+@pytest.mark.parametrize("ntypes", [1, 3])
+def test_dilute_gas_vs_direct_sum(pkg, ntypes):
+    """ragged input: a dilute periodic gas (density 0.02: most bins empty, many atoms without any neighbor) through the
+    sparse-bin form of the list build (vector width 2).  The list equals the brute-force minimum-image pair set and the
+    forces / energy equal a direct O(N^2) sum at 1e-11 -- an oracle-independent check of empty and ragged bins."""
+    rng = np.random.default_rng(11 + ntypes)
+    n, L, cutoff, skin = 1500, 42.0, 2.5, 0.3
+    x = np.zeros((n, 3))
+    k = 0
+    while k < n:   # random insertion with a 0.9 sigma exclusion radius
+        c = rng.uniform(0, L, 3)
+        d = x[:k] - c
+        d -= L * np.round(d / L)
+        if k == 0 or (np.einsum("ij,ij->i", d, d) > 0.81).all():
+            x[k] = c
+            k += 1
+    typ = rng.integers(1, ntypes + 1, n).astype(np.int32)
+    tag = np.arange(1, n + 1, dtype=np.int32)
+    md = pkg.B200MD("lj", ntypes)
+    md.box([0, 0, 0], [L] * 3)
+    p = md.pair_style("lj/cut", cutoff)
+    for t in range(1, ntypes + 1):
+        md.set_mass(t, 1.0 + 0.5 * t)
+        p.coeff(t, t, 1.0 / t, 1.0 + 0.05 * t, cutoff - 0.1 * (t - 1))
+    p.modify(shift=True, mix="arithmetic")
+    md.neighbor.set(skin, "bin")
+    md.neighbor.modify(every=1, delay=0, check=1)
+    md.create_atoms(x, np.zeros((n, 3)), typ, tag)
+    md.setup()
+    t = p.tables
+    cut = np.sqrt(t["cutsq"])
+    # brute force with minimum image
+    d = x[:, None, :] - x[None, :, :]
+    d -= L * np.round(d / L)
+    rsq = np.einsum("ijk,ijk->ij", d, d)
+    np.fill_diagonal(rsq, 1e30)
+    cn = (cut + skin)[typ[:, None], typ[None, :]]
+    want_pairs = {(int(tag[i]), int(tag[j])) for i, j in zip(*np.nonzero(rsq <= cn * cn))}
+    got = md.neighbor_tag_pairs()
+    assert {(int(a), int(b)) for a, b in got} == want_pairs and len(got) == len(want_pairs)
+    numneigh, _ = md.neighbor_list()
+    assert (numneigh == 0).sum() > 10          # the case really has isolated atoms
+    inr = rsq < t["cutsq"][typ[:, None], typ[None, :]]
+    r2 = np.where(inr, 1.0 / np.where(inr, rsq, 1.0), 0.0)
+    r6 = r2 ** 3
+    A, B = typ[:, None], typ[None, :]
+    fpair = r6 * (t["lj1"][A, B] * r6 - t["lj2"][A, B]) * r2
+    fref = np.einsum("ij,ijk->ik", fpair, d)
+    eref = 0.5 * np.where(inr, r6 * (t["lj3"][A, B] * r6 - t["lj4"][A, B]) - t["offset"][A, B], 0.0).sum()
+    g = md.gather()
+    assert np.abs(g["f"] - fref).max() <= 1e-11 * np.abs(fref).max()
+    assert abs(md.thermo_log[-1]["pe"] - eref) <= 1e-11 * abs(eref)
+    md.close()
