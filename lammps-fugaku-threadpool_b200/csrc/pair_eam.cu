@@ -537,7 +537,8 @@ int pair_eam_rho_part(b200md_ctx *c, int part)
   const EAMParams P = eam_params(c);
   const int ntiles = cdiv(n, TILE), cnt = part ? c->ntiles_ghost : ntiles - c->ntiles_ghost;
   const int *list = c->tile_list.p + (part ? ntiles - c->ntiles_ghost : 0);
-  const int threads = EAM1T_THREADS, blocks = cdiv(cnt * TILE, threads);
+  // the small second launch (6-9 % of the tiles) in 128-thread blocks: finer tail than 3 waves of 512-thread blocks
+  const int threads = part ? 128 : EAM1T_THREADS, blocks = cdiv(cnt * TILE, threads);
   const size_t n1 = (size_t) T.nr + 1, smemA = 4 * n1 * 8;
   TRY(dev_ensure(c, c->posfp, (size_t) n + c->nghost));
   if (cnt == 0) return B200MD_OK;
@@ -557,7 +558,8 @@ int pair_eam_force_part(b200md_ctx *c, int part)
   const int ntiles = cdiv(n, TILE), cnt = part ? c->ntiles_ghost : ntiles - c->ntiles_ghost;
   if (cnt == 0) return B200MD_OK;
   const int *list = c->tile_list.p + (part ? ntiles - c->ntiles_ghost : 0);
-  const int threads = EAM1T_THREADS, blocks = cdiv(cnt * TILE, threads);
+  // the small second launch (6-9 % of the tiles) in 128-thread blocks: finer tail than 3 waves of 512-thread blocks
+  const int threads = part ? 128 : EAM1T_THREADS, blocks = cdiv(cnt * TILE, threads);
   const size_t n1 = (size_t) T.nr + 1, smemC = 7 * n1 * 8;
   TRY(eam_attrs_1t(c));
   KProf kp(c, KC_PAIR);

@@ -207,13 +207,29 @@ void VerletB200::download()
     // one rank: every atom is still local; write back by tag so host order, mask and any other per-atom
     // property stay what they were
     if (n != atom->nlocal) error->one(FLERR, "Run style verlet/b200: device holds {} atoms, host {}", n, atom->nlocal);
-    std::vector<std::pair<tagint, int>> where(n);
-    for (int i = 0; i < n; i++) where[i] = {atom->tag[i], i};
-    std::sort(where.begin(), where.end());
+    // tag -> host index: a direct table when the tags are reasonably dense (the usual 1..N), else a sorted list
+    tagint maxtag = 0;
+    for (int i = 0; i < n; i++) maxtag = std::max(maxtag, atom->tag[i]);
+    const bool dense = maxtag > 0 && (bigint) maxtag <= 4 * (bigint) n + 1024;
+    std::vector<int> slot;
+    std::vector<std::pair<tagint, int>> where;
+    if (dense) {
+      slot.assign((size_t) maxtag + 1, -1);
+      for (int i = 0; i < n; i++) slot[atom->tag[i]] = i;
+    } else {
+      where.resize(n);
+      for (int i = 0; i < n; i++) where[i] = {atom->tag[i], i};
+      std::sort(where.begin(), where.end());
+    }
     for (int s = 0; s < n; s++) {
-      auto it = std::lower_bound(where.begin(), where.end(), std::make_pair((tagint) tag[s], -1));
-      if (it == where.end() || it->first != tag[s]) error->one(FLERR, "Run style verlet/b200: unknown atom tag {} came back", tag[s]);
-      const int i = it->second;
+      int i = -1;
+      if (dense) {
+        if (tag[s] >= 1 && tag[s] <= maxtag) i = slot[tag[s]];
+      } else {
+        auto it = std::lower_bound(where.begin(), where.end(), std::make_pair((tagint) tag[s], -1));
+        if (it != where.end() && it->first == tag[s]) i = it->second;
+      }
+      if (i < 0) error->one(FLERR, "Run style verlet/b200: unknown atom tag {} came back", tag[s]);
       for (int k = 0; k < 3; k++) {
         atom->x[i][k] = x[3 * s + k];
         atom->v[i][k] = v[3 * s + k];
