@@ -172,8 +172,13 @@ struct b200md_ctx {
   BinGeom bg;
   DevBuf<int> bin_count, bin_start, atom_bin, cell_list, perm, scan_tmp;
   DevBuf<unsigned char> atom_sub;
-  DevBuf<int> binrec_tag;     // tags in cell_list order (bonded systems only)
-  DevBuf<double> binrec;      // BinRec[nall] (16 B each): FP32 candidate records in cell_list order (neigh.cu)
+  // candidate records of the list build (neigh.cu): SoA in cell_list order with every bin padded to the build's vector
+  // width, so the 3 x (tg + 2) bins of a staged row are one contiguous, 16-byte aligned range of each array
+  DevBuf<float> rec_xyz;      // [3][rec_cap] FP32 coordinates relative to the bin-grid origin
+  DevBuf<int> rec_jt;         // [rec_cap] index | (type - 1) << 28
+  DevBuf<int> rec_tag;        // [rec_cap] tags (bonded / molecular systems only)
+  DevBuf<int> pbin_start;     // [mbins + 1] padded start of every bin
+  size_t rec_cap = 0;
 
   // neighbor list
   int maxneigh = 0;

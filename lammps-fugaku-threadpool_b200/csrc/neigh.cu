@@ -361,32 +361,78 @@ k_build_fp64(const double4 *__restrict__ pos, int nlocal, BinGeom g, const int *
 // atom: 27 candidate steps per atom (500 candidates over 18.5 useful lanes) at 28 instructions each.  Here a lane
 // scans its own 500 candidates (15.6 steps per atom at 32 lanes) at about 14 instructions per candidate.
 // ------------------------------------------------------------------------------------------------
-struct BinRec { float x, y, z; int jt; };
 #define BR_JMASK 0x0FFFFFFF
+#define SEG_FAR 1.0e18f   /* coordinate of a padding record: rsq = inf, never <= any cutoff */
 
-__global__ void k_binrec_fill(const double4 *__restrict__ pos, const int *__restrict__ cell_list, int nall, double ox, double oy,
-                              double oz, BinRec *__restrict__ rec, const int *__restrict__ tag, int *__restrict__ rec_tag)
+// candidate records, SoA, in cell_list order with every bin padded to the build's vector width VW: padded population
+// of each bin (its exclusive scan is pbin_start)
+__global__ void k_pad_count(const int *__restrict__ bin_start, int mbins, int vw, int *__restrict__ cnt)
 {
-  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b > mbins) return;
+  cnt[b] = b < mbins ? ((bin_start[b + 1] - bin_start[b] + vw - 1) & ~(vw - 1)) : 0;
+}
+
+// record of cell_list position k: FP32 coordinates relative to the bin-grid origin, j | (type-1) << 28, tag
+__global__ void k_rec_fill(const double4 *__restrict__ pos, const int *__restrict__ cell_list, const int *__restrict__ atom_bin,
+                           const int *__restrict__ bin_start, const int *__restrict__ pbin_start, int nall, double ox, double oy,
+                           double oz, float *__restrict__ rx, float *__restrict__ ry, float *__restrict__ rz,
+                           int *__restrict__ rjt, const int *__restrict__ tag, int *__restrict__ rtag)
+{
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= nall) return;
   const int j = cell_list[k];
+  const int b = atom_bin[j];
+  const int d = pbin_start[b] + k - bin_start[b];
   const double4 p = pos[j];
-  BinRec r;
-  r.x = (float) (p.x - ox);
-  r.y = (float) (p.y - oy);
-  r.z = (float) (p.z - oz);
-  r.jt = j | ((pos_type(p) - 1) << 28);
-  rec[k] = r;
-  if (rec_tag) rec_tag[k] = tag[j];  // bonded systems: the candidate's tag, for the special-partner test
+  rx[d] = (float) (p.x - ox);
+  ry[d] = (float) (p.y - oy);
+  rz[d] = (float) (p.z - oz);
+  rjt[d] = j | ((pos_type(p) - 1) << 28);
+  if (rtag) rtag[d] = tag[j];  // bonded / molecular systems: the candidate's tag, for the special-partner test
 }
 
-__device__ __forceinline__ BinRec ld_rec(const BinRec *__restrict__ p)
+// the padding records at the end of every bin: never accepted
+__global__ void k_rec_pad(const int *__restrict__ bin_start, const int *__restrict__ pbin_start, int mbins, float *__restrict__ rx,
+                          float *__restrict__ ry, float *__restrict__ rz, int *__restrict__ rjt, int *__restrict__ rtag)
 {
-  const int4 v = __ldg(reinterpret_cast<const int4 *>(p));
-  BinRec r;
-  r.x = __int_as_float(v.x); r.y = __int_as_float(v.y); r.z = __int_as_float(v.z); r.jt = v.w;
-  return r;
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= mbins) return;
+  for (int d = pbin_start[b] + bin_start[b + 1] - bin_start[b]; d < pbin_start[b + 1]; d++) {
+    rx[d] = ry[d] = rz[d] = SEG_FAR;
+    rjt[d] = BR_JMASK;
+    if (rtag) rtag[d] = 0;
+  }
 }
+
+// ---- 1-D bulk copies global -> shared through the TMA engine (cp.async.bulk + mbarrier; SASS: UBLKCP, SYNCS) ----
+#ifndef B200MD_CUDAEMU
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned) __cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, int count)
+{
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes)
+{
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned bytes, unsigned long long *bar)
+{
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned phase)
+{
+  unsigned done = 0;
+  while (!done)
+    asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(done)
+                 : "r"(smem_u32(bar)), "r"(phase)
+                 : "memory");
+}
+#endif
 
 // BONDED == 1 (in.chain): a candidate within the cutoff whose tag is one of the atom's 1-2 partners is NOT listed
 // (special_bonds lj weight 0, NPair::find_special src/npair.h:125-158 -> -1) but recorded as the device index of that
@@ -404,17 +450,24 @@ struct BondBuild {
   int flag[4];                 // 0 drop, 1 ordinary neighbor, 2 keep with the class in bits 28-29 of the entry
 };
 #define SEG_THREADS 128
-// shared-memory plan of a segment: SoA candidate arrays of `cap` elements (cap a multiple of 4, every staged bin padded
-// to a multiple of VW with records that can never be accepted), so a thread reads VW candidates with one LDS.128 (VW = 4,
-// dense bins) or LDS.64 (VW = 2, sparse bins such as in.chain's 3 beads per bin, where padding to 4 would add a third
-// more candidates) per array and every bin range is VW-aligned: no per-candidate range tests
+// shared-memory plan of a segment: SoA candidate arrays of `cap` elements.  The records arrive already padded (every bin
+// to a multiple of VW with records that can never be accepted: k_rec_fill / k_rec_pad), so a thread reads VW candidates
+// with one LDS.128 (VW = 4, dense bins) or LDS.64 (VW = 2, sparse bins such as in.chain's 3 beads per bin, where
+// padding to 4 would add a third more candidates) per array and every bin range is VW-aligned: no per-candidate range
+// tests.  A staged row (the 3 x (tg + 2) bins of one (dz, dy)) is ONE contiguous range of each global array: with VW = 4
+// it is 16-byte aligned and goes to shared memory as 1-D bulk copies through the TMA engine (cp.async.bulk, completion
+// on an mbarrier) -- 36 copies issued by one thread instead of a thousand LDG/STS pairs.
 //   float x[cap], y[cap], z[cap]; int jt[cap] (index | (type-1) << 28); int tag[cap] (BONDED);
 //   int bs[9][tg+3]  cell_list position of each staged bin's first record (+ the end);
-//   int po[9][tg+3]  staged (padded) offset of each staged bin (+ the end)
-#define SEG_FAR 1.0e18f   /* coordinate of a padding record: rsq = inf, never <= any cutoff */
+//   int po[9][tg+3]  staged offset of each staged bin (+ the end)
+struct RecArrays {
+  const float *x, *y, *z;   // [rec_cap]
+  const int *jt;            // [rec_cap]
+  const int *pbin_start;    // [mbins + 1]
+};
 template <int ONETYPE, int BONDED, int VW>
 __global__ void __launch_bounds__(SEG_THREADS)
-k_build_seg(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int nlocal, BinGeom g,
+k_build_seg(const double4 *__restrict__ pos, RecArrays rec, int nlocal, BinGeom g,
             const int *__restrict__ bin_start, const double *__restrict__ cutneighsq, int ntypes, float tol, int maxneigh,
             int *__restrict__ numneigh, int *__restrict__ neigh, int *__restrict__ flags, int *__restrict__ tile_ghost,
             BondBuild bb, int tg, int cap)
@@ -428,7 +481,8 @@ k_build_seg(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int
   int *s_po = s_bs + 9 * W;
   __shared__ double s_cut[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
   __shared__ float s_cutf[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
-  __shared__ int s_total;
+  __shared__ int s_row[10];                       // staged offset of each row (+ the total)
+  __shared__ unsigned long long s_bar;            // mbarrier of the bulk copies (8-byte aligned by its type)
   const int nt1 = ntypes + 1;
   for (int k = threadIdx.x; k < nt1 * nt1; k += blockDim.x) { s_cut[k] = cutneighsq[k]; s_cutf[k] = (float) cutneighsq[k]; }
   const int nsegx = (g.nbin[0] + tg - 1) / tg;
@@ -437,73 +491,71 @@ k_build_seg(const double4 *__restrict__ pos, const BinRec *__restrict__ rec, int
   const int gx = min(tg, g.nbin[0] - sx * tg);
   const int bx0 = BIN_MARGIN + sx * tg, by = oby + BIN_MARGIN, bz = obz + BIN_MARGIN;
   const int nq = gx + 3;   // bin starts per row: bins bx0-1 .. bx0+gx, plus the end of the last
+  // s_po first holds the padded global start of every staged bin; turned into staged offsets below
   for (int idx = threadIdx.x; idx < 9 * nq; idx += blockDim.x) {
     const int r = idx / nq, q = idx - r * nq;
     const int first = ((bz + r / 3 - 1) * g.mbin[1] + (by + r % 3 - 1)) * g.mbin[0] + bx0 - 1;
     s_bs[r * W + q] = bin_start[first + q];
+    s_po[r * W + q] = rec.pbin_start[first + q];
   }
+#ifndef B200MD_CUDAEMU
+  if (VW == 4 && threadIdx.x == 0) mbar_init(&s_bar, 1);
+#endif
   __syncthreads();
-  // padded staging offsets: exclusive scan of roundup4(bin population) over the 9 x (gx + 2) staged bins (warp 0)
-  if (threadIdx.x < 32) {
-    const int lane = threadIdx.x, nb = 9 * (gx + 2);
-    int carry = 0;
-    for (int b0 = 0; b0 < nb; b0 += 32) {
-      const int b = b0 + lane;
-      int cnt = 0, r = 0, q = 0;
-      if (b < nb) {
-        r = b / (gx + 2);
-        q = b - r * (gx + 2);
-        cnt = (s_bs[r * W + q + 1] - s_bs[r * W + q] + VW - 1) & ~(VW - 1);
-      }
-      int incl = cnt;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int y = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += y;
-      }
-      if (b < nb) {
-        s_po[r * W + q] = carry + incl - cnt;
-        if (q == gx + 1) s_po[r * W + q + 1] = carry + incl;   // end of the row = start of the next row's first bin
-      }
-      carry += __shfl_sync(0xffffffffu, incl, 31);
+  if (threadIdx.x == 0) {
+    int off = 0;
+    for (int r = 0; r < 9; r++) {
+      s_row[r] = off;
+      off += s_po[r * W + gx + 2] - s_po[r * W];
     }
-    if (lane == 0) s_total = carry;
+    s_row[9] = off;
   }
   __syncthreads();
-  const int total = s_total;
+  const int total = s_row[9];
   if (total > cap) {   // denser than the staging area allows: report the size wanted, the host grows it and redoes the build
     if (threadIdx.x == 0) atomicMax(&flags[6], total);
     return;
   }
-  // stage: coalesced 16-byte record loads, scattered into the SoA arrays at the padded offset of the record's bin
+  // stage the 9 rows
+  bool bulk = false;
+#ifndef B200MD_CUDAEMU
+  bulk = VW == 4;
+  if (bulk && threadIdx.x == 0) {
+    mbar_expect_tx(&s_bar, (unsigned) total * (BONDED ? 20u : 16u));
+    for (int r = 0; r < 9; r++) {
+      const int gs = s_po[r * W], len = s_po[r * W + gx + 2] - gs, so = s_row[r];
+      if (len == 0) continue;
+      const unsigned bytes = (unsigned) len * 4u;
+      bulk_g2s(s_x + so, rec.x + gs, bytes, &s_bar);
+      bulk_g2s(s_y + so, rec.y + gs, bytes, &s_bar);
+      bulk_g2s(s_z + so, rec.z + gs, bytes, &s_bar);
+      bulk_g2s(s_jt + so, rec.jt + gs, bytes, &s_bar);
+      if (BONDED) bulk_g2s(s_tag + so, bb.rec_tag + gs, bytes, &s_bar);
+    }
+  }
+#endif
+  if (!bulk) {
 #pragma unroll 1
-  for (int r = 0; r < 9; r++) {
-    const int ks = s_bs[r * W], len = s_bs[r * W + gx + 2] - ks;
-    const int4 *src = reinterpret_cast<const int4 *>(rec + ks);
-    for (int k = threadIdx.x; k < len; k += blockDim.x) {
-      const int4 v = __ldg(src + k);
-      const int gk = ks + k;
-      int qlo = 0, qhi = gx + 1;   // the bin holding cell_list position gk: largest q with bs[q] <= gk
-      while (qlo < qhi) {
-        const int mid = (qlo + qhi + 1) >> 1;
-        if (s_bs[r * W + mid] <= gk) qlo = mid;
-        else qhi = mid - 1;
+    for (int r = 0; r < 9; r++) {
+      const int gs = s_po[r * W], len = s_po[r * W + gx + 2] - gs, so = s_row[r];
+      for (int k = threadIdx.x; k < len; k += blockDim.x) {
+        s_x[so + k] = __ldg(rec.x + gs + k);
+        s_y[so + k] = __ldg(rec.y + gs + k);
+        s_z[so + k] = __ldg(rec.z + gs + k);
+        s_jt[so + k] = __ldg(rec.jt + gs + k);
+        if (BONDED) s_tag[so + k] = __ldg(bb.rec_tag + gs + k);
       }
-      const int d = s_po[r * W + qlo] + gk - s_bs[r * W + qlo];
-      s_x[d] = __int_as_float(v.x); s_y[d] = __int_as_float(v.y); s_z[d] = __int_as_float(v.z);
-      s_jt[d] = v.w;
-      if (BONDED) s_tag[d] = __ldg(bb.rec_tag + gk);
     }
   }
-  for (int idx = threadIdx.x; idx < 9 * (gx + 2); idx += blockDim.x) {   // the padding records of every bin
-    const int r = idx / (gx + 2), q = idx - r * (gx + 2);
-    const int cnt = s_bs[r * W + q + 1] - s_bs[r * W + q];
-    for (int d = s_po[r * W + q] + cnt; d < s_po[r * W + q + 1]; d++) {
-      s_x[d] = s_y[d] = s_z[d] = SEG_FAR;
-      s_jt[d] = BR_JMASK;
-      if (BONDED) s_tag[d] = 0;
-    }
+  __syncthreads();   // the copies are issued (or done): s_po's global starts are no longer needed as such
+  // global padded starts -> staged offsets, one thread per row (the row's first entry is read before it is rewritten)
+  for (int r = threadIdx.x; r < 9; r += blockDim.x) {
+    const int g0 = s_po[r * W], so = s_row[r];
+    for (int q = nq - 1; q >= 0; q--) s_po[r * W + q] = so + s_po[r * W + q] - g0;
   }
+#ifndef B200MD_CUDAEMU
+  if (bulk) mbar_wait(&s_bar, 0);
+#endif
   __syncthreads();
   const float cut1 = s_cutf[nt1 + 1];
   const int own_s = s_bs[4 * W + 1], own_e = s_bs[4 * W + 1 + gx];
@@ -842,18 +894,7 @@ int neigh_build_lists(b200md_ctx *c)
     const double tol = build_tolerance(c, &cutsq_min);
     if (tol < 0.01 * cutsq_min && !c->build_fp64) {
       const BinGeom &g = c->bg;
-      TRY(dev_ensure(c, c->binrec, (size_t) nall * 2));  // 16-byte records held as double pairs
       KProf kp(c, KC_NEIGH);
-      BinRec *rec = reinterpret_cast<BinRec *>(c->binrec.p);
-      int *rec_tag = nullptr;
-      if (c->bonds.maxb > 0 || c->special.on) {
-        TRY(dev_ensure(c, c->binrec_tag, (size_t) nall));
-        rec_tag = c->binrec_tag.p;
-      }
-      k_binrec_fill<<<cdiv(nall, 256), 256, 0, c->stream>>>(c->pos.p, c->cell_list.p, nall, g.lo[0] - BIN_MARGIN / g.inv[0],
-                                                            g.lo[1] - BIN_MARGIN / g.inv[1], g.lo[2] - BIN_MARGIN / g.inv[2], rec,
-                                                            c->tag.p, rec_tag);
-      LAUNCH_CHECK();
       const int nown = g.nbin[0] * g.nbin[1] * g.nbin[2];
       int *tile_ghost = nullptr;
       if (c->overlap) {  // tile flags for the interior / boundary split of the force kernels
@@ -866,7 +907,6 @@ int neigh_build_lists(b200md_ctx *c)
       const bool bonded = c->bonds.maxb > 0, special = c->special.on && !bonded;
       if (special) {
         if (!c->host_ghosts) return b200md_fail(c, B200MD_ERR_ARG, "general special-bond lists are a host-ghost mode feature (b200md_host_special)");
-        bb.rec_tag = c->binrec_tag.p;
         bb.spec_n3 = c->special.n3.p;
         bb.spec_tags = c->special.tags.p;
         bb.maxspecial = c->special.maxspecial;
@@ -874,7 +914,6 @@ int neigh_build_lists(b200md_ctx *c)
       }
       if (bonded) {
         TRY(dev_ensure(c, c->bonds.idx, (size_t) n * c->bonds.maxb));
-        bb.rec_tag = c->binrec_tag.p;
         bb.tag = c->tag.p;
         bb.partner_by_tag = c->bonds.partner_by_tag.p;
         bb.bond_idx = c->bonds.idx.p;
@@ -893,6 +932,35 @@ int neigh_build_lists(b200md_ctx *c)
       if (c->seg_cap == 0 && c->seg_cap_user > 0) c->seg_cap = (c->seg_cap_user + 3) & ~3;   // test knob: start too small, exercise the retry
       // (every staged bin is padded to a multiple of vw records: + (vw - 1) / 2 on average)
       const int vw = (per_bin >= 8.0 && !(c->special.on && c->bonds.maxb == 0)) ? 4 : 2;
+      // the candidate records: FP32, SoA, every bin padded to vw (k_pad_count -> scan -> k_rec_fill + k_rec_pad)
+      {
+        const int mb = g.mbins;
+        const size_t cap_rec = (((size_t) nall + (size_t) (vw - 1) * (size_t) (mb < nall ? mb : nall)) + 63) & ~(size_t) 63;
+        TRY(dev_ensure(c, c->pbin_start, (size_t) mb + 1));
+        TRY(dev_ensure(c, c->rec_jt, cap_rec));
+        if (c->rec_xyz.n < 3 * c->rec_jt.n) TRY(dev_ensure(c, c->rec_xyz, 3 * c->rec_jt.n, false, false));
+        c->rec_cap = c->rec_xyz.n / 3 & ~(size_t) 3;
+        int *rtag = nullptr;
+        if (bonded || special) {
+          TRY(dev_ensure(c, c->rec_tag, c->rec_cap));
+          rtag = c->rec_tag.p;
+        }
+        // bin_count is free after the sort: it holds the padded populations until the scan has run
+        k_pad_count<<<cdiv(mb + 1, 256), 256, 0, c->stream>>>(c->bin_start.p, mb, vw, c->bin_count.p);
+        LAUNCH_CHECK();
+        TRY(exclusive_scan(c, c->bin_count.p, c->pbin_start.p, mb + 1));
+        float *rx = c->rec_xyz.p, *ry = rx + c->rec_cap, *rz = ry + c->rec_cap;
+        k_rec_fill<<<cdiv(nall, 256), 256, 0, c->stream>>>(c->pos.p, c->cell_list.p, c->atom_bin.p, c->bin_start.p, c->pbin_start.p, nall,
+                                                          g.lo[0] - BIN_MARGIN / g.inv[0], g.lo[1] - BIN_MARGIN / g.inv[1],
+                                                          g.lo[2] - BIN_MARGIN / g.inv[2], rx, ry, rz, c->rec_jt.p, c->tag.p, rtag);
+        LAUNCH_CHECK();
+        if (vw > 1) {
+          k_rec_pad<<<cdiv(mb, 256), 256, 0, c->stream>>>(c->bin_start.p, c->pbin_start.p, mb, rx, ry, rz, c->rec_jt.p, rtag);
+          LAUNCH_CHECK();
+        }
+        bb.rec_tag = rtag;
+      }
+      const RecArrays rec = {c->rec_xyz.p, c->rec_xyz.p + c->rec_cap, c->rec_xyz.p + 2 * c->rec_cap, c->rec_jt.p, c->pbin_start.p};
       if (c->seg_cap == 0) c->seg_cap = (int) (1.08 * 9.0 * (tg + 2) * ((double) nall / (nown > 0 ? nown : 1) + 0.5 * (vw - 1))) + 64;
       if (c->seg_cap > nall + 27 * (tg + 2)) c->seg_cap = nall + 27 * (tg + 2);   // no segment can stage more than exists
       c->seg_cap = (c->seg_cap + 3) & ~3;

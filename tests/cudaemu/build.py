@@ -107,6 +107,9 @@ def rewrite(text: str, name: str) -> str:
     # the two inline-PTX helpers of ctx.cuh
     text = re.sub(r'asm\("ld\.global\.nc\.v4\.f64[^;]*;"[^;]*;', "r = *p;", text)
     text = re.sub(r'asm\("rcp\.approx\.ftz\.f64[^;]*;"[^;]*;', "y = 1.0 / x;", text)
+    # sm_100-only paths (TMA bulk copies + mbarrier) sit in `#ifndef B200MD_CUDAEMU ... #endif` blocks with a plain-C
+    # equivalent beside them; the emulation compiles with -DB200MD_CUDAEMU=1, drop the blocks before the PTX check
+    text = re.sub(r"#ifndef B200MD_CUDAEMU\n.*?\n#endif\n", "", text, flags=re.S)
     if "asm(" in text or "asm volatile" in text:
         raise RuntimeError(f"{name}: inline PTX the emulation does not know")
     # comm.cu binds NCCL by dlopen: hand it the in-process stand-in for emulated ranks (threads) instead
