@@ -302,6 +302,22 @@ int b200md_build_bins_per_block(const b200md_ctx *ctx);
  * Unknown key: B200MD_ERR_ARG. */
 int b200md_tune(b200md_ctx *ctx, const char *key, int value);
 
+/* No counterpart in the reference: added for callers that may not allocate
+ * device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * The kinetic-energy sum of b200md_thermo -- sum_i mass[type[i]] * |v_i|^2 over n atoms, the quantity
+ * ComputeTemp::compute_scalar multiplies by mvv2e / (dof * boltz) -- computed without a context and without any
+ * allocation: no cudaMalloc / cudaFree / allocating library call.  The per-block partial sums go to a fixed
+ * file-scope device array of 65536 doubles (512 KiB, held by every GPU that loads the library until the process
+ * exits), so n <= b200md_ke_noalloc_max_atoms() = 16 777 216; a larger n returns B200MD_ERR_ARG with a message in
+ * b200md_last_error(NULL).  All pointers are DEVICE pointers on `device`, caller-owned: vx, vy, vz [n], type [n]
+ * (1-based), mass [ntypes+1], sum_mv2 [1] (written on `stream`, a cudaStream_t or NULL; the call does not synchronise).
+ * Every call on a device shares the one array: calls that overlap on the GPU race -- order them on one stream.  Nothing
+ * in the array has to start at zero (each call overwrites every element it later reads).  The array's device address
+ * is looked up once per device, on the first call for that device. */
+int b200md_ke_noalloc(int device, int n, const double *vx, const double *vy, const double *vz, const int *type,
+                      const double *mass, double *sum_mv2, void *stream);
+int b200md_ke_noalloc_max_atoms(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -13,7 +13,7 @@ from pathlib import Path
 HERE = Path(__file__).resolve().parent
 CSRC = HERE / "csrc"
 LIB = HERE / "libb200md.so"
-SOURCES = ["capi.cu", "neigh.cu", "pair_lj.cu", "pair_eam.cu", "nve.cu", "comm.cu", "eam_host.cu", "bond.cu"]
+SOURCES = ["capi.cu", "neigh.cu", "pair_lj.cu", "pair_eam.cu", "nve.cu", "comm.cu", "eam_host.cu", "bond.cu", "noalloc.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
          "-Xcompiler", "-O2"]

@@ -75,6 +75,8 @@ PROTOTYPES = {
     "b200md_tune": (_i, [_vp, C.c_char_p, _i]),
     "b200md_host_special": (_i, [_vp, _i, _i, _vp, _i, _vp, _vp, _vp]),
     "b200md_build_bins_per_block": (_i, [_vp]),
+    "b200md_ke_noalloc": (_i, [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "b200md_ke_noalloc_max_atoms": (_i, []),
 }
 
 _lib = None

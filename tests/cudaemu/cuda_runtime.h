@@ -27,6 +27,9 @@
 #define __host__
 #define __forceinline__ inline
 #define __launch_bounds__(...)
+#ifndef __align__
+#define __align__(n) __attribute__((aligned(n)))
+#endif
 #define __shared__ static thread_local   /* one block at a time per host thread (= per emulated rank) */
 #ifndef __restrict__
 #define __restrict__ __restrict
@@ -86,6 +89,9 @@ static inline const char *cudaGetErrorString(cudaError_t e) { return e == cudaSu
 static inline cudaError_t cudaGetLastError() { return cudaSuccess; }
 static inline cudaError_t cudaGetDeviceCount(int *n) { *n = 64; return cudaSuccess; }   // one emulated device per host thread
 static inline cudaError_t cudaSetDevice(int) { return cudaSuccess; }
+static inline cudaError_t cudaGetDevice(int *d) { *d = 0; return cudaSuccess; }
+// a __device__ variable is a plain host variable here: its address is the "device" address
+template <class T> static inline cudaError_t cudaGetSymbolAddress(void **p, const T &sym) { *p = (void *) &sym; return cudaSuccess; }
 static inline cudaError_t cudaGetDeviceProperties(cudaDeviceProp *p, int)
 {
   memset(p, 0, sizeof(*p));

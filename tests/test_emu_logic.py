@@ -762,3 +762,26 @@ def test_emu_fp64_fallback_build_keeps_the_physics(emu, name):
     md.run(int(g["nmore"][0]))
     np.testing.assert_allclose(thermo_vec(md.thermo_log[-1]), g["b_thermo"][:3], rtol=THERMO_RTOL)
     md.close()
+
+
+def test_emu_ke_noalloc_matches_thermo(emu):
+    """b200md_ke_noalloc (fixed file-scope scratch array, no allocation) against b200md_thermo's kinetic energy, two
+    calls in a row with the larger system first; the size limit is refused with a message.  Under the emulator a
+    device pointer is a host pointer, so numpy arrays stand in for the caller's device buffers."""
+    L = emu.lib.load()
+    for name in ("lj2_864", "lj_500"):
+        g = load_golden(name)
+        md = make_device_system(emu, name, g)
+        md.setup()
+        md.run(3)
+        ke = md.thermo()["ke"]
+        a = md.gather(sort_by_tag=False)
+        v = np.ascontiguousarray(a["v"].T)
+        typ, mass, out = a["type"].astype(np.int32), np.asarray(md.mass, dtype=np.float64), np.full(1, -1.0)
+        p = emu.lib.ptr
+        assert L.b200md_ke_noalloc(0, v.shape[1], p(v[0]), p(v[1]), p(v[2]), p(typ), p(mass), p(out), None) == 0
+        np.testing.assert_allclose(0.5 * out[0], ke, rtol=1e-12)
+        md.close()
+    nmax = L.b200md_ke_noalloc_max_atoms()
+    assert L.b200md_ke_noalloc(0, nmax + 1, p(v[0]), p(v[1]), p(v[2]), p(typ), p(mass), p(out), None) != 0
+    assert "exceed" in L.b200md_last_error(None).decode()
