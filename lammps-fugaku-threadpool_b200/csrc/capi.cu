@@ -79,7 +79,7 @@ extern "C" int b200md_destroy(b200md_ctx *c)
   dev_free(c, c->tag); dev_free(c, c->tag_tmp); dev_free(c, c->image); dev_free(c, c->image_tmp);
   dev_free(c, c->rho); dev_free(c, c->fp); dev_free(c, c->posfp); dev_free(c, c->cutneighsq_d);
   dev_free(c, c->bin_count); dev_free(c, c->bin_start); dev_free(c, c->atom_bin); dev_free(c, c->cell_list);
-  dev_free(c, c->perm); dev_free(c, c->scan_tmp); dev_free(c, c->rec_xyz); dev_free(c, c->rec_jt); dev_free(c, c->pbin_start); dev_free(c, c->atom_sub); dev_free(c, c->numneigh); dev_free(c, c->neigh); dev_free(c, c->tile_ghost); dev_free(c, c->tile_list); dev_free(c, c->tile_pos);
+  dev_free(c, c->perm); dev_free(c, c->scan_tmp); dev_free(c, c->rec_xyz); dev_free(c, c->rec_jt); dev_free(c, c->pbin_start); dev_free(c, c->atom_sub); dev_free(c, c->numneigh); dev_free(c, c->neigh); dev_free(c, c->numneigh_in); dev_free(c, c->neigh_in); dev_free(c, c->tile_ghost); dev_free(c, c->tile_list); dev_free(c, c->tile_pos);
   dev_free(c, c->send_idx); dev_free(c, c->border_blockcnt); dev_free(c, c->border_total); dev_free(c, c->send_dir);
   dev_free(c, c->sendbuf_i); dev_free(c, c->allcounts); dev_free(c, c->sendbuf4); dev_free(c, c->recvbuf4); dev_free(c, c->sendbuf1);
   dev_free(c, c->partials); dev_free(c, c->stage); dev_free(c, c->peratom); dev_free(c, c->special.n3); dev_free(c, c->special.tags);

@@ -183,6 +183,7 @@ struct b200md_ctx {
   // neighbor list
   int maxneigh = 0;
   DevBuf<int> numneigh, neigh;
+  DevBuf<int> numneigh_in, neigh_in;   // EAM single-type path: the entries inside the force cutoff, left by the rho pass for the force pass of the same step
   DevBuf<int> tile_ghost;     // [ntiles]: != 0 if an atom of the 32-atom tile has a ghost among its candidates (overlap mode)
   DevBuf<int> tile_list, tile_pos;   // tile numbers, ghost-free tiles first (ascending), then the others; scan scratch
   int ntiles_ghost = 0;       // tiles in the second part

@@ -236,7 +236,7 @@ __global__ void __launch_bounds__(EAM1T_THREADS, 2)
 k_eam_rho_fp_1t(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
                 int nlocal, EAMParams P, const double *__restrict__ tab1, double *__restrict__ rho_out,
                 double *__restrict__ fp_out, double4 *__restrict__ posfp, double *__restrict__ partials,
-                const int *__restrict__ tile_list, int part)
+                const int *__restrict__ tile_list, int part, int *__restrict__ numneigh_in, int *__restrict__ neigh_in)
 {
   extern __shared__ double s_t[];  // [4][n1]: rhor c3..c6
   const int n1 = P.nr + 1;
@@ -254,10 +254,14 @@ k_eam_rho_fp_1t(const double4 *__restrict__ pos, const int *__restrict__ numneig
     const int n = numneigh[i];
     const int *nb = neigh + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
     double rho = 0.0;
+    // the entries inside the force cutoff (58 % of the Cu melt's list: cutforce 4.95 of cutneigh 5.95), in list order, for
+    // the force pass of this step: it then gathers and evaluates those alone
+    int *const w0 = neigh_in + (size_t) (i >> 5) * TILE * maxneigh + (i & 31);
+    int *wp = w0;
     // software pipeline (see k_lj_force): next batch of list entries in flight while PF gathers are issued together
     constexpr int PF = 4;
     const int nlast = max(n - 1, 0);
-    unsigned enx[PF];
+    unsigned enx[PF], cur[PF];
 #pragma unroll
     for (int u = 0; u < PF; u++) enx[u] = (unsigned) __ldcs(nb + (size_t) min(u, nlast) * TILE);
     for (int k0 = 0; k0 < n; k0 += PF) {
@@ -265,12 +269,17 @@ k_eam_rho_fp_1t(const double4 *__restrict__ pos, const int *__restrict__ numneig
 #pragma unroll
       for (int u = 0; u < PF; u++) pj[u] = ld_pos256(pos + (enx[u] & CLJMASK));
 #pragma unroll
-      for (int u = 0; u < PF; u++) enx[u] = (unsigned) __ldcs(nb + (size_t) min(k0 + PF + u, nlast) * TILE);
+      for (int u = 0; u < PF; u++) {
+        cur[u] = enx[u];
+        enx[u] = (unsigned) __ldcs(nb + (size_t) min(k0 + PF + u, nlast) * TILE);
+      }
 #pragma unroll
       for (int u = 0; u < PF; u++) {
         const double dx = pi.x - pj[u].x, dy = pi.y - pj[u].y, dz = pi.z - pj[u].z;
         const double rsq = dx * dx + dy * dy + dz * dz;
         if (rsq < P.cutforcesq && k0 + u < n) {
+          *wp = (int) cur[u];
+          wp += TILE;
           double p = rsq * rsqrt(rsq) * P.rdr + 1.0;
           int m = (int) p;
           m = min(m, P.nr - 1);
@@ -280,6 +289,7 @@ k_eam_rho_fp_1t(const double4 *__restrict__ pos, const int *__restrict__ numneig
         }
       }
     }
+    numneigh_in[i] = (int) ((wp - w0) / TILE);
     double p = rho * P.rdrho + 1.0;
     int m = (int) p;
     m = max(1, min(m, P.nrho - 1));
@@ -299,6 +309,8 @@ k_eam_rho_fp_1t(const double4 *__restrict__ pos, const int *__restrict__ numneig
   if (EFLAG) block_partials_e<1>(acc, partials);
 }
 
+// numneigh / neigh here are the IN-RANGE lists the rho pass of the same step left (numneigh_in, neigh_in): a subsequence of
+// the full list in the same order, so the sums run over the same terms in the same order as over the full list
 template <int EVFLAG, int SPLIT>
 __global__ void __launch_bounds__(EAM1T_THREADS, 2)
 k_eam_force_1t(const double4 *__restrict__ posfp, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
@@ -433,6 +445,14 @@ static int eam_attrs_1t(b200md_ctx *c)
   return B200MD_OK;
 }
 
+// the in-range lists of the single-type path: same shape as the full list (sized with it, so a grown maxneigh regrows them)
+static int eam_inrange_ensure(b200md_ctx *c)
+{
+  const size_t ntiles = (size_t) cdiv(c->nlocal, TILE);
+  TRY(dev_ensure(c, c->numneigh_in, (size_t) c->nlocal));
+  return dev_ensure(c, c->neigh_in, ntiles * TILE * c->maxneigh);
+}
+
 // {x,y,z,fp} records of atoms [first, first+n) from pos + fp (host-ghost mode: ghost fp arrives through the host)
 __global__ void k_posfp_fill(const double4 *__restrict__ pos, const double *__restrict__ fp, double4 *__restrict__ posfp,
                              int first, int n)
@@ -454,11 +474,12 @@ int pair_eam_rho(b200md_ctx *c, int ev)
     const int threads = EAM1T_THREADS, blocks = cdiv(n, threads);
     const size_t n1 = (size_t) T.nr + 1, smemA = 4 * n1 * 8;
     TRY(dev_ensure(c, c->posfp, (size_t) n + c->nghost));
+    TRY(eam_inrange_ensure(c));
     if (ev) TRY(dev_ensure(c, c->partials, (size_t) blocks * 8));
     TRY(eam_attrs_1t(c));
     {
       KProf kp(c, KC_EAM_RHO);
-#define A1 c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->rho.p, c->fp.p, c->posfp.p, c->partials.p, nullptr, -1
+#define A1 c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->rho.p, c->fp.p, c->posfp.p, c->partials.p, nullptr, -1, c->numneigh_in.p, c->neigh_in.p
       if (ev) k_eam_rho_fp_1t<1, 0><<<blocks, threads, smemA, c->stream>>>(A1);
       else k_eam_rho_fp_1t<0, 0><<<blocks, threads, smemA, c->stream>>>(A1);
 #undef A1
@@ -496,7 +517,7 @@ int pair_eam_force(b200md_ctx *c, int ev, bool ghost_from_fp)
     }
     {
       KProf kp(c, KC_PAIR);
-#define C1 c->posfp.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, -1
+#define C1 c->posfp.p, c->numneigh_in.p, c->neigh_in.p, c->maxneigh, n, P, T.tab1, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, -1
       if (ev) k_eam_force_1t<1, 0><<<blocks, threads, smemC, c->stream>>>(C1);
       else k_eam_force_1t<0, 0><<<blocks, threads, smemC, c->stream>>>(C1);
 #undef C1
@@ -541,11 +562,13 @@ int pair_eam_rho_part(b200md_ctx *c, int part)
   const int threads = part ? 128 : EAM1T_THREADS, blocks = cdiv(cnt * TILE, threads);
   const size_t n1 = (size_t) T.nr + 1, smemA = 4 * n1 * 8;
   TRY(dev_ensure(c, c->posfp, (size_t) n + c->nghost));
+  TRY(eam_inrange_ensure(c));
   if (cnt == 0) return B200MD_OK;
   TRY(eam_attrs_1t(c));
   KProf kp(c, KC_EAM_RHO);
   k_eam_rho_fp_1t<0, 1><<<blocks, threads, smemA, c->stream>>>(c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->rho.p,
-                                                                c->fp.p, c->posfp.p, c->partials.p, list, cnt);
+                                                                c->fp.p, c->posfp.p, c->partials.p, list, cnt, c->numneigh_in.p,
+                                                                c->neigh_in.p);
   LAUNCH_CHECK();
   return B200MD_OK;
 }
@@ -563,7 +586,7 @@ int pair_eam_force_part(b200md_ctx *c, int part)
   const size_t n1 = (size_t) T.nr + 1, smemC = 7 * n1 * 8;
   TRY(eam_attrs_1t(c));
   KProf kp(c, KC_PAIR);
-  k_eam_force_1t<0, 1><<<blocks, threads, smemC, c->stream>>>(c->posfp.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, P, T.tab1, c->f[0].p,
+  k_eam_force_1t<0, 1><<<blocks, threads, smemC, c->stream>>>(c->posfp.p, c->numneigh_in.p, c->neigh_in.p, c->maxneigh, n, P, T.tab1, c->f[0].p,
                                                                c->f[1].p, c->f[2].p, c->partials.p, list, cnt);
   LAUNCH_CHECK();
   return B200MD_OK;
@@ -587,7 +610,7 @@ int pair_eam_force_range(b200md_ctx *c, int first, int count)
   const size_t n1 = (size_t) T.nr + 1, smemC = 7 * n1 * 8;
   TRY(eam_attrs_1t(c));
   KProf kp(c, KC_PAIR);
-  k_eam_force_1t<0, 2><<<blocks, threads, smemC, c->stream>>>(c->posfp.p, c->numneigh.p, c->neigh.p, c->maxneigh, first + count, P, T.tab1,
+  k_eam_force_1t<0, 2><<<blocks, threads, smemC, c->stream>>>(c->posfp.p, c->numneigh_in.p, c->neigh_in.p, c->maxneigh, first + count, P, T.tab1,
                                                                c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, first);
   LAUNCH_CHECK();
   return B200MD_OK;
