@@ -299,6 +299,7 @@ int b200md_build_bins_per_block(const b200md_ctx *ctx);
  *   "host_pipeline"  0/1  b200md_step_host as a three-stream chunk pipeline (default 1) or serial copy-compute-copy
  *   "hs_min_chunk"   n    smallest system the pipeline splits into ranges (default 65536)
  *   "build_gb" n, "build_fp64" 0/1   test knobs of the list build (bins per block; force the all-FP64 fallback kernel)
+ *   "build_bond_general" 0/1         test knob: bonded build with the closest-image choice even where a tag is unique
  * Unknown key: B200MD_ERR_ARG. */
 int b200md_tune(b200md_ctx *ctx, const char *key, int value);
 

@@ -334,7 +334,6 @@ void bond_release(b200md_ctx *c)
   dev_free(c, c->bonds.type_by_tag);
   dev_free(c, c->bonds.idx);
   dev_free(c, c->bonds.best);
-  dev_free(c, c->rec_tag);
   dev_free(c, c->langevin.rand_d);
   dev_free(c, c->langevin.gamma_d);
   if (c->langevin.rand_h) cudaFreeHost(c->langevin.rand_h);

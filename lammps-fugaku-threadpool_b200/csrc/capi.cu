@@ -79,7 +79,7 @@ extern "C" int b200md_destroy(b200md_ctx *c)
   dev_free(c, c->tag); dev_free(c, c->tag_tmp); dev_free(c, c->image); dev_free(c, c->image_tmp);
   dev_free(c, c->rho); dev_free(c, c->fp); dev_free(c, c->posfp); dev_free(c, c->cutneighsq_d);
   dev_free(c, c->bin_count); dev_free(c, c->bin_start); dev_free(c, c->atom_bin); dev_free(c, c->cell_list);
-  dev_free(c, c->perm); dev_free(c, c->scan_tmp); dev_free(c, c->rec_xyz); dev_free(c, c->rec_jt); dev_free(c, c->pbin_start); dev_free(c, c->atom_sub); dev_free(c, c->numneigh); dev_free(c, c->neigh); dev_free(c, c->numneigh_in); dev_free(c, c->neigh_in); dev_free(c, c->tile_ghost); dev_free(c, c->tile_list); dev_free(c, c->tile_pos);
+  dev_free(c, c->perm); dev_free(c, c->scan_tmp); dev_free(c, c->rec); dev_free(c, c->pbin_start); dev_free(c, c->atom_sub); dev_free(c, c->numneigh); dev_free(c, c->neigh); dev_free(c, c->numneigh_in); dev_free(c, c->neigh_in); dev_free(c, c->tile_ghost); dev_free(c, c->tile_list); dev_free(c, c->tile_pos);
   dev_free(c, c->send_idx); dev_free(c, c->border_blockcnt); dev_free(c, c->border_total); dev_free(c, c->send_dir);
   dev_free(c, c->sendbuf_i); dev_free(c, c->allcounts); dev_free(c, c->sendbuf4); dev_free(c, c->recvbuf4); dev_free(c, c->sendbuf1);
   dev_free(c, c->partials); dev_free(c, c->stage); dev_free(c, c->peratom); dev_free(c, c->special.n3); dev_free(c, c->special.tags);
@@ -1203,6 +1203,7 @@ extern "C" int b200md_profile(b200md_ctx *c, int level)
 //   "host_pipeline" 0/1  b200md_step_host as a three-stream chunk pipeline (0: serial copy - compute - copy)
 //   "hs_min_chunk"  n    smallest system the pipeline splits into ranges (tests lower it)
 //   "build_gb" n, "build_fp64" 0/1   test knobs of the list build: bins per block; force the all-FP64 fallback kernel
+//   "build_bond_general" 0/1         test knob: bonded build with the closest-image choice even where images are unique
 extern "C" int b200md_tune(b200md_ctx *c, const char *key, int value)
 {
   NEED_CTX();
@@ -1212,6 +1213,8 @@ extern "C" int b200md_tune(b200md_ctx *c, const char *key, int value)
   else if (!strcmp(key, "hs_min_chunk")) c->hs_min_chunk = value > 0 ? value : 65536;
   else if (!strcmp(key, "build_gb")) c->build_gb_user = value > 0 ? value : 0;     // test knob
   else if (!strcmp(key, "build_fp64")) c->build_fp64 = value != 0;                 // test knob
+  else if (!strcmp(key, "build_threads")) { c->build_threads = value; c->seg_cap = 0; }   // 128 or 256 threads per block of the list build
+  else if (!strcmp(key, "build_bond_general")) c->build_bond_general = value != 0; // test knob
   else if (!strcmp(key, "build_seg_cap")) { c->seg_cap_user = value > 0 ? value : 0; c->seg_cap = 0; }   // test knob
   else return b200md_fail(c, B200MD_ERR_ARG, "b200md_tune: unknown key '%s'", key);
   return B200MD_OK;

@@ -172,13 +172,11 @@ struct b200md_ctx {
   BinGeom bg;
   DevBuf<int> bin_count, bin_start, atom_bin, cell_list, perm, scan_tmp;
   DevBuf<unsigned char> atom_sub;
-  // candidate records of the list build (neigh.cu): SoA in cell_list order with every bin padded to the build's vector
-  // width, so the 3 x (tg + 2) bins of a staged row are one contiguous, 16-byte aligned range of each array
-  DevBuf<float> rec_xyz;      // [3][rec_cap] FP32 coordinates relative to the bin-grid origin
-  DevBuf<int> rec_jt;         // [rec_cap] index | (type - 1) << 28
-  DevBuf<int> rec_tag;        // [rec_cap] tags (bonded / molecular systems only)
+  // candidate records of the list build (neigh.cu): cell_list order, every bin padded to the build's vector width, so the
+  // 3 x (tg + 2) bins of a staged row are ONE contiguous, 16-byte aligned range
+  DevBuf<float> rec;          // [rec_cap * nf] groups of vw records {x[vw], y[vw], z[vw], jt[vw] (, tag[vw])}: FP32 coordinates
+                              // relative to the bin-grid origin, index | (type - 1) << 28, tags for bonded / molecular systems
   DevBuf<int> pbin_start;     // [mbins + 1] padded start of every bin
-  size_t rec_cap = 0;
 
   // neighbor list
   int maxneigh = 0;
@@ -246,6 +244,8 @@ struct b200md_ctx {
   int hs_min_chunk = 65536;   // smallest system the pipeline splits into ranges
   int build_gb_user = 0;      // test knob: bins of an x-row per block in the list build (0 = by bin population)
   int seg_cap_user = 0;       // test knob: initial staging capacity of the list build (records)
+  int build_threads = 128;    // threads per block of the list build (128 or 256; the bins per block follow)
+  int build_bond_general = 0; // test knob: bonded build with the closest-image choice (BONDED 1) even where a tag is unique inside the cutoff
   int build_fp64 = 0;         // test knob: force the all-FP64 build kernel (otherwise only huge boxes with tiny cutoffs use it)
   int debug_timing = 0;       // per-phase wall times of every rebuild on stderr (B200MD_DEBUG_TIMING, read at create)
 

@@ -11,6 +11,7 @@
 // owned atoms are physically re-ordered by bin at every rebuild, ghosts are made in ONE stage from the
 // 26 direction masks instead of the reference's 6 staged swaps (same ghost set when every sub-domain is
 // at least one ghost cutoff wide), and the list is a full list in a blocked-transposed layout.
+#include <type_traits>
 #include <utility>
 
 #include "ctx.cuh"
@@ -364,8 +365,10 @@ k_build_fp64(const double4 *__restrict__ pos, int nlocal, BinGeom g, const int *
 #define BR_JMASK 0x0FFFFFFF
 #define SEG_FAR 1.0e18f   /* coordinate of a padding record: rsq = inf, never <= any cutoff */
 
-// candidate records, SoA, in cell_list order with every bin padded to the build's vector width VW: padded population
-// of each bin (its exclusive scan is pbin_start)
+// candidate records in cell_list order, every bin padded to the build's vector width VW (2 or 4) with records that can
+// never be accepted, laid out in GROUPS of VW records: {x[VW], y[VW], z[VW], jt[VW] (, tag[VW])} -- NF = 4 or 5 32-bit
+// fields -- so that the build reads a group's fields at fixed offsets from ONE pointer (LDS.128 / LDS.64 per field) and a
+// staged row is one contiguous range.  k_pad_count: padded population of each bin (its exclusive scan is pbin_start)
 __global__ void k_pad_count(const int *__restrict__ bin_start, int mbins, int vw, int *__restrict__ cnt)
 {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -373,11 +376,16 @@ __global__ void k_pad_count(const int *__restrict__ bin_start, int mbins, int vw
   cnt[b] = b < mbins ? ((bin_start[b + 1] - bin_start[b] + vw - 1) & ~(vw - 1)) : 0;
 }
 
-// record of cell_list position k: FP32 coordinates relative to the bin-grid origin, j | (type-1) << 28, tag
+// word of field f of record d (lg = log2 VW)
+__host__ __device__ __forceinline__ size_t rec_word(int d, int f, int lg, int nf)
+{
+  return ((((size_t) (d >> lg)) * nf + f) << lg) + (d & ((1 << lg) - 1));
+}
+
+// record of cell_list position k: FP32 coordinates relative to the bin-grid origin, j | (type-1) << 28, tag (nf == 5)
 __global__ void k_rec_fill(const double4 *__restrict__ pos, const int *__restrict__ cell_list, const int *__restrict__ atom_bin,
                            const int *__restrict__ bin_start, const int *__restrict__ pbin_start, int nall, double ox, double oy,
-                           double oz, float *__restrict__ rx, float *__restrict__ ry, float *__restrict__ rz,
-                           int *__restrict__ rjt, const int *__restrict__ tag, int *__restrict__ rtag)
+                           double oz, float *__restrict__ rec, int lg, int nf, const int *__restrict__ tag)
 {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= nall) return;
@@ -385,23 +393,25 @@ __global__ void k_rec_fill(const double4 *__restrict__ pos, const int *__restric
   const int b = atom_bin[j];
   const int d = pbin_start[b] + k - bin_start[b];
   const double4 p = pos[j];
-  rx[d] = (float) (p.x - ox);
-  ry[d] = (float) (p.y - oy);
-  rz[d] = (float) (p.z - oz);
-  rjt[d] = j | ((pos_type(p) - 1) << 28);
-  if (rtag) rtag[d] = tag[j];  // bonded / molecular systems: the candidate's tag, for the special-partner test
+  int *reci = reinterpret_cast<int *>(rec);
+  rec[rec_word(d, 0, lg, nf)] = (float) (p.x - ox);
+  rec[rec_word(d, 1, lg, nf)] = (float) (p.y - oy);
+  rec[rec_word(d, 2, lg, nf)] = (float) (p.z - oz);
+  reci[rec_word(d, 3, lg, nf)] = j | ((pos_type(p) - 1) << 28);
+  if (nf == 5) reci[rec_word(d, 4, lg, nf)] = tag[j];  // bonded / molecular systems: the candidate's tag, for the special-partner test
 }
 
 // the padding records at the end of every bin: never accepted
-__global__ void k_rec_pad(const int *__restrict__ bin_start, const int *__restrict__ pbin_start, int mbins, float *__restrict__ rx,
-                          float *__restrict__ ry, float *__restrict__ rz, int *__restrict__ rjt, int *__restrict__ rtag)
+__global__ void k_rec_pad(const int *__restrict__ bin_start, const int *__restrict__ pbin_start, int mbins, float *__restrict__ rec,
+                          int lg, int nf)
 {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= mbins) return;
+  int *reci = reinterpret_cast<int *>(rec);
   for (int d = pbin_start[b] + bin_start[b + 1] - bin_start[b]; d < pbin_start[b + 1]; d++) {
-    rx[d] = ry[d] = rz[d] = SEG_FAR;
-    rjt[d] = BR_JMASK;
-    if (rtag) rtag[d] = 0;
+    rec[rec_word(d, 0, lg, nf)] = rec[rec_word(d, 1, lg, nf)] = rec[rec_word(d, 2, lg, nf)] = SEG_FAR;
+    reci[rec_word(d, 3, lg, nf)] = BR_JMASK;
+    if (nf == 5) reci[rec_word(d, 4, lg, nf)] = 0;
   }
 }
 
@@ -434,11 +444,10 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned phas
 }
 #endif
 
-// BONDED == 1 (in.chain): a candidate within the cutoff whose tag is one of the atom's 1-2 partners is NOT listed
+// BONDED == 1 / 3 (in.chain): a candidate within the cutoff whose tag is one of the atom's 1-2 partners is NOT listed
 // (special_bonds lj weight 0, NPair::find_special src/npair.h:125-158 -> -1) but recorded as the device index of that
 // bond partner; of several periodic images the closest wins (Domain::closest_image).
 struct BondBuild {
-  const int *rec_tag;          // [nall] tag of each record, cell_list order
   const int *tag;              // [nall]
   const int *partner_by_tag;   // [ntags][maxb], 0 = empty
   int *bond_idx;               // [nlocal][maxb] out
@@ -449,34 +458,37 @@ struct BondBuild {
   int maxspecial;
   int flag[4];                 // 0 drop, 1 ordinary neighbor, 2 keep with the class in bits 28-29 of the entry
 };
-#define SEG_THREADS 128
-// shared-memory plan of a segment: SoA candidate arrays of `cap` elements.  The records arrive already padded (every bin
-// to a multiple of VW with records that can never be accepted: k_rec_fill / k_rec_pad), so a thread reads VW candidates
-// with one LDS.128 (VW = 4, dense bins) or LDS.64 (VW = 2, sparse bins such as in.chain's 3 beads per bin, where
-// padding to 4 would add a third more candidates) per array and every bin range is VW-aligned: no per-candidate range
-// tests.  A staged row (the 3 x (tg + 2) bins of one (dz, dy)) is ONE contiguous range of each global array: with VW = 4
-// it is 16-byte aligned and goes to shared memory as 1-D bulk copies through the TMA engine (cp.async.bulk, completion
-// on an mbarrier) -- 36 copies issued by one thread instead of a thousand LDG/STS pairs.
-//   float x[cap], y[cap], z[cap]; int jt[cap] (index | (type-1) << 28); int tag[cap] (BONDED);
+#define SEG_THREADS 128       /* default block: about 112 owned atoms */
+#define SEG_MAX_THREADS 256   /* "build_threads" (b200md_tune) may ask for this many */
+// shared-memory plan of a segment: `cap` candidate records in the grouped layout of k_rec_fill (a thread reads the VW
+// candidates of a group with one LDS.128 (VW = 4, dense bins) or LDS.64 (VW = 2, sparse bins such as in.chain's 3 beads
+// per bin, where padding to 4 would add a third more candidates) per field, all at fixed offsets from one pointer), every
+// bin range VW-aligned: no per-candidate range tests.  A staged row (the 3 x (tg + 2) bins of one (dz, dy)) is ONE
+// contiguous range of the global records: where a group is a multiple of 16 bytes it goes to shared memory as one 1-D
+// bulk copy through the TMA engine (cp.async.bulk, completion on an mbarrier) -- 9 copies issued by one thread.
+//   float rec[cap * NF];
 //   int bs[9][tg+3]  cell_list position of each staged bin's first record (+ the end);
-//   int po[9][tg+3]  staged offset of each staged bin (+ the end)
+//   int po[9][tg+3]  staged offset (in records) of each staged bin (+ the end)
+// BONDED: 0 atomic; 1 bonds, any box (of several periodic images of a partner the closest wins); 2 the general special
+// lists of host-ghost molecular systems; 3 bonds, at most 2 per atom, in a box wider than 2 cutoffs in every periodic
+// dimension (a tag then appears at most once inside the cutoff: no image choice to make) -- in.chain.
 struct RecArrays {
-  const float *x, *y, *z;   // [rec_cap]
-  const int *jt;            // [rec_cap]
+  const float *rec;         // [rec_cap * NF]
   const int *pbin_start;    // [mbins + 1]
 };
 template <int ONETYPE, int BONDED, int VW>
-__global__ void __launch_bounds__(SEG_THREADS)
+__global__ void __launch_bounds__(SEG_MAX_THREADS)
 k_build_seg(const double4 *__restrict__ pos, RecArrays rec, int nlocal, BinGeom g,
-            const int *__restrict__ bin_start, const double *__restrict__ cutneighsq, int ntypes, float tol, int maxneigh,
+            const int *__restrict__ bin_start, const double *__restrict__ cutneighsq, int ntypes, float tol, float hw, int maxneigh,
             int *__restrict__ numneigh, int *__restrict__ neigh, int *__restrict__ flags, int *__restrict__ tile_ghost,
             BondBuild bb, int tg, int cap)
 {
+  constexpr int NF = BONDED ? 5 : 4;   // 32-bit fields per record
+  constexpr int GW = NF * VW;          // words per group
+  constexpr int LG = VW == 4 ? 2 : 1;
   extern __shared__ int4 s_dyn[];
-  float *s_x = reinterpret_cast<float *>(s_dyn), *s_y = s_x + cap, *s_z = s_y + cap;
-  int *s_jt = reinterpret_cast<int *>(s_z + cap);
-  int *s_tag = s_jt + cap;                                           // BONDED only
-  int *s_bs = s_tag + (BONDED ? cap : 0);
+  float *s_rec = reinterpret_cast<float *>(s_dyn);
+  int *s_bs = reinterpret_cast<int *>(s_dyn) + (size_t) cap * NF;
   const int W = tg + 3;
   int *s_po = s_bs + 9 * W;
   __shared__ double s_cut[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
@@ -498,8 +510,9 @@ k_build_seg(const double4 *__restrict__ pos, RecArrays rec, int nlocal, BinGeom 
     s_bs[r * W + q] = bin_start[first + q];
     s_po[r * W + q] = rec.pbin_start[first + q];
   }
+  constexpr bool BULK_OK = (GW * 4) % 16 == 0;   // a row's bytes and its two addresses are multiples of 16
 #ifndef B200MD_CUDAEMU
-  if (VW == 4 && threadIdx.x == 0) mbar_init(&s_bar, 1);
+  if (BULK_OK && threadIdx.x == 0) mbar_init(&s_bar, 1);
 #endif
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -519,32 +532,23 @@ k_build_seg(const double4 *__restrict__ pos, RecArrays rec, int nlocal, BinGeom 
   // stage the 9 rows
   bool bulk = false;
 #ifndef B200MD_CUDAEMU
-  bulk = VW == 4;
+  bulk = BULK_OK;
   if (bulk && threadIdx.x == 0) {
-    mbar_expect_tx(&s_bar, (unsigned) total * (BONDED ? 20u : 16u));
+    mbar_expect_tx(&s_bar, (unsigned) total * (unsigned) (NF * 4));
     for (int r = 0; r < 9; r++) {
       const int gs = s_po[r * W], len = s_po[r * W + gx + 2] - gs, so = s_row[r];
       if (len == 0) continue;
-      const unsigned bytes = (unsigned) len * 4u;
-      bulk_g2s(s_x + so, rec.x + gs, bytes, &s_bar);
-      bulk_g2s(s_y + so, rec.y + gs, bytes, &s_bar);
-      bulk_g2s(s_z + so, rec.z + gs, bytes, &s_bar);
-      bulk_g2s(s_jt + so, rec.jt + gs, bytes, &s_bar);
-      if (BONDED) bulk_g2s(s_tag + so, bb.rec_tag + gs, bytes, &s_bar);
+      bulk_g2s(s_rec + (size_t) so * NF, rec.rec + (size_t) gs * NF, (unsigned) len * (unsigned) (NF * 4), &s_bar);
     }
   }
 #endif
-  if (!bulk) {
+  if (!bulk) {   // groups of 40 bytes (VW = 2 with tags): 8-byte units
 #pragma unroll 1
     for (int r = 0; r < 9; r++) {
       const int gs = s_po[r * W], len = s_po[r * W + gx + 2] - gs, so = s_row[r];
-      for (int k = threadIdx.x; k < len; k += blockDim.x) {
-        s_x[so + k] = __ldg(rec.x + gs + k);
-        s_y[so + k] = __ldg(rec.y + gs + k);
-        s_z[so + k] = __ldg(rec.z + gs + k);
-        s_jt[so + k] = __ldg(rec.jt + gs + k);
-        if (BONDED) s_tag[so + k] = __ldg(bb.rec_tag + gs + k);
-      }
+      const float2 *src = reinterpret_cast<const float2 *>(rec.rec + (size_t) gs * NF);
+      float2 *dst = reinterpret_cast<float2 *>(s_rec + (size_t) so * NF);
+      for (int k = threadIdx.x; k < len * NF / 2; k += blockDim.x) dst[k] = __ldg(src + k);
     }
   }
   __syncthreads();   // the copies are issued (or done): s_po's global starts are no longer needed as such
@@ -557,8 +561,14 @@ k_build_seg(const double4 *__restrict__ pos, RecArrays rec, int nlocal, BinGeom 
   if (bulk) mbar_wait(&s_bar, 0);
 #endif
   __syncthreads();
+  const int *s_reci = reinterpret_cast<const int *>(s_rec);
+  auto word = [](int d, int f) -> int { return (((d >> LG) * NF + f) << LG) + (d & (VW - 1)); };
   const float cut1 = s_cutf[nt1 + 1];
   const int own_s = s_bs[4 * W + 1], own_e = s_bs[4 * W + 1 + gx];
+  // a group's appends start at row min(n, ncap) and take at most VW rows: they stay inside the tile's rows without a
+  // clamp per entry.  Past ncap the rows are wrong, but the count stays true and the host redoes every build whose
+  // longest list exceeds maxneigh - 4 with longer rows.
+  const int ncap = maxneigh - VW;
   int nmax = 0;
   // the segment's own records (centre row, bins 1..gx); owned atoms come first in every bin's records (cell_list is
   // index-ordered within a bin, ghosts have index >= nlocal)
@@ -566,18 +576,19 @@ k_build_seg(const double4 *__restrict__ pos, RecArrays rec, int nlocal, BinGeom 
     int bl = 0;   // my bin inside the segment, from my position in cell_list (exact; a float coordinate is not)
     while (slot >= s_bs[4 * W + bl + 2]) bl++;
     const int mine = s_po[4 * W + bl + 1] + slot - s_bs[4 * W + bl + 1];
-    const int myjt = s_jt[mine];
+    const int myjt = s_reci[word(mine, 3)];
     const int i = myjt & BR_JMASK;
     if (i >= nlocal) continue;
     const int trow = ONETYPE ? 0 : (((unsigned) myjt >> 28) + 1) * nt1;
     int *const nbp = neigh + ((size_t) (i >> 5) * TILE * maxneigh + (i & 31));
-    const int nlastrow = maxneigh - 1;
-    const float mx = s_x[mine], my = s_y[mine], mz = s_z[mine];
+    const float mx = s_rec[word(mine, 0)], my = s_rec[word(mine, 1)], mz = s_rec[word(mine, 2)];
     const float2 nx = make_float2(-mx, -mx), ny = make_float2(-my, -my), nz = make_float2(-mz, -mz);
+    const float2 ncut = make_float2(-cut1, -cut1);
     int n = 0;
     bool ghost_near = false;   // overlap mode: a ghost record among my candidates (a superset of "a ghost in my list")
     int ptag[B200MD_MAXBONDS], pbest[B200MD_MAXBONDS];
     float prsq[B200MD_MAXBONDS];
+    int ptag0 = 0, ptag1 = 0, pb0 = -1, pb1 = -1;
     if (BONDED == 1) {
       const int ti = bb.tag[i];
 #pragma unroll
@@ -587,7 +598,11 @@ k_build_seg(const double4 *__restrict__ pos, RecArrays rec, int nlocal, BinGeom 
         prsq[m] = 3.0e38f;
       }
     }
-    const float cut_lo1 = cut1 - tol, cut_hi1 = cut1 + tol;
+    if (BONDED == 3) {
+      const int ti = bb.tag[i];
+      ptag0 = bb.partner_by_tag[(size_t) (ti - 1) * bb.maxb];
+      ptag1 = bb.maxb > 1 ? bb.partner_by_tag[(size_t) (ti - 1) * bb.maxb + 1] : 0;
+    }
     // the ambiguity band (about 1 candidate in 10^4): the reference's FP64 expression decides
     auto exact = [&](const int jt) -> bool {
       const double4 pi = pos[i], pj = pos[jt & BR_JMASK];
@@ -595,42 +610,121 @@ k_build_seg(const double4 *__restrict__ pos, RecArrays rec, int nlocal, BinGeom 
       const double r2 = __dadd_rn(__dadd_rn(__dmul_rn(ddx, ddx), __dmul_rn(ddy, ddy)), __dmul_rn(ddz, ddz));
       return r2 <= s_cut[(ONETYPE ? nt1 : trow) + (ONETYPE ? 1 : ((unsigned) jt >> 28) + 1)];
     };
-    // predicated append.  Entries beyond maxneigh pile up in the last row: the count flags the overflow and the host
-    // redoes the build with longer rows.
-    auto append = [&](const int jt, const float rsq, const int k, bool accept) {
-      const int j = ONETYPE ? jt : (jt & BR_JMASK);   // one type: the type bits are zero
-      accept = accept && j != i;
-      int entry = j;
-      if (BONDED == 1) {
-        // branch-free: with 2 bonds per bead some lane of a warp meets a partner at most steps, and a divergent body
-        // run by 3-4 lanes was a fifth of this kernel's instructions (ncu source view, profiles/r02_ncu_build.md).
-        // Empty slots hold tag 0, padding records carry tag 0 but are never accepted.
-        const int tj = s_tag[k];
-        bool partner = false;
+    // the VW verdicts of a group appended in order.  SELF: the centre row alone holds my own record.
+    auto append_group = [&](auto self_c, const bool (&a)[VW], const int (&js)[VW], const int (&ts)[VW], const float (&rs)[VW]) {
+      constexpr bool SELF = decltype(self_c)::value;
+      const int n0 = min(n, ncap);
+      int row = n0;
 #pragma unroll
-        for (int m = 0; m < B200MD_MAXBONDS; m++) {
-          const bool hit = accept && tj == ptag[m];
-          const bool closer = hit && rsq < prsq[m];
-          partner |= hit;
-          prsq[m] = closer ? rsq : prsq[m];
-          pbest[m] = closer ? j : pbest[m];
-        }
-        accept = accept && !partner;
-      }
-      if (BONDED == 2 && accept) {   // NPair::find_special: first match in the atom's 1-2 | 1-3 | 1-4 list decides
-        const int tj = s_tag[k];
-        const int n1 = bb.spec_n3[3 * i], n2 = bb.spec_n3[3 * i + 1], n3 = bb.spec_n3[3 * i + 2];
-        const int *sp = bb.spec_tags + (size_t) i * bb.maxspecial;
-        for (int m = 0; m < n3; m++)
-          if (sp[m] == tj) {
-            const int which = m < n1 ? 1 : (m < n2 ? 2 : 3);
-            if (bb.flag[which] == 0) accept = false;
-            else if (bb.flag[which] == 2) entry = j | (which << CLBITS);
-            break;
+      for (int u = 0; u < VW; u++) {
+        const int j = ONETYPE ? js[u] : (js[u] & BR_JMASK);   // one type: the type bits are zero
+        bool accept = a[u];
+        if (SELF) accept = accept && j != i;
+        int entry = j;
+        if (BONDED == 1) {
+          // branch-free: with 2 bonds per bead some lane of a warp meets a partner at most steps, and a divergent body
+          // run by 3-4 lanes was a fifth of this kernel's instructions (ncu source view, profiles/r02_ncu_build.md).
+          // Empty slots hold tag 0, padding records carry tag 0 but are never accepted.
+          const int tj = ts[u];
+          bool partner = false;
+#pragma unroll
+          for (int m = 0; m < B200MD_MAXBONDS; m++) {
+            const bool hit = accept && tj == ptag[m];
+            const bool closer = hit && rs[u] < prsq[m];
+            partner |= hit;
+            prsq[m] = closer ? rs[u] : prsq[m];
+            pbest[m] = closer ? j : pbest[m];
           }
+          accept = accept && !partner;
+        }
+        if (BONDED == 3) {   // a partner inside the cutoff is unique: no distance to compare
+          const int tj = ts[u];
+          const bool h0 = accept && tj == ptag0, h1 = accept && tj == ptag1;
+          pb0 = h0 ? j : pb0;
+          pb1 = h1 ? j : pb1;
+          accept = accept && !(h0 || h1);
+        }
+        if (BONDED == 2 && accept) {   // NPair::find_special: first match in the atom's 1-2 | 1-3 | 1-4 list decides
+          const int tj = ts[u];
+          const int n1 = bb.spec_n3[3 * i], n2 = bb.spec_n3[3 * i + 1], n3 = bb.spec_n3[3 * i + 2];
+          const int *sp = bb.spec_tags + (size_t) i * bb.maxspecial;
+          for (int m = 0; m < n3; m++)
+            if (sp[m] == tj) {
+              const int which = m < n1 ? 1 : (m < n2 ? 2 : 3);
+              if (bb.flag[which] == 0) accept = false;
+              else if (bb.flag[which] == 2) entry = j | (which << CLBITS);
+              break;
+            }
+        }
+        if (accept) {
+          nbp[(size_t) row * TILE] = entry;
+          row++;
+        }
       }
-      if (accept) nbp[(size_t) min(n, nlastrow) * TILE] = entry;
-      n += accept ? 1 : 0;
+      n += row - n0;
+    };
+    // one group: VW squared distances through the packed FP32 pipe (fadd2 / fmul2 / ffma2; same operations and rounding
+    // as the scalar form rsq = fma(dz, dz, fma(dy, dy, dx * dx)) that build_tolerance() bounds), d = rsq - cutoff, the
+    // verdict d <= 0 on the common path, and ONE rare branch for the group: taken iff some |d| <= hw (hw covers the
+    // rigorous FP32 error bound tol and the rounding of d), where the FP64 expression decides for those candidates
+    auto group = [&](auto self_c, const float *gp) {
+      float rs[VW], d[VW];
+      int js[VW], ts[VW];
+      if constexpr (VW == 4) {
+        const float4 X = *reinterpret_cast<const float4 *>(gp), Y = *reinterpret_cast<const float4 *>(gp + 4),
+                     Z = *reinterpret_cast<const float4 *>(gp + 8);
+        const int4 J = *reinterpret_cast<const int4 *>(gp + 12);
+        const float2 dxa = __fadd2_rn(make_float2(X.x, X.y), nx), dxb = __fadd2_rn(make_float2(X.z, X.w), nx);
+        const float2 dya = __fadd2_rn(make_float2(Y.x, Y.y), ny), dyb = __fadd2_rn(make_float2(Y.z, Y.w), ny);
+        const float2 dza = __fadd2_rn(make_float2(Z.x, Z.y), nz), dzb = __fadd2_rn(make_float2(Z.z, Z.w), nz);
+        const float2 ra = __ffma2_rn(dza, dza, __ffma2_rn(dya, dya, __fmul2_rn(dxa, dxa)));
+        const float2 rb = __ffma2_rn(dzb, dzb, __ffma2_rn(dyb, dyb, __fmul2_rn(dxb, dxb)));
+        rs[0] = ra.x; rs[1] = ra.y; rs[2] = rb.x; rs[3] = rb.y;
+        js[0] = J.x; js[1] = J.y; js[2] = J.z; js[3] = J.w;
+        if (BONDED) {
+          const int4 T = *reinterpret_cast<const int4 *>(gp + 16);
+          ts[0] = T.x; ts[1] = T.y; ts[2] = T.z; ts[3] = T.w;
+        }
+        if (ONETYPE) {
+          const float2 da = __fadd2_rn(ra, ncut), db = __fadd2_rn(rb, ncut);
+          d[0] = da.x; d[1] = da.y; d[2] = db.x; d[3] = db.y;
+        }
+      } else {
+        const float2 X = *reinterpret_cast<const float2 *>(gp), Y = *reinterpret_cast<const float2 *>(gp + 2),
+                     Z = *reinterpret_cast<const float2 *>(gp + 4);
+        const int2 J = *reinterpret_cast<const int2 *>(gp + 6);
+        const float2 dxa = __fadd2_rn(X, nx), dya = __fadd2_rn(Y, ny), dza = __fadd2_rn(Z, nz);
+        const float2 ra = __ffma2_rn(dza, dza, __ffma2_rn(dya, dya, __fmul2_rn(dxa, dxa)));
+        rs[0] = ra.x; rs[1] = ra.y;
+        js[0] = J.x; js[1] = J.y;
+        if (BONDED) {
+          const int2 T = *reinterpret_cast<const int2 *>(gp + 8);
+          ts[0] = T.x; ts[1] = T.y;
+        }
+        if (ONETYPE) {
+          const float2 da = __fadd2_rn(ra, ncut);
+          d[0] = da.x; d[1] = da.y;
+        }
+      }
+      if (!ONETYPE) {
+#pragma unroll
+        for (int u = 0; u < VW; u++) d[u] = rs[u] - s_cutf[trow + ((unsigned) js[u] >> 28) + 1];
+      }
+      bool acc[VW];
+      float dmin = fabsf(d[0]);
+#pragma unroll
+      for (int u = 0; u < VW; u++) {
+        acc[u] = d[u] <= 0.f;
+        if (u) dmin = fminf(dmin, fabsf(d[u]));
+      }
+      if (__builtin_expect(dmin <= hw, 0)) {
+        bool a2[VW];
+#pragma unroll
+        for (int u = 0; u < VW; u++) a2[u] = fabsf(d[u]) <= hw ? exact(js[u]) : acc[u];
+        append_group(self_c, a2, js, ts, rs);
+      } else {
+        append_group(self_c, acc, js, ts, rs);
+      }
     };
 #pragma unroll 1
     for (int r = 0; r < 9; r++) {
@@ -639,72 +733,14 @@ k_build_seg(const double4 *__restrict__ pos, RecArrays rec, int nlocal, BinGeom 
 #pragma unroll
         for (int q = 0; q < 3; q++) {
           const int cnt = s_bs[r * W + bl + q + 1] - s_bs[r * W + bl + q];
-          if (cnt > 0) ghost_near |= (s_jt[s_po[r * W + bl + q] + cnt - 1] & BR_JMASK) >= nlocal;
+          if (cnt > 0) ghost_near |= (s_reci[word(s_po[r * W + bl + q] + cnt - 1, 3)] & BR_JMASK) >= nlocal;
         }
       }
-      // VW verdicts from VW FP32 distances: one compare each on the common path (provisionally inside iff
-      // rsq <= cut + tol), then ONE rare branch for the group: taken iff the largest provisionally-inside distance
-      // lies above cut - tol, i.e. some candidate sits in the ambiguity band
-      auto group = [&](const float (&rs)[VW], const int (&js)[VW], const int k0) {
-        bool acc[VW];
-        if (ONETYPE) {
-          float worst = 0.f;
-#pragma unroll
-          for (int u = 0; u < VW; u++) {
-            acc[u] = rs[u] <= cut_hi1;
-            worst = fmaxf(worst, acc[u] ? rs[u] : 0.f);
-          }
-          if (__builtin_expect(worst > cut_lo1, 0)) {
-#pragma unroll
-            for (int u = 0; u < VW; u++)
-              if (acc[u] && rs[u] > cut_lo1) acc[u] = exact(js[u]);
-          }
-        } else {
-          bool band = false;
-          float cl[VW];
-#pragma unroll
-          for (int u = 0; u < VW; u++) {
-            const float cut = s_cutf[trow + ((unsigned) js[u] >> 28) + 1];
-            cl[u] = cut - tol;
-            acc[u] = rs[u] <= cut + tol;
-            band |= acc[u] && rs[u] > cl[u];
-          }
-          if (__builtin_expect(band, 0)) {
-#pragma unroll
-            for (int u = 0; u < VW; u++)
-              if (acc[u] && rs[u] > cl[u]) acc[u] = exact(js[u]);
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < VW; u++) append(js[u], rs[u], k0 + u, acc[u]);
-      };
-      // packed FP32 (fadd2 / fmul2 / ffma2): two squared distances per instruction triple; same operations and rounding
-      // as the scalar form rsq = fma(dz, dz, fma(dy, dy, dx * dx)) that build_tolerance() bounds
-      if constexpr (VW == 4) {
-        for (int k = lo; k < hi; k += 4) {
-          const float4 X = *reinterpret_cast<const float4 *>(s_x + k), Y = *reinterpret_cast<const float4 *>(s_y + k),
-                       Z = *reinterpret_cast<const float4 *>(s_z + k);
-          const int4 J = *reinterpret_cast<const int4 *>(s_jt + k);
-          const float2 dxa = __fadd2_rn(make_float2(X.x, X.y), nx), dxb = __fadd2_rn(make_float2(X.z, X.w), nx);
-          const float2 dya = __fadd2_rn(make_float2(Y.x, Y.y), ny), dyb = __fadd2_rn(make_float2(Y.z, Y.w), ny);
-          const float2 dza = __fadd2_rn(make_float2(Z.x, Z.y), nz), dzb = __fadd2_rn(make_float2(Z.z, Z.w), nz);
-          const float2 ra = __ffma2_rn(dza, dza, __ffma2_rn(dya, dya, __fmul2_rn(dxa, dxa)));
-          const float2 rb = __ffma2_rn(dzb, dzb, __ffma2_rn(dyb, dyb, __fmul2_rn(dxb, dxb)));
-          const float rs[VW] = {ra.x, ra.y, rb.x, rb.y};
-          const int js[VW] = {J.x, J.y, J.z, J.w};
-          group(rs, js, k);
-        }
+      const float *gp = s_rec + (size_t) lo * NF, *const ge = s_rec + (size_t) hi * NF;
+      if (r == 4) {
+        for (; gp < ge; gp += GW) group(std::true_type{}, gp);
       } else {
-        for (int k = lo; k < hi; k += 2) {
-          const float2 X = *reinterpret_cast<const float2 *>(s_x + k), Y = *reinterpret_cast<const float2 *>(s_y + k),
-                       Z = *reinterpret_cast<const float2 *>(s_z + k);
-          const int2 J = *reinterpret_cast<const int2 *>(s_jt + k);
-          const float2 dxa = __fadd2_rn(X, nx), dya = __fadd2_rn(Y, ny), dza = __fadd2_rn(Z, nz);
-          const float2 ra = __ffma2_rn(dza, dza, __ffma2_rn(dya, dya, __fmul2_rn(dxa, dxa)));
-          const float rs[VW] = {ra.x, ra.y};
-          const int js[VW] = {J.x, J.y};
-          group(rs, js, k);
-        }
+        for (; gp < ge; gp += GW) group(std::false_type{}, gp);
       }
     }
     numneigh[i] = n;
@@ -715,6 +751,11 @@ k_build_seg(const double4 *__restrict__ pos, RecArrays rec, int nlocal, BinGeom 
           bb.bond_idx[(size_t) i * bb.maxb + m] = pbest[m];
           if (ptag[m] != 0 && pbest[m] < 0) flags[5] = 1;  // "Bond atoms missing" (src/ntopo_bond_all.cpp:56-61)
         }
+    }
+    if (BONDED == 3) {
+      bb.bond_idx[(size_t) i * bb.maxb] = pb0;
+      if (bb.maxb > 1) bb.bond_idx[(size_t) i * bb.maxb + 1] = pb1;
+      if ((ptag0 != 0 && pb0 < 0) || (ptag1 != 0 && pb1 < 0)) flags[5] = 1;
     }
     if (tile_ghost && ghost_near) tile_ghost[i >> 5] = 1;   // several lanes may write the same 1
     nmax = max(nmax, n);
@@ -903,7 +944,7 @@ int neigh_build_lists(b200md_ctx *c)
         tile_ghost = c->tile_ghost.p;
       }
       c->tiles_valid = tile_ghost != nullptr;
-      BondBuild bb = {nullptr, nullptr, nullptr, nullptr, 0, nullptr, nullptr, 0, {1, 1, 1, 1}};
+      BondBuild bb = {nullptr, nullptr, nullptr, 0, nullptr, nullptr, 0, {1, 1, 1, 1}};
       const bool bonded = c->bonds.maxb > 0, special = c->special.on && !bonded;
       if (special) {
         if (!c->host_ghosts) return b200md_fail(c, B200MD_ERR_ARG, "general special-bond lists are a host-ghost mode feature (b200md_host_special)");
@@ -922,45 +963,45 @@ int neigh_build_lists(b200md_ctx *c)
       // bins per block: about 112 owned atoms on 128 threads (lj melt: 18.5 atoms per bin -> 6 bins; chain melt: 3 per
       // bin -> 37); "build_gb" overrides (tests)
       const double per_bin = (double) n / (nown > 0 ? nown : 1);
-      int tg = c->build_gb_user > 0 ? c->build_gb_user : (int) (112.0 / (per_bin > 0.1 ? per_bin : 0.1) + 0.5);
+      const int bthreads = c->build_threads == SEG_MAX_THREADS ? SEG_MAX_THREADS : SEG_THREADS;
+      int tg = c->build_gb_user > 0 ? c->build_gb_user : (int) (0.875 * bthreads / (per_bin > 0.1 ? per_bin : 0.1) + 0.5);
       tg = tg < 1 ? 1 : (tg > g.nbin[0] ? g.nbin[0] : tg);
       // staging area: the 3 x 3 x (tg + 2) bins of a segment with 8 % head room; a denser segment reports its size
       // through flags[6] and the build is redone with room for it (like the maxneigh retry below)
-      const size_t rec_bytes = (bonded || special) ? 20 : 16;
+      const size_t rec_bytes = (bonded || special) ? 20 : 16;   // 4 or 5 fields per staged record
       auto seg_smem = [&](int t, int cap) { return (size_t) cap * rec_bytes + (size_t) (2 * 9 * (t + 3)) * sizeof(int); };
       if (c->seg_cap_tg != tg) { c->seg_cap = 0; c->seg_cap_tg = tg; }
       if (c->seg_cap == 0 && c->seg_cap_user > 0) c->seg_cap = (c->seg_cap_user + 3) & ~3;   // test knob: start too small, exercise the retry
       // (every staged bin is padded to a multiple of vw records: + (vw - 1) / 2 on average)
       const int vw = (per_bin >= 8.0 && !(c->special.on && c->bonds.maxb == 0)) ? 4 : 2;
-      // the candidate records: FP32, SoA, every bin padded to vw (k_pad_count -> scan -> k_rec_fill + k_rec_pad)
+      // the candidate records: FP32, groups of vw, every bin padded to vw (k_pad_count -> scan -> k_rec_fill + k_rec_pad)
+      const int nf = (bonded || special) ? 5 : 4, lg = vw == 4 ? 2 : 1;
       {
         const int mb = g.mbins;
         const size_t cap_rec = (((size_t) nall + (size_t) (vw - 1) * (size_t) (mb < nall ? mb : nall)) + 63) & ~(size_t) 63;
         TRY(dev_ensure(c, c->pbin_start, (size_t) mb + 1));
-        TRY(dev_ensure(c, c->rec_jt, cap_rec));
-        if (c->rec_xyz.n < 3 * c->rec_jt.n) TRY(dev_ensure(c, c->rec_xyz, 3 * c->rec_jt.n, false, false));
-        c->rec_cap = c->rec_xyz.n / 3 & ~(size_t) 3;
-        int *rtag = nullptr;
-        if (bonded || special) {
-          TRY(dev_ensure(c, c->rec_tag, c->rec_cap));
-          rtag = c->rec_tag.p;
-        }
+        TRY(dev_ensure(c, c->rec, cap_rec * nf));
         // bin_count is free after the sort: it holds the padded populations until the scan has run
         k_pad_count<<<cdiv(mb + 1, 256), 256, 0, c->stream>>>(c->bin_start.p, mb, vw, c->bin_count.p);
         LAUNCH_CHECK();
         TRY(exclusive_scan(c, c->bin_count.p, c->pbin_start.p, mb + 1));
-        float *rx = c->rec_xyz.p, *ry = rx + c->rec_cap, *rz = ry + c->rec_cap;
         k_rec_fill<<<cdiv(nall, 256), 256, 0, c->stream>>>(c->pos.p, c->cell_list.p, c->atom_bin.p, c->bin_start.p, c->pbin_start.p, nall,
                                                           g.lo[0] - BIN_MARGIN / g.inv[0], g.lo[1] - BIN_MARGIN / g.inv[1],
-                                                          g.lo[2] - BIN_MARGIN / g.inv[2], rx, ry, rz, c->rec_jt.p, c->tag.p, rtag);
+                                                          g.lo[2] - BIN_MARGIN / g.inv[2], c->rec.p, lg, nf, c->tag.p);
         LAUNCH_CHECK();
-        if (vw > 1) {
-          k_rec_pad<<<cdiv(mb, 256), 256, 0, c->stream>>>(c->bin_start.p, c->pbin_start.p, mb, rx, ry, rz, c->rec_jt.p, rtag);
-          LAUNCH_CHECK();
-        }
-        bb.rec_tag = rtag;
+        k_rec_pad<<<cdiv(mb, 256), 256, 0, c->stream>>>(c->bin_start.p, c->pbin_start.p, mb, c->rec.p, lg, nf);
+        LAUNCH_CHECK();
       }
-      const RecArrays rec = {c->rec_xyz.p, c->rec_xyz.p + c->rec_cap, c->rec_xyz.p + 2 * c->rec_cap, c->rec_jt.p, c->pbin_start.p};
+      const RecArrays rec = {c->rec.p, c->pbin_start.p};
+      // bonds without an image choice: at most 2 per atom and every periodic dimension wider than 2 cutoffs
+      bool unique_images = c->bonds.maxb <= 2 && !c->build_bond_general;
+      for (int k = 0; k < 3; k++)
+        if (c->periodic[k] && !(c->prd[k] > 2.0 * c->cutneighmax)) unique_images = false;
+      // half-width of the band in which the FP64 expression decides: the FP32 error bound + the rounding of rsq - cutoff
+      double cutsq_max = 0.0;
+      for (int i = 1; i <= c->ntypes; i++)
+        for (int j = 1; j <= c->ntypes; j++) cutsq_max = fmax(cutsq_max, c->cutneighsq_h[i * (c->ntypes + 1) + j]);
+      const float hw = (float) (tol * 1.0001 + cutsq_max * 2.4e-7);
       if (c->seg_cap == 0) c->seg_cap = (int) (1.08 * 9.0 * (tg + 2) * ((double) nall / (nown > 0 ? nown : 1) + 0.5 * (vw - 1))) + 64;
       if (c->seg_cap > nall + 27 * (tg + 2)) c->seg_cap = nall + 27 * (tg + 2);   // no segment can stage more than exists
       c->seg_cap = (c->seg_cap + 3) & ~3;
@@ -978,25 +1019,31 @@ int neigh_build_lists(b200md_ctx *c)
         CU(cudaFuncSetAttribute(k_build_seg<0, 0, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(cudaFuncSetAttribute(k_build_seg<1, 1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(cudaFuncSetAttribute(k_build_seg<0, 1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(cudaFuncSetAttribute(k_build_seg<1, 3, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(cudaFuncSetAttribute(k_build_seg<0, 3, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(cudaFuncSetAttribute(k_build_seg<1, 0, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(cudaFuncSetAttribute(k_build_seg<0, 0, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(cudaFuncSetAttribute(k_build_seg<1, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(cudaFuncSetAttribute(k_build_seg<0, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(cudaFuncSetAttribute(k_build_seg<1, 3, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(cudaFuncSetAttribute(k_build_seg<0, 3, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(cudaFuncSetAttribute(k_build_seg<0, 2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr_done[c->device & 63] = true;
       }
       const size_t bsmem = seg_smem(tg, c->seg_cap);
-#define BB_ARGS c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d, tile_ghost, bb, tg, c->seg_cap
-#define BB_LAUNCH(OT, BD, V) k_build_seg<OT, BD, V><<<bgrid, SEG_THREADS, bsmem, c->stream>>>(BB_ARGS)
+#define BB_ARGS c->pos.p, rec, n, g, c->bin_start.p, c->cutneighsq_d.p, c->ntypes, (float) tol, hw, c->maxneigh, c->numneigh.p, c->neigh.p, c->flags_d, tile_ghost, bb, tg, c->seg_cap
+#define BB_LAUNCH(OT, BD, V) k_build_seg<OT, BD, V><<<bgrid, bthreads, bsmem, c->stream>>>(BB_ARGS)
       const int bgrid = cdiv(g.nbin[0], tg) * g.nbin[1] * g.nbin[2];
       const int ot = c->ntypes == 1;
       if (special) {   // molecular systems under the stock loop: the multi-type kernel, narrow vectors (small systems)
         BB_LAUNCH(0, 2, 2);
       } else if (vw == 4) {
-        if (bonded) { if (ot) BB_LAUNCH(1, 1, 4); else BB_LAUNCH(0, 1, 4); }
+        if (bonded && unique_images) { if (ot) BB_LAUNCH(1, 3, 4); else BB_LAUNCH(0, 3, 4); }
+        else if (bonded) { if (ot) BB_LAUNCH(1, 1, 4); else BB_LAUNCH(0, 1, 4); }
         else { if (ot) BB_LAUNCH(1, 0, 4); else BB_LAUNCH(0, 0, 4); }
       } else {
-        if (bonded) { if (ot) BB_LAUNCH(1, 1, 2); else BB_LAUNCH(0, 1, 2); }
+        if (bonded && unique_images) { if (ot) BB_LAUNCH(1, 3, 2); else BB_LAUNCH(0, 3, 2); }
+        else if (bonded) { if (ot) BB_LAUNCH(1, 1, 2); else BB_LAUNCH(0, 1, 2); }
         else { if (ot) BB_LAUNCH(1, 0, 2); else BB_LAUNCH(0, 0, 2); }
       }
 #undef BB_LAUNCH
@@ -1031,14 +1078,16 @@ int neigh_build_lists(b200md_ctx *c)
       CU(cudaMemsetAsync(c->flags_d + 1, 0, sizeof(int), c->stream));
       continue;
     }
-    if (c->flags_h[1] > c->maxneigh) {  // "Neighbor list overflow": grow and redo instead of aborting
-      c->maxneigh = (c->flags_h[1] + c->flags_h[1] / 8 + 7) / 8 * 8;
+    // (k_build_seg appends a group of up to 4 entries without a per-entry clamp: its rows are right only while every
+    // list stays within maxneigh - 4)
+    if (c->flags_h[1] > c->maxneigh - 4) {  // "Neighbor list overflow": grow and redo instead of aborting
+      c->maxneigh = (c->flags_h[1] + c->flags_h[1] / 8 + 4 + 7) / 8 * 8;
       CU(cudaMemsetAsync(c->flags_d + 1, 0, sizeof(int), c->stream));
       continue;
     }
     break;
   }
-  if (c->flags_h[1] > c->maxneigh) return b200md_fail(c, B200MD_ERR_NEIGH_OVERFLOW, "Neighbor list overflow");
+  if (c->flags_h[1] > c->maxneigh - 4) return b200md_fail(c, B200MD_ERR_NEIGH_OVERFLOW, "Neighbor list overflow");
 
   ph.mark("build");
   if (c->dist_check) {

@@ -70,6 +70,10 @@ def test_emu_chain_setup(emu):
     chain.test_chain_setup_forces_vs_reference(emu)
 
 
+def test_emu_chain_bond_build_variants(emu):
+    chain.test_chain_bond_build_variants_agree(emu)
+
+
 def test_emu_chain_100_steps(emu):
     chain.test_chain_100_steps_vs_reference_and_shipped_log(emu)
 

@@ -82,6 +82,24 @@ def test_chain_setup_forces_vs_reference(pkg):
     md.close()
 
 
+def test_chain_bond_build_variants_agree(pkg):
+    """the list build resolves bond partners in two ways: where every periodic dimension is wider than two cutoffs a
+    partner's tag is unique inside the cutoff (the default here), otherwise the closest of several images wins.  On this
+    box both must leave the same lists, bond partners and forces, bit for bit."""
+    g = load_golden("chain_32k")
+    out = []
+    for general in (0, 1):
+        md = make_chain_device(pkg, g, langevin=False)
+        md.tune("build_bond_general", general)
+        md.run(12)
+        assert md.neigh_stats()["builds"] >= 2
+        a = md.gather()
+        out.append((a["x"], a["f"], md.neighbor_list()))
+        md.close()
+    assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][1], out[1][1])
+    assert np.array_equal(out[0][2][0], out[1][2][0]) and np.array_equal(out[0][2][1], out[1][2][1])
+
+
 def test_chain_100_steps_vs_reference_and_shipped_log(pkg):
     """the benchmark itself: 100 steps, thermo <= 1e-6 of the reference run here and of the shipped log
     (bench/log.6Oct16.chain.fixed.icc.1: T, E_pair/N, E_mol/N, TotEng/N, P at step 100; 25 neighbor builds)"""
