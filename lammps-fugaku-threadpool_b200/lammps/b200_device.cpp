@@ -51,8 +51,10 @@ void B200Device::release(LAMMPS *lmp)
   }
 }
 
-B200Device::B200Device(LAMMPS *lmp) : Pointers(lmp), ctx(nullptr), resident(0), resident_step(-1), refs(0)
+B200Device::B200Device(LAMMPS *lmp)
+    : Pointers(lmp), ctx(nullptr), resident(0), resident_step(-1), want_host_list(0), host_list_fresh(0), refs(0)
 {
+  if (const char *h = getenv("B200MD_HOST_LIST")) want_host_list = atoi(h) != 0;
   // one context per MPI rank; the NCCL id is minted on rank 0 and broadcast over `world`
   // (what replaces the MPI communicator of Comm on the device side, include/b200md.h)
   int me = comm->me, nprocs = comm->nprocs;

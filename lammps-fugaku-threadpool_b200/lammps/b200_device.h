@@ -23,6 +23,8 @@ class B200Device : protected Pointers {
   int device_id;      // CUDA device of this rank
   int resident;       // 1 while VerletB200::run owns the atoms on the device (pair/fix host hooks are idle)
   bigint resident_step;
+  int want_host_list;     // B200MD_HOST_LIST=1: the pair styles request a host NeighList, served by npair full/bin/atomonly/b200
+  int host_list_fresh;    // set by that NPair class when it rebuilt the device list on this step; compute() then does not
 
   // status -> error->one(FLERR, text), like GPU_EXTRA::check_flag
   void check(int status, const char *file, int line);
@@ -46,6 +48,7 @@ class B200PairTables {
  public:
   virtual ~B200PairTables() noexcept(false) {}
   virtual void device_tables(B200Device *) = 0;
+  virtual void device_tables_once(B200Device *) = 0;    // load them unless they are loaded
 };
 
 }    // namespace LAMMPS_NS

@@ -37,6 +37,7 @@ void PairEAMB200::init_style()
   array2spline();
   embedstep = -1;
   if (atom->molecular != Atom::ATOMIC) error->all(FLERR, "Pair style eam/b200 requires atom_style atomic");
+  if (dev->want_host_list) neighbor->add_request(this, NeighConst::REQ_FULL);    // see PairLJCutB200::init_style
   tables_loaded = 0;
   dev->announce("pair eam/b200");
 }
@@ -77,7 +78,8 @@ void PairEAMB200::compute(int eflag, int vflag)
     memory->create(numforce, nmax, "pair:numforce");
   }
   B200_CHECK(dev, b200md_host_atoms(dev->ctx, nlocal, nghost, &atom->x[0][0], atom->type, domain->sublo, domain->subhi,
-                                    neighbor->ago == 0));
+                                    neighbor->ago == 0 && !dev->host_list_fresh));
+  dev->host_list_fresh = 0;
   double e_embed = 0.0, e_pair = 0.0, v[6] = {0, 0, 0, 0, 0, 0};
   B200_CHECK(dev, b200md_host_eam_rho(dev->ctx, eflag_global, rho, fp, &e_embed));
   comm->forward_comm(this);    // ghost fp from their owners, on the host (pair_eam.cpp:251)

@@ -38,7 +38,10 @@ void PairLJCutB200::init_style()
   // special_bonds fene only (VerletB200::init checks)
   if (atom->molecular == Atom::TEMPLATE) error->all(FLERR, "Pair style lj/cut/b200 does not support atom_style template");
   cut_respa = nullptr;    // PairLJCut::init_style sets it (its constructor does not); init_one reads it
-  // no host NeighList is requested: Neighbor still runs decide/exchange/borders, the list lives on the device
+  // no host NeighList is requested: Neighbor still runs decide/exchange/borders, the list lives on the device.
+  // B200MD_HOST_LIST=1 (atomic systems): a full list is requested and npair full/bin/atomonly/b200 fills it from the
+  // device list at every rebuild, for lammps_neighlist_element_neighbors and other host-side readers
+  if (dev->want_host_list && atom->molecular == Atom::ATOMIC) neighbor->add_request(this, NeighConst::REQ_FULL);
   tables_loaded = 0;
   dev->announce("pair lj/cut/b200");
 }
@@ -67,7 +70,7 @@ void PairLJCutB200::compute(int eflag, int vflag)
 
   const int nlocal = atom->nlocal, nghost = atom->nghost;
   if (nlocal == 0) return;
-  if (neighbor->ago == 0) {
+  if (neighbor->ago == 0 && !dev->host_list_fresh) {
     // the special-bond lists as Neighbor would hand them to NPair::find_special (src/npair.h:125-158); tagint is int
     // (LAMMPS_SMALLBIG) and Atom's 2-d arrays are contiguous (Memory::create)
     if (atom->molecular == Atom::MOLECULAR && atom->maxspecial > 0)
@@ -77,7 +80,8 @@ void PairLJCutB200::compute(int eflag, int vflag)
       B200_CHECK(dev, b200md_host_special(dev->ctx, nlocal, nlocal + nghost, nullptr, 0, nullptr, nullptr, nullptr));
   }
   B200_CHECK(dev, b200md_host_atoms(dev->ctx, nlocal, nghost, &atom->x[0][0], atom->type, domain->sublo, domain->subhi,
-                                    neighbor->ago == 0));
+                                    neighbor->ago == 0 && !dev->host_list_fresh));
+  dev->host_list_fresh = 0;
   double e = 0.0, v[6] = {0, 0, 0, 0, 0, 0};
   B200_CHECK(dev, b200md_pair_compute(dev->ctx, eflag_global, vflag_global, &e, v));
   B200_CHECK(dev, b200md_host_forces(dev->ctx, &atom->f[0][0], 1));

@@ -23,6 +23,7 @@ class PairLJCutB200 : public PairLJCut, public B200PairTables {
   void init_style() override;
   double memory_usage() override;
   void device_tables(B200Device *) override;
+  void device_tables_once(B200Device *d) override { if (!tables_loaded) device_tables(d); }
 
  private:
   B200Device *dev;

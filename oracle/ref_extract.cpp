@@ -12,6 +12,9 @@
 // usage: ref_extract <out-prefix> <pair-style> <lammps command line args ...>
 //   e.g. ref_extract /tmp/lj lj/cut -in in.lj -var x 1 -log none -screen none
 #include "library.h"
+#ifdef B200_STYLES   // built a second time as oracle/_ref/b200_extract (tests/lammps_host/Makefile): the same reader with the
+#include "b200_register.h"   // b200 style classes registered, i.e. the list a library user sees under -sf b200
+#endif
 
 #include <cmath>
 #include <cstdint>
@@ -33,6 +36,9 @@ int main(int argc, char **argv)
   for (int i = 3; i < argc; i++) largs.push_back(argv[i]);
   void *lmp = lammps_open_no_mpi((int) largs.size(), largs.data(), nullptr);
   if (!lmp) return 2;
+#ifdef B200_STYLES
+  LAMMPS_NS::b200_register_styles((LAMMPS_NS::LAMMPS *) lmp);
+#endif
   // the library constructor only records "-in file"; main() is what normally runs it (src/main.cpp:77)
   for (int i = 3; i + 1 < argc; i++)
     if (std::string(argv[i]) == "-in" || std::string(argv[i]) == "-i") lammps_file(lmp, argv[i + 1]);

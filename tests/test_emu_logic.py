@@ -197,6 +197,11 @@ def test_emu_lammps_thermo_matches_reference(emu_lmp, kind, n, loop, tmp_path):
     lh.test_thermo_matches_reference(kind, n, loop, tmp_path)
 
 
+@pytest.mark.parametrize("kind,n,steps", [("lj", 6, 25), ("eam", 6, 12)])
+def test_emu_lammps_device_list_through_library_api(emu_lmp, kind, n, steps, tmp_path):
+    lh.check_device_list_through_library_api(tmp_path, kind, n, steps)
+
+
 @pytest.mark.parametrize("name,units", [("unittest_atomic_pair_eam", "metal"), ("unittest_atomic_pair_eam_real", "real")])
 def test_emu_lammps_unittest_eam_yaml(emu_lmp, name, units, tmp_path):
     """host-ghost mode on a box thinner than the cutoff (several periodic image layers made by LAMMPS), two

@@ -169,6 +169,75 @@ def test_thermo_matches_reference(kind, n, loop, tmp_path):
     np.testing.assert_allclose(G[0, 1:], R[0, 1:], rtol=1e-10, atol=1e-12)
 
 
+# ---- the device neighbor list as the reference's C library API exposes it (src/library.h:220-224) ----
+REF_EXTRACT = REFDIR / "ref_extract"
+B200_EXTRACT = REFDIR / "b200_extract"
+
+
+def read_extract(prefix):
+    """(.meta dict, undirected canonical (tag_lo, tag_hi, image code) rows, directed row count, forces by tag)"""
+    meta = {}
+    for line in Path(str(prefix) + ".meta").read_text().splitlines():
+        k, *v = line.split()
+        meta[k] = [float(t) for t in v]
+    n = int(meta["nlocal"][0])
+    raw = np.fromfile(str(prefix) + ".atoms.bin", dtype=np.uint8)
+    tag = raw[:4 * n].view(np.int32)
+    f = raw[8 * n + 48 * n:8 * n + 72 * n].view(np.float64).reshape(n, 3)
+    order = np.argsort(tag)
+    t = np.fromfile(str(prefix) + ".neigh.bin", dtype=np.int32).reshape(-1, 3)
+    ti, tj, code = t[:, 0].astype(np.int64), t[:, 1].astype(np.int64), t[:, 2] & 63
+    s = np.stack([(code >> (2 * d) & 3) - 1 for d in range(3)], axis=1)
+    # the pair seen from the other atom carries the opposite image shift
+    flip = (ti > tj) | ((ti == tj) & ((s[:, 0] < 0) | ((s[:, 0] == 0) & ((s[:, 1] < 0) | ((s[:, 1] == 0) & (s[:, 2] < 0))))))
+    lo, hi = np.where(flip, tj, ti), np.where(flip, ti, tj)
+    s = np.where(flip[:, None], -s, s)
+    key = ((lo * (1 << 31) + hi) * 64 + (s[:, 0] + 1) + 4 * (s[:, 1] + 1) + 16 * (s[:, 2] + 1))
+    return meta, key, len(t), f[order]
+
+
+def check_device_list_through_library_api(tmp_path, kind, n, steps):
+    """`b200_extract` is the oracle's list reader (oracle/ref_extract.cpp: lammps_find_pair_neighlist,
+    lammps_neighlist_num_elements, lammps_neighlist_element_neighbors) linked with the b200 style classes.  With
+    B200MD_HOST_LIST=1 the b200 pair style requests a full list and npair full/bin/atomonly/b200 fills it from the device
+    list: every undirected (tag, tag, image) pair of the reference's half list appears exactly twice, nothing else does,
+    and the forces computed from that device list equal the reference's."""
+    if not B200_EXTRACT.exists() or not REF_EXTRACT.exists():
+        pytest.skip("oracle/_ref host binaries not shipped")
+    text = (IN_LJ if kind == "lj" else IN_EAM).replace("run 100", f"run {steps}")
+    style = "lj/cut" if kind == "lj" else "eam"
+    (tmp_path / "in.ref").write_text(text.format(n=n, pot=POT, runstyle=""))
+    (tmp_path / "in.b200").write_text(text.format(n=n, pot=POT, runstyle=STOCK_LOOP))
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    ref = subprocess.run([str(REF_EXTRACT), str(tmp_path / "ref"), style, "-in", str(tmp_path / "in.ref"), "-log", "none"],
+                         cwd=tmp_path, env=env, capture_output=True, text=True)
+    assert ref.returncode == 0, ref.stdout[-2000:] + ref.stderr[-2000:]
+    got = subprocess.run([str(B200_EXTRACT), str(tmp_path / "b200"), style + "/b200", "-sf", "b200", "-in", str(tmp_path / "in.b200"),
+                          "-log", "none"], cwd=tmp_path, env=dict(env, B200MD_HOST_LIST="1"), capture_output=True, text=True)
+    assert got.returncode == 0, got.stdout[-3000:] + got.stderr[-2000:]
+    assert f"b200: pair {style}/b200 on CUDA device" in got.stdout, got.stdout[-2000:]
+    assert "b200: npair full/bin/atomonly/b200" in got.stdout, got.stdout[-2000:]
+    mr, kr, nr, fr = read_extract(tmp_path / "ref")
+    mg, kg, ng, fg = read_extract(tmp_path / "b200")
+    assert nr > 0 and ng == 2 * nr            # full list = both directions of the half list
+    ur, cr = np.unique(kr, return_counts=True)
+    ug, cg = np.unique(kg, return_counts=True)
+    assert np.all(cr == 1) and np.all(cg == 2)
+    assert np.array_equal(ur, ug)
+    assert np.abs(fg - fr).max() <= 1e-9 * np.abs(fr).max()
+    # without the switch no host list exists (the device needs none): the reader finds nothing to read
+    none = subprocess.run([str(B200_EXTRACT), str(tmp_path / "none"), style + "/b200", "-sf", "b200", "-in", str(tmp_path / "in.b200"),
+                           "-log", "none"], cwd=tmp_path, env=env, capture_output=True, text=True)
+    assert none.returncode == 0 and not (tmp_path / "none.neigh.bin").exists()
+    assert "npairs 0" in (tmp_path / "none.meta").read_text()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind,n,steps", [("lj", 8, 25), ("eam", 8, 12)])
+def test_device_list_through_library_api(kind, n, steps, tmp_path):
+    check_device_list_through_library_api(tmp_path, kind, n, steps)
+
+
 # ---- the reference's own known-answer test for pair eam, run through the reference hosting the b200 styles ----
 IN_UNITTEST_EAM = """atom_style atomic
 atom_modify map array
