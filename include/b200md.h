@@ -300,6 +300,9 @@ int b200md_build_bins_per_block(const b200md_ctx *ctx);
  *   "hs_min_chunk"   n    smallest system the pipeline splits into ranges (default 65536)
  *   "build_gb" n, "build_fp64" 0/1   test knobs of the list build (bins per block; force the all-FP64 fallback kernel)
  *   "build_bond_general" 0/1         test knob: bonded build with the closest-image choice even where a tag is unique
+ *   "build_threads"  128|256  threads per block of the list build (default 128, the faster one on B200)
+ *   "fuse_nve"       0/1  fix nve inside the force kernel on steps of b200md_run that neither tally nor end the call
+ *                         (default 1; 0 = the separate integrate kernels; results are bit-identical)
  * Unknown key: B200MD_ERR_ARG. */
 int b200md_tune(b200md_ctx *ctx, const char *key, int value);
 

@@ -19,56 +19,65 @@ __device__ __forceinline__ double warp_sum_b(double v)
   return v;
 }
 
+// all bonds of owned atom i (tag ti, position pi), both directions being stored: the force on i into (fxi, fyi, fzi);
+// with EVFLAG half of each bond's energy and virial into acc
+template <int EVFLAG>
+__device__ __forceinline__ void fene_atom(const double4 *__restrict__ pos, int i, const double4 pi, int ti, int maxb,
+                                          const int *__restrict__ bond_idx, const int *__restrict__ bond_type_by_tag,
+                                          const FeneParams &P, int *__restrict__ flags, double &fxi, double &fyi, double &fzi,
+                                          double (&acc)[7])
+{
+  const double CUBEROOT2 = 1.25992104989487316476;  // MY_CUBEROOT2 (src/math_const.h)
+  for (int m = 0; m < maxb; m++) {
+    const int j = bond_idx[(size_t) i * maxb + m];
+    if (j < 0) continue;  // no bond in this slot
+    const int type = bond_type_by_tag[(size_t) (ti - 1) * maxb + m];
+    const double4 pj = ld_pos256(pos + j);
+    const double delx = pi.x - pj.x, dely = pi.y - pj.y, delz = pi.z - pj.z;
+    const double rsq = delx * delx + dely * dely + delz * delz;
+    const double r0sq = P.r0[type] * P.r0[type];
+    double rlogarg = 1.0 - rsq / r0sq;
+    if (rlogarg < 0.1) {
+      if (rlogarg <= -3.0) flags[4] = 1;  // "Bad FENE bond" (bond_fene.cpp:88)
+      rlogarg = 0.1;
+    }
+    double fbond = -P.k[type] / rlogarg, sr6 = 0.0;
+    const double s2 = P.sigma[type] * P.sigma[type];
+    const bool lj = rsq < CUBEROOT2 * s2;
+    if (lj) {
+      const double sr2 = s2 / rsq;
+      sr6 = sr2 * sr2 * sr2;
+      fbond += 48.0 * P.epsilon[type] * sr6 * (sr6 - 0.5) / rsq;
+    }
+    fxi += delx * fbond;
+    fyi += dely * fbond;
+    fzi += delz * fbond;
+    if (EVFLAG) {
+      double ebond = -0.5 * P.k[type] * r0sq * log(rlogarg);
+      if (lj) ebond += 4.0 * P.epsilon[type] * sr6 * (sr6 - 1.0) + P.epsilon[type];
+      const double hf = 0.5 * fbond;  // each bond is visited from both of its atoms
+      acc[0] += 0.5 * ebond;
+      acc[1] += delx * delx * hf;
+      acc[2] += dely * dely * hf;
+      acc[3] += delz * delz * hf;
+      acc[4] += delx * dely * hf;
+      acc[5] += delx * delz * hf;
+      acc[6] += dely * delz * hf;
+    }
+  }
+}
+
 template <int EVFLAG>
 __global__ void __launch_bounds__(256)
 k_bond_fene(const double4 *__restrict__ pos, const int *__restrict__ tag, int nlocal, int maxb,
             const int *__restrict__ bond_idx, const int *__restrict__ bond_type_by_tag, FeneParams P, double *__restrict__ fx,
             double *__restrict__ fy, double *__restrict__ fz, double *__restrict__ partials, int *__restrict__ flags)
 {
-  const double CUBEROOT2 = 1.25992104989487316476;  // MY_CUBEROOT2 (src/math_const.h)
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
   if (i < nlocal) {
-    const double4 pi = pos[i];
-    const int ti = tag[i];
     double fxi = 0.0, fyi = 0.0, fzi = 0.0;
-    for (int m = 0; m < maxb; m++) {
-      const int j = bond_idx[(size_t) i * maxb + m];
-      if (j < 0) continue;  // no bond in this slot
-      const int type = bond_type_by_tag[(size_t) (ti - 1) * maxb + m];
-      const double4 pj = ld_pos256(pos + j);
-      const double delx = pi.x - pj.x, dely = pi.y - pj.y, delz = pi.z - pj.z;
-      const double rsq = delx * delx + dely * dely + delz * delz;
-      const double r0sq = P.r0[type] * P.r0[type];
-      double rlogarg = 1.0 - rsq / r0sq;
-      if (rlogarg < 0.1) {
-        if (rlogarg <= -3.0) flags[4] = 1;  // "Bad FENE bond" (bond_fene.cpp:88)
-        rlogarg = 0.1;
-      }
-      double fbond = -P.k[type] / rlogarg, sr6 = 0.0;
-      const double s2 = P.sigma[type] * P.sigma[type];
-      const bool lj = rsq < CUBEROOT2 * s2;
-      if (lj) {
-        const double sr2 = s2 / rsq;
-        sr6 = sr2 * sr2 * sr2;
-        fbond += 48.0 * P.epsilon[type] * sr6 * (sr6 - 0.5) / rsq;
-      }
-      fxi += delx * fbond;
-      fyi += dely * fbond;
-      fzi += delz * fbond;
-      if (EVFLAG) {
-        double ebond = -0.5 * P.k[type] * r0sq * log(rlogarg);
-        if (lj) ebond += 4.0 * P.epsilon[type] * sr6 * (sr6 - 1.0) + P.epsilon[type];
-        const double hf = 0.5 * fbond;  // each bond is visited from both of its atoms
-        acc[0] += 0.5 * ebond;
-        acc[1] += delx * delx * hf;
-        acc[2] += dely * dely * hf;
-        acc[3] += delz * delz * hf;
-        acc[4] += delx * dely * hf;
-        acc[5] += delx * delz * hf;
-        acc[6] += dely * delz * hf;
-      }
-    }
+    fene_atom<EVFLAG>(pos, i, pos[i], tag[i], maxb, bond_idx, bond_type_by_tag, P, flags, fxi, fyi, fzi, acc);
     fx[i] += fxi;
     fy[i] += fyi;
     fz[i] += fzi;
@@ -139,19 +148,51 @@ __host__ __device__ __forceinline__ void langevin_counter_uniforms(int seed, int
 }
 
 struct LangevinGamma { double g1[B200MD_MAXTYPES + 1], g2[B200MD_MAXTYPES + 1]; };
+// f += gamma1 * v + gamma2 * (u - 0.5) for one atom, u from the counter generator
+__device__ __forceinline__ void langevin_counter_kick(const LangevinGamma &G, int type, int seed, int tagi, int64_t step, double vx,
+                                                      double vy, double vz, double &fx, double &fy, double &fz)
+{
+  const double g1 = G.g1[type], g2 = G.g2[type];
+  double u[3];
+  langevin_counter_uniforms(seed, tagi, step, u);
+  fx = __dadd_rn(fx, __dadd_rn(__dmul_rn(g1, vx), __dmul_rn(g2, u[0] - 0.5)));
+  fy = __dadd_rn(fy, __dadd_rn(__dmul_rn(g1, vy), __dmul_rn(g2, u[1] - 0.5)));
+  fz = __dadd_rn(fz, __dadd_rn(__dmul_rn(g1, vz), __dmul_rn(g2, u[2] - 0.5)));
+}
 __global__ void k_langevin_counter(const double4 *__restrict__ pos, const int *__restrict__ tag, int nlocal, const double *__restrict__ vx,
                                    const double *__restrict__ vy, const double *__restrict__ vz, int seed, int64_t step, LangevinGamma G,
                                    double *__restrict__ fx, double *__restrict__ fy, double *__restrict__ fz)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nlocal) return;
-  const int type = pos_type(pos[i]);
-  const double g1 = G.g1[type], g2 = G.g2[type];
-  double u[3];
-  langevin_counter_uniforms(seed, tag[i], step, u);
-  fx[i] += g1 * vx[i] + g2 * (u[0] - 0.5);
-  fy[i] += g1 * vy[i] + g2 * (u[1] - 0.5);
-  fz[i] += g1 * vz[i] + g2 * (u[2] - 0.5);
+  double a = fx[i], b = fy[i], cz = fz[i];
+  langevin_counter_kick(G, pos_type(pos[i]), seed, tag[i], step, vx[i], vy[i], vz[i], a, b, cz);
+  fx[i] = a;
+  fy[i] = b;
+  fz[i] = cz;
+}
+
+// What follows the pair force on a step of in.chain that neither tallies nor ends the run, in ONE pass per atom instead
+// of three streaming kernels: the FENE bonds of atom i (k_bond_fene), the thermostat kick (k_langevin_counter; counter
+// mode only -- the replay mode draws on the host), FixNVE::final_integrate and the next step's initial_integrate
+// (k_nve_final_initial) -- the same operations in the same order, so the trajectory is bit-identical.  Bond partners are
+// gathered from the OLD positions; the new ones go to the second position buffer (NVEFuse, ctx.cuh).
+template <int LANGEVIN>
+__global__ void __launch_bounds__(256)
+k_chain_post(const double4 *__restrict__ pos, const int *__restrict__ tag, int nlocal, int maxb, const int *__restrict__ bond_idx,
+             const int *__restrict__ bond_type_by_tag, FeneParams P, const double *__restrict__ fx, const double *__restrict__ fy,
+             const double *__restrict__ fz, int *__restrict__ flags, int seed, int64_t step, LangevinGamma G, NVEFuse nve)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nlocal) return;
+  const double4 pi = pos[i];
+  const int ti = tag[i];
+  double acc[7];
+  double bx = 0.0, by = 0.0, bz = 0.0;
+  if (maxb > 0) fene_atom<0>(pos, i, pi, ti, maxb, bond_idx, bond_type_by_tag, P, flags, bx, by, bz, acc);
+  double a = fx[i] + bx, b = fy[i] + by, cz = fz[i] + bz;
+  if (LANGEVIN) langevin_counter_kick(G, pos_type(pi), seed, ti, step, nve.vx[i], nve.vy[i], nve.vz[i], a, b, cz);
+  nve_fused_update(nve, i, pi, a, b, cz);
 }
 
 int bond_compute(b200md_ctx *c, int ev)
@@ -220,6 +261,52 @@ double RanMarsHost::uniform()
 }
 
 // FixLangevin::post_force for timestep `ntimestep` of a run [beginstep, endstep] (compute_target, :773-787)
+// gfactor1 / gfactor2 of the step (FixLangevin::compute_target :773-787, init :284-298; ratio = 1), g2 times sqrt(T)
+static void langevin_gammas(const b200md_ctx *c, int64_t ntimestep, double *g1, double *g2)
+{
+  const LangevinState &L = c->langevin;
+  double delta = (double) (ntimestep - L.beginstep);
+  if (delta != 0.0) delta /= (double) (L.endstep - L.beginstep);
+  const double t_target = L.t_start + delta * (L.t_stop - L.t_start);
+  const double tsqrt = sqrt(t_target);
+  for (int t = 1; t <= c->ntypes; t++) {
+    double a = -c->mass_h[t] / L.t_period / c->ftm2v;
+    double b = sqrt(c->mass_h[t]) / c->ftm2v;
+    b *= sqrt(24.0 * c->boltz / L.t_period / L.dt / c->mvv2e);
+    a *= 1.0 / 1.0;
+    b *= 1.0 / sqrt(1.0);
+    g1[t] = a;
+    g2[t] = b * tsqrt;
+  }
+  g1[0] = g2[0] = 0.0;
+}
+
+// bonds + thermostat + fix nve of a step that neither tallies nor ends the run, fused (k_chain_post); false if this
+// system's extras cannot be fused (replay-mode thermostat)
+bool chain_post_usable(const b200md_ctx *c) { return !c->langevin.on || c->langevin.rng_mode == 1; }
+
+int chain_post_fused(b200md_ctx *c, int64_t ntimestep)
+{
+  NVEFuse nve = {};
+  if (!nve_fuse_args(c, nve)) return b200md_fail(c, B200MD_ERR_ARG, "chain_post_fused without a fused-integration request");
+  if (c->bonds.maxb && !c->bonds.idx_valid) return b200md_fail(c, B200MD_ERR_ARG, "bond partners were not resolved by the last neighbor build");
+  const int n = c->nlocal;
+  LangevinGamma G = {};
+  if (c->langevin.on) {
+    double g1[B200MD_MAXTYPES + 1], g2[B200MD_MAXTYPES + 1];
+    langevin_gammas(c, ntimestep, g1, g2);
+    for (int t = 0; t <= c->ntypes; t++) { G.g1[t] = g1[t]; G.g2[t] = g2[t]; }
+  }
+  KProf kp(c, KC_NVE);
+#define P_ARGS c->pos.p, c->tag.p, n, c->bonds.maxb, c->bonds.idx.p, c->bonds.type_by_tag.p, c->bonds.fene, c->f[0].p, c->f[1].p, c->f[2].p, c->flags_d, c->langevin.seed, ntimestep, G, nve
+  if (c->langevin.on) k_chain_post<1><<<cdiv(n, 256), 256, 0, c->stream>>>(P_ARGS);
+  else k_chain_post<0><<<cdiv(n, 256), 256, 0, c->stream>>>(P_ARGS);
+#undef P_ARGS
+  LAUNCH_CHECK();
+  c->fuse.done = true;
+  return B200MD_OK;
+}
+
 int langevin_apply(b200md_ctx *c, int64_t ntimestep)
 {
   LangevinState &L = c->langevin;
@@ -230,21 +317,8 @@ int langevin_apply(b200md_ctx *c, int64_t ntimestep)
       return b200md_fail(c, B200MD_ERR_ARG, "fix langevin replay mode supports one rank (RanMars(seed + me) per rank); use the counter mode (b200md_langevin_rng)");
     if ((int) L.order.size() != n) return b200md_fail(c, B200MD_ERR_ARG, "fix langevin: b200md_langevin_order must list every owned atom");
   }
-  double delta = (double) (ntimestep - L.beginstep);
-  if (delta != 0.0) delta /= (double) (L.endstep - L.beginstep);
-  const double t_target = L.t_start + delta * (L.t_stop - L.t_start);
-  const double tsqrt = sqrt(t_target);
   double g1[B200MD_MAXTYPES + 1], g2[B200MD_MAXTYPES + 1];
-  for (int t = 1; t <= c->ntypes; t++) {  // gfactor1/gfactor2 (:284-298), ratio = 1
-    double a = -c->mass_h[t] / L.t_period / c->ftm2v;
-    double b = sqrt(c->mass_h[t]) / c->ftm2v;
-    b *= sqrt(24.0 * c->boltz / L.t_period / L.dt / c->mvv2e);
-    a *= 1.0 / 1.0;
-    b *= 1.0 / sqrt(1.0);
-    g1[t] = a;
-    g2[t] = b * tsqrt;
-  }
-  g1[0] = g2[0] = 0.0;
+  langevin_gammas(c, ntimestep, g1, g2);
   if (L.rng_mode == 1) {
     LangevinGamma G;
     for (int t = 0; t <= B200MD_MAXTYPES; t++) { G.g1[t] = t <= c->ntypes ? g1[t] : 0.0; G.g2[t] = t <= c->ntypes ? g2[t] : 0.0; }

@@ -11,6 +11,8 @@
 #include "ctx.cuh"
 
 int nve_final_initial(b200md_ctx *c, double dtv, double dtf);
+bool chain_post_usable(const b200md_ctx *c);
+int chain_post_fused(b200md_ctx *c, int64_t ntimestep);
 int comm_init(b200md_ctx *c, const void *nccl_id);
 void comm_destroy(b200md_ctx *c);
 
@@ -746,7 +748,12 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
   NEED_CTX();
   if (!c->setup_done) TRY(b200md_setup(c));
   const double dtv = dt, dtf = 0.5 * dt * c->ftm2v;  // FixNVE::init (src/fix_nve.cpp:51-58)
+  struct FuseGuard {   // the fused-integration request never outlives this call, whatever path returns
+    b200md_ctx *c;
+    ~FuseGuard() { c->fuse.on = c->fuse.done = false; }
+  } fuse_guard{c};
   bool pending_final = false;                         // final_integrate of the previous step still to do
+  bool ahead = false;   // ... or already done, with this step's initial_integrate, by the previous step's force kernel
   const bool extras = c->bonds.maxb > 0 || c->langevin.on;  // in.chain: bond forces / fix langevin after the pair force
   if (c->langevin.on) {
     if (!c->langevin.bounds_set) {  // Run::command (src/run.cpp:172-176): this call is the whole run
@@ -761,16 +768,26 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
     const int ev = (istep == nsteps) || (thermo_every > 0 && c->ntimestep % thermo_every == 0);
     {
       Sect s(c, SECT_MODIFY);
-      if (pending_final) TRY(nve_final_initial(c, dtv, dtf));
+      if (ahead) {}
+      else if (pending_final) TRY(nve_final_initial(c, dtv, dtf));
       else TRY(nve_initial(c, dtv, dtf));
-      pending_final = false;
+      pending_final = ahead = false;
     }
     int nflag = 0;
     {
       Sect s(c, SECT_NEIGH);
       TRY(neigh_decide(c, &nflag));
     }
+    // a step that neither tallies nor ends the run leaves its final_integrate to the next step's fused kernel -- or,
+    // with fix nve alone, to the force kernel itself (INTEG in pair_lj.cu / pair_eam.cu), which writes the next
+    // positions into pos_tmp (free between rebuilds; same capacity as pos)
+    const bool fuse_step = c->fuse_nve && !ev && istep != nsteps;
+    c->fuse.on = fuse_step && !extras;
+    c->fuse.done = false;
+    c->fuse.dtv = dtv;
+    c->fuse.dtf = dtf;
     if (!nflag && !ev && overlap_usable(c)) {
+      if (c->fuse.on) TRY(dev_ensure(c, c->pos_tmp, c->pos.n, false, false));
       Sect s(c, SECT_PAIR);
       TRY(halo_and_force_overlapped(c));
     } else {
@@ -781,8 +798,26 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
         Sect s(c, SECT_NEIGH);
         TRY(neigh_rebuild(c));
       }
+      if (c->fuse.on) TRY(dev_ensure(c, c->pos_tmp, c->pos.n, false, false));
       Sect s(c, SECT_PAIR);
       TRY(force_compute(c, ev, ev));
+    }
+    c->fuse.on = false;
+    if (c->fuse.done) {   // v and the next positions are written: the owned part of pos_tmp becomes pos (ghosts follow
+      std::swap(c->pos, c->pos_tmp);   // by the next halo or rebuild)
+      c->fuse.done = false;
+      ahead = true;
+      continue;
+    }
+    if (extras && fuse_step && chain_post_usable(c)) {   // bonds + thermostat + fix nve in one pass per atom (bond.cu)
+      c->fuse.on = true;
+      TRY(dev_ensure(c, c->pos_tmp, c->pos.n, false, false));
+      TRY(chain_post_fused(c, c->ntimestep));
+      c->fuse.on = false;
+      std::swap(c->pos, c->pos_tmp);
+      c->fuse.done = false;
+      ahead = true;
+      continue;
     }
     if (extras) {  // Verlet::run: force->bond->compute, then modify->post_force (src/verlet.cpp:325-347)
       TRY(bond_compute(c, ev));
@@ -1199,6 +1234,7 @@ extern "C" int b200md_profile(b200md_ctx *c, int level)
 }
 
 // execution knobs, per context; defaults are the measured winners.  Unknown key: B200MD_ERR_ARG.
+//   "fuse_nve"      0/1  fix nve inside the force kernel on steps that neither tally nor end a run (default 1)
 //   "overlap"       0/1  halo exchange on its own stream under the force kernels of the ghost-free tiles
 //   "host_pipeline" 0/1  b200md_step_host as a three-stream chunk pipeline (0: serial copy - compute - copy)
 //   "hs_min_chunk"  n    smallest system the pipeline splits into ranges (tests lower it)
@@ -1208,7 +1244,8 @@ extern "C" int b200md_tune(b200md_ctx *c, const char *key, int value)
 {
   NEED_CTX();
   if (!key) return b200md_fail(c, B200MD_ERR_ARG, "b200md_tune: key == NULL");
-  if (!strcmp(key, "overlap")) c->overlap = value != 0;   // takes effect with the next list build (tile flags)
+  if (!strcmp(key, "fuse_nve")) c->fuse_nve = value != 0;
+  else if (!strcmp(key, "overlap")) c->overlap = value != 0;   // takes effect with the next list build (tile flags)
   else if (!strcmp(key, "host_pipeline")) c->host_pipeline = value != 0;
   else if (!strcmp(key, "hs_min_chunk")) c->hs_min_chunk = value > 0 ? value : 65536;
   else if (!strcmp(key, "build_gb")) c->build_gb_user = value > 0 ? value : 0;     // test knob

@@ -192,6 +192,10 @@ struct b200md_ctx {
   // overlap (default on several ranks, b200md_tune "overlap"): the per-step halo runs on s_comm while the main stream
   // computes the tiles whose lists hold no ghost; hstream != nullptr redirects the halo kernels and NCCL calls there
   int overlap = 0;
+  // fix nve fused into the force kernel (b200md_run, steps that neither tally nor end the run; pair_lj.cu): the request
+  // for the force evaluation under way, and whether the kernels honoured it (new positions then sit in pos_tmp)
+  struct { bool on = false, done = false; double dtv = 0.0, dtf = 0.0; } fuse;
+  int fuse_nve = 1;           // "fuse_nve" (b200md_tune)
   cudaStream_t s_comm = nullptr, hstream = nullptr;
   cudaEvent_t ev_main = nullptr, ev_halo = nullptr;
   HaloPlan hp;
@@ -299,6 +303,37 @@ template <class T> int dev_ensure(b200md_ctx *c, DevBuf<T> &b, size_t n, bool ke
   b.n = want;
   c->bytes_held += (double) want * sizeof(T);
   return B200MD_OK;
+}
+
+// fix nve fused into a force kernel (k_lj_force / k_eam_force_1t, INTEG): what the kernel needs beside its own arguments
+struct NVEFuse {
+  double *vx, *vy, *vz;
+  const double *mass;
+  double4 *pos_next;
+  double dtv, dtf;
+};
+// the fused integration wanted by b200md_run for the force evaluation under way, if any (capi.cu sets c->fuse; the
+// launchers that honour it set c->fuse.done)
+static inline bool nve_fuse_args(b200md_ctx *c, NVEFuse &a)
+{
+  if (!c->fuse.on) return false;
+  a = {c->v[0].p, c->v[1].p, c->v[2].p, c->mass_d.p, c->pos_tmp.p, c->fuse.dtv, c->fuse.dtf};
+  return true;
+}
+// the epilogue itself: FixNVE::final_integrate of this step + initial_integrate of the next for atom i holding force
+// (fx, fy, fz); operations and order of k_nve_final_initial (nve.cu).  p0 = the atom's position record {x, y, z, type}
+__device__ __forceinline__ void nve_fused_update(const NVEFuse &nve, int i, const double4 p0, double fx, double fy, double fz)
+{
+  const double dtfm = nve.dtf / nve.mass[__double2loint(p0.w)];
+  const double gx = __dmul_rn(dtfm, fx), gy = __dmul_rn(dtfm, fy), gz = __dmul_rn(dtfm, fz);
+  const double a = __dadd_rn(__dadd_rn(nve.vx[i], gx), gx);
+  const double b = __dadd_rn(__dadd_rn(nve.vy[i], gy), gy);
+  const double cz = __dadd_rn(__dadd_rn(nve.vz[i], gz), gz);
+  nve.vx[i] = a;
+  nve.vy[i] = b;
+  nve.vz[i] = cz;
+  nve.pos_next[i] = make_double4(__dadd_rn(p0.x, __dmul_rn(nve.dtv, a)), __dadd_rn(p0.y, __dmul_rn(nve.dtv, b)),
+                                 __dadd_rn(p0.z, __dmul_rn(nve.dtv, cz)), p0.w);
 }
 
 template <class T> void dev_free(b200md_ctx *c, DevBuf<T> &b)

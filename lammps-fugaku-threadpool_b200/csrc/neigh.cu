@@ -494,6 +494,7 @@ k_build_seg(const double4 *__restrict__ pos, RecArrays rec, int nlocal, BinGeom 
   __shared__ double s_cut[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
   __shared__ float s_cutf[(B200MD_MAXTYPES + 1) * (B200MD_MAXTYPES + 1)];
   __shared__ int s_row[10];                       // staged offset of each row (+ the total)
+  __shared__ int s_g0[9], s_len[9];               // global padded start and length (records) of each row
   __shared__ unsigned long long s_bar;            // mbarrier of the bulk copies (8-byte aligned by its type)
   const int nt1 = ntypes + 1;
   for (int k = threadIdx.x; k < nt1 * nt1; k += blockDim.x) { s_cut[k] = cutneighsq[k]; s_cutf[k] = (float) cutneighsq[k]; }
@@ -519,7 +520,9 @@ k_build_seg(const double4 *__restrict__ pos, RecArrays rec, int nlocal, BinGeom 
     int off = 0;
     for (int r = 0; r < 9; r++) {
       s_row[r] = off;
-      off += s_po[r * W + gx + 2] - s_po[r * W];
+      s_g0[r] = s_po[r * W];
+      s_len[r] = s_po[r * W + gx + 2] - s_po[r * W];
+      off += s_len[r];
     }
     s_row[9] = off;
   }
@@ -536,7 +539,7 @@ k_build_seg(const double4 *__restrict__ pos, RecArrays rec, int nlocal, BinGeom 
   if (bulk && threadIdx.x == 0) {
     mbar_expect_tx(&s_bar, (unsigned) total * (unsigned) (NF * 4));
     for (int r = 0; r < 9; r++) {
-      const int gs = s_po[r * W], len = s_po[r * W + gx + 2] - gs, so = s_row[r];
+      const int gs = s_g0[r], len = s_len[r], so = s_row[r];
       if (len == 0) continue;
       bulk_g2s(s_rec + (size_t) so * NF, rec.rec + (size_t) gs * NF, (unsigned) len * (unsigned) (NF * 4), &s_bar);
     }
@@ -545,17 +548,16 @@ k_build_seg(const double4 *__restrict__ pos, RecArrays rec, int nlocal, BinGeom 
   if (!bulk) {   // groups of 40 bytes (VW = 2 with tags): 8-byte units
 #pragma unroll 1
     for (int r = 0; r < 9; r++) {
-      const int gs = s_po[r * W], len = s_po[r * W + gx + 2] - gs, so = s_row[r];
+      const int gs = s_g0[r], len = s_len[r], so = s_row[r];
       const float2 *src = reinterpret_cast<const float2 *>(rec.rec + (size_t) gs * NF);
       float2 *dst = reinterpret_cast<float2 *>(s_rec + (size_t) so * NF);
       for (int k = threadIdx.x; k < len * NF / 2; k += blockDim.x) dst[k] = __ldg(src + k);
     }
   }
-  __syncthreads();   // the copies are issued (or done): s_po's global starts are no longer needed as such
-  // global padded starts -> staged offsets, one thread per row (the row's first entry is read before it is rewritten)
-  for (int r = threadIdx.x; r < 9; r += blockDim.x) {
-    const int g0 = s_po[r * W], so = s_row[r];
-    for (int q = nq - 1; q >= 0; q--) s_po[r * W + q] = so + s_po[r * W + q] - g0;
+  // global padded starts -> staged offsets (every element on its own: the row's start was saved in s_g0)
+  for (int idx = threadIdx.x; idx < 9 * nq; idx += blockDim.x) {
+    const int r = idx / nq, q = idx - r * nq;
+    s_po[r * W + q] += s_row[r] - s_g0[r];
   }
 #ifndef B200MD_CUDAEMU
   if (bulk) mbar_wait(&s_bar, 0);
@@ -573,8 +575,14 @@ k_build_seg(const double4 *__restrict__ pos, RecArrays rec, int nlocal, BinGeom 
   // the segment's own records (centre row, bins 1..gx); owned atoms come first in every bin's records (cell_list is
   // index-ordered within a bin, ghosts have index >= nlocal)
   for (int slot = own_s + threadIdx.x; slot < own_e; slot += blockDim.x) {
-    int bl = 0;   // my bin inside the segment, from my position in cell_list (exact; a float coordinate is not)
-    while (slot >= s_bs[4 * W + bl + 2]) bl++;
+    // my bin inside the segment, from my position in cell_list (exact; a float coordinate is not): the last bl in
+    // [0, gx) with s_bs[4W + bl + 1] <= slot (bin starts ascend; empty bins repeat a start)
+    int bl = 0;
+    for (int hi = gx - 1; bl < hi;) {
+      const int mid = (bl + hi + 1) >> 1;
+      if (s_bs[4 * W + mid + 1] <= slot) bl = mid;
+      else hi = mid - 1;
+    }
     const int mine = s_po[4 * W + bl + 1] + slot - s_bs[4 * W + bl + 1];
     const int myjt = s_reci[word(mine, 3)];
     const int i = myjt & BR_JMASK;

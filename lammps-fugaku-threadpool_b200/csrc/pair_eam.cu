@@ -311,11 +311,13 @@ k_eam_rho_fp_1t(const double4 *__restrict__ pos, const int *__restrict__ numneig
 
 // numneigh / neigh here are the IN-RANGE lists the rho pass of the same step left (numneigh_in, neigh_in): a subsequence of
 // the full list in the same order, so the sums run over the same terms in the same order as over the full list
-template <int EVFLAG, int SPLIT>
+// INTEG: fix nve fused behind the force of atom i, see k_lj_force (pos = the position records {x, y, z, type})
+template <int EVFLAG, int SPLIT, int INTEG>
 __global__ void __launch_bounds__(EAM1T_THREADS, 2)
 k_eam_force_1t(const double4 *__restrict__ posfp, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
                int nlocal, EAMParams P, const double *__restrict__ tab1, double *__restrict__ fx, double *__restrict__ fy,
-               double *__restrict__ fz, double *__restrict__ partials, const int *__restrict__ tile_list, int part)
+               double *__restrict__ fz, double *__restrict__ partials, const int *__restrict__ tile_list, int part,
+               const double4 *__restrict__ pos, NVEFuse nve)
 {
   extern __shared__ double s_t[];  // [7][n1]: rhor c0..c2 (derivative), z2r c3..c6 (value; derivative derived)
   const int n1 = P.nr + 1;
@@ -381,9 +383,13 @@ k_eam_force_1t(const double4 *__restrict__ posfp, const int *__restrict__ numnei
         }
       }
     }
-    fx[i] = fxi;
-    fy[i] = fyi;
-    fz[i] = fzi;
+    if (INTEG) {
+      nve_fused_update(nve, i, pos[i], fxi, fyi, fzi);
+    } else {
+      fx[i] = fxi;
+      fy[i] = fyi;
+      fz[i] = fzi;
+    }
   }
   if (EVFLAG) block_partials_e<7>(acc, partials);
 }
@@ -433,13 +439,15 @@ static int eam_attrs_1t(b200md_ctx *c)
 {
   static bool attr_done[64] = {};  // per device: a process may hold contexts on several GPUs
   if (!attr_done[c->device & 63]) {
-    CU(cudaFuncSetAttribute(k_eam_force_1t<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    CU(cudaFuncSetAttribute(k_eam_force_1t<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CU(cudaFuncSetAttribute(k_eam_force_1t<0, 0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CU(cudaFuncSetAttribute(k_eam_force_1t<1, 0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CU(cudaFuncSetAttribute(k_eam_force_1t<0, 0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CU(cudaFuncSetAttribute(k_eam_force_1t<0, 1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CU(cudaFuncSetAttribute(k_eam_rho_fp_1t<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CU(cudaFuncSetAttribute(k_eam_rho_fp_1t<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CU(cudaFuncSetAttribute(k_eam_rho_fp_1t<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    CU(cudaFuncSetAttribute(k_eam_force_1t<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    CU(cudaFuncSetAttribute(k_eam_force_1t<0, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CU(cudaFuncSetAttribute(k_eam_force_1t<0, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CU(cudaFuncSetAttribute(k_eam_force_1t<0, 2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     attr_done[c->device & 63] = true;
   }
   return B200MD_OK;
@@ -515,11 +523,16 @@ int pair_eam_force(b200md_ctx *c, int ev, bool ghost_from_fp)
       k_posfp_fill<<<cdiv(c->nghost, 256), 256, 0, c->stream>>>(c->pos.p, c->fp.p, c->posfp.p, n, c->nghost);
       LAUNCH_CHECK();
     }
+    NVEFuse nve = {};
+    const bool integ = !ev && nve_fuse_args(c, nve);
     {
       KProf kp(c, KC_PAIR);
-#define C1 c->posfp.p, c->numneigh_in.p, c->neigh_in.p, c->maxneigh, n, P, T.tab1, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, -1
-      if (ev) k_eam_force_1t<1, 0><<<blocks, threads, smemC, c->stream>>>(C1);
-      else k_eam_force_1t<0, 0><<<blocks, threads, smemC, c->stream>>>(C1);
+#define C1 c->posfp.p, c->numneigh_in.p, c->neigh_in.p, c->maxneigh, n, P, T.tab1, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, -1, c->pos.p, nve
+      if (ev) k_eam_force_1t<1, 0, 0><<<blocks, threads, smemC, c->stream>>>(C1);
+      else if (integ) {
+        k_eam_force_1t<0, 0, 1><<<blocks, threads, smemC, c->stream>>>(C1);
+        c->fuse.done = true;
+      } else k_eam_force_1t<0, 0, 0><<<blocks, threads, smemC, c->stream>>>(C1);
 #undef C1
       LAUNCH_CHECK();
     }
@@ -585,9 +598,15 @@ int pair_eam_force_part(b200md_ctx *c, int part)
   const int threads = part ? 128 : EAM1T_THREADS, blocks = cdiv(cnt * TILE, threads);
   const size_t n1 = (size_t) T.nr + 1, smemC = 7 * n1 * 8;
   TRY(eam_attrs_1t(c));
+  NVEFuse nve = {};
+  const bool integ = nve_fuse_args(c, nve);
   KProf kp(c, KC_PAIR);
-  k_eam_force_1t<0, 1><<<blocks, threads, smemC, c->stream>>>(c->posfp.p, c->numneigh_in.p, c->neigh_in.p, c->maxneigh, n, P, T.tab1, c->f[0].p,
-                                                               c->f[1].p, c->f[2].p, c->partials.p, list, cnt);
+#define C1 c->posfp.p, c->numneigh_in.p, c->neigh_in.p, c->maxneigh, n, P, T.tab1, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, list, cnt, c->pos.p, nve
+  if (integ) {
+    k_eam_force_1t<0, 1, 1><<<blocks, threads, smemC, c->stream>>>(C1);
+    c->fuse.done = true;
+  } else k_eam_force_1t<0, 1, 0><<<blocks, threads, smemC, c->stream>>>(C1);
+#undef C1
   LAUNCH_CHECK();
   return B200MD_OK;
 }
@@ -610,8 +629,8 @@ int pair_eam_force_range(b200md_ctx *c, int first, int count)
   const size_t n1 = (size_t) T.nr + 1, smemC = 7 * n1 * 8;
   TRY(eam_attrs_1t(c));
   KProf kp(c, KC_PAIR);
-  k_eam_force_1t<0, 2><<<blocks, threads, smemC, c->stream>>>(c->posfp.p, c->numneigh_in.p, c->neigh_in.p, c->maxneigh, first + count, P, T.tab1,
-                                                               c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, first);
+  k_eam_force_1t<0, 2, 0><<<blocks, threads, smemC, c->stream>>>(c->posfp.p, c->numneigh_in.p, c->neigh_in.p, c->maxneigh, first + count, P, T.tab1,
+                                                                  c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, first, c->pos.p, NVEFuse{});
   LAUNCH_CHECK();
   return B200MD_OK;
 }

@@ -48,12 +48,17 @@ template <int NC> __device__ __forceinline__ void block_partials(double (&acc)[N
 // SPLIT 1 (overlap mode): warp w works on the 32-atom tile tile_list[w], w < part -- the launch covers either the
 // ghost-free tiles (they run while the halo is still in flight) or the others, each as a compact list made at the
 // rebuild, so neither launch carries idle blocks.  SPLIT 2 (host-buffer pipeline): the atom range [part, nlocal).
-template <int EVFLAG, int ONETYPE, int SPLIT>
+// INTEG (steps that neither tally nor end a run, fix nve alone): the thread that holds f_i also does what follows it in
+// the timestep -- FixNVE::final_integrate of this step and initial_integrate of the next (src/fix_nve.cpp:64-141; the
+// operations and their order are k_nve_final_initial's, nve.cu) -- and writes the new position into the second
+// position buffer (other threads still gather the old ones).  f is not stored; the streaming pass over x, v, f of the
+// separate kernel (136 B per atom) is gone.  (NVEFuse, nve_fused_update: ctx.cuh)
+template <int EVFLAG, int ONETYPE, int SPLIT, int INTEG>
 __global__ void __launch_bounds__(128)
 k_lj_force(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
            int nlocal, LJOne one, const double *__restrict__ tables, int ntypes, double *__restrict__ fx,
            double *__restrict__ fy, double *__restrict__ fz, double *__restrict__ partials,
-           const int *__restrict__ tile_list, int part)
+           const int *__restrict__ tile_list, int part, NVEFuse nve)
 {
   extern __shared__ double s_tab[];   // 6 tables of (ntypes+1)^2, then special_lj[4] ([0] = 1), when !ONETYPE
   const int nt1 = ntypes + 1, nt2 = nt1 * nt1;
@@ -134,9 +139,13 @@ k_lj_force(const double4 *__restrict__ pos, const int *__restrict__ numneigh, co
         }
       }
     }
-    fx[i] = fxi;
-    fy[i] = fyi;
-    fz[i] = fzi;
+    if (INTEG) {
+      nve_fused_update(nve, i, pi, fxi, fyi, fzi);
+    } else {
+      fx[i] = fxi;
+      fy[i] = fyi;
+      fz[i] = fzi;
+    }
   }
   if (EVFLAG) block_partials<7>(acc, partials);
 }
@@ -175,15 +184,21 @@ int pair_lj_compute(b200md_ctx *c, int eflag, int vflag)
   LJOne one = {c->lj.h_onetype[0], c->lj.h_onetype[1], c->lj.h_onetype[2], c->lj.h_onetype[3], c->lj.h_onetype[4], c->lj.h_onetype[5]};
   const int onetype = (c->lj.ntypes == 1) && !c->special.on;
   size_t smem = onetype ? 0 : ((size_t) 6 * (c->lj.ntypes + 1) * (c->lj.ntypes + 1) + 4) * sizeof(double);
+  NVEFuse nve = {};
+  const bool integ = !ev && nve_fuse_args(c, nve);
   {
     KProf kp(c, KC_PAIR);
-#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, -1
+#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, -1, nve
     if (ev) {
-      if (onetype) k_lj_force<1, 1, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
-      else k_lj_force<1, 0, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+      if (onetype) k_lj_force<1, 1, 0, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+      else k_lj_force<1, 0, 0, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+    } else if (integ) {
+      if (onetype) k_lj_force<0, 1, 0, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+      else k_lj_force<0, 0, 0, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+      c->fuse.done = true;
     } else {
-      if (onetype) k_lj_force<0, 1, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
-      else k_lj_force<0, 0, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+      if (onetype) k_lj_force<0, 1, 0, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+      else k_lj_force<0, 0, 0, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
     }
 #undef LJ_ARGS
     LAUNCH_CHECK();
@@ -203,10 +218,18 @@ int pair_lj_compute_part(b200md_ctx *c, int part)
   LJOne one = {c->lj.h_onetype[0], c->lj.h_onetype[1], c->lj.h_onetype[2], c->lj.h_onetype[3], c->lj.h_onetype[4], c->lj.h_onetype[5]};
   const int onetype = (c->lj.ntypes == 1) && !c->special.on;
   size_t smem = onetype ? 0 : ((size_t) 6 * (c->lj.ntypes + 1) * (c->lj.ntypes + 1) + 4) * sizeof(double);
+  NVEFuse nve = {};
+  const bool integ = nve_fuse_args(c, nve);
   KProf kp(c, KC_PAIR);
-#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, list, cnt
-  if (onetype) k_lj_force<0, 1, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
-  else k_lj_force<0, 0, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, list, cnt, nve
+  if (integ) {
+    if (onetype) k_lj_force<0, 1, 1, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+    else k_lj_force<0, 0, 1, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+    c->fuse.done = true;
+  } else {
+    if (onetype) k_lj_force<0, 1, 1, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+    else k_lj_force<0, 0, 1, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+  }
 #undef LJ_ARGS
   LAUNCH_CHECK();
   return B200MD_OK;
@@ -224,9 +247,9 @@ int pair_lj_compute_range(b200md_ctx *c, int first, int count)
   const int onetype = (c->lj.ntypes == 1) && !c->special.on;
   size_t smem = onetype ? 0 : ((size_t) 6 * (c->lj.ntypes + 1) * (c->lj.ntypes + 1) + 4) * sizeof(double);
   KProf kp(c, KC_PAIR);
-#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, first + count, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, first
-  if (onetype) k_lj_force<0, 1, 2><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
-  else k_lj_force<0, 0, 2><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, first + count, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, first, NVEFuse{}
+  if (onetype) k_lj_force<0, 1, 2, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+  else k_lj_force<0, 0, 2, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
 #undef LJ_ARGS
   LAUNCH_CHECK();
   return B200MD_OK;

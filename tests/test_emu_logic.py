@@ -74,6 +74,11 @@ def test_emu_chain_bond_build_variants(emu):
     chain.test_chain_bond_build_variants_agree(emu)
 
 
+@pytest.mark.parametrize("thermostat", [False, True])
+def test_emu_chain_fused_post_force(emu, thermostat):
+    chain.test_chain_fused_post_force_equals_separate_kernels(emu, thermostat)
+
+
 def test_emu_chain_100_steps(emu):
     chain.test_chain_100_steps_vs_reference_and_shipped_log(emu)
 
@@ -139,6 +144,12 @@ def test_emu_dilute_gas_and_special_bonds_direct_sums(emu, ntypes):
     gp.test_dilute_gas_vs_direct_sum(emu, ntypes)
     if ntypes == 1:
         gp.test_host_ghost_special_bonds_vs_direct_sum(emu)
+
+
+@pytest.mark.parametrize("name,steps", [("lj_500", 45), ("eam_500", 30)])
+@pytest.mark.parametrize("overlap", [0, 1])
+def test_emu_fused_nve_equals_separate_kernels(emu, name, steps, overlap):
+    gp.test_fused_nve_equals_separate_kernels(emu, name, steps, overlap)
 
 
 def test_emu_piecewise_api_and_error_paths(emu):

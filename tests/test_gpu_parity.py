@@ -274,6 +274,27 @@ def test_overlapped_halo_equals_plain(pkg, name, steps):
     b.close()
 
 
+@pytest.mark.parametrize("name,steps", [("lj_500", 45), ("eam_500", 30)])
+@pytest.mark.parametrize("overlap", [0, 1])
+def test_fused_nve_equals_separate_kernels(pkg, name, steps, overlap):
+    """fix nve inside the force kernel (steps that neither tally nor end the run; the default) == the separate
+    integrate kernels, bit for bit, through rebuilds, with a thermo step in the middle and in overlap mode too: the
+    same operations in the same order, only the kernel they run in and the position double buffer differ."""
+    g = load_golden(name)
+    out = []
+    for fuse in (0, 1):
+        md = make_device_system(pkg, name, g)
+        md.tune("fuse_nve", fuse)
+        md.tune("overlap", overlap)
+        md.run(steps, thermo_every=20)
+        md.run(7)   # a second call: starts from the state the first one left (no integration pending across calls)
+        out.append((md.gather(), [t["pe"] for t in md.thermo_log], md.neigh_stats()))
+        md.close()
+    (ga, ea, sa), (gb, eb, sb) = out
+    assert sa == sb and sa["builds"] >= 2 and ea == eb
+    assert np.array_equal(ga["x"], gb["x"]) and np.array_equal(ga["v"], gb["v"]) and np.array_equal(ga["f"], gb["f"])
+
+
 def test_run_to_run_bitwise_reproducible(pkg):
     g = load_golden("eam_500")
     out = []

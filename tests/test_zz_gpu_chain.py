@@ -100,6 +100,29 @@ def test_chain_bond_build_variants_agree(pkg):
     assert np.array_equal(out[0][2][0], out[1][2][0]) and np.array_equal(out[0][2][1], out[1][2][1])
 
 
+@pytest.mark.parametrize("thermostat", [False, True])
+def test_chain_fused_post_force_equals_separate_kernels(pkg, thermostat):
+    """on steps that neither tally nor end the run the FENE bonds, the (counter-mode) thermostat kick and fix nve run as
+    ONE pass per atom writing the next positions into the second position buffer (the default); with "fuse_nve" 0 they
+    are the separate kernels.  Same operations in the same order: bit-identical state, through rebuilds, with a thermo
+    step in the middle and across two run calls."""
+    g = load_golden("chain_32k")
+    out = []
+    for fuse in (0, 1):
+        md = make_chain_device(pkg, g, langevin=False)
+        if thermostat:
+            md.fix("langevin", 1.0, 1.0, 10.0, 904297, rng="counter")
+        md.tune("fuse_nve", fuse)
+        md.run(14, thermo_every=5)
+        md.run(5)
+        a = md.gather()
+        out.append((a["x"], a["v"], a["f"], [t["pe"] for t in md.thermo_log], md.neigh_stats()))
+        md.close()
+    assert out[0][4] == out[1][4] and out[0][4]["builds"] >= 2 and out[0][3] == out[1][3]
+    for k in range(3):
+        assert np.array_equal(out[0][k], out[1][k])
+
+
 def test_chain_100_steps_vs_reference_and_shipped_log(pkg):
     """the benchmark itself: 100 steps, thermo <= 1e-6 of the reference run here and of the shipped log
     (bench/log.6Oct16.chain.fixed.icc.1: T, E_pair/N, E_mol/N, TotEng/N, P at step 100; 25 neighbor builds)"""
