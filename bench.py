@@ -41,6 +41,7 @@ BYTES_EAM_RHO = 28 + 4 * NBAR_EAM + 8 + 16  # pass A + B fused: x_i,type + ids +
 BYTES_EAM_FORCE = 28 + 8 + 4 * NBAR_EAM + 24
 BYTES_NEIGH_CHAIN = 28 + 4 * 4.87 + 4      # neighbor build of in.chain (4.87 stored half-list neighbors per bead), per build
 BYTES_CHAIN_PAIR = 52 + 4 * 4.87            # its lj/cut 1.12 force kernel
+BYTES_NVE = 192.0                           # fix nve, SURVEY section 8d (initial + final integrate: x rw, v rw twice, f r twice)
 BYTES_LJ_STEP = 394.0                       # pair 202 + nve 192 (no rebuild)
 BYTES_EAM_STEP = 606.0
 
@@ -752,14 +753,26 @@ def main():
         except Exception:
             dram = {}
 
-        def roof(w, cls, bytes_per_atom, dram_key=None):
+        def roof(w, cls, bytes_per_atom, dram_key=None, fused_nve=False):
             kms, kc = w["kernel_ms"][cls]
             if kc == 0 or kms <= 0.0:
                 return None
             avg_ms = kms / kc
+            rows = None
+            if fused_nve:
+                # fix nve runs INSIDE this kernel on the steps that neither tally nor end the run (INTEG variants): those
+                # launches do two of SURVEY section 8d's rows.  Separate integrate launches seen in the timed steps: one
+                # initial_integrate at the start plus one per unfused step.
+                nve_launches = w["kernel_ms"]["nve"][1]
+                fused = min(1.0, max(0.0, 1.0 - (nve_launches - 1) / max(args.steps, 1)))
+                rows = {"pair_row_bytes_per_atom": bytes_per_atom, "nve_row_bytes_per_atom": BYTES_NVE, "fused_share_of_steps": fused,
+                        "frac_pair_row_only": bytes_per_atom * w["atoms_per_gpu"] / (avg_ms * 1e-3) / 1e9 / peak}
+                bytes_per_atom = bytes_per_atom + BYTES_NVE * fused
             ach = bytes_per_atom * w["atoms_per_gpu"] / (avg_ms * 1e-3) / 1e9
             r = {"bound": "hbm", "kernel": cls, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
                  "avg_launch_ms": avg_ms, "launches": kc, "algorithmic_bytes_per_atom": bytes_per_atom, "peak_source": peak_src}
+            if rows:
+                r["rows"] = rows
             if dram_key in dram:
                 r["traffic"] = dram[dram_key]["bytes_per_atom"] * w["atoms_per_gpu"]
                 r["traffic_source"] = (f"ncu dram__bytes_read+write = {dram[dram_key]['bytes_per_atom']} B/atom on "
@@ -771,7 +784,7 @@ def main():
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": workload_config(args.cells, world),
                 "working_set_gb": lj["mem_gb"], "clocks": lj["clocks"], "gpu_launches": lj["launches"],
-                "roofline": roof(lj, "pair", BYTES_LJ_PAIR, "pair_lj"),
+                "roofline": roof(lj, "pair", BYTES_LJ_PAIR, "pair_lj", fused_nve=True),
                 "step_roofline": {"algorithmic_bytes_per_atom_step": BYTES_LJ_STEP,
                                   "frac_of_hbm_peak": BYTES_LJ_STEP * lj["atoms_per_gpu"] / (lj["ms"] / args.steps * 1e-3) / 1e9 / peak},
                 "kernel_ms": lj["kernel_ms"], "ms_profiled_pass": lj["ms_profiled_pass"],
@@ -785,7 +798,7 @@ def main():
         if eam is not None:
             line["eam"] = {"value": eam["value"], "unit": "Matom-steps/s", "ms_per_step": eam["ms"] / args.steps,
                            "workload": f"EAM Cu {eam['atoms_per_gpu']} atoms per GPU ({eam['natoms']} total; bench/in.eam scaled)",
-                           "roofline": roof(eam, "pair", BYTES_EAM_FORCE, "pair_eam"), "roofline_rho": roof(eam, "eam_rho", BYTES_EAM_RHO, "eam_rho"),
+                           "roofline": roof(eam, "pair", BYTES_EAM_FORCE, "pair_eam", fused_nve=True), "roofline_rho": roof(eam, "eam_rho", BYTES_EAM_RHO, "eam_rho"),
                            "step_frac_of_hbm_peak": BYTES_EAM_STEP * eam["atoms_per_gpu"] / (eam["ms"] / args.steps * 1e-3) / 1e9 / peak,
                            "kernel_ms": eam["kernel_ms"], "gpu_launches": eam["launches"], "clocks": eam["clocks"],
                            "thermo": {"step0": eam["thermo0"], "last": eam["thermo1"]}, "neigh": eam["neigh"], "e2e": eam.get("e2e"),
