@@ -750,7 +750,7 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
   const double dtv = dt, dtf = 0.5 * dt * c->ftm2v;  // FixNVE::init (src/fix_nve.cpp:51-58)
   struct FuseGuard {   // the fused-integration request never outlives this call, whatever path returns
     b200md_ctx *c;
-    ~FuseGuard() { c->fuse.on = c->fuse.done = false; }
+    ~FuseGuard() { c->fuse.on = c->fuse.done = c->fuse.check = c->check_ahead = false; }
   } fuse_guard{c};
   bool pending_final = false;                         // final_integrate of the previous step still to do
   bool ahead = false;   // ... or already done, with this step's initial_integrate, by the previous step's force kernel
@@ -786,6 +786,11 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
     c->fuse.done = false;
     c->fuse.dtv = dtv;
     c->fuse.dtf = dtf;
+    {   // will the next step's Neighbor::decide look at the distances (ago is 0 after a rebuild on this step)?
+      const int ago_next = (nflag ? 0 : c->ago) + 1;
+      c->fuse.check = fuse_step && c->dist_check && ago_next >= c->delay && ago_next % c->every == 0;
+      if (c->fuse.check) CU(cudaMemsetAsync(c->flags_d + 2, 0, sizeof(int), c->stream));
+    }
     if (!nflag && !ev && overlap_usable(c)) {
       if (c->fuse.on) TRY(dev_ensure(c, c->pos_tmp, c->pos.n, false, false));
       Sect s(c, SECT_PAIR);
@@ -805,6 +810,7 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
     c->fuse.on = false;
     if (c->fuse.done) {   // v and the next positions are written: the owned part of pos_tmp becomes pos (ghosts follow
       std::swap(c->pos, c->pos_tmp);   // by the next halo or rebuild)
+      c->check_ahead = c->fuse.check;
       c->fuse.done = false;
       ahead = true;
       continue;
@@ -815,6 +821,7 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
       TRY(chain_post_fused(c, c->ntimestep));
       c->fuse.on = false;
       std::swap(c->pos, c->pos_tmp);
+      c->check_ahead = c->fuse.check;
       c->fuse.done = false;
       ahead = true;
       continue;

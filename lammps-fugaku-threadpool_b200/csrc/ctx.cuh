@@ -194,7 +194,10 @@ struct b200md_ctx {
   int overlap = 0;
   // fix nve fused into the force kernel (b200md_run, steps that neither tally nor end the run; pair_lj.cu): the request
   // for the force evaluation under way, and whether the kernels honoured it (new positions then sit in pos_tmp)
-  struct { bool on = false, done = false; double dtv = 0.0, dtf = 0.0; } fuse;
+  // check: the fused epilogue also runs Neighbor::check_distance for the next step (which will decide with it);
+  // check_ahead: flags_d[2] already holds that verdict for the step now starting
+  struct { bool on = false, done = false, check = false; double dtv = 0.0, dtf = 0.0; } fuse;
+  bool check_ahead = false;
   int fuse_nve = 1;           // "fuse_nve" (b200md_tune)
   cudaStream_t s_comm = nullptr, hstream = nullptr;
   cudaEvent_t ev_main = nullptr, ev_halo = nullptr;
@@ -311,13 +314,25 @@ struct NVEFuse {
   const double *mass;
   double4 *pos_next;
   double dtv, dtf;
+  // Neighbor::check_distance of the NEXT step, done on the positions just made (nullptr: that step does not check)
+  const double4 *xhold;
+  double triggersq;
+  int *moved_flag;
 };
+// has the atom moved more than half the skin since the last build?  (Neighbor::check_distance, src/neighbor.cpp:2322-2374)
+__device__ __forceinline__ bool moved_beyond_trigger(const double4 a, const double4 b, double triggersq)
+{
+  const double dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z;
+  const double rsq = dx * dx + dy * dy + dz * dz;
+  return rsq > triggersq;
+}
 // the fused integration wanted by b200md_run for the force evaluation under way, if any (capi.cu sets c->fuse; the
 // launchers that honour it set c->fuse.done)
 static inline bool nve_fuse_args(b200md_ctx *c, NVEFuse &a)
 {
   if (!c->fuse.on) return false;
-  a = {c->v[0].p, c->v[1].p, c->v[2].p, c->mass_d.p, c->pos_tmp.p, c->fuse.dtv, c->fuse.dtf};
+  a = {c->v[0].p, c->v[1].p, c->v[2].p, c->mass_d.p, c->pos_tmp.p, c->fuse.dtv, c->fuse.dtf,
+       c->fuse.check ? c->xhold.p : nullptr, c->triggersq, c->flags_d + 2};
   return true;
 }
 // the epilogue itself: FixNVE::final_integrate of this step + initial_integrate of the next for atom i holding force
@@ -332,8 +347,10 @@ __device__ __forceinline__ void nve_fused_update(const NVEFuse &nve, int i, cons
   nve.vx[i] = a;
   nve.vy[i] = b;
   nve.vz[i] = cz;
-  nve.pos_next[i] = make_double4(__dadd_rn(p0.x, __dmul_rn(nve.dtv, a)), __dadd_rn(p0.y, __dmul_rn(nve.dtv, b)),
-                                 __dadd_rn(p0.z, __dmul_rn(nve.dtv, cz)), p0.w);
+  const double4 pn = make_double4(__dadd_rn(p0.x, __dmul_rn(nve.dtv, a)), __dadd_rn(p0.y, __dmul_rn(nve.dtv, b)),
+                                  __dadd_rn(p0.z, __dmul_rn(nve.dtv, cz)), p0.w);
+  nve.pos_next[i] = pn;
+  if (nve.xhold && moved_beyond_trigger(pn, nve.xhold[i], nve.triggersq)) *nve.moved_flag = 1;
 }
 
 template <class T> void dev_free(b200md_ctx *c, DevBuf<T> &b)

@@ -607,7 +607,7 @@ k_build_seg(const double4 *__restrict__ pos, RecArrays rec, int nlocal, BinGeom 
       }
     }
     if (BONDED == 3) {
-      const int ti = bb.tag[i];
+      const int ti = s_reci[word(mine, 4)];   // my own tag, from my staged record
       ptag0 = bb.partner_by_tag[(size_t) (ti - 1) * bb.maxb];
       ptag1 = bb.maxb > 1 ? bb.partner_by_tag[(size_t) (ti - 1) * bb.maxb + 1] : 0;
     }
@@ -812,17 +812,18 @@ __global__ void k_check_distance(const double4 *__restrict__ pos, const double4 
 {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  double4 a = pos[i], b = xhold[i];
-  double dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z;
-  double rsq = dx * dx + dy * dy + dz * dz;
-  if (rsq > triggersq) flags[2] = 1;
+  if (moved_beyond_trigger(pos[i], xhold[i], triggersq)) flags[2] = 1;
 }
 
 int neigh_check_distance(b200md_ctx *c, int *moved)
 {
-  CU(cudaMemsetAsync(c->flags_d + 2, 0, sizeof(int), c->stream));
-  k_check_distance<<<cdiv(c->nlocal, 256), 256, 0, c->stream>>>(c->pos.p, c->xhold.p, c->nlocal, c->triggersq, c->flags_d);
-  LAUNCH_CHECK();
+  if (c->check_ahead) {   // the previous step's fused integration already compared these positions with xhold
+    c->check_ahead = false;
+  } else {
+    CU(cudaMemsetAsync(c->flags_d + 2, 0, sizeof(int), c->stream));
+    k_check_distance<<<cdiv(c->nlocal, 256), 256, 0, c->stream>>>(c->pos.p, c->xhold.p, c->nlocal, c->triggersq, c->flags_d);
+    LAUNCH_CHECK();
+  }
   TRY(comm_allreduce_max_int(c, c->flags_d + 2, 1));  // the MPI_Allreduce of Neighbor::check_distance (src/neighbor.cpp:2371)
   CU(cudaMemcpyAsync(c->flags_h + 2, c->flags_d + 2, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
