@@ -11,60 +11,13 @@
 // lies within the neighbor cutoff (FENE: r < R0), is dropped from the pair list there (special_bonds lj weight 0) and
 // recorded in bond_idx instead.
 #include "ctx.cuh"
+#include "bond_dev.cuh"
 
 __device__ __forceinline__ double warp_sum_b(double v)
 {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
   return v;
-}
-
-// all bonds of owned atom i (tag ti, position pi), both directions being stored: the force on i into (fxi, fyi, fzi);
-// with EVFLAG half of each bond's energy and virial into acc
-template <int EVFLAG>
-__device__ __forceinline__ void fene_atom(const double4 *__restrict__ pos, int i, const double4 pi, int ti, int maxb,
-                                          const int *__restrict__ bond_idx, const int *__restrict__ bond_type_by_tag,
-                                          const FeneParams &P, int *__restrict__ flags, double &fxi, double &fyi, double &fzi,
-                                          double (&acc)[7])
-{
-  const double CUBEROOT2 = 1.25992104989487316476;  // MY_CUBEROOT2 (src/math_const.h)
-  for (int m = 0; m < maxb; m++) {
-    const int j = bond_idx[(size_t) i * maxb + m];
-    if (j < 0) continue;  // no bond in this slot
-    const int type = bond_type_by_tag[(size_t) (ti - 1) * maxb + m];
-    const double4 pj = ld_pos256(pos + j);
-    const double delx = pi.x - pj.x, dely = pi.y - pj.y, delz = pi.z - pj.z;
-    const double rsq = delx * delx + dely * dely + delz * delz;
-    const double r0sq = P.r0[type] * P.r0[type];
-    double rlogarg = 1.0 - rsq / r0sq;
-    if (rlogarg < 0.1) {
-      if (rlogarg <= -3.0) flags[4] = 1;  // "Bad FENE bond" (bond_fene.cpp:88)
-      rlogarg = 0.1;
-    }
-    double fbond = -P.k[type] / rlogarg, sr6 = 0.0;
-    const double s2 = P.sigma[type] * P.sigma[type];
-    const bool lj = rsq < CUBEROOT2 * s2;
-    if (lj) {
-      const double sr2 = s2 / rsq;
-      sr6 = sr2 * sr2 * sr2;
-      fbond += 48.0 * P.epsilon[type] * sr6 * (sr6 - 0.5) / rsq;
-    }
-    fxi += delx * fbond;
-    fyi += dely * fbond;
-    fzi += delz * fbond;
-    if (EVFLAG) {
-      double ebond = -0.5 * P.k[type] * r0sq * log(rlogarg);
-      if (lj) ebond += 4.0 * P.epsilon[type] * sr6 * (sr6 - 1.0) + P.epsilon[type];
-      const double hf = 0.5 * fbond;  // each bond is visited from both of its atoms
-      acc[0] += 0.5 * ebond;
-      acc[1] += delx * delx * hf;
-      acc[2] += dely * dely * hf;
-      acc[3] += delz * delz * hf;
-      acc[4] += delx * dely * hf;
-      acc[5] += delx * delz * hf;
-      acc[6] += dely * delz * hf;
-    }
-  }
 }
 
 template <int EVFLAG>
@@ -118,47 +71,7 @@ __global__ void k_langevin(const double4 *__restrict__ pos, const int *__restric
   fz[i] = __dadd_rn(fz[i], __dadd_rn(fdrag2, fran2));
 }
 
-// ---- counter-based mode: Philox4x32-10 (Salmon et al., SC'11) keyed by the fix's seed, counter = (tag, timestep) ----
-// The three numbers of an atom depend on nothing but (seed, tag, step): independent of the rank count, of the atom
-// order and of how a run is split into calls; no host work and no copy per step.  Statistically equivalent to the
-// reference's thermostat, not stream-compatible with it (that is what the replay mode above is for).
-__host__ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1,
-                                                       uint32_t out[4])
-{
-#pragma unroll
-  for (int r = 0; r < 10; r++) {
-    const uint64_t p0 = (uint64_t) 0xD2511F53u * c0, p1 = (uint64_t) 0xCD9E8D57u * c2;
-    const uint32_t n0 = (uint32_t) (p1 >> 32) ^ c1 ^ k0, n1 = (uint32_t) p1, n2 = (uint32_t) (p0 >> 32) ^ c3 ^ k1, n3 = (uint32_t) p0;
-    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
-    k0 += 0x9E3779B9u;
-    k1 += 0xBB67AE85u;
-  }
-  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
-}
-// uniform in (0,1) with 32 random bits, symmetric about 1/2 (so u - 0.5 has exactly zero mean over the 2^32 values)
-__host__ __device__ __forceinline__ double u01_32(uint32_t x) { return ((double) x + 0.5) * 2.3283064365386963e-10; }
-__host__ __device__ __forceinline__ void langevin_counter_uniforms(int seed, int tag, int64_t step, double u[3])
-{
-  uint32_t r[4];
-  philox4x32_10((uint32_t) tag, (uint32_t) (uint64_t) step, (uint32_t) ((uint64_t) step >> 32), 0x4c616e67u /* "Lang" */, (uint32_t) seed,
-                0x62323030u /* "b200" */, r);
-  u[0] = u01_32(r[0]);
-  u[1] = u01_32(r[1]);
-  u[2] = u01_32(r[2]);
-}
-
-struct LangevinGamma { double g1[B200MD_MAXTYPES + 1], g2[B200MD_MAXTYPES + 1]; };
-// f += gamma1 * v + gamma2 * (u - 0.5) for one atom, u from the counter generator
-__device__ __forceinline__ void langevin_counter_kick(const LangevinGamma &G, int type, int seed, int tagi, int64_t step, double vx,
-                                                      double vy, double vz, double &fx, double &fy, double &fz)
-{
-  const double g1 = G.g1[type], g2 = G.g2[type];
-  double u[3];
-  langevin_counter_uniforms(seed, tagi, step, u);
-  fx = __dadd_rn(fx, __dadd_rn(__dmul_rn(g1, vx), __dmul_rn(g2, u[0] - 0.5)));
-  fy = __dadd_rn(fy, __dadd_rn(__dmul_rn(g1, vy), __dmul_rn(g2, u[1] - 0.5)));
-  fz = __dadd_rn(fz, __dadd_rn(__dmul_rn(g1, vz), __dmul_rn(g2, u[2] - 0.5)));
-}
+// ---- counter-based mode: Philox4x32-10 keyed by the fix's seed, counter = (tag, timestep): bond_dev.cuh ----
 __global__ void k_langevin_counter(const double4 *__restrict__ pos, const int *__restrict__ tag, int nlocal, const double *__restrict__ vx,
                                    const double *__restrict__ vy, const double *__restrict__ vz, int seed, int64_t step, LangevinGamma G,
                                    double *__restrict__ fx, double *__restrict__ fy, double *__restrict__ fz)
@@ -177,22 +90,13 @@ __global__ void k_langevin_counter(const double4 *__restrict__ pos, const int *_
 // mode only -- the replay mode draws on the host), FixNVE::final_integrate and the next step's initial_integrate
 // (k_nve_final_initial) -- the same operations in the same order, so the trajectory is bit-identical.  Bond partners are
 // gathered from the OLD positions; the new ones go to the second position buffer (NVEFuse, ctx.cuh).
-template <int LANGEVIN>
 __global__ void __launch_bounds__(256)
-k_chain_post(const double4 *__restrict__ pos, const int *__restrict__ tag, int nlocal, int maxb, const int *__restrict__ bond_idx,
-             const int *__restrict__ bond_type_by_tag, FeneParams P, const double *__restrict__ fx, const double *__restrict__ fy,
-             const double *__restrict__ fz, int *__restrict__ flags, int seed, int64_t step, LangevinGamma G, NVEFuse nve)
+k_chain_post(const double4 *__restrict__ pos, int nlocal, const double *__restrict__ fx, const double *__restrict__ fy,
+             const double *__restrict__ fz, ChainPost cp, NVEFuse nve)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nlocal) return;
-  const double4 pi = pos[i];
-  const int ti = tag[i];
-  double acc[7];
-  double bx = 0.0, by = 0.0, bz = 0.0;
-  if (maxb > 0) fene_atom<0>(pos, i, pi, ti, maxb, bond_idx, bond_type_by_tag, P, flags, bx, by, bz, acc);
-  double a = fx[i] + bx, b = fy[i] + by, cz = fz[i] + bz;
-  if (LANGEVIN) langevin_counter_kick(G, pos_type(pi), seed, ti, step, nve.vx[i], nve.vy[i], nve.vz[i], a, b, cz);
-  nve_fused_update(nve, i, pi, a, b, cz);
+  chain_post_atom(cp, nve, pos, i, pos[i], fx[i], fy[i], fz[i]);
 }
 
 int bond_compute(b200md_ctx *c, int ev)
@@ -285,23 +189,37 @@ static void langevin_gammas(const b200md_ctx *c, int64_t ntimestep, double *g1, 
 // system's extras cannot be fused (replay-mode thermostat)
 bool chain_post_usable(const b200md_ctx *c) { return !c->langevin.on || c->langevin.rng_mode == 1; }
 
+// the arguments of chain_post_atom for this step (bond tables, thermostat factors)
+int chain_post_args(b200md_ctx *c, int64_t ntimestep, ChainPost &cp)
+{
+  if (c->bonds.maxb && !c->bonds.idx_valid) return b200md_fail(c, B200MD_ERR_ARG, "bond partners were not resolved by the last neighbor build");
+  cp = {};
+  cp.tag = c->tag.p;
+  cp.maxb = c->bonds.maxb;
+  cp.bond_idx = c->bonds.idx.p;
+  cp.bond_type_by_tag = c->bonds.type_by_tag.p;
+  cp.P = c->bonds.fene;
+  cp.flags = c->flags_d;
+  cp.langevin = c->langevin.on ? 1 : 0;
+  cp.seed = c->langevin.seed;
+  cp.step = ntimestep;
+  if (c->langevin.on) {
+    double g1[B200MD_MAXTYPES + 1], g2[B200MD_MAXTYPES + 1];
+    langevin_gammas(c, ntimestep, g1, g2);
+    for (int t = 0; t <= c->ntypes; t++) { cp.G.g1[t] = g1[t]; cp.G.g2[t] = g2[t]; }
+  }
+  return B200MD_OK;
+}
+
 int chain_post_fused(b200md_ctx *c, int64_t ntimestep)
 {
   NVEFuse nve = {};
   if (!nve_fuse_args(c, nve)) return b200md_fail(c, B200MD_ERR_ARG, "chain_post_fused without a fused-integration request");
-  if (c->bonds.maxb && !c->bonds.idx_valid) return b200md_fail(c, B200MD_ERR_ARG, "bond partners were not resolved by the last neighbor build");
+  ChainPost cp;
+  TRY(chain_post_args(c, ntimestep, cp));
   const int n = c->nlocal;
-  LangevinGamma G = {};
-  if (c->langevin.on) {
-    double g1[B200MD_MAXTYPES + 1], g2[B200MD_MAXTYPES + 1];
-    langevin_gammas(c, ntimestep, g1, g2);
-    for (int t = 0; t <= c->ntypes; t++) { G.g1[t] = g1[t]; G.g2[t] = g2[t]; }
-  }
   KProf kp(c, KC_NVE);
-#define P_ARGS c->pos.p, c->tag.p, n, c->bonds.maxb, c->bonds.idx.p, c->bonds.type_by_tag.p, c->bonds.fene, c->f[0].p, c->f[1].p, c->f[2].p, c->flags_d, c->langevin.seed, ntimestep, G, nve
-  if (c->langevin.on) k_chain_post<1><<<cdiv(n, 256), 256, 0, c->stream>>>(P_ARGS);
-  else k_chain_post<0><<<cdiv(n, 256), 256, 0, c->stream>>>(P_ARGS);
-#undef P_ARGS
+  k_chain_post<<<cdiv(n, 256), 256, 0, c->stream>>>(c->pos.p, n, c->f[0].p, c->f[1].p, c->f[2].p, cp, nve);
   LAUNCH_CHECK();
   c->fuse.done = true;
   return B200MD_OK;

@@ -750,7 +750,7 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
   const double dtv = dt, dtf = 0.5 * dt * c->ftm2v;  // FixNVE::init (src/fix_nve.cpp:51-58)
   struct FuseGuard {   // the fused-integration request never outlives this call, whatever path returns
     b200md_ctx *c;
-    ~FuseGuard() { c->fuse.on = c->fuse.done = c->fuse.check = c->check_ahead = false; }
+    ~FuseGuard() { c->fuse.on = c->fuse.done = c->fuse.check = c->fuse.chain = c->check_ahead = false; }
   } fuse_guard{c};
   bool pending_final = false;                         // final_integrate of the previous step still to do
   bool ahead = false;   // ... or already done, with this step's initial_integrate, by the previous step's force kernel
@@ -782,7 +782,10 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
     // with fix nve alone, to the force kernel itself (INTEG in pair_lj.cu / pair_eam.cu), which writes the next
     // positions into pos_tmp (free between rebuilds; same capacity as pos)
     const bool fuse_step = c->fuse_nve && !ev && istep != nsteps;
-    c->fuse.on = fuse_step && !extras;
+    // (in.chain: the lj/cut kernel's epilogue also takes the bonds and the counter-mode thermostat; other pair styles
+    // with bonds leave them to k_chain_post below)
+    c->fuse.chain = extras && c->pair_style == 1 && chain_post_usable(c);
+    c->fuse.on = fuse_step && (!extras || c->fuse.chain);
     c->fuse.done = false;
     c->fuse.dtv = dtv;
     c->fuse.dtf = dtf;

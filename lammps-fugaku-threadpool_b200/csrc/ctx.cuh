@@ -196,7 +196,8 @@ struct b200md_ctx {
   // for the force evaluation under way, and whether the kernels honoured it (new positions then sit in pos_tmp)
   // check: the fused epilogue also runs Neighbor::check_distance for the next step (which will decide with it);
   // check_ahead: flags_d[2] already holds that verdict for the step now starting
-  struct { bool on = false, done = false, check = false; double dtv = 0.0, dtf = 0.0; } fuse;
+  // chain: the epilogue also runs the FENE bonds and the counter-mode thermostat of its atom (k_lj_force INTEG 2)
+  struct { bool on = false, done = false, check = false, chain = false; double dtv = 0.0, dtf = 0.0; } fuse;
   bool check_ahead = false;
   int fuse_nve = 1;           // "fuse_nve" (b200md_tune)
   cudaStream_t s_comm = nullptr, hstream = nullptr;

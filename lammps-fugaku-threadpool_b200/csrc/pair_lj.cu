@@ -4,6 +4,7 @@
 // Energy / virial (EVFLAG) follow Pair::ev_tally_full (src/pair.cpp:1115-1160): half of each pair term
 // per visit, reduced per block and then in a fixed order (reproducible run to run).
 #include "ctx.cuh"
+#include "bond_dev.cuh"
 
 struct LJOne { double cutsq, lj1, lj2, lj3, lj4, offset; };
 
@@ -58,7 +59,7 @@ __global__ void __launch_bounds__(128)
 k_lj_force(const double4 *__restrict__ pos, const int *__restrict__ numneigh, const int *__restrict__ neigh, int maxneigh,
            int nlocal, LJOne one, const double *__restrict__ tables, int ntypes, double *__restrict__ fx,
            double *__restrict__ fy, double *__restrict__ fz, double *__restrict__ partials,
-           const int *__restrict__ tile_list, int part, NVEFuse nve)
+           const int *__restrict__ tile_list, int part, NVEFuse nve, ChainPost cp)
 {
   extern __shared__ double s_tab[];   // 6 tables of (ntypes+1)^2, then special_lj[4] ([0] = 1), when !ONETYPE
   const int nt1 = ntypes + 1, nt2 = nt1 * nt1;
@@ -139,7 +140,9 @@ k_lj_force(const double4 *__restrict__ pos, const int *__restrict__ numneigh, co
         }
       }
     }
-    if (INTEG) {
+    if (INTEG == 2) {   // in.chain: bonds and thermostat kick of atom i, then fix nve, all on the force in registers
+      chain_post_atom(cp, nve, pos, i, pi, fxi, fyi, fzi);
+    } else if (INTEG) {
       nve_fused_update(nve, i, pi, fxi, fyi, fzi);
     } else {
       fx[i] = fxi;
@@ -185,13 +188,19 @@ int pair_lj_compute(b200md_ctx *c, int eflag, int vflag)
   const int onetype = (c->lj.ntypes == 1) && !c->special.on;
   size_t smem = onetype ? 0 : ((size_t) 6 * (c->lj.ntypes + 1) * (c->lj.ntypes + 1) + 4) * sizeof(double);
   NVEFuse nve = {};
+  ChainPost cp = {};
   const bool integ = !ev && nve_fuse_args(c, nve);
+  if (integ && c->fuse.chain) TRY(chain_post_args(c, c->ntimestep, cp));
   {
     KProf kp(c, KC_PAIR);
-#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, -1, nve
+#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, -1, nve, cp
     if (ev) {
       if (onetype) k_lj_force<1, 1, 0, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
       else k_lj_force<1, 0, 0, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+    } else if (integ && c->fuse.chain) {
+      if (onetype) k_lj_force<0, 1, 0, 2><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+      else k_lj_force<0, 0, 0, 2><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+      c->fuse.done = true;
     } else if (integ) {
       if (onetype) k_lj_force<0, 1, 0, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
       else k_lj_force<0, 0, 0, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
@@ -219,10 +228,16 @@ int pair_lj_compute_part(b200md_ctx *c, int part)
   const int onetype = (c->lj.ntypes == 1) && !c->special.on;
   size_t smem = onetype ? 0 : ((size_t) 6 * (c->lj.ntypes + 1) * (c->lj.ntypes + 1) + 4) * sizeof(double);
   NVEFuse nve = {};
+  ChainPost cp = {};
   const bool integ = nve_fuse_args(c, nve);
+  if (integ && c->fuse.chain) TRY(chain_post_args(c, c->ntimestep, cp));
   KProf kp(c, KC_PAIR);
-#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, list, cnt, nve
-  if (integ) {
+#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, n, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, list, cnt, nve, cp
+  if (integ && c->fuse.chain) {
+    if (onetype) k_lj_force<0, 1, 1, 2><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+    else k_lj_force<0, 0, 1, 2><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
+    c->fuse.done = true;
+  } else if (integ) {
     if (onetype) k_lj_force<0, 1, 1, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
     else k_lj_force<0, 0, 1, 1><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
     c->fuse.done = true;
@@ -247,7 +262,7 @@ int pair_lj_compute_range(b200md_ctx *c, int first, int count)
   const int onetype = (c->lj.ntypes == 1) && !c->special.on;
   size_t smem = onetype ? 0 : ((size_t) 6 * (c->lj.ntypes + 1) * (c->lj.ntypes + 1) + 4) * sizeof(double);
   KProf kp(c, KC_PAIR);
-#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, first + count, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, first, NVEFuse{}
+#define LJ_ARGS c->pos.p, c->numneigh.p, c->neigh.p, c->maxneigh, first + count, one, c->lj.d, c->lj.ntypes, c->f[0].p, c->f[1].p, c->f[2].p, c->partials.p, nullptr, first, NVEFuse{}, ChainPost{}
   if (onetype) k_lj_force<0, 1, 2, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
   else k_lj_force<0, 0, 2, 0><<<blocks, threads, smem, c->stream>>>(LJ_ARGS);
 #undef LJ_ARGS
