@@ -78,6 +78,14 @@ int b200md_nghost(const b200md_ctx *ctx);
 /* copy owned atoms back (device order; use `tag` to identify).  Any pointer may be NULL.
  * Mirrors atomKK->sync(Host, X_MASK|V_MASK|F_MASK|...) of the KOKKOS package. */
 int b200md_download_atoms(b200md_ctx *ctx, double *x, double *v, double *f, int *type, int *tag, int *image);
+/* the same copy-back in the CALLER's order: host_tag[n] are the tags of the caller's n = b200md_nlocal() atoms in its own
+ * order (Atom::tag), maxtag their maximum; row i of x / v / f / image receives the atom whose tag is host_tag[i] -- the
+ * permutation runs on the device, so the copies land straight in Atom::x / v / f / image (what VerletB200 does at every
+ * output step on one rank; the role of atomKK->sync(Host, ...) with the host's own atom order, src/KOKKOS/atom_kokkos.h).
+ * Needs reasonably dense tags (maxtag <= 4 n + 1024: a direct table), else B200MD_ERR_ARG and b200md_download_atoms
+ * serves; a tag the caller does not hold: B200MD_ERR_ARG.  Any output pointer may be NULL. */
+int b200md_download_atoms_by_tag(b200md_ctx *ctx, int n, const int *host_tag, int maxtag, double *x, double *v, double *f,
+                                 int *image);
 /* owned + ghost positions and tags (ghosts after owned), for neighbor-list parity checks */
 int b200md_download_all(b200md_ctx *ctx, double *x /*[nall][3]*/, int *tag /*[nall]*/);
 /* refresh positions/velocities of the resident owned atoms from host arrays given in TAG order

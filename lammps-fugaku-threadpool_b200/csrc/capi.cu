@@ -297,6 +297,87 @@ extern "C" int b200md_download_atoms(b200md_ctx *c, double *x, double *v, double
   return B200MD_OK;
 }
 
+// ---- owned atoms back in the CALLER's order: the permutation by tag done on the device ----------------------------
+__global__ void k_slot_fill(const int *__restrict__ host_tag, int n, int maxtag, int *__restrict__ slot, int *__restrict__ flags)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int t = host_tag[i];
+  if (t < 1 || t > maxtag) flags[3] = 1;
+  else slot[t] = i;
+}
+// device atom s goes to row slot[tag[s]] of the output: WHAT 0 = position, 1 = three SoA arrays, 2 = one int array
+template <int WHAT>
+__global__ void k_by_slot(const int *__restrict__ tag, const int *__restrict__ slot, int maxtag, int n, const double4 *__restrict__ pos,
+                          const double *__restrict__ a, const double *__restrict__ b, const double *__restrict__ cc,
+                          const int *__restrict__ ia, double *__restrict__ out3, int *__restrict__ outi, int *__restrict__ flags)
+{
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n) return;
+  const int t = tag[s];
+  const int i = (t >= 1 && t <= maxtag) ? slot[t] : -1;
+  if (i < 0) { flags[3] = 1; return; }   // a tag the caller does not hold
+  if (WHAT == 0) {
+    const double4 p = pos[s];
+    out3[3 * (size_t) i] = p.x; out3[3 * (size_t) i + 1] = p.y; out3[3 * (size_t) i + 2] = p.z;
+  } else if (WHAT == 1) {
+    out3[3 * (size_t) i] = a[s]; out3[3 * (size_t) i + 1] = b[s]; out3[3 * (size_t) i + 2] = cc[s];
+  } else {
+    outi[i] = ia[s];
+  }
+}
+
+extern "C" int b200md_download_atoms_by_tag(b200md_ctx *c, int n, const int *host_tag, int maxtag, double *x, double *v, double *f,
+                                            int *image)
+{
+  NEED_CTX();
+  if (n != c->nlocal || n <= 0) return b200md_fail(c, B200MD_ERR_ARG, "download_atoms_by_tag: the caller holds %d atoms, the device %d", n, c->nlocal);
+  if (!host_tag || maxtag < 1) return b200md_fail(c, B200MD_ERR_ARG, "download_atoms_by_tag: host_tag[n] and maxtag are required");
+  if ((int64_t) maxtag > 4 * (int64_t) n + 1024)
+    return b200md_fail(c, B200MD_ERR_ARG, "download_atoms_by_tag: tags too sparse for a direct table (maxtag %d for %d atoms); use b200md_download_atoms", maxtag, n);
+  // scratch: host tags [n] + slot table [maxtag + 1] (ints), then one 3 x n (or n) output at a time
+  const size_t ints = (size_t) n + (size_t) maxtag + 1;
+  const size_t head = (ints * 4 + 255) / 256 * 256;
+  TRY(stage_bytes(c, head + (size_t) n * 24));
+  int *d_htag = (int *) c->stage.p, *d_slot = d_htag + n;
+  double *out3 = (double *) ((char *) c->stage.p + head);
+  const int g = cdiv(n, 256);
+  CU(cudaMemsetAsync(c->flags_d + 3, 0, sizeof(int), c->stream));
+  CU(cudaMemcpyAsync(d_htag, host_tag, (size_t) n * 4, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemsetAsync(d_slot, 0xff, ((size_t) maxtag + 1) * 4, c->stream));
+  k_slot_fill<<<g, 256, 0, c->stream>>>(d_htag, n, maxtag, d_slot, c->flags_d);
+  LAUNCH_CHECK();
+#define BY_SLOT(W, OUT3, OUTI, A, B, CC, IA) k_by_slot<W><<<g, 256, 0, c->stream>>>(c->tag.p, d_slot, maxtag, n, c->pos.p, A, B, CC, IA, OUT3, OUTI, c->flags_d)
+  if (x) {
+    BY_SLOT(0, out3, nullptr, nullptr, nullptr, nullptr, nullptr);
+    LAUNCH_CHECK();
+    CU(cudaMemcpyAsync(x, out3, (size_t) n * 24, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+  }
+  if (v) {
+    BY_SLOT(1, out3, nullptr, c->v[0].p, c->v[1].p, c->v[2].p, nullptr);
+    LAUNCH_CHECK();
+    CU(cudaMemcpyAsync(v, out3, (size_t) n * 24, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+  }
+  if (f) {
+    BY_SLOT(1, out3, nullptr, c->f[0].p, c->f[1].p, c->f[2].p, nullptr);
+    LAUNCH_CHECK();
+    CU(cudaMemcpyAsync(f, out3, (size_t) n * 24, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+  }
+  if (image) {
+    BY_SLOT(2, nullptr, (int *) out3, nullptr, nullptr, nullptr, c->image.p);
+    LAUNCH_CHECK();
+    CU(cudaMemcpyAsync(image, out3, (size_t) n * 4, cudaMemcpyDeviceToHost, c->stream));
+  }
+#undef BY_SLOT
+  CU(cudaMemcpyAsync(c->flags_h + 3, c->flags_d + 3, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  if (c->flags_h[3]) return b200md_fail(c, B200MD_ERR_ARG, "download_atoms_by_tag: the caller's tags and the device's do not match (a tag outside 1..maxtag or unknown to the caller)");
+  return B200MD_OK;
+}
+
 extern "C" int b200md_download_all(b200md_ctx *c, double *x, int *tag)
 {
   NEED_CTX();

@@ -200,6 +200,18 @@ void VerletB200::setup(int flag)
 void VerletB200::download()
 {
   const int n = b200md_nlocal(dev->ctx);
+  if (comm->nprocs == 1 && n == atom->nlocal && n > 0) {
+    // one rank, reasonably dense tags (the usual 1..N): the device permutes into the host's own order and the copies
+    // land straight in Atom's arrays (Memory::create makes x, v, f contiguous n x 3 blocks; tagint and imageint are int
+    // under LAMMPS_SMALLBIG) -- no staging vectors, no scatter loop on the host
+    tagint maxtag = 0;
+    for (int i = 0; i < n; i++) maxtag = std::max(maxtag, atom->tag[i]);
+    if (maxtag > 0 && (bigint) maxtag <= 4 * (bigint) n + 1024) {
+      B200_CHECK(dev, b200md_download_atoms_by_tag(dev->ctx, n, atom->tag, (int) maxtag, &atom->x[0][0], &atom->v[0][0], &atom->f[0][0],
+                                                   atom->image));
+      return;
+    }
+  }
   std::vector<double> x((size_t) 3 * n), v((size_t) 3 * n), f((size_t) 3 * n);
   std::vector<int> type(n), tag(n), image(n);
   B200_CHECK(dev, b200md_download_atoms(dev->ctx, x.data(), v.data(), f.data(), type.data(), tag.data(), image.data()));

@@ -29,6 +29,7 @@ PROTOTYPES = {
     "b200md_nlocal": (_i, [_vp]),
     "b200md_nghost": (_i, [_vp]),
     "b200md_download_atoms": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "b200md_download_atoms_by_tag": (_i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp]),
     "b200md_download_all": (_i, [_vp, _vp, _vp]),
     "b200md_lj_init": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "b200md_eam_init": (_i, [_vp, _i, _i, _i, _d, _d, _d, _d, _i, _vp, _i, _vp, _i, _vp, _vp, _vp, _vp]),

@@ -459,6 +459,16 @@ class B200MD:
             x, v, f, t, tag, img = x[o], v[o], f[o], t[o], tag[o], img[o]
         return dict(x=x, v=v, f=f, type=t, tag=tag, image=img)
 
+    def gather_in_order(self, host_tag) -> dict:
+        """owned atoms in the order of the caller's tag array (b200md_download_atoms_by_tag: the permutation runs on
+        the device) -- what VerletB200 writes back into Atom::x / v / f / image"""
+        host_tag = np.ascontiguousarray(host_tag, dtype=np.int32)
+        n = len(host_tag)
+        x, v, f, img = np.empty((n, 3)), np.empty((n, 3)), np.empty((n, 3)), np.empty(n, dtype=np.int32)
+        self.ctx.call("b200md_download_atoms_by_tag", n, lib.ptr(host_tag), int(host_tag.max()), lib.ptr(x), lib.ptr(v), lib.ptr(f),
+                      lib.ptr(img))
+        return dict(x=x, v=v, f=f, tag=host_tag, image=img)
+
     def peratom(self, sort_by_tag: bool = True) -> dict:
         """compute pe/atom + compute stress/atom NULL pair: per-atom pair energy and virial (xx yy zz xy xz yz, energy
         units: stress/atom multiplies by -nktv2p) of the current configuration"""

@@ -153,6 +153,7 @@ def test_emu_fused_nve_equals_separate_kernels(emu, name, steps, overlap):
 
 
 def test_emu_piecewise_api_and_error_paths(emu):
+    gp.test_download_in_the_callers_order(emu)
     gp.test_piecewise_api_equals_device_loop(emu)
     gp.test_error_paths(emu)
     gp.test_run_to_run_bitwise_reproducible(emu)

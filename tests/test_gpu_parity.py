@@ -295,6 +295,35 @@ def test_fused_nve_equals_separate_kernels(pkg, name, steps, overlap):
     assert np.array_equal(ga["x"], gb["x"]) and np.array_equal(ga["v"], gb["v"]) and np.array_equal(ga["f"], gb["f"])
 
 
+def test_download_in_the_callers_order(pkg):
+    """b200md_download_atoms_by_tag (the permutation by tag on the device; what verlet/b200 writes back into Atom's
+    arrays) == b200md_download_atoms + the permutation on the host, for a shuffled caller order, after steps that
+    re-sorted the device atoms; tags the caller does not hold and sparse tags are refused"""
+    g = load_golden("lj_500")
+    md = make_device_system(pkg, "lj_500", g)
+    md.run(25)
+    a = md.gather(sort_by_tag=False)
+    rng = np.random.default_rng(5)
+    host_tag = rng.permutation(a["tag"]).astype(np.int32)
+    b = md.gather_in_order(host_tag)
+    where = np.empty(int(a["tag"].max()) + 1, dtype=np.int64)
+    where[a["tag"]] = np.arange(len(a["tag"]))
+    o = where[host_tag]
+    for k in ("x", "v", "f", "image"):
+        assert np.array_equal(b[k], a[k][o]), k
+    bad = host_tag.copy()
+    bad[3] = bad[4]            # a tag twice, so one device tag is unknown to the caller
+    with pytest.raises(pkg.lib.B200MDError) as e:
+        md.gather_in_order(bad)
+    assert "do not match" in str(e.value)
+    sparse = host_tag.copy()
+    sparse[0] = 10 * len(sparse) + 5000
+    with pytest.raises(pkg.lib.B200MDError) as e:
+        md.gather_in_order(sparse)
+    assert "sparse" in str(e.value)
+    md.close()
+
+
 def test_run_to_run_bitwise_reproducible(pkg):
     g = load_golden("eam_500")
     out = []
