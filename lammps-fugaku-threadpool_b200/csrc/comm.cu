@@ -286,12 +286,23 @@ __global__ void k_mask_fill(const double4 *__restrict__ pos, int n, MaskGeom mg,
                             signed char *__restrict__ send_dir)
 {
   __shared__ int wcnt[MASK_BLOCK / 32];
+  __shared__ int s_cnt[NBITS];   // this block's count per direction: most blocks (interior atoms) have none at all
+  __shared__ int s_any;
+  if (threadIdx.x == 0) s_any = 0;
+  __syncthreads();
+  if (threadIdx.x < NBITS) {
+    const int cn = blockcnt[threadIdx.x * nblk + blockIdx.x];
+    s_cnt[threadIdx.x] = cn;
+    if (cn) s_any = 1;
+  }
+  __syncthreads();
+  if (!s_any) return;   // block-uniform
   int i = blockIdx.x * MASK_BLOCK + threadIdx.x;
   unsigned m = 0;
   if (i < n) m = atom_mask<MODE>(mg, pos[i]);
   int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   for (int d = 0; d < NBITS; d++) {
-    if (blockcnt[d * nblk + blockIdx.x] == 0) continue;  // block-uniform
+    if (s_cnt[d] == 0) continue;  // block-uniform
     unsigned b = __ballot_sync(0xffffffffu, (m >> d) & 1u);
     if (lane == 0) wcnt[w] = __popc(b);
     __syncthreads();

@@ -5,7 +5,7 @@
 //                                                           k_bin_sortseg / k_permute_owned
 //   Comm::exchange / CommBrick::borders                  -> comm.cu (single-stage, 26 directions)
 //   NPair::build           (src/npair_half_bin_atomonly_newton.cpp:33-113, full-list semantics of
-//                           src/npair_full_bin_atomonly.cpp) -> k_build_full
+//                           src/npair_full_bin_atomonly.cpp) -> k_build_seg (k_build_fp64: the all-FP64 fallback)
 //   Neighbor::check_distance (src/neighbor.cpp:2322-2374) -> k_check_distance
 // This is a from-scratch design: bins are >= cutneighmax wide (27-bin stencil, 9 contiguous x-rows),
 // owned atoms are physically re-ordered by bin at every rebuild, ghosts are made in ONE stage from the
@@ -342,13 +342,13 @@ k_build_fp64(const double4 *__restrict__ pos, int nlocal, BinGeom g, const int *
 
 // ------------------------------------------------------------------------------------------------
 // neighbor build, the default: ONE THREAD PER OWNED ATOM over candidates staged in shared memory.
-//   * k_binrec_fill stages every binned atom (owned + ghost, in cell_list order) as a 16-byte record
-//     {float x, y, z relative to the bin-grid origin; j | (type-1) << 28}.
+//   * k_rec_fill writes every binned atom (owned + ghost, in cell_list order, bins padded to the vector width) as a
+//     record {float x, y, z relative to the bin-grid origin; j | (type-1) << 28 (; tag)}, in groups of VW records.
 //   * a block owns a SEGMENT of tg consecutive bins of one x-row (about 112 owned atoms).  Bins are >= the neighbor
 //     cutoff wide, so every candidate of its atoms lies in the 3 x 3 x (tg + 2) bins around it: 9 CONTIGUOUS record
-//     ranges, copied once into shared memory with coalesced 16-byte loads.
+//     ranges, brought into shared memory by 9 bulk copies (cp.async.bulk + mbarrier).
 //   * every thread then walks the 27 bins around ITS atom's bin (9 sub-ranges of the staged rows) with LDS.128 --
-//     the lanes of a warp sit in 2 or 3 bins, so a step reads 2 or 3 distinct addresses (broadcast) -- two candidates
+//     the lanes of a warp sit in 2 or 3 bins, so a step reads 2 or 3 distinct addresses -- VW candidates
 //     per iteration through the packed FP32 pipe (fadd2 / fmul2 / ffma2).  The decision is final when
 //     |rsq_f - cutneighsq| > tol, where tol rigorously bounds the FP32 error (derivation at build_tolerance()).  Inside
 //     the band (about 1 candidate in 10^4) the reference's own FP64 expression decides:
@@ -360,7 +360,8 @@ k_build_fp64(const double4 *__restrict__ pos, int nlocal, BinGeom g, const int *
 // Why this form (ncu, profiles/r02_ncu_build.md): the warp-per-bin kernel of round 1 (lanes = the 18.5 atoms of a bin,
 // candidates broadcast from global memory) was ISSUE-bound -- 81 % issue-slot utilisation, 757 warp instructions per
 // atom: 27 candidate steps per atom (500 candidates over 18.5 useful lanes) at 28 instructions each.  Here a lane
-// scans its own 500 candidates (15.6 steps per atom at 32 lanes) at about 14 instructions per candidate.
+// scans its own 500 candidates (15.6 steps per atom at 32 lanes) at 12 instructions per candidate (48 per group of 4;
+// profiles/r02_ncu_build_eam_v2.md: now the L1 data pipe, 67 %, is the busiest unit).
 // ------------------------------------------------------------------------------------------------
 #define BR_JMASK 0x0FFFFFFF
 #define SEG_FAR 1.0e18f   /* coordinate of a padding record: rsq = inf, never <= any cutoff */
