@@ -61,6 +61,8 @@ def parse_args():
     ap.add_argument("--parity-steps", type=int, default=0, help="steps of the full-size parity leg (default min(W+K, 50))")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--halo-put", action="store_true",
+                    help="N > 1: per-step halo as the fused pack-and-put kernel over peer memory instead of NCCL send/recv")
     return ap.parse_args()
 
 
@@ -242,8 +244,15 @@ def run_workload(torch, dist, pkg, kind, cells, args, device, nranks, rank, nccl
     md.box([0, 0, 0], box)
     md.create_atoms(x, v, np.ones(len(x), dtype=np.int32), tag, natoms_total=natoms_total)
     del x, v, tag
+    if nranks > 1 and getattr(args, "halo_put", False):
+        def allgather(blob):
+            got = [None] * nranks
+            dist.all_gather_object(got, blob)
+            return got
+        md.halo_put(max(1 << 20, md.nlocal // 4), allgather)   # landing buffers for up to a quarter of the owned atoms in ghosts
     md.setup()
     out = dict(natoms=natoms_total, atoms_per_gpu=md.nlocal, thermo0=md.thermo_log[-1])
+    out["halo"] = "pack-and-put over peer memory" if (nranks > 1 and getattr(args, "halo_put", False)) else ("nccl send/recv" if nranks > 1 else "self")
 
     # ---- parity leg (untimed, before the warm-up): thermo at step 0 and after P steps against the unmodified reference
     # on the SAME input at the SAME size (N = 1), or against closed forms of the perfect lattice (any N)
@@ -788,7 +797,7 @@ def main():
                 "step_roofline": {"algorithmic_bytes_per_atom_step": BYTES_LJ_STEP,
                                   "frac_of_hbm_peak": BYTES_LJ_STEP * lj["atoms_per_gpu"] / (lj["ms"] / args.steps * 1e-3) / 1e9 / peak},
                 "kernel_ms": lj["kernel_ms"], "ms_profiled_pass": lj["ms_profiled_pass"],
-                "thermo": {"step0": lj["thermo0"], "last": lj["thermo1"]}, "neigh": lj["neigh"], "nghost": lj["nghost"]}
+                "thermo": {"step0": lj["thermo0"], "last": lj["thermo1"]}, "neigh": lj["neigh"], "nghost": lj["nghost"], "halo": lj.get("halo")}
         line["e2e"] = lj.get("e2e")
         if parity:
             line["parity"] = parity.get("lj")

@@ -146,6 +146,19 @@ int b200md_neigh_stats(b200md_ctx *ctx, int64_t *nbuilds, int64_t *ndanger, int 
  * full, so the reference's reverse_comm of ghost forces (:598-639) has no device counterpart.
  * Comm::exchange and Comm::borders (:652-979) run inside b200md_neigh_build.  Collective. */
 int b200md_halo_forward(b200md_ctx *ctx);
+/* The per-step halo as ONE fused pack-and-put kernel over peer memory (NVLink P2P) instead of pack + ncclSend/ncclRecv
+ * (what src/KOKKOS/comm_kokkos.cpp:184-262 does with GPU-aware MPI, one step further: no send buffer, no library
+ * kernel).  Every rank of one box calls b200md_halo_put_export (allocates its landing buffer of 2 x cap_records ghost
+ * records and returns the B200MD_IPC_HANDLE_BYTES cudaIpc handle), the host all-gathers handles and capacities
+ * (MPI_Allgather / torch.distributed.all_gather), every rank calls b200md_halo_put_import with all of them, then
+ * b200md_tune(ctx, "halo_put", 1).  From the next list build on the position / {x,y,z,fp} halos of b200md_run use it
+ * whenever every rank's ghosts fit its landing buffer (agreed collectively at each rebuild; NCCL otherwise).  Ranks must
+ * be processes of one node with peer access between their GPUs.  Results are bit-identical to the NCCL halo. */
+#define B200MD_IPC_HANDLE_BYTES 64
+int b200md_halo_put_export(b200md_ctx *ctx, int64_t cap_records, void *handle_out);
+int b200md_halo_put_import(b200md_ctx *ctx, int nranks, const void *handles, const int64_t *caps);
+/* halos served by the put path so far (0: every halo went through NCCL) */
+int64_t b200md_halo_put_count(const b200md_ctx *ctx);
 /* CommBrick::setup (src/comm_brick.cpp:191-483) for the single-stage 26-direction scheme, host only (no
  * device needed): peer_send[d] = rank that receives what `rank` sends in direction d, peer_recv[d] = rank
  * whose direction-d messages `rank` receives; -1 = none (non-periodic face).  d = 0..25 enumerates
@@ -309,6 +322,8 @@ int b200md_build_bins_per_block(const b200md_ctx *ctx);
  *   "build_gb" n, "build_fp64" 0/1   test knobs of the list build (bins per block; force the all-FP64 fallback kernel)
  *   "build_bond_general" 0/1         test knob: bonded build with the closest-image choice even where a tag is unique
  *   "build_threads"  128|256  threads per block of the list build (default 128, the faster one on B200)
+ *   "halo_put"       0/1  per-step halo as a fused pack-and-put kernel over peer memory (after b200md_halo_put_import;
+ *                         default 0: NCCL send/recv)
  *   "fuse_nve"       0/1  fix nve inside the force kernel on steps of b200md_run that neither tally nor end the call
  *                         (default 1; 0 = the separate integrate kernels; results are bit-identical)
  * Unknown key: B200MD_ERR_ARG. */

@@ -1335,7 +1335,8 @@ extern "C" int b200md_tune(b200md_ctx *c, const char *key, int value)
 {
   NEED_CTX();
   if (!key) return b200md_fail(c, B200MD_ERR_ARG, "b200md_tune: key == NULL");
-  if (!strcmp(key, "fuse_nve")) c->fuse_nve = value != 0;
+  if (!strcmp(key, "halo_put")) c->put.enabled = value != 0;   // takes effect with the next list build
+  else if (!strcmp(key, "fuse_nve")) c->fuse_nve = value != 0;
   else if (!strcmp(key, "overlap")) c->overlap = value != 0;   // takes effect with the next list build (tile flags)
   else if (!strcmp(key, "host_pipeline")) c->host_pipeline = value != 0;
   else if (!strcmp(key, "hs_min_chunk")) c->hs_min_chunk = value > 0 ? value : 65536;

@@ -17,6 +17,7 @@
 #include <nccl.h>
 
 #include <utility>
+#include <vector>
 
 #include "ctx.cuh"
 
@@ -95,6 +96,13 @@ int comm_init(b200md_ctx *c, const void *nccl_id)
 
 void comm_destroy(b200md_ctx *c)
 {
+  for (int r = 0; r < 64; r++)
+    if (c->put.peer_base[r]) { cudaIpcCloseMemHandle(c->put.peer_base[r]); c->put.peer_base[r] = nullptr; }
+  if (c->put.base) cudaFree(c->put.base);
+  if (c->put.done_d) cudaFree(c->put.done_d);
+  c->put.base = nullptr;
+  c->put.done_d = nullptr;
+  c->put.imported = c->put.epoch_ok = false;
   if (c->nccl) g_nccl.CommDestroy((ncclComm_t) c->nccl);
   c->nccl = nullptr;
 }
@@ -430,6 +438,9 @@ static bool any_remote(const b200md_ctx *c)
   return false;
 }
 
+static int put_plan_epoch(b200md_ctx *c);
+int halo_put_check(b200md_ctx *c);
+
 // CommBrick::borders
 int comm_borders(b200md_ctx *c)
 {
@@ -480,6 +491,149 @@ int comm_borders(b200md_ctx *c)
     TRY(sendrecv_dirs(c, (const char *) c->sendbuf_i.p, c->hp.soff, c->sendcount, (char *) (c->tag.p + n), c->hp.goff,
                       c->recvcount, sizeof(int)));
   }
+  TRY(halo_put_check(c));
+  return put_plan_epoch(c);
+}
+
+// ------------------------------------------------------------------------------------------------
+// halo as ONE fused pack-and-put kernel over peer memory (NVLink P2P through cudaIpc mappings) instead of
+// pack -> send buffer -> 26 ncclSend/ncclRecv: CommBrick::forward_comm (src/comm_brick.cpp:538-591) without a staging
+// copy on the sender and without a communication kernel of a library.
+//   sender   k_halo_pack_put: record e of direction d goes straight to landing[parity][goff_peer[d] + e - soff[d]] in the
+//            receiver's memory; every block fences (system scope) and counts itself done; the last block to finish
+//            stores the halo's sequence number into the receiver's flag of every direction it served
+//   receiver k_halo_wait (one warp) spins on its own flags until every direction it expects carries this sequence number,
+//            then k_halo_unpack copies the landed records into the ghost slots
+// Two landing buffers alternate by halo parity: a rank can be at most one halo ahead of the peer that still reads the
+// other buffer (to put halo k+2 it needs halo k+1 from that peer, which the peer packs after unpacking halo k).
+// Rebuild-time exchanges (counts, borders with tags, migration) stay on NCCL; they also order the epochs.
+// ------------------------------------------------------------------------------------------------
+#define PUT_FLAG_BYTES 256
+struct PutPlan {
+  double4 *dst[NDIR];   // first landing record of direction d in the receiver's memory (nullptr: self or nothing to send)
+  int *flag[NDIR];      // the receiver's flag of direction d for this parity
+  unsigned seq;
+};
+
+__global__ void k_halo_pack_put(double4 *__restrict__ arr, const int *__restrict__ send_idx, const signed char *__restrict__ send_dir,
+                                int nsend, int nlocal, HaloPlan hp, PutPlan pp, int *__restrict__ done)
+{
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e < nsend) {
+    const int d = send_dir[e], s = send_idx[e];
+    double4 p = arr[s];
+    p.x += hp.shift[d][0];
+    p.y += hp.shift[d][1];
+    p.z += hp.shift[d][2];
+    if (hp.self[d]) arr[nlocal + hp.goff[d] + (e - hp.soff[d])] = p;
+    else pp.dst[d][e - hp.soff[d]] = p;
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int t = atomicAdd(done, 1);
+    if (t == (int) gridDim.x - 1) {   // every block's records are visible system-wide: raise the receivers' flags
+      *done = 0;
+      __threadfence_system();
+      for (int d = 0; d < NDIR; d++)
+        if (pp.flag[d]) *(volatile int *) pp.flag[d] = (int) pp.seq;
+      __threadfence_system();
+    }
+  }
+}
+
+// lane d waits for direction d; gives up after about two seconds of GPU time (a peer that died must not hang the box)
+__global__ void k_halo_wait(const int *__restrict__ flags, unsigned mask, unsigned seq, int *__restrict__ timed_out)
+{
+  const int d = threadIdx.x;
+  if (d < NDIR && ((mask >> d) & 1u)) {
+    const volatile int *f = flags + d;
+    const long long t0 = clock64();
+    while ((int) ((unsigned) *f - seq) < 0) {
+      if (clock64() - t0 > 4000000000LL) { *timed_out = 1; break; }
+    }
+  }
+  __threadfence_system();
+}
+
+__global__ void k_halo_unpack(double4 *__restrict__ arr, const double4 *__restrict__ landing, int nlocal, int nghost, HaloPlan hp,
+                              unsigned remote_mask)
+{
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= nghost) return;
+  int d = 0;
+  while (d < NDIR - 1 && g >= hp.goff[d + 1]) d++;
+  if ((remote_mask >> d) & 1u) {   // (landed through L2 by a peer: read around L1)
+    const double2 *q = reinterpret_cast<const double2 *>(landing + g);
+    const double2 a = __ldcg(q), b = __ldcg(q + 1);
+    arr[nlocal + g] = make_double4(a.x, a.y, b.x, b.y);
+  }
+}
+
+// after borders(): does every rank's ghost set fit its landing buffer, and where does each of my directions land?
+static int put_plan_epoch(b200md_ctx *c)
+{
+  c->put.epoch_ok = false;
+  if (c->nranks == 1 || !c->put.enabled || !c->put.imported) return B200MD_OK;
+  TRY(dev_ensure(c, c->allcounts, (size_t) 32 * (c->nranks + 1)));
+  int mine[32] = {0};
+  for (int d = 0; d < NDIR; d++) mine[d] = c->hp.goff[d];
+  mine[31] = (size_t) c->nghost <= c->put.cap ? 1 : 0;
+  int *mine_d = c->allcounts.p, *all_d = c->allcounts.p + 32;
+  CU(cudaMemcpyAsync(mine_d, mine, 32 * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+  NC(g_nccl.AllGather(mine_d, all_d, 32, ncclInt, (ncclComm_t) c->nccl, c->stream));
+  std::vector<int> all((size_t) 32 * c->nranks);
+  CU(cudaMemcpyAsync(all.data(), all_d, all.size() * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  bool ok = true;
+  for (int r = 0; r < c->nranks; r++) ok = ok && all[(size_t) 32 * r + 31] == 1;
+  for (int d = 0; d < NDIR; d++) {
+    const int peer = c->peer_send[d];
+    c->put.peer_goff[d] = (peer >= 0 && peer != c->rank) ? all[(size_t) 32 * peer + d] : 0;
+    if (peer >= 0 && peer != c->rank && !c->put.peer_base[peer]) ok = false;
+  }
+  c->put.epoch_ok = ok;
+  return B200MD_OK;
+}
+
+static int halo_forward_put(b200md_ctx *c, double4 *arr)
+{
+  cudaStream_t st = c->hstream ? c->hstream : c->stream;
+  const unsigned seq = ++c->put.seq, par = seq & 1u;
+  PutPlan pp = {};
+  pp.seq = seq;
+  unsigned wait_mask = 0;
+  for (int d = 0; d < NDIR; d++) {
+    const int ps = c->peer_send[d], pr = c->peer_recv[d];
+    if (ps >= 0 && ps != c->rank && c->sendcount[d] > 0) {
+      char *pb = (char *) c->put.peer_base[ps];
+      pp.dst[d] = (double4 *) (pb + PUT_FLAG_BYTES) + (size_t) par * c->put.peer_cap[ps] + c->put.peer_goff[d];
+      pp.flag[d] = (int *) pb + par * 32 + d;
+    }
+    if (pr >= 0 && pr != c->rank && c->recvcount[d] > 0) wait_mask |= 1u << d;
+  }
+  KProf kp(c, KC_HALO);
+  const int blocks = cdiv(c->nsend > 0 ? c->nsend : 1, 256);
+  k_halo_pack_put<<<blocks, 256, 0, st>>>(arr, c->send_idx.p, c->send_dir.p, c->nsend, c->nlocal, c->hp, pp, c->put.done_d);
+  LAUNCH_CHECK();
+  if (wait_mask) {
+    k_halo_wait<<<1, 32, 0, st>>>((const int *) c->put.base + par * 32, wait_mask, seq, c->put.done_d + 1);
+    LAUNCH_CHECK();
+    const double4 *landing = (const double4 *) (c->put.base + PUT_FLAG_BYTES) + (size_t) par * c->put.cap;
+    k_halo_unpack<<<cdiv(c->nghost, 256), 256, 0, st>>>(arr, landing, c->nlocal, c->nghost, c->hp, wait_mask);
+    LAUNCH_CHECK();
+  }
+  return B200MD_OK;
+}
+
+// a wait of the put halo gave up (read where the step synchronises anyway: at every rebuild)
+int halo_put_check(b200md_ctx *c)
+{
+  if (!c->put.done_d || !c->put.epoch_ok) return B200MD_OK;
+  int t = 0;
+  CU(cudaMemcpyAsync(&t, c->put.done_d + 1, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  if (t) return b200md_fail(c, B200MD_ERR_CUDA, "halo put: a peer's records did not arrive within the wait limit");
   return B200MD_OK;
 }
 
@@ -487,6 +641,7 @@ int comm_borders(b200md_ctx *c)
 // and passes w through (type for the position array, fp for the EAM {x,y,z,fp} array)
 int halo_forward_vec4(b200md_ctx *c, double4 *arr)
 {
+  if (c->put.epoch_ok) return halo_forward_put(c, arr);
   if (c->nsend > 0) {
     KProf kp(c, KC_HALO);
     k_halo_pack_pos<0><<<cdiv(c->nsend, 256), 256, 0, c->hstream ? c->hstream : c->stream>>>(arr, c->tag.p, c->send_idx.p, c->send_dir.p, c->nsend,
@@ -633,3 +788,44 @@ int comm_exchange(b200md_ctx *c)
   c->nmigrated += st;
   return B200MD_OK;
 }
+
+// ---- halo put: the landing buffer of this rank and the mappings of the peers' -------------------------------------
+extern "C" int b200md_halo_put_export(b200md_ctx *c, int64_t cap_records, void *handle_out)
+{
+  if (!c) return b200md_fail(nullptr, B200MD_ERR_ARG, "NULL context");
+  if (!handle_out || cap_records <= 0) return b200md_fail(c, B200MD_ERR_ARG, "halo_put_export: cap_records > 0 and handle_out[64] are required");
+  CU(cudaSetDevice(c->device));
+  if (c->put.base) return b200md_fail(c, B200MD_ERR_ARG, "halo_put_export: already exported");
+  const size_t bytes = PUT_FLAG_BYTES + (size_t) 2 * (size_t) cap_records * sizeof(double4);
+  CU(cudaMalloc((void **) &c->put.base, bytes));
+  CU(cudaMemset(c->put.base, 0, PUT_FLAG_BYTES));
+  CU(cudaMalloc((void **) &c->put.done_d, 2 * sizeof(int)));
+  CU(cudaMemset(c->put.done_d, 0, 2 * sizeof(int)));
+  c->put.cap = (size_t) cap_records;
+  c->bytes_held += (double) bytes;
+  cudaIpcMemHandle_t h;
+  CU(cudaIpcGetMemHandle(&h, c->put.base));
+  static_assert(sizeof(h) == B200MD_IPC_HANDLE_BYTES, "cudaIpcMemHandle_t size");
+  memcpy(handle_out, &h, sizeof(h));
+  return B200MD_OK;
+}
+
+extern "C" int b200md_halo_put_import(b200md_ctx *c, int nranks, const void *handles, const int64_t *caps)
+{
+  if (!c) return b200md_fail(nullptr, B200MD_ERR_ARG, "NULL context");
+  if (nranks != c->nranks || nranks > 64 || !handles || !caps) return b200md_fail(c, B200MD_ERR_ARG, "halo_put_import: handles[nranks][64] and caps[nranks] of this communicator's ranks (at most 64)");
+  if (!c->put.base) return b200md_fail(c, B200MD_ERR_ARG, "halo_put_import before halo_put_export");
+  CU(cudaSetDevice(c->device));
+  for (int r = 0; r < nranks; r++) {   // every other rank of the box (at most 7): any of them may become a neighbor
+    c->put.peer_cap[r] = (size_t) caps[r];
+    if (r == c->rank || c->put.peer_base[r]) continue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, (const char *) handles + (size_t) r * B200MD_IPC_HANDLE_BYTES, sizeof(h));
+    CU(cudaIpcOpenMemHandle(&c->put.peer_base[r], h, cudaIpcMemLazyEnablePeerAccess));
+  }
+  c->put.imported = true;
+  return B200MD_OK;
+}
+
+// halos that went through the put path so far (0: every halo used NCCL)
+extern "C" int64_t b200md_halo_put_count(const b200md_ctx *c) { return c ? (int64_t) c->put.seq : 0; }

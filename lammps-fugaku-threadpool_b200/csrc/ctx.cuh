@@ -212,6 +212,22 @@ struct b200md_ctx {
   DevBuf<signed char> send_dir;
   DevBuf<double4> sendbuf4, recvbuf4;
   DevBuf<double> sendbuf1;
+  // per-step halo as a fused pack-and-put over peer memory (comm.cu, "halo_put"): the pack kernel writes every remote
+  // record straight into the receiver's landing buffer over NVLink and raises the receiver's per-direction flag; the
+  // receiver waits on its own flags and copies the records into the ghost slots.  One cudaMalloc per rank, exported by
+  // cudaIpcGetMemHandle: [2][32] int flags (256 B), then two landing buffers (by halo parity) of `cap` records.
+  struct PutState {
+    int enabled = 0;              // "halo_put" (b200md_tune)
+    bool imported = false;        // the peers' allocations are mapped
+    bool epoch_ok = false;        // agreed by all ranks at the last borders(): every rank's ghosts fit its landing buffer
+    size_t cap = 0;               // records per landing buffer
+    char *base = nullptr;         // my allocation
+    void *peer_base[64] = {};     // the peers' (mapped), indexed by rank
+    size_t peer_cap[64] = {};
+    unsigned seq = 0;             // halos put so far (the same number on every rank)
+    int *done_d = nullptr;        // [2]: blocks of the pack kernel that finished; a wait that timed out
+    int peer_goff[NDIR] = {};     // ghost offset of direction d on the rank that receives my direction d
+  } put;
 
   // reductions / flags
   DevBuf<double> partials;  // [nblocks][8]

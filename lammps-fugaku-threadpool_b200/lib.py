@@ -12,6 +12,7 @@ from .build import LIB, build
 OK = 0
 ERR_NAMES = {1: "NONFINITE", 2: "NEIGH_OVERFLOW", 3: "LOST_ATOMS", 4: "CUDA", 5: "ARG", 6: "DOMAIN"}
 NCCL_ID_BYTES = 128
+IPC_HANDLE_BYTES = 64   # B200MD_IPC_HANDLE_BYTES
 
 _vp, _i, _d, _i64 = C.c_void_p, C.c_int, C.c_double, C.c_int64
 
@@ -31,6 +32,9 @@ PROTOTYPES = {
     "b200md_download_atoms": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "b200md_download_atoms_by_tag": (_i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp]),
     "b200md_download_all": (_i, [_vp, _vp, _vp]),
+    "b200md_halo_put_export": (_i, [_vp, C.c_int64, _vp]),
+    "b200md_halo_put_import": (_i, [_vp, _i, _vp, _vp]),
+    "b200md_halo_put_count": (C.c_int64, [_vp]),
     "b200md_lj_init": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "b200md_eam_init": (_i, [_vp, _i, _i, _i, _d, _d, _d, _d, _i, _vp, _i, _vp, _i, _vp, _vp, _vp, _vp]),
     "b200md_eam_init_funcfl": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp]),

@@ -459,6 +459,19 @@ class B200MD:
             x, v, f, t, tag, img = x[o], v[o], f[o], t[o], tag[o], img[o]
         return dict(x=x, v=v, f=f, type=t, tag=tag, image=img)
 
+    def halo_put(self, cap_records: int, allgather) -> None:
+        """Switch the per-step halo to the fused pack-and-put kernel over peer memory (b200md_halo_put_export / _import +
+        b200md_tune "halo_put"): `allgather(bytes) -> [bytes of rank 0, rank 1, ...]` is the host's collective
+        (torch.distributed.all_gather_object, MPI_Allgather); cap_records = ghost records a landing buffer holds."""
+        h = np.zeros(lib.IPC_HANDLE_BYTES, dtype=np.uint8)
+        self.ctx.call("b200md_halo_put_export", int(cap_records), lib.ptr(h))
+        blobs = allgather(h.tobytes() + np.int64(cap_records).tobytes())
+        n = lib.IPC_HANDLE_BYTES
+        handles = np.frombuffer(b"".join(b[:n] for b in blobs), dtype=np.uint8).copy()
+        caps = np.array([np.frombuffer(b[n:n + 8], dtype=np.int64)[0] for b in blobs], dtype=np.int64)
+        self.ctx.call("b200md_halo_put_import", len(blobs), lib.ptr(handles), lib.ptr(caps))
+        self.tune("halo_put", 1)
+
     def gather_in_order(self, host_tag) -> dict:
         """owned atoms in the order of the caller's tag array (b200md_download_atoms_by_tag: the permutation runs on
         the device) -- what VerletB200 writes back into Atom::x / v / f / image"""

@@ -41,6 +41,12 @@ def _worker(rank, world, grid, kind, cells, steps, port, outdir, backend):
         md = bench.make_system(pkg, kind, rank, world, rank, ids[0], grid)
         md.box([0, 0, 0], box)
         md.create_atoms(x, v, np.ones(len(x), dtype=np.int32), tag, natoms_total=natoms)
+        if os.environ.get("B200MD_TEST_HALO_PUT"):   # per-step halo as the fused pack-and-put kernel over peer memory
+            def allgather(blob):
+                got = [None] * world
+                dist.all_gather_object(got, blob)
+                return got
+            md.halo_put(int(os.environ["B200MD_TEST_HALO_PUT"]), allgather)
         md.setup()
         t0 = md.thermo_log[-1]
         numneigh, _ = md.neighbor_list()
@@ -51,7 +57,7 @@ def _worker(rank, world, grid, kind, cells, steps, port, outdir, backend):
         st = md.neigh_stats()
         out.update(thermo0=np.array([t0["pe"], t0["ke"], t0["press"]]), thermo1=np.array([t1["pe"], t1["ke"], t1["press"]]),
                    x1=g["x"], v1=g["v"], f1=g["f"], tag1=g["tag"], builds=np.array([st["builds"], st["dangerous"]]),
-                   nlocal1=np.array([md.nlocal]))
+                   nlocal1=np.array([md.nlocal]), puts=np.array([int(md.ctx.L.b200md_halo_put_count(md.ctx.h))]))
         md.close()
     np.savez(Path(outdir) / f"rank{rank}.npz", **out)
     dist.barrier()

@@ -261,6 +261,20 @@ class _AllSum:
         return tot
 
 
+class _AllGatherBytes:
+    """the host-side all-gather of the halo-put handles, ranks being threads"""
+    def __init__(self, n):
+        self.n, self.bar, self.parts, self.lock = n, threading.Barrier(n, timeout=300), {}, threading.Lock()
+
+    def __call__(self, rank, blob):
+        with self.lock:
+            self.parts[rank] = blob
+        self.bar.wait()
+        out = [self.parts[r] for r in range(self.n)]
+        self.bar.wait()
+        return out
+
+
 def run_decomposed_emu(pkg, world, grid, kind, cells, steps, host_steps=0, configure=None, tune=None):
     """tests/multirank_util._worker with threads for ranks; optionally `host_steps` more steps through
     b200md_step_host (the bench's e2e leg: atoms migrate between ranks at its rebuilds)"""
@@ -289,7 +303,7 @@ def run_decomposed_emu(pkg, world, grid, kind, cells, steps, host_steps=0, confi
             g = md.gather()
             st = md.neigh_stats()
             out.update(thermo1=np.array([t1["pe"], t1["ke"], t1["press"]]), x1=g["x"], tag1=g["tag"], builds=st["builds"],
-                       nlocal1=md.nlocal, temp0=t0["temp"], temp1=t1["temp"])
+                       nlocal1=md.nlocal, temp0=t0["temp"], temp1=t1["temp"], puts=int(md.ctx.L.b200md_halo_put_count(md.ctx.h)))
             if host_steps:
                 n = md.nlocal
                 cap = n + n // 8 + 64
@@ -381,6 +395,23 @@ def test_emu_decomposed_overlap_equals_plain(emu, kind, world, grid, cells, step
     for ra, rb in zip(a, b):
         assert np.array_equal(ra["tag1"], rb["tag1"]) and np.array_equal(ra["x1"], rb["x1"])
         assert np.array_equal(ra["thermo1"], rb["thermo1"]) and ra["builds"] == rb["builds"]
+
+
+@pytest.mark.parametrize("kind,world,grid,cells,steps,overlap", [("lj", 4, (2, 2, 1), 6, 45, 1), ("eam", 8, (2, 2, 2), 5, 30, 1),
+                                                                   ("eam", 2, (2, 1, 1), 6, 30, 0)])
+def test_emu_halo_put_equals_nccl_halo(emu, kind, world, grid, cells, steps, overlap):
+    """the per-step halo as the fused pack-and-put kernel over peer memory (flags, two landing buffers by parity, wait +
+    unpack on the receiver) against the NCCL send/recv halo: same trajectory, bit for bit, through rebuilds and
+    migration; a landing buffer too small for the ghosts makes every rank fall back to NCCL together"""
+    a = run_decomposed_emu(emu, world, grid, kind, cells, steps, tune={"overlap": overlap})
+    for cap in (200000, 16):
+        gather = _AllGatherBytes(world)
+        b = run_decomposed_emu(emu, world, grid, kind, cells, steps, tune={"overlap": overlap},
+                               configure=lambda md: md.halo_put(cap, lambda blob: gather(md.rank, blob)))
+        for ra, rb in zip(a, b):
+            assert np.array_equal(ra["tag1"], rb["tag1"]) and np.array_equal(ra["x1"], rb["x1"])
+            assert np.array_equal(ra["thermo1"], rb["thermo1"]) and ra["builds"] == rb["builds"]
+            assert ra["puts"] == 0 and (rb["puts"] >= steps // 2 if cap > 16 else rb["puts"] == 0)
 
 
 @pytest.mark.parametrize("kind,world,grid", [("lj", 2, (2, 1, 1)), ("eam", 4, (2, 2, 1))])

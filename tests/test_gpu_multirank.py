@@ -72,3 +72,25 @@ def test_decomposed_equals_single_gpu(pkg, kind, world, grid, cells, steps):
     dx -= box * np.round(dx / box)
     assert np.abs(dx).max() < 1e-6
     assert sum(int(r["nlocal1"][0]) for r in res) == len(tag)
+
+
+@pytest.mark.parametrize("kind,world,grid,cells,steps", [
+    ("lj", 2, (2, 1, 1), 8, 60),
+    ("eam", 2, (2, 1, 1), 8, 40),
+    ("eam", 4, (2, 2, 1), 8, 40),
+    ("lj", 8, (2, 2, 2), 6, 60),
+])
+def test_halo_put_equals_nccl_halo(pkg, kind, world, grid, cells, steps, monkeypatch):
+    """the per-step halo as ONE fused pack-and-put kernel over peer memory (cudaIpc mappings of the peers' landing
+    buffers, per-direction flags, wait + unpack on the receiver) against pack + ncclSend/ncclRecv: bit-identical
+    trajectories through rebuilds and migration, and the put path really ran"""
+    if _ngpu() < world:
+        pytest.skip(f"needs {world} GPUs")
+    monkeypatch.delenv("B200MD_TEST_HALO_PUT", raising=False)
+    a = run_decomposed(world, grid, kind, cells, steps, backend="nccl", port=29671 + world)
+    monkeypatch.setenv("B200MD_TEST_HALO_PUT", "400000")
+    b = run_decomposed(world, grid, kind, cells, steps, backend="nccl", port=29681 + world)
+    for ra, rb in zip(a, b):
+        assert int(ra["puts"][0]) == 0 and int(rb["puts"][0]) >= steps // 2
+        assert np.array_equal(ra["tag1"], rb["tag1"]) and np.array_equal(ra["x1"], rb["x1"]) and np.array_equal(ra["f1"], rb["f1"])
+        assert np.array_equal(ra["thermo1"], rb["thermo1"]) and np.array_equal(ra["builds"], rb["builds"])
