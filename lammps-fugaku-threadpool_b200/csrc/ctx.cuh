@@ -269,6 +269,7 @@ struct b200md_ctx {
   int build_gb_user = 0;      // test knob: bins of an x-row per block in the list build (0 = by bin population)
   int seg_cap_user = 0;       // test knob: initial staging capacity of the list build (records)
   int build_threads = 128;    // threads per block of the list build (128 or 256; the bins per block follow)
+  bool xhold_by_permute = false;   // the rebuild's permutation kernel wrote xhold (neigh_build_lists then does not copy it)
   int build_bond_general = 0; // test knob: bonded build with the closest-image choice (BONDED 1) even where a tag is unique inside the cutoff
   int build_fp64 = 0;         // test knob: force the all-FP64 build kernel (otherwise only huge boxes with tiny cutoffs use it)
   int debug_timing = 0;       // per-phase wall times of every rebuild on stderr (B200MD_DEBUG_TIMING, read at create)

@@ -217,12 +217,14 @@ __global__ void k_permute_owned(const int *__restrict__ perm, int n, const doubl
                                 double4 *__restrict__ pos_o, const double *__restrict__ vx, const double *__restrict__ vy,
                                 const double *__restrict__ vz, double *__restrict__ vx_o, double *__restrict__ vy_o,
                                 double *__restrict__ vz_o, const int *__restrict__ tag, int *__restrict__ tag_o,
-                                const int *__restrict__ image, int *__restrict__ image_o)
+                                const int *__restrict__ image, int *__restrict__ image_o, double4 *__restrict__ xhold)
 {
   int s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= n) return;
   int i = perm[s];
-  pos_o[s] = pos[i];
+  const double4 p = pos[i];
+  pos_o[s] = p;
+  if (xhold) xhold[s] = p;   // Neighbor::build's xhold = x of the owned atoms at this build (src/neighbor.cpp:2412-2430)
   vx_o[s] = vx[i];
   vy_o[s] = vy[i];
   vz_o[s] = vz[i];
@@ -400,19 +402,12 @@ __global__ void k_rec_fill(const double4 *__restrict__ pos, const int *__restric
   rec[rec_word(d, 2, lg, nf)] = (float) (p.z - oz);
   reci[rec_word(d, 3, lg, nf)] = j | ((pos_type(p) - 1) << 28);
   if (nf == 5) reci[rec_word(d, 4, lg, nf)] = tag[j];  // bonded / molecular systems: the candidate's tag, for the special-partner test
-}
-
-// the padding records at the end of every bin: never accepted
-__global__ void k_rec_pad(const int *__restrict__ bin_start, const int *__restrict__ pbin_start, int mbins, float *__restrict__ rec,
-                          int lg, int nf)
-{
-  const int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= mbins) return;
-  int *reci = reinterpret_cast<int *>(rec);
-  for (int d = pbin_start[b] + bin_start[b + 1] - bin_start[b]; d < pbin_start[b + 1]; d++) {
-    rec[rec_word(d, 0, lg, nf)] = rec[rec_word(d, 1, lg, nf)] = rec[rec_word(d, 2, lg, nf)] = SEG_FAR;
-    reci[rec_word(d, 3, lg, nf)] = BR_JMASK;
-    if (nf == 5) reci[rec_word(d, 4, lg, nf)] = 0;
+  if (k == bin_start[b + 1] - 1) {   // the bin's last record also writes its padding: never accepted
+    for (int e = d + 1; e < pbin_start[b + 1]; e++) {
+      rec[rec_word(e, 0, lg, nf)] = rec[rec_word(e, 1, lg, nf)] = rec[rec_word(e, 2, lg, nf)] = SEG_FAR;
+      reci[rec_word(e, 3, lg, nf)] = BR_JMASK;
+      if (nf == 5) reci[rec_word(e, 4, lg, nf)] = 0;
+    }
   }
 }
 
@@ -891,10 +886,12 @@ int neigh_rebuild(b200md_ctx *c)
   TRY(dev_ensure(c, c->tag_tmp, c->tag.n, false, false));
   TRY(dev_ensure(c, c->image_tmp, c->image.n, false, false));
   for (int k = 0; k < 3; k++) TRY(dev_ensure(c, c->v_tmp[k], c->v[k].n, false, false));
+  if (c->dist_check) TRY(dev_ensure(c, c->xhold, (size_t) n));
   k_permute_owned<<<cdiv(n, 256), 256, 0, c->stream>>>(c->perm.p, n, c->pos.p, c->pos_tmp.p, c->v[0].p, c->v[1].p, c->v[2].p,
                                                         c->v_tmp[0].p, c->v_tmp[1].p, c->v_tmp[2].p, c->tag.p, c->tag_tmp.p,
-                                                        c->image.p, c->image_tmp.p);
+                                                        c->image.p, c->image_tmp.p, c->dist_check ? c->xhold.p : nullptr);
   LAUNCH_CHECK();
+  c->xhold_by_permute = c->dist_check != 0;
   std::swap(c->pos, c->pos_tmp);
   std::swap(c->tag, c->tag_tmp);
   std::swap(c->image, c->image_tmp);
@@ -984,7 +981,7 @@ int neigh_build_lists(b200md_ctx *c)
       if (c->seg_cap == 0 && c->seg_cap_user > 0) c->seg_cap = (c->seg_cap_user + 3) & ~3;   // test knob: start too small, exercise the retry
       // (every staged bin is padded to a multiple of vw records: + (vw - 1) / 2 on average)
       const int vw = (per_bin >= 8.0 && !(c->special.on && c->bonds.maxb == 0)) ? 4 : 2;
-      // the candidate records: FP32, groups of vw, every bin padded to vw (k_pad_count -> scan -> k_rec_fill + k_rec_pad)
+      // the candidate records: FP32, groups of vw, every bin padded to vw (k_pad_count -> scan -> k_rec_fill)
       const int nf = (bonded || special) ? 5 : 4, lg = vw == 4 ? 2 : 1;
       {
         const int mb = g.mbins;
@@ -998,8 +995,6 @@ int neigh_build_lists(b200md_ctx *c)
         k_rec_fill<<<cdiv(nall, 256), 256, 0, c->stream>>>(c->pos.p, c->cell_list.p, c->atom_bin.p, c->bin_start.p, c->pbin_start.p, nall,
                                                           g.lo[0] - BIN_MARGIN / g.inv[0], g.lo[1] - BIN_MARGIN / g.inv[1],
                                                           g.lo[2] - BIN_MARGIN / g.inv[2], c->rec.p, lg, nf, c->tag.p);
-        LAUNCH_CHECK();
-        k_rec_pad<<<cdiv(mb, 256), 256, 0, c->stream>>>(c->bin_start.p, c->pbin_start.p, mb, c->rec.p, lg, nf);
         LAUNCH_CHECK();
       }
       const RecArrays rec = {c->rec.p, c->pbin_start.p};
@@ -1100,10 +1095,11 @@ int neigh_build_lists(b200md_ctx *c)
   if (c->flags_h[1] > c->maxneigh - 4) return b200md_fail(c, B200MD_ERR_NEIGH_OVERFLOW, "Neighbor list overflow");
 
   ph.mark("build");
-  if (c->dist_check) {
+  if (c->dist_check && !c->xhold_by_permute) {   // (the rebuild's permutation already wrote it; this is the host-ghost entry)
     TRY(dev_ensure(c, c->xhold, (size_t) n));
     CU(cudaMemcpyAsync(c->xhold.p, c->pos.p, (size_t) n * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
   }
+  c->xhold_by_permute = false;
   ph.mark("xhold");
   c->ago = 0;
   c->nbuilds++;
