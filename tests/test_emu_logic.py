@@ -297,7 +297,8 @@ def run_decomposed_emu(pkg, world, grid, kind, cells, steps, host_steps=0, confi
             md.setup()
             t0 = md.thermo_log[-1]
             numneigh, _ = md.neighbor_list()
-            out = dict(box=np.array(box), nneigh0=int(numneigh.sum()), thermo0=np.array([t0["pe"], t0["ke"], t0["press"]]))
+            out = dict(box=np.array(box), nneigh0=int(numneigh.sum()), thermo0=np.array([t0["pe"], t0["ke"], t0["press"]]),
+                       nghost0=md.nghost)
             md.run(steps)
             t1 = md.thermo_log[-1]
             g = md.gather()
@@ -412,6 +413,18 @@ def test_emu_halo_put_equals_nccl_halo(emu, kind, world, grid, cells, steps, ove
             assert np.array_equal(ra["tag1"], rb["tag1"]) and np.array_equal(ra["x1"], rb["x1"])
             assert np.array_equal(ra["thermo1"], rb["thermo1"]) and ra["builds"] == rb["builds"]
             assert ra["puts"] == 0 and (rb["puts"] >= steps // 2 if cap > 16 else rb["puts"] == 0)
+    if kind == "eam" and world == 8:
+        # landing buffers that hold the ghosts of some list epochs and not of others (the ghost count moves by a few
+        # atoms from rebuild to rebuild): the ranks switch between the put halo and NCCL together, parity carries on
+        cap = int(np.median([r["nghost0"] for r in a]))
+        gather = _AllGatherBytes(world)
+        b = run_decomposed_emu(emu, world, grid, kind, cells, steps, tune={"overlap": overlap},
+                               configure=lambda md: md.halo_put(cap, lambda blob: gather(md.rank, blob)))
+        for ra, rb in zip(a, b):
+            assert np.array_equal(ra["tag1"], rb["tag1"]) and np.array_equal(ra["x1"], rb["x1"])
+            assert np.array_equal(ra["thermo1"], rb["thermo1"]) and ra["builds"] == rb["builds"]
+        assert len({r["puts"] for r in b}) == 1   # every rank served the same halos by put
+        print("put halos with a tight landing buffer:", b[0]["puts"], "of", 2 * steps)
 
 
 @pytest.mark.parametrize("kind,world,grid", [("lj", 2, (2, 1, 1)), ("eam", 4, (2, 2, 1))])
