@@ -198,12 +198,35 @@ def time_resident(torch, dist, md, steps, warmup, device, nranks):
     return float(ms.item()), int(launches)
 
 
+def numa_local_affinity(device):
+    """Pin this process to the CPUs next to its GPU (nvmlDeviceGetCpuAffinity) so that the pinned host buffers of the e2e
+    leg are allocated on that NUMA node and the copies do not cross the socket link -- several ranks on one host otherwise
+    share whatever node the scheduler put them on.  Returns (old affinity, new affinity) or None if it cannot be done."""
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(int(device))
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        near = {64 * w + b for w, m in enumerate(words) for b in range(64) if (int(m) >> b) & 1}
+        old = os.sched_getaffinity(0)
+        new = near & old
+        if not new or new == old:
+            return None
+        os.sched_setaffinity(0, new)
+        return old, new
+    except Exception:  # noqa: BLE001  (no NVML, no permission, cgroup without those CPUs ...)
+        return None
+
+
 def time_host_buffers(torch, dist, md, steps, warmup, device, nranks):
     """The same steps through the host-buffer entry point (b200md_step_host): every step copies x, v from pinned
     host arrays to the device and x, v, f back -- what a Pair/Fix plugin under the stock host-resident Verlet
     loop pays (the reference GPU package's model).  Returns (ms for K steps, h2d bytes/step, d2h bytes/step)."""
     n = md.nlocal
     cap = n + n // 64 + 1024  # room for atoms that migrate in at a rebuild (several ranks)
+    aff = numa_local_affinity(device)
+    time_host_buffers.numa = None if aff is None else {"cpus_before": len(aff[0]), "cpus_near_gpu": len(aff[1])}
     hx = torch.empty((cap, 3), dtype=torch.float64).pin_memory()
     hv = torch.empty((cap, 3), dtype=torch.float64).pin_memory()
     hf = torch.empty((cap, 3), dtype=torch.float64).pin_memory()
@@ -233,6 +256,8 @@ def time_host_buffers(torch, dist, md, steps, warmup, device, nranks):
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
         dist.all_reduce(ms, op=dist.ReduceOp.SUM)
         ms[0] = mx[0]
+    if aff is not None:
+        os.sched_setaffinity(0, aff[0])   # the CPU legs that follow use every core again
     return float(ms[0].item()), int(ms[1].item()), int(ms[2].item())
 
 
@@ -366,7 +391,7 @@ def run_e2e(torch, dist, md, out, args, device, nranks):
     ems, bi, bo = time_host_buffers(torch, dist, md, k, 3, device, nranks)
     out["e2e"] = dict(value=out["natoms"] * k / (ems * 1e-3) / 1e6, unit="Matom-steps/s", h2d_bytes_per_step=bi,
                       d2h_bytes_per_step=bo, steps=k, api="b200md_step_host (pinned host x,v in; x,v,f out every step)",
-                      form="three-stream pipeline")
+                      form="three-stream pipeline", numa=getattr(time_host_buffers, "numa", None))
 
 
 class Watchdog:
